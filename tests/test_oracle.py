@@ -1,0 +1,223 @@
+"""CPU tests that pin the oracle (oracle/jumbo_mae_oracle.py).
+
+The reference ships no tests, so these are hand-derivable
+known-answer cases, one named test per assumed third-party default, plus a check
+against the committed fixture tests/golden/tiny_step.npz.
+"""
+import math
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import jumbo_mae_oracle as O
+
+GOLDEN = os.path.join(os.path.dirname(__file__), "golden", "tiny_step.npz")
+
+
+def test_flops_and_param_counts_match_survey():
+    fwd, step = O.flops_per_image(O.vit_b16())
+    assert abs(fwd / 1e9 - 20.491) < 1e-3 and abs(step / 1e9 - 61.417) < 1e-3
+    fwd, step = O.flops_per_image(O.vit_l16())
+    assert abs(fwd / 1e9 - 45.001) < 1e-3 and abs(step / 1e9 - 134.925) < 1e-3
+    fwd, step = O.flops_per_image(O.vit_h14())
+    assert abs(fwd / 1e9 - 104.509) < 1e-3 and abs(step / 1e9 - 313.430) < 1e-3
+
+
+def test_masking_known_answer():
+    # src/utils_mae.py:90-96 with a hand-checkable noise vector
+    noise = np.array([0.9, 0.1, 0.5, 0.3, 0.7, 0.2, 0.8, 0.4], dtype=np.float32)
+    ids_shuffle, ids_restore, mask = O.masking_from_noise(noise, 2)
+    assert ids_shuffle.tolist() == [1, 5, 3, 7, 2, 4, 6, 0]
+    assert ids_restore.tolist() == [7, 0, 4, 2, 5, 1, 6, 3]
+    assert mask.tolist() == [1, 0, 1, 1, 1, 0, 1, 1]
+    assert ids_shuffle.dtype == np.int32 and ids_restore.dtype == np.int32
+
+
+def test_masking_is_stable_on_ties():
+    noise = np.array([0.5, 0.25, 0.5, 0.25, 0.5], dtype=np.float32)
+    ids_shuffle, ids_restore, _ = O.masking_from_noise(noise, 2)
+    assert ids_shuffle.tolist() == [1, 3, 0, 2, 4]          # equal keys keep index order
+    assert ids_restore[ids_shuffle].tolist() == [0, 1, 2, 3, 4]
+
+
+def test_random_masking_shapes_and_gather():
+    x = torch.arange(2 * 8 * 3, dtype=torch.float32).reshape(2, 8, 3)
+    noise = np.array([0.9, 0.1, 0.5, 0.3, 0.7, 0.2, 0.8, 0.4], dtype=np.float32)
+    kept, mask, ids_restore = O.random_masking(x, noise, 2)
+    assert kept.shape == (2, 2, 3) and mask.shape == (2, 8) and ids_restore.shape == (8,)
+    assert torch.equal(kept, x[:, [1, 5]])
+    assert torch.equal(mask[0], mask[1])                    # ONE permutation per call
+    assert mask.sum().item() == 2 * 6
+
+
+def test_extract_merge_patches_roundtrip():
+    x = torch.randn(2, 32, 32, 3)
+    p = O.extract_patches(x, 8)
+    assert p.shape == (2, 16, 192)
+    assert torch.equal(O.merge_patches(p, 8), x)
+    # (ph, pw, c) order: element [0, patch(1,2), (3,4,c=1)] is pixel (8+3, 16+4, 1)
+    assert p[0, 1 * 4 + 2, (3 * 8 + 4) * 3 + 1] == x[0, 11, 20, 1]
+
+
+def test_patch_mse_all_ones_mask_is_plain_mse():
+    o, t = torch.randn(3, 16, 12), torch.randn(3, 16, 12)
+    assert torch.allclose(O.patch_mse_loss(o, t), ((o - t) ** 2).mean(), atol=1e-6)
+    mask = torch.zeros(3, 16)
+    mask[:, ::4] = 1
+    want = ((o - t) ** 2).mean(-1)[:, ::4].mean()
+    assert torch.allclose(O.patch_mse_loss(o, t, mask), want, atol=1e-6)
+
+
+def test_sincos_known_values():
+    e = O.fixed_sincos2d_embeddings(3, 4, 8)
+    assert e.shape == (3, 4, 8)
+    f = [1.0, 1.0 / 10000.0]                                # linspace(0,1,2) includes the endpoint
+    a, b = 2, 3                                             # first axis -> last two groups
+    want = [math.sin(b * f[0]), math.sin(b * f[1]), math.cos(b * f[0]), math.cos(b * f[1]),
+            math.sin(a * f[0]), math.sin(a * f[1]), math.cos(a * f[0]), math.cos(a * f[1])]
+    assert np.allclose(e[a, b].numpy(), want, atol=1e-6)
+
+
+def test_layernorm_default_eps_and_biased_variance():
+    x = torch.tensor([[1.0, 2.0, 3.0, 6.0]])
+    y = O.layer_norm(x, torch.ones(4), torch.zeros(4))
+    var = ((x - 3.0) ** 2).mean()                           # biased
+    assert torch.allclose(y, (x - 3.0) / torch.sqrt(var + 1e-6), atol=1e-6)
+    assert torch.allclose(y, torch.nn.functional.layer_norm(x, (4,), eps=1e-6), atol=1e-6)
+
+
+def test_gelu_is_tanh_approximation():
+    x = torch.linspace(-4, 4, 33)
+    assert torch.allclose(O.gelu_tanh(x), torch.nn.functional.gelu(x, approximate="tanh"), atol=1e-6)
+    assert not torch.allclose(O.gelu_tanh(x), torch.nn.functional.gelu(x), atol=1e-5)
+
+
+def test_attention_q_scale_after_bias():
+    torch.manual_seed(0)
+    d, h = 8, 2
+    p = {n: {"kernel": torch.randn(d, h, d // h), "bias": torch.randn(h, d // h)} for n in ("wq", "wk", "wv")}
+    p["wo"] = {"kernel": torch.randn(h, d // h, d), "bias": torch.randn(d)}
+    x = torch.randn(1, 5, d)
+    y = O.attention(x, p, h)
+    q = (x @ p["wq"]["kernel"].reshape(d, d) + p["wq"]["bias"].reshape(d)) / math.sqrt(d // h)
+    k = x @ p["wk"]["kernel"].reshape(d, d) + p["wk"]["bias"].reshape(d)
+    v = x @ p["wv"]["kernel"].reshape(d, d) + p["wv"]["bias"].reshape(d)
+    outs = []
+    for i in range(h):
+        s = slice(i * d // h, (i + 1) * d // h)
+        outs.append(torch.softmax(q[0, :, s] @ k[0, :, s].T, -1) @ v[0, :, s])
+    want = torch.cat(outs, -1) @ p["wo"]["kernel"].reshape(d, d) + p["wo"]["bias"]
+    assert torch.allclose(y[0], want, atol=1e-5)
+
+
+def test_jumbo_residual_is_post_norm():
+    cfg = O.tiny()
+    p = O.init_params(cfg, 0, randomize_all=True)["model"]
+    x = torch.randn(2, cfg.keep + 3, cfg.dim)
+    lp = p["layer_0"]
+    y = O.jumbo_layer(x, lp, p["jumbo_mlp"], cfg.heads, 3)
+    x1 = x + O.attention(O.layer_norm(x, lp["norm1"]["scale"], lp["norm1"]["bias"]), lp["attn"], cfg.heads)
+    c = O.layer_norm(x1[:, :3].reshape(2, -1), lp["norm3"]["scale"], lp["norm3"]["bias"])
+    want_c = c + O.feed_forward(c, p["jumbo_mlp"])
+    assert torch.allclose(y[:, :3].reshape(2, -1), want_c, atol=1e-5)
+
+
+def test_lr_schedule_endpoints():
+    cfg = O.vit_b16()
+    peak = 1.5e-4 * 4096 / 256
+    assert abs(O.lr_schedule(0, cfg) - 1e-6) < 1e-12
+    assert abs(O.lr_schedule(cfg.warmup_steps, cfg) - peak) < 1e-12
+    assert abs(O.lr_schedule(cfg.training_steps, cfg) - 1e-5) < 1e-12
+    assert abs(O.lr_schedule(cfg.training_steps + 100, cfg) - 1e-5) < 1e-12
+    half = cfg.warmup_steps // 2
+    assert abs(O.lr_schedule(half, cfg) - (1e-6 + (peak - 1e-6) * half / cfg.warmup_steps)) < 1e-9
+
+
+def test_adamw_first_step_and_decay_mask():
+    cfg = O.vit_b16()
+    p, g = torch.tensor([1.0, -2.0]), torch.tensor([0.5, -0.25])
+    z = torch.zeros(2)
+    new_p, m, v = O.adamw_leaf(p, g, z, z, 0, 1e-3, cfg, decay=False)
+    # t=1: m_hat = g, v_hat = g^2 -> u = g / (|g| + eps) = sign(g)
+    assert torch.allclose(new_p, p - 1e-3 * torch.sign(g), atol=1e-9)
+    assert torch.allclose(m, 0.1 * g) and torch.allclose(v, 0.05 * g * g)
+    new_p2, _, _ = O.adamw_leaf(p, g, z, z, 0, 1e-3, cfg, decay=True)
+    assert torch.allclose(new_p2, new_p - 1e-3 * 0.05 * p, atol=1e-9)
+
+
+def test_weight_decay_only_on_kernel_leaves():
+    cfg = O.tiny()
+    st = O.create_state(cfg, randomize_all=True)
+    images, noise = O.synthetic_batch(cfg, 2)
+    zero = O.tree_map(torch.zeros_like, st.params)
+    st2, _, _ = O.training_step(st, images, noise, grads_override=zero)
+    lr = O.lr_schedule(0, cfg)
+    for path, new in O.tree_leaves(st2.params):
+        old = dict(O.tree_leaves(st.params))[path]
+        if path[-1] == "kernel":
+            assert torch.allclose(new, old * (1 - lr * cfg.weight_decay), atol=1e-9)
+        else:
+            assert torch.equal(new, old)
+
+
+def test_grads_match_finite_differences_f64():
+    cfg = O.golden_tiny()
+    st = O.create_state(cfg, dtype=torch.float64, randomize_all=True)
+    images, noise = O.synthetic_batch(cfg, 2)
+    loss, grads = O.loss_and_grads(st.params, images, noise, cfg)
+    leaf = st.params["model"]["jumbo_mlp"]["w1"]["kernel"]
+    g = grads["model"]["jumbo_mlp"]["w1"]["kernel"]
+    eps = 1e-6
+    for idx in [(0, 0), (5, 7), (20, 100)]:
+        old = leaf[idx].item()
+        leaf[idx] = old + eps
+        lp = O.pretrain_forward(st.params, images, noise, cfg)["loss"].item()
+        leaf[idx] = old - eps
+        lm = O.pretrain_forward(st.params, images, noise, cfg)["loss"].item()
+        leaf[idx] = old
+        assert abs((lp - lm) / (2 * eps) - g[idx].item()) < 1e-6 * max(1.0, abs(g[idx].item()) * 1e3)
+
+
+@pytest.mark.parametrize("name,norm_pix", [("tiny", False), ("tiny_normpix", True)])
+def test_oracle_reproduces_committed_golden(name, norm_pix):
+    z = np.load(GOLDEN)
+    cfg = O.golden_tiny(norm_pix_loss=norm_pix)
+    state = O.create_state(cfg, seed=0, dtype=torch.float64, randomize_all=True)
+    # params come from the fixture, not from torch's RNG
+    for path, leaf in O.tree_leaves(state.params):
+        leaf.copy_(torch.from_numpy(z["tiny/params/" + "/".join(path)]))
+    images = torch.from_numpy(z[f"{name}/images"])
+    noise = z[f"{name}/noise"]
+    collect = {}
+    loss, grads = O.loss_and_grads(state.params, images, noise, cfg, collect)
+    assert abs(float(loss) - float(z[f"{name}/loss"])) < 1e-10
+    assert np.array_equal(collect["ids_restore"].numpy(), z[f"{name}/ids_restore"])
+    assert np.array_equal(collect["mask"].numpy().astype(np.float32), z[f"{name}/mask"])
+    for k in ("enc_in", "enc_out", "dec_in", "dec_out", "image_output"):
+        assert np.allclose(collect[k].detach().numpy(), z[f"{name}/act/{k}"], atol=1e-5)
+    for path, g in O.tree_leaves(grads):
+        s = z[f"{name}/grad_stats/" + "/".join(path)]
+        assert abs(g.sum().item() - s[0]) < 1e-9 + 1e-9 * abs(s[0])
+        assert abs(g.norm().item() - s[1]) < 1e-9 + 1e-9 * abs(s[1])
+    new_state, metrics, _ = O.training_step(state, images, noise)
+    assert abs(metrics["learning_rate"] - float(z[f"{name}/lr"])) < 1e-15
+    old = dict(O.tree_leaves(state.params))
+    for path, p in O.tree_leaves(new_state.params):
+        d = p - old[path]
+        s = z[f"{name}/delta_stats/" + "/".join(path)]
+        assert abs(d.norm().item() - s[1]) < 1e-12 + 1e-7 * abs(s[1])
+
+
+def test_f32_oracle_close_to_f64_golden():
+    z = np.load(GOLDEN)
+    cfg = O.golden_tiny()
+    state = O.create_state(cfg, seed=0, dtype=torch.float32, randomize_all=True)
+    for path, leaf in O.tree_leaves(state.params):
+        leaf.copy_(torch.from_numpy(z["tiny/params/" + "/".join(path)]).float())
+    loss, grads = O.loss_and_grads(state.params, torch.from_numpy(z["tiny/images"]), z["tiny/noise"], cfg)
+    assert abs(float(loss) - float(z["tiny/loss"])) < 1e-5
+    for path, g in O.tree_leaves(grads):
+        want = torch.from_numpy(z["tiny/grads/" + "/".join(path)])
+        assert (g - want).norm() <= 1e-4 * want.norm() + 1e-7
