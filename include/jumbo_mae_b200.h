@@ -1,0 +1,170 @@
+/*
+ * jumbo_mae_b200.h -- C ABI of the B200 (sm_100a) kernel library for the Jumbo-CLS
+ * MAE pre-training step of antofuller/jumbo_mae_tpu.
+ *
+ * The reference has no native code: every op below replaces what XLA executes for
+ * the cited Python lines (paths relative to the reference checkout).  A JAX host
+ * binds these through thin XLA-FFI handlers; the in-tree host
+ * (jumbo_mae_tpu_b200/) binds them with ctypes.
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer unless it says "host";
+ *   - `stream` is a cudaStream_t passed as void*; calls only enqueue work: no
+ *     allocation, no synchronisation, no host read-back;
+ *   - workspaces are caller-owned; jm_*_workspace() returns the bytes needed;
+ *   - return value 0 = success, non-zero = failure with a message available from
+ *     jm_last_error() (thread-local).  Nothing throws across this boundary;
+ *   - activations are row-major [rows, features]; "ld*" arguments are row strides
+ *     in ELEMENTS; bf16 is the raw 16-bit pattern (uint16_t).
+ */
+#ifndef JUMBO_MAE_B200_H_
+#define JUMBO_MAE_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef uint16_t jm_bf16;
+
+const char* jm_last_error(void);
+int jm_version(void);
+/* 1 if the current device is sm_100 (B200); the library refuses to run elsewhere. */
+int jm_device_ok(void);
+
+/* ---------------------------------------------------------------- masking
+ * random_masking, src/utils_mae.py:88-96, with the uniform noise as an input:
+ * ids_shuffle = stable ascending argsort(noise); ids_restore = argsort(ids_shuffle);
+ * mask_row[i] = 1 if ids_restore[i] >= keep else 0 (the reference's mask is this row
+ * broadcast over the batch: one permutation per call).  length <= 1024. */
+int jm_mask_sort(const float* noise, int length, int keep, int32_t* ids_shuffle, int32_t* ids_restore,
+                 float* mask_row, void* stream);
+
+/* index_sequence, src/utils_mae.py:84-85: out[b, i, :] = x[b, ids[i], :] (f32). */
+int jm_index_sequence(const float* x, const int32_t* ids, int batch, int length_in, int length_out, int dim,
+                      float* out, void* stream);
+
+/* ---------------------------------------------------------------- pixels
+ * PretrainModule pre-processing (src/pretraining.py:90-91) fused with
+ * extract_patches (src/utils_mae.py:67-73) and the token gather of random_masking:
+ * out[b*rows_per_image + row_off + i, e] = normalised pixel e of patch ids[i] of image b
+ * ((ph, pw, c) element order), bf16, zero in columns [P, ldo).  ids == NULL selects
+ * patches 0..n_sel-1.  Rows [0,row_off) of each image block are zero-filled. */
+int jm_patchify(const uint8_t* images, int batch, int image_size, int patch_size, const int32_t* ids, int n_sel,
+                int rows_per_image, int row_off, jm_bf16* out, long ldo, void* stream);
+
+/* extract_patches on the normalised image as f32 (reference signature; tests only). */
+int jm_extract_patches(const uint8_t* images, int batch, int image_size, int patch_size, float* out, void* stream);
+
+/* patch_mse_loss (src/utils_mae.py:51-64) fused with the target computation
+ * (src/pretraining.py:113-118).  pred is [batch*(J+N), P] f32 with leading J non-patch
+ * rows per image.  Writes loss[0] (mean over images of mean over masked patches of the
+ * per-patch MSE) and, if dpred != NULL, dpred (bf16, same shape, ld = lddp) = d loss /
+ * d pred * grad_scale (zero on unmasked and CLS rows).
+ * workspace: jm_patch_loss_workspace(batch, N) bytes. */
+size_t jm_patch_loss_workspace(int batch, int num_patches);
+int jm_patch_loss(const float* pred, long ldp, const uint8_t* images, const float* mask_row, int batch,
+                  int image_size, int patch_size, int num_cls, int norm_pix, float grad_scale, float* loss,
+                  jm_bf16* dpred, long lddp, void* workspace, size_t workspace_bytes, void* stream);
+
+/* ---------------------------------------------------------------- LayerNorm
+ * flax.linen.LayerNorm as used at src/modeling.py:155-156,177-179,238,282:
+ * y = (x - mean) * rsqrt(E[x^2]-mean^2 + eps) * gamma + beta, f32 statistics.
+ * y_bf16 and/or y_f32 may be NULL.  mean/rstd [rows] are saved for the backward. */
+int jm_layernorm_fwd(const float* x, long ldx, int rows, int dim, const float* gamma, const float* beta, float eps,
+                     jm_bf16* y_bf16, long ldy, float* y_f32, long ldyf, float* mean, float* rstd, void* stream);
+
+/* Backward of the above.  dx = (dres ? dres : 0) + LN'(dy); rows with
+ * (row % row_period) < row_skip are left untouched (used for the CLS rows of the
+ * Jumbo layer, src/modeling.py:194-204).  dgamma/dbeta are ACCUMULATED (+=).
+ * workspace: jm_layernorm_bwd_workspace(rows, dim) bytes. */
+size_t jm_layernorm_bwd_workspace(int rows, int dim);
+int jm_layernorm_bwd(const jm_bf16* dy, long lddy, const float* x, long ldx, const float* mean, const float* rstd,
+                     const float* gamma, int rows, int dim, const float* dres, long lddres, float* dx, long lddx,
+                     jm_bf16* dx_bf16, long lddxb, int row_period, int row_skip, float* dgamma, float* dbeta,
+                     void* workspace, size_t workspace_bytes, void* stream);
+
+/* ---------------------------------------------------------------- GEMM
+ * D = epilogue(A * B), bf16 operands, f32 accumulation in tensor memory
+ * (tcgen05.mma fed by TMA).  Replaces every Dense / DenseGeneral / Conv contraction
+ * of src/modeling.py:108-148 and src/pretraining.py:84-85, forward and backward.
+ *   A: a_mn_major == 0 -> stored [M, K] row-major (ld = lda);
+ *      a_mn_major == 1 -> stored [K, M] row-major (the transposed view, for dW = X^T dY)
+ *   B: b_mn_major == 0 -> stored [N, K] row-major; b_mn_major == 1 -> stored [K, N] row-major
+ *      (a Flax kernel [in, out] is B with b_mn_major = 1 in the forward pass and
+ *       b_mn_major = 0 in the input-gradient pass)
+ * Epilogue, applied in this order to v = acc:
+ *   v += bias[col]; if (col < col_scale_n) v *= col_scale;
+ *   act == 1 (GELU-tanh, src/modeling.py:148): out_bf16 <- v (pre-activation), out2_bf16 <- gelu(v)
+ *   act == 2 (GELU backward): v *= gelu'(aux[row, col])
+ *   v += pe[pe_idx[(row % row_period) - row_skip], col]   (positional embedding, modeling.py:123)
+ *   v += residual[row, col]
+ *   rows with (row % row_period) < row_skip: row_mask_mode 1 -> zeros are stored,
+ *   2 -> nothing is stored.
+ *   accumulate != 0 -> out_f32 += v (atomic; also used for split-K), else out_f32 = v.
+ */
+typedef struct jm_gemm_args {
+  int M, N, K;
+  const jm_bf16* A; long lda; int a_mn_major;
+  const jm_bf16* B; long ldb; int b_mn_major;
+  float* out_f32; long ldo_f32;
+  jm_bf16* out_bf16; long ldo_bf16;
+  jm_bf16* out2_bf16; long ldo2_bf16;
+  const float* bias;
+  const float* residual; long ldr;
+  const jm_bf16* aux; long ldaux;
+  const float* pe; const int32_t* pe_idx; long ldpe;
+  int act;
+  float col_scale; int col_scale_n;
+  int row_period, row_skip, row_mask_mode;
+  int accumulate;
+  int splits;      /* 0 = choose automatically */
+  int block_n;     /* 0 = choose automatically (64, 128 or 256) */
+} jm_gemm_args;
+int jm_gemm(const jm_gemm_args* args, void* stream);
+
+/* ---------------------------------------------------------------- attention
+ * Attention core of src/modeling.py:136-137 for short sequences: per (image, head)
+ * softmax(q k^T) v with q already scaled.  qkv is [batch*T, 3*heads*hd] bf16 with
+ * columns [q | k | v], each head-major.  lse [batch, heads, T] f32 is saved. */
+int jm_attention_fwd(const jm_bf16* qkv, long ldqkv, int batch, int T, int heads, int head_dim, jm_bf16* out,
+                     long ldo, float* lse, void* stream);
+/* dqkv (same layout as qkv) from dout; the q part is multiplied by q_scale so that it
+ * is the gradient w.r.t. the un-scaled projection. */
+int jm_attention_bwd(const jm_bf16* qkv, long ldqkv, const jm_bf16* out, long ldo, const jm_bf16* dout, long lddo,
+                     const float* lse, int batch, int T, int heads, int head_dim, float q_scale, jm_bf16* dqkv,
+                     long lddqkv, void* stream);
+
+/* ---------------------------------------------------------------- token assembly
+ * CLS prepend (src/modeling.py:249-250,257): x[b, j, :] = cls[j, :] for j < J. */
+int jm_fill_cls(float* x, int batch, int T, int J, int dim, const float* cls, void* stream);
+
+/* Decoder input assembly (src/pretraining.py:96-106 + src/modeling.py:289-292):
+ * out[b, j<J] = y[b, j]; out[b, J+i] = (ids_restore[i] < n ? y[b, J+ids_restore[i]] : mask_emb) + dec_wpe[i]. */
+int jm_unshuffle_fwd(const float* y, const int32_t* ids_restore, const float* mask_emb, const float* dec_wpe,
+                     int batch, int N, int n, int J, int dim, float* out, void* stream);
+/* Its backward: dy (bf16, [batch*(J+n), dim]) and dmask_emb (+=, f32 [dim]). */
+int jm_unshuffle_bwd(const float* dout, const int32_t* ids_restore, int batch, int N, int n, int J, int dim,
+                     jm_bf16* dy, float* dmask_emb, void* stream);
+
+/* Column sums (bias gradients): out[c] += sum over rows r with (r % row_period) >= row_skip
+ * of x[r, c].  x is bf16 (is_f32 == 0) or f32. */
+int jm_colsum(const void* x, int is_f32, long ldx, int rows, int cols, int row_period, int row_skip, float* out,
+              void* stream);
+
+/* ---------------------------------------------------------------- optimizer
+ * optax.adamw leaf update (src/pretraining.py:223-234) over a flat parameter buffer:
+ * g' = g * grad_scale; m = b1 m + (1-b1) g'; v = b2 v + (1-b2) g'^2;
+ * u = (m / bc1) / (sqrt(v / bc2) + eps) + (i < n_decay ? wd * p : 0); p -= lr * u.
+ * Also writes the bf16 compute copy of p. */
+int jm_adamw(float* p, const float* g, float* m, float* v, jm_bf16* p_bf16, long n, long n_decay, float lr,
+             float b1, float b2, float eps, float wd, float bc1, float bc2, float grad_scale, void* stream);
+
+int jm_cast_bf16(const float* x, jm_bf16* y, long n, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* JUMBO_MAE_B200_H_ */

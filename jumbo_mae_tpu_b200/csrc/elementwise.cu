@@ -1,0 +1,729 @@
+// HBM-bound kernels of the MAE step: masking sort, pixel pre-processing / patchify,
+// masked-patch MSE, LayerNorm forward/backward, token assembly, bias-gradient column
+// sums and the fused AdamW.  All are coalesced, vectorised (8/16-byte accesses) and
+// sized from the problem, not from a tile shape: none of them has data reuse to stage.
+#include "../../include/jumbo_mae_b200.h"
+#include "common.cuh"
+
+namespace jm {
+
+// src/dataset.py:37-38, demoted to f32 exactly as JAX does at src/pretraining.py:91
+__constant__ float c_mean[3] = {0.485f, 0.456f, 0.406f};
+__constant__ float c_std[3] = {0.229f, 0.224f, 0.225f};
+
+__device__ __forceinline__ float norm_pixel(uint8_t u, int c) {
+  // (u / 255 - mean) / std with IEEE ops, no contraction: matches the f32 oracle bit for bit
+  return __fdiv_rn(__fsub_rn(__fdiv_rn(static_cast<float>(u), 255.0f), c_mean[c]), c_std[c]);
+}
+
+__device__ __forceinline__ float block_sum(float v, float* red /* >= 32 floats */) {
+  v = warp_sum(v);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = (blockDim.x + 31) >> 5;
+  __syncthreads();
+  if (lane == 0) red[warp] = v;
+  __syncthreads();
+  float t = (lane < nw) ? red[lane] : 0.f;
+  t = warp_sum(t);
+  return t;
+}
+
+// ---------------------------------------------------------------- masking sort
+// Stable ascending argsort by rank counting in shared memory: rank(i) = #{j : key_j < key_i or
+// (key_j == key_i and j < i)}.  length <= 1024, one thread per element, bit-exact and
+// tie-stable like jnp.argsort (NaN sorts last).
+__global__ void mask_sort_kernel(const float* __restrict__ noise, int L, int keep, int* __restrict__ ids_shuffle,
+                                 int* __restrict__ ids_restore, float* __restrict__ mask_row) {
+  extern __shared__ float s_noise[];
+  const int i = threadIdx.x;
+  if (i < L) s_noise[i] = noise[i];
+  __syncthreads();
+  if (i >= L) return;
+  const float me = s_noise[i];
+  const bool me_nan = me != me;
+  int rank = 0;
+  for (int j = 0; j < L; ++j) {
+    const float o = s_noise[j];
+    const bool o_nan = o != o;
+    bool less;
+    if (me_nan) less = !o_nan || j < i;           // every non-NaN precedes a NaN; NaNs keep index order
+    else less = !o_nan && (o < me || (o == me && j < i));
+    rank += less ? 1 : 0;
+  }
+  ids_shuffle[rank] = i;
+  ids_restore[i] = rank;
+  mask_row[i] = rank >= keep ? 1.0f : 0.0f;
+}
+
+__global__ void index_sequence_kernel(const float* __restrict__ x, const int* __restrict__ ids, int length_in,
+                                      int length_out, int dim, float* __restrict__ out) {
+  const int i = blockIdx.x, b = blockIdx.y;
+  const float* src = x + (static_cast<long>(b) * length_in + ids[i]) * dim;
+  float* dst = out + (static_cast<long>(b) * length_out + i) * dim;
+  for (int c = threadIdx.x; c < dim; c += blockDim.x) dst[c] = src[c];
+}
+
+// ---------------------------------------------------------------- patchify
+__global__ void patchify_kernel(const uint8_t* __restrict__ images, int S, int p, const int* __restrict__ ids,
+                                int n_sel, int rows_per_image, int row_off, __nv_bfloat16* __restrict__ out,
+                                long ldo) {
+  const int r = blockIdx.x, b = blockIdx.y;
+  __nv_bfloat16* dst = out + (static_cast<long>(b) * rows_per_image + r) * ldo;
+  const int P = p * p * 3;
+  if (r < row_off || r >= row_off + n_sel) {
+    for (int e = threadIdx.x; e < ldo; e += blockDim.x) dst[e] = __float2bfloat16(0.f);
+    return;
+  }
+  const int g = S / p;
+  const int patch = ids ? ids[r - row_off] : (r - row_off);
+  const int gy = patch / g, gx = patch - gy * g;
+  const uint8_t* img = images + static_cast<long>(b) * 3 * S * S;
+  for (int e = threadIdx.x; e < ldo; e += blockDim.x) {
+    float v = 0.f;
+    if (e < P) {
+      const int c = e % 3, pix = e / 3;
+      const int ph = pix / p, pw = pix - ph * p;
+      v = norm_pixel(img[(static_cast<long>(c) * S + gy * p + ph) * S + gx * p + pw], c);
+    }
+    dst[e] = __float2bfloat16(v);
+  }
+}
+
+__global__ void extract_patches_kernel(const uint8_t* __restrict__ images, int S, int p, float* __restrict__ out) {
+  const int patch = blockIdx.x, b = blockIdx.y;
+  const int P = p * p * 3, g = S / p;
+  const int gy = patch / g, gx = patch - gy * g;
+  const uint8_t* img = images + static_cast<long>(b) * 3 * S * S;
+  float* dst = out + (static_cast<long>(b) * g * g + patch) * P;
+  for (int e = threadIdx.x; e < P; e += blockDim.x) {
+    const int c = e % 3, pix = e / 3;
+    const int ph = pix / p, pw = pix - ph * p;
+    dst[e] = norm_pixel(img[(static_cast<long>(c) * S + gy * p + ph) * S + gx * p + pw], c);
+  }
+}
+
+// ---------------------------------------------------------------- masked patch MSE
+constexpr int kLossThreads = 256;
+constexpr int kLossMaxPer = 8;  // P <= 2048
+
+__global__ void __launch_bounds__(kLossThreads)
+patch_loss_kernel(const float* __restrict__ pred, long ldp, const uint8_t* __restrict__ images,
+                  const float* __restrict__ mask_row, int S, int p, int J, int norm_pix, float grad_scale,
+                  float* __restrict__ partial, __nv_bfloat16* __restrict__ dpred, long lddp, int batch) {
+  __shared__ float red[32];
+  const int g = S / p, N = g * g, P = p * p * 3;
+  const int t = blockIdx.x;  // token index within the image, 0 .. J+N-1
+  const int b = blockIdx.y;
+  const long row = static_cast<long>(b) * (J + N) + t;
+  const int patch = t - J;
+  const bool masked = patch >= 0 && mask_row[patch] > 0.f;
+  if (!masked) {
+    if (patch >= 0 && threadIdx.x == 0) partial[static_cast<long>(b) * N + patch] = 0.f;
+    if (dpred)
+      for (int e = threadIdx.x; e < P; e += blockDim.x) dpred[row * lddp + e] = __float2bfloat16(0.f);
+    return;
+  }
+  float cnt = 0.f;
+  for (int i = threadIdx.x; i < N; i += blockDim.x) cnt += mask_row[i] > 0.f ? 1.f : 0.f;
+  const float num_masked = block_sum(cnt, red);
+
+  const int gy = patch / g, gx = patch - gy * g;
+  const uint8_t* img = images + static_cast<long>(b) * 3 * S * S;
+  float tv[kLossMaxPer];
+  float s = 0.f;
+#pragma unroll
+  for (int k = 0; k < kLossMaxPer; ++k) {
+    const int e = threadIdx.x + k * kLossThreads;
+    tv[k] = 0.f;
+    if (e < P) {
+      const int c = e % 3, pix = e / 3;
+      const int ph = pix / p, pw = pix - ph * p;
+      tv[k] = norm_pixel(img[(static_cast<long>(c) * S + gy * p + ph) * S + gx * p + pw], c);
+      s += tv[k];
+    }
+  }
+  if (norm_pix) {  // src/pretraining.py:115-118, jnp.var is the biased variance
+    const float mean = block_sum(s, red) / P;
+    float ss = 0.f;
+#pragma unroll
+    for (int k = 0; k < kLossMaxPer; ++k) {
+      const int e = threadIdx.x + k * kLossThreads;
+      if (e < P) ss += (tv[k] - mean) * (tv[k] - mean);
+    }
+    const float var = block_sum(ss, red) / P;
+    const float inv = 1.0f / sqrtf(var + 1e-6f);
+#pragma unroll
+    for (int k = 0; k < kLossMaxPer; ++k) tv[k] = (tv[k] - mean) * inv;
+  }
+  const float gscale = 2.0f * grad_scale / (static_cast<float>(P) * num_masked * static_cast<float>(batch));
+  float sq = 0.f;
+#pragma unroll
+  for (int k = 0; k < kLossMaxPer; ++k) {
+    const int e = threadIdx.x + k * kLossThreads;
+    if (e < P) {
+      const float d = pred[row * ldp + e] - tv[k];
+      sq += d * d;
+      if (dpred) dpred[row * lddp + e] = __float2bfloat16(d * gscale);
+    }
+  }
+  const float tot = block_sum(sq, red);
+  if (threadIdx.x == 0) partial[static_cast<long>(b) * N + patch] = tot / P;
+}
+
+__global__ void patch_loss_finalize_kernel(const float* __restrict__ partial, const float* __restrict__ mask_row,
+                                           int N, int batch, float* __restrict__ loss) {
+  __shared__ float red[32];
+  float cnt = 0.f;
+  for (int i = threadIdx.x; i < N; i += blockDim.x) cnt += mask_row[i] > 0.f ? 1.f : 0.f;
+  const float num_masked = block_sum(cnt, red);
+  float s = 0.f;
+  const long total = static_cast<long>(batch) * N;
+  for (long i = threadIdx.x; i < total; i += blockDim.x) s += partial[i];
+  const float tot = block_sum(s, red);
+  if (threadIdx.x == 0) loss[0] = tot / (num_masked * static_cast<float>(batch));
+}
+
+// ---------------------------------------------------------------- LayerNorm
+constexpr int kLnWarps = 8;
+
+__global__ void __launch_bounds__(kLnWarps * 32)
+layernorm_fwd_kernel(const float* __restrict__ x, long ldx, int rows, int D, const float* __restrict__ gamma,
+                     const float* __restrict__ beta, float eps, __nv_bfloat16* __restrict__ yb, long ldy,
+                     float* __restrict__ yf, long ldyf, float* __restrict__ mean_out, float* __restrict__ rstd_out) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const long row = static_cast<long>(blockIdx.x) * kLnWarps + warp;
+  if (row >= rows) return;
+  const float* xr = x + row * ldx;
+  float s = 0.f, ss = 0.f;
+  for (int c = lane * 4; c < D; c += 128) {
+    const float4 v = *reinterpret_cast<const float4*>(xr + c);
+    s += v.x + v.y + v.z + v.w;
+    ss += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
+  }
+  s = warp_sum(s), ss = warp_sum(ss);
+  const float mean = s / D;
+  const float var = fmaxf(ss / D - mean * mean, 0.f);  // flax "fast variance"
+  const float rstd = 1.0f / sqrtf(var + eps);
+  if (lane == 0) {
+    if (mean_out) mean_out[row] = mean;
+    if (rstd_out) rstd_out[row] = rstd;
+  }
+  for (int c = lane * 4; c < D; c += 128) {
+    const float4 v = *reinterpret_cast<const float4*>(xr + c);
+    const float4 g = *reinterpret_cast<const float4*>(gamma + c);
+    const float4 b = *reinterpret_cast<const float4*>(beta + c);
+    float4 y;
+    y.x = (v.x - mean) * rstd * g.x + b.x;
+    y.y = (v.y - mean) * rstd * g.y + b.y;
+    y.z = (v.z - mean) * rstd * g.z + b.z;
+    y.w = (v.w - mean) * rstd * g.w + b.w;
+    if (yb) {
+      uint2 u = {pack_bf16(y.x, y.y), pack_bf16(y.z, y.w)};
+      *reinterpret_cast<uint2*>(yb + row * ldy + c) = u;
+    }
+    if (yf) *reinterpret_cast<float4*>(yf + row * ldyf + c) = y;
+  }
+}
+
+constexpr int kLnBwdMaxBlocks = 592;  // 4 x 148
+
+// dx = dres + rstd * (dy*g - mean(dy*g) - xhat * mean(dy*g*xhat)); per-block dgamma/dbeta partials
+// are accumulated in shared memory and written to the workspace [block][2][D].
+__global__ void __launch_bounds__(kLnWarps * 32)
+layernorm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, long lddy, const float* __restrict__ x, long ldx,
+                     const float* __restrict__ mean, const float* __restrict__ rstd, const float* __restrict__ gamma,
+                     int rows, int D, const float* __restrict__ dres, long lddres, float* __restrict__ dx, long lddx,
+                     __nv_bfloat16* __restrict__ dxb, long lddxb, int row_period, int row_skip,
+                     float* __restrict__ ws) {
+  extern __shared__ float s_acc[];  // [2][D]
+  for (int c = threadIdx.x; c < 2 * D; c += blockDim.x) s_acc[c] = 0.f;
+  __syncthreads();
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (long row = static_cast<long>(blockIdx.x) * kLnWarps + warp; row < rows;
+       row += static_cast<long>(gridDim.x) * kLnWarps) {
+    if (row_period > 0 && (row % row_period) < row_skip) continue;
+    const __nv_bfloat16* dyr = dy + row * lddy;
+    const float* xr = x + row * ldx;
+    const float mu = mean[row], rs = rstd[row];
+    float c1 = 0.f, c2 = 0.f;
+    for (int c = lane * 4; c < D; c += 128) {
+      const uint2 u = *reinterpret_cast<const uint2*>(dyr + c);
+      const float2 d01 = unpack_bf16(u.x), d23 = unpack_bf16(u.y);
+      const float4 xv = *reinterpret_cast<const float4*>(xr + c);
+      const float4 g = *reinterpret_cast<const float4*>(gamma + c);
+      const float d[4] = {d01.x, d01.y, d23.x, d23.y};
+      const float xh[4] = {(xv.x - mu) * rs, (xv.y - mu) * rs, (xv.z - mu) * rs, (xv.w - mu) * rs};
+      const float gg[4] = {g.x, g.y, g.z, g.w};
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        c1 += d[j] * gg[j];
+        c2 += d[j] * gg[j] * xh[j];
+        atomicAdd(&s_acc[c + j], d[j] * xh[j]);
+        atomicAdd(&s_acc[D + c + j], d[j]);
+      }
+    }
+    c1 = warp_sum(c1) / D, c2 = warp_sum(c2) / D;
+    for (int c = lane * 4; c < D; c += 128) {
+      const uint2 u = *reinterpret_cast<const uint2*>(dyr + c);
+      const float2 d01 = unpack_bf16(u.x), d23 = unpack_bf16(u.y);
+      const float4 xv = *reinterpret_cast<const float4*>(xr + c);
+      const float4 g = *reinterpret_cast<const float4*>(gamma + c);
+      float4 o;
+      o.x = rs * (d01.x * g.x - c1 - (xv.x - mu) * rs * c2);
+      o.y = rs * (d01.y * g.y - c1 - (xv.y - mu) * rs * c2);
+      o.z = rs * (d23.x * g.z - c1 - (xv.z - mu) * rs * c2);
+      o.w = rs * (d23.y * g.w - c1 - (xv.w - mu) * rs * c2);
+      if (dres) {
+        const float4 r = *reinterpret_cast<const float4*>(dres + row * lddres + c);
+        o.x += r.x, o.y += r.y, o.z += r.z, o.w += r.w;
+      }
+      if (dx) *reinterpret_cast<float4*>(dx + row * lddx + c) = o;
+      if (dxb) {
+        uint2 w = {pack_bf16(o.x, o.y), pack_bf16(o.z, o.w)};
+        *reinterpret_cast<uint2*>(dxb + row * lddxb + c) = w;
+      }
+    }
+  }
+  __syncthreads();
+  float* out = ws + static_cast<long>(blockIdx.x) * 2 * D;
+  for (int c = threadIdx.x; c < 2 * D; c += blockDim.x) out[c] = s_acc[c];
+}
+
+// Fast path for dim <= NV*128: the row and the per-lane dgamma/dbeta partial sums stay in
+// registers (one global read of dy and x per row); shared memory is touched once per block.
+template <int NV>
+__global__ void __launch_bounds__(kLnWarps * 32)
+layernorm_bwd_reg_kernel(const __nv_bfloat16* __restrict__ dy, long lddy, const float* __restrict__ x, long ldx,
+                         const float* __restrict__ mean, const float* __restrict__ rstd,
+                         const float* __restrict__ gamma, int rows, int D, const float* __restrict__ dres,
+                         long lddres, float* __restrict__ dx, long lddx, __nv_bfloat16* __restrict__ dxb, long lddxb,
+                         int row_period, int row_skip, float* __restrict__ ws) {
+  extern __shared__ float s_acc[];  // [2][D]
+  for (int c = threadIdx.x; c < 2 * D; c += blockDim.x) s_acc[c] = 0.f;
+  __syncthreads();
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  float gm[NV][4], ag[NV][4], ab[NV][4];
+#pragma unroll
+  for (int k = 0; k < NV; ++k) {
+    const int c = lane * 4 + k * 128;
+    float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (c < D) g = *reinterpret_cast<const float4*>(gamma + c);
+    gm[k][0] = g.x, gm[k][1] = g.y, gm[k][2] = g.z, gm[k][3] = g.w;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) ag[k][j] = 0.f, ab[k][j] = 0.f;
+  }
+  for (long row = static_cast<long>(blockIdx.x) * kLnWarps + warp; row < rows;
+       row += static_cast<long>(gridDim.x) * kLnWarps) {
+    if (row_period > 0 && (row % row_period) < row_skip) continue;
+    const __nv_bfloat16* dyr = dy + row * lddy;
+    const float* xr = x + row * ldx;
+    const float mu = mean[row], rs = rstd[row];
+    float d[NV][4], xh[NV][4];
+    float c1 = 0.f, c2 = 0.f;
+#pragma unroll
+    for (int k = 0; k < NV; ++k) {
+      const int c = lane * 4 + k * 128;
+      uint2 u = make_uint2(0u, 0u);
+      float4 xv = make_float4(mu, mu, mu, mu);
+      if (c < D) {
+        u = *reinterpret_cast<const uint2*>(dyr + c);
+        xv = *reinterpret_cast<const float4*>(xr + c);
+      }
+      const float2 d01 = unpack_bf16(u.x), d23 = unpack_bf16(u.y);
+      d[k][0] = d01.x, d[k][1] = d01.y, d[k][2] = d23.x, d[k][3] = d23.y;
+      xh[k][0] = (xv.x - mu) * rs, xh[k][1] = (xv.y - mu) * rs, xh[k][2] = (xv.z - mu) * rs,
+      xh[k][3] = (xv.w - mu) * rs;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float dg = d[k][j] * gm[k][j];
+        c1 += dg;
+        c2 += dg * xh[k][j];
+        ag[k][j] += d[k][j] * xh[k][j];
+        ab[k][j] += d[k][j];
+      }
+    }
+    c1 = warp_sum(c1) / D, c2 = warp_sum(c2) / D;
+#pragma unroll
+    for (int k = 0; k < NV; ++k) {
+      const int c = lane * 4 + k * 128;
+      if (c < D) {
+        float o[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) o[j] = rs * (d[k][j] * gm[k][j] - c1 - xh[k][j] * c2);
+        if (dres) {
+          const float4 r = *reinterpret_cast<const float4*>(dres + row * lddres + c);
+          o[0] += r.x, o[1] += r.y, o[2] += r.z, o[3] += r.w;
+        }
+        if (dx) *reinterpret_cast<float4*>(dx + row * lddx + c) = make_float4(o[0], o[1], o[2], o[3]);
+        if (dxb) {
+          uint2 w = {pack_bf16(o[0], o[1]), pack_bf16(o[2], o[3])};
+          *reinterpret_cast<uint2*>(dxb + row * lddxb + c) = w;
+        }
+      }
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < NV; ++k) {
+    const int c = lane * 4 + k * 128;
+    if (c < D) {
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        atomicAdd(&s_acc[c + j], ag[k][j]);
+        atomicAdd(&s_acc[D + c + j], ab[k][j]);
+      }
+    }
+  }
+  __syncthreads();
+  float* out = ws + static_cast<long>(blockIdx.x) * 2 * D;
+  for (int c = threadIdx.x; c < 2 * D; c += blockDim.x) out[c] = s_acc[c];
+}
+
+__global__ void ln_param_reduce_kernel(const float* __restrict__ ws, int nblocks, int D, float* __restrict__ dgamma,
+                                       float* __restrict__ dbeta) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= 2 * D) return;
+  float s = 0.f;
+  for (int b = 0; b < nblocks; ++b) s += ws[static_cast<long>(b) * 2 * D + c];
+  if (c < D) {
+    if (dgamma) dgamma[c] += s;
+  } else {
+    if (dbeta) dbeta[c - D] += s;
+  }
+}
+
+// ---------------------------------------------------------------- token assembly
+__global__ void fill_cls_kernel(float* __restrict__ x, int T, int J, int dim, const float* __restrict__ cls) {
+  const int j = blockIdx.x, b = blockIdx.y;
+  float* dst = x + (static_cast<long>(b) * T + j) * dim;
+  for (int c = threadIdx.x; c < dim; c += blockDim.x) dst[c] = cls[static_cast<long>(j) * dim + c];
+}
+
+__global__ void unshuffle_fwd_kernel(const float* __restrict__ y, const int* __restrict__ ids_restore,
+                                     const float* __restrict__ mask_emb, const float* __restrict__ wpe, int N, int n,
+                                     int J, int dim, float* __restrict__ out) {
+  const int t = blockIdx.x, b = blockIdx.y;
+  float* dst = out + (static_cast<long>(b) * (J + N) + t) * dim;
+  const float* src;
+  const float* pe = nullptr;
+  if (t < J) {
+    src = y + (static_cast<long>(b) * (J + n) + t) * dim;
+  } else {
+    const int i = t - J, r = ids_restore[i];
+    src = r < n ? y + (static_cast<long>(b) * (J + n) + J + r) * dim : mask_emb;
+    pe = wpe + static_cast<long>(i) * dim;
+  }
+  for (int c = threadIdx.x * 4; c < dim; c += blockDim.x * 4) {
+    float4 v = *reinterpret_cast<const float4*>(src + c);
+    if (pe) {
+      const float4 q = *reinterpret_cast<const float4*>(pe + c);
+      v.x += q.x, v.y += q.y, v.z += q.z, v.w += q.w;
+    }
+    *reinterpret_cast<float4*>(dst + c) = v;
+  }
+}
+
+constexpr int kUnshufBwdImgs = 16;
+__global__ void unshuffle_bwd_kernel(const float* __restrict__ dout, const int* __restrict__ ids_restore, int batch,
+                                     int N, int n, int J, int dim, __nv_bfloat16* __restrict__ dy,
+                                     float* __restrict__ dmask) {
+  const int t = blockIdx.x;
+  const int b0 = blockIdx.y * kUnshufBwdImgs;
+  const int b1 = min(batch, b0 + kUnshufBwdImgs);
+  int dst_tok;  // -1: mask token
+  if (t < J) dst_tok = t;
+  else {
+    const int r = ids_restore[t - J];
+    dst_tok = r < n ? J + r : -1;
+  }
+  for (int c = threadIdx.x * 4; c < dim; c += blockDim.x * 4) {
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int b = b0; b < b1; ++b) {
+      const float4 v = *reinterpret_cast<const float4*>(dout + (static_cast<long>(b) * (J + N) + t) * dim + c);
+      if (dst_tok >= 0) {
+        uint2 u = {pack_bf16(v.x, v.y), pack_bf16(v.z, v.w)};
+        *reinterpret_cast<uint2*>(dy + (static_cast<long>(b) * (J + n) + dst_tok) * dim + c) = u;
+      } else {
+        acc.x += v.x, acc.y += v.y, acc.z += v.z, acc.w += v.w;
+      }
+    }
+    if (dst_tok < 0 && dmask) {
+      atomicAdd(dmask + c + 0, acc.x);
+      atomicAdd(dmask + c + 1, acc.y);
+      atomicAdd(dmask + c + 2, acc.z);
+      atomicAdd(dmask + c + 3, acc.w);
+    }
+  }
+}
+
+// ---------------------------------------------------------------- column sums
+template <bool F32>
+__global__ void __launch_bounds__(256)
+colsum_kernel(const void* __restrict__ xv, long ldx, int rows, int cols, int row_period, int row_skip,
+              int rows_per_block, float* __restrict__ out) {
+  __shared__ float4 s_part[4][64];
+  const int tx = threadIdx.x & 63, ty = threadIdx.x >> 6;
+  const int c = (blockIdx.x * 64 + tx) * 4;
+  const int r0 = blockIdx.y * rows_per_block;
+  const int r1 = min(rows, r0 + rows_per_block);
+  float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (c < cols) {
+    for (int r = r0 + ty; r < r1; r += 4) {
+      if (row_period > 0 && (r % row_period) < row_skip) continue;
+      if (F32) {
+        const float4 v = *reinterpret_cast<const float4*>(static_cast<const float*>(xv) + r * ldx + c);
+        acc.x += v.x, acc.y += v.y, acc.z += v.z, acc.w += v.w;
+      } else {
+        const uint2 u = *reinterpret_cast<const uint2*>(static_cast<const __nv_bfloat16*>(xv) + r * ldx + c);
+        const float2 a = unpack_bf16(u.x), b = unpack_bf16(u.y);
+        acc.x += a.x, acc.y += a.y, acc.z += b.x, acc.w += b.y;
+      }
+    }
+  }
+  s_part[ty][tx] = acc;
+  __syncthreads();
+  if (ty == 0 && c < cols) {
+    float4 t = s_part[0][tx];
+    for (int k = 1; k < 4; ++k) {
+      const float4 o = s_part[k][tx];
+      t.x += o.x, t.y += o.y, t.z += o.z, t.w += o.w;
+    }
+    atomicAdd(out + c + 0, t.x);
+    atomicAdd(out + c + 1, t.y);
+    atomicAdd(out + c + 2, t.z);
+    atomicAdd(out + c + 3, t.w);
+  }
+}
+
+// ---------------------------------------------------------------- AdamW
+__global__ void __launch_bounds__(256)
+adamw_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m, float* __restrict__ v,
+             __nv_bfloat16* __restrict__ pb, long n4, long n_decay4, float lr, float b1, float b2, float eps,
+             float wd, float bc1, float bc2, float gscale) {
+  const float omb1 = 1.0f - b1, omb2 = 1.0f - b2;
+  for (long i = static_cast<long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n4;
+       i += static_cast<long>(gridDim.x) * blockDim.x) {
+    float4 pv = reinterpret_cast<float4*>(p)[i];
+    const float4 gv = reinterpret_cast<const float4*>(g)[i];
+    float4 mv = reinterpret_cast<float4*>(m)[i];
+    float4 vv = reinterpret_cast<float4*>(v)[i];
+    const float decay = i < n_decay4 ? wd : 0.f;
+    float* pp = reinterpret_cast<float*>(&pv);
+    const float* gp = reinterpret_cast<const float*>(&gv);
+    float* mp = reinterpret_cast<float*>(&mv);
+    float* vp = reinterpret_cast<float*>(&vv);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const float gg = gp[j] * gscale;
+      mp[j] = b1 * mp[j] + omb1 * gg;
+      vp[j] = b2 * vp[j] + omb2 * gg * gg;
+      const float mh = mp[j] / bc1, vh = vp[j] / bc2;
+      const float u = mh / (sqrtf(vh) + eps) + decay * pp[j];
+      pp[j] = pp[j] - lr * u;
+    }
+    reinterpret_cast<float4*>(p)[i] = pv;
+    reinterpret_cast<float4*>(m)[i] = mv;
+    reinterpret_cast<float4*>(v)[i] = vv;
+    if (pb) {
+      uint2 u = {pack_bf16(pp[0], pp[1]), pack_bf16(pp[2], pp[3])};
+      reinterpret_cast<uint2*>(pb)[i] = u;
+    }
+  }
+}
+
+__global__ void cast_bf16_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ y, long n) {
+  for (long i = static_cast<long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n;
+       i += static_cast<long>(gridDim.x) * blockDim.x)
+    y[i] = __float2bfloat16(x[i]);
+}
+
+}  // namespace jm
+
+using namespace jm;
+#define STREAM static_cast<cudaStream_t>(stream)
+
+extern "C" int jm_mask_sort(const float* noise, int length, int keep, int32_t* ids_shuffle, int32_t* ids_restore,
+                            float* mask_row, void* stream) {
+  JM_CHECK(length > 0 && length <= 1024, "jm_mask_sort: length must be in [1, 1024] (got %d)", length);
+  JM_CHECK(keep >= 0 && keep <= length, "jm_mask_sort: keep out of range");
+  const int threads = (length + 31) / 32 * 32;
+  mask_sort_kernel<<<1, threads, length * sizeof(float), STREAM>>>(noise, length, keep, ids_shuffle, ids_restore,
+                                                                   mask_row);
+  JM_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int jm_index_sequence(const float* x, const int32_t* ids, int batch, int length_in, int length_out,
+                                 int dim, float* out, void* stream) {
+  if (batch == 0 || length_out == 0) return 0;
+  index_sequence_kernel<<<dim3(length_out, batch), 128, 0, STREAM>>>(x, ids, length_in, length_out, dim, out);
+  JM_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int jm_patchify(const uint8_t* images, int batch, int image_size, int patch_size, const int32_t* ids,
+                           int n_sel, int rows_per_image, int row_off, jm_bf16* out, long ldo, void* stream) {
+  JM_CHECK(image_size % patch_size == 0, "jm_patchify: image size must be a multiple of the patch size");
+  JM_CHECK(ldo >= patch_size * patch_size * 3, "jm_patchify: ldo smaller than the patch dimension");
+  JM_CHECK(row_off + n_sel <= rows_per_image, "jm_patchify: rows_per_image too small");
+  if (batch == 0) return 0;
+  patchify_kernel<<<dim3(rows_per_image, batch), 256, 0, STREAM>>>(
+      images, image_size, patch_size, ids, n_sel, rows_per_image, row_off, reinterpret_cast<__nv_bfloat16*>(out), ldo);
+  JM_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int jm_extract_patches(const uint8_t* images, int batch, int image_size, int patch_size, float* out,
+                                  void* stream) {
+  JM_CHECK(image_size % patch_size == 0, "jm_extract_patches: image size must be a multiple of the patch size");
+  if (batch == 0) return 0;
+  const int g = image_size / patch_size;
+  extract_patches_kernel<<<dim3(g * g, batch), 256, 0, STREAM>>>(images, image_size, patch_size, out);
+  JM_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" size_t jm_patch_loss_workspace(int batch, int num_patches) {
+  return static_cast<size_t>(batch) * num_patches * sizeof(float);
+}
+
+extern "C" int jm_patch_loss(const float* pred, long ldp, const uint8_t* images, const float* mask_row, int batch,
+                             int image_size, int patch_size, int num_cls, int norm_pix, float grad_scale, float* loss,
+                             jm_bf16* dpred, long lddp, void* workspace, size_t workspace_bytes, void* stream) {
+  const int g = image_size / patch_size, N = g * g, P = patch_size * patch_size * 3;
+  JM_CHECK(P <= kLossThreads * kLossMaxPer, "jm_patch_loss: patch dimension %d too large", P);
+  JM_CHECK(batch > 0, "jm_patch_loss: empty batch");
+  JM_CHECK(workspace && workspace_bytes >= jm_patch_loss_workspace(batch, N), "jm_patch_loss: workspace too small");
+  float* partial = static_cast<float*>(workspace);
+  patch_loss_kernel<<<dim3(num_cls + N, batch), kLossThreads, 0, STREAM>>>(
+      pred, ldp, images, mask_row, image_size, patch_size, num_cls, norm_pix, grad_scale, partial,
+      reinterpret_cast<__nv_bfloat16*>(dpred), lddp, batch);
+  JM_CUDA(cudaGetLastError());
+  patch_loss_finalize_kernel<<<1, 1024, 0, STREAM>>>(partial, mask_row, N, batch, loss);
+  JM_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int jm_layernorm_fwd(const float* x, long ldx, int rows, int dim, const float* gamma, const float* beta,
+                                float eps, jm_bf16* y_bf16, long ldy, float* y_f32, long ldyf, float* mean,
+                                float* rstd, void* stream) {
+  JM_CHECK(dim % 4 == 0 && ldx % 4 == 0, "jm_layernorm_fwd: dim and ldx must be multiples of 4");
+  JM_CHECK(!y_bf16 || ldy % 4 == 0, "jm_layernorm_fwd: ldy must be a multiple of 4");
+  JM_CHECK(!y_f32 || ldyf % 4 == 0, "jm_layernorm_fwd: ldyf must be a multiple of 4");
+  if (rows == 0) return 0;
+  const int grid = (rows + kLnWarps - 1) / kLnWarps;
+  layernorm_fwd_kernel<<<grid, kLnWarps * 32, 0, STREAM>>>(x, ldx, rows, dim, gamma, beta, eps,
+                                                           reinterpret_cast<__nv_bfloat16*>(y_bf16), ldy, y_f32, ldyf,
+                                                           mean, rstd);
+  JM_CUDA(cudaGetLastError());
+  return 0;
+}
+
+static int ln_bwd_blocks(int rows) {
+  const int need = (rows + kLnWarps - 1) / kLnWarps;
+  return need < kLnBwdMaxBlocks ? need : kLnBwdMaxBlocks;
+}
+
+extern "C" size_t jm_layernorm_bwd_workspace(int rows, int dim) {
+  return static_cast<size_t>(ln_bwd_blocks(rows)) * 2 * dim * sizeof(float);
+}
+
+extern "C" int jm_layernorm_bwd(const jm_bf16* dy, long lddy, const float* x, long ldx, const float* mean,
+                                const float* rstd, const float* gamma, int rows, int dim, const float* dres,
+                                long lddres, float* dx, long lddx, jm_bf16* dx_bf16, long lddxb, int row_period,
+                                int row_skip, float* dgamma, float* dbeta, void* workspace, size_t workspace_bytes,
+                                void* stream) {
+  JM_CHECK(dim % 4 == 0 && ldx % 4 == 0 && lddy % 4 == 0, "jm_layernorm_bwd: dim/ld must be multiples of 4");
+  JM_CHECK(dim * 2 * sizeof(float) <= 96 * 1024, "jm_layernorm_bwd: dim %d too large", dim);
+  if (rows == 0) return 0;
+  JM_CHECK(workspace && workspace_bytes >= jm_layernorm_bwd_workspace(rows, dim),
+           "jm_layernorm_bwd: workspace too small");
+  const int grid = ln_bwd_blocks(rows);
+  const size_t smem = static_cast<size_t>(2) * dim * sizeof(float);
+  if (smem > 48 * 1024) {
+    JM_CUDA(cudaFuncSetAttribute(layernorm_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
+  }
+#define JM_LN_BWD_ARGS                                                                                          \
+  reinterpret_cast<const __nv_bfloat16*>(dy), lddy, x, ldx, mean, rstd, gamma, rows, dim, dres, lddres, dx, lddx, \
+      reinterpret_cast<__nv_bfloat16*>(dx_bf16), lddxb, row_period, row_skip, static_cast<float*>(workspace)
+  if (dim <= 128) layernorm_bwd_reg_kernel<1><<<grid, kLnWarps * 32, smem, STREAM>>>(JM_LN_BWD_ARGS);
+  else if (dim <= 256) layernorm_bwd_reg_kernel<2><<<grid, kLnWarps * 32, smem, STREAM>>>(JM_LN_BWD_ARGS);
+  else if (dim <= 512) layernorm_bwd_reg_kernel<4><<<grid, kLnWarps * 32, smem, STREAM>>>(JM_LN_BWD_ARGS);
+  else if (dim <= 768) layernorm_bwd_reg_kernel<6><<<grid, kLnWarps * 32, smem, STREAM>>>(JM_LN_BWD_ARGS);
+  else if (dim <= 1024) layernorm_bwd_reg_kernel<8><<<grid, kLnWarps * 32, smem, STREAM>>>(JM_LN_BWD_ARGS);
+  else if (dim <= 1280) layernorm_bwd_reg_kernel<10><<<grid, kLnWarps * 32, smem, STREAM>>>(JM_LN_BWD_ARGS);
+  else layernorm_bwd_kernel<<<grid, kLnWarps * 32, smem, STREAM>>>(JM_LN_BWD_ARGS);
+#undef JM_LN_BWD_ARGS
+  ln_param_reduce_kernel<<<(2 * dim + 255) / 256, 256, 0, STREAM>>>(static_cast<const float*>(workspace), grid, dim,
+                                                                    dgamma, dbeta);
+  JM_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int jm_fill_cls(float* x, int batch, int T, int J, int dim, const float* cls, void* stream) {
+  if (batch == 0 || J == 0) return 0;
+  fill_cls_kernel<<<dim3(J, batch), 256, 0, STREAM>>>(x, T, J, dim, cls);
+  JM_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int jm_unshuffle_fwd(const float* y, const int32_t* ids_restore, const float* mask_emb,
+                                const float* dec_wpe, int batch, int N, int n, int J, int dim, float* out,
+                                void* stream) {
+  JM_CHECK(dim % 4 == 0, "jm_unshuffle_fwd: dim must be a multiple of 4");
+  if (batch == 0) return 0;
+  unshuffle_fwd_kernel<<<dim3(J + N, batch), 128, 0, STREAM>>>(y, ids_restore, mask_emb, dec_wpe, N, n, J, dim, out);
+  JM_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int jm_unshuffle_bwd(const float* dout, const int32_t* ids_restore, int batch, int N, int n, int J,
+                                int dim, jm_bf16* dy, float* dmask_emb, void* stream) {
+  JM_CHECK(dim % 4 == 0, "jm_unshuffle_bwd: dim must be a multiple of 4");
+  if (batch == 0) return 0;
+  unshuffle_bwd_kernel<<<dim3(J + N, (batch + kUnshufBwdImgs - 1) / kUnshufBwdImgs), 128, 0, STREAM>>>(
+      dout, ids_restore, batch, N, n, J, dim, reinterpret_cast<__nv_bfloat16*>(dy), dmask_emb);
+  JM_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int jm_colsum(const void* x, int is_f32, long ldx, int rows, int cols, int row_period, int row_skip,
+                         float* out, void* stream) {
+  JM_CHECK(cols % 4 == 0 && ldx % 4 == 0, "jm_colsum: cols and ldx must be multiples of 4");
+  if (rows == 0 || cols == 0) return 0;
+  const int gx = (cols + 255) / 256;
+  int gy = (4 * sm_count() + gx - 1) / gx;
+  if (gy < 1) gy = 1;
+  int rows_per_block = (rows + gy - 1) / gy;
+  if (rows_per_block < 32) rows_per_block = 32;
+  gy = (rows + rows_per_block - 1) / rows_per_block;
+  if (is_f32)
+    colsum_kernel<true><<<dim3(gx, gy), 256, 0, STREAM>>>(x, ldx, rows, cols, row_period, row_skip, rows_per_block, out);
+  else
+    colsum_kernel<false><<<dim3(gx, gy), 256, 0, STREAM>>>(x, ldx, rows, cols, row_period, row_skip, rows_per_block, out);
+  JM_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int jm_adamw(float* p, const float* g, float* m, float* v, jm_bf16* p_bf16, long n, long n_decay,
+                        float lr, float b1, float b2, float eps, float wd, float bc1, float bc2, float grad_scale,
+                        void* stream) {
+  JM_CHECK(n % 4 == 0 && n_decay % 4 == 0, "jm_adamw: n and n_decay must be multiples of 4");
+  if (n == 0) return 0;
+  const long n4 = n / 4;
+  long blocks = (n4 + 255) / 256;
+  const long cap = static_cast<long>(sm_count()) * 8;
+  if (blocks > cap) blocks = cap;
+  adamw_kernel<<<static_cast<int>(blocks), 256, 0, STREAM>>>(p, g, m, v, reinterpret_cast<__nv_bfloat16*>(p_bf16), n4,
+                                                            n_decay / 4, lr, b1, b2, eps, wd, bc1, bc2, grad_scale);
+  JM_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int jm_cast_bf16(const float* x, jm_bf16* y, long n, void* stream) {
+  if (n == 0) return 0;
+  long blocks = (n + 255) / 256;
+  const long cap = static_cast<long>(sm_count()) * 8;
+  if (blocks > cap) blocks = cap;
+  cast_bf16_kernel<<<static_cast<int>(blocks), 256, 0, STREAM>>>(x, reinterpret_cast<__nv_bfloat16*>(y), n);
+  JM_CUDA(cudaGetLastError());
+  return 0;
+}

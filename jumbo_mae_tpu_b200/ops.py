@@ -1,0 +1,229 @@
+"""Tensor-level wrappers over the C ABI (include/jumbo_mae_b200.h).
+
+Each function validates dtypes/devices, derives row strides from the tensors and
+enqueues the kernel on torch's current stream.  No arithmetic happens in Python or in
+PyTorch here: without the CUDA library these functions raise.
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import Optional
+
+import torch
+
+from . import _lib
+from ._lib import GemmArgs, check, ptr, stream_ptr
+
+BF16, F32, I32, U8 = torch.bfloat16, torch.float32, torch.int32, torch.uint8
+
+
+def _chk(t: Optional[torch.Tensor], dtype, name: str) -> None:
+    if t is None:
+        return
+    if not t.is_cuda:
+        raise _lib.JmError(f"{name} must be a CUDA tensor")
+    if t.dtype != dtype:
+        raise _lib.JmError(f"{name} must be {dtype}, got {t.dtype}")
+
+
+def _ld(t: Optional[torch.Tensor]) -> int:
+    """Row stride (elements) of a 2-D view whose last dim is contiguous."""
+    if t is None:
+        return 0
+    if t.dim() < 2:
+        return t.shape[-1] if t.dim() == 1 else 0
+    if t.stride(-1) != 1:
+        raise _lib.JmError("innermost dimension must be contiguous")
+    return t.stride(-2)
+
+
+# ------------------------------------------------------------------ masking
+def mask_sort(noise: torch.Tensor, keep: int):
+    """noise f32 [L] -> (ids_shuffle i32 [L], ids_restore i32 [L], mask_row f32 [L])."""
+    _chk(noise, F32, "noise")
+    L = noise.numel()
+    ids_shuffle = torch.empty(L, dtype=I32, device=noise.device)
+    ids_restore = torch.empty(L, dtype=I32, device=noise.device)
+    mask_row = torch.empty(L, dtype=F32, device=noise.device)
+    check(_lib.load().jm_mask_sort(ptr(noise), L, keep, ptr(ids_shuffle), ptr(ids_restore), ptr(mask_row),
+                                   stream_ptr()))
+    return ids_shuffle, ids_restore, mask_row
+
+
+def index_sequence(x: torch.Tensor, ids: torch.Tensor) -> torch.Tensor:
+    _chk(x, F32, "x"), _chk(ids, I32, "ids")
+    x = x.contiguous()
+    B, L, D = x.shape
+    out = torch.empty(B, ids.numel(), D, dtype=F32, device=x.device)
+    check(_lib.load().jm_index_sequence(ptr(x), ptr(ids), B, L, ids.numel(), D, ptr(out), stream_ptr()))
+    return out
+
+
+# ------------------------------------------------------------------ pixels
+def patchify(images: torch.Tensor, patch_size: int, ids: Optional[torch.Tensor], n_sel: int, rows_per_image: int,
+             row_off: int, out: torch.Tensor) -> torch.Tensor:
+    _chk(images, U8, "images"), _chk(ids, I32, "ids"), _chk(out, BF16, "out")
+    B, C, H, W = images.shape
+    assert C == 3 and H == W and images.is_contiguous()
+    check(_lib.load().jm_patchify(ptr(images), B, H, patch_size, ptr(ids), n_sel, rows_per_image, row_off, ptr(out),
+                                  _ld(out), stream_ptr()))
+    return out
+
+
+def extract_patches_u8(images: torch.Tensor, patch_size: int) -> torch.Tensor:
+    _chk(images, U8, "images")
+    B, C, H, W = images.shape
+    g = H // patch_size
+    out = torch.empty(B, g * g, patch_size * patch_size * 3, dtype=F32, device=images.device)
+    check(_lib.load().jm_extract_patches(ptr(images.contiguous()), B, H, patch_size, ptr(out), stream_ptr()))
+    return out
+
+
+def patch_loss_workspace(batch: int, num_patches: int) -> int:
+    return int(_lib.load().jm_patch_loss_workspace(batch, num_patches))
+
+
+def patch_loss(pred: torch.Tensor, images: torch.Tensor, mask_row: torch.Tensor, patch_size: int, num_cls: int,
+               norm_pix: bool, grad_scale: float, loss: torch.Tensor, dpred: Optional[torch.Tensor],
+               workspace: torch.Tensor) -> None:
+    _chk(pred, F32, "pred"), _chk(images, U8, "images"), _chk(mask_row, F32, "mask_row")
+    _chk(loss, F32, "loss"), _chk(dpred, BF16, "dpred")
+    B, _, H, _ = images.shape
+    check(_lib.load().jm_patch_loss(ptr(pred), _ld(pred), ptr(images), ptr(mask_row), B, H, patch_size, num_cls,
+                                    int(norm_pix), grad_scale, ptr(loss), ptr(dpred), _ld(dpred), ptr(workspace),
+                                    workspace.numel() * workspace.element_size(), stream_ptr()))
+
+
+# ------------------------------------------------------------------ LayerNorm
+def layernorm_fwd(x: torch.Tensor, gamma: torch.Tensor, beta: torch.Tensor, eps: float,
+                  y_bf16: Optional[torch.Tensor], y_f32: Optional[torch.Tensor], mean: Optional[torch.Tensor],
+                  rstd: Optional[torch.Tensor], rows: Optional[int] = None, dim: Optional[int] = None,
+                  ldx: Optional[int] = None, ldy: Optional[int] = None, ldyf: Optional[int] = None) -> None:
+    _chk(x, F32, "x"), _chk(gamma, F32, "gamma"), _chk(beta, F32, "beta")
+    _chk(y_bf16, BF16, "y_bf16"), _chk(y_f32, F32, "y_f32"), _chk(mean, F32, "mean"), _chk(rstd, F32, "rstd")
+    rows = x.shape[0] if rows is None else rows
+    dim = x.shape[-1] if dim is None else dim
+    check(_lib.load().jm_layernorm_fwd(ptr(x), _ld(x) if ldx is None else ldx, rows, dim, ptr(gamma), ptr(beta), eps,
+                                       ptr(y_bf16), (_ld(y_bf16) if ldy is None else ldy), ptr(y_f32),
+                                       (_ld(y_f32) if ldyf is None else ldyf), ptr(mean), ptr(rstd), stream_ptr()))
+
+
+def layernorm_bwd_workspace(rows: int, dim: int) -> int:
+    return int(_lib.load().jm_layernorm_bwd_workspace(rows, dim))
+
+
+def layernorm_bwd(dy: torch.Tensor, x: torch.Tensor, mean: torch.Tensor, rstd: torch.Tensor, gamma: torch.Tensor,
+                  dres: Optional[torch.Tensor], dx: Optional[torch.Tensor], dx_bf16: Optional[torch.Tensor],
+                  dgamma: torch.Tensor, dbeta: torch.Tensor, workspace: torch.Tensor, row_period: int = 0,
+                  row_skip: int = 0, rows: Optional[int] = None, dim: Optional[int] = None,
+                  lddy: Optional[int] = None, ldx: Optional[int] = None, lddres: Optional[int] = None,
+                  lddx: Optional[int] = None, lddxb: Optional[int] = None) -> None:
+    _chk(dy, BF16, "dy"), _chk(x, F32, "x"), _chk(mean, F32, "mean"), _chk(rstd, F32, "rstd")
+    _chk(gamma, F32, "gamma"), _chk(dres, F32, "dres"), _chk(dx, F32, "dx"), _chk(dx_bf16, BF16, "dx_bf16")
+    _chk(dgamma, F32, "dgamma"), _chk(dbeta, F32, "dbeta")
+    rows = x.shape[0] if rows is None else rows
+    dim = x.shape[-1] if dim is None else dim
+    check(_lib.load().jm_layernorm_bwd(
+        ptr(dy), _ld(dy) if lddy is None else lddy, ptr(x), _ld(x) if ldx is None else ldx, ptr(mean), ptr(rstd),
+        ptr(gamma), rows, dim, ptr(dres), (_ld(dres) if lddres is None else lddres), ptr(dx),
+        (_ld(dx) if lddx is None else lddx), ptr(dx_bf16), (_ld(dx_bf16) if lddxb is None else lddxb), row_period,
+        row_skip, ptr(dgamma), ptr(dbeta), ptr(workspace), workspace.numel() * workspace.element_size(),
+        stream_ptr()))
+
+
+# ------------------------------------------------------------------ GEMM
+def gemm(A: torch.Tensor, B: torch.Tensor, M: int, N: int, K: int, *, a_mn: bool = False, b_mn: bool = False,
+         lda: Optional[int] = None, ldb: Optional[int] = None,
+         out_f32: Optional[torch.Tensor] = None, ldo_f32: Optional[int] = None,
+         out_bf16: Optional[torch.Tensor] = None, ldo_bf16: Optional[int] = None,
+         out2_bf16: Optional[torch.Tensor] = None, ldo2_bf16: Optional[int] = None,
+         bias: Optional[torch.Tensor] = None,
+         residual: Optional[torch.Tensor] = None, ldr: Optional[int] = None,
+         aux: Optional[torch.Tensor] = None, ldaux: Optional[int] = None,
+         pe: Optional[torch.Tensor] = None, pe_idx: Optional[torch.Tensor] = None,
+         act: int = 0, col_scale: float = 1.0, col_scale_n: int = 0,
+         row_period: int = 0, row_skip: int = 0, row_mask_mode: int = 0,
+         accumulate: bool = False, splits: int = 0, block_n: int = 0) -> None:
+    """D = epilogue(A @ B) through jm_gemm; see include/jumbo_mae_b200.h for the epilogue order."""
+    _chk(A, BF16, "A"), _chk(B, BF16, "B"), _chk(out_f32, F32, "out_f32"), _chk(out_bf16, BF16, "out_bf16")
+    _chk(out2_bf16, BF16, "out2_bf16"), _chk(bias, F32, "bias"), _chk(residual, F32, "residual")
+    _chk(aux, BF16, "aux"), _chk(pe, F32, "pe"), _chk(pe_idx, I32, "pe_idx")
+    a = GemmArgs()
+    a.M, a.N, a.K = M, N, K
+    a.A, a.lda, a.a_mn_major = ptr(A), (_ld(A) if lda is None else lda), int(a_mn)
+    a.B, a.ldb, a.b_mn_major = ptr(B), (_ld(B) if ldb is None else ldb), int(b_mn)
+    a.out_f32, a.ldo_f32 = ptr(out_f32), (_ld(out_f32) if ldo_f32 is None else ldo_f32)
+    a.out_bf16, a.ldo_bf16 = ptr(out_bf16), (_ld(out_bf16) if ldo_bf16 is None else ldo_bf16)
+    a.out2_bf16, a.ldo2_bf16 = ptr(out2_bf16), (_ld(out2_bf16) if ldo2_bf16 is None else ldo2_bf16)
+    a.bias = ptr(bias)
+    a.residual, a.ldr = ptr(residual), (_ld(residual) if ldr is None else ldr)
+    a.aux, a.ldaux = ptr(aux), (_ld(aux) if ldaux is None else ldaux)
+    a.pe, a.pe_idx, a.ldpe = ptr(pe), ptr(pe_idx), _ld(pe)
+    a.act = act
+    a.col_scale, a.col_scale_n = col_scale, col_scale_n
+    a.row_period, a.row_skip, a.row_mask_mode = row_period, row_skip, row_mask_mode
+    a.accumulate, a.splits, a.block_n = int(accumulate), splits, block_n
+    check(_lib.load().jm_gemm(ctypes.byref(a), stream_ptr()))
+
+
+# ------------------------------------------------------------------ attention
+def attention_fwd(qkv: torch.Tensor, batch: int, T: int, heads: int, head_dim: int, out: torch.Tensor,
+                  lse: torch.Tensor) -> None:
+    _chk(qkv, BF16, "qkv"), _chk(out, BF16, "out"), _chk(lse, F32, "lse")
+    check(_lib.load().jm_attention_fwd(ptr(qkv), _ld(qkv), batch, T, heads, head_dim, ptr(out), _ld(out), ptr(lse),
+                                       stream_ptr()))
+
+
+def attention_bwd(qkv: torch.Tensor, out: torch.Tensor, dout: torch.Tensor, lse: torch.Tensor, batch: int, T: int,
+                  heads: int, head_dim: int, q_scale: float, dqkv: torch.Tensor) -> None:
+    _chk(qkv, BF16, "qkv"), _chk(out, BF16, "out"), _chk(dout, BF16, "dout"), _chk(lse, F32, "lse")
+    _chk(dqkv, BF16, "dqkv")
+    check(_lib.load().jm_attention_bwd(ptr(qkv), _ld(qkv), ptr(out), _ld(out), ptr(dout), _ld(dout), ptr(lse), batch,
+                                       T, heads, head_dim, q_scale, ptr(dqkv), _ld(dqkv), stream_ptr()))
+
+
+# ------------------------------------------------------------------ token assembly
+def fill_cls(x: torch.Tensor, batch: int, T: int, J: int, dim: int, cls: torch.Tensor) -> None:
+    _chk(x, F32, "x"), _chk(cls, F32, "cls")
+    check(_lib.load().jm_fill_cls(ptr(x), batch, T, J, dim, ptr(cls), stream_ptr()))
+
+
+def unshuffle_fwd(y: torch.Tensor, ids_restore: torch.Tensor, mask_emb: torch.Tensor, dec_wpe: torch.Tensor,
+                  batch: int, N: int, n: int, J: int, dim: int, out: torch.Tensor) -> None:
+    _chk(y, F32, "y"), _chk(ids_restore, I32, "ids_restore"), _chk(mask_emb, F32, "mask_emb")
+    _chk(dec_wpe, F32, "dec_wpe"), _chk(out, F32, "out")
+    check(_lib.load().jm_unshuffle_fwd(ptr(y), ptr(ids_restore), ptr(mask_emb), ptr(dec_wpe), batch, N, n, J, dim,
+                                       ptr(out), stream_ptr()))
+
+
+def unshuffle_bwd(dout: torch.Tensor, ids_restore: torch.Tensor, batch: int, N: int, n: int, J: int, dim: int,
+                  dy: torch.Tensor, dmask_emb: torch.Tensor) -> None:
+    _chk(dout, F32, "dout"), _chk(ids_restore, I32, "ids_restore"), _chk(dy, BF16, "dy")
+    _chk(dmask_emb, F32, "dmask_emb")
+    check(_lib.load().jm_unshuffle_bwd(ptr(dout), ptr(ids_restore), batch, N, n, J, dim, ptr(dy), ptr(dmask_emb),
+                                       stream_ptr()))
+
+
+def colsum(x: torch.Tensor, rows: int, cols: int, out: torch.Tensor, row_period: int = 0, row_skip: int = 0,
+           ldx: Optional[int] = None) -> None:
+    if x.dtype not in (BF16, F32):
+        raise _lib.JmError("colsum input must be bf16 or f32")
+    _chk(out, F32, "out")
+    check(_lib.load().jm_colsum(ptr(x), int(x.dtype == F32), _ld(x) if ldx is None else ldx, rows, cols, row_period,
+                                row_skip, ptr(out), stream_ptr()))
+
+
+# ------------------------------------------------------------------ optimizer
+def adamw(p: torch.Tensor, g: torch.Tensor, m: torch.Tensor, v: torch.Tensor, p_bf16: Optional[torch.Tensor],
+          n_decay: int, lr: float, b1: float, b2: float, eps: float, wd: float, bc1: float, bc2: float,
+          grad_scale: float = 1.0) -> None:
+    for t, nm in ((p, "p"), (g, "g"), (m, "m"), (v, "v")):
+        _chk(t, F32, nm)
+    _chk(p_bf16, BF16, "p_bf16")
+    check(_lib.load().jm_adamw(ptr(p), ptr(g), ptr(m), ptr(v), ptr(p_bf16), p.numel(), n_decay, lr, b1, b2, eps, wd,
+                               bc1, bc2, grad_scale, stream_ptr()))
+
+
+def cast_bf16(x: torch.Tensor, y: torch.Tensor) -> None:
+    _chk(x, F32, "x"), _chk(y, BF16, "y")
+    check(_lib.load().jm_cast_bf16(ptr(x), ptr(y), x.numel(), stream_ptr()))

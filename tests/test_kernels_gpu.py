@@ -1,0 +1,386 @@
+"""GPU parity tests of the individual kernels, called through the C ABI (ctypes) and
+checked against the CPU oracle (oracle/jumbo_mae_oracle.py) or, for the floating-point
+GEMM/attention at sizes the oracle cannot reach in seconds, against a torch fp32
+restatement of the same operands.  Tolerances are written next to each assert.
+"""
+import math
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import jumbo_mae_oracle as O
+
+pytestmark = pytest.mark.gpu
+
+BF16 = torch.bfloat16
+
+
+@pytest.fixture(scope="module")
+def ops():
+    from jumbo_mae_tpu_b200 import _lib, ops as _ops
+    _lib.require_device()
+    return _ops
+
+
+def dev(t):
+    return t.cuda()
+
+
+# ------------------------------------------------------------------ masking: bit exact
+@pytest.mark.parametrize("L,keep", [(196, 49), (256, 64), (16, 4), (1, 0), (1024, 256), (5, 5)])
+def test_mask_sort_bit_exact(ops, L, keep):
+    rng = np.random.default_rng(L)
+    noise = rng.random(L, dtype=np.float32)
+    ids_s, ids_r, mask = ops.mask_sort(dev(torch.from_numpy(noise)), keep)
+    ws, wr, wm = O.masking_from_noise(noise, keep)
+    assert np.array_equal(ids_s.cpu().numpy(), ws)
+    assert np.array_equal(ids_r.cpu().numpy(), wr)
+    assert np.array_equal(mask.cpu().numpy(), wm)
+
+
+def test_mask_sort_ties_stable(ops):
+    noise = np.array([0.5, 0.25, 0.5, 0.25, 0.5, 0.0, 0.0, 1.0] * 12, dtype=np.float32)
+    ids_s, ids_r, mask = ops.mask_sort(dev(torch.from_numpy(noise)), 24)
+    ws, wr, wm = O.masking_from_noise(noise, 24)
+    assert np.array_equal(ids_s.cpu().numpy(), ws)
+    assert np.array_equal(ids_r.cpu().numpy(), wr)
+    assert np.array_equal(mask.cpu().numpy(), wm)
+    # permutation property at any size: ids_restore[ids_shuffle] == arange
+    assert torch.equal(ids_r[ids_s.long()].cpu(), torch.arange(len(noise), dtype=torch.int32))
+
+
+def test_index_sequence(ops):
+    x = torch.randn(3, 16, 20)
+    ids = torch.tensor([5, 0, 15, 7], dtype=torch.int32)
+    got = ops.index_sequence(dev(x), dev(ids))
+    assert torch.equal(got.cpu(), O.index_sequence(x, ids))          # pure copy: exact
+
+
+# ------------------------------------------------------------------ pixels
+@pytest.mark.parametrize("S,p", [(32, 8), (224, 16), (224, 14)])
+def test_extract_patches_bit_exact(ops, S, p):
+    g = torch.Generator().manual_seed(0)
+    images = torch.randint(0, 256, (2, 3, S, S), generator=g, dtype=torch.uint8)
+    got = ops.extract_patches_u8(dev(images), p)
+    want = O.extract_patches(O.preprocess(images), p)
+    assert torch.equal(got.cpu(), want)                               # same IEEE ops: bit exact
+
+
+def test_patchify_kept_rows(ops):
+    S, p, J = 32, 8, 3
+    g = torch.Generator().manual_seed(1)
+    images = torch.randint(0, 256, (2, 3, S, S), generator=g, dtype=torch.uint8)
+    ids = torch.tensor([7, 2, 11, 0], dtype=torch.int32)
+    P, ld = p * p * 3, 200
+    out = torch.full((2 * (J + 4), ld), 7.0, dtype=BF16, device="cuda")
+    ops.patchify(dev(images), p, dev(ids), 4, J + 4, J, out)
+    want = O.extract_patches(O.preprocess(images), p)[:, ids.long()]
+    got = out.float().cpu().reshape(2, J + 4, ld)
+    assert torch.equal(got[:, :J], torch.zeros(2, J, ld))
+    assert torch.equal(got[:, J:, P:], torch.zeros(2, 4, ld - P))
+    assert torch.equal(got[:, J:, :P], want.to(BF16).float())          # exact after the same bf16 rounding
+
+
+@pytest.mark.parametrize("norm_pix", [False, True])
+def test_patch_loss_and_grad(ops, norm_pix):
+    S, p, J, B = 32, 8, 3, 3
+    N, P = (S // p) ** 2, p * p * 3
+    g = torch.Generator().manual_seed(2)
+    images = torch.randint(0, 256, (B, 3, S, S), generator=g, dtype=torch.uint8)
+    noise = torch.rand(N, generator=g).numpy()
+    _, _, mask_row = O.masking_from_noise(noise, 4)
+    pred = torch.randn(B, J + N, P, generator=g)
+    # oracle
+    pr = pred[:, J:].clone().requires_grad_(True)
+    tgt = O.extract_patches(O.preprocess(images), p)
+    if norm_pix:
+        tgt = (tgt - tgt.mean(-1, keepdim=True)) / torch.sqrt(tgt.var(-1, keepdim=True, unbiased=False) + 1e-6)
+    mask = torch.from_numpy(mask_row)[None].expand(B, N)
+    want = O.patch_mse_loss(pr, tgt, mask)
+    want.backward()
+    # kernel
+    loss = torch.zeros(1, device="cuda")
+    dpred = torch.full((B * (J + N), P), 9.0, dtype=BF16, device="cuda")
+    ws = torch.empty(ops.patch_loss_workspace(B, N), dtype=torch.uint8, device="cuda")
+    ops.patch_loss(dev(pred.reshape(-1, P)), dev(images), dev(torch.from_numpy(mask_row)), p, J, norm_pix, 1.0,
+                   loss, dpred, ws)
+    assert abs(loss.item() - want.item()) < 1e-5 * abs(want.item())   # f32 reduction order only
+    got = dpred.float().cpu().reshape(B, J + N, P)
+    assert torch.equal(got[:, :J], torch.zeros(B, J, P))
+    # bf16 output: 2^-8 relative
+    assert torch.allclose(got[:, J:], pr.grad, rtol=2 ** -7, atol=1e-9)
+
+
+# ------------------------------------------------------------------ LayerNorm
+@pytest.mark.parametrize("rows,D", [(37, 64), (300, 512), (260, 768), (16, 2304), (9, 1280)])
+def test_layernorm_fwd(ops, rows, D):
+    g = torch.Generator().manual_seed(D)
+    x = torch.randn(rows, D, generator=g) * 2 + 0.5
+    gamma, beta = torch.randn(D, generator=g), torch.randn(D, generator=g)
+    want = O.layer_norm(x, gamma, beta)
+    yb = torch.empty(rows, D, dtype=BF16, device="cuda")
+    yf = torch.empty(rows, D, device="cuda")
+    mean, rstd = torch.empty(rows, device="cuda"), torch.empty(rows, device="cuda")
+    ops.layernorm_fwd(dev(x), dev(gamma), dev(beta), 1e-6, yb, yf, mean, rstd)
+    assert torch.allclose(yf.cpu(), want, rtol=1e-5, atol=2e-5)       # f32, different summation order
+    assert torch.allclose(yb.float().cpu(), want, rtol=2 ** -7, atol=1e-6)
+    assert torch.allclose(mean.cpu(), x.mean(-1), atol=1e-5)
+
+
+def test_layernorm_fwd_strided_rows(ops):
+    # the Jumbo view: rows of J*d taken every T*d elements (src/modeling.py:194-197)
+    B, T, J, d = 5, 7, 3, 64
+    x = torch.randn(B, T, d)
+    gamma, beta = torch.randn(J * d), torch.randn(J * d)
+    want = O.layer_norm(x[:, :J].reshape(B, J * d), gamma, beta)
+    yf = torch.empty(B, J * d, device="cuda")
+    xd = dev(x)
+    ops.layernorm_fwd(xd, dev(gamma), dev(beta), 1e-6, None, yf, None, None, rows=B, dim=J * d, ldx=T * d)
+    assert torch.allclose(yf.cpu(), want, rtol=1e-5, atol=2e-5)
+
+
+@pytest.mark.parametrize("rows,D,period,skip", [(64, 64, 0, 0), (500, 512, 0, 0), (260, 768, 52, 3),
+                                                (12, 2304, 0, 0), (40, 1280, 0, 0)])
+def test_layernorm_bwd(ops, rows, D, period, skip):
+    g = torch.Generator().manual_seed(D + rows)
+    x = (torch.randn(rows, D, generator=g) * 2 + 0.5).requires_grad_(True)
+    gamma = torch.randn(D, generator=g).requires_grad_(True)
+    beta = torch.randn(D, generator=g).requires_grad_(True)
+    dy = torch.randn(rows, D, generator=g).to(BF16)
+    dres = torch.randn(rows, D, generator=g)
+    keep = torch.ones(rows, dtype=torch.bool)
+    if period:
+        keep = (torch.arange(rows) % period) >= skip
+    y = O.layer_norm(x, gamma, beta)
+    (y * dy.float() * keep[:, None]).sum().backward()
+    want_dx = x.grad + dres
+    # kernel
+    mean = x.detach().mean(-1)
+    var = torch.clamp((x.detach() ** 2).mean(-1) - mean ** 2, min=0)
+    rstd = torch.rsqrt(var + 1e-6)
+    dx = torch.full((rows, D), 5.0, device="cuda")
+    dxb = torch.full((rows, D), 5.0, dtype=BF16, device="cuda")
+    dgamma = torch.ones(D, device="cuda")          # accumulated into
+    dbeta = torch.ones(D, device="cuda")
+    ws = torch.empty(ops.layernorm_bwd_workspace(rows, D), dtype=torch.uint8, device="cuda")
+    ops.layernorm_bwd(dev(dy), dev(x.detach()), dev(mean), dev(rstd), dev(gamma.detach()), dev(dres), dx, dxb,
+                      dgamma, dbeta, ws, row_period=period, row_skip=skip)
+    got = dx.cpu()
+    assert torch.allclose(got[keep], want_dx[keep], rtol=1e-4, atol=1e-4)
+    assert torch.equal(got[~keep], torch.full_like(got[~keep], 5.0))   # skipped rows untouched
+    assert torch.allclose(dxb.float().cpu()[keep], want_dx[keep], rtol=2 ** -7, atol=1e-3)
+    scale = max(1.0, math.sqrt(rows))
+    assert torch.allclose(dgamma.cpu() - 1, gamma.grad, rtol=1e-4, atol=1e-4 * scale)
+    assert torch.allclose(dbeta.cpu() - 1, beta.grad, rtol=1e-4, atol=1e-4 * scale)
+
+
+# ------------------------------------------------------------------ token assembly
+def test_fill_cls_and_unshuffle(ops):
+    B, N, n, J, d = 3, 16, 4, 3, 32
+    g = torch.Generator().manual_seed(3)
+    noise = torch.rand(N, generator=g).numpy()
+    _, ids_restore, _ = O.masking_from_noise(noise, n)
+    y = torch.randn(B, J + n, d, generator=g)
+    mask_emb = torch.randn(d, generator=g)
+    wpe = torch.randn(N, d, generator=g)
+    out = torch.empty(B * (J + N), d, device="cuda")
+    ids_d = dev(torch.from_numpy(ids_restore))
+    ops.unshuffle_fwd(dev(y.reshape(-1, d)), ids_d, dev(mask_emb), dev(wpe), B, N, n, J, d, out)
+    # src/pretraining.py:96-106 + src/modeling.py:289-292
+    image_x = torch.cat([y[:, J:], mask_emb.expand(B, N - n, d)], dim=1)
+    image_x = O.index_sequence(image_x, torch.from_numpy(ids_restore)) + wpe
+    want = torch.cat([y[:, :J], image_x], dim=1)
+    assert torch.equal(out.cpu().reshape(B, J + N, d), want)          # copies and one f32 add: exact
+
+    dout = torch.randn(B, J + N, d, generator=g)
+    dy = torch.full((B * (J + n), d), 3.0, dtype=BF16, device="cuda")
+    dmask = torch.ones(d, device="cuda")
+    ops.unshuffle_bwd(dev(dout.reshape(-1, d)), ids_d, B, N, n, J, d, dy, dmask)
+    yy = y.clone().requires_grad_(True)
+    me = mask_emb.clone().requires_grad_(True)
+    ix = torch.cat([yy[:, J:], me.expand(B, N - n, d)], dim=1)
+    full = torch.cat([yy[:, :J], O.index_sequence(ix, torch.from_numpy(ids_restore)) + wpe], dim=1)
+    (full * dout).sum().backward()
+    assert torch.equal(dy.float().cpu().reshape(B, J + n, d), yy.grad.to(BF16).float())
+    assert torch.allclose(dmask.cpu() - 1, me.grad, rtol=1e-5, atol=1e-5)
+
+    x = torch.zeros(B * 7, d, device="cuda")
+    cls = torch.randn(J, d, generator=g)
+    ops.fill_cls(x, B, 7, J, d, dev(cls))
+    got = x.cpu().reshape(B, 7, d)
+    assert torch.equal(got[:, :J], cls.expand(B, J, d)) and torch.equal(got[:, J:], torch.zeros(B, 4, d))
+
+
+@pytest.mark.parametrize("f32", [False, True])
+def test_colsum(ops, f32):
+    rows, cols = 1000, 260
+    g = torch.Generator().manual_seed(4)
+    x = torch.randn(rows, 264, generator=g)
+    x = x if f32 else x.to(BF16)
+    out = torch.ones(cols, device="cuda")
+    ops.colsum(dev(x), rows, cols, out, row_period=10, row_skip=2)
+    keep = (torch.arange(rows) % 10) >= 2
+    want = x.float()[keep][:, :cols].sum(0)
+    assert torch.allclose(out.cpu() - 1, want, rtol=1e-4, atol=1e-3)
+
+
+# ------------------------------------------------------------------ AdamW
+def test_adamw_matches_oracle(ops):
+    cfg = O.vit_b16()
+    n, n_decay = 4096, 1024
+    g = torch.Generator().manual_seed(5)
+    p, grad = torch.randn(n, generator=g), torch.randn(n, generator=g) * 1e-3
+    m, v = torch.randn(n, generator=g) * 1e-3, torch.rand(n, generator=g) * 1e-6
+    count, lr = 7, 3e-4
+    want_p, want_m, want_v = p.clone(), m.clone(), v.clone()
+    a, b, c = O.adamw_leaf(p[:n_decay], grad[:n_decay], m[:n_decay], v[:n_decay], count, lr, cfg, decay=True)
+    want_p[:n_decay], want_m[:n_decay], want_v[:n_decay] = a, b, c
+    a, b, c = O.adamw_leaf(p[n_decay:], grad[n_decay:], m[n_decay:], v[n_decay:], count, lr, cfg, decay=False)
+    want_p[n_decay:], want_m[n_decay:], want_v[n_decay:] = a, b, c
+    pd, gd, md, vd = dev(p), dev(grad), dev(m), dev(v)
+    pb = torch.empty(n, dtype=BF16, device="cuda")
+    t = count + 1
+    ops.adamw(pd, gd, md, vd, pb, n_decay, lr, cfg.adam_b1, cfg.adam_b2, cfg.adam_eps, cfg.weight_decay,
+              1 - cfg.adam_b1 ** t, 1 - cfg.adam_b2 ** t, 1.0)
+    # identical f32 formula; allow a couple of ulp for fma contraction / division rounding
+    assert torch.allclose(pd.cpu(), want_p, rtol=3e-7, atol=1e-9)
+    assert torch.allclose(md.cpu(), want_m, rtol=3e-7, atol=1e-12)
+    assert torch.allclose(vd.cpu(), want_v, rtol=3e-7, atol=1e-15)
+    assert torch.equal(pb.float().cpu(), pd.cpu().to(BF16).float())
+
+
+# ------------------------------------------------------------------ GEMM
+def _gemm_ref(A, B, a_mn, b_mn):
+    Af = A.float().t() if a_mn else A.float()
+    Bf = B.float() if b_mn else B.float().t()
+    return Af @ Bf
+
+
+GEMM_CASES = [
+    # M, N, K, a_mn, b_mn, block_n
+    (128, 128, 64, False, False, 128),
+    (512, 384, 320, False, False, 128),
+    (256, 192, 128, False, False, 64),
+    (256, 512, 128, False, False, 256),
+    (512, 384, 320, False, True, 128),
+    (384, 512, 192, False, True, 256),
+    (384, 256, 1000, True, True, 128),
+    (384, 256, 328, True, False, 64),
+    (200, 588, 72, False, True, 0),          # ragged M, N, K (ViT-H/14 head width)
+    (1, 64, 8, False, True, 0),              # single row
+    (4160, 2304, 768, False, True, 0),       # persistent: more tiles than SMs
+]
+
+
+@pytest.mark.parametrize("M,N,K,a_mn,b_mn,bn", GEMM_CASES)
+def test_gemm_plain(ops, M, N, K, a_mn, b_mn, bn):
+    g = torch.Generator(device="cuda").manual_seed(M + N + K)
+    A = torch.randn((K, M) if a_mn else (M, K), generator=g, device="cuda").to(BF16)
+    B = torch.randn((K, N) if b_mn else (N, K), generator=g, device="cuda").to(BF16)
+    out = torch.full((M, N), float("nan"), device="cuda")
+    ops.gemm(A, B, M, N, K, a_mn=a_mn, b_mn=b_mn, out_f32=out, block_n=bn)
+    ref = _gemm_ref(A, B, a_mn, b_mn)
+    # exact bf16 products, f32 accumulation in a different order: 1e-5 relative to the row scale
+    assert (out - ref).abs().max().item() <= 2e-5 * ref.abs().max().item() * math.sqrt(K)
+
+
+def test_gemm_epilogue_bias_scale_residual_bf16(ops):
+    M, N, K = 300, 256, 192
+    g = torch.Generator(device="cuda").manual_seed(0)
+    A = torch.randn(M, K, generator=g, device="cuda").to(BF16)
+    W = (torch.randn(K, N, generator=g, device="cuda") * 0.1).to(BF16)
+    bias = torch.randn(N, generator=g, device="cuda")
+    res = torch.randn(M, N, generator=g, device="cuda")
+    out = torch.empty(M, N, device="cuda")
+    outb = torch.empty(M, N, dtype=BF16, device="cuda")
+    ops.gemm(A, W, M, N, K, b_mn=True, out_f32=out, out_bf16=outb, bias=bias, residual=res, col_scale=0.125,
+             col_scale_n=64)
+    ref = A.float() @ W.float() + bias
+    ref[:, :64] *= 0.125
+    ref = ref + res
+    assert torch.allclose(out, ref, rtol=1e-5, atol=1e-4)
+    assert torch.allclose(outb.float(), ref, rtol=2 ** -7, atol=1e-3)
+
+
+def test_gemm_epilogue_gelu_fwd_and_bwd_with_row_mask(ops):
+    M, N, K, T, J = 28, 128, 64, 7, 3
+    g = torch.Generator(device="cuda").manual_seed(1)
+    A = torch.randn(M, K, generator=g, device="cuda").to(BF16)
+    W = (torch.randn(K, N, generator=g, device="cuda") * 0.2).to(BF16)
+    bias = torch.randn(N, generator=g, device="cuda")
+    h = torch.empty(M, N, dtype=BF16, device="cuda")
+    gl = torch.empty(M, N, dtype=BF16, device="cuda")
+    ops.gemm(A, W, M, N, K, b_mn=True, out_bf16=h, out2_bf16=gl, bias=bias, act=1, row_period=T, row_skip=J,
+             row_mask_mode=1)
+    keep = ((torch.arange(M, device="cuda") % T) >= J)[:, None]
+    pre = (A.float() @ W.float() + bias) * keep
+    assert torch.allclose(h.float(), pre, rtol=2 ** -7, atol=1e-3)
+    assert torch.allclose(gl.float(), O.gelu_tanh(pre.cpu()).cuda() * keep, rtol=2 ** -7, atol=2e-3)
+    # backward: dH = (dY @ W2^T) * gelu'(h), CLS rows zeroed
+    dY = torch.randn(M, K, generator=g, device="cuda").to(BF16)
+    W2 = (torch.randn(N, K, generator=g, device="cuda") * 0.2).to(BF16)          # Flax kernel [in=N, out=K]
+    dH = torch.empty(M, N, dtype=BF16, device="cuda")
+    ops.gemm(dY, W2, M, N, K, b_mn=False, out_bf16=dH, aux=h, act=2, row_period=T, row_skip=J, row_mask_mode=1)
+    hh = h.float().cpu().requires_grad_(True)
+    O.gelu_tanh(hh).sum().backward()
+    ref = (dY.float() @ W2.float().t()) * hh.grad.cuda() * keep
+    assert torch.allclose(dH.float(), ref, rtol=2 ** -6, atol=2e-3)
+
+
+def test_gemm_epilogue_posemb_and_skip_rows(ops):
+    M, N, K, T, J, n = 21, 64, 72, 7, 3, 4
+    g = torch.Generator(device="cuda").manual_seed(2)
+    A = torch.randn(M, K + 8, generator=g, device="cuda").to(BF16)
+    W = (torch.randn(K, N, generator=g, device="cuda") * 0.2).to(BF16)
+    bias = torch.randn(N, generator=g, device="cuda")
+    pe = torch.randn(16, N, generator=g, device="cuda")
+    idx = torch.tensor([5, 0, 15, 9], dtype=torch.int32, device="cuda")
+    out = torch.full((M, N), -7.0, device="cuda")
+    ops.gemm(A, W, M, N, K, b_mn=True, out_f32=out, bias=bias, pe=pe, pe_idx=idx, row_period=T, row_skip=J,
+             row_mask_mode=2)
+    ref = A[:, :K].float() @ W.float() + bias
+    r = torch.arange(M, device="cuda") % T
+    keep = r >= J
+    ref[keep] += pe[idx[(r[keep] - J).long()].long()]
+    assert torch.allclose(out[keep], ref[keep], rtol=1e-5, atol=1e-4)
+    assert torch.equal(out[~keep], torch.full_like(out[~keep], -7.0))
+
+
+def test_gemm_weight_grad_accumulate_and_split_k(ops):
+    # dW += X^T dY with both operands token-major (MN-major), split-K over tokens
+    tokens, din, dout = 3000, 256, 384
+    g = torch.Generator(device="cuda").manual_seed(3)
+    X = torch.randn(tokens, din, generator=g, device="cuda").to(BF16)
+    dY = torch.randn(tokens, dout, generator=g, device="cuda").to(BF16)
+    dW = torch.ones(din, dout, device="cuda")
+    ops.gemm(X, dY, din, dout, tokens, a_mn=True, b_mn=True, out_f32=dW, accumulate=True)
+    ref = X.float().t() @ dY.float() + 1
+    assert torch.allclose(dW, ref, rtol=1e-4, atol=2e-3)
+    dW2 = torch.zeros(din, dout, device="cuda")
+    ops.gemm(X, dY, din, dout, tokens, a_mn=True, b_mn=True, out_f32=dW2, accumulate=True, splits=5, block_n=128)
+    assert torch.allclose(dW2, ref - 1, rtol=1e-4, atol=2e-3)
+
+
+def test_gemm_strided_jumbo_store(ops):
+    # Jumbo FFN output written straight into the CLS rows of x: row stride T*d (src/modeling.py:203-204)
+    B, T, J, d = 6, 7, 3, 64
+    g = torch.Generator(device="cuda").manual_seed(4)
+    A = torch.randn(B, 4 * J * d, generator=g, device="cuda").to(BF16)
+    W = (torch.randn(4 * J * d, J * d, generator=g, device="cuda") * 0.05).to(BF16)
+    res = torch.randn(B, J * d, generator=g, device="cuda")
+    x = torch.zeros(B, T, d, device="cuda")
+    ops.gemm(A, W, B, J * d, 4 * J * d, b_mn=True, out_f32=x, ldo_f32=T * d, residual=res)
+    ref = A.float() @ W.float() + res
+    assert torch.allclose(x[:, :J].reshape(B, J * d), ref, rtol=1e-5, atol=1e-3)
+    assert torch.equal(x[:, J:], torch.zeros(B, T - J, d, device="cuda"))
+
+
+def test_gemm_rejects_bad_arguments(ops):
+    from jumbo_mae_tpu_b200._lib import JmError
+    A = torch.zeros(8, 12, dtype=BF16, device="cuda")
+    B = torch.zeros(12, 8, dtype=BF16, device="cuda")
+    with pytest.raises(JmError):
+        ops.gemm(A, B, 8, 8, 12, b_mn=True, out_f32=torch.zeros(8, 8, device="cuda"), lda=12)   # ld % 8 != 0
+    with pytest.raises(JmError):
+        ops.gemm(A, B, 8, 8, 12, b_mn=True)                                                     # no output
