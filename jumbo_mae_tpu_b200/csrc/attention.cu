@@ -1,9 +1,474 @@
+// Fused short-sequence attention, forward and backward, for the 49+J / 196+J token counts of
+// the MAE encoder / decoder (src/modeling.py:136-137: softmax(q k^T) v per image and head).
+//
+// One CTA per (image, head); the whole K and V of that pair live in shared memory and every
+// warp owns a 16-row strip (flash-attention-2 style: scores never leave registers, online
+// softmax over 64-key chunks).  The backward recomputes the scores from the saved
+// log-sum-exp: phase 1 (warp = 16 queries) produces dQ, phase 2 (warp = 16 keys) produces
+// dK and dV, so no cross-warp reduction or atomics are needed.
+//
+// Tensor-core path: mma.sync.m16n8k16 bf16 with ldmatrix operands.  These tiles are 16..272
+// rows by 32..80 columns -- far below a 128-row tcgen05 tile -- and the op is ~3 % of the
+// step's FLOPs, so the legacy warp-level MMA is the better fit here.
 #include "../../include/jumbo_mae_b200.h"
 #include "common.cuh"
-extern "C" int jm_attention_fwd(const jm_bf16*, long, int, int, int, int, jm_bf16*, long, float*, void*) {
-  return jm::fail("jm_attention_fwd: not built yet");
+
+namespace jm {
+
+constexpr float kLog2e = 1.4426950408889634f;
+
+__device__ __forceinline__ void ldsm_x4(uint32_t (&r)[4], uint32_t addr) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0, %1, %2, %3}, [%4];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
+               : "r"(addr));
 }
-extern "C" int jm_attention_bwd(const jm_bf16*, long, const jm_bf16*, long, const jm_bf16*, long, const float*, int,
-                                int, int, int, float, jm_bf16*, long, void*) {
-  return jm::fail("jm_attention_bwd: not built yet");
+__device__ __forceinline__ void ldsm_x4_t(uint32_t (&r)[4], uint32_t addr) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0, %1, %2, %3}, [%4];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
+               : "r"(addr));
+}
+__device__ __forceinline__ void mma_bf16(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+  asm volatile(
+      "mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, {%8, %9}, "
+      "{%0, %1, %2, %3};"
+      : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+      : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+
+// Address helpers (element offsets inside a [rows][LDS] bf16 tile), lane-dependent:
+//   A operand 16x16 at (r0, k0), row-major                      -> a_off
+//   B operand from [n][k] storage, two n-tiles (n0, n0+8), k0   -> bn_off   (plain ldmatrix)
+//   B operand from [k][n] storage, k0 (16 rows), n-tiles n0,n0+8 -> bt_off  (ldmatrix.trans)
+template <int LDS>
+__device__ __forceinline__ int a_off(int lane, int r0, int k0) {
+  return (r0 + (lane & 7) + ((lane >> 3) & 1) * 8) * LDS + k0 + (lane >> 4) * 8;
+}
+template <int LDS>
+__device__ __forceinline__ int bn_off(int lane, int n0, int k0) {
+  return (n0 + (lane & 7) + (lane >> 4) * 8) * LDS + k0 + ((lane >> 3) & 1) * 8;
+}
+template <int LDS>
+__device__ __forceinline__ int bt_off(int lane, int k0, int n0) {
+  return (k0 + (lane & 7) + ((lane >> 3) & 1) * 8) * LDS + n0 + (lane >> 4) * 8;
+}
+
+// Cooperative load of rows [0, rows_pad) x HD bf16 of one head into a padded smem tile; rows >= T are zero.
+template <int HD, int LDS>
+__device__ __forceinline__ void load_head(const __nv_bfloat16* __restrict__ src, long ld, int T, int rows_pad,
+                                          __nv_bfloat16* dst) {
+  constexpr int CH = HD / 8;
+  for (int idx = threadIdx.x; idx < rows_pad * CH; idx += blockDim.x) {
+    const int row = idx / CH, ch = idx - row * CH;
+    uint4 v = make_uint4(0u, 0u, 0u, 0u);
+    if (row < T) v = *reinterpret_cast<const uint4*>(src + row * ld + ch * 8);
+    *reinterpret_cast<uint4*>(dst + row * LDS + ch * 8) = v;
+  }
+}
+
+template <int HD>
+__global__ void attn_fwd_kernel(const __nv_bfloat16* __restrict__ qkv, long ldqkv, int T, int heads,
+                                __nv_bfloat16* __restrict__ out, long ldo, float* __restrict__ lse) {
+  constexpr int LDS = HD + 8;
+  extern __shared__ __align__(16) uint8_t smem_raw[];
+  __nv_bfloat16* sK = reinterpret_cast<__nv_bfloat16*>(smem_raw);
+  const int Tp = (T + 63) / 64 * 64;
+  const int Tq = (T + 15) / 16 * 16;
+  const int nstrips = Tq / 16, nwarps = blockDim.x >> 5;
+  __nv_bfloat16* sV = sK + Tp * LDS;
+  __nv_bfloat16* sQ = sV + Tp * LDS;
+  const int b = blockIdx.x / heads, h = blockIdx.x - b * heads;
+  const int d = heads * HD;
+  const __nv_bfloat16* base = qkv + static_cast<long>(b) * T * ldqkv + h * HD;
+  load_head<HD, LDS>(base, ldqkv, T, Tq, sQ);
+  load_head<HD, LDS>(base + d, ldqkv, T, Tp, sK);
+  load_head<HD, LDS>(base + 2 * d, ldqkv, T, Tp, sV);
+  __syncthreads();
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int g = lane >> 2, t4 = lane & 3;
+  const uint32_t sQa = smem_u32(sQ), sKa = smem_u32(sK), sVa = smem_u32(sV);
+
+  for (int strip = warp; strip < nstrips; strip += nwarps) {
+  const int row0 = strip * 16;
+  uint32_t qf[HD / 16][4];
+#pragma unroll
+  for (int ks = 0; ks < HD / 16; ++ks) ldsm_x4(qf[ks], sQa + 2 * a_off<LDS>(lane, row0, ks * 16));
+
+  float o[HD / 8][4];
+#pragma unroll
+  for (int i = 0; i < HD / 8; ++i) o[i][0] = o[i][1] = o[i][2] = o[i][3] = 0.f;
+  float m[2] = {-INFINITY, -INFINITY}, l[2] = {0.f, 0.f};
+
+  for (int kc = 0; kc < Tp; kc += 64) {
+    float s[8][4];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) s[i][0] = s[i][1] = s[i][2] = s[i][3] = 0.f;
+#pragma unroll
+    for (int ks = 0; ks < HD / 16; ++ks) {
+#pragma unroll
+      for (int np = 0; np < 4; ++np) {
+        uint32_t kb[4];
+        ldsm_x4(kb, sKa + 2 * bn_off<LDS>(lane, kc + np * 16, ks * 16));
+        mma_bf16(s[2 * np], qf[ks], kb[0], kb[1]);
+        mma_bf16(s[2 * np + 1], qf[ks], kb[2], kb[3]);
+      }
+    }
+    float mx[2] = {-INFINITY, -INFINITY};
+#pragma unroll
+    for (int nt = 0; nt < 8; ++nt)
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const int key = kc + nt * 8 + 2 * t4 + (e & 1);
+        if (key >= T) s[nt][e] = -INFINITY;
+        mx[e >> 1] = fmaxf(mx[e >> 1], s[nt][e]);
+      }
+    float alpha[2];
+#pragma unroll
+    for (int r = 0; r < 2; ++r) {
+      mx[r] = fmaxf(mx[r], __shfl_xor_sync(0xffffffffu, mx[r], 1));
+      mx[r] = fmaxf(mx[r], __shfl_xor_sync(0xffffffffu, mx[r], 2));
+      const float mn = fmaxf(m[r], mx[r]);
+      alpha[r] = exp2f((m[r] - mn) * kLog2e);
+      m[r] = mn;
+      l[r] *= alpha[r];
+    }
+#pragma unroll
+    for (int nt = 0; nt < 8; ++nt)
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const float p = exp2f((s[nt][e] - m[e >> 1]) * kLog2e);
+        s[nt][e] = p;
+        l[e >> 1] += p;
+      }
+#pragma unroll
+    for (int i = 0; i < HD / 8; ++i) {
+      o[i][0] *= alpha[0], o[i][1] *= alpha[0];
+      o[i][2] *= alpha[1], o[i][3] *= alpha[1];
+    }
+#pragma unroll
+    for (int kk = 0; kk < 4; ++kk) {
+      uint32_t a[4];
+      a[0] = pack_bf16(s[2 * kk][0], s[2 * kk][1]);
+      a[1] = pack_bf16(s[2 * kk][2], s[2 * kk][3]);
+      a[2] = pack_bf16(s[2 * kk + 1][0], s[2 * kk + 1][1]);
+      a[3] = pack_bf16(s[2 * kk + 1][2], s[2 * kk + 1][3]);
+#pragma unroll
+      for (int np = 0; np < HD / 16; ++np) {
+        uint32_t vb[4];
+        ldsm_x4_t(vb, sVa + 2 * bt_off<LDS>(lane, kc + kk * 16, np * 16));
+        mma_bf16(o[2 * np], a, vb[0], vb[1]);
+        mma_bf16(o[2 * np + 1], a, vb[2], vb[3]);
+      }
+    }
+  }
+#pragma unroll
+  for (int r = 0; r < 2; ++r) {
+    l[r] += __shfl_xor_sync(0xffffffffu, l[r], 1);
+    l[r] += __shfl_xor_sync(0xffffffffu, l[r], 2);
+    const int row = row0 + g + 8 * r;
+    if (row < T) {
+      const float inv = 1.0f / l[r];
+      __nv_bfloat16* dst = out + (static_cast<long>(b) * T + row) * ldo + h * HD + 2 * t4;
+#pragma unroll
+      for (int i = 0; i < HD / 8; ++i)
+        *reinterpret_cast<uint32_t*>(dst + i * 8) = pack_bf16(o[i][2 * r] * inv, o[i][2 * r + 1] * inv);
+      if (t4 == 0) lse[(static_cast<long>(b) * heads + h) * T + row] = m[r] + logf(l[r]);
+    }
+  }
+  }  // strip
+}
+
+template <int HD>
+__global__ void attn_bwd_kernel(const __nv_bfloat16* __restrict__ qkv, long ldqkv,
+                                const __nv_bfloat16* __restrict__ out, long ldo,
+                                const __nv_bfloat16* __restrict__ dout, long lddo, const float* __restrict__ lse,
+                                int T, int heads, float q_scale, __nv_bfloat16* __restrict__ dqkv, long lddqkv) {
+  constexpr int LDS = HD + 8;
+  extern __shared__ __align__(16) uint8_t smem_raw[];
+  const int Tp = (T + 63) / 64 * 64;
+  __nv_bfloat16* sQ = reinterpret_cast<__nv_bfloat16*>(smem_raw);
+  __nv_bfloat16* sK = sQ + Tp * LDS;
+  __nv_bfloat16* sV = sK + Tp * LDS;
+  __nv_bfloat16* sdO = sV + Tp * LDS;
+  float* sL = reinterpret_cast<float*>(sdO + Tp * LDS);
+  float* sD = sL + Tp;
+  const int b = blockIdx.x / heads, h = blockIdx.x - b * heads;
+  const int d = heads * HD;
+  const __nv_bfloat16* base = qkv + static_cast<long>(b) * T * ldqkv + h * HD;
+  load_head<HD, LDS>(base, ldqkv, T, Tp, sQ);
+  load_head<HD, LDS>(base + d, ldqkv, T, Tp, sK);
+  load_head<HD, LDS>(base + 2 * d, ldqkv, T, Tp, sV);
+  load_head<HD, LDS>(dout + static_cast<long>(b) * T * lddo + h * HD, lddo, T, Tp, sdO);
+  __syncthreads();
+  // D[row] = sum_c dO[row, c] * O[row, c]; padded rows get lse = +big so that their P is exactly 0
+  for (int row = threadIdx.x; row < Tp; row += blockDim.x) {
+    float acc = 0.f, L = 1e30f;
+    if (row < T) {
+      const __nv_bfloat16* orow = out + (static_cast<long>(b) * T + row) * ldo + h * HD;
+#pragma unroll
+      for (int c = 0; c < HD; c += 8) {
+        const uint4 ov = *reinterpret_cast<const uint4*>(orow + c);
+        const uint4 dv = *reinterpret_cast<const uint4*>(sdO + row * LDS + c);
+        const uint32_t oo[4] = {ov.x, ov.y, ov.z, ov.w}, dd[4] = {dv.x, dv.y, dv.z, dv.w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const float2 a = unpack_bf16(oo[j]), c2 = unpack_bf16(dd[j]);
+          acc += a.x * c2.x + a.y * c2.y;
+        }
+      }
+      L = lse[(static_cast<long>(b) * heads + h) * T + row];
+    }
+    sD[row] = acc;
+    sL[row] = L;
+  }
+  __syncthreads();
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int g = lane >> 2, t4 = lane & 3;
+  const int nstrips = (T + 15) / 16, nwarps = blockDim.x >> 5;
+  const uint32_t sQa = smem_u32(sQ), sKa = smem_u32(sK), sVa = smem_u32(sV), sdOa = smem_u32(sdO);
+
+  // ---------------- phase 1: a warp's 16 queries -> dQ
+  for (int strip = warp; strip < nstrips; strip += nwarps) {
+    const int row0 = strip * 16;
+    uint32_t qf[HD / 16][4], dof[HD / 16][4];
+#pragma unroll
+    for (int ks = 0; ks < HD / 16; ++ks) {
+      ldsm_x4(qf[ks], sQa + 2 * a_off<LDS>(lane, row0, ks * 16));
+      ldsm_x4(dof[ks], sdOa + 2 * a_off<LDS>(lane, row0, ks * 16));
+    }
+    const float Lr[2] = {sL[row0 + g], sL[row0 + g + 8]};
+    const float Dr[2] = {sD[row0 + g], sD[row0 + g + 8]};
+    float dq[HD / 8][4];
+#pragma unroll
+    for (int i = 0; i < HD / 8; ++i) dq[i][0] = dq[i][1] = dq[i][2] = dq[i][3] = 0.f;
+    for (int kc = 0; kc < Tp; kc += 32) {
+      float s[4][4], dp[4][4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int e = 0; e < 4; ++e) s[i][e] = 0.f, dp[i][e] = 0.f;
+#pragma unroll
+      for (int ks = 0; ks < HD / 16; ++ks) {
+#pragma unroll
+        for (int np = 0; np < 2; ++np) {
+          uint32_t kb[4], vb[4];
+          ldsm_x4(kb, sKa + 2 * bn_off<LDS>(lane, kc + np * 16, ks * 16));
+          mma_bf16(s[2 * np], qf[ks], kb[0], kb[1]);
+          mma_bf16(s[2 * np + 1], qf[ks], kb[2], kb[3]);
+          ldsm_x4(vb, sVa + 2 * bn_off<LDS>(lane, kc + np * 16, ks * 16));
+          mma_bf16(dp[2 * np], dof[ks], vb[0], vb[1]);
+          mma_bf16(dp[2 * np + 1], dof[ks], vb[2], vb[3]);
+        }
+      }
+#pragma unroll
+      for (int nt = 0; nt < 4; ++nt)
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const int key = kc + nt * 8 + 2 * t4 + (e & 1);
+          const float p = key < T ? exp2f((s[nt][e] - Lr[e >> 1]) * kLog2e) : 0.f;
+          s[nt][e] = p * (dp[nt][e] - Dr[e >> 1]);   // dS
+        }
+#pragma unroll
+      for (int kk = 0; kk < 2; ++kk) {
+        uint32_t a[4];
+        a[0] = pack_bf16(s[2 * kk][0], s[2 * kk][1]);
+        a[1] = pack_bf16(s[2 * kk][2], s[2 * kk][3]);
+        a[2] = pack_bf16(s[2 * kk + 1][0], s[2 * kk + 1][1]);
+        a[3] = pack_bf16(s[2 * kk + 1][2], s[2 * kk + 1][3]);
+#pragma unroll
+        for (int np = 0; np < HD / 16; ++np) {
+          uint32_t kb[4];
+          ldsm_x4_t(kb, sKa + 2 * bt_off<LDS>(lane, kc + kk * 16, np * 16));
+          mma_bf16(dq[2 * np], a, kb[0], kb[1]);
+          mma_bf16(dq[2 * np + 1], a, kb[2], kb[3]);
+        }
+      }
+    }
+#pragma unroll
+    for (int r = 0; r < 2; ++r) {
+      const int row = row0 + g + 8 * r;
+      if (row < T) {
+        __nv_bfloat16* dst = dqkv + (static_cast<long>(b) * T + row) * lddqkv + h * HD + 2 * t4;
+#pragma unroll
+        for (int i = 0; i < HD / 8; ++i)
+          *reinterpret_cast<uint32_t*>(dst + i * 8) = pack_bf16(dq[i][2 * r] * q_scale, dq[i][2 * r + 1] * q_scale);
+      }
+    }
+  }
+
+  // ---------------- phase 2: a warp's 16 keys -> dK, dV (transposed problem)
+  for (int strip = warp; strip < nstrips; strip += nwarps) {
+    const int row0 = strip * 16;
+    uint32_t kf[HD / 16][4], vf[HD / 16][4];
+#pragma unroll
+    for (int ks = 0; ks < HD / 16; ++ks) {
+      ldsm_x4(kf[ks], sKa + 2 * a_off<LDS>(lane, row0, ks * 16));
+      ldsm_x4(vf[ks], sVa + 2 * a_off<LDS>(lane, row0, ks * 16));
+    }
+    float dk[HD / 8][4], dv[HD / 8][4];
+#pragma unroll
+    for (int i = 0; i < HD / 8; ++i)
+#pragma unroll
+      for (int e = 0; e < 4; ++e) dk[i][e] = 0.f, dv[i][e] = 0.f;
+    for (int qc = 0; qc < Tp; qc += 32) {
+      float st[4][4], dpt[4][4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int e = 0; e < 4; ++e) st[i][e] = 0.f, dpt[i][e] = 0.f;
+#pragma unroll
+      for (int ks = 0; ks < HD / 16; ++ks) {
+#pragma unroll
+        for (int np = 0; np < 2; ++np) {
+          uint32_t qb[4], ob[4];
+          ldsm_x4(qb, sQa + 2 * bn_off<LDS>(lane, qc + np * 16, ks * 16));
+          mma_bf16(st[2 * np], kf[ks], qb[0], qb[1]);
+          mma_bf16(st[2 * np + 1], kf[ks], qb[2], qb[3]);
+          ldsm_x4(ob, sdOa + 2 * bn_off<LDS>(lane, qc + np * 16, ks * 16));
+          mma_bf16(dpt[2 * np], vf[ks], ob[0], ob[1]);
+          mma_bf16(dpt[2 * np + 1], vf[ks], ob[2], ob[3]);
+        }
+      }
+      uint32_t pa[2][4], dsa[2][4];
+#pragma unroll
+      for (int nt = 0; nt < 4; ++nt) {
+        const int q0 = qc + nt * 8 + 2 * t4;
+        const float2 L2 = *reinterpret_cast<const float2*>(sL + q0);
+        const float2 D2 = *reinterpret_cast<const float2*>(sD + q0);
+        float p[4], ds[4];
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const float L = (e & 1) ? L2.y : L2.x, D = (e & 1) ? D2.y : D2.x;
+          p[e] = exp2f((st[nt][e] - L) * kLog2e);
+          ds[e] = p[e] * (dpt[nt][e] - D);
+        }
+        pa[nt >> 1][(nt & 1) * 2 + 0] = pack_bf16(p[0], p[1]);
+        pa[nt >> 1][(nt & 1) * 2 + 1] = pack_bf16(p[2], p[3]);
+        dsa[nt >> 1][(nt & 1) * 2 + 0] = pack_bf16(ds[0], ds[1]);
+        dsa[nt >> 1][(nt & 1) * 2 + 1] = pack_bf16(ds[2], ds[3]);
+      }
+#pragma unroll
+      for (int kk = 0; kk < 2; ++kk) {
+#pragma unroll
+        for (int np = 0; np < HD / 16; ++np) {
+          uint32_t ob[4], qb[4];
+          ldsm_x4_t(ob, sdOa + 2 * bt_off<LDS>(lane, qc + kk * 16, np * 16));
+          mma_bf16(dv[2 * np], pa[kk], ob[0], ob[1]);
+          mma_bf16(dv[2 * np + 1], pa[kk], ob[2], ob[3]);
+          ldsm_x4_t(qb, sQa + 2 * bt_off<LDS>(lane, qc + kk * 16, np * 16));
+          mma_bf16(dk[2 * np], dsa[kk], qb[0], qb[1]);
+          mma_bf16(dk[2 * np + 1], dsa[kk], qb[2], qb[3]);
+        }
+      }
+    }
+#pragma unroll
+    for (int r = 0; r < 2; ++r) {
+      const int row = row0 + g + 8 * r;
+      if (row < T) {
+        __nv_bfloat16* dst = dqkv + (static_cast<long>(b) * T + row) * lddqkv + h * HD + 2 * t4;
+#pragma unroll
+        for (int i = 0; i < HD / 8; ++i) {
+          *reinterpret_cast<uint32_t*>(dst + d + i * 8) = pack_bf16(dk[i][2 * r], dk[i][2 * r + 1]);
+          *reinterpret_cast<uint32_t*>(dst + 2 * d + i * 8) = pack_bf16(dv[i][2 * r], dv[i][2 * r + 1]);
+        }
+      }
+    }
+  }
+}
+
+static size_t fwd_smem(int T, int hd) {
+  const int Tp = (T + 63) / 64 * 64, Tq = (T + 15) / 16 * 16;
+  return static_cast<size_t>(2 * Tp + Tq) * (hd + 8) * 2;
+}
+static size_t bwd_smem(int T, int hd) {
+  const int Tp = (T + 63) / 64 * 64;
+  return static_cast<size_t>(4 * Tp) * (hd + 8) * 2 + static_cast<size_t>(2 * Tp) * 4;
+}
+
+// Warps per CTA: one per 16-row strip when the register file allows it, otherwise the strips
+// are dealt round-robin to fewer warps.  Each of the 4 SM sub-partitions holds 16384 registers
+// and warps are spread evenly over them, so ceil(warps / 4) * 32 * regs must fit in 16384.
+static int pick_warps(const void* kern, int T, int* warps) {
+  cudaFuncAttributes fa;
+  JM_CUDA(cudaFuncGetAttributes(&fa, kern));
+  const int per_warp = (fa.numRegs + 7) / 8 * 8 * 32;
+  int max_warps = (16384 / per_warp) * 4;
+  if (max_warps > 32) max_warps = 32;
+  JM_CHECK(max_warps >= 1, "attention kernel needs %d registers per thread", fa.numRegs);
+  const int strips = (T + 15) / 16;
+  const int rounds = (strips + max_warps - 1) / max_warps;
+  *warps = (strips + rounds - 1) / rounds;
+  return 0;
+}
+
+template <int HD>
+static int launch_fwd(const jm_bf16* qkv, long ldqkv, int batch, int T, int heads, jm_bf16* out, long ldo,
+                      float* lse, cudaStream_t stream) {
+  const size_t smem = fwd_smem(T, HD);
+  auto kern = attn_fwd_kernel<HD>;
+  if (smem > 48 * 1024) JM_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  int warps = 0;
+  if (pick_warps(reinterpret_cast<const void*>(kern), T, &warps)) return 1;
+  const int threads = warps * 32;
+  kern<<<batch * heads, threads, smem, stream>>>(reinterpret_cast<const __nv_bfloat16*>(qkv), ldqkv, T, heads,
+                                                 reinterpret_cast<__nv_bfloat16*>(out), ldo, lse);
+  JM_CUDA(cudaGetLastError());
+  return 0;
+}
+
+template <int HD>
+static int launch_bwd(const jm_bf16* qkv, long ldqkv, const jm_bf16* out, long ldo, const jm_bf16* dout, long lddo,
+                      const float* lse, int batch, int T, int heads, float q_scale, jm_bf16* dqkv, long lddqkv,
+                      cudaStream_t stream) {
+  const size_t smem = bwd_smem(T, HD);
+  auto kern = attn_bwd_kernel<HD>;
+  if (smem > 48 * 1024) JM_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  int warps = 0;
+  if (pick_warps(reinterpret_cast<const void*>(kern), T, &warps)) return 1;
+  const int threads = warps * 32;
+  kern<<<batch * heads, threads, smem, stream>>>(
+      reinterpret_cast<const __nv_bfloat16*>(qkv), ldqkv, reinterpret_cast<const __nv_bfloat16*>(out), ldo,
+      reinterpret_cast<const __nv_bfloat16*>(dout), lddo, lse, T, heads, q_scale,
+      reinterpret_cast<__nv_bfloat16*>(dqkv), lddqkv);
+  JM_CUDA(cudaGetLastError());
+  return 0;
+}
+
+static int check_attn(const char* who, int batch, int T, int heads, int hd, long ld0, long ld1) {
+  JM_CHECK(batch > 0 && heads > 0, "%s: empty problem", who);
+  JM_CHECK(T >= 1 && T <= 512, "%s: sequence length %d outside [1, 512]", who, T);
+  JM_CHECK(hd == 32 || hd == 64 || hd == 80, "%s: head_dim %d not in {32, 64, 80}", who, hd);
+  JM_CHECK(ld0 % 8 == 0 && ld1 % 8 == 0, "%s: row strides must be multiples of 8 elements", who);
+  return 0;
+}
+
+}  // namespace jm
+
+extern "C" int jm_attention_fwd(const jm_bf16* qkv, long ldqkv, int batch, int T, int heads, int head_dim,
+                                jm_bf16* out, long ldo, float* lse, void* stream_) {
+  using namespace jm;
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  if (check_attn("jm_attention_fwd", batch, T, heads, head_dim, ldqkv, ldo)) return 1;
+  JM_CHECK(fwd_smem(T, head_dim) <= 227 * 1024, "jm_attention_fwd: T=%d hd=%d does not fit shared memory", T,
+           head_dim);
+  if (head_dim == 32) return launch_fwd<32>(qkv, ldqkv, batch, T, heads, out, ldo, lse, stream);
+  if (head_dim == 64) return launch_fwd<64>(qkv, ldqkv, batch, T, heads, out, ldo, lse, stream);
+  return launch_fwd<80>(qkv, ldqkv, batch, T, heads, out, ldo, lse, stream);
+}
+
+extern "C" int jm_attention_bwd(const jm_bf16* qkv, long ldqkv, const jm_bf16* out, long ldo, const jm_bf16* dout,
+                                long lddo, const float* lse, int batch, int T, int heads, int head_dim,
+                                float q_scale, jm_bf16* dqkv, long lddqkv, void* stream_) {
+  using namespace jm;
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  if (check_attn("jm_attention_bwd", batch, T, heads, head_dim, ldqkv, lddqkv)) return 1;
+  JM_CHECK(ldo % 8 == 0 && lddo % 8 == 0, "jm_attention_bwd: row strides must be multiples of 8 elements");
+  JM_CHECK(bwd_smem(T, head_dim) <= 227 * 1024, "jm_attention_bwd: T=%d hd=%d does not fit shared memory", T,
+           head_dim);
+  if (head_dim == 32)
+    return launch_bwd<32>(qkv, ldqkv, out, ldo, dout, lddo, lse, batch, T, heads, q_scale, dqkv, lddqkv, stream);
+  if (head_dim == 64)
+    return launch_bwd<64>(qkv, ldqkv, out, ldo, dout, lddo, lse, batch, T, heads, q_scale, dqkv, lddqkv, stream);
+  return launch_bwd<80>(qkv, ldqkv, out, ldo, dout, lddo, lse, batch, T, heads, q_scale, dqkv, lddqkv, stream);
 }

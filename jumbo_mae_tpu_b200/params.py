@@ -1,0 +1,221 @@
+"""Flat parameter storage with a Flax-shaped view tree.
+
+The reference keeps its parameters in a Flax pytree (names in SURVEY.md section 8a;
+src/modeling.py:106-298, src/pretraining.py:82-85).  The kernels want (a) one contiguous
+f32 master buffer so that AdamW and the gradient all-reduce are single passes, (b) a bf16
+compute copy at the same offsets for the TMA-fed GEMMs, and (c) q/k/v projection weights
+fused into one [d, 3d] matrix.  ``ParamStore`` lays the leaves out once and exposes the
+reference's tree as (possibly strided) views, so ``state.params["model"]["layer_0"]
+["attn"]["wq"]["kernel"]`` still has shape [d, heads, head_dim].
+
+Layout rules
+  * leaves whose Flax name is ``kernel`` come first: optax's weight-decay mask
+    (src/pretraining.py:233) becomes the single boundary ``n_decay``;
+  * every leaf starts at a multiple of 64 elements (TMA needs 16-byte alignment);
+  * 2-D kernels get a row stride rounded up to 8 elements (ViT-H/14's 588-wide head).
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+from typing import Dict, List, Tuple
+
+import torch
+
+from .config import MAEConfig
+
+ALIGN = 64
+
+
+def _round_up(x: int, m: int) -> int:
+    return (x + m - 1) // m * m
+
+
+@dataclass
+class Leaf:
+    name: str               # internal name, e.g. "model/layer_0/attn/wqkv/kernel"
+    rows: int               # 2-D storage shape [rows, cols] with row stride ld (1-D: rows = 1)
+    cols: int
+    ld: int
+    decay: bool
+    offset: int = 0
+
+    @property
+    def size(self) -> int:
+        return self.rows * self.ld
+
+
+def _leaves(cfg: MAEConfig) -> List[Leaf]:
+    d, dd, J, P = cfg.dim, cfg.dec_dim, cfg.num_cls_tokens, cfg.patch_dim
+    out: List[Leaf] = []
+
+    def kernel(name, rows, cols):
+        out.append(Leaf(name, rows, cols, _round_up(cols, 8), True))
+
+    def vec(name, n):
+        out.append(Leaf(name, 1, n, n, False))
+
+    def block(prefix, dim, with_norm3):
+        kernel(f"{prefix}/attn/wqkv/kernel", dim, 3 * dim)
+        vec(f"{prefix}/attn/wqkv/bias", 3 * dim)
+        kernel(f"{prefix}/attn/wo/kernel", dim, dim)
+        vec(f"{prefix}/attn/wo/bias", dim)
+        kernel(f"{prefix}/ff/w1/kernel", dim, 4 * dim)
+        vec(f"{prefix}/ff/w1/bias", 4 * dim)
+        kernel(f"{prefix}/ff/w2/kernel", 4 * dim, dim)
+        vec(f"{prefix}/ff/w2/bias", dim)
+        for nm, n in (("norm1", dim), ("norm2", dim)) + ((("norm3", J * dim),) if with_norm3 else ()):
+            vec(f"{prefix}/{nm}/scale", n)
+            vec(f"{prefix}/{nm}/bias", n)
+
+    kernel("model/embed/wte/kernel", P, d)
+    vec("model/embed/wte/bias", d)
+    vec("model/cls_tokens", J * d)
+    kernel("model/jumbo_mlp/w1/kernel", J * d, 4 * J * d)
+    vec("model/jumbo_mlp/w1/bias", 4 * J * d)
+    kernel("model/jumbo_mlp/w2/kernel", 4 * J * d, J * d)
+    vec("model/jumbo_mlp/w2/bias", J * d)
+    for i in range(cfg.layers):
+        block(f"model/layer_{i}", d, True)
+    vec("model/norm/scale", d)
+    vec("model/norm/bias", d)
+    for i in range(cfg.dec_layers):
+        block(f"decoder_model/dec_layer_{i}", dd, False)
+    vec("decoder_model/dec_norm/scale", dd)
+    vec("decoder_model/dec_norm/bias", dd)
+    vec("image_mask_embedding", dd)
+    kernel("decoder_proj/kernel", d, dd)
+    vec("decoder_proj/bias", dd)
+    kernel("decoder_image_output/kernel", dd, P)
+    vec("decoder_image_output/bias", P)
+    return out
+
+
+class ParamStore:
+    """Flat f32 master parameters (+ bf16 compute copy, gradients, Adam moments)."""
+
+    def __init__(self, cfg: MAEConfig, device="cuda"):
+        self.cfg = cfg
+        leaves = _leaves(cfg)
+        ordered = [l for l in leaves if l.decay] + [l for l in leaves if not l.decay]
+        off = 0
+        for leaf in ordered:
+            leaf.offset = off
+            off += _round_up(leaf.size, ALIGN)
+            if leaf.decay:
+                self.n_decay = off
+        self.total = off
+        self.leaves: Dict[str, Leaf] = {l.name: l for l in ordered}
+        self.device = torch.device(device)
+        self.p = torch.zeros(self.total, dtype=torch.float32, device=self.device)
+        self.p16 = torch.zeros(self.total, dtype=torch.bfloat16, device=self.device)
+        self.g = torch.zeros(self.total, dtype=torch.float32, device=self.device)
+        self.m = torch.zeros(self.total, dtype=torch.float32, device=self.device)
+        self.v = torch.zeros(self.total, dtype=torch.float32, device=self.device)
+
+    # ------------------------------------------------------------- raw views
+    def view(self, buf: torch.Tensor, name: str) -> torch.Tensor:
+        """[rows, ld] (2-D kernels) or [cols] (vectors) view of a leaf inside ``buf``."""
+        l = self.leaves[name]
+        flat = buf[l.offset:l.offset + l.size]
+        return flat.view(l.rows, l.ld) if l.rows > 1 or l.decay else flat
+
+    def w(self, name: str) -> torch.Tensor:        # bf16 compute copy
+        return self.view(self.p16, name)
+
+    def f(self, name: str) -> torch.Tensor:        # f32 master
+        return self.view(self.p, name)
+
+    def grad(self, name: str) -> torch.Tensor:
+        return self.view(self.g, name)
+
+    def ld(self, name: str) -> int:
+        return self.leaves[name].ld
+
+    # ------------------------------------------------------------- Flax-shaped trees
+    def tree(self, buf: torch.Tensor | None = None) -> dict:
+        """The reference's parameter pytree as views into ``buf`` (default: f32 masters)."""
+        buf = self.p if buf is None else buf
+        cfg = self.cfg
+        J = cfg.num_cls_tokens
+
+        def k(name):                       # 2-D kernel without the stride padding
+            l = self.leaves[name]
+            return self.view(buf, name)[:, :l.cols]
+
+        def v(name):
+            return self.view(buf, name)
+
+        def attn(prefix, dim, heads):
+            hd = dim // heads
+            wqkv, bqkv = k(f"{prefix}/wqkv/kernel"), v(f"{prefix}/wqkv/bias")
+            out = {}
+            for i, nm in enumerate(("wq", "wk", "wv")):
+                out[nm] = {"kernel": wqkv[:, i * dim:(i + 1) * dim].unflatten(1, (heads, hd)),
+                           "bias": bqkv[i * dim:(i + 1) * dim].view(heads, hd)}
+            out["wo"] = {"kernel": k(f"{prefix}/wo/kernel").unflatten(0, (heads, hd)), "bias": v(f"{prefix}/wo/bias")}
+            return out
+
+        def ff(prefix):
+            return {"w1": {"kernel": k(f"{prefix}/w1/kernel"), "bias": v(f"{prefix}/w1/bias")},
+                    "w2": {"kernel": k(f"{prefix}/w2/kernel"), "bias": v(f"{prefix}/w2/bias")}}
+
+        def ln(prefix):
+            return {"scale": v(f"{prefix}/scale"), "bias": v(f"{prefix}/bias")}
+
+        model = {
+            "embed": {"wte": {"kernel": k("model/embed/wte/kernel").view(cfg.patch_size, cfg.patch_size, 3, cfg.dim),
+                              "bias": v("model/embed/wte/bias")}},
+            "cls_tokens": v("model/cls_tokens").view(1, J, cfg.dim),
+            "jumbo_mlp": ff("model/jumbo_mlp"),
+            "norm": ln("model/norm"),
+        }
+        for i in range(cfg.layers):
+            p = f"model/layer_{i}"
+            model[f"layer_{i}"] = {"attn": attn(f"{p}/attn", cfg.dim, cfg.heads), "ff": ff(f"{p}/ff"),
+                                   "norm1": ln(f"{p}/norm1"), "norm2": ln(f"{p}/norm2"), "norm3": ln(f"{p}/norm3")}
+        dec = {"dec_norm": ln("decoder_model/dec_norm")}
+        for i in range(cfg.dec_layers):
+            p = f"decoder_model/dec_layer_{i}"
+            dec[f"dec_layer_{i}"] = {"attn": attn(f"{p}/attn", cfg.dec_dim, cfg.dec_heads), "ff": ff(f"{p}/ff"),
+                                     "norm1": ln(f"{p}/norm1"), "norm2": ln(f"{p}/norm2")}
+        return {
+            "model": model,
+            "decoder_model": dec,
+            "image_mask_embedding": v("image_mask_embedding").view(1, 1, cfg.dec_dim),
+            "decoder_proj": {"kernel": k("decoder_proj/kernel"), "bias": v("decoder_proj/bias")},
+            "decoder_image_output": {"kernel": k("decoder_image_output/kernel"),
+                                     "bias": v("decoder_image_output/bias")},
+        }
+
+    def load_tree(self, tree: dict) -> None:
+        """Copies a Flax-shaped tree of (CPU or CUDA) tensors into the masters and refreshes bf16."""
+        mine = self.tree()
+
+        def walk(dst, src, path):
+            for key, val in dst.items():
+                if key not in src:
+                    raise KeyError(f"parameter tree is missing {'/'.join(path + (key,))}")
+                if isinstance(val, dict):
+                    walk(val, src[key], path + (key,))
+                else:
+                    s = src[key]
+                    if tuple(s.shape) != tuple(val.shape):
+                        raise ValueError(f"{'/'.join(path + (key,))}: shape {tuple(s.shape)} != {tuple(val.shape)}")
+                    val.copy_(s.to(device=val.device, dtype=val.dtype))
+        walk(mine, tree, ())
+        self.refresh_bf16()
+
+    def refresh_bf16(self) -> None:
+        from . import ops
+        ops.cast_bf16(self.p, self.p16)
+
+
+def tree_leaves(tree: dict, prefix: Tuple[str, ...] = ()):
+    out = []
+    for key in sorted(tree.keys()):
+        val = tree[key]
+        if isinstance(val, dict):
+            out.extend(tree_leaves(val, prefix + (key,)))
+        else:
+            out.append((prefix + (key,), val))
+    return out

@@ -245,8 +245,9 @@ def test_adamw_matches_oracle(ops):
               1 - cfg.adam_b1 ** t, 1 - cfg.adam_b2 ** t, 1.0)
     # identical f32 formula; allow a couple of ulp for fma contraction / division rounding
     assert torch.allclose(pd.cpu(), want_p, rtol=3e-7, atol=1e-9)
-    assert torch.allclose(md.cpu(), want_m, rtol=3e-7, atol=1e-12)
-    assert torch.allclose(vd.cpu(), want_v, rtol=3e-7, atol=1e-15)
+    # m and v are sums of two rounded terms: an fma keeps one of them exact, so allow 2 ulp of the larger term
+    assert torch.allclose(md.cpu(), want_m, rtol=3e-7, atol=2 * 1.2e-7 * want_m.abs().max().item())
+    assert torch.allclose(vd.cpu(), want_v, rtol=3e-7, atol=2 * 1.2e-7 * want_v.abs().max().item())
     assert torch.equal(pb.float().cpu(), pd.cpu().to(BF16).float())
 
 
@@ -277,7 +278,10 @@ GEMM_CASES = [
 def test_gemm_plain(ops, M, N, K, a_mn, b_mn, bn):
     g = torch.Generator(device="cuda").manual_seed(M + N + K)
     A = torch.randn((K, M) if a_mn else (M, K), generator=g, device="cuda").to(BF16)
-    B = torch.randn((K, N) if b_mn else (N, K), generator=g, device="cuda").to(BF16)
+    # operand row strides must be multiples of 8 elements (16 bytes for TMA): pad, then view
+    ldn, ldk = (N + 7) // 8 * 8, (K + 7) // 8 * 8
+    B = torch.randn((K, ldn) if b_mn else (N, ldk), generator=g, device="cuda").to(BF16)
+    B = B[:, :N] if b_mn else B[:, :K]
     out = torch.full((M, N), float("nan"), device="cuda")
     ops.gemm(A, B, M, N, K, a_mn=a_mn, b_mn=b_mn, out_f32=out, block_n=bn)
     ref = _gemm_ref(A, B, a_mn, b_mn)
@@ -384,3 +388,59 @@ def test_gemm_rejects_bad_arguments(ops):
         ops.gemm(A, B, 8, 8, 12, b_mn=True, out_f32=torch.zeros(8, 8, device="cuda"), lda=12)   # ld % 8 != 0
     with pytest.raises(JmError):
         ops.gemm(A, B, 8, 8, 12, b_mn=True)                                                     # no output
+
+
+# ------------------------------------------------------------------ attention
+def _attn_ref(qkv, B, T, H, hd):
+    """Attention core of oracle.attention (src/modeling.py:136-137) on the stored (already scaled) q."""
+    d = H * hd
+    q, k, v = [qkv.float()[:, i * d:(i + 1) * d].reshape(B, T, H, hd) for i in range(3)]
+    z = torch.einsum("bqhd,bkhd->bhqk", q, k)
+    p = torch.softmax(z, dim=-1)
+    return torch.einsum("bhqk,bkhd->bqhd", p, v).reshape(B * T, d), torch.logsumexp(z, dim=-1)
+
+
+ATTN_CASES = [(3, 52, 12, 64), (1, 199, 2, 64), (2, 199, 16, 32), (2, 67, 4, 80), (1, 259, 4, 32), (2, 7, 2, 32), (2, 19, 2, 32),
+              (1, 1, 1, 64), (1, 64, 2, 64)]
+
+
+@pytest.mark.parametrize("B,T,H,hd", ATTN_CASES)
+def test_attention_fwd(ops, B, T, H, hd):
+    d = H * hd
+    g = torch.Generator(device="cuda").manual_seed(T)
+    qkv = torch.randn(B * T, 3 * d, generator=g, device="cuda")
+    qkv[:, :d] *= hd ** -0.5
+    qkv = qkv.to(BF16)
+    out = torch.full((B * T, d), float("nan"), dtype=BF16, device="cuda")
+    lse = torch.full((B, H, T), float("nan"), device="cuda")
+    ops.attention_fwd(qkv, B, T, H, hd, out, lse)
+    ref, ref_lse = _attn_ref(qkv, B, T, H, hd)
+    # P is rounded to bf16 before P.V and the output is bf16: 2^-7 of the value scale
+    assert (out.float() - ref).abs().max().item() <= 2 ** -6 * ref.abs().max().item()
+    assert torch.allclose(lse, ref_lse, rtol=1e-4, atol=1e-4)
+
+
+@pytest.mark.parametrize("B,T,H,hd", ATTN_CASES)
+def test_attention_bwd(ops, B, T, H, hd):
+    d = H * hd
+    g = torch.Generator(device="cuda").manual_seed(T + 1)
+    qkv = torch.randn(B * T, 3 * d, generator=g, device="cuda")
+    scale = hd ** -0.5
+    qkv[:, :d] *= scale
+    qkv = qkv.to(BF16)
+    dout = torch.randn(B * T, d, generator=g, device="cuda").to(BF16)
+    out = torch.empty(B * T, d, dtype=BF16, device="cuda")
+    lse = torch.empty(B, H, T, device="cuda")
+    ops.attention_fwd(qkv, B, T, H, hd, out, lse)
+    dqkv = torch.full((B * T, 3 * d), float("nan"), dtype=BF16, device="cuda")
+    ops.attention_bwd(qkv, out, dout, lse, B, T, H, hd, scale, dqkv)
+    x = qkv.float().requires_grad_(True)
+    ref, _ = _attn_ref(x, B, T, H, hd)
+    (ref * dout.float()).sum().backward()
+    want = x.grad.clone()
+    want[:, :d] *= scale           # gradient w.r.t. the un-scaled q projection
+    got = dqkv.float()
+    for i, name in enumerate("qkv"):
+        a, b = got[:, i * d:(i + 1) * d], want[:, i * d:(i + 1) * d]
+        rel = ((a - b).norm() / (b.norm() + 1e-6)).item()   # T == 1: dq = dk = 0 exactly
+        assert rel < 2e-2, f"d{name}: rel l2 {rel}"          # bf16 P / dS operands, bf16 outputs
