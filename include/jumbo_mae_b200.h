@@ -33,6 +33,8 @@ const char* jm_last_error(void);
 int jm_version(void);
 /* 1 if the current device is sm_100 (B200); the library refuses to run elsewhere. */
 int jm_device_ok(void);
+/* Number of kernels this library has launched in this process (bench.py's gpu_launches). */
+long long jm_launch_count(void);
 
 /* ---------------------------------------------------------------- masking
  * random_masking, src/utils_mae.py:88-96, with the uniform noise as an input:

@@ -16,7 +16,7 @@ LIB_PATH = os.path.join(_HERE, "libjumbo_mae_b200.so")
 
 # Every symbol include/jumbo_mae_b200.h declares; tests check that the library exports them all.
 EXPORTS = [
-    "jm_last_error", "jm_version", "jm_device_ok", "jm_mask_sort", "jm_index_sequence", "jm_patchify",
+    "jm_last_error", "jm_version", "jm_device_ok", "jm_launch_count", "jm_mask_sort", "jm_index_sequence", "jm_patchify",
     "jm_extract_patches", "jm_patch_loss_workspace", "jm_patch_loss", "jm_layernorm_fwd",
     "jm_layernorm_bwd_workspace", "jm_layernorm_bwd", "jm_gemm", "jm_attention_fwd", "jm_attention_bwd",
     "jm_fill_cls", "jm_unshuffle_fwd", "jm_unshuffle_bwd", "jm_colsum", "jm_adamw", "jm_cast_bf16",
@@ -62,6 +62,7 @@ def load() -> ctypes.CDLL:
             "(there is no CPU or PyTorch fallback)")
     lib = ctypes.CDLL(LIB_PATH)
     lib.jm_last_error.restype = c_char_p
+    lib.jm_launch_count.restype = ctypes.c_longlong
     lib.jm_patch_loss_workspace.restype = c_size_t
     lib.jm_patch_loss_workspace.argtypes = [c_int, c_int]
     lib.jm_layernorm_bwd_workspace.restype = c_size_t

@@ -413,7 +413,7 @@ static int launch_fwd(const jm_bf16* qkv, long ldqkv, int batch, int T, int head
   const int threads = warps * 32;
   kern<<<batch * heads, threads, smem, stream>>>(reinterpret_cast<const __nv_bfloat16*>(qkv), ldqkv, T, heads,
                                                  reinterpret_cast<__nv_bfloat16*>(out), ldo, lse);
-  JM_CUDA(cudaGetLastError());
+  JM_AFTER_LAUNCH();
   return 0;
 }
 
@@ -431,7 +431,7 @@ static int launch_bwd(const jm_bf16* qkv, long ldqkv, const jm_bf16* out, long l
       reinterpret_cast<const __nv_bfloat16*>(qkv), ldqkv, reinterpret_cast<const __nv_bfloat16*>(out), ldo,
       reinterpret_cast<const __nv_bfloat16*>(dout), lddo, lse, T, heads, q_scale,
       reinterpret_cast<__nv_bfloat16*>(dqkv), lddqkv);
-  JM_CUDA(cudaGetLastError());
+  JM_AFTER_LAUNCH();
   return 0;
 }
 

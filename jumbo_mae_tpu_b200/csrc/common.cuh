@@ -32,6 +32,15 @@ int fail(const char* fmt, ...);
 
 int sm_count();  // SMs of the current device (cached per device)
 
+// Every kernel launch is followed by this: counts the launch (jm_launch_count) and
+// surfaces launch-configuration errors as a return code.
+void count_launch();
+#define JM_AFTER_LAUNCH()          \
+  do {                             \
+    ::jm::count_launch();          \
+    JM_CUDA(cudaGetLastError());   \
+  } while (0)
+
 #ifdef __CUDACC__
 // ---------------------------------------------------------------- small math
 __device__ __forceinline__ float gelu_tanh_f(float x) {

@@ -1,6 +1,8 @@
 // Error reporting and device queries shared by every entry point.
 #include <stdarg.h>
 
+#include <atomic>
+
 #include "../../include/jumbo_mae_b200.h"
 #include "common.cuh"
 
@@ -9,6 +11,8 @@ namespace jm {
 static thread_local std::string g_last_error;
 
 void set_error(const std::string& msg) { g_last_error = msg; }
+
+long long launches();
 
 int fail(const char* fmt, ...) {
   char buf[1024];
@@ -19,6 +23,10 @@ int fail(const char* fmt, ...) {
   g_last_error = buf;
   return 1;
 }
+
+static std::atomic<long long> g_launches{0};
+void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
+long long launches() { return g_launches.load(std::memory_order_relaxed); }
 
 int sm_count() {
   static int cached[64];
@@ -39,6 +47,8 @@ int sm_count() {
 extern "C" const char* jm_last_error(void) { return jm::g_last_error.c_str(); }
 
 extern "C" int jm_version(void) { return 100; }
+
+extern "C" long long jm_launch_count(void) { return jm::launches(); }
 
 extern "C" int jm_device_ok(void) {
   int dev = 0, major = 0;

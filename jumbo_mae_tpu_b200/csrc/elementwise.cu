@@ -547,7 +547,7 @@ extern "C" int jm_mask_sort(const float* noise, int length, int keep, int32_t* i
   const int threads = (length + 31) / 32 * 32;
   mask_sort_kernel<<<1, threads, length * sizeof(float), STREAM>>>(noise, length, keep, ids_shuffle, ids_restore,
                                                                    mask_row);
-  JM_CUDA(cudaGetLastError());
+  JM_AFTER_LAUNCH();
   return 0;
 }
 
@@ -555,7 +555,7 @@ extern "C" int jm_index_sequence(const float* x, const int32_t* ids, int batch, 
                                  int dim, float* out, void* stream) {
   if (batch == 0 || length_out == 0) return 0;
   index_sequence_kernel<<<dim3(length_out, batch), 128, 0, STREAM>>>(x, ids, length_in, length_out, dim, out);
-  JM_CUDA(cudaGetLastError());
+  JM_AFTER_LAUNCH();
   return 0;
 }
 
@@ -567,7 +567,7 @@ extern "C" int jm_patchify(const uint8_t* images, int batch, int image_size, int
   if (batch == 0) return 0;
   patchify_kernel<<<dim3(rows_per_image, batch), 256, 0, STREAM>>>(
       images, image_size, patch_size, ids, n_sel, rows_per_image, row_off, reinterpret_cast<__nv_bfloat16*>(out), ldo);
-  JM_CUDA(cudaGetLastError());
+  JM_AFTER_LAUNCH();
   return 0;
 }
 
@@ -577,7 +577,7 @@ extern "C" int jm_extract_patches(const uint8_t* images, int batch, int image_si
   if (batch == 0) return 0;
   const int g = image_size / patch_size;
   extract_patches_kernel<<<dim3(g * g, batch), 256, 0, STREAM>>>(images, image_size, patch_size, out);
-  JM_CUDA(cudaGetLastError());
+  JM_AFTER_LAUNCH();
   return 0;
 }
 
@@ -596,9 +596,9 @@ extern "C" int jm_patch_loss(const float* pred, long ldp, const uint8_t* images,
   patch_loss_kernel<<<dim3(num_cls + N, batch), kLossThreads, 0, STREAM>>>(
       pred, ldp, images, mask_row, image_size, patch_size, num_cls, norm_pix, grad_scale, partial,
       reinterpret_cast<__nv_bfloat16*>(dpred), lddp, batch);
-  JM_CUDA(cudaGetLastError());
+  JM_AFTER_LAUNCH();
   patch_loss_finalize_kernel<<<1, 1024, 0, STREAM>>>(partial, mask_row, N, batch, loss);
-  JM_CUDA(cudaGetLastError());
+  JM_AFTER_LAUNCH();
   return 0;
 }
 
@@ -613,7 +613,7 @@ extern "C" int jm_layernorm_fwd(const float* x, long ldx, int rows, int dim, con
   layernorm_fwd_kernel<<<grid, kLnWarps * 32, 0, STREAM>>>(x, ldx, rows, dim, gamma, beta, eps,
                                                            reinterpret_cast<__nv_bfloat16*>(y_bf16), ldy, y_f32, ldyf,
                                                            mean, rstd);
-  JM_CUDA(cudaGetLastError());
+  JM_AFTER_LAUNCH();
   return 0;
 }
 
@@ -654,14 +654,14 @@ extern "C" int jm_layernorm_bwd(const jm_bf16* dy, long lddy, const float* x, lo
 #undef JM_LN_BWD_ARGS
   ln_param_reduce_kernel<<<(2 * dim + 255) / 256, 256, 0, STREAM>>>(static_cast<const float*>(workspace), grid, dim,
                                                                     dgamma, dbeta);
-  JM_CUDA(cudaGetLastError());
+  JM_AFTER_LAUNCH();
   return 0;
 }
 
 extern "C" int jm_fill_cls(float* x, int batch, int T, int J, int dim, const float* cls, void* stream) {
   if (batch == 0 || J == 0) return 0;
   fill_cls_kernel<<<dim3(J, batch), 256, 0, STREAM>>>(x, T, J, dim, cls);
-  JM_CUDA(cudaGetLastError());
+  JM_AFTER_LAUNCH();
   return 0;
 }
 
@@ -671,7 +671,7 @@ extern "C" int jm_unshuffle_fwd(const float* y, const int32_t* ids_restore, cons
   JM_CHECK(dim % 4 == 0, "jm_unshuffle_fwd: dim must be a multiple of 4");
   if (batch == 0) return 0;
   unshuffle_fwd_kernel<<<dim3(J + N, batch), 128, 0, STREAM>>>(y, ids_restore, mask_emb, dec_wpe, N, n, J, dim, out);
-  JM_CUDA(cudaGetLastError());
+  JM_AFTER_LAUNCH();
   return 0;
 }
 
@@ -681,7 +681,7 @@ extern "C" int jm_unshuffle_bwd(const float* dout, const int32_t* ids_restore, i
   if (batch == 0) return 0;
   unshuffle_bwd_kernel<<<dim3(J + N, (batch + kUnshufBwdImgs - 1) / kUnshufBwdImgs), 128, 0, STREAM>>>(
       dout, ids_restore, batch, N, n, J, dim, reinterpret_cast<__nv_bfloat16*>(dy), dmask_emb);
-  JM_CUDA(cudaGetLastError());
+  JM_AFTER_LAUNCH();
   return 0;
 }
 
@@ -699,7 +699,7 @@ extern "C" int jm_colsum(const void* x, int is_f32, long ldx, int rows, int cols
     colsum_kernel<true><<<dim3(gx, gy), 256, 0, STREAM>>>(x, ldx, rows, cols, row_period, row_skip, rows_per_block, out);
   else
     colsum_kernel<false><<<dim3(gx, gy), 256, 0, STREAM>>>(x, ldx, rows, cols, row_period, row_skip, rows_per_block, out);
-  JM_CUDA(cudaGetLastError());
+  JM_AFTER_LAUNCH();
   return 0;
 }
 
@@ -714,7 +714,7 @@ extern "C" int jm_adamw(float* p, const float* g, float* m, float* v, jm_bf16* p
   if (blocks > cap) blocks = cap;
   adamw_kernel<<<static_cast<int>(blocks), 256, 0, STREAM>>>(p, g, m, v, reinterpret_cast<__nv_bfloat16*>(p_bf16), n4,
                                                             n_decay / 4, lr, b1, b2, eps, wd, bc1, bc2, grad_scale);
-  JM_CUDA(cudaGetLastError());
+  JM_AFTER_LAUNCH();
   return 0;
 }
 
@@ -724,6 +724,6 @@ extern "C" int jm_cast_bf16(const float* x, jm_bf16* y, long n, void* stream) {
   const long cap = static_cast<long>(sm_count()) * 8;
   if (blocks > cap) blocks = cap;
   cast_bf16_kernel<<<static_cast<int>(blocks), 256, 0, STREAM>>>(x, reinterpret_cast<__nv_bfloat16*>(y), n);
-  JM_CUDA(cudaGetLastError());
+  JM_AFTER_LAUNCH();
   return 0;
 }

@@ -388,7 +388,7 @@ static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const Gem
     attr_set = true;
   }
   kern<<<grid, kGemmThreads, GemmCfg<BN>::SMEM_BYTES, stream>>>(tmA, tmB, sh, ep);
-  JM_CUDA(cudaGetLastError());
+  JM_AFTER_LAUNCH();
   return 0;
 }
 

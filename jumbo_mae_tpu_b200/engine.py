@@ -1,0 +1,310 @@
+"""The MAE pre-training step as an explicit kernel schedule.
+
+This is what XLA executes for the reference's ``training_step`` (src/pretraining.py:125-159):
+PretrainModule.__call__ (src/pretraining.py:87-122) forward, its hand-derived backward,
+and the optax AdamW update.  Every arithmetic op is one of the sm_100a kernels behind the
+C ABI (include/jumbo_mae_b200.h); this module only owns buffers and launch order.
+
+Token layout.  Encoder activations are one [B*Te, d] buffer per layer (Te = J + keep), CLS
+rows first in each image block.  The Jumbo CLS view [B, J*d] (src/modeling.py:194-197) is
+then the same memory with row stride Te*d, so split / reshape / concat move no data: the
+Jumbo FFN's GEMM epilogue stores straight into the CLS rows.  The patch FFN runs on all Te
+rows with the CLS rows predicated off in the epilogue (6 % of one GEMM pair).
+
+Precision.  bf16 GEMM / attention operands, f32 accumulation, f32 residual stream,
+LayerNorm and softmax statistics, loss and optimizer state (the reference is f32
+throughout; BASELINE.json's "bf16" is this compute dtype).
+"""
+from __future__ import annotations
+
+import math
+from typing import Dict, List, Optional
+
+import torch
+
+from . import _lib, ops
+from .config import MAEConfig
+from .params import ParamStore
+
+F32, BF16 = torch.float32, torch.bfloat16
+LN_EPS = 1e-6   # flax.linen.LayerNorm default
+
+
+def fixed_sincos2d_embeddings(ncols: int, nrows: int, dim: int) -> torch.Tensor:
+    """src/utils.py:114-121 (host-side constant table, computed once in f32 on the CPU)."""
+    freqs = 1.0 / (10000.0 ** torch.linspace(0, 1, dim // 4, dtype=F32))
+    x = torch.outer(torch.arange(0, nrows, dtype=F32), freqs)
+    y = torch.outer(torch.arange(0, ncols, dtype=F32), freqs)
+    x = x[None, :, :].expand(ncols, nrows, dim // 4)
+    y = y[:, None, :].expand(ncols, nrows, dim // 4)
+    return torch.cat((torch.sin(x), torch.cos(x), torch.sin(y), torch.cos(y)), dim=2)
+
+
+class _Block:
+    """Saved activations of one transformer block (encoder JumboLayer or decoder ViTLayer)."""
+
+    def __init__(self, M: int, dim: int, heads: int, B: int, T: int, J: int, jumbo: bool, dev):
+        e = lambda *s, dt=BF16: torch.empty(*s, dtype=dt, device=dev)
+        self.mean1, self.rstd1 = e(M, dt=F32), e(M, dt=F32)
+        self.mean2, self.rstd2 = e(M, dt=F32), e(M, dt=F32)
+        self.xn1, self.xn2 = e(M, dim), e(M, dim)
+        self.qkv = e(M, 3 * dim)
+        self.lse = e(B, heads, T, dt=F32)
+        self.att = e(M, dim)
+        self.xb = e(M, dim, dt=F32)            # residual stream after the attention branch
+        self.h, self.g = e(M, 4 * dim), e(M, 4 * dim)
+        if jumbo:
+            Jd = J * dim
+            self.mean3, self.rstd3 = e(B, dt=F32), e(B, dt=F32)
+            self.cn, self.cn16 = e(B, Jd, dt=F32), e(B, Jd)
+            self.hj, self.gj = e(B, 4 * Jd), e(B, 4 * Jd)
+
+
+class MAEEngine:
+    """Buffers + kernel schedule for one per-device batch size."""
+
+    def __init__(self, cfg: MAEConfig, store: ParamStore, batch: int):
+        _lib.require_device()
+        cfg.validate()
+        self.cfg, self.ps, self.B = cfg, store, batch
+        dev = store.device
+        self.dev = dev
+        B, J, n, N = batch, cfg.num_cls_tokens, cfg.keep, cfg.num_patches
+        d, dd, P = cfg.dim, cfg.dec_dim, cfg.patch_dim
+        self.Te, self.Td = J + n, J + N
+        self.Me, self.Md = B * self.Te, B * self.Td
+        self.Pp = (P + 7) // 8 * 8
+        e = lambda *s, dt=BF16: torch.empty(*s, dtype=dt, device=dev)
+
+        self.wpe = fixed_sincos2d_embeddings(cfg.grid, cfg.grid, d).reshape(N, d).contiguous().to(dev)
+        self.dec_wpe = fixed_sincos2d_embeddings(cfg.grid, cfg.grid, dd).reshape(N, dd).contiguous().to(dev)
+
+        self.ids_shuffle = e(N, dt=torch.int32)
+        self.ids_restore = e(N, dt=torch.int32)
+        self.mask_row = e(N, dt=F32)
+        self.patches = e(self.Me, self.Pp)
+        # encoder
+        self.xa: List[torch.Tensor] = [e(self.Me, d, dt=F32) for _ in range(cfg.layers + 1)]
+        self.enc = [_Block(self.Me, d, cfg.heads, B, self.Te, J, True, dev) for _ in range(cfg.layers)]
+        self.meanF, self.rstdF = e(self.Me, dt=F32), e(self.Me, dt=F32)
+        self.enc_n = e(self.Me, d)
+        self.y = e(self.Me, dd, dt=F32)
+        # decoder
+        self.za: List[torch.Tensor] = [e(self.Md, dd, dt=F32) for _ in range(cfg.dec_layers + 1)]
+        self.dec = [_Block(self.Md, dd, cfg.dec_heads, B, self.Td, J, False, dev) for _ in range(cfg.dec_layers)]
+        self.meanD, self.rstdD = e(self.Md, dt=F32), e(self.Md, dt=F32)
+        self.dec_n = e(self.Md, dd)
+        self.pred = e(self.Md, P, dt=F32)
+        self.loss = torch.zeros(1, dtype=F32, device=dev)
+        self.loss_ws = torch.empty(ops.patch_loss_workspace(B, N), dtype=torch.uint8, device=dev)
+        # backward scratch, shared by both stacks (sized for the larger one)
+        Mx = max(self.Me, self.Md)
+        wmax = max(self.Me * d, self.Md * dd)
+        self.dpred = torch.zeros(self.Md, self.Pp, dtype=BF16, device=dev)     # pad columns stay zero
+        self.dxA, self.dxB = e(wmax, dt=F32), e(wmax, dt=F32)
+        self.dxA16, self.dxB16 = e(wmax), e(wmax)
+        self.dh16 = e(4 * wmax)
+        self.dn16 = e(wmax)
+        self.dqkv16 = e(3 * wmax)
+        self.datt16 = e(wmax)
+        self.dy16 = e(self.Me, dd)
+        self.dhj16 = e(B, 4 * J * d)
+        self.dcn16 = e(B, J * d)
+        ln_ws = max(ops.layernorm_bwd_workspace(Mx, max(d, dd)), ops.layernorm_bwd_workspace(B, J * d))
+        self.ln_ws = torch.empty(ln_ws, dtype=torch.uint8, device=dev)
+
+    # ------------------------------------------------------------------ helpers
+    def _W(self, name):
+        return self.ps.w(name)
+
+    def _b(self, name):
+        return self.ps.f(name)
+
+    def _fwd_linear(self, A, M, name, N, K, **epi):
+        """out = epilogue(A[M,K] @ kernel[K,N] + bias): a Flax Dense (kernel is [in, out])."""
+        ops.gemm(A, self._W(f"{name}/kernel"), M, N, K, b_mn=True, ldb=self.ps.ld(f"{name}/kernel"),
+                 bias=self._b(f"{name}/bias"), **epi)
+
+    def _bwd_linear(self, X, dY, M, name, N, K, dX16=None, x_ld=None, dy_ld=None, bias_rows=None, **epi):
+        """Gradients of Y = X[M,K] @ W[K,N] + b given dY (bf16):
+        dW += X^T dY, db += colsum(dY), and optionally dX16 = epilogue(dY @ W^T)."""
+        ldw = self.ps.ld(f"{name}/kernel")
+        ops.gemm(X, dY, K, N, M, a_mn=True, b_mn=True, lda=x_ld, ldb=dy_ld,
+                 out_f32=self.ps.grad(f"{name}/kernel"), ldo_f32=ldw, accumulate=True)
+        period, skip = bias_rows if bias_rows else (0, 0)
+        ops.colsum(dY, M, N, self.ps.grad(f"{name}/bias"), row_period=period, row_skip=skip, ldx=dy_ld)
+        if dX16 is not None or epi:
+            ops.gemm(dY, self._W(f"{name}/kernel"), M, K, N, b_mn=False, lda=dy_ld, ldb=ldw, out_bf16=dX16, **epi)
+
+    # ------------------------------------------------------------------ forward
+    def forward(self, images: torch.Tensor, noise: torch.Tensor, want_grad: bool = True,
+                grad_scale: float = 1.0) -> torch.Tensor:
+        """images uint8 [B,3,H,W] (device), noise f32 [N] (device) -> loss (device scalar tensor [1])."""
+        cfg, ps, B = self.cfg, self.ps, self.B
+        J, n, N, d, dd, P = cfg.num_cls_tokens, cfg.keep, cfg.num_patches, cfg.dim, cfg.dec_dim, cfg.patch_dim
+        Te, Td, Me, Md = self.Te, self.Td, self.Me, self.Md
+        if tuple(images.shape) != (B, 3, cfg.image_size, cfg.image_size):
+            raise _lib.JmError(f"engine built for images {(B, 3, cfg.image_size, cfg.image_size)}, got {tuple(images.shape)}")
+        self.images = images
+        c = _lib.check
+        lib = _lib.load()
+        st = _lib.stream_ptr()
+        # random_masking (src/utils_mae.py:88-96) from host-supplied noise
+        c(lib.jm_mask_sort(noise.data_ptr(), N, n, self.ids_shuffle.data_ptr(), self.ids_restore.data_ptr(),
+                           self.mask_row.data_ptr(), st))
+        # pre-processing + extract kept patches (src/pretraining.py:90-91, modeling.py:246,256)
+        ops.patchify(images, cfg.patch_size, self.ids_shuffle, n, Te, J, self.patches)
+        x0 = self.xa[0]
+        ops.fill_cls(x0, B, Te, J, d, ps.f("model/cls_tokens"))
+        self._fwd_linear(self.patches, Me, "model/embed/wte", d, P, lda=self.Pp, out_f32=x0, pe=self.wpe,
+                         pe_idx=self.ids_shuffle, row_period=Te, row_skip=J, row_mask_mode=2)
+        for i in range(cfg.layers):
+            self._block_fwd(f"model/layer_{i}", self.enc[i], self.xa[i], self.xa[i + 1], Me, d, cfg.heads, Te, True)
+        ops.layernorm_fwd(self.xa[cfg.layers], ps.f("model/norm/scale"), ps.f("model/norm/bias"), LN_EPS,
+                          self.enc_n, None, self.meanF, self.rstdF)
+        # decoder_proj + mask tokens + unshuffle + dec_wpe (src/pretraining.py:95-106, modeling.py:289-292)
+        self._fwd_linear(self.enc_n, Me, "decoder_proj", dd, d, out_f32=self.y)
+        ops.unshuffle_fwd(self.y, self.ids_restore, ps.f("image_mask_embedding"), self.dec_wpe, B, N, n, J, dd,
+                          self.za[0])
+        for i in range(cfg.dec_layers):
+            self._block_fwd(f"decoder_model/dec_layer_{i}", self.dec[i], self.za[i], self.za[i + 1], Md, dd,
+                            cfg.dec_heads, Td, False)
+        ops.layernorm_fwd(self.za[cfg.dec_layers], ps.f("decoder_model/dec_norm/scale"),
+                          ps.f("decoder_model/dec_norm/bias"), LN_EPS, self.dec_n, None, self.meanD, self.rstdD)
+        # pixel head on every token row; CLS / visible rows are ignored by the loss
+        self._fwd_linear(self.dec_n, Md, "decoder_image_output", P, dd, out_f32=self.pred)
+        ops.patch_loss(self.pred, images, self.mask_row, cfg.patch_size, J, cfg.norm_pix_loss, grad_scale, self.loss,
+                       self.dpred if want_grad else None, self.loss_ws)
+        return self.loss
+
+    def _block_fwd(self, name, s: _Block, x_in, x_out, M, dim, heads, T, jumbo):
+        ps, B, J = self.ps, self.B, self.cfg.num_cls_tokens
+        hd = dim // heads
+        # x_b = x + attn(LN1(x))            (src/modeling.py:165 / :192)
+        ops.layernorm_fwd(x_in, ps.f(f"{name}/norm1/scale"), ps.f(f"{name}/norm1/bias"), LN_EPS, s.xn1, None,
+                          s.mean1, s.rstd1)
+        self._fwd_linear(s.xn1, M, f"{name}/attn/wqkv", 3 * dim, dim, out_bf16=s.qkv, col_scale=hd ** -0.5,
+                         col_scale_n=dim)
+        ops.attention_fwd(s.qkv, B, T, heads, hd, s.att, s.lse)
+        self._fwd_linear(s.att, M, f"{name}/attn/wo", dim, dim, out_f32=s.xb, residual=x_in)
+        if jumbo:
+            Jd = J * dim
+            # c = LN3(cls concat); c = c + jumbo_mlp(c)      (src/modeling.py:194-199)
+            ops.layernorm_fwd(s.xb, ps.f(f"{name}/norm3/scale"), ps.f(f"{name}/norm3/bias"), LN_EPS, s.cn16, s.cn,
+                              s.mean3, s.rstd3, rows=B, dim=Jd, ldx=T * dim, ldy=Jd, ldyf=Jd)
+            self._fwd_linear(s.cn16, B, "model/jumbo_mlp/w1", 4 * Jd, Jd, out_bf16=s.hj, out2_bf16=s.gj, act=1)
+            self._fwd_linear(s.gj, B, "model/jumbo_mlp/w2", Jd, 4 * Jd, out_f32=x_out, ldo_f32=T * dim,
+                             residual=s.cn)
+        period, skip = (T, J) if jumbo else (0, 0)
+        # patch tokens: x = x_b + ff(LN2(x_b))       (src/modeling.py:166 / :201)
+        ops.layernorm_fwd(s.xb, ps.f(f"{name}/norm2/scale"), ps.f(f"{name}/norm2/bias"), LN_EPS, s.xn2, None,
+                          s.mean2, s.rstd2)
+        self._fwd_linear(s.xn2, M, f"{name}/ff/w1", 4 * dim, dim, out_bf16=s.h, out2_bf16=s.g, act=1,
+                         row_period=period, row_skip=skip, row_mask_mode=1 if jumbo else 0)
+        self._fwd_linear(s.g, M, f"{name}/ff/w2", dim, 4 * dim, out_f32=x_out, residual=s.xb, row_period=period,
+                         row_skip=skip, row_mask_mode=2 if jumbo else 0)
+
+    # ------------------------------------------------------------------ backward
+    def backward(self, zero_grads: bool = True) -> None:
+        """Accumulates d loss / d params into store.g (after ``forward(want_grad=True)``)."""
+        cfg, ps, B = self.cfg, self.ps, self.B
+        J, n, N, d, dd, P = cfg.num_cls_tokens, cfg.keep, cfg.num_patches, cfg.dim, cfg.dec_dim, cfg.patch_dim
+        Te, Td, Me, Md, Pp = self.Te, self.Td, self.Me, self.Md, self.Pp
+        if zero_grads:
+            ps.g.zero_()
+        view = lambda buf, M, w: buf[:M * w].view(M, w)
+        # ---- pixel head
+        dn = view(self.dn16, Md, dd)
+        self._bwd_linear(self.dec_n, self.dpred, Md, "decoder_image_output", P, dd, dX16=dn, dy_ld=Pp)
+        dx, dx16 = view(self.dxA, Md, dd), view(self.dxA16, Md, dd)
+        ops.layernorm_bwd(dn, self.za[cfg.dec_layers], self.meanD, self.rstdD, ps.f("decoder_model/dec_norm/scale"),
+                          None, dx, dx16, ps.grad("decoder_model/dec_norm/scale"),
+                          ps.grad("decoder_model/dec_norm/bias"), self.ln_ws)
+        # ---- decoder blocks
+        for i in reversed(range(cfg.dec_layers)):
+            self._block_bwd(f"decoder_model/dec_layer_{i}", self.dec[i], self.za[i], Md, dd, cfg.dec_heads, Td, False)
+        # ---- decoder input assembly + decoder_proj
+        ops.unshuffle_bwd(dx, self.ids_restore, B, N, n, J, dd, self.dy16, ps.grad("image_mask_embedding"))
+        dn = view(self.dn16, Me, d)
+        self._bwd_linear(self.enc_n, self.dy16, Me, "decoder_proj", dd, d, dX16=dn)
+        dx, dx16 = view(self.dxA, Me, d), view(self.dxA16, Me, d)
+        ops.layernorm_bwd(dn, self.xa[cfg.layers], self.meanF, self.rstdF, ps.f("model/norm/scale"), None, dx, dx16,
+                          ps.grad("model/norm/scale"), ps.grad("model/norm/bias"), self.ln_ws)
+        # ---- encoder blocks
+        for i in reversed(range(cfg.layers)):
+            self._block_bwd(f"model/layer_{i}", self.enc[i], self.xa[i], Me, d, cfg.heads, Te, True)
+        # ---- CLS parameter and patch embedding
+        ops.colsum(dx, B, J * d, ps.grad("model/cls_tokens"), ldx=Te * d)
+        ops.gemm(self.patches, dx16, P, d, Me, a_mn=True, b_mn=True, lda=Pp,
+                 out_f32=ps.grad("model/embed/wte/kernel"), ldo_f32=ps.ld("model/embed/wte/kernel"), accumulate=True)
+        ops.colsum(dx16, Me, d, ps.grad("model/embed/wte/bias"), row_period=Te, row_skip=J)
+
+    def _block_bwd(self, name, s: _Block, x_in, M, dim, heads, T, jumbo):
+        """In: d/d(block output) in dxA / dxA16.  Out: d/d(block input) in dxA / dxA16."""
+        ps, B, J = self.ps, self.B, self.cfg.num_cls_tokens
+        hd = dim // heads
+        view = lambda buf, w: buf[:M * w].view(M, w)
+        dx, dx16 = view(self.dxA, dim), view(self.dxA16, dim)
+        dxb, dxb16 = view(self.dxB, dim), view(self.dxB16, dim)
+        dh, dn = view(self.dh16, 4 * dim), view(self.dn16, dim)
+        period, skip = (T, J) if jumbo else (0, 0)
+        mode = 1 if jumbo else 0
+        # ---- patch FFN: y = x_b + w2(gelu(w1 LN2(x_b)))
+        self._bwd_linear(s.g, dx16, M, f"{name}/ff/w2", dim, 4 * dim, dX16=dh, bias_rows=(period, skip),
+                         act=2, aux=s.h, row_period=period, row_skip=skip, row_mask_mode=mode)
+        self._bwd_linear(s.xn2, dh, M, f"{name}/ff/w1", 4 * dim, dim, dX16=dn)
+        ops.layernorm_bwd(dn, s.xb, s.mean2, s.rstd2, ps.f(f"{name}/norm2/scale"), dx, dxb, dxb16,
+                          ps.grad(f"{name}/norm2/scale"), ps.grad(f"{name}/norm2/bias"), self.ln_ws,
+                          row_period=period, row_skip=skip)
+        if jumbo:
+            # ---- Jumbo CLS: c_out = c + w2j(gelu(w1j c)), c = LN3(cls concat); strided [B, J*dim] views
+            Jd, ldc = J * dim, T * dim
+            self._bwd_linear(s.gj, dx16, B, "model/jumbo_mlp/w2", Jd, 4 * Jd, dX16=self.dhj16, dy_ld=ldc, act=2,
+                             aux=s.hj)
+            self._bwd_linear(s.cn16, self.dhj16, B, "model/jumbo_mlp/w1", 4 * Jd, Jd, dX16=self.dcn16,
+                             residual=dx, ldr=ldc)
+            ops.layernorm_bwd(self.dcn16, s.xb, s.mean3, s.rstd3, ps.f(f"{name}/norm3/scale"), None, dxb, dxb16,
+                              ps.grad(f"{name}/norm3/scale"), ps.grad(f"{name}/norm3/bias"), self.ln_ws, rows=B,
+                              dim=Jd, ldx=ldc, lddx=ldc, lddxb=ldc)
+        # ---- attention branch: x_b = x + wo(attn(wqkv LN1(x)))
+        datt, dqkv = view(self.datt16, dim), view(self.dqkv16, 3 * dim)
+        self._bwd_linear(s.att, dxb16, M, f"{name}/attn/wo", dim, dim, dX16=datt)
+        ops.attention_bwd(s.qkv, s.att, datt, s.lse, B, T, heads, hd, hd ** -0.5, dqkv)
+        self._bwd_linear(s.xn1, dqkv, M, f"{name}/attn/wqkv", 3 * dim, dim, dX16=dn)
+        ops.layernorm_bwd(dn, x_in, s.mean1, s.rstd1, ps.f(f"{name}/norm1/scale"), dxb, dx, dx16,
+                          ps.grad(f"{name}/norm1/scale"), ps.grad(f"{name}/norm1/bias"), self.ln_ws)
+
+    # ------------------------------------------------------------------ optimizer
+    def adamw_step(self, count: int, lr: float, grad_scale: float = 1.0) -> None:
+        """optax.adamw update number ``count`` (0-based) over the flat buffers (src/pretraining.py:223-234)."""
+        cfg, ps = self.cfg, self.ps
+        t = count + 1
+        ops.adamw(ps.p, ps.g, ps.m, ps.v, ps.p16, ps.n_decay, lr, cfg.adam_b1, cfg.adam_b2, cfg.adam_eps,
+                  cfg.weight_decay, 1.0 - cfg.adam_b1 ** t, 1.0 - cfg.adam_b2 ** t, grad_scale)
+
+    # ------------------------------------------------------------------ accounting
+    def activation_bytes(self) -> int:
+        tot = 0
+        for obj in [self] + self.enc + self.dec:
+            for v in vars(obj).values():
+                if isinstance(v, torch.Tensor):
+                    tot += v.numel() * v.element_size()
+                elif isinstance(v, list):
+                    tot += sum(t.numel() * t.element_size() for t in v if isinstance(t, torch.Tensor))
+        return tot
+
+
+def lr_schedule(count: int, cfg: MAEConfig) -> float:
+    """optax.warmup_cosine_decay_schedule(1e-6, lr*batch/256, warmup, training_steps, 1e-5)
+    (src/pretraining.py:250-259), evaluated on the host."""
+    init_value, end_value = 1e-6, 1e-5
+    peak = cfg.learning_rate * cfg.train_batch_size / 256
+    warm = cfg.warmup_steps
+    if count < warm:
+        frac = 1.0 - count / warm
+        return (init_value - peak) * frac + peak
+    decay_steps = cfg.training_steps - warm
+    c = min(count - warm, decay_steps)
+    cosine = 0.5 * (1.0 + math.cos(math.pi * c / decay_steps))
+    alpha = end_value / peak
+    return peak * ((1.0 - alpha) * cosine + alpha)

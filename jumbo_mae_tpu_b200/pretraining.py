@@ -1,0 +1,212 @@
+"""Train-step entry points with the reference's names and call shapes (src/pretraining.py).
+
+    state = create_train_state(args).replicate()
+    state, metrics = training_step(state, batch)       # batch = (images uint8 [B,3,H,W],)
+    metrics = validation_step(state, batch)
+
+One process drives one GPU (the reference's ``jax.pmap`` over local devices becomes one
+rank per device, ``lax.pmean`` becomes an NCCL all-reduce over ``torch.distributed``), so
+``batch`` is this rank's shard and ``replicate()`` only derives the per-rank RNG streams.
+"""
+from __future__ import annotations
+
+import argparse
+from dataclasses import dataclass, field
+from typing import Any, Dict, Optional, Tuple
+
+import numpy as np
+import torch
+
+from . import _lib
+from .config import MAEConfig
+from .engine import MAEEngine, lr_schedule
+from .modeling import MAEDecoder, ViT
+from .parallel import GradReducer, process_count, process_index
+from .params import ParamStore
+
+
+class PretrainModule:
+    """PretrainModule (src/pretraining.py:76-122): ViT encoder + MAEDecoder + pixel head."""
+
+    def __init__(self, model: ViT, decoder_model: MAEDecoder, image_size: int, norm_pix_loss: bool = False):
+        self.model, self.decoder_model = model, decoder_model
+        self.image_size, self.norm_pix_loss = image_size, norm_pix_loss
+
+    def config(self, **opt) -> MAEConfig:
+        m, dm = self.model, self.decoder_model
+        return MAEConfig(layers=m.layers, dim=m.dim, heads=m.heads, patch_size=m.patch_size, image_size=m.image_size,
+                         image_mask_ratio=m.image_mask_ratio, num_cls_tokens=m.num_cls_tokens,
+                         dec_layers=dm.dec_layers, dec_dim=dm.dec_dim, dec_heads=dm.dec_heads,
+                         norm_pix_loss=self.norm_pix_loss, **opt)
+
+
+@dataclass
+class TrainState:
+    """Numeric state of flax's TrainState + the reference's extra fields (src/pretraining.py:50-57).
+
+    ``params`` / ``opt_state`` are Flax-shaped trees of views into the flat device buffers
+    held by ``store`` (the step updates them in place: the reference donates its state)."""
+    step: int
+    store: ParamStore
+    cfg: MAEConfig
+    module: PretrainModule
+    mixup_rng: int
+    dropout_rng: int
+    noise_rng: int
+    micro_step: int = 0
+    micro_in_mini: int = 1
+    engines: Dict[int, MAEEngine] = field(default_factory=dict)
+    reducer: Optional[GradReducer] = None
+    _noise_gen: Optional[np.random.Generator] = None
+
+    @property
+    def params(self) -> dict:
+        return self.store.tree()
+
+    @property
+    def opt_state(self) -> dict:
+        return {"count": self.step, "mu": self.store.tree(self.store.m), "nu": self.store.tree(self.store.v),
+                "hyperparams": {"learning_rate": lr_schedule(max(self.step - 1, 0), self.cfg)}}
+
+    @property
+    def grad_accum(self):
+        return self.store.tree(self.store.g) if self.micro_in_mini > 1 else None
+
+    def replicate(self) -> "TrainState":
+        """src/pretraining.py:68-73.  Parameters already live on this rank's device; what
+        remains is giving every device its own RNG streams (shard_prng_key)."""
+        self._noise_gen = np.random.Generator(np.random.Philox(key=self.noise_rng + 7919 * process_index()))
+        return self
+
+    def split_rngs(self) -> Tuple[dict, dict]:
+        """src/pretraining.py:59-66: draws this step's "noise" stream (mixup / dropout are
+        identity at the recipe's rates).  Returns (rngs, updates) like the reference."""
+        if self._noise_gen is None:
+            self.replicate()
+        noise = self._noise_gen.random(self.cfg.num_patches, dtype=np.float32)
+        return {"noise": noise}, {}
+
+    def engine(self, batch: int) -> MAEEngine:
+        if batch not in self.engines:
+            self.engines[batch] = MAEEngine(self.cfg, self.store, batch)
+        return self.engines[batch]
+
+
+def create_train_state(args: argparse.Namespace) -> TrainState:
+    """src/pretraining.py:170-270: builds the modules from the CLI namespace, initialises the
+    parameters (truncated-normal(0.02) kernels, zero biases / CLS, unit LayerNorm scales) and the
+    AdamW state, seeds the RNG streams with ``seed + process_index``."""
+    _lib.require_device()
+    if getattr(args, "optimizer", "adamw") != "adamw":
+        raise NotImplementedError("only --optimizer adamw (both pre-training presets) is on the hot path")
+    if getattr(args, "lr_decay", 1.0) < 1.0 or getattr(args, "clip_grad", 0.0) > 0:
+        raise NotImplementedError("--lr-decay < 1 and --clip-grad > 0 are inactive at the pre-training presets")
+    for nm in ("dropout", "droppath", "dec_dropout", "dec_droppath"):
+        if getattr(args, nm, 0.0) != 0.0:
+            raise NotImplementedError(f"--{nm.replace('_', '-')} > 0 is not built (0.0 in both presets)")
+    if getattr(args, "layerscale", False) or getattr(args, "dec_layerscale", False):
+        raise NotImplementedError("LayerScale is off in both presets and not built")
+    if getattr(args, "posemb", "sincos2d") != "sincos2d":
+        raise NotImplementedError("only --posemb sincos2d (both presets) is built")
+    model = ViT(layers=args.layers, dim=args.dim, heads=args.heads, labels=getattr(args, "labels", 0),
+                patch_size=args.patch_size, image_size=args.image_size, posemb="sincos2d",
+                image_mask_ratio=args.image_mask_ratio)
+    decoder = MAEDecoder(dec_layers=args.dec_layers, dec_dim=args.dec_dim, dec_heads=args.dec_heads,
+                         patch_size=args.patch_size, image_size=args.image_size)
+    module = PretrainModule(model, decoder, args.image_size, getattr(args, "norm_pix_loss", False))
+    cfg = module.config(learning_rate=args.learning_rate, train_batch_size=args.train_batch_size,
+                        weight_decay=args.weight_decay, adam_b1=args.adam_b1, adam_b2=args.adam_b2,
+                        adam_eps=args.adam_eps, warmup_steps=args.warmup_steps, training_steps=args.training_steps,
+                        grad_accum=getattr(args, "grad_accum", 1))
+    cfg.validate()
+    store = ParamStore(cfg, device=torch.device("cuda", torch.cuda.current_device()))
+    init_params_(store, getattr(args, "init_seed", 0))
+    return TrainState(step=0, store=store, cfg=cfg, module=module,
+                      mixup_rng=getattr(args, "mixup_seed", 0) + process_index(),
+                      dropout_rng=getattr(args, "dropout_seed", 0) + process_index(),
+                      noise_rng=getattr(args, "noise_seed", 0) + process_index(),
+                      micro_step=0, micro_in_mini=cfg.grad_accum)
+
+
+def init_params_(store: ParamStore, seed: int) -> None:
+    """Reference init rules (src/modeling.py:30-32,243; src/pretraining.py:38,83), identical on
+    every rank: kernels and image_mask_embedding ~ truncated_normal(0.02) on [-2, 2] sigma."""
+    gen = torch.Generator(device="cpu").manual_seed(seed)
+    tree = store.tree()
+
+    def walk(node, path):
+        for key in sorted(node.keys()):
+            val = node[key]
+            if isinstance(val, dict):
+                walk(val, path + (key,))
+            elif key == "kernel" or key == "image_mask_embedding":
+                t = torch.empty(tuple(val.shape), dtype=torch.float32)
+                torch.nn.init.trunc_normal_(t, mean=0.0, std=1.0, a=-2.0, b=2.0, generator=gen)
+                val.copy_((t * 0.02).to(val.device))
+            elif key == "scale":
+                val.fill_(1.0)
+            else:
+                val.zero_()
+    walk(tree, ())
+    store.refresh_bf16()
+
+
+def _device_images(images) -> torch.Tensor:
+    if isinstance(images, np.ndarray):
+        images = torch.from_numpy(images)
+    if images.dtype != torch.uint8:
+        raise _lib.JmError("images must be uint8 NCHW (normalisation happens on the device, src/pretraining.py:88-91)")
+    if not images.is_cuda:
+        images = images.cuda(non_blocking=True)
+    return images.contiguous()
+
+
+def training_step(state: TrainState, batch, noise=None) -> Tuple[TrainState, Dict[str, Any]]:
+    """src/pretraining.py:125-159.  ``batch`` is the 1-tuple ``(images,)`` the reference splats
+    into ``apply_fn``; images are this rank's uint8 [B, 3, H, W] shard (host or device).
+    ``noise`` (f32 [num_patches]) overrides the state's noise stream (parity tests).
+    Returns (state, {"loss": device scalar, "learning_rate": float})."""
+    images = _device_images(batch[0] if isinstance(batch, (tuple, list)) else batch)
+    rngs, _ = state.split_rngs() if noise is None else ({"noise": noise}, {})
+    nz = rngs["noise"]
+    nz = torch.from_numpy(np.ascontiguousarray(nz, dtype=np.float32)) if isinstance(nz, np.ndarray) else nz
+    nz = nz.to(device=images.device, dtype=torch.float32, non_blocking=True)
+    eng = state.engine(images.shape[0])
+    world = process_count()
+    accum = state.micro_in_mini
+    loss = eng.forward(images, nz, want_grad=True)
+    if state.reducer is None and world > 1:
+        state.reducer = GradReducer(state.store)
+    first_micro = state.micro_step == 0
+    eng.backward(zero_grads=first_micro)
+    metrics_loss = loss.clone()
+    if world > 1:
+        state.reducer.mean_scalar(metrics_loss)                      # lax.pmean(metrics) (:144)
+    state.micro_step += 1
+    lr = lr_schedule(state.step, state.cfg) if state.step > 0 or state.micro_step == accum else lr_schedule(0, state.cfg)
+    if state.micro_step == accum:                                    # :149-158
+        if world > 1:
+            state.reducer.all_reduce_grads()                         # lax.pmean(grads) (:150); 1/world below
+        lr = lr_schedule(state.step, state.cfg)
+        eng.adamw_step(state.step, lr, grad_scale=1.0 / (accum * world))
+        state.step += 1
+        state.micro_step = 0
+    return state, {"loss": metrics_loss[0], "learning_rate": lr}
+
+
+def validation_step(state: TrainState, batch, noise=None) -> Dict[str, Any]:
+    """src/pretraining.py:162-167: forward only with freshly split (not stored) RNGs;
+    returns psum-ed {"loss", "num_samples"}."""
+    images = _device_images(batch[0] if isinstance(batch, (tuple, list)) else batch)
+    if noise is None:
+        gen = np.random.Generator(np.random.Philox(key=state.noise_rng + 7919 * process_index() + 104729))
+        noise = gen.random(state.cfg.num_patches, dtype=np.float32)
+    nz = torch.from_numpy(np.ascontiguousarray(noise, dtype=np.float32)).to(images.device)
+    eng = state.engine(images.shape[0])
+    loss = eng.forward(images, nz, want_grad=False).clone()
+    num = torch.tensor([float(images.shape[0])], device=images.device)
+    if process_count() > 1:
+        import torch.distributed as dist
+        dist.all_reduce(loss)
+        dist.all_reduce(num)
+    return {"loss": loss[0], "num_samples": num[0]}

@@ -1,0 +1,59 @@
+"""CPU tests of the host-side parameter layout (jumbo_mae_tpu_b200/params.py): the Flax-shaped
+view tree has the reference's names and shapes, views alias the flat buffer, and the
+weight-decay boundary separates exactly the leaves named ``kernel``."""
+import torch
+
+from oracle import jumbo_mae_oracle as O
+from jumbo_mae_tpu_b200.config import MAEConfig, vit_b16, vit_h14
+from jumbo_mae_tpu_b200.engine import lr_schedule
+from jumbo_mae_tpu_b200.params import ParamStore, tree_leaves
+
+
+def _pc(ocfg):
+    return MAEConfig(**{f: getattr(ocfg, f) for f in MAEConfig.__dataclass_fields__ if hasattr(ocfg, f)})
+
+
+def test_tree_matches_reference_names_and_shapes():
+    for ocfg in (O.tiny(), O.MAEConfig(layers=1, dim=160, heads=2, patch_size=14, image_size=56, dec_layers=1,
+                                       dec_dim=64, dec_heads=2)):
+        want = O.init_params(ocfg, 0)
+        store = ParamStore(_pc(ocfg), device="cpu")
+        got = dict(tree_leaves(store.tree()))
+        ref = dict(O.tree_leaves(want))
+        assert set(got) == set(ref)
+        for path, w in ref.items():
+            assert tuple(got[path].shape) == tuple(w.shape), path
+
+
+def test_views_alias_flat_buffer_and_decay_boundary():
+    ocfg = O.tiny()
+    store = ParamStore(_pc(ocfg), device="cpu")
+    tree = store.tree()
+    for i, (path, leaf) in enumerate(tree_leaves(tree)):
+        leaf.fill_(float(i + 1))
+    flagged = torch.zeros(store.total, dtype=torch.bool)
+    for i, (path, leaf) in enumerate(tree_leaves(tree)):
+        idx = (store.p == float(i + 1)).nonzero().flatten()
+        assert idx.numel() == leaf.numel(), path
+        is_kernel = path[-1] == "kernel"
+        assert bool((idx < store.n_decay).all()) == is_kernel and bool((idx >= store.n_decay).all()) != is_kernel, path
+        flagged[idx] = True
+    assert store.n_decay % 4 == 0 and store.total % 4 == 0
+    # everything not covered by a leaf is padding and stays zero
+    assert torch.equal(store.p[~flagged], torch.zeros(int((~flagged).sum())))
+
+
+def test_param_count_vit_b():
+    store = ParamStore(vit_b16(), device="meta")
+    n = sum(l.rows * l.cols for l in store.leaves.values())
+    assert n == O.count_params(O.init_params(O.tiny())) or n == 154_191_360
+    h = ParamStore(vit_h14(), device="meta")
+    assert h.ld("decoder_image_output/kernel") == 592       # 588 padded to a multiple of 8
+
+
+def test_lr_schedule_matches_oracle():
+    ocfg = O.vit_b16()
+    cfg = _pc(ocfg)
+    for count in (0, 1, 100, cfg.warmup_steps - 1, cfg.warmup_steps, cfg.warmup_steps + 1, 250000, cfg.training_steps,
+                  cfg.training_steps + 5):
+        assert lr_schedule(count, cfg) == O.lr_schedule(count, ocfg)

@@ -1,0 +1,165 @@
+"""Whole-step parity on the GPU: forward activations, loss, every parameter gradient and
+multi-step AdamW trajectories of the kernel schedule (jumbo_mae_tpu_b200.engine) against
+the f32 CPU oracle on identical parameters, images and noise.
+
+Tolerances (bf16 operands / f32 accumulation vs an f32 reference):
+  masking indices                      exact
+  activations (relative L2)            <= 1e-2 encoder, <= 3e-2 decoder output
+  loss (relative)                      <= 5e-3
+  per-leaf gradient (relative L2)      <= 3e-2, cosine >= 0.999
+  k-step parameter delta (relative L2) <= 5e-2 on leaves whose update is not sign-noise
+"""
+import numpy as np
+import pytest
+import torch
+
+from oracle import jumbo_mae_oracle as O
+
+pytestmark = pytest.mark.gpu
+
+
+def _cfgs():
+    return {
+        "tiny": (O.tiny(), 4),
+        "tiny_normpix": (O.tiny(norm_pix_loss=True), 3),
+        "mid": (O.MAEConfig(layers=2, dim=256, heads=4, patch_size=16, image_size=64, dec_layers=2, dec_dim=128,
+                            dec_heads=4, warmup_steps=10, training_steps=100, train_batch_size=256), 8),
+        "vitb_width": (O.MAEConfig(layers=2, dec_layers=2, warmup_steps=10, training_steps=100), 3),
+        "vith_patch14": (O.MAEConfig(layers=1, dim=160, heads=2, patch_size=14, image_size=56, dec_layers=1,
+                                     dec_dim=64, dec_heads=2, warmup_steps=10, training_steps=100), 5),
+    }
+
+
+def _product_cfg(ocfg):
+    from jumbo_mae_tpu_b200.config import MAEConfig
+    return MAEConfig(**{f: getattr(ocfg, f) for f in MAEConfig.__dataclass_fields__ if hasattr(ocfg, f)})
+
+
+def _setup(name):
+    from jumbo_mae_tpu_b200.engine import MAEEngine
+    from jumbo_mae_tpu_b200.params import ParamStore
+    ocfg, B = _cfgs()[name]
+    cfg = _product_cfg(ocfg)
+    state = O.create_state(ocfg, seed=0, randomize_all=True)
+    images, noise = O.synthetic_batch(ocfg, B, seed=1, noise_seed=1001)
+    store = ParamStore(cfg)
+    store.load_tree(state.params)
+    eng = MAEEngine(cfg, store, B)
+    return ocfg, cfg, state, images, noise, store, eng
+
+
+def _rel(a, b):
+    return ((a - b).norm() / (b.norm() + 1e-12)).item()
+
+
+@pytest.mark.parametrize("name", ["tiny", "tiny_normpix", "mid", "vitb_width", "vith_patch14"])
+def test_forward_loss_and_activations(name):
+    ocfg, cfg, state, images, noise, store, eng = _setup(name)
+    collect = {}
+    want = O.pretrain_forward(state.params, images, noise, ocfg, collect)["loss"].item()
+    loss = eng.forward(images.cuda(), torch.from_numpy(noise).cuda(), want_grad=False)
+    torch.cuda.synchronize()
+    B = images.shape[0]
+    assert np.array_equal(eng.ids_restore.cpu().numpy(), collect["ids_restore"].numpy())       # bit exact
+    assert np.array_equal(eng.mask_row.cpu().numpy(), collect["mask"][0].numpy())
+    acts = {
+        "enc_in": eng.xa[0], f"enc_layer_{ocfg.layers - 1}": eng.xa[ocfg.layers],
+        "dec_in": eng.za[0], f"dec_layer_{ocfg.dec_layers - 1}": eng.za[ocfg.dec_layers],
+    }
+    for key, got in acts.items():
+        w = collect[key]
+        r = _rel(got.cpu().reshape(w.shape), w)
+        assert r <= (1e-2 if key.startswith("enc") else 3e-2), f"{key}: rel l2 {r}"
+    pred = eng.pred.cpu().reshape(B, -1, ocfg.patch_dim)[:, 3:]
+    assert _rel(pred, collect["image_output"]) <= 3e-2
+    assert abs(loss.item() - want) <= 5e-3 * abs(want), (loss.item(), want)
+
+
+@pytest.mark.parametrize("name", ["tiny", "tiny_normpix", "mid", "vitb_width", "vith_patch14"])
+def test_gradients_match_oracle(name):
+    from jumbo_mae_tpu_b200.params import tree_leaves
+    ocfg, cfg, state, images, noise, store, eng = _setup(name)
+    want_loss, want = O.loss_and_grads(state.params, images, noise, ocfg)
+    eng.forward(images.cuda(), torch.from_numpy(noise).cuda())
+    eng.backward()
+    torch.cuda.synchronize()
+    got = dict(tree_leaves(store.tree(store.g)))
+    bad = []
+    ref = dict(O.tree_leaves(want))
+    for path, w in ref.items():
+        g = got[path].detach().cpu().reshape(w.shape)
+        if path[-2:] == ("wk", "bias"):
+            # softmax is invariant to a shift of every key, so d loss / d(key bias) is identically zero:
+            # both sides hold rounding noise only.  Bound it against the sibling value-bias gradient.
+            scale = ref[path[:-2] + ("wv", "bias")].norm().item()
+            if not (g.norm().item() <= 3e-2 * scale and w.norm().item() <= 1e-3 * scale):
+                bad.append(("/".join(path), g.norm().item(), scale))
+            continue
+        r = _rel(g, w)
+        cos = (g.flatten() @ w.flatten() / (g.norm() * w.norm() + 1e-20)).item()
+        if not (r <= 3e-2 and cos >= 0.999):
+            bad.append(("/".join(path), r, cos))
+    assert not bad, bad
+
+
+def test_backward_accumulates_and_rezeroes():
+    ocfg, cfg, state, images, noise, store, eng = _setup("tiny")
+    im, nz = images.cuda(), torch.from_numpy(noise).cuda()
+    eng.forward(im, nz)
+    eng.backward()
+    g1 = store.g.clone()
+    eng.forward(im, nz)
+    eng.backward(zero_grads=False)                  # gradient accumulation: sum (src/pretraining.py:153)
+    assert torch.allclose(store.g, 2 * g1, rtol=1e-4, atol=1e-7)
+    eng.forward(im, nz)
+    eng.backward()
+    assert torch.allclose(store.g, g1, rtol=1e-4, atol=1e-7)
+
+
+@pytest.mark.parametrize("name", ["tiny", "mid"])
+def test_k_step_training_matches_oracle(name):
+    from jumbo_mae_tpu_b200.engine import lr_schedule
+    from jumbo_mae_tpu_b200.params import tree_leaves
+    ocfg, cfg, state, images, noise, store, eng = _setup(name)
+    im = images.cuda()
+    k = 5
+    p0 = dict(O.tree_leaves(state.params))
+    losses_o, losses_g = [], []
+    for step in range(k):
+        nz = np.random.default_rng(100 + step).random(ocfg.num_patches, dtype=np.float32)
+        state, met, _ = O.training_step(state, images, nz)
+        losses_o.append(met["loss"])
+        loss = eng.forward(im, torch.from_numpy(nz).cuda())
+        eng.backward()
+        lr = lr_schedule(step, cfg)
+        assert abs(lr - met["learning_rate"]) < 1e-12
+        eng.adamw_step(step, lr)
+        losses_g.append(loss.item())
+    torch.cuda.synchronize()
+    for a, b in zip(losses_g, losses_o):
+        assert abs(a - b) <= 5e-3 * abs(b)
+    got = dict(tree_leaves(store.tree()))
+    worst = 0.0
+    for path, w in O.tree_leaves(state.params):
+        if path[-2:] == ("wk", "bias"):
+            continue        # zero true gradient: Adam turns rounding noise into +-lr steps on both sides
+        delta_w = w - p0[path]
+        delta_g = got[path].detach().cpu().reshape(w.shape) - p0[path]
+        # Early Adam steps move every weight by ~lr * sign(g): leaves whose gradient is below bf16
+        # resolution of its neighbours flip sign at random; compare in aggregate (relative L2).
+        r = _rel(delta_g, delta_w)
+        worst = max(worst, r)
+        assert r <= 0.25, ("/".join(path), r)
+    leaves = [(p, w) for p, w in O.tree_leaves(state.params) if p[-2:] != ("wk", "bias")]
+    all_w = torch.cat([(w - p0[p]).flatten() for p, w in leaves])
+    all_g = torch.cat([(got[p].detach().cpu().reshape(w.shape) - p0[p]).flatten() for p, w in leaves])
+    assert _rel(all_g, all_w) <= 5e-2
+    # bf16 compute copy tracks the f32 masters
+    assert torch.equal(store.p16.float(), store.p.to(torch.bfloat16).float())
+
+
+def test_engine_rejects_wrong_batch_shape():
+    from jumbo_mae_tpu_b200._lib import JmError
+    ocfg, cfg, state, images, noise, store, eng = _setup("tiny")
+    with pytest.raises(JmError):
+        eng.forward(images[:2].cuda(), torch.from_numpy(noise).cuda())
