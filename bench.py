@@ -1,0 +1,340 @@
+#!/usr/bin/env python
+"""Headline benchmark: MAE ViT-B/16 (Jumbo CLS) pre-training step throughput on B200.
+
+    python bench.py --gpus 1 --steps K --warmup W            # this repo's CUDA path
+    python bench.py --impl reference --gpus 1 --steps K ...  # the reference algorithm on host cores
+    torchrun --nproc-per-node N bench.py --gpus N ...        # one rank per GPU, NCCL
+
+Workload (BASELINE.json configs[1]): ViT-B/16, 224 px, mask 0.75, decoder 8 x 512 (16 heads),
+Jumbo CLS J = 3, bf16 compute, GLOBAL batch 4096 synthetic uint8 images per optimizer step,
+run as micro-batches of 512 per GPU with the reference's gradient-accumulation semantics
+(4096 / (512 * N) micro-steps per rank, one gradient all-reduce and one AdamW per step).
+One "step" = one optimizer step = forward + backward of 4096 images + all-reduce + AdamW.
+
+Prints ONE JSON line (rank 0).  `value` is whole-job images/s with inputs resident in HBM;
+`e2e` is the same step through the public API (`training_step`) with pinned-host uint8 images
+copied in and the loss read back every micro-step inside the timed region.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+
+def preset_args(name: str, global_batch: int) -> argparse.Namespace:
+    """The reference's CLI namespace for its pre-training presets (config/pretrain/*.sh)."""
+    shapes = {
+        "vit_b16": dict(layers=12, dim=768, heads=12, patch_size=16, training_steps=1281167 * 1600 // 4096),
+        "vit_l16": dict(layers=24, dim=1024, heads=16, patch_size=16, training_steps=1281167 * 800 // 4096),
+        "vit_h14": dict(layers=32, dim=1280, heads=16, patch_size=14, training_steps=1281167 * 800 // 4096),
+    }[name]
+    return argparse.Namespace(
+        image_mask_ratio=0.75, labels=0, image_size=224, posemb="sincos2d", pooling="cls", dropout=0.0, droppath=0.0,
+        layerscale=False, grad_ckpt=False, dec_layers=8, dec_dim=512, dec_heads=16, dec_layerscale=False,
+        dec_posemb="sincos2d", dec_dropout=0.0, dec_droppath=0.0, norm_pix_loss=False, init_seed=0, mixup_seed=0,
+        dropout_seed=0, noise_seed=0, optimizer="adamw", learning_rate=1.5e-4, weight_decay=0.05, adam_b1=0.9,
+        adam_b2=0.95, adam_eps=1e-8, lr_decay=1.0, clip_grad=0.0, grad_accum=1, train_batch_size=global_batch,
+        warmup_steps=1281167 * 40 // 4096, **shapes)
+
+
+def measured_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            p = json.load(f)
+        return {"bf16_burst": p["bf16_tflops"], "bf16_sustained": p.get("bf16_tflops_sustained", p["bf16_tflops"]),
+                "hbm": p["hbm_gbs"], "source": "measured"}
+    # /opt/skills/guides/B200_PROFILING.md fallback
+    return {"bf16_burst": 1590.0, "bf16_sustained": 1400.0, "hbm": 6650.0, "source": "fallback"}
+
+
+class ClockSampler:
+    """Samples nvidia-smi clocks / throttle reasons every 200 ms while a timed region runs."""
+
+    FIELDS = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+              "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+              "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.FIELDS}", "--format=csv,noheader,nounits", "-i", str(self.index),
+                 "-lms", "200"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+
+    def summary(self):
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in self.lines:
+            parts = [p.strip() for p in line.split(",")]
+            if len(parts) < 7:
+                continue
+            try:
+                sm.append(float(parts[0]))
+                mx.append(float(parts[1]))
+            except ValueError:
+                continue
+            for nm, val in zip(names, parts[3:7]):
+                if val.lower().startswith("active"):
+                    reasons.add(nm)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(mx)), "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+# ---------------------------------------------------------------------------------------------
+def cpu_oracle_rate(config: str, batch: int, steps: int, warmup: int):
+    """Times the CPU restatement of the reference step (oracle/) on the host cores."""
+    from oracle import jumbo_mae_oracle as O
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    ocfg = {"vit_b16": O.vit_b16, "vit_l16": O.vit_l16, "vit_h14": O.vit_h14}[config]()
+    state = O.create_state(ocfg, seed=0)
+    images, noise = O.synthetic_batch(ocfg, batch, seed=0, noise_seed=1000)
+    for _ in range(warmup):
+        state, _, _ = O.training_step(state, images, noise)
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        state, met, _ = O.training_step(state, images, noise)
+    dt = time.perf_counter() - t0
+    return batch * steps / dt, dt / steps, cores, met["loss"]
+
+
+def run_reference(args):
+    """--impl reference: the reference's own algorithm on the box's host cores.  The JAX
+    reference cannot be installed here (no jax/flax/optax wheels, no network), so this arm
+    times the CPU port in oracle/ (kind = "port") on a bounded sample: batch 8 per step."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    batch = 8 if args.steps + args.warmup <= 10 else 4
+    ips, sec, cores, loss = cpu_oracle_rate(args.config, batch, args.steps, args.warmup)
+    sample = f"{args.config} MAE step, batch {batch} per step, {args.warmup} warm-up + {args.steps} timed, f32 torch-CPU"
+    line = {
+        "impl": "reference", "metric": "mae_pretrain_images_per_sec", "value": ips, "unit": "images/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": sec * 1e3,
+        "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": workload_config(args, 0, 0, 1),
+        "cpu_baseline": {"value": ips, "unit": "images/s", "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": ips, "unit": "images/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0, "loss": loss,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def workload_config(args, micro, accum, world):
+    return {
+        "workload": f"MAE {args.config} 224px mask 0.75 decoder 8x512 Jumbo CLS J=3, global batch {args.global_batch} "
+                    f"synthetic uint8 (BASELINE.json configs[1])",
+        "global_batch": args.global_batch, "micro_batch": micro, "grad_accum": accum, "parallelism": f"dp{world}",
+        "norm_pix_loss": False,
+        "l2": "inputs larger than L2: every micro-batch streams >20 GB of activations through a 126 MB L2",
+    }
+
+
+# ---------------------------------------------------------------------------------------------
+def run_ours(args):
+    from jumbo_mae_tpu_b200 import _lib, ops
+    from jumbo_mae_tpu_b200 import parallel
+    from jumbo_mae_tpu_b200.engine import lr_schedule
+    from jumbo_mae_tpu_b200.pretraining import create_train_state, training_step
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    parallel.init_from_env("nccl")
+    import torch.distributed as dist
+    _lib.require_device()
+    lib = _lib.load()
+    peaks = measured_peaks()
+
+    micro = min(args.micro_batch, args.global_batch // world)
+    accum = args.global_batch // (micro * world)
+    assert micro * accum * world == args.global_batch, "global batch must divide into micro-batches"
+    ns = preset_args(args.config, args.global_batch)
+    ns.grad_accum = accum
+    state = create_train_state(ns).replicate()
+    cfg = state.cfg
+    eng = state.engine(micro)
+    reducer = parallel.GradReducer(state.store) if world > 1 else None
+    state.reducer = reducer
+    dev = torch.device("cuda", local)
+
+    gen = torch.Generator().manual_seed(rank)
+    host_images = [torch.randint(0, 256, (micro, 3, cfg.image_size, cfg.image_size), generator=gen,
+                                 dtype=torch.uint8).pin_memory() for _ in range(accum)]
+    dev_images = [h.to(dev) for h in host_images]
+    ngen = np.random.Generator(np.random.Philox(key=1000 + rank))
+    total_micro = (args.steps + args.warmup) * accum
+    dev_noise = torch.from_numpy(ngen.random((total_micro, cfg.num_patches), dtype=np.float32)).to(dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    counter = {"micro": 0, "step": 0}
+
+    def resident_step():
+        for i in range(accum):
+            eng.forward(dev_images[i], dev_noise[counter["micro"] % total_micro])
+            eng.backward(zero_grads=(i == 0))
+            counter["micro"] += 1
+        if reducer is not None:
+            reducer.all_reduce_grads()
+        eng.adamw_step(counter["step"], lr_schedule(counter["step"], cfg), grad_scale=1.0 / (accum * world))
+        counter["step"] += 1
+
+    def timed(fn, steps):
+        barrier()
+        sampler = ClockSampler(local)
+        sampler.start()
+        l0 = lib.jm_launch_count()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        launches = lib.jm_launch_count() - l0
+        ms = e0.elapsed_time(e1)
+        sampler.stop()
+        barrier()
+        t = torch.tensor([ms], device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return t.item(), launches, sampler.summary()
+
+    for _ in range(args.warmup):
+        resident_step()
+    ms, launches, clocks = timed(resident_step, args.steps)
+    ms_per_step = ms / args.steps
+    value = args.global_batch / (ms_per_step / 1e3)
+    final_loss = eng.loss.item()
+
+    # ---- e2e through the public API: pinned host images in, loss out, every micro-step
+    state.step, state.micro_step = counter["step"], 0
+    e2e_losses = []
+
+    def e2e_step():
+        for i in range(accum):
+            _, metrics = training_step(state, (host_images[i],))
+            e2e_losses.append(metrics["loss"].item())          # device -> host read of the step's result
+
+    e2e_step()                                                  # warm-up of the API path (allocations)
+    ms_e2e, _, _ = timed(e2e_step, args.steps)
+    e2e_value = args.global_batch / (ms_e2e / args.steps / 1e3)
+    h2d = accum * (micro * 3 * cfg.image_size * cfg.image_size + cfg.num_patches * 4)
+    d2h = accum * 4
+
+    # ---- roofline of the dominant kernel: the tcgen05 GEMM, at the decoder-FFN shape that holds the
+    # largest share of the step's FLOPs, timed live with CUDA events.
+    from jumbo_mae_tpu_b200.config import flops_per_image
+    M, N, K = micro * (cfg.num_patches + cfg.num_cls_tokens), 4 * cfg.dec_dim, cfg.dec_dim
+    A = torch.randn(M, K, device=dev).to(torch.bfloat16)
+    W = torch.randn(K, N, device=dev).to(torch.bfloat16)
+    bias = torch.zeros(N, device=dev)
+    h = torch.empty(M, N, dtype=torch.bfloat16, device=dev)
+    g = torch.empty(M, N, dtype=torch.bfloat16, device=dev)
+
+    def one_gemm():
+        ops.gemm(A, W, M, N, K, b_mn=True, out_bf16=h, out2_bf16=g, bias=bias, act=1)
+    for _ in range(5):
+        one_gemm()
+    reps = 30
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    e0.record()
+    for _ in range(reps):
+        one_gemm()
+    e1.record()
+    torch.cuda.synchronize()
+    gemm_ms = e0.elapsed_time(e1) / reps
+    gemm_tflops = 2.0 * M * N * K / (gemm_ms * 1e-3) / 1e12
+    fwd_flops, step_flops = flops_per_image(cfg)
+    step_tflops_per_gpu = step_flops * args.global_batch / world / (ms_per_step * 1e-3) / 1e12
+
+    line = {
+        "metric": "mae_pretrain_images_per_sec", "value": value, "unit": "images/s", "n_gpus": world,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
+        "scaling": "strong", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+        "config": workload_config(args, micro, accum, world),
+        "roofline": {
+            "bound": "tensor", "kernel": f"gemm_kernel<256> decoder FFN w1+GELU M={M} N={N} K={K}",
+            "achieved": gemm_tflops, "peak": peaks["bf16_burst"], "unit": "TFLOP/s",
+            "frac": gemm_tflops / peaks["bf16_burst"], "traffic": None,
+            "peak_source": f"{peaks['source']} (burst: kernel timed alone)", "kernel_ms": gemm_ms,
+        },
+        "step_roofline": {
+            "bound": "tensor", "achieved": step_tflops_per_gpu, "peak": peaks["bf16_sustained"], "unit": "TFLOP/s",
+            "frac": step_tflops_per_gpu / peaks["bf16_sustained"],
+            "flops_per_image": step_flops, "peak_source": f"{peaks['source']} (sustained: long step)",
+        },
+        "e2e": {"value": e2e_value, "unit": "images/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                "ms_per_step": ms_e2e / args.steps},
+        "gpu_launches": int(launches),
+        "clocks": clocks,
+        "loss": final_loss,
+    }
+    if world == 1 and not args.no_cpu_baseline:
+        ips, sec, cores, _ = cpu_oracle_rate(args.config, 8, 3, 1)
+        line["cpu_baseline"] = {"value": ips, "unit": "images/s", "cores": cores, "kind": "port",
+                                "sample": f"{args.config} MAE step, batch 8, 1 warm-up + 3 timed steps of the f32 "
+                                          f"torch-CPU port in oracle/ ({sec:.2f} s/step)"}
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--config", default="vit_b16", choices=["vit_b16", "vit_l16", "vit_h14"])
+    ap.add_argument("--global-batch", type=int, default=4096)
+    ap.add_argument("--micro-batch", type=int, default=512)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -95,3 +95,14 @@ def vit_l16(**kw) -> MAEConfig:
 
 def vit_h14(**kw) -> MAEConfig:
     return MAEConfig(layers=32, dim=1280, heads=16, patch_size=14, **kw)
+
+
+def flops_per_image(cfg: MAEConfig):
+    """Algorithmic (forward, full step) FLOPs per image: SURVEY.md section 8d / BASELINE.md section 3.
+    Counts the patch embedding on the kept patches and the pixel head on the masked rows only."""
+    n, m, N = cfg.keep, cfg.num_masked, cfg.num_patches
+    J, d, L, P = cfg.num_cls_tokens, cfg.dim, cfg.layers, cfg.patch_dim
+    Te, Td, dd, dl = n + J, N + J, cfg.dec_dim, cfg.dec_layers
+    fwd = 2.0 * (n * P * d + L * (4 * Te * d * d + 2 * Te * Te * d + 8 * n * d * d + 8 * J * J * d * d)
+                 + Te * d * dd + dl * (12 * Td * dd * dd + 2 * Td * Td * dd) + m * dd * P)
+    return fwd, 3.0 * fwd - 2.0 * n * P * d

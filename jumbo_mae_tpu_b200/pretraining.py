@@ -183,11 +183,10 @@ def training_step(state: TrainState, batch, noise=None) -> Tuple[TrainState, Dic
     if world > 1:
         state.reducer.mean_scalar(metrics_loss)                      # lax.pmean(metrics) (:144)
     state.micro_step += 1
-    lr = lr_schedule(state.step, state.cfg) if state.step > 0 or state.micro_step == accum else lr_schedule(0, state.cfg)
+    lr = lr_schedule(state.step, state.cfg)                          # hyperparams["learning_rate"] (:159)
     if state.micro_step == accum:                                    # :149-158
         if world > 1:
             state.reducer.all_reduce_grads()                         # lax.pmean(grads) (:150); 1/world below
-        lr = lr_schedule(state.step, state.cfg)
         eng.adamw_step(state.step, lr, grad_scale=1.0 / (accum * world))
         state.step += 1
         state.micro_step = 0
