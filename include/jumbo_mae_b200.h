@@ -71,6 +71,27 @@ int jm_patch_loss(const float* pred, long ldp, const uint8_t* images, const floa
                   int image_size, int patch_size, int num_cls, int norm_pix, float grad_scale, float* loss,
                   jm_bf16* dpred, long lddp, void* workspace, size_t workspace_bytes, void* stream);
 
+/* jm_patch_loss without a workspace argument and without any allocation.  It has no counterpart
+ * in the reference; it exists for hosts that are not allowed to allocate device memory around the
+ * call: an XLA-FFI handler (XLA owns every device buffer and a handler must not call cudaMalloc),
+ * a service that runs under a fixed memory budget carved out at start-up, or an embedding whose
+ * memory pool belongs to somebody else.
+ *
+ * The per-patch partial sums go to a fixed array inside the library instead
+ * (JM_PATCH_LOSS_STATIC_MAX floats = 4 MiB, reserved on every GPU that loads the library until
+ * the process exits).  Results are identical to jm_patch_loss.
+ *   - batch * num_patches must not exceed JM_PATCH_LOSS_STATIC_MAX; larger problems are refused
+ *     with an error (use jm_patch_loss and your own workspace);
+ *   - the first call on each device looks the array's address up (one cudaGetSymbolAddress, no
+ *     allocation); make that first call outside any stream capture;
+ *   - all calls on a device share the one array: two calls whose kernels can overlap on the GPU
+ *     (different streams, no dependency) race on it.  Issue them on one stream or order them
+ *     with events.  Nothing needs clearing between calls: each call rewrites every entry it reads. */
+#define JM_PATCH_LOSS_STATIC_MAX (1 << 20)
+int jm_patch_loss_static(const float* pred, long ldp, const uint8_t* images, const float* mask_row, int batch,
+                         int image_size, int patch_size, int num_cls, int norm_pix, float grad_scale, float* loss,
+                         jm_bf16* dpred, long lddp, void* stream);
+
 /* ---------------------------------------------------------------- LayerNorm
  * flax.linen.LayerNorm as used at src/modeling.py:155-156,177-179,238,282:
  * y = (x - mean) * rsqrt(E[x^2]-mean^2 + eps) * gamma + beta, f32 statistics.

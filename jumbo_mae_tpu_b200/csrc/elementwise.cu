@@ -602,6 +602,59 @@ extern "C" int jm_patch_loss(const float* pred, long ldp, const uint8_t* images,
   return 0;
 }
 
+// ---------------------------------------------------------------- allocation-free loss entry point
+// Scratch for jm_patch_loss_static: one per-patch partial sum per (image, patch).  The array is
+// part of the library image, so every GPU that loads libjumbo_mae_b200.so reserves
+// JM_PATCH_LOSS_STATIC_MAX * 4 bytes (4 MiB) until the process exits.
+namespace jm {
+static __device__ __align__(256) float g_patch_loss_static_scratch[JM_PATCH_LOSS_STATIC_MAX];
+
+// In host code the array's name is only a handle for the runtime, not a device address; the
+// address is looked up once per device (with that device current) and cached here.
+static int patch_loss_static_scratch(float** out) {
+  static float* cached[64];
+  static std::mutex mu;
+  int dev = 0;
+  JM_CUDA(cudaGetDevice(&dev));
+  JM_CHECK(dev >= 0 && dev < 64, "jm_patch_loss_static: device ordinal %d out of range", dev);
+  std::lock_guard<std::mutex> lock(mu);
+  if (cached[dev] == nullptr) {
+    float* p = nullptr;
+    JM_CUDA(cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_patch_loss_static_scratch));
+    JM_CHECK(p != nullptr, "jm_patch_loss_static: cudaGetSymbolAddress returned a null address");
+    cached[dev] = p;
+  }
+  *out = cached[dev];
+  return 0;
+}
+}  // namespace jm
+
+extern "C" int jm_patch_loss_static(const float* pred, long ldp, const uint8_t* images, const float* mask_row,
+                                    int batch, int image_size, int patch_size, int num_cls, int norm_pix,
+                                    float grad_scale, float* loss, jm_bf16* dpred, long lddp, void* stream) {
+  JM_CHECK(patch_size > 0 && image_size > 0 && image_size % patch_size == 0,
+           "jm_patch_loss_static: image size must be a positive multiple of the patch size");
+  const int g = image_size / patch_size, N = g * g, P = patch_size * patch_size * 3;
+  JM_CHECK(P <= kLossThreads * kLossMaxPer, "jm_patch_loss_static: patch dimension %d too large", P);
+  JM_CHECK(batch > 0, "jm_patch_loss_static: empty batch");
+  const long need = static_cast<long>(batch) * N;
+  JM_CHECK(need <= JM_PATCH_LOSS_STATIC_MAX,
+           "jm_patch_loss_static: batch * patches = %ld exceeds the built-in scratch of %d entries; "
+           "use jm_patch_loss with a caller-owned workspace",
+           need, JM_PATCH_LOSS_STATIC_MAX);
+  float* partial = nullptr;
+  if (patch_loss_static_scratch(&partial)) return 1;
+  // Every entry [0, batch * N) is overwritten by the first kernel (zero for visible patches), so the
+  // previous call's contents never leak into this one and nothing has to be cleared first.
+  patch_loss_kernel<<<dim3(num_cls + N, batch), kLossThreads, 0, STREAM>>>(
+      pred, ldp, images, mask_row, image_size, patch_size, num_cls, norm_pix, grad_scale, partial,
+      reinterpret_cast<__nv_bfloat16*>(dpred), lddp, batch);
+  JM_AFTER_LAUNCH();
+  patch_loss_finalize_kernel<<<1, 1024, 0, STREAM>>>(partial, mask_row, N, batch, loss);
+  JM_AFTER_LAUNCH();
+  return 0;
+}
+
 extern "C" int jm_layernorm_fwd(const float* x, long ldx, int rows, int dim, const float* gamma, const float* beta,
                                 float eps, jm_bf16* y_bf16, long ldy, float* y_f32, long ldyf, float* mean,
                                 float* rstd, void* stream) {
