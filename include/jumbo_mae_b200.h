@@ -155,10 +155,11 @@ int jm_gemm(const jm_gemm_args* args, void* stream);
 int jm_attention_fwd(const jm_bf16* qkv, long ldqkv, int batch, int T, int heads, int head_dim, jm_bf16* out,
                      long ldo, float* lse, void* stream);
 /* dqkv (same layout as qkv) from dout; the q part is multiplied by q_scale so that it
- * is the gradient w.r.t. the un-scaled projection. */
+ * is the gradient w.r.t. the un-scaled projection.  delta_ws: caller-owned scratch of
+ * batch*heads*T floats (receives rowsum(dout * out)). */
 int jm_attention_bwd(const jm_bf16* qkv, long ldqkv, const jm_bf16* out, long ldo, const jm_bf16* dout, long lddo,
-                     const float* lse, int batch, int T, int heads, int head_dim, float q_scale, jm_bf16* dqkv,
-                     long lddqkv, void* stream);
+                     const float* lse, float* delta_ws, int batch, int T, int heads, int head_dim, float q_scale,
+                     jm_bf16* dqkv, long lddqkv, void* stream);
 
 /* ---------------------------------------------------------------- token assembly
  * CLS prepend (src/modeling.py:249-250,257): x[b, j, :] = cls[j, :] for j < J. */

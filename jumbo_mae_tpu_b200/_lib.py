@@ -80,7 +80,7 @@ def load() -> ctypes.CDLL:
                              c_int, P, P, P, c_size_t, P],
         "jm_gemm": [POINTER(GemmArgs), P],
         "jm_attention_fwd": [P, c_long, c_int, c_int, c_int, c_int, P, c_long, P, P],
-        "jm_attention_bwd": [P, c_long, P, c_long, P, c_long, P, c_int, c_int, c_int, c_int, c_float, P, c_long, P],
+        "jm_attention_bwd": [P, c_long, P, c_long, P, c_long, P, P, c_int, c_int, c_int, c_int, c_float, P, c_long, P],
         "jm_fill_cls": [P, c_int, c_int, c_int, c_int, P, P],
         "jm_unshuffle_fwd": [P, P, P, P, c_int, c_int, c_int, c_int, c_int, P, P],
         "jm_unshuffle_bwd": [P, P, c_int, c_int, c_int, c_int, c_int, P, P, P],

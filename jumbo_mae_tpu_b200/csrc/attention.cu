@@ -52,17 +52,25 @@ __device__ __forceinline__ int bt_off(int lane, int k0, int n0) {
   return (k0 + (lane & 7) + ((lane >> 3) & 1) * 8) * LDS + n0 + (lane >> 4) * 8;
 }
 
-// Cooperative load of rows [0, rows_pad) x HD bf16 of one head into a padded smem tile; rows >= T are zero.
+// Cooperative asynchronous load (cp.async, 16 bytes per request, zero-fill for rows >= T) of rows
+// [0, rows_pad) x HD bf16 of one head into a padded smem tile.  All requests of a CTA are in flight
+// together; cp_async_wait_all() + __syncthreads() publishes them.
 template <int HD, int LDS>
 __device__ __forceinline__ void load_head(const __nv_bfloat16* __restrict__ src, long ld, int T, int rows_pad,
                                           __nv_bfloat16* dst) {
   constexpr int CH = HD / 8;
   for (int idx = threadIdx.x; idx < rows_pad * CH; idx += blockDim.x) {
     const int row = idx / CH, ch = idx - row * CH;
-    uint4 v = make_uint4(0u, 0u, 0u, 0u);
-    if (row < T) v = *reinterpret_cast<const uint4*>(src + row * ld + ch * 8);
-    *reinterpret_cast<uint4*>(dst + row * LDS + ch * 8) = v;
+    const bool ok = row < T;
+    const __nv_bfloat16* g = src + (ok ? row : 0) * ld + ch * 8;
+    const uint32_t sa = smem_u32(dst + row * LDS + ch * 8);
+    const int bytes = ok ? 16 : 0;
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(sa), "l"(g), "r"(bytes) : "memory");
   }
+}
+__device__ __forceinline__ void cp_async_wait_all() {
+  asm volatile("cp.async.commit_group;" ::: "memory");
+  asm volatile("cp.async.wait_group 0;" ::: "memory");
 }
 
 template <int HD>
@@ -82,6 +90,7 @@ __global__ void attn_fwd_kernel(const __nv_bfloat16* __restrict__ qkv, long ldqk
   load_head<HD, LDS>(base, ldqkv, T, Tq, sQ);
   load_head<HD, LDS>(base + d, ldqkv, T, Tp, sK);
   load_head<HD, LDS>(base + 2 * d, ldqkv, T, Tp, sV);
+  cp_async_wait_all();
   __syncthreads();
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -178,11 +187,38 @@ __global__ void attn_fwd_kernel(const __nv_bfloat16* __restrict__ qkv, long ldqk
   }  // strip
 }
 
+// delta[b, h, t] = sum_c dO[b*T+t, h*hd+c] * O[b*T+t, h*hd+c]  (one thread per (token, head))
+__global__ void attn_delta_kernel(const __nv_bfloat16* __restrict__ out, long ldo,
+                                  const __nv_bfloat16* __restrict__ dout, long lddo, int batch, int T, int heads,
+                                  int hd, float* __restrict__ delta) {
+  const long idx = static_cast<long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  const long total = static_cast<long>(batch) * T * heads;
+  if (idx >= total) return;
+  const int h = static_cast<int>(idx % heads);
+  const long tok = idx / heads;
+  const __nv_bfloat16* o = out + tok * ldo + h * hd;
+  const __nv_bfloat16* g = dout + tok * lddo + h * hd;
+  float acc = 0.f;
+  for (int c = 0; c < hd; c += 8) {
+    const uint4 ov = *reinterpret_cast<const uint4*>(o + c);
+    const uint4 dv = *reinterpret_cast<const uint4*>(g + c);
+    const uint32_t oo[4] = {ov.x, ov.y, ov.z, ov.w}, dd[4] = {dv.x, dv.y, dv.z, dv.w};
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const float2 a = unpack_bf16(oo[j]), b = unpack_bf16(dd[j]);
+      acc += a.x * b.x + a.y * b.y;
+    }
+  }
+  const long b = tok / T;
+  const int t = static_cast<int>(tok - b * T);
+  delta[(b * heads + h) * T + t] = acc;
+}
+
 template <int HD>
 __global__ void attn_bwd_kernel(const __nv_bfloat16* __restrict__ qkv, long ldqkv,
-                                const __nv_bfloat16* __restrict__ out, long ldo,
                                 const __nv_bfloat16* __restrict__ dout, long lddo, const float* __restrict__ lse,
-                                int T, int heads, float q_scale, __nv_bfloat16* __restrict__ dqkv, long lddqkv) {
+                                const float* __restrict__ delta, int T, int heads, float q_scale,
+                                __nv_bfloat16* __restrict__ dqkv, long lddqkv) {
   constexpr int LDS = HD + 8;
   extern __shared__ __align__(16) uint8_t smem_raw[];
   const int Tp = (T + 63) / 64 * 64;
@@ -199,28 +235,13 @@ __global__ void attn_bwd_kernel(const __nv_bfloat16* __restrict__ qkv, long ldqk
   load_head<HD, LDS>(base + d, ldqkv, T, Tp, sK);
   load_head<HD, LDS>(base + 2 * d, ldqkv, T, Tp, sV);
   load_head<HD, LDS>(dout + static_cast<long>(b) * T * lddo + h * HD, lddo, T, Tp, sdO);
-  __syncthreads();
-  // D[row] = sum_c dO[row, c] * O[row, c]; padded rows get lse = +big so that their P is exactly 0
+  // saved log-sum-exp and D = rowsum(dO * O); padded rows get lse = +big so that their P is exactly 0
   for (int row = threadIdx.x; row < Tp; row += blockDim.x) {
-    float acc = 0.f, L = 1e30f;
-    if (row < T) {
-      const __nv_bfloat16* orow = out + (static_cast<long>(b) * T + row) * ldo + h * HD;
-#pragma unroll
-      for (int c = 0; c < HD; c += 8) {
-        const uint4 ov = *reinterpret_cast<const uint4*>(orow + c);
-        const uint4 dv = *reinterpret_cast<const uint4*>(sdO + row * LDS + c);
-        const uint32_t oo[4] = {ov.x, ov.y, ov.z, ov.w}, dd[4] = {dv.x, dv.y, dv.z, dv.w};
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          const float2 a = unpack_bf16(oo[j]), c2 = unpack_bf16(dd[j]);
-          acc += a.x * c2.x + a.y * c2.y;
-        }
-      }
-      L = lse[(static_cast<long>(b) * heads + h) * T + row];
-    }
-    sD[row] = acc;
-    sL[row] = L;
+    const long i = (static_cast<long>(b) * heads + h) * T + row;
+    sL[row] = row < T ? lse[i] : 1e30f;
+    sD[row] = row < T ? delta[i] : 0.f;
   }
+  cp_async_wait_all();
   __syncthreads();
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -394,7 +415,7 @@ static int pick_warps(const void* kern, int T, int* warps) {
   JM_CUDA(cudaFuncGetAttributes(&fa, kern));
   const int per_warp = (fa.numRegs + 7) / 8 * 8 * 32;
   int max_warps = (16384 / per_warp) * 4;
-  if (max_warps > 32) max_warps = 32;
+  if (max_warps > 8) max_warps = 8;  // small CTAs: several (image, head) pairs per SM overlap load and math
   JM_CHECK(max_warps >= 1, "attention kernel needs %d registers per thread", fa.numRegs);
   const int strips = (T + 15) / 16;
   const int rounds = (strips + max_warps - 1) / max_warps;
@@ -419,18 +440,22 @@ static int launch_fwd(const jm_bf16* qkv, long ldqkv, int batch, int T, int head
 
 template <int HD>
 static int launch_bwd(const jm_bf16* qkv, long ldqkv, const jm_bf16* out, long ldo, const jm_bf16* dout, long lddo,
-                      const float* lse, int batch, int T, int heads, float q_scale, jm_bf16* dqkv, long lddqkv,
-                      cudaStream_t stream) {
+                      const float* lse, float* delta, int batch, int T, int heads, float q_scale, jm_bf16* dqkv,
+                      long lddqkv, cudaStream_t stream) {
   const size_t smem = bwd_smem(T, HD);
   auto kern = attn_bwd_kernel<HD>;
   if (smem > 48 * 1024) JM_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int warps = 0;
   if (pick_warps(reinterpret_cast<const void*>(kern), T, &warps)) return 1;
   const int threads = warps * 32;
+  const long total = static_cast<long>(batch) * T * heads;
+  attn_delta_kernel<<<static_cast<int>((total + 255) / 256), 256, 0, stream>>>(
+      reinterpret_cast<const __nv_bfloat16*>(out), ldo, reinterpret_cast<const __nv_bfloat16*>(dout), lddo, batch, T,
+      heads, HD, delta);
+  JM_AFTER_LAUNCH();
   kern<<<batch * heads, threads, smem, stream>>>(
-      reinterpret_cast<const __nv_bfloat16*>(qkv), ldqkv, reinterpret_cast<const __nv_bfloat16*>(out), ldo,
-      reinterpret_cast<const __nv_bfloat16*>(dout), lddo, lse, T, heads, q_scale,
-      reinterpret_cast<__nv_bfloat16*>(dqkv), lddqkv);
+      reinterpret_cast<const __nv_bfloat16*>(qkv), ldqkv, reinterpret_cast<const __nv_bfloat16*>(dout), lddo, lse,
+      delta, T, heads, q_scale, reinterpret_cast<__nv_bfloat16*>(dqkv), lddqkv);
   JM_AFTER_LAUNCH();
   return 0;
 }
@@ -458,17 +483,18 @@ extern "C" int jm_attention_fwd(const jm_bf16* qkv, long ldqkv, int batch, int T
 }
 
 extern "C" int jm_attention_bwd(const jm_bf16* qkv, long ldqkv, const jm_bf16* out, long ldo, const jm_bf16* dout,
-                                long lddo, const float* lse, int batch, int T, int heads, int head_dim,
-                                float q_scale, jm_bf16* dqkv, long lddqkv, void* stream_) {
+                                long lddo, const float* lse, float* delta_ws, int batch, int T, int heads,
+                                int head_dim, float q_scale, jm_bf16* dqkv, long lddqkv, void* stream_) {
   using namespace jm;
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   if (check_attn("jm_attention_bwd", batch, T, heads, head_dim, ldqkv, lddqkv)) return 1;
   JM_CHECK(ldo % 8 == 0 && lddo % 8 == 0, "jm_attention_bwd: row strides must be multiples of 8 elements");
+  JM_CHECK(delta_ws != nullptr, "jm_attention_bwd: delta workspace (batch*heads*T floats) is required");
   JM_CHECK(bwd_smem(T, head_dim) <= 227 * 1024, "jm_attention_bwd: T=%d hd=%d does not fit shared memory", T,
            head_dim);
   if (head_dim == 32)
-    return launch_bwd<32>(qkv, ldqkv, out, ldo, dout, lddo, lse, batch, T, heads, q_scale, dqkv, lddqkv, stream);
+    return launch_bwd<32>(qkv, ldqkv, out, ldo, dout, lddo, lse, delta_ws, batch, T, heads, q_scale, dqkv, lddqkv, stream);
   if (head_dim == 64)
-    return launch_bwd<64>(qkv, ldqkv, out, ldo, dout, lddo, lse, batch, T, heads, q_scale, dqkv, lddqkv, stream);
-  return launch_bwd<80>(qkv, ldqkv, out, ldo, dout, lddo, lse, batch, T, heads, q_scale, dqkv, lddqkv, stream);
+    return launch_bwd<64>(qkv, ldqkv, out, ldo, dout, lddo, lse, delta_ws, batch, T, heads, q_scale, dqkv, lddqkv, stream);
+  return launch_bwd<80>(qkv, ldqkv, out, ldo, dout, lddo, lse, delta_ws, batch, T, heads, q_scale, dqkv, lddqkv, stream);
 }

@@ -24,8 +24,11 @@ namespace jm {
 constexpr int BM = 128;
 constexpr int BK = 64;  // 64 bf16 = 128 bytes = one SWIZZLE_128B row
 constexpr int UMMA_K = 16;
-constexpr int kGemmThreads = 256;
 constexpr int kEpiWarp0 = 4;
+constexpr int kEpiWarps = 8;  // two per TMEM lane quarter, each takes half of the tile's columns
+constexpr int kGemmThreads = (kEpiWarp0 + kEpiWarps) * 32;
+constexpr int kStageRowBytes = 128;                    // 32 f32 columns
+constexpr int kStageBytesPerWarp = 32 * kStageRowBytes;  // 32 rows
 
 struct GemmShape {
   int M, N, K;
@@ -62,7 +65,8 @@ struct GemmCfg {
   static constexpr int STAGES = (BN == 256) ? 4 : ((BN == 128) ? 6 : 8);
   static constexpr int TMEM_COLS = 2 * BN;
   static constexpr int BAR_BYTES = (2 * STAGES + 4) * 8 + 16;
-  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + BAR_BYTES + 1024;  // +1024: manual alignment
+  static constexpr int EPI_BYTES = kEpiWarps * kStageBytesPerWarp;  // epilogue transpose staging
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + EPI_BYTES + BAR_BYTES + 1024;  // +1024: alignment
 };
 
 __device__ __forceinline__ void store_f32x4(float* p, float4 v, bool atomic) {
@@ -73,111 +77,307 @@ __device__ __forceinline__ void store_f32x4(float* p, float4 v, bool atomic) {
   }
 }
 
-// Epilogue for 8 consecutive columns [col, col+8) of one row; nvalid in {0, 4, 8} columns are in range.
-__device__ __forceinline__ void epilogue8(const EpiParams& ep, float (&v)[8], long row, int col, int nvalid, int rp,
-                                          bool masked) {
-  if (ep.bias) {
+__device__ __forceinline__ float tanh_fast(float x) {
+  float y;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+// GELU-tanh (src/modeling.py:148) and its derivative with the hardware tanh (abs. error ~5e-4,
+// below the bf16 resolution of the values they are stored in).
+__device__ __forceinline__ float gelu_fast(float x) {
+  const float u = 0.7978845608028654f * (x + 0.044715f * x * x * x);
+  return 0.5f * x * (1.0f + tanh_fast(u));
+}
+__device__ __forceinline__ float gelu_grad_fast(float x) {
+  const float x2 = x * x;
+  const float t = tanh_fast(0.7978845608028654f * (x + 0.044715f * x * x2));
+  return 0.5f * (1.0f + t) + 0.5f * x * (1.0f - t * t) * 0.7978845608028654f * (1.0f + 0.134145f * x2);
+}
+
+// Epilogue specialisations: straight-line code per kind (the generic one keeps every runtime switch).
+enum : int {
+  EPI_BF16 = 0,      // out_bf16 = (acc + bias) * scale
+  EPI_F32 = 1,       // out_f32 (=|+=) acc + bias [+ pe] [+ residual]          (residual prefetched)
+  EPI_GELU_FWD = 2,  // out_bf16 = h = acc + bias, out2_bf16 = gelu(h)
+  EPI_GELU_BWD = 3,  // out_bf16 = acc * gelu'(aux)                             (aux prefetched)
+  EPI_GENERIC = 4,
+};
+
+template <int EPI>
+struct EpiPrefetch {  // global operand of one lane for its 4 rows x 8 columns of a 32x32 chunk
+};
+template <>
+struct EpiPrefetch<EPI_F32> {
+  float4 v[4][2];
+};
+template <>
+struct EpiPrefetch<EPI_GELU_BWD> {
+  uint4 v[4];
+};
+
+__device__ __forceinline__ void store_bf16x8(__nv_bfloat16* p, const float (&v)[8], int ncols) {
+  if (ncols >= 8) {
+    *reinterpret_cast<uint4*>(p) =
+        make_uint4(pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]), pack_bf16(v[4], v[5]), pack_bf16(v[6], v[7]));
+  } else {
+    *reinterpret_cast<uint2*>(p) = make_uint2(pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]));
+  }
+}
+
+// Fused epilogue for 8 consecutive columns [col, col+8) of one row (ncols = 8, or 4 at a ragged edge), in the
+// coalesced layout: 4 lanes cover the 32 columns of a chunk row.  sc/bs hold the per-column scale and the
+// pre-scaled bias (v = acc * sc + bs), hoisted per chunk; `affine` says whether they are non-trivial.
+template <int EPI>
+__device__ __forceinline__ void epilogue8(const EpiParams& ep, float (&v)[8], const float (&sc)[8],
+                                          const float (&bs)[8], bool affine, long off_row, int row, int col,
+                                          int ncols, bool zero, const EpiPrefetch<EPI>& pf, int it) {
+  if (affine) {
 #pragma unroll
-    for (int h = 0; h < 2; ++h)
-      if (4 * h < nvalid) {
-        float4 b = *reinterpret_cast<const float4*>(ep.bias + col + 4 * h);
-        v[4 * h + 0] += b.x, v[4 * h + 1] += b.y, v[4 * h + 2] += b.z, v[4 * h + 3] += b.w;
+    for (int j = 0; j < 8; ++j) v[j] = fmaf(v[j], sc[j], bs[j]);
+  }
+  if constexpr (EPI == EPI_BF16) {
+    if (zero) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) v[j] = 0.f;
+    }
+    store_bf16x8(ep.out_bf16 + off_row * ep.ldo_bf16 + col, v, ncols);
+  } else if constexpr (EPI == EPI_F32) {
+    if (ep.pe && !zero) {
+      const float* pe = ep.pe + static_cast<long>(ep.pe_idx[row % ep.row_period - ep.row_skip]) * ep.ldpe + col;
+      const float4 a = *reinterpret_cast<const float4*>(pe);
+      v[0] += a.x, v[1] += a.y, v[2] += a.z, v[3] += a.w;
+      if (ncols >= 8) {
+        const float4 b = *reinterpret_cast<const float4*>(pe + 4);
+        v[4] += b.x, v[5] += b.y, v[6] += b.z, v[7] += b.w;
       }
-  }
-  if (col < ep.col_scale_n) {
+    }
+    const float4 r0 = pf.v[it][0], r1 = pf.v[it][1];
+    v[0] += r0.x, v[1] += r0.y, v[2] += r0.z, v[3] += r0.w;
+    v[4] += r1.x, v[5] += r1.y, v[6] += r1.z, v[7] += r1.w;
+    if (zero) {
 #pragma unroll
-    for (int j = 0; j < 8; ++j)
-      if (col + j < ep.col_scale_n) v[j] *= ep.col_scale;
-  }
-  if (ep.act == 1) {
-    // pre-activation -> out_bf16, gelu -> out2_bf16 (handled below through v / pre)
-    float pre[8];
+      for (int j = 0; j < 8; ++j) v[j] = 0.f;
+    }
+    float* o = ep.out_f32 + off_row * ep.ldo_f32 + col;
+    store_f32x4(o, make_float4(v[0], v[1], v[2], v[3]), ep.accumulate != 0);
+    if (ncols >= 8) store_f32x4(o + 4, make_float4(v[4], v[5], v[6], v[7]), ep.accumulate != 0);
+  } else if constexpr (EPI == EPI_GELU_FWD) {
+    float g[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
-      pre[j] = masked ? 0.f : v[j];
-      v[j] = masked ? 0.f : gelu_tanh_f(v[j]);
+      if (zero) v[j] = 0.f;
+      g[j] = gelu_fast(v[j]);
     }
-    if (ep.out_bf16) {
-      __nv_bfloat16* p = ep.out_bf16 + row * ep.ldo_bf16 + col;
-      if (nvalid == 8) {
-        uint4 u = {pack_bf16(pre[0], pre[1]), pack_bf16(pre[2], pre[3]), pack_bf16(pre[4], pre[5]),
-                   pack_bf16(pre[6], pre[7])};
-        *reinterpret_cast<uint4*>(p) = u;
-      } else if (nvalid == 4) {
-        uint2 u = {pack_bf16(pre[0], pre[1]), pack_bf16(pre[2], pre[3])};
-        *reinterpret_cast<uint2*>(p) = u;
-      }
+    if (ep.out_bf16) store_bf16x8(ep.out_bf16 + off_row * ep.ldo_bf16 + col, v, ncols);
+    if (ep.out2_bf16) store_bf16x8(ep.out2_bf16 + off_row * ep.ldo2_bf16 + col, g, ncols);
+  } else if constexpr (EPI == EPI_GELU_BWD) {
+    const uint4 u = pf.v[it];
+    const uint32_t w[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const float2 a = unpack_bf16(w[j]);
+      v[2 * j] *= gelu_grad_fast(a.x);
+      v[2 * j + 1] *= gelu_grad_fast(a.y);
     }
-    if (ep.out2_bf16) {
-      __nv_bfloat16* p = ep.out2_bf16 + row * ep.ldo2_bf16 + col;
-      if (nvalid == 8) {
-        uint4 u = {pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]), pack_bf16(v[4], v[5]), pack_bf16(v[6], v[7])};
-        *reinterpret_cast<uint4*>(p) = u;
-      } else if (nvalid == 4) {
-        uint2 u = {pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3])};
-        *reinterpret_cast<uint2*>(p) = u;
-      }
+    if (zero) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) v[j] = 0.f;
     }
-    return;
-  }
-  if (ep.act == 2) {
-    const __nv_bfloat16* a = ep.aux + row * ep.ldaux + col;
-    if (nvalid == 8) {
-      uint4 u = *reinterpret_cast<const uint4*>(a);
-      float2 f0 = unpack_bf16(u.x), f1 = unpack_bf16(u.y), f2 = unpack_bf16(u.z), f3 = unpack_bf16(u.w);
-      v[0] *= gelu_tanh_grad_f(f0.x), v[1] *= gelu_tanh_grad_f(f0.y);
-      v[2] *= gelu_tanh_grad_f(f1.x), v[3] *= gelu_tanh_grad_f(f1.y);
-      v[4] *= gelu_tanh_grad_f(f2.x), v[5] *= gelu_tanh_grad_f(f2.y);
-      v[6] *= gelu_tanh_grad_f(f3.x), v[7] *= gelu_tanh_grad_f(f3.y);
-    } else if (nvalid == 4) {
-      uint2 u = *reinterpret_cast<const uint2*>(a);
-      float2 f0 = unpack_bf16(u.x), f1 = unpack_bf16(u.y);
-      v[0] *= gelu_tanh_grad_f(f0.x), v[1] *= gelu_tanh_grad_f(f0.y);
-      v[2] *= gelu_tanh_grad_f(f1.x), v[3] *= gelu_tanh_grad_f(f1.y);
+    store_bf16x8(ep.out_bf16 + off_row * ep.ldo_bf16 + col, v, ncols);
+  } else {
+    if (ep.act == 1) {
+      float g[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        if (zero) v[j] = 0.f;
+        g[j] = gelu_fast(v[j]);
+      }
+      if (ep.out_bf16) store_bf16x8(ep.out_bf16 + off_row * ep.ldo_bf16 + col, v, ncols);
+      if (ep.out2_bf16) store_bf16x8(ep.out2_bf16 + off_row * ep.ldo2_bf16 + col, g, ncols);
+      return;
     }
-  }
-  if (ep.pe && !masked) {
-    const float* pe = ep.pe + static_cast<long>(ep.pe_idx[rp - ep.row_skip]) * ep.ldpe + col;
 #pragma unroll
-    for (int h = 0; h < 2; ++h)
-      if (4 * h < nvalid) {
-        float4 b = *reinterpret_cast<const float4*>(pe + 4 * h);
-        v[4 * h + 0] += b.x, v[4 * h + 1] += b.y, v[4 * h + 2] += b.z, v[4 * h + 3] += b.w;
+    for (int hh = 0; hh < 2; ++hh) {
+      if (hh * 4 >= ncols) break;
+      const int c4 = col + hh * 4;
+      float* x = v + hh * 4;
+      if (ep.act == 2) {
+        const uint2 u = *reinterpret_cast<const uint2*>(ep.aux + off_row * ep.ldaux + c4);
+        const float2 a = unpack_bf16(u.x), b = unpack_bf16(u.y);
+        x[0] *= gelu_grad_fast(a.x), x[1] *= gelu_grad_fast(a.y);
+        x[2] *= gelu_grad_fast(b.x), x[3] *= gelu_grad_fast(b.y);
       }
-  }
-  if (ep.residual) {
-    const float* r = ep.residual + row * ep.ldr + col;
-#pragma unroll
-    for (int h = 0; h < 2; ++h)
-      if (4 * h < nvalid) {
-        float4 b = *reinterpret_cast<const float4*>(r + 4 * h);
-        v[4 * h + 0] += b.x, v[4 * h + 1] += b.y, v[4 * h + 2] += b.z, v[4 * h + 3] += b.w;
+      if (ep.pe && !zero) {
+        const float4 b = *reinterpret_cast<const float4*>(
+            ep.pe + static_cast<long>(ep.pe_idx[row % ep.row_period - ep.row_skip]) * ep.ldpe + c4);
+        x[0] += b.x, x[1] += b.y, x[2] += b.z, x[3] += b.w;
       }
+      if (ep.residual) {
+        const float4 b = *reinterpret_cast<const float4*>(ep.residual + off_row * ep.ldr + c4);
+        x[0] += b.x, x[1] += b.y, x[2] += b.z, x[3] += b.w;
+      }
+      if (zero) x[0] = x[1] = x[2] = x[3] = 0.f;
+      if (ep.out_f32)
+        store_f32x4(ep.out_f32 + off_row * ep.ldo_f32 + c4, make_float4(x[0], x[1], x[2], x[3]), ep.accumulate != 0);
+    }
+    if (ep.out_bf16) store_bf16x8(ep.out_bf16 + off_row * ep.ldo_bf16 + col, v, ncols);
   }
-  if (masked) {
+}
+
+// Issues the global loads one lane needs for chunk (tile t, chunk c) of its warp: the f32 residual
+// (EPI_F32) or the bf16 pre-activation (EPI_GELU_BWD).  Called one chunk ahead so that the HBM
+// latency hides behind the previous chunk's work / the MMA main loop.
+template <int EPI, int BN>
+__device__ __forceinline__ void epi_prefetch(EpiPrefetch<EPI>& pf, const EpiParams& ep, const GemmShape& sh, int t,
+                                             int c, int q, int half, int lane, int total_tiles) {
+  if constexpr (EPI == EPI_F32 || EPI == EPI_GELU_BWD) {
+    const int tiles_mn = sh.num_m * sh.num_n;
+    const bool tile_ok = t < total_tiles;
+    const int rem = tile_ok ? t % tiles_mn : 0;
+    const int m_blk = rem / sh.num_n, n_blk = rem - m_blk * sh.num_n;
+    const int col = n_blk * BN + half * (BN / 2) + c * 32 + (lane & 3) * 8;
+    const int row0 = m_blk * BM + q * 32 + (lane >> 2);
+    const int ncols = sh.N - col;
 #pragma unroll
-    for (int j = 0; j < 8; ++j) v[j] = 0.f;
-  }
-  if (ep.out_f32) {
-    float* p = ep.out_f32 + row * ep.ldo_f32 + col;
-#pragma unroll
-    for (int h = 0; h < 2; ++h)
-      if (4 * h < nvalid)
-        store_f32x4(p + 4 * h, make_float4(v[4 * h], v[4 * h + 1], v[4 * h + 2], v[4 * h + 3]), ep.accumulate != 0);
-  }
-  if (ep.out_bf16) {
-    __nv_bfloat16* p = ep.out_bf16 + row * ep.ldo_bf16 + col;
-    if (nvalid == 8) {
-      uint4 u = {pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]), pack_bf16(v[4], v[5]), pack_bf16(v[6], v[7])};
-      *reinterpret_cast<uint4*>(p) = u;
-    } else if (nvalid == 4) {
-      uint2 u = {pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3])};
-      *reinterpret_cast<uint2*>(p) = u;
+    for (int it = 0; it < 4; ++it) {
+      const int row = row0 + it * 8;
+      const bool ok = tile_ok && ncols >= 4 && row < sh.M;
+      if constexpr (EPI == EPI_F32) {
+        pf.v[it][0] = make_float4(0.f, 0.f, 0.f, 0.f);
+        pf.v[it][1] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (ok && ep.residual) {
+          const float* r = ep.residual + static_cast<long>(row) * ep.ldr + col;
+          pf.v[it][0] = *reinterpret_cast<const float4*>(r);
+          if (ncols >= 8) pf.v[it][1] = *reinterpret_cast<const float4*>(r + 4);
+        }
+      } else {
+        pf.v[it] = make_uint4(0u, 0u, 0u, 0u);
+        if (ok) {
+          const __nv_bfloat16* a = ep.aux + static_cast<long>(row) * ep.ldaux + col;
+          if (ncols >= 8) {
+            pf.v[it] = *reinterpret_cast<const uint4*>(a);
+          } else {
+            const uint2 u = *reinterpret_cast<const uint2*>(a);
+            pf.v[it].x = u.x, pf.v[it].y = u.y;
+          }
+        }
+      }
     }
   }
 }
 
-template <int BN, bool A_MN, bool B_MN>
+// Epilogue warps.  TMEM hands each thread one accumulator ROW (32 consecutive columns); global memory
+// wants a warp to write consecutive COLUMNS.  Each warp transposes 32x32 f32 chunks through a private,
+// XOR-swizzled 4 KB staging tile (conflict-free both ways), then runs the fused epilogue with 4 lanes
+// covering the 128 contiguous bytes of a chunk row (8 columns per lane, 8 rows per warp instruction):
+// all global loads and stores are coalesced 16-byte accesses.
+template <int EPI, int BN>
+__device__ __forceinline__ void epilogue_role(const EpiParams& ep, const GemmShape& sh, uint8_t* sEpi,
+                                              uint64_t* tfull, uint64_t* tempty, uint32_t tmem_base, int warp,
+                                              int lane, int total_tiles) {
+  const int e = warp - kEpiWarp0;
+  const int q = e & 3;      // TMEM lane quarter == warp % 4
+  const int half = e >> 2;  // which half of the tile's columns
+  constexpr int HALF_N = BN / 2;
+  constexpr int NCHUNK = HALF_N / 32;
+  const uint32_t stage_addr = smem_u32(sEpi + e * kStageBytesPerWarp);
+  const int rsub = lane >> 2, cu = lane & 3;
+  const int tiles_mn = sh.num_m * sh.num_n;
+  EpiPrefetch<EPI> pf;
+  epi_prefetch<EPI, BN>(pf, ep, sh, blockIdx.x, 0, q, half, lane, total_tiles);
+  int iter = 0;
+  for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++iter) {
+    const int rem = t % tiles_mn;
+    const int m_blk = rem / sh.num_n, n_blk = rem - m_blk * sh.num_n;
+    const int acc = iter & 1;
+    const uint32_t acc_phase = (iter >> 1) & 1;
+    // this lane's 4 rows are the same for every chunk of the tile: resolve the row predicates once
+    const int row0 = m_blk * BM + q * 32 + rsub;
+    uint32_t store_mask = 0, zero_mask = 0;
+#pragma unroll
+    for (int it = 0; it < 4; ++it) {
+      const int row = row0 + it * 8;
+      bool st = row < sh.M, zr = false;
+      if (ep.row_period > 0 && (row % ep.row_period) < ep.row_skip) {
+        if (ep.row_mask_mode == 2) st = false;
+        if (ep.row_mask_mode == 1) zr = true;
+      }
+      store_mask |= (st ? 1u : 0u) << it;
+      zero_mask |= (zr ? 1u : 0u) << it;
+    }
+    mbar_wait(&tfull[acc], acc_phase);
+    tc_fence_after();
+    const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * BN + half * HALF_N;
+#pragma unroll
+    for (int c = 0; c < NCHUNK; ++c) {
+      const int col0 = n_blk * BN + half * HALF_N + c * 32;
+      const bool live = col0 < sh.N;  // warp-uniform
+      if (live) {
+        uint32_t r[32];
+        tmem_ld_32x32(t_addr + c * 32, r);
+        tmem_ld_wait();
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+          const uint32_t a = stage_addr + lane * kStageRowBytes + ((u ^ (lane & 7)) << 4);
+          asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(r[4 * u]), "r"(r[4 * u + 1]),
+                       "r"(r[4 * u + 2]), "r"(r[4 * u + 3])
+                       : "memory");
+        }
+      }
+      if (c == NCHUNK - 1) {  // accumulator fully drained: hand the TMEM buffer back to the MMA warp
+        tc_fence_before();
+        mbar_arrive(&tempty[acc]);
+      }
+      __syncwarp();
+      const EpiPrefetch<EPI> cur = pf;
+      if (c + 1 < NCHUNK) epi_prefetch<EPI, BN>(pf, ep, sh, t, c + 1, q, half, lane, total_tiles);
+      else epi_prefetch<EPI, BN>(pf, ep, sh, t + static_cast<int>(gridDim.x), 0, q, half, lane, total_tiles);
+      const int col = col0 + cu * 8;
+      const int ncols = sh.N - col;
+      if (live && ncols >= 4) {
+        float sc[8], bs[8];
+        const bool scaled = col < ep.col_scale_n;            // warp-uniform per chunk up to the boundary
+        const bool affine = ep.bias != nullptr || col0 < ep.col_scale_n;
+        if (affine) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            sc[j] = (scaled && col + j < ep.col_scale_n) ? ep.col_scale : 1.f;
+            bs[j] = 0.f;
+          }
+          if (ep.bias) {
+            const float4 b0 = *reinterpret_cast<const float4*>(ep.bias + col);
+            bs[0] = b0.x * sc[0], bs[1] = b0.y * sc[1], bs[2] = b0.z * sc[2], bs[3] = b0.w * sc[3];
+            if (ncols >= 8) {
+              const float4 b1 = *reinterpret_cast<const float4*>(ep.bias + col + 4);
+              bs[4] = b1.x * sc[4], bs[5] = b1.y * sc[5], bs[6] = b1.z * sc[6], bs[7] = b1.w * sc[7];
+            }
+          }
+        }
+#pragma unroll
+        for (int it = 0; it < 4; ++it) {
+          const int rloc = it * 8 + rsub;
+          float v[8];
+          const uint32_t a0 = stage_addr + rloc * kStageRowBytes + (((2 * cu) ^ (rloc & 7)) << 4);
+          const uint32_t a1 = stage_addr + rloc * kStageRowBytes + (((2 * cu + 1) ^ (rloc & 7)) << 4);
+          asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
+                       : "=f"(v[0]), "=f"(v[1]), "=f"(v[2]), "=f"(v[3])
+                       : "r"(a0));
+          asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
+                       : "=f"(v[4]), "=f"(v[5]), "=f"(v[6]), "=f"(v[7])
+                       : "r"(a1));
+          if (store_mask & (1u << it)) {
+            const int row = row0 + it * 8;
+            epilogue8<EPI>(ep, v, sc, bs, affine, static_cast<long>(row), row, col, ncols,
+                           (zero_mask >> it) & 1u, cur, it);
+          }
+        }
+      }
+      __syncwarp();
+    }
+  }
+}
+
+template <int BN, bool A_MN, bool B_MN, int EPI>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmShape sh,
             const EpiParams ep) {
@@ -188,7 +388,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   uint8_t* sA = smem;
   uint8_t* sB = smem + STAGES * Cfg::A_BYTES;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + STAGES * Cfg::STAGE_BYTES);
+  uint8_t* sEpi = smem + STAGES * Cfg::STAGE_BYTES;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sEpi + Cfg::EPI_BYTES);
   uint64_t* full = bars;
   uint64_t* empty = bars + STAGES;
   uint64_t* tfull = bars + 2 * STAGES;
@@ -209,7 +410,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     }
     for (int a = 0; a < 2; ++a) {
       mbar_init(&tfull[a], 1);
-      mbar_init(&tempty[a], 128);
+      mbar_init(&tempty[a], kEpiWarps * 32);
     }
     fence_barrier_init();
   }
@@ -293,51 +494,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       }
     }
   } else if (warp >= kEpiWarp0) {
-    const int q = warp - kEpiWarp0;  // TMEM lane quarter == warp % 4
-    int iter = 0;
-    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++iter) {
-      const int split = t / tiles_mn;
-      const int rem = t - split * tiles_mn;
-      const int m_blk = rem / sh.num_n, n_blk = rem - m_blk * sh.num_n;
-      const int acc = iter & 1;
-      const uint32_t acc_phase = (iter >> 1) & 1;
-      mbar_wait(&tfull[acc], acc_phase);
-      tc_fence_after();
-      const long row = static_cast<long>(m_blk) * BM + q * 32 + lane;
-      const bool row_ok = row < sh.M;
-      int rp = 0;
-      bool masked = false;
-      if (ep.row_period > 0) {
-        rp = static_cast<int>(row % ep.row_period);
-        masked = rp < ep.row_skip;
-      }
-      const bool do_store = row_ok && !(masked && ep.row_mask_mode == 2);
-      const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * BN;
-#pragma unroll 1
-      for (int c0 = 0; c0 < BN; c0 += 32) {
-        const int col0 = n_blk * BN + c0;
-        if (col0 >= sh.N) break;  // warp-uniform
-        uint32_t r[32];
-        tmem_ld_32x32(t_addr + c0, r);
-        tmem_ld_wait();
-        if (do_store) {
-#pragma unroll
-          for (int j8 = 0; j8 < 4; ++j8) {
-            const int col = col0 + j8 * 8;
-            int nvalid = sh.N - col;
-            nvalid = nvalid >= 8 ? 8 : (nvalid >= 4 ? 4 : 0);
-            if (nvalid > 0) {
-              float v[8];
-#pragma unroll
-              for (int j = 0; j < 8; ++j) v[j] = __uint_as_float(r[j8 * 8 + j]);
-              epilogue8(ep, v, row, col, nvalid, rp, masked && ep.row_mask_mode == 1);
-            }
-          }
-        }
-      }
-      tc_fence_before();
-      mbar_arrive(&tempty[acc]);
-    }
+    epilogue_role<EPI, BN>(ep, sh, sEpi, tfull, tempty, tmem_base, warp, lane, total_tiles);
   }
 
   tc_fence_before();
@@ -378,10 +535,10 @@ static int make_tmap(CUtensorMap* map, const void* ptr, long inner, long outer, 
   return 0;
 }
 
-template <int BN, bool A_MN, bool B_MN>
+template <int BN, bool A_MN, bool B_MN, int EPI>
 static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmShape& sh, const EpiParams& ep,
                        int grid, cudaStream_t stream) {
-  auto kern = gemm_kernel<BN, A_MN, B_MN>;
+  auto kern = gemm_kernel<BN, A_MN, B_MN, EPI>;
   static bool attr_set = false;  // per template instantiation; benign race (idempotent)
   if (!attr_set) {
     JM_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, GemmCfg<BN>::SMEM_BYTES));
@@ -392,13 +549,31 @@ static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const Gem
   return 0;
 }
 
+template <int BN, bool A_MN, bool B_MN>
+static int dispatch_epi(int epi, const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmShape& sh,
+                        const EpiParams& ep, int grid, cudaStream_t stream) {
+  switch (epi) {
+    case EPI_BF16: return launch_gemm<BN, A_MN, B_MN, EPI_BF16>(tmA, tmB, sh, ep, grid, stream);
+    case EPI_F32: return launch_gemm<BN, A_MN, B_MN, EPI_F32>(tmA, tmB, sh, ep, grid, stream);
+    case EPI_GELU_FWD: return launch_gemm<BN, A_MN, B_MN, EPI_GELU_FWD>(tmA, tmB, sh, ep, grid, stream);
+    case EPI_GELU_BWD: return launch_gemm<BN, A_MN, B_MN, EPI_GELU_BWD>(tmA, tmB, sh, ep, grid, stream);
+    default: return launch_gemm<BN, A_MN, B_MN, EPI_GENERIC>(tmA, tmB, sh, ep, grid, stream);
+  }
+}
+
 template <int BN>
-static int dispatch_major(bool a_mn, bool b_mn, const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmShape& sh,
-                          const EpiParams& ep, int grid, cudaStream_t stream) {
-  if (!a_mn && !b_mn) return launch_gemm<BN, false, false>(tmA, tmB, sh, ep, grid, stream);
-  if (!a_mn && b_mn) return launch_gemm<BN, false, true>(tmA, tmB, sh, ep, grid, stream);
-  if (a_mn && !b_mn) return launch_gemm<BN, true, false>(tmA, tmB, sh, ep, grid, stream);
-  return launch_gemm<BN, true, true>(tmA, tmB, sh, ep, grid, stream);
+static int dispatch_major(bool a_mn, bool b_mn, int epi, const CUtensorMap& tmA, const CUtensorMap& tmB,
+                          const GemmShape& sh, const EpiParams& ep, int grid, cudaStream_t stream) {
+  if (!a_mn && !b_mn) return dispatch_epi<BN, false, false>(epi, tmA, tmB, sh, ep, grid, stream);
+  if (!a_mn && b_mn) return dispatch_epi<BN, false, true>(epi, tmA, tmB, sh, ep, grid, stream);
+  // transposed-A products are weight gradients: f32 accumulate epilogue (anything else: generic)
+  if (epi != EPI_F32) epi = EPI_GENERIC;
+  if (a_mn && !b_mn) {
+    if (epi == EPI_F32) return launch_gemm<BN, true, false, EPI_F32>(tmA, tmB, sh, ep, grid, stream);
+    return launch_gemm<BN, true, false, EPI_GENERIC>(tmA, tmB, sh, ep, grid, stream);
+  }
+  if (epi == EPI_F32) return launch_gemm<BN, true, true, EPI_F32>(tmA, tmB, sh, ep, grid, stream);
+  return launch_gemm<BN, true, true, EPI_GENERIC>(tmA, tmB, sh, ep, grid, stream);
 }
 
 }  // namespace jm
@@ -414,10 +589,14 @@ extern "C" int jm_gemm(const jm_gemm_args* a, void* stream_) {
   JM_CHECK(a->act != 2 || a->aux, "jm_gemm: act=2 needs aux");
   JM_CHECK(!a->pe || (a->pe_idx && a->row_period > 0), "jm_gemm: pe needs pe_idx and row_period");
   JM_CHECK(!a->out_f32 || a->ldo_f32 % 4 == 0, "jm_gemm: ldo_f32 must be a multiple of 4");
-  JM_CHECK(!a->out_bf16 || a->ldo_bf16 % 4 == 0, "jm_gemm: ldo_bf16 must be a multiple of 4");
-  JM_CHECK(!a->out2_bf16 || a->ldo2_bf16 % 4 == 0, "jm_gemm: ldo2_bf16 must be a multiple of 4");
+  JM_CHECK(!a->out_bf16 || a->ldo_bf16 % 8 == 0, "jm_gemm: ldo_bf16 must be a multiple of 8");
+  JM_CHECK(!a->out2_bf16 || a->ldo2_bf16 % 8 == 0, "jm_gemm: ldo2_bf16 must be a multiple of 8");
+  JM_CHECK(((reinterpret_cast<uintptr_t>(a->out_bf16) | reinterpret_cast<uintptr_t>(a->out2_bf16) |
+             reinterpret_cast<uintptr_t>(a->aux) | reinterpret_cast<uintptr_t>(a->out_f32) |
+             reinterpret_cast<uintptr_t>(a->residual) | reinterpret_cast<uintptr_t>(a->bias)) & 15) == 0,
+           "jm_gemm: epilogue pointers must be 16-byte aligned");
   JM_CHECK(!a->residual || a->ldr % 4 == 0, "jm_gemm: ldr must be a multiple of 4");
-  JM_CHECK(!a->aux || a->ldaux % 4 == 0, "jm_gemm: ldaux must be a multiple of 4");
+  JM_CHECK(!a->aux || a->ldaux % 8 == 0, "jm_gemm: ldaux must be a multiple of 8");
 
   const int sms = sm_count();
   JM_CHECK(sms > 0, "jm_gemm: no CUDA device");
@@ -486,7 +665,14 @@ extern "C" int jm_gemm(const jm_gemm_args* a, void* stream_) {
   const long total = static_cast<long>(num_m) * num_n * splits;
   const int grid = static_cast<int>(total < sms ? total : sms);
   const bool amn = a->a_mn_major != 0, bmn = a->b_mn_major != 0;
-  if (bn == 256) return dispatch_major<256>(amn, bmn, tmA, tmB, sh, ep, grid, stream);
-  if (bn == 128) return dispatch_major<128>(amn, bmn, tmA, tmB, sh, ep, grid, stream);
-  return dispatch_major<64>(amn, bmn, tmA, tmB, sh, ep, grid, stream);
+  int epi = EPI_GENERIC;
+  const bool only_bf16 = ep.out_bf16 && !ep.out_f32 && !ep.out2_bf16;
+  const bool only_f32 = ep.out_f32 && !ep.out_bf16 && !ep.out2_bf16;
+  if (ep.act == 1 && !ep.out_f32 && !ep.residual && !ep.pe) epi = EPI_GELU_FWD;
+  else if (ep.act == 2 && only_bf16 && !ep.residual && !ep.pe) epi = EPI_GELU_BWD;
+  else if (ep.act == 0 && only_f32) epi = EPI_F32;
+  else if (ep.act == 0 && only_bf16 && !ep.residual && !ep.pe) epi = EPI_BF16;
+  if (bn == 256) return dispatch_major<256>(amn, bmn, epi, tmA, tmB, sh, ep, grid, stream);
+  if (bn == 128) return dispatch_major<128>(amn, bmn, epi, tmA, tmB, sh, ep, grid, stream);
+  return dispatch_major<64>(amn, bmn, epi, tmA, tmB, sh, ep, grid, stream);
 }

@@ -107,6 +107,7 @@ class MAEEngine:
         self.dn16 = e(wmax)
         self.dqkv16 = e(3 * wmax)
         self.datt16 = e(wmax)
+        self.delta_ws = e(B * max(cfg.heads * self.Te, cfg.dec_heads * self.Td), dt=F32)
         self.dy16 = e(self.Me, dd)
         self.dhj16 = e(B, 4 * J * d)
         self.dcn16 = e(B, J * d)
@@ -269,7 +270,7 @@ class MAEEngine:
         # ---- attention branch: x_b = x + wo(attn(wqkv LN1(x)))
         datt, dqkv = view(self.datt16, dim), view(self.dqkv16, 3 * dim)
         self._bwd_linear(s.att, dxb16, M, f"{name}/attn/wo", dim, dim, dX16=datt)
-        ops.attention_bwd(s.qkv, s.att, datt, s.lse, B, T, heads, hd, hd ** -0.5, dqkv)
+        ops.attention_bwd(s.qkv, s.att, datt, s.lse, B, T, heads, hd, hd ** -0.5, dqkv, self.delta_ws)
         self._bwd_linear(s.xn1, dqkv, M, f"{name}/attn/wqkv", 3 * dim, dim, dX16=dn)
         ops.layernorm_bwd(dn, x_in, s.mean1, s.rstd1, ps.f(f"{name}/norm1/scale"), dxb, dx, dx16,
                           ps.grad(f"{name}/norm1/scale"), ps.grad(f"{name}/norm1/bias"), self.ln_ws)

@@ -175,11 +175,17 @@ def attention_fwd(qkv: torch.Tensor, batch: int, T: int, heads: int, head_dim: i
 
 
 def attention_bwd(qkv: torch.Tensor, out: torch.Tensor, dout: torch.Tensor, lse: torch.Tensor, batch: int, T: int,
-                  heads: int, head_dim: int, q_scale: float, dqkv: torch.Tensor) -> None:
+                  heads: int, head_dim: int, q_scale: float, dqkv: torch.Tensor,
+                  delta_ws: Optional[torch.Tensor] = None) -> None:
     _chk(qkv, BF16, "qkv"), _chk(out, BF16, "out"), _chk(dout, BF16, "dout"), _chk(lse, F32, "lse")
-    _chk(dqkv, BF16, "dqkv")
-    check(_lib.load().jm_attention_bwd(ptr(qkv), _ld(qkv), ptr(out), _ld(out), ptr(dout), _ld(dout), ptr(lse), batch,
-                                       T, heads, head_dim, q_scale, ptr(dqkv), _ld(dqkv), stream_ptr()))
+    _chk(dqkv, BF16, "dqkv"), _chk(delta_ws, F32, "delta_ws")
+    if delta_ws is None:
+        delta_ws = torch.empty(batch * heads * T, dtype=F32, device=qkv.device)
+    if delta_ws.numel() < batch * heads * T:
+        raise _lib.JmError("attention_bwd: delta_ws too small")
+    check(_lib.load().jm_attention_bwd(ptr(qkv), _ld(qkv), ptr(out), _ld(out), ptr(dout), _ld(dout), ptr(lse),
+                                       ptr(delta_ws), batch, T, heads, head_dim, q_scale, ptr(dqkv), _ld(dqkv),
+                                       stream_ptr()))
 
 
 # ------------------------------------------------------------------ token assembly
