@@ -207,10 +207,17 @@ def run_ours(args):
 
     counter = {"micro": 0, "step": 0}
 
+    use_graph = os.environ.get("JM_NO_GRAPH", "0") != "1"
+    if use_graph:
+        eng.capture_graphs()
+
     def resident_step():
         for i in range(accum):
-            eng.forward(dev_images[i], dev_noise[counter["micro"] % total_micro])
-            eng.backward(zero_grads=(i == 0))
+            if use_graph:
+                eng.run_graph(dev_images[i], dev_noise[counter["micro"] % total_micro], zero_grads=(i == 0))
+            else:
+                eng.forward(dev_images[i], dev_noise[counter["micro"] % total_micro])
+                eng.backward(zero_grads=(i == 0))
             counter["micro"] += 1
         if reducer is not None:
             reducer.all_reduce_grads()
@@ -229,6 +236,8 @@ def run_ours(args):
         e1.record()
         torch.cuda.synchronize()
         launches = lib.jm_launch_count() - l0
+        if use_graph:     # kernels inside a replayed graph are not re-counted by the library: add them
+            launches += steps * accum * eng.graph_launches
         ms = e0.elapsed_time(e1)
         sampler.stop()
         barrier()

@@ -275,6 +275,43 @@ class MAEEngine:
         ops.layernorm_bwd(dn, x_in, s.mean1, s.rstd1, ps.f(f"{name}/norm1/scale"), dxb, dx, dx16,
                           ps.grad(f"{name}/norm1/scale"), ps.grad(f"{name}/norm1/bias"), self.ln_ws)
 
+    # ------------------------------------------------------------------ CUDA graphs
+    def capture_graphs(self) -> None:
+        """Records forward + backward of one micro-batch into two CUDA graphs (gradients zeroed first /
+        accumulated) over static input buffers, so that a micro-step is one graph launch instead of
+        ~1800 kernel launches issued from Python."""
+        cfg, B = self.cfg, self.B
+        self.images_buf = torch.empty(B, 3, cfg.image_size, cfg.image_size, dtype=torch.uint8, device=self.dev)
+        self.noise_buf = torch.zeros(cfg.num_patches, dtype=F32, device=self.dev)
+        side = torch.cuda.Stream(device=self.dev)
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):                  # eager warm-up: one-time function attributes, module load
+            self.images_buf.zero_()
+            self.forward(self.images_buf, self.noise_buf)
+            self.backward(zero_grads=True)
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+        self.graphs = {}
+        lib = _lib.load()
+        for zero in (True, False):
+            g = torch.cuda.CUDAGraph()
+            l0 = lib.jm_launch_count()
+            with torch.cuda.graph(g):
+                self.forward(self.images_buf, self.noise_buf)
+                self.backward(zero_grads=zero)
+            self.graph_launches = lib.jm_launch_count() - l0
+            self.graphs[zero] = g
+        self.ps.g.zero_()
+
+    def run_graph(self, images: torch.Tensor, noise: torch.Tensor, zero_grads: bool) -> torch.Tensor:
+        """forward + backward through the captured graph; images may be a pinned host tensor."""
+        if not hasattr(self, "graphs"):
+            self.capture_graphs()
+        self.images_buf.copy_(images, non_blocking=True)
+        self.noise_buf.copy_(noise, non_blocking=True)
+        self.graphs[bool(zero_grads)].replay()
+        return self.loss
+
     # ------------------------------------------------------------------ optimizer
     def adamw_step(self, count: int, lr: float, grad_scale: float = 1.0) -> None:
         """optax.adamw update number ``count`` (0-based) over the flat buffers (src/pretraining.py:223-234)."""

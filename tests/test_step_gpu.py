@@ -163,3 +163,65 @@ def test_engine_rejects_wrong_batch_shape():
     ocfg, cfg, state, images, noise, store, eng = _setup("tiny")
     with pytest.raises(JmError):
         eng.forward(images[:2].cuda(), torch.from_numpy(noise).cuda())
+
+
+def _tiny_args(**kw):
+    import argparse
+    base = dict(layers=2, dim=64, heads=2, labels=0, patch_size=8, image_size=32, image_mask_ratio=0.75,
+                dec_layers=2, dec_dim=64, dec_heads=2, norm_pix_loss=False, init_seed=0, mixup_seed=0,
+                dropout_seed=0, noise_seed=0, optimizer="adamw", learning_rate=1.5e-4, weight_decay=0.05,
+                adam_b1=0.9, adam_b2=0.95, adam_eps=1e-8, lr_decay=1.0, clip_grad=0.0, grad_accum=1,
+                train_batch_size=256, warmup_steps=10, training_steps=100, posemb="sincos2d", dropout=0.0,
+                droppath=0.0, dec_dropout=0.0, dec_droppath=0.0, layerscale=False, dec_layerscale=False)
+    base.update(kw)
+    return argparse.Namespace(**base)
+
+
+@pytest.mark.parametrize("accum", [1, 2])
+def test_training_step_api_matches_oracle(accum):
+    """create_train_state / training_step / validation_step (reference names, src/pretraining.py:125-270),
+    through the CUDA-graph path, with host uint8 batches, against the oracle with the same parameters."""
+    from jumbo_mae_tpu_b200.pretraining import create_train_state, training_step, validation_step
+    from jumbo_mae_tpu_b200.params import tree_leaves
+    state = create_train_state(_tiny_args(grad_accum=accum)).replicate()
+    ocfg = O.tiny()
+    ostate = O.create_state(ocfg, seed=0, randomize_all=True)
+    state.store.load_tree(ostate.params)
+    images, noise = O.synthetic_batch(ocfg, 4 * accum, seed=5, noise_seed=6)
+    val = validation_step(state, (images[:4],), noise=noise)
+    want_val = O.pretrain_forward(ostate.params, images[:4], noise, ocfg)["loss"].item()
+    assert abs(val["loss"].item() - want_val) <= 5e-3 * want_val and val["num_samples"].item() == 4
+    # reference semantics of accumulation: grads of micro-batches are summed then divided (:135,:153)
+    grads = None
+    for i in range(accum):
+        _, g = O.loss_and_grads(ostate.params, images[4 * i:4 * i + 4], noise, ocfg)
+        grads = g if grads is None else O.tree_map(lambda a, b: a + b, grads, g)
+    grads = O.tree_map(lambda a: a / accum, grads)
+    want_state, want_metrics, _ = O.training_step(ostate, images[:4], noise, grads_override=grads)
+    for i in range(accum):
+        state, metrics = training_step(state, (images[4 * i:4 * i + 4].pin_memory(),), noise=noise)
+        assert state.step == (1 if i == accum - 1 else 0)
+    assert abs(metrics["learning_rate"] - want_metrics["learning_rate"]) < 1e-12
+    assert torch.isfinite(metrics["loss"]).item()
+    got = dict(tree_leaves(state.params))
+    p0 = dict(O.tree_leaves(ostate.params))
+    leaves = [(p, w) for p, w in O.tree_leaves(want_state.params) if p[-2:] != ("wk", "bias")]
+    dw = torch.cat([(w - p0[p]).flatten() for p, w in leaves])
+    dg = torch.cat([(got[p].detach().cpu().reshape(w.shape) - p0[p]).flatten() for p, w in leaves])
+    assert _rel(dg, dw) <= 5e-2
+    assert set(state.opt_state) >= {"count", "mu", "nu", "hyperparams"}
+
+
+def test_cuda_graph_path_equals_eager():
+    ocfg, cfg, state, images, noise, store, eng = _setup("mid")
+    im, nz = images.cuda(), torch.from_numpy(noise).cuda()
+    loss_e = eng.forward(im, nz).clone()
+    eng.backward()
+    g_e = store.g.clone()
+    loss_g = eng.run_graph(im, nz, zero_grads=True).clone()
+    torch.cuda.synchronize()
+    assert loss_e.item() == loss_g.item()
+    # identical kernels; only the f32 atomics of the weight-gradient epilogues may reorder
+    assert torch.allclose(store.g, g_e, rtol=1e-4, atol=1e-7)
+    eng.run_graph(im, nz, zero_grads=False)
+    assert torch.allclose(store.g, 2 * g_e, rtol=1e-4, atol=1e-7)
