@@ -102,12 +102,16 @@ int jm_layernorm_fwd(const float* x, long ldx, int rows, int dim, const float* g
 /* Backward of the above.  dx = (dres ? dres : 0) + LN'(dy); rows with
  * (row % row_period) < row_skip are left untouched (used for the CLS rows of the
  * Jumbo layer, src/modeling.py:194-204).  dgamma/dbeta are ACCUMULATED (+=).
+ * dcol (optional, [dim], +=) receives the column sums of dx over the rows with
+ * (row % dcol_period) >= dcol_skip: dx is the gradient flowing into the Dense that
+ * produced the residual branch, so this is that Dense's bias gradient for free.
  * workspace: jm_layernorm_bwd_workspace(rows, dim) bytes. */
 size_t jm_layernorm_bwd_workspace(int rows, int dim);
 int jm_layernorm_bwd(const jm_bf16* dy, long lddy, const float* x, long ldx, const float* mean, const float* rstd,
                      const float* gamma, int rows, int dim, const float* dres, long lddres, float* dx, long lddx,
                      jm_bf16* dx_bf16, long lddxb, int row_period, int row_skip, float* dgamma, float* dbeta,
-                     void* workspace, size_t workspace_bytes, void* stream);
+                     float* dcol, int dcol_period, int dcol_skip, void* workspace, size_t workspace_bytes,
+                     void* stream);
 
 /* ---------------------------------------------------------------- GEMM
  * D = epilogue(A * B), bf16 operands, f32 accumulation in tensor memory
@@ -145,6 +149,7 @@ typedef struct jm_gemm_args {
   int accumulate;
   int splits;      /* 0 = choose automatically */
   int block_n;     /* 0 = choose automatically (64, 128 or 256) */
+  float* colsum;   /* optional [N]: += column sums of the stored output (fused bias gradient) */
 } jm_gemm_args;
 int jm_gemm(const jm_gemm_args* args, void* stream);
 
@@ -156,10 +161,11 @@ int jm_attention_fwd(const jm_bf16* qkv, long ldqkv, int batch, int T, int heads
                      long ldo, float* lse, void* stream);
 /* dqkv (same layout as qkv) from dout; the q part is multiplied by q_scale so that it
  * is the gradient w.r.t. the un-scaled projection.  delta_ws: caller-owned scratch of
- * batch*heads*T floats (receives rowsum(dout * out)). */
+ * batch*heads*T floats (receives rowsum(dout * out)).  dbias (optional, [3*heads*hd], +=)
+ * receives the column sums of dqkv, i.e. the gradient of the fused q/k/v bias. */
 int jm_attention_bwd(const jm_bf16* qkv, long ldqkv, const jm_bf16* out, long ldo, const jm_bf16* dout, long lddo,
                      const float* lse, float* delta_ws, int batch, int T, int heads, int head_dim, float q_scale,
-                     jm_bf16* dqkv, long lddqkv, void* stream);
+                     jm_bf16* dqkv, long lddqkv, float* dbias, void* stream);
 
 /* ---------------------------------------------------------------- token assembly
  * CLS prepend (src/modeling.py:249-250,257): x[b, j, :] = cls[j, :] for j < J. */
@@ -174,9 +180,9 @@ int jm_unshuffle_bwd(const float* dout, const int32_t* ids_restore, int batch, i
                      jm_bf16* dy, float* dmask_emb, void* stream);
 
 /* Column sums (bias gradients): out[c] += sum over rows r with (r % row_period) >= row_skip
- * of x[r, c].  x is bf16 (is_f32 == 0) or f32. */
-int jm_colsum(const void* x, int is_f32, long ldx, int rows, int cols, int row_period, int row_skip, float* out,
-              void* stream);
+ * (row_invert != 0: < row_skip) of x[r, c].  x is bf16 (is_f32 == 0) or f32. */
+int jm_colsum(const void* x, int is_f32, long ldx, int rows, int cols, int row_period, int row_skip,
+              int row_invert, float* out, void* stream);
 
 /* ---------------------------------------------------------------- optimizer
  * optax.adamw leaf update (src/pretraining.py:223-234) over a flat parameter buffer:

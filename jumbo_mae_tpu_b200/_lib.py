@@ -45,6 +45,7 @@ class GemmArgs(ctypes.Structure):
         ("accumulate", c_int),
         ("splits", c_int),
         ("block_n", c_int),
+        ("colsum", c_void_p),
     ]
 
 
@@ -77,14 +78,14 @@ def load() -> ctypes.CDLL:
         "jm_patch_loss_static": [P, c_long, P, P, c_int, c_int, c_int, c_int, c_int, c_float, P, P, c_long, P],
         "jm_layernorm_fwd": [P, c_long, c_int, c_int, P, P, c_float, P, c_long, P, c_long, P, P, P],
         "jm_layernorm_bwd": [P, c_long, P, c_long, P, P, P, c_int, c_int, P, c_long, P, c_long, P, c_long, c_int,
-                             c_int, P, P, P, c_size_t, P],
+                             c_int, P, P, P, c_int, c_int, P, c_size_t, P],
         "jm_gemm": [POINTER(GemmArgs), P],
         "jm_attention_fwd": [P, c_long, c_int, c_int, c_int, c_int, P, c_long, P, P],
-        "jm_attention_bwd": [P, c_long, P, c_long, P, c_long, P, P, c_int, c_int, c_int, c_int, c_float, P, c_long, P],
+        "jm_attention_bwd": [P, c_long, P, c_long, P, c_long, P, P, c_int, c_int, c_int, c_int, c_float, P, c_long, P, P],
         "jm_fill_cls": [P, c_int, c_int, c_int, c_int, P, P],
         "jm_unshuffle_fwd": [P, P, P, P, c_int, c_int, c_int, c_int, c_int, P, P],
         "jm_unshuffle_bwd": [P, P, c_int, c_int, c_int, c_int, c_int, P, P, P],
-        "jm_colsum": [P, c_int, c_long, c_int, c_int, c_int, c_int, P, P],
+        "jm_colsum": [P, c_int, c_long, c_int, c_int, c_int, c_int, c_int, P, P],
         "jm_adamw": [P, P, P, P, P, c_long, c_long, c_float, c_float, c_float, c_float, c_float, c_float, c_float,
                      c_float, P],
         "jm_cast_bf16": [P, P, c_long, P],

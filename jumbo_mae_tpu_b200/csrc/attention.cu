@@ -218,7 +218,7 @@ template <int HD>
 __global__ void attn_bwd_kernel(const __nv_bfloat16* __restrict__ qkv, long ldqkv,
                                 const __nv_bfloat16* __restrict__ dout, long lddo, const float* __restrict__ lse,
                                 const float* __restrict__ delta, int T, int heads, float q_scale,
-                                __nv_bfloat16* __restrict__ dqkv, long lddqkv) {
+                                __nv_bfloat16* __restrict__ dqkv, long lddqkv, float* __restrict__ dbias) {
   constexpr int LDS = HD + 8;
   extern __shared__ __align__(16) uint8_t smem_raw[];
   const int Tp = (T + 63) / 64 * 64;
@@ -228,6 +228,8 @@ __global__ void attn_bwd_kernel(const __nv_bfloat16* __restrict__ qkv, long ldqk
   __nv_bfloat16* sdO = sV + Tp * LDS;
   float* sL = reinterpret_cast<float*>(sdO + Tp * LDS);
   float* sD = sL + Tp;
+  float* sBias = sD + Tp;  // [3][HD] column sums of dq, dk, dv over this (image, head)
+  for (int i = threadIdx.x; i < 3 * HD; i += blockDim.x) sBias[i] = 0.f;
   const int b = blockIdx.x / heads, h = blockIdx.x - b * heads;
   const int d = heads * HD;
   const __nv_bfloat16* base = qkv + static_cast<long>(b) * T * ldqkv + h * HD;
@@ -316,6 +318,21 @@ __global__ void attn_bwd_kernel(const __nv_bfloat16* __restrict__ qkv, long ldqk
           *reinterpret_cast<uint32_t*>(dst + i * 8) = pack_bf16(dq[i][2 * r] * q_scale, dq[i][2 * r + 1] * q_scale);
       }
     }
+    if (dbias != nullptr) {  // padded query rows have dS == 0, so they add nothing
+#pragma unroll
+      for (int i = 0; i < HD / 8; ++i) {
+        float c0 = dq[i][0] + dq[i][2], c1 = dq[i][1] + dq[i][3];
+#pragma unroll
+        for (int o = 4; o < 32; o <<= 1) {
+          c0 += __shfl_xor_sync(0xffffffffu, c0, o);
+          c1 += __shfl_xor_sync(0xffffffffu, c1, o);
+        }
+        if (g == 0) {
+          atomicAdd(&sBias[i * 8 + 2 * t4], c0 * q_scale);
+          atomicAdd(&sBias[i * 8 + 2 * t4 + 1], c1 * q_scale);
+        }
+      }
+    }
   }
 
   // ---------------- phase 2: a warp's 16 keys -> dK, dV (transposed problem)
@@ -395,6 +412,34 @@ __global__ void attn_bwd_kernel(const __nv_bfloat16* __restrict__ qkv, long ldqk
         }
       }
     }
+    if (dbias != nullptr) {
+      const float m0 = (row0 + g) < T ? 1.f : 0.f, m1 = (row0 + g + 8) < T ? 1.f : 0.f;  // padded key rows
+#pragma unroll
+      for (int i = 0; i < HD / 8; ++i) {
+        float k0 = dk[i][0] * m0 + dk[i][2] * m1, k1 = dk[i][1] * m0 + dk[i][3] * m1;
+        float v0 = dv[i][0] * m0 + dv[i][2] * m1, v1 = dv[i][1] * m0 + dv[i][3] * m1;
+#pragma unroll
+        for (int o = 4; o < 32; o <<= 1) {
+          k0 += __shfl_xor_sync(0xffffffffu, k0, o);
+          k1 += __shfl_xor_sync(0xffffffffu, k1, o);
+          v0 += __shfl_xor_sync(0xffffffffu, v0, o);
+          v1 += __shfl_xor_sync(0xffffffffu, v1, o);
+        }
+        if (g == 0) {
+          atomicAdd(&sBias[HD + i * 8 + 2 * t4], k0);
+          atomicAdd(&sBias[HD + i * 8 + 2 * t4 + 1], k1);
+          atomicAdd(&sBias[2 * HD + i * 8 + 2 * t4], v0);
+          atomicAdd(&sBias[2 * HD + i * 8 + 2 * t4 + 1], v1);
+        }
+      }
+    }
+  }
+  if (dbias != nullptr) {
+    __syncthreads();
+    for (int i = threadIdx.x; i < 3 * HD; i += blockDim.x) {
+      const int part = i / HD, c = i - part * HD;
+      atomicAdd(dbias + part * d + h * HD + c, sBias[i]);
+    }
   }
 }
 
@@ -404,7 +449,7 @@ static size_t fwd_smem(int T, int hd) {
 }
 static size_t bwd_smem(int T, int hd) {
   const int Tp = (T + 63) / 64 * 64;
-  return static_cast<size_t>(4 * Tp) * (hd + 8) * 2 + static_cast<size_t>(2 * Tp) * 4;
+  return static_cast<size_t>(4 * Tp) * (hd + 8) * 2 + static_cast<size_t>(2 * Tp) * 4 + 3 * hd * 4;
 }
 
 // Warps per CTA: one per 16-row strip when the register file allows it, otherwise the strips
@@ -441,7 +486,7 @@ static int launch_fwd(const jm_bf16* qkv, long ldqkv, int batch, int T, int head
 template <int HD>
 static int launch_bwd(const jm_bf16* qkv, long ldqkv, const jm_bf16* out, long ldo, const jm_bf16* dout, long lddo,
                       const float* lse, float* delta, int batch, int T, int heads, float q_scale, jm_bf16* dqkv,
-                      long lddqkv, cudaStream_t stream) {
+                      long lddqkv, float* dbias, cudaStream_t stream) {
   const size_t smem = bwd_smem(T, HD);
   auto kern = attn_bwd_kernel<HD>;
   if (smem > 48 * 1024) JM_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -455,7 +500,7 @@ static int launch_bwd(const jm_bf16* qkv, long ldqkv, const jm_bf16* out, long l
   JM_AFTER_LAUNCH();
   kern<<<batch * heads, threads, smem, stream>>>(
       reinterpret_cast<const __nv_bfloat16*>(qkv), ldqkv, reinterpret_cast<const __nv_bfloat16*>(dout), lddo, lse,
-      delta, T, heads, q_scale, reinterpret_cast<__nv_bfloat16*>(dqkv), lddqkv);
+      delta, T, heads, q_scale, reinterpret_cast<__nv_bfloat16*>(dqkv), lddqkv, dbias);
   JM_AFTER_LAUNCH();
   return 0;
 }
@@ -484,7 +529,8 @@ extern "C" int jm_attention_fwd(const jm_bf16* qkv, long ldqkv, int batch, int T
 
 extern "C" int jm_attention_bwd(const jm_bf16* qkv, long ldqkv, const jm_bf16* out, long ldo, const jm_bf16* dout,
                                 long lddo, const float* lse, float* delta_ws, int batch, int T, int heads,
-                                int head_dim, float q_scale, jm_bf16* dqkv, long lddqkv, void* stream_) {
+                                int head_dim, float q_scale, jm_bf16* dqkv, long lddqkv, float* dbias,
+                                void* stream_) {
   using namespace jm;
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   if (check_attn("jm_attention_bwd", batch, T, heads, head_dim, ldqkv, lddqkv)) return 1;
@@ -493,8 +539,11 @@ extern "C" int jm_attention_bwd(const jm_bf16* qkv, long ldqkv, const jm_bf16* o
   JM_CHECK(bwd_smem(T, head_dim) <= 227 * 1024, "jm_attention_bwd: T=%d hd=%d does not fit shared memory", T,
            head_dim);
   if (head_dim == 32)
-    return launch_bwd<32>(qkv, ldqkv, out, ldo, dout, lddo, lse, delta_ws, batch, T, heads, q_scale, dqkv, lddqkv, stream);
+    return launch_bwd<32>(qkv, ldqkv, out, ldo, dout, lddo, lse, delta_ws, batch, T, heads, q_scale, dqkv, lddqkv, dbias,
+                          stream);
   if (head_dim == 64)
-    return launch_bwd<64>(qkv, ldqkv, out, ldo, dout, lddo, lse, delta_ws, batch, T, heads, q_scale, dqkv, lddqkv, stream);
-  return launch_bwd<80>(qkv, ldqkv, out, ldo, dout, lddo, lse, delta_ws, batch, T, heads, q_scale, dqkv, lddqkv, stream);
+    return launch_bwd<64>(qkv, ldqkv, out, ldo, dout, lddo, lse, delta_ws, batch, T, heads, q_scale, dqkv, lddqkv, dbias,
+                          stream);
+  return launch_bwd<80>(qkv, ldqkv, out, ldo, dout, lddo, lse, delta_ws, batch, T, heads, q_scale, dqkv, lddqkv, dbias,
+                          stream);
 }

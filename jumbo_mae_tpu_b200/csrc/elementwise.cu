@@ -224,7 +224,7 @@ layernorm_fwd_kernel(const float* __restrict__ x, long ldx, int rows, int D, con
   }
 }
 
-constexpr int kLnBwdMaxBlocks = 592;  // 4 x 148
+constexpr int kLnBwdMaxBlocks = 444;  // 3 x 148
 
 // dx = dres + rstd * (dy*g - mean(dy*g) - xhat * mean(dy*g*xhat)); per-block dgamma/dbeta partials
 // are accumulated in shared memory and written to the workspace [block][2][D].
@@ -233,9 +233,9 @@ layernorm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, long lddy, const floa
                      const float* __restrict__ mean, const float* __restrict__ rstd, const float* __restrict__ gamma,
                      int rows, int D, const float* __restrict__ dres, long lddres, float* __restrict__ dx, long lddx,
                      __nv_bfloat16* __restrict__ dxb, long lddxb, int row_period, int row_skip,
-                     float* __restrict__ ws) {
-  extern __shared__ float s_acc[];  // [2][D]
-  for (int c = threadIdx.x; c < 2 * D; c += blockDim.x) s_acc[c] = 0.f;
+                     float* __restrict__ ws, int /*want_dcol*/, int /*dcol_period*/, int /*dcol_skip*/) {
+  extern __shared__ float s_acc[];  // [3][D] (the dcol part is not produced by this fallback)
+  for (int c = threadIdx.x; c < 3 * D; c += blockDim.x) s_acc[c] = 0.f;
   __syncthreads();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   for (long row = static_cast<long>(blockIdx.x) * kLnWarps + warp; row < rows;
@@ -284,8 +284,8 @@ layernorm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, long lddy, const floa
     }
   }
   __syncthreads();
-  float* out = ws + static_cast<long>(blockIdx.x) * 2 * D;
-  for (int c = threadIdx.x; c < 2 * D; c += blockDim.x) out[c] = s_acc[c];
+  float* out = ws + static_cast<long>(blockIdx.x) * 3 * D;
+  for (int c = threadIdx.x; c < 3 * D; c += blockDim.x) out[c] = s_acc[c];
 }
 
 // Fast path for dim <= NV*128: the row and the per-lane dgamma/dbeta partial sums stay in
@@ -296,12 +296,13 @@ layernorm_bwd_reg_kernel(const __nv_bfloat16* __restrict__ dy, long lddy, const 
                          const float* __restrict__ mean, const float* __restrict__ rstd,
                          const float* __restrict__ gamma, int rows, int D, const float* __restrict__ dres,
                          long lddres, float* __restrict__ dx, long lddx, __nv_bfloat16* __restrict__ dxb, long lddxb,
-                         int row_period, int row_skip, float* __restrict__ ws) {
-  extern __shared__ float s_acc[];  // [2][D]
-  for (int c = threadIdx.x; c < 2 * D; c += blockDim.x) s_acc[c] = 0.f;
+                         int row_period, int row_skip, float* __restrict__ ws, int want_dcol, int dcol_period,
+                         int dcol_skip) {
+  extern __shared__ float s_acc[];  // [3][D]: dgamma, dbeta, column sums of dx
+  for (int c = threadIdx.x; c < 3 * D; c += blockDim.x) s_acc[c] = 0.f;
   __syncthreads();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  float gm[NV][4], ag[NV][4], ab[NV][4];
+  float gm[NV][4], ag[NV][4], ab[NV][4], ac[NV][4];
 #pragma unroll
   for (int k = 0; k < NV; ++k) {
     const int c = lane * 4 + k * 128;
@@ -309,11 +310,12 @@ layernorm_bwd_reg_kernel(const __nv_bfloat16* __restrict__ dy, long lddy, const 
     if (c < D) g = *reinterpret_cast<const float4*>(gamma + c);
     gm[k][0] = g.x, gm[k][1] = g.y, gm[k][2] = g.z, gm[k][3] = g.w;
 #pragma unroll
-    for (int j = 0; j < 4; ++j) ag[k][j] = 0.f, ab[k][j] = 0.f;
+    for (int j = 0; j < 4; ++j) ag[k][j] = 0.f, ab[k][j] = 0.f, ac[k][j] = 0.f;
   }
   for (long row = static_cast<long>(blockIdx.x) * kLnWarps + warp; row < rows;
        row += static_cast<long>(gridDim.x) * kLnWarps) {
     if (row_period > 0 && (row % row_period) < row_skip) continue;
+    const bool col_row = want_dcol && !(dcol_period > 0 && (row % dcol_period) < dcol_skip);
     const __nv_bfloat16* dyr = dy + row * lddy;
     const float* xr = x + row * ldx;
     const float mu = mean[row], rs = rstd[row];
@@ -358,6 +360,10 @@ layernorm_bwd_reg_kernel(const __nv_bfloat16* __restrict__ dy, long lddy, const 
           uint2 w = {pack_bf16(o[0], o[1]), pack_bf16(o[2], o[3])};
           *reinterpret_cast<uint2*>(dxb + row * lddxb + c) = w;
         }
+        if (col_row) {
+#pragma unroll
+          for (int j = 0; j < 4; ++j) ac[k][j] += o[j];
+        }
       }
     }
   }
@@ -369,24 +375,38 @@ layernorm_bwd_reg_kernel(const __nv_bfloat16* __restrict__ dy, long lddy, const 
       for (int j = 0; j < 4; ++j) {
         atomicAdd(&s_acc[c + j], ag[k][j]);
         atomicAdd(&s_acc[D + c + j], ab[k][j]);
+        if (want_dcol) atomicAdd(&s_acc[2 * D + c + j], ac[k][j]);
       }
     }
   }
   __syncthreads();
-  float* out = ws + static_cast<long>(blockIdx.x) * 2 * D;
-  for (int c = threadIdx.x; c < 2 * D; c += blockDim.x) out[c] = s_acc[c];
+  float* out = ws + static_cast<long>(blockIdx.x) * 3 * D;
+  for (int c = threadIdx.x; c < 3 * D; c += blockDim.x) out[c] = s_acc[c];
 }
 
-__global__ void ln_param_reduce_kernel(const float* __restrict__ ws, int nblocks, int D, float* __restrict__ dgamma,
-                                       float* __restrict__ dbeta) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= 2 * D) return;
+// out[c] += sum over blocks of ws[block][c]; 32 columns x 8 block-groups per CTA
+__global__ void __launch_bounds__(256)
+ln_param_reduce_kernel(const float* __restrict__ ws, int nblocks, int D, float* __restrict__ dgamma,
+                       float* __restrict__ dbeta, float* __restrict__ dcol) {
+  __shared__ float red[8][33];
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int c = blockIdx.x * 32 + tx;
   float s = 0.f;
-  for (int b = 0; b < nblocks; ++b) s += ws[static_cast<long>(b) * 2 * D + c];
-  if (c < D) {
-    if (dgamma) dgamma[c] += s;
-  } else {
-    if (dbeta) dbeta[c - D] += s;
+  if (c < 3 * D)
+    for (int b = ty; b < nblocks; b += 8) s += ws[static_cast<long>(b) * 3 * D + c];
+  red[ty][tx] = s;
+  __syncthreads();
+  if (ty == 0 && c < 3 * D) {
+    float t = 0.f;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) t += red[k][tx];
+    if (c < D) {
+      if (dgamma) dgamma[c] += t;
+    } else if (c < 2 * D) {
+      if (dbeta) dbeta[c - D] += t;
+    } else {
+      if (dcol) dcol[c - 2 * D] += t;
+    }
   }
 }
 
@@ -458,7 +478,7 @@ __global__ void unshuffle_bwd_kernel(const float* __restrict__ dout, const int* 
 template <bool F32>
 __global__ void __launch_bounds__(256)
 colsum_kernel(const void* __restrict__ xv, long ldx, int rows, int cols, int row_period, int row_skip,
-              int rows_per_block, float* __restrict__ out) {
+              int row_invert, int rows_per_block, float* __restrict__ out) {
   __shared__ float4 s_part[4][64];
   const int tx = threadIdx.x & 63, ty = threadIdx.x >> 6;
   const int c = (blockIdx.x * 64 + tx) * 4;
@@ -467,7 +487,7 @@ colsum_kernel(const void* __restrict__ xv, long ldx, int rows, int cols, int row
   float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
   if (c < cols) {
     for (int r = r0 + ty; r < r1; r += 4) {
-      if (row_period > 0 && (r % row_period) < row_skip) continue;
+      if (row_period > 0 && (((r % row_period) < row_skip) != (row_invert != 0))) continue;
       if (F32) {
         const float4 v = *reinterpret_cast<const float4*>(static_cast<const float*>(xv) + r * ldx + c);
         acc.x += v.x, acc.y += v.y, acc.z += v.z, acc.w += v.w;
@@ -676,27 +696,30 @@ static int ln_bwd_blocks(int rows) {
 }
 
 extern "C" size_t jm_layernorm_bwd_workspace(int rows, int dim) {
-  return static_cast<size_t>(ln_bwd_blocks(rows)) * 2 * dim * sizeof(float);
+  return static_cast<size_t>(ln_bwd_blocks(rows)) * 3 * dim * sizeof(float);
 }
 
 extern "C" int jm_layernorm_bwd(const jm_bf16* dy, long lddy, const float* x, long ldx, const float* mean,
                                 const float* rstd, const float* gamma, int rows, int dim, const float* dres,
                                 long lddres, float* dx, long lddx, jm_bf16* dx_bf16, long lddxb, int row_period,
-                                int row_skip, float* dgamma, float* dbeta, void* workspace, size_t workspace_bytes,
-                                void* stream) {
+                                int row_skip, float* dgamma, float* dbeta, float* dcol, int dcol_period,
+                                int dcol_skip, void* workspace, size_t workspace_bytes, void* stream) {
   JM_CHECK(dim % 4 == 0 && ldx % 4 == 0 && lddy % 4 == 0, "jm_layernorm_bwd: dim/ld must be multiples of 4");
-  JM_CHECK(dim * 2 * sizeof(float) <= 96 * 1024, "jm_layernorm_bwd: dim %d too large", dim);
+  JM_CHECK(dim * 3 * sizeof(float) <= 96 * 1024, "jm_layernorm_bwd: dim %d too large", dim);
+  JM_CHECK(dcol == nullptr || dim <= 1280, "jm_layernorm_bwd: dcol is only produced for dim <= 1280");
   if (rows == 0) return 0;
   JM_CHECK(workspace && workspace_bytes >= jm_layernorm_bwd_workspace(rows, dim),
            "jm_layernorm_bwd: workspace too small");
   const int grid = ln_bwd_blocks(rows);
-  const size_t smem = static_cast<size_t>(2) * dim * sizeof(float);
+  const size_t smem = static_cast<size_t>(3) * dim * sizeof(float);
   if (smem > 48 * 1024) {
     JM_CUDA(cudaFuncSetAttribute(layernorm_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
   }
+  const int want_dcol = dcol != nullptr ? 1 : 0;
 #define JM_LN_BWD_ARGS                                                                                          \
   reinterpret_cast<const __nv_bfloat16*>(dy), lddy, x, ldx, mean, rstd, gamma, rows, dim, dres, lddres, dx, lddx, \
-      reinterpret_cast<__nv_bfloat16*>(dx_bf16), lddxb, row_period, row_skip, static_cast<float*>(workspace)
+      reinterpret_cast<__nv_bfloat16*>(dx_bf16), lddxb, row_period, row_skip, static_cast<float*>(workspace), \
+      want_dcol, dcol_period, dcol_skip
   if (dim <= 128) layernorm_bwd_reg_kernel<1><<<grid, kLnWarps * 32, smem, STREAM>>>(JM_LN_BWD_ARGS);
   else if (dim <= 256) layernorm_bwd_reg_kernel<2><<<grid, kLnWarps * 32, smem, STREAM>>>(JM_LN_BWD_ARGS);
   else if (dim <= 512) layernorm_bwd_reg_kernel<4><<<grid, kLnWarps * 32, smem, STREAM>>>(JM_LN_BWD_ARGS);
@@ -705,8 +728,8 @@ extern "C" int jm_layernorm_bwd(const jm_bf16* dy, long lddy, const float* x, lo
   else if (dim <= 1280) layernorm_bwd_reg_kernel<10><<<grid, kLnWarps * 32, smem, STREAM>>>(JM_LN_BWD_ARGS);
   else layernorm_bwd_kernel<<<grid, kLnWarps * 32, smem, STREAM>>>(JM_LN_BWD_ARGS);
 #undef JM_LN_BWD_ARGS
-  ln_param_reduce_kernel<<<(2 * dim + 255) / 256, 256, 0, STREAM>>>(static_cast<const float*>(workspace), grid, dim,
-                                                                    dgamma, dbeta);
+  ln_param_reduce_kernel<<<(3 * dim + 31) / 32, 256, 0, STREAM>>>(static_cast<const float*>(workspace), grid, dim,
+                                                                  dgamma, dbeta, dcol);
   JM_AFTER_LAUNCH();
   return 0;
 }
@@ -739,7 +762,7 @@ extern "C" int jm_unshuffle_bwd(const float* dout, const int32_t* ids_restore, i
 }
 
 extern "C" int jm_colsum(const void* x, int is_f32, long ldx, int rows, int cols, int row_period, int row_skip,
-                         float* out, void* stream) {
+                         int row_invert, float* out, void* stream) {
   JM_CHECK(cols % 4 == 0 && ldx % 4 == 0, "jm_colsum: cols and ldx must be multiples of 4");
   if (rows == 0 || cols == 0) return 0;
   const int gx = (cols + 255) / 256;
@@ -749,9 +772,11 @@ extern "C" int jm_colsum(const void* x, int is_f32, long ldx, int rows, int cols
   if (rows_per_block < 32) rows_per_block = 32;
   gy = (rows + rows_per_block - 1) / rows_per_block;
   if (is_f32)
-    colsum_kernel<true><<<dim3(gx, gy), 256, 0, STREAM>>>(x, ldx, rows, cols, row_period, row_skip, rows_per_block, out);
+    colsum_kernel<true><<<dim3(gx, gy), 256, 0, STREAM>>>(x, ldx, rows, cols, row_period, row_skip, row_invert,
+                                                          rows_per_block, out);
   else
-    colsum_kernel<false><<<dim3(gx, gy), 256, 0, STREAM>>>(x, ldx, rows, cols, row_period, row_skip, rows_per_block, out);
+    colsum_kernel<false><<<dim3(gx, gy), 256, 0, STREAM>>>(x, ldx, rows, cols, row_period, row_skip, row_invert,
+                                                           rows_per_block, out);
   JM_AFTER_LAUNCH();
   return 0;
 }

@@ -55,6 +55,7 @@ struct EpiParams {
   int col_scale_n;
   int row_period, row_skip, row_mask_mode;
   int accumulate;
+  float* colsum;  // optional [N]: += column sums of the stored values (bias gradient of the producer Dense)
 };
 
 template <int BN>
@@ -334,6 +335,7 @@ __device__ __forceinline__ void epilogue_role(const EpiParams& ep, const GemmSha
       else epi_prefetch<EPI, BN>(pf, ep, sh, t + static_cast<int>(gridDim.x), 0, q, half, lane, total_tiles);
       const int col = col0 + cu * 8;
       const int ncols = sh.N - col;
+      float cs[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
       if (live && ncols >= 4) {
         float sc[8], bs[8];
         const bool scaled = col < ep.col_scale_n;            // warp-uniform per chunk up to the boundary
@@ -369,7 +371,22 @@ __device__ __forceinline__ void epilogue_role(const EpiParams& ep, const GemmSha
             const int row = row0 + it * 8;
             epilogue8<EPI>(ep, v, sc, bs, affine, static_cast<long>(row), row, col, ncols,
                            (zero_mask >> it) & 1u, cur, it);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) cs[j] += v[j];
           }
+        }
+      }
+      if (ep.colsum != nullptr && live) {  // warp-uniform: fold the 8 row-lanes, one atomic per column
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          cs[j] += __shfl_xor_sync(0xffffffffu, cs[j], 4);
+          cs[j] += __shfl_xor_sync(0xffffffffu, cs[j], 8);
+          cs[j] += __shfl_xor_sync(0xffffffffu, cs[j], 16);
+        }
+        if (rsub == 0 && ncols >= 4) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j)
+            if (j < ncols) atomicAdd(ep.colsum + col + j, cs[j]);
         }
       }
       __syncwarp();
@@ -661,6 +678,8 @@ extern "C" int jm_gemm(const jm_gemm_args* a, void* stream_) {
   ep.col_scale = a->col_scale, ep.col_scale_n = a->col_scale_n;
   ep.row_period = a->row_period, ep.row_skip = a->row_skip, ep.row_mask_mode = a->row_mask_mode;
   ep.accumulate = (a->accumulate || splits > 1) ? 1 : 0;
+  ep.colsum = a->colsum;
+  JM_CHECK(!a->colsum || a->act != 1, "jm_gemm: colsum is not defined for the GELU-forward epilogue");
 
   const long total = static_cast<long>(num_m) * num_n * splits;
   const int grid = static_cast<int>(total < sms ? total : sms);

@@ -126,14 +126,17 @@ class MAEEngine:
         ops.gemm(A, self._W(f"{name}/kernel"), M, N, K, b_mn=True, ldb=self.ps.ld(f"{name}/kernel"),
                  bias=self._b(f"{name}/bias"), **epi)
 
-    def _bwd_linear(self, X, dY, M, name, N, K, dX16=None, x_ld=None, dy_ld=None, bias_rows=None, **epi):
+    def _bwd_linear(self, X, dY, M, name, N, K, dX16=None, x_ld=None, dy_ld=None, bias_rows=None, bias=True,
+                    **epi):
         """Gradients of Y = X[M,K] @ W[K,N] + b given dY (bf16):
-        dW += X^T dY, db += colsum(dY), and optionally dX16 = epilogue(dY @ W^T)."""
+        dW += X^T dY, db += colsum(dY) (bias=False: the producer of dY already accumulated it),
+        and optionally dX16 = epilogue(dY @ W^T)."""
         ldw = self.ps.ld(f"{name}/kernel")
         ops.gemm(X, dY, K, N, M, a_mn=True, b_mn=True, lda=x_ld, ldb=dy_ld,
                  out_f32=self.ps.grad(f"{name}/kernel"), ldo_f32=ldw, accumulate=True)
-        period, skip = bias_rows if bias_rows else (0, 0)
-        ops.colsum(dY, M, N, self.ps.grad(f"{name}/bias"), row_period=period, row_skip=skip, ldx=dy_ld)
+        if bias:
+            period, skip = bias_rows if bias_rows else (0, 0)
+            ops.colsum(dY, M, N, self.ps.grad(f"{name}/bias"), row_period=period, row_skip=skip, ldx=dy_ld)
         if dX16 is not None or epi:
             ops.gemm(dY, self._W(f"{name}/kernel"), M, K, N, b_mn=False, lda=dy_ld, ldb=ldw, out_bf16=dX16, **epi)
 
@@ -218,30 +221,39 @@ class MAEEngine:
         dn = view(self.dn16, Md, dd)
         self._bwd_linear(self.dec_n, self.dpred, Md, "decoder_image_output", P, dd, dX16=dn, dy_ld=Pp)
         dx, dx16 = view(self.dxA, Md, dd), view(self.dxA16, Md, dd)
+        # (every LayerNorm backward also emits the column sums of the dx it produces: that dx is the
+        #  output gradient of the previous block's ff/w2, i.e. its bias gradient)
         ops.layernorm_bwd(dn, self.za[cfg.dec_layers], self.meanD, self.rstdD, ps.f("decoder_model/dec_norm/scale"),
                           None, dx, dx16, ps.grad("decoder_model/dec_norm/scale"),
-                          ps.grad("decoder_model/dec_norm/bias"), self.ln_ws)
+                          ps.grad("decoder_model/dec_norm/bias"), self.ln_ws,
+                          dcol=ps.grad(f"decoder_model/dec_layer_{cfg.dec_layers - 1}/ff/w2/bias"))
         # ---- decoder blocks
         for i in reversed(range(cfg.dec_layers)):
-            self._block_bwd(f"decoder_model/dec_layer_{i}", self.dec[i], self.za[i], Md, dd, cfg.dec_heads, Td, False)
+            below = ps.grad(f"decoder_model/dec_layer_{i - 1}/ff/w2/bias") if i > 0 else None
+            self._block_bwd(f"decoder_model/dec_layer_{i}", self.dec[i], self.za[i], Md, dd, cfg.dec_heads, Td, False,
+                            below)
         # ---- decoder input assembly + decoder_proj
         ops.unshuffle_bwd(dx, self.ids_restore, B, N, n, J, dd, self.dy16, ps.grad("image_mask_embedding"))
         dn = view(self.dn16, Me, d)
         self._bwd_linear(self.enc_n, self.dy16, Me, "decoder_proj", dd, d, dX16=dn)
         dx, dx16 = view(self.dxA, Me, d), view(self.dxA16, Me, d)
         ops.layernorm_bwd(dn, self.xa[cfg.layers], self.meanF, self.rstdF, ps.f("model/norm/scale"), None, dx, dx16,
-                          ps.grad("model/norm/scale"), ps.grad("model/norm/bias"), self.ln_ws)
+                          ps.grad("model/norm/scale"), ps.grad("model/norm/bias"), self.ln_ws,
+                          dcol=ps.grad(f"model/layer_{cfg.layers - 1}/ff/w2/bias"), dcol_period=Te, dcol_skip=J)
         # ---- encoder blocks
         for i in reversed(range(cfg.layers)):
-            self._block_bwd(f"model/layer_{i}", self.enc[i], self.xa[i], Me, d, cfg.heads, Te, True)
-        # ---- CLS parameter and patch embedding
+            below = ps.grad(f"model/layer_{i - 1}/ff/w2/bias") if i > 0 else ps.grad("model/embed/wte/bias")
+            self._block_bwd(f"model/layer_{i}", self.enc[i], self.xa[i], Me, d, cfg.heads, Te, True, below)
+        # ---- CLS parameter and patch embedding (its bias gradient came from layer 0's LN1 backward)
         ops.colsum(dx, B, J * d, ps.grad("model/cls_tokens"), ldx=Te * d)
         ops.gemm(self.patches, dx16, P, d, Me, a_mn=True, b_mn=True, lda=Pp,
                  out_f32=ps.grad("model/embed/wte/kernel"), ldo_f32=ps.ld("model/embed/wte/kernel"), accumulate=True)
-        ops.colsum(dx16, Me, d, ps.grad("model/embed/wte/bias"), row_period=Te, row_skip=J)
 
-    def _block_bwd(self, name, s: _Block, x_in, M, dim, heads, T, jumbo):
-        """In: d/d(block output) in dxA / dxA16.  Out: d/d(block input) in dxA / dxA16."""
+    def _block_bwd(self, name, s: _Block, x_in, M, dim, heads, T, jumbo, dcol_below):
+        """In: d/d(block output) in dxA / dxA16.  Out: d/d(block input) in dxA / dxA16.
+        Bias gradients are produced where their dY is produced (LayerNorm backward, GELU-backward GEMM
+        epilogue, attention backward); ``dcol_below`` is the ff/w2 (or patch-embed) bias gradient of the
+        block below, whose output gradient this block's LN1 backward emits."""
         ps, B, J = self.ps, self.B, self.cfg.num_cls_tokens
         hd = dim // heads
         view = lambda buf, w: buf[:M * w].view(M, w)
@@ -251,29 +263,34 @@ class MAEEngine:
         period, skip = (T, J) if jumbo else (0, 0)
         mode = 1 if jumbo else 0
         # ---- patch FFN: y = x_b + w2(gelu(w1 LN2(x_b)))
-        self._bwd_linear(s.g, dx16, M, f"{name}/ff/w2", dim, 4 * dim, dX16=dh, bias_rows=(period, skip),
-                         act=2, aux=s.h, row_period=period, row_skip=skip, row_mask_mode=mode)
-        self._bwd_linear(s.xn2, dh, M, f"{name}/ff/w1", 4 * dim, dim, dX16=dn)
+        self._bwd_linear(s.g, dx16, M, f"{name}/ff/w2", dim, 4 * dim, dX16=dh, bias=False, act=2, aux=s.h,
+                         row_period=period, row_skip=skip, row_mask_mode=mode,
+                         colsum=ps.grad(f"{name}/ff/w1/bias"))
+        self._bwd_linear(s.xn2, dh, M, f"{name}/ff/w1", 4 * dim, dim, dX16=dn, bias=False)
         ops.layernorm_bwd(dn, s.xb, s.mean2, s.rstd2, ps.f(f"{name}/norm2/scale"), dx, dxb, dxb16,
                           ps.grad(f"{name}/norm2/scale"), ps.grad(f"{name}/norm2/bias"), self.ln_ws,
-                          row_period=period, row_skip=skip)
+                          row_period=period, row_skip=skip, dcol=ps.grad(f"{name}/attn/wo/bias"))
         if jumbo:
             # ---- Jumbo CLS: c_out = c + w2j(gelu(w1j c)), c = LN3(cls concat); strided [B, J*dim] views
             Jd, ldc = J * dim, T * dim
             self._bwd_linear(s.gj, dx16, B, "model/jumbo_mlp/w2", Jd, 4 * Jd, dX16=self.dhj16, dy_ld=ldc, act=2,
-                             aux=s.hj)
-            self._bwd_linear(s.cn16, self.dhj16, B, "model/jumbo_mlp/w1", 4 * Jd, Jd, dX16=self.dcn16,
+                             aux=s.hj, colsum=ps.grad("model/jumbo_mlp/w1/bias"))
+            self._bwd_linear(s.cn16, self.dhj16, B, "model/jumbo_mlp/w1", 4 * Jd, Jd, dX16=self.dcn16, bias=False,
                              residual=dx, ldr=ldc)
             ops.layernorm_bwd(self.dcn16, s.xb, s.mean3, s.rstd3, ps.f(f"{name}/norm3/scale"), None, dxb, dxb16,
                               ps.grad(f"{name}/norm3/scale"), ps.grad(f"{name}/norm3/bias"), self.ln_ws, rows=B,
                               dim=Jd, ldx=ldc, lddx=ldc, lddxb=ldc)
+            # wo bias: LN2 backward covered the patch rows, add the CLS rows LN3 backward just wrote
+            ops.colsum(dxb16, M, dim, ps.grad(f"{name}/attn/wo/bias"), row_period=T, row_skip=J, row_invert=True)
         # ---- attention branch: x_b = x + wo(attn(wqkv LN1(x)))
         datt, dqkv = view(self.datt16, dim), view(self.dqkv16, 3 * dim)
-        self._bwd_linear(s.att, dxb16, M, f"{name}/attn/wo", dim, dim, dX16=datt)
-        ops.attention_bwd(s.qkv, s.att, datt, s.lse, B, T, heads, hd, hd ** -0.5, dqkv, self.delta_ws)
-        self._bwd_linear(s.xn1, dqkv, M, f"{name}/attn/wqkv", 3 * dim, dim, dX16=dn)
+        self._bwd_linear(s.att, dxb16, M, f"{name}/attn/wo", dim, dim, dX16=datt, bias=False)
+        ops.attention_bwd(s.qkv, s.att, datt, s.lse, B, T, heads, hd, hd ** -0.5, dqkv, self.delta_ws,
+                          dbias=ps.grad(f"{name}/attn/wqkv/bias"))
+        self._bwd_linear(s.xn1, dqkv, M, f"{name}/attn/wqkv", 3 * dim, dim, dX16=dn, bias=False)
         ops.layernorm_bwd(dn, x_in, s.mean1, s.rstd1, ps.f(f"{name}/norm1/scale"), dxb, dx, dx16,
-                          ps.grad(f"{name}/norm1/scale"), ps.grad(f"{name}/norm1/bias"), self.ln_ws)
+                          ps.grad(f"{name}/norm1/scale"), ps.grad(f"{name}/norm1/bias"), self.ln_ws,
+                          dcol=dcol_below, dcol_period=period, dcol_skip=skip)
 
     # ------------------------------------------------------------------ CUDA graphs
     def capture_graphs(self) -> None:

@@ -117,7 +117,9 @@ def layernorm_bwd(dy: torch.Tensor, x: torch.Tensor, mean: torch.Tensor, rstd: t
                   dgamma: torch.Tensor, dbeta: torch.Tensor, workspace: torch.Tensor, row_period: int = 0,
                   row_skip: int = 0, rows: Optional[int] = None, dim: Optional[int] = None,
                   lddy: Optional[int] = None, ldx: Optional[int] = None, lddres: Optional[int] = None,
-                  lddx: Optional[int] = None, lddxb: Optional[int] = None) -> None:
+                  lddx: Optional[int] = None, lddxb: Optional[int] = None, dcol: Optional[torch.Tensor] = None,
+                  dcol_period: int = 0, dcol_skip: int = 0) -> None:
+    _chk(dcol, F32, "dcol")
     _chk(dy, BF16, "dy"), _chk(x, F32, "x"), _chk(mean, F32, "mean"), _chk(rstd, F32, "rstd")
     _chk(gamma, F32, "gamma"), _chk(dres, F32, "dres"), _chk(dx, F32, "dx"), _chk(dx_bf16, BF16, "dx_bf16")
     _chk(dgamma, F32, "dgamma"), _chk(dbeta, F32, "dbeta")
@@ -127,8 +129,8 @@ def layernorm_bwd(dy: torch.Tensor, x: torch.Tensor, mean: torch.Tensor, rstd: t
         ptr(dy), _ld(dy) if lddy is None else lddy, ptr(x), _ld(x) if ldx is None else ldx, ptr(mean), ptr(rstd),
         ptr(gamma), rows, dim, ptr(dres), (_ld(dres) if lddres is None else lddres), ptr(dx),
         (_ld(dx) if lddx is None else lddx), ptr(dx_bf16), (_ld(dx_bf16) if lddxb is None else lddxb), row_period,
-        row_skip, ptr(dgamma), ptr(dbeta), ptr(workspace), workspace.numel() * workspace.element_size(),
-        stream_ptr()))
+        row_skip, ptr(dgamma), ptr(dbeta), ptr(dcol), dcol_period, dcol_skip, ptr(workspace),
+        workspace.numel() * workspace.element_size(), stream_ptr()))
 
 
 # ------------------------------------------------------------------ GEMM
@@ -143,7 +145,8 @@ def gemm(A: torch.Tensor, B: torch.Tensor, M: int, N: int, K: int, *, a_mn: bool
          pe: Optional[torch.Tensor] = None, pe_idx: Optional[torch.Tensor] = None,
          act: int = 0, col_scale: float = 1.0, col_scale_n: int = 0,
          row_period: int = 0, row_skip: int = 0, row_mask_mode: int = 0,
-         accumulate: bool = False, splits: int = 0, block_n: int = 0) -> None:
+         accumulate: bool = False, splits: int = 0, block_n: int = 0,
+         colsum: Optional[torch.Tensor] = None) -> None:
     """D = epilogue(A @ B) through jm_gemm; see include/jumbo_mae_b200.h for the epilogue order."""
     _chk(A, BF16, "A"), _chk(B, BF16, "B"), _chk(out_f32, F32, "out_f32"), _chk(out_bf16, BF16, "out_bf16")
     _chk(out2_bf16, BF16, "out2_bf16"), _chk(bias, F32, "bias"), _chk(residual, F32, "residual")
@@ -163,6 +166,8 @@ def gemm(A: torch.Tensor, B: torch.Tensor, M: int, N: int, K: int, *, a_mn: bool
     a.col_scale, a.col_scale_n = col_scale, col_scale_n
     a.row_period, a.row_skip, a.row_mask_mode = row_period, row_skip, row_mask_mode
     a.accumulate, a.splits, a.block_n = int(accumulate), splits, block_n
+    _chk(colsum, F32, "colsum")
+    a.colsum = ptr(colsum)
     check(_lib.load().jm_gemm(ctypes.byref(a), stream_ptr()))
 
 
@@ -176,16 +181,16 @@ def attention_fwd(qkv: torch.Tensor, batch: int, T: int, heads: int, head_dim: i
 
 def attention_bwd(qkv: torch.Tensor, out: torch.Tensor, dout: torch.Tensor, lse: torch.Tensor, batch: int, T: int,
                   heads: int, head_dim: int, q_scale: float, dqkv: torch.Tensor,
-                  delta_ws: Optional[torch.Tensor] = None) -> None:
+                  delta_ws: Optional[torch.Tensor] = None, dbias: Optional[torch.Tensor] = None) -> None:
     _chk(qkv, BF16, "qkv"), _chk(out, BF16, "out"), _chk(dout, BF16, "dout"), _chk(lse, F32, "lse")
-    _chk(dqkv, BF16, "dqkv"), _chk(delta_ws, F32, "delta_ws")
+    _chk(dqkv, BF16, "dqkv"), _chk(delta_ws, F32, "delta_ws"), _chk(dbias, F32, "dbias")
     if delta_ws is None:
         delta_ws = torch.empty(batch * heads * T, dtype=F32, device=qkv.device)
     if delta_ws.numel() < batch * heads * T:
         raise _lib.JmError("attention_bwd: delta_ws too small")
     check(_lib.load().jm_attention_bwd(ptr(qkv), _ld(qkv), ptr(out), _ld(out), ptr(dout), _ld(dout), ptr(lse),
                                        ptr(delta_ws), batch, T, heads, head_dim, q_scale, ptr(dqkv), _ld(dqkv),
-                                       stream_ptr()))
+                                       ptr(dbias), stream_ptr()))
 
 
 # ------------------------------------------------------------------ token assembly
@@ -211,12 +216,12 @@ def unshuffle_bwd(dout: torch.Tensor, ids_restore: torch.Tensor, batch: int, N: 
 
 
 def colsum(x: torch.Tensor, rows: int, cols: int, out: torch.Tensor, row_period: int = 0, row_skip: int = 0,
-           ldx: Optional[int] = None) -> None:
+           ldx: Optional[int] = None, row_invert: bool = False) -> None:
     if x.dtype not in (BF16, F32):
         raise _lib.JmError("colsum input must be bf16 or f32")
     _chk(out, F32, "out")
     check(_lib.load().jm_colsum(ptr(x), int(x.dtype == F32), _ld(x) if ldx is None else ldx, rows, cols, row_period,
-                                row_skip, ptr(out), stream_ptr()))
+                                row_skip, int(row_invert), ptr(out), stream_ptr()))
 
 
 # ------------------------------------------------------------------ optimizer

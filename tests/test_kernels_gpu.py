@@ -164,8 +164,12 @@ def test_layernorm_bwd(ops, rows, D, period, skip):
     dgamma = torch.ones(D, device="cuda")          # accumulated into
     dbeta = torch.ones(D, device="cuda")
     ws = torch.empty(ops.layernorm_bwd_workspace(rows, D), dtype=torch.uint8, device="cuda")
+    dcol = torch.ones(D, device="cuda") if D <= 1280 else None
     ops.layernorm_bwd(dev(dy), dev(x.detach()), dev(mean), dev(rstd), dev(gamma.detach()), dev(dres), dx, dxb,
-                      dgamma, dbeta, ws, row_period=period, row_skip=skip)
+                      dgamma, dbeta, ws, row_period=period, row_skip=skip, dcol=dcol, dcol_period=7, dcol_skip=2)
+    if dcol is not None:      # fused bias gradient: column sums of dx over rows with row % 7 >= 2
+        sel = keep & ((torch.arange(rows) % 7) >= 2)
+        assert torch.allclose(dcol.cpu() - 1, want_dx[sel].sum(0), rtol=1e-4, atol=1e-3 * max(1.0, math.sqrt(rows)))
     got = dx.cpu()
     assert torch.allclose(got[keep], want_dx[keep], rtol=1e-4, atol=1e-4)
     assert torch.equal(got[~keep], torch.full_like(got[~keep], 5.0))   # skipped rows untouched
@@ -223,6 +227,9 @@ def test_colsum(ops, f32):
     keep = (torch.arange(rows) % 10) >= 2
     want = x.float()[keep][:, :cols].sum(0)
     assert torch.allclose(out.cpu() - 1, want, rtol=1e-4, atol=1e-3)
+    out2 = torch.zeros(cols, device="cuda")
+    ops.colsum(dev(x), rows, cols, out2, row_period=10, row_skip=2, row_invert=True)
+    assert torch.allclose(out2.cpu(), x.float()[~keep][:, :cols].sum(0), rtol=1e-4, atol=1e-3)
 
 
 # ------------------------------------------------------------------ AdamW
@@ -325,11 +332,14 @@ def test_gemm_epilogue_gelu_fwd_and_bwd_with_row_mask(ops):
     dY = torch.randn(M, K, generator=g, device="cuda").to(BF16)
     W2 = (torch.randn(N, K, generator=g, device="cuda") * 0.2).to(BF16)          # Flax kernel [in=N, out=K]
     dH = torch.empty(M, N, dtype=BF16, device="cuda")
-    ops.gemm(dY, W2, M, N, K, b_mn=False, out_bf16=dH, aux=h, act=2, row_period=T, row_skip=J, row_mask_mode=1)
+    cs = torch.ones(N, device="cuda")
+    ops.gemm(dY, W2, M, N, K, b_mn=False, out_bf16=dH, aux=h, act=2, row_period=T, row_skip=J, row_mask_mode=1,
+             colsum=cs)
     hh = h.float().cpu().requires_grad_(True)
     O.gelu_tanh(hh).sum().backward()
     ref = (dY.float() @ W2.float().t()) * hh.grad.cuda() * keep
     assert torch.allclose(dH.float(), ref, rtol=2 ** -6, atol=2e-3)
+    assert torch.allclose(cs - 1, ref.sum(0), rtol=1e-2, atol=2e-2)           # fused bias gradient
 
 
 def test_gemm_epilogue_posemb_and_skip_rows(ops):
@@ -433,7 +443,8 @@ def test_attention_bwd(ops, B, T, H, hd):
     lse = torch.empty(B, H, T, device="cuda")
     ops.attention_fwd(qkv, B, T, H, hd, out, lse)
     dqkv = torch.full((B * T, 3 * d), float("nan"), dtype=BF16, device="cuda")
-    ops.attention_bwd(qkv, out, dout, lse, B, T, H, hd, scale, dqkv)
+    dbias = torch.ones(3 * d, device="cuda")
+    ops.attention_bwd(qkv, out, dout, lse, B, T, H, hd, scale, dqkv, dbias=dbias)
     x = qkv.float().requires_grad_(True)
     ref, _ = _attn_ref(x, B, T, H, hd)
     (ref * dout.float()).sum().backward()
@@ -444,3 +455,6 @@ def test_attention_bwd(ops, B, T, H, hd):
         a, b = got[:, i * d:(i + 1) * d], want[:, i * d:(i + 1) * d]
         rel = ((a - b).norm() / (b.norm() + 1e-6)).item()   # T == 1: dq = dk = 0 exactly
         assert rel < 2e-2, f"d{name}: rel l2 {rel}"          # bf16 P / dS operands, bf16 outputs
+    # fused q/k/v bias gradient = column sums (the k part is ~0: softmax shift invariance)
+    wb = want.sum(0)
+    assert (dbias - 1 - wb).norm().item() <= 2e-2 * wb.norm().item() + 1e-3
