@@ -73,118 +73,143 @@ __device__ __forceinline__ void cp_async_wait_all() {
   asm volatile("cp.async.wait_group 0;" ::: "memory");
 }
 
+__device__ __forceinline__ float ex2f(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
+// One chunk of NT*8 keys for a warp's 16 query rows: S = Q K^T, online softmax (log2 domain), O += P V.
+// TAIL: keys >= T exist in this chunk and must be masked (only ever the last chunk).
+template <int HD, int NT, bool TAIL>
+__device__ __forceinline__ void fwd_chunk(const uint32_t (&qf)[HD / 16][4], uint32_t sKa, uint32_t sVa, int kc, int T,
+                                          int lane, float (&o)[HD / 8][4], float (&m)[2], float (&l)[2]) {
+  constexpr int LDS = HD + 8;
+  const int t4 = lane & 3;
+  float s[NT][4];
+#pragma unroll
+  for (int i = 0; i < NT; ++i) s[i][0] = s[i][1] = s[i][2] = s[i][3] = 0.f;
+#pragma unroll
+  for (int ks = 0; ks < HD / 16; ++ks) {
+#pragma unroll
+    for (int np = 0; np < NT / 2; ++np) {
+      uint32_t kb[4];
+      ldsm_x4(kb, sKa + 2 * bn_off<LDS>(lane, kc + np * 16, ks * 16));
+      mma_bf16(s[2 * np], qf[ks], kb[0], kb[1]);
+      mma_bf16(s[2 * np + 1], qf[ks], kb[2], kb[3]);
+    }
+  }
+  float mx[2] = {-INFINITY, -INFINITY};
+#pragma unroll
+  for (int nt = 0; nt < NT; ++nt)
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      if (TAIL) {
+        const int key = kc + nt * 8 + 2 * t4 + (e & 1);
+        if (key >= T) s[nt][e] = -INFINITY;
+      }
+      mx[e >> 1] = fmaxf(mx[e >> 1], s[nt][e]);
+    }
+  float alpha[2], mneg[2];
+#pragma unroll
+  for (int r = 0; r < 2; ++r) {
+    mx[r] = fmaxf(mx[r], __shfl_xor_sync(0xffffffffu, mx[r], 1));
+    mx[r] = fmaxf(mx[r], __shfl_xor_sync(0xffffffffu, mx[r], 2));
+    const float mn = fmaxf(m[r], mx[r] * kLog2e);  // running max of s * log2(e)
+    alpha[r] = ex2f(m[r] - mn);
+    m[r] = mn;
+    mneg[r] = -mn;
+    l[r] *= alpha[r];
+  }
+#pragma unroll
+  for (int nt = 0; nt < NT; ++nt)
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const float p = ex2f(fmaf(s[nt][e], kLog2e, mneg[e >> 1]));
+      s[nt][e] = p;
+      l[e >> 1] += p;
+    }
+#pragma unroll
+  for (int i = 0; i < HD / 8; ++i) {
+    o[i][0] *= alpha[0], o[i][1] *= alpha[0];
+    o[i][2] *= alpha[1], o[i][3] *= alpha[1];
+  }
+#pragma unroll
+  for (int kk = 0; kk < NT / 2; ++kk) {
+    uint32_t a[4];
+    a[0] = pack_bf16(s[2 * kk][0], s[2 * kk][1]);
+    a[1] = pack_bf16(s[2 * kk][2], s[2 * kk][3]);
+    a[2] = pack_bf16(s[2 * kk + 1][0], s[2 * kk + 1][1]);
+    a[3] = pack_bf16(s[2 * kk + 1][2], s[2 * kk + 1][3]);
+#pragma unroll
+    for (int np = 0; np < HD / 16; ++np) {
+      uint32_t vb[4];
+      ldsm_x4_t(vb, sVa + 2 * bt_off<LDS>(lane, kc + kk * 16, np * 16));
+      mma_bf16(o[2 * np], a, vb[0], vb[1]);
+      mma_bf16(o[2 * np + 1], a, vb[2], vb[3]);
+    }
+  }
+}
+
 template <int HD>
-__global__ void attn_fwd_kernel(const __nv_bfloat16* __restrict__ qkv, long ldqkv, int T, int heads,
+__global__ void __launch_bounds__(256, HD == 32 ? 3 : 1)
+attn_fwd_kernel(const __nv_bfloat16* __restrict__ qkv, long ldqkv, int T, int heads,
                                 __nv_bfloat16* __restrict__ out, long ldo, float* __restrict__ lse) {
   constexpr int LDS = HD + 8;
   extern __shared__ __align__(16) uint8_t smem_raw[];
   __nv_bfloat16* sK = reinterpret_cast<__nv_bfloat16*>(smem_raw);
-  const int Tp = (T + 63) / 64 * 64;
-  const int Tq = (T + 15) / 16 * 16;
-  const int nstrips = Tq / 16, nwarps = blockDim.x >> 5;
-  __nv_bfloat16* sV = sK + Tp * LDS;
-  __nv_bfloat16* sQ = sV + Tp * LDS;
+  const int Tk = (T + 15) / 16 * 16;  // keys / queries padded to the 16-row MMA granule (zero rows)
+  const int nstrips = Tk / 16, nwarps = blockDim.x >> 5;
+  __nv_bfloat16* sV = sK + Tk * LDS;
+  __nv_bfloat16* sQ = sV + Tk * LDS;
   const int b = blockIdx.x / heads, h = blockIdx.x - b * heads;
   const int d = heads * HD;
   const __nv_bfloat16* base = qkv + static_cast<long>(b) * T * ldqkv + h * HD;
-  load_head<HD, LDS>(base, ldqkv, T, Tq, sQ);
-  load_head<HD, LDS>(base + d, ldqkv, T, Tp, sK);
-  load_head<HD, LDS>(base + 2 * d, ldqkv, T, Tp, sV);
+  load_head<HD, LDS>(base, ldqkv, T, Tk, sQ);
+  load_head<HD, LDS>(base + d, ldqkv, T, Tk, sK);
+  load_head<HD, LDS>(base + 2 * d, ldqkv, T, Tk, sV);
   cp_async_wait_all();
   __syncthreads();
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int g = lane >> 2, t4 = lane & 3;
   const uint32_t sQa = smem_u32(sQ), sKa = smem_u32(sK), sVa = smem_u32(sV);
+  const int nfull = Tk / 64, rem = Tk - nfull * 64;
+  const bool ragged = T != Tk;
 
   for (int strip = warp; strip < nstrips; strip += nwarps) {
-  const int row0 = strip * 16;
-  uint32_t qf[HD / 16][4];
+    const int row0 = strip * 16;
+    uint32_t qf[HD / 16][4];
 #pragma unroll
-  for (int ks = 0; ks < HD / 16; ++ks) ldsm_x4(qf[ks], sQa + 2 * a_off<LDS>(lane, row0, ks * 16));
+    for (int ks = 0; ks < HD / 16; ++ks) ldsm_x4(qf[ks], sQa + 2 * a_off<LDS>(lane, row0, ks * 16));
+    float o[HD / 8][4];
+#pragma unroll
+    for (int i = 0; i < HD / 8; ++i) o[i][0] = o[i][1] = o[i][2] = o[i][3] = 0.f;
+    float m[2] = {-INFINITY, -INFINITY}, l[2] = {0.f, 0.f};
 
-  float o[HD / 8][4];
-#pragma unroll
-  for (int i = 0; i < HD / 8; ++i) o[i][0] = o[i][1] = o[i][2] = o[i][3] = 0.f;
-  float m[2] = {-INFINITY, -INFINITY}, l[2] = {0.f, 0.f};
-
-  for (int kc = 0; kc < Tp; kc += 64) {
-    float s[8][4];
-#pragma unroll
-    for (int i = 0; i < 8; ++i) s[i][0] = s[i][1] = s[i][2] = s[i][3] = 0.f;
-#pragma unroll
-    for (int ks = 0; ks < HD / 16; ++ks) {
-#pragma unroll
-      for (int np = 0; np < 4; ++np) {
-        uint32_t kb[4];
-        ldsm_x4(kb, sKa + 2 * bn_off<LDS>(lane, kc + np * 16, ks * 16));
-        mma_bf16(s[2 * np], qf[ks], kb[0], kb[1]);
-        mma_bf16(s[2 * np + 1], qf[ks], kb[2], kb[3]);
-      }
+    for (int c = 0; c < nfull; ++c) {
+      if (rem == 0 && c == nfull - 1 && ragged) fwd_chunk<HD, 8, true>(qf, sKa, sVa, c * 64, T, lane, o, m, l);
+      else fwd_chunk<HD, 8, false>(qf, sKa, sVa, c * 64, T, lane, o, m, l);
     }
-    float mx[2] = {-INFINITY, -INFINITY};
-#pragma unroll
-    for (int nt = 0; nt < 8; ++nt)
-#pragma unroll
-      for (int e = 0; e < 4; ++e) {
-        const int key = kc + nt * 8 + 2 * t4 + (e & 1);
-        if (key >= T) s[nt][e] = -INFINITY;
-        mx[e >> 1] = fmaxf(mx[e >> 1], s[nt][e]);
-      }
-    float alpha[2];
+    if (rem == 16) fwd_chunk<HD, 2, true>(qf, sKa, sVa, nfull * 64, T, lane, o, m, l);
+    else if (rem == 32) fwd_chunk<HD, 4, true>(qf, sKa, sVa, nfull * 64, T, lane, o, m, l);
+    else if (rem == 48) fwd_chunk<HD, 6, true>(qf, sKa, sVa, nfull * 64, T, lane, o, m, l);
+
 #pragma unroll
     for (int r = 0; r < 2; ++r) {
-      mx[r] = fmaxf(mx[r], __shfl_xor_sync(0xffffffffu, mx[r], 1));
-      mx[r] = fmaxf(mx[r], __shfl_xor_sync(0xffffffffu, mx[r], 2));
-      const float mn = fmaxf(m[r], mx[r]);
-      alpha[r] = exp2f((m[r] - mn) * kLog2e);
-      m[r] = mn;
-      l[r] *= alpha[r];
-    }
+      l[r] += __shfl_xor_sync(0xffffffffu, l[r], 1);
+      l[r] += __shfl_xor_sync(0xffffffffu, l[r], 2);
+      const int row = row0 + g + 8 * r;
+      if (row < T) {
+        const float inv = 1.0f / l[r];
+        __nv_bfloat16* dst = out + (static_cast<long>(b) * T + row) * ldo + h * HD + 2 * t4;
 #pragma unroll
-    for (int nt = 0; nt < 8; ++nt)
-#pragma unroll
-      for (int e = 0; e < 4; ++e) {
-        const float p = exp2f((s[nt][e] - m[e >> 1]) * kLog2e);
-        s[nt][e] = p;
-        l[e >> 1] += p;
-      }
-#pragma unroll
-    for (int i = 0; i < HD / 8; ++i) {
-      o[i][0] *= alpha[0], o[i][1] *= alpha[0];
-      o[i][2] *= alpha[1], o[i][3] *= alpha[1];
-    }
-#pragma unroll
-    for (int kk = 0; kk < 4; ++kk) {
-      uint32_t a[4];
-      a[0] = pack_bf16(s[2 * kk][0], s[2 * kk][1]);
-      a[1] = pack_bf16(s[2 * kk][2], s[2 * kk][3]);
-      a[2] = pack_bf16(s[2 * kk + 1][0], s[2 * kk + 1][1]);
-      a[3] = pack_bf16(s[2 * kk + 1][2], s[2 * kk + 1][3]);
-#pragma unroll
-      for (int np = 0; np < HD / 16; ++np) {
-        uint32_t vb[4];
-        ldsm_x4_t(vb, sVa + 2 * bt_off<LDS>(lane, kc + kk * 16, np * 16));
-        mma_bf16(o[2 * np], a, vb[0], vb[1]);
-        mma_bf16(o[2 * np + 1], a, vb[2], vb[3]);
+        for (int i = 0; i < HD / 8; ++i)
+          *reinterpret_cast<uint32_t*>(dst + i * 8) = pack_bf16(o[i][2 * r] * inv, o[i][2 * r + 1] * inv);
+        if (t4 == 0) lse[(static_cast<long>(b) * heads + h) * T + row] = m[r] * 0.6931471805599453f + logf(l[r]);
       }
     }
   }
-#pragma unroll
-  for (int r = 0; r < 2; ++r) {
-    l[r] += __shfl_xor_sync(0xffffffffu, l[r], 1);
-    l[r] += __shfl_xor_sync(0xffffffffu, l[r], 2);
-    const int row = row0 + g + 8 * r;
-    if (row < T) {
-      const float inv = 1.0f / l[r];
-      __nv_bfloat16* dst = out + (static_cast<long>(b) * T + row) * ldo + h * HD + 2 * t4;
-#pragma unroll
-      for (int i = 0; i < HD / 8; ++i)
-        *reinterpret_cast<uint32_t*>(dst + i * 8) = pack_bf16(o[i][2 * r] * inv, o[i][2 * r + 1] * inv);
-      if (t4 == 0) lse[(static_cast<long>(b) * heads + h) * T + row] = m[r] + logf(l[r]);
-    }
-  }
-  }  // strip
 }
 
 // delta[b, h, t] = sum_c dO[b*T+t, h*hd+c] * O[b*T+t, h*hd+c]  (one thread per (token, head))
@@ -214,33 +239,147 @@ __global__ void attn_delta_kernel(const __nv_bfloat16* __restrict__ out, long ld
   delta[(b * heads + h) * T + t] = acc;
 }
 
+// Backward phase 1, one chunk of NT*8 keys for a warp's 16 queries: dQ += dS K with
+// P = exp(S - lse), dS = P * (dP - D), dP = dO V^T.  Lr2 = lse * log2(e).
+template <int HD, int NT, bool TAIL>
+__device__ __forceinline__ void bwd_q_chunk(const uint32_t (&qf)[HD / 16][4], const uint32_t (&dof)[HD / 16][4],
+                                            uint32_t sKa, uint32_t sVa, int kc, int T, int lane,
+                                            const float (&Lr2)[2], const float (&Dr)[2], float (&dq)[HD / 8][4]) {
+  constexpr int LDS = HD + 8;
+  const int t4 = lane & 3;
+  float s[NT][4], dp[NT][4];
+#pragma unroll
+  for (int i = 0; i < NT; ++i)
+#pragma unroll
+    for (int e = 0; e < 4; ++e) s[i][e] = 0.f, dp[i][e] = 0.f;
+#pragma unroll
+  for (int ks = 0; ks < HD / 16; ++ks) {
+#pragma unroll
+    for (int np = 0; np < NT / 2; ++np) {
+      uint32_t kb[4], vb[4];
+      ldsm_x4(kb, sKa + 2 * bn_off<LDS>(lane, kc + np * 16, ks * 16));
+      mma_bf16(s[2 * np], qf[ks], kb[0], kb[1]);
+      mma_bf16(s[2 * np + 1], qf[ks], kb[2], kb[3]);
+      ldsm_x4(vb, sVa + 2 * bn_off<LDS>(lane, kc + np * 16, ks * 16));
+      mma_bf16(dp[2 * np], dof[ks], vb[0], vb[1]);
+      mma_bf16(dp[2 * np + 1], dof[ks], vb[2], vb[3]);
+    }
+  }
+#pragma unroll
+  for (int nt = 0; nt < NT; ++nt)
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      float p = ex2f(fmaf(s[nt][e], kLog2e, -Lr2[e >> 1]));
+      if (TAIL) {
+        const int key = kc + nt * 8 + 2 * t4 + (e & 1);
+        if (key >= T) p = 0.f;
+      }
+      s[nt][e] = p * (dp[nt][e] - Dr[e >> 1]);  // dS
+    }
+#pragma unroll
+  for (int kk = 0; kk < NT / 2; ++kk) {
+    uint32_t a[4];
+    a[0] = pack_bf16(s[2 * kk][0], s[2 * kk][1]);
+    a[1] = pack_bf16(s[2 * kk][2], s[2 * kk][3]);
+    a[2] = pack_bf16(s[2 * kk + 1][0], s[2 * kk + 1][1]);
+    a[3] = pack_bf16(s[2 * kk + 1][2], s[2 * kk + 1][3]);
+#pragma unroll
+    for (int np = 0; np < HD / 16; ++np) {
+      uint32_t kb[4];
+      ldsm_x4_t(kb, sKa + 2 * bt_off<LDS>(lane, kc + kk * 16, np * 16));
+      mma_bf16(dq[2 * np], a, kb[0], kb[1]);
+      mma_bf16(dq[2 * np + 1], a, kb[2], kb[3]);
+    }
+  }
+}
+
+// Backward phase 2, one chunk of NT*8 queries for a warp's 16 keys (transposed problem):
+// dV += P^T dO, dK += dS^T Q.  Padded queries carry lse = +big (P = 0) and zero dO rows.
+template <int HD, int NT>
+__device__ __forceinline__ void bwd_kv_chunk(const uint32_t (&kf)[HD / 16][4], const uint32_t (&vf)[HD / 16][4],
+                                             uint32_t sQa, uint32_t sdOa, const float* sL2, const float* sD, int qc,
+                                             int lane, float (&dk)[HD / 8][4], float (&dv)[HD / 8][4]) {
+  constexpr int LDS = HD + 8;
+  const int t4 = lane & 3;
+  float st[NT][4], dpt[NT][4];
+#pragma unroll
+  for (int i = 0; i < NT; ++i)
+#pragma unroll
+    for (int e = 0; e < 4; ++e) st[i][e] = 0.f, dpt[i][e] = 0.f;
+#pragma unroll
+  for (int ks = 0; ks < HD / 16; ++ks) {
+#pragma unroll
+    for (int np = 0; np < NT / 2; ++np) {
+      uint32_t qb[4], ob[4];
+      ldsm_x4(qb, sQa + 2 * bn_off<LDS>(lane, qc + np * 16, ks * 16));
+      mma_bf16(st[2 * np], kf[ks], qb[0], qb[1]);
+      mma_bf16(st[2 * np + 1], kf[ks], qb[2], qb[3]);
+      ldsm_x4(ob, sdOa + 2 * bn_off<LDS>(lane, qc + np * 16, ks * 16));
+      mma_bf16(dpt[2 * np], vf[ks], ob[0], ob[1]);
+      mma_bf16(dpt[2 * np + 1], vf[ks], ob[2], ob[3]);
+    }
+  }
+  uint32_t pa[NT / 2][4], dsa[NT / 2][4];
+#pragma unroll
+  for (int nt = 0; nt < NT; ++nt) {
+    const int q0 = qc + nt * 8 + 2 * t4;
+    const float2 L2 = *reinterpret_cast<const float2*>(sL2 + q0);
+    const float2 D2 = *reinterpret_cast<const float2*>(sD + q0);
+    float p[4], ds[4];
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const float L = (e & 1) ? L2.y : L2.x, D = (e & 1) ? D2.y : D2.x;
+      p[e] = ex2f(fmaf(st[nt][e], kLog2e, -L));
+      ds[e] = p[e] * (dpt[nt][e] - D);
+    }
+    pa[nt >> 1][(nt & 1) * 2 + 0] = pack_bf16(p[0], p[1]);
+    pa[nt >> 1][(nt & 1) * 2 + 1] = pack_bf16(p[2], p[3]);
+    dsa[nt >> 1][(nt & 1) * 2 + 0] = pack_bf16(ds[0], ds[1]);
+    dsa[nt >> 1][(nt & 1) * 2 + 1] = pack_bf16(ds[2], ds[3]);
+  }
+#pragma unroll
+  for (int kk = 0; kk < NT / 2; ++kk) {
+#pragma unroll
+    for (int np = 0; np < HD / 16; ++np) {
+      uint32_t ob[4], qb[4];
+      ldsm_x4_t(ob, sdOa + 2 * bt_off<LDS>(lane, qc + kk * 16, np * 16));
+      mma_bf16(dv[2 * np], pa[kk], ob[0], ob[1]);
+      mma_bf16(dv[2 * np + 1], pa[kk], ob[2], ob[3]);
+      ldsm_x4_t(qb, sQa + 2 * bt_off<LDS>(lane, qc + kk * 16, np * 16));
+      mma_bf16(dk[2 * np], dsa[kk], qb[0], qb[1]);
+      mma_bf16(dk[2 * np + 1], dsa[kk], qb[2], qb[3]);
+    }
+  }
+}
+
 template <int HD>
-__global__ void attn_bwd_kernel(const __nv_bfloat16* __restrict__ qkv, long ldqkv,
+__global__ void __launch_bounds__(256, HD == 32 ? 2 : 1)
+attn_bwd_kernel(const __nv_bfloat16* __restrict__ qkv, long ldqkv,
                                 const __nv_bfloat16* __restrict__ dout, long lddo, const float* __restrict__ lse,
                                 const float* __restrict__ delta, int T, int heads, float q_scale,
                                 __nv_bfloat16* __restrict__ dqkv, long lddqkv, float* __restrict__ dbias) {
   constexpr int LDS = HD + 8;
   extern __shared__ __align__(16) uint8_t smem_raw[];
-  const int Tp = (T + 63) / 64 * 64;
+  const int Tk = (T + 15) / 16 * 16;
   __nv_bfloat16* sQ = reinterpret_cast<__nv_bfloat16*>(smem_raw);
-  __nv_bfloat16* sK = sQ + Tp * LDS;
-  __nv_bfloat16* sV = sK + Tp * LDS;
-  __nv_bfloat16* sdO = sV + Tp * LDS;
-  float* sL = reinterpret_cast<float*>(sdO + Tp * LDS);
-  float* sD = sL + Tp;
-  float* sBias = sD + Tp;  // [3][HD] column sums of dq, dk, dv over this (image, head)
+  __nv_bfloat16* sK = sQ + Tk * LDS;
+  __nv_bfloat16* sV = sK + Tk * LDS;
+  __nv_bfloat16* sdO = sV + Tk * LDS;
+  float* sL2 = reinterpret_cast<float*>(sdO + Tk * LDS);  // lse * log2(e)
+  float* sD = sL2 + Tk;
+  float* sBias = sD + Tk;  // [3][HD] column sums of dq, dk, dv over this (image, head)
   for (int i = threadIdx.x; i < 3 * HD; i += blockDim.x) sBias[i] = 0.f;
   const int b = blockIdx.x / heads, h = blockIdx.x - b * heads;
   const int d = heads * HD;
   const __nv_bfloat16* base = qkv + static_cast<long>(b) * T * ldqkv + h * HD;
-  load_head<HD, LDS>(base, ldqkv, T, Tp, sQ);
-  load_head<HD, LDS>(base + d, ldqkv, T, Tp, sK);
-  load_head<HD, LDS>(base + 2 * d, ldqkv, T, Tp, sV);
-  load_head<HD, LDS>(dout + static_cast<long>(b) * T * lddo + h * HD, lddo, T, Tp, sdO);
+  load_head<HD, LDS>(base, ldqkv, T, Tk, sQ);
+  load_head<HD, LDS>(base + d, ldqkv, T, Tk, sK);
+  load_head<HD, LDS>(base + 2 * d, ldqkv, T, Tk, sV);
+  load_head<HD, LDS>(dout + static_cast<long>(b) * T * lddo + h * HD, lddo, T, Tk, sdO);
   // saved log-sum-exp and D = rowsum(dO * O); padded rows get lse = +big so that their P is exactly 0
-  for (int row = threadIdx.x; row < Tp; row += blockDim.x) {
+  for (int row = threadIdx.x; row < Tk; row += blockDim.x) {
     const long i = (static_cast<long>(b) * heads + h) * T + row;
-    sL[row] = row < T ? lse[i] : 1e30f;
+    sL2[row] = row < T ? lse[i] * kLog2e : 1e30f;
     sD[row] = row < T ? delta[i] : 0.f;
   }
   cp_async_wait_all();
@@ -248,8 +387,10 @@ __global__ void attn_bwd_kernel(const __nv_bfloat16* __restrict__ qkv, long ldqk
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int g = lane >> 2, t4 = lane & 3;
-  const int nstrips = (T + 15) / 16, nwarps = blockDim.x >> 5;
+  const int nstrips = Tk / 16, nwarps = blockDim.x >> 5;
   const uint32_t sQa = smem_u32(sQ), sKa = smem_u32(sK), sVa = smem_u32(sV), sdOa = smem_u32(sdO);
+  const int nfull = Tk / 32, rem = Tk - nfull * 32;  // rem in {0, 16}
+  const bool ragged = T != Tk;
 
   // ---------------- phase 1: a warp's 16 queries -> dQ
   for (int strip = warp; strip < nstrips; strip += nwarps) {
@@ -260,54 +401,18 @@ __global__ void attn_bwd_kernel(const __nv_bfloat16* __restrict__ qkv, long ldqk
       ldsm_x4(qf[ks], sQa + 2 * a_off<LDS>(lane, row0, ks * 16));
       ldsm_x4(dof[ks], sdOa + 2 * a_off<LDS>(lane, row0, ks * 16));
     }
-    const float Lr[2] = {sL[row0 + g], sL[row0 + g + 8]};
+    const float Lr2[2] = {sL2[row0 + g], sL2[row0 + g + 8]};
     const float Dr[2] = {sD[row0 + g], sD[row0 + g + 8]};
     float dq[HD / 8][4];
 #pragma unroll
     for (int i = 0; i < HD / 8; ++i) dq[i][0] = dq[i][1] = dq[i][2] = dq[i][3] = 0.f;
-    for (int kc = 0; kc < Tp; kc += 32) {
-      float s[4][4], dp[4][4];
-#pragma unroll
-      for (int i = 0; i < 4; ++i)
-#pragma unroll
-        for (int e = 0; e < 4; ++e) s[i][e] = 0.f, dp[i][e] = 0.f;
-#pragma unroll
-      for (int ks = 0; ks < HD / 16; ++ks) {
-#pragma unroll
-        for (int np = 0; np < 2; ++np) {
-          uint32_t kb[4], vb[4];
-          ldsm_x4(kb, sKa + 2 * bn_off<LDS>(lane, kc + np * 16, ks * 16));
-          mma_bf16(s[2 * np], qf[ks], kb[0], kb[1]);
-          mma_bf16(s[2 * np + 1], qf[ks], kb[2], kb[3]);
-          ldsm_x4(vb, sVa + 2 * bn_off<LDS>(lane, kc + np * 16, ks * 16));
-          mma_bf16(dp[2 * np], dof[ks], vb[0], vb[1]);
-          mma_bf16(dp[2 * np + 1], dof[ks], vb[2], vb[3]);
-        }
-      }
-#pragma unroll
-      for (int nt = 0; nt < 4; ++nt)
-#pragma unroll
-        for (int e = 0; e < 4; ++e) {
-          const int key = kc + nt * 8 + 2 * t4 + (e & 1);
-          const float p = key < T ? exp2f((s[nt][e] - Lr[e >> 1]) * kLog2e) : 0.f;
-          s[nt][e] = p * (dp[nt][e] - Dr[e >> 1]);   // dS
-        }
-#pragma unroll
-      for (int kk = 0; kk < 2; ++kk) {
-        uint32_t a[4];
-        a[0] = pack_bf16(s[2 * kk][0], s[2 * kk][1]);
-        a[1] = pack_bf16(s[2 * kk][2], s[2 * kk][3]);
-        a[2] = pack_bf16(s[2 * kk + 1][0], s[2 * kk + 1][1]);
-        a[3] = pack_bf16(s[2 * kk + 1][2], s[2 * kk + 1][3]);
-#pragma unroll
-        for (int np = 0; np < HD / 16; ++np) {
-          uint32_t kb[4];
-          ldsm_x4_t(kb, sKa + 2 * bt_off<LDS>(lane, kc + kk * 16, np * 16));
-          mma_bf16(dq[2 * np], a, kb[0], kb[1]);
-          mma_bf16(dq[2 * np + 1], a, kb[2], kb[3]);
-        }
-      }
+    for (int c = 0; c < nfull; ++c) {
+      if (rem == 0 && c == nfull - 1 && ragged)
+        bwd_q_chunk<HD, 4, true>(qf, dof, sKa, sVa, c * 32, T, lane, Lr2, Dr, dq);
+      else
+        bwd_q_chunk<HD, 4, false>(qf, dof, sKa, sVa, c * 32, T, lane, Lr2, Dr, dq);
     }
+    if (rem == 16) bwd_q_chunk<HD, 2, true>(qf, dof, sKa, sVa, nfull * 32, T, lane, Lr2, Dr, dq);
 #pragma unroll
     for (int r = 0; r < 2; ++r) {
       const int row = row0 + g + 8 * r;
@@ -349,57 +454,8 @@ __global__ void attn_bwd_kernel(const __nv_bfloat16* __restrict__ qkv, long ldqk
     for (int i = 0; i < HD / 8; ++i)
 #pragma unroll
       for (int e = 0; e < 4; ++e) dk[i][e] = 0.f, dv[i][e] = 0.f;
-    for (int qc = 0; qc < Tp; qc += 32) {
-      float st[4][4], dpt[4][4];
-#pragma unroll
-      for (int i = 0; i < 4; ++i)
-#pragma unroll
-        for (int e = 0; e < 4; ++e) st[i][e] = 0.f, dpt[i][e] = 0.f;
-#pragma unroll
-      for (int ks = 0; ks < HD / 16; ++ks) {
-#pragma unroll
-        for (int np = 0; np < 2; ++np) {
-          uint32_t qb[4], ob[4];
-          ldsm_x4(qb, sQa + 2 * bn_off<LDS>(lane, qc + np * 16, ks * 16));
-          mma_bf16(st[2 * np], kf[ks], qb[0], qb[1]);
-          mma_bf16(st[2 * np + 1], kf[ks], qb[2], qb[3]);
-          ldsm_x4(ob, sdOa + 2 * bn_off<LDS>(lane, qc + np * 16, ks * 16));
-          mma_bf16(dpt[2 * np], vf[ks], ob[0], ob[1]);
-          mma_bf16(dpt[2 * np + 1], vf[ks], ob[2], ob[3]);
-        }
-      }
-      uint32_t pa[2][4], dsa[2][4];
-#pragma unroll
-      for (int nt = 0; nt < 4; ++nt) {
-        const int q0 = qc + nt * 8 + 2 * t4;
-        const float2 L2 = *reinterpret_cast<const float2*>(sL + q0);
-        const float2 D2 = *reinterpret_cast<const float2*>(sD + q0);
-        float p[4], ds[4];
-#pragma unroll
-        for (int e = 0; e < 4; ++e) {
-          const float L = (e & 1) ? L2.y : L2.x, D = (e & 1) ? D2.y : D2.x;
-          p[e] = exp2f((st[nt][e] - L) * kLog2e);
-          ds[e] = p[e] * (dpt[nt][e] - D);
-        }
-        pa[nt >> 1][(nt & 1) * 2 + 0] = pack_bf16(p[0], p[1]);
-        pa[nt >> 1][(nt & 1) * 2 + 1] = pack_bf16(p[2], p[3]);
-        dsa[nt >> 1][(nt & 1) * 2 + 0] = pack_bf16(ds[0], ds[1]);
-        dsa[nt >> 1][(nt & 1) * 2 + 1] = pack_bf16(ds[2], ds[3]);
-      }
-#pragma unroll
-      for (int kk = 0; kk < 2; ++kk) {
-#pragma unroll
-        for (int np = 0; np < HD / 16; ++np) {
-          uint32_t ob[4], qb[4];
-          ldsm_x4_t(ob, sdOa + 2 * bt_off<LDS>(lane, qc + kk * 16, np * 16));
-          mma_bf16(dv[2 * np], pa[kk], ob[0], ob[1]);
-          mma_bf16(dv[2 * np + 1], pa[kk], ob[2], ob[3]);
-          ldsm_x4_t(qb, sQa + 2 * bt_off<LDS>(lane, qc + kk * 16, np * 16));
-          mma_bf16(dk[2 * np], dsa[kk], qb[0], qb[1]);
-          mma_bf16(dk[2 * np + 1], dsa[kk], qb[2], qb[3]);
-        }
-      }
-    }
+    for (int c = 0; c < nfull; ++c) bwd_kv_chunk<HD, 4>(kf, vf, sQa, sdOa, sL2, sD, c * 32, lane, dk, dv);
+    if (rem == 16) bwd_kv_chunk<HD, 2>(kf, vf, sQa, sdOa, sL2, sD, nfull * 32, lane, dk, dv);
 #pragma unroll
     for (int r = 0; r < 2; ++r) {
       const int row = row0 + g + 8 * r;
@@ -444,12 +500,12 @@ __global__ void attn_bwd_kernel(const __nv_bfloat16* __restrict__ qkv, long ldqk
 }
 
 static size_t fwd_smem(int T, int hd) {
-  const int Tp = (T + 63) / 64 * 64, Tq = (T + 15) / 16 * 16;
-  return static_cast<size_t>(2 * Tp + Tq) * (hd + 8) * 2;
+  const int Tk = (T + 15) / 16 * 16;
+  return static_cast<size_t>(3 * Tk) * (hd + 8) * 2;
 }
 static size_t bwd_smem(int T, int hd) {
-  const int Tp = (T + 63) / 64 * 64;
-  return static_cast<size_t>(4 * Tp) * (hd + 8) * 2 + static_cast<size_t>(2 * Tp) * 4 + 3 * hd * 4;
+  const int Tk = (T + 15) / 16 * 16;
+  return static_cast<size_t>(4 * Tk) * (hd + 8) * 2 + static_cast<size_t>(2 * Tk) * 4 + 3 * hd * 4;
 }
 
 // Warps per CTA: one per 16-row strip when the register file allows it, otherwise the strips
@@ -474,6 +530,7 @@ static int launch_fwd(const jm_bf16* qkv, long ldqkv, int batch, int T, int head
   const size_t smem = fwd_smem(T, HD);
   auto kern = attn_fwd_kernel<HD>;
   if (smem > 48 * 1024) JM_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  JM_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
   int warps = 0;
   if (pick_warps(reinterpret_cast<const void*>(kern), T, &warps)) return 1;
   const int threads = warps * 32;
@@ -490,6 +547,7 @@ static int launch_bwd(const jm_bf16* qkv, long ldqkv, const jm_bf16* out, long l
   const size_t smem = bwd_smem(T, HD);
   auto kern = attn_bwd_kernel<HD>;
   if (smem > 48 * 1024) JM_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  JM_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
   int warps = 0;
   if (pick_warps(reinterpret_cast<const void*>(kern), T, &warps)) return 1;
   const int threads = warps * 32;

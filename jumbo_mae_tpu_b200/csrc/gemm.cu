@@ -86,13 +86,17 @@ __device__ __forceinline__ float tanh_fast(float x) {
 // GELU-tanh (src/modeling.py:148) and its derivative with the hardware tanh (abs. error ~5e-4,
 // below the bf16 resolution of the values they are stored in).
 __device__ __forceinline__ float gelu_fast(float x) {
-  const float u = 0.7978845608028654f * (x + 0.044715f * x * x * x);
-  return 0.5f * x * (1.0f + tanh_fast(u));
+  const float x2 = x * x;
+  const float u = x * fmaf(x2, 0.0356774081f, 0.7978845608f);  // sqrt(2/pi) * (x + 0.044715 x^3)
+  const float hx = 0.5f * x;
+  return fmaf(hx, tanh_fast(u), hx);
 }
 __device__ __forceinline__ float gelu_grad_fast(float x) {
   const float x2 = x * x;
-  const float t = tanh_fast(0.7978845608028654f * (x + 0.044715f * x * x2));
-  return 0.5f * (1.0f + t) + 0.5f * x * (1.0f - t * t) * 0.7978845608028654f * (1.0f + 0.134145f * x2);
+  const float t = tanh_fast(x * fmaf(x2, 0.0356774081f, 0.7978845608f));
+  const float du = fmaf(x2, 0.1070322243f, 0.7978845608f);      // d/dx of the tanh argument
+  const float a = (0.5f * x) * fmaf(-t, t, 1.0f);
+  return fmaf(a, du, fmaf(0.5f, t, 0.5f));
 }
 
 // Epilogue specialisations: straight-line code per kind (the generic one keeps every runtime switch).
@@ -116,8 +120,9 @@ struct EpiPrefetch<EPI_GELU_BWD> {
   uint4 v[4];
 };
 
+template <bool FULL>
 __device__ __forceinline__ void store_bf16x8(__nv_bfloat16* p, const float (&v)[8], int ncols) {
-  if (ncols >= 8) {
+  if (FULL || ncols >= 8) {
     *reinterpret_cast<uint4*>(p) =
         make_uint4(pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]), pack_bf16(v[4], v[5]), pack_bf16(v[6], v[7]));
   } else {
@@ -125,29 +130,38 @@ __device__ __forceinline__ void store_bf16x8(__nv_bfloat16* p, const float (&v)[
   }
 }
 
-// Fused epilogue for 8 consecutive columns [col, col+8) of one row (ncols = 8, or 4 at a ragged edge), in the
-// coalesced layout: 4 lanes cover the 32 columns of a chunk row.  sc/bs hold the per-column scale and the
-// pre-scaled bias (v = acc * sc + bs), hoisted per chunk; `affine` says whether they are non-trivial.
-template <int EPI>
+// Fused epilogue for 8 consecutive columns [col, col+8) of one row (FULL: all 8 in range, else ncols is 8
+// or 4 at a ragged edge), in the coalesced layout: 4 lanes cover the 32 columns of a chunk row.  sc/bs hold
+// the per-column scale and the pre-scaled bias (v = acc * sc + bs), hoisted per chunk; `affine` says whether
+// they are non-trivial.  `zero` rows store zeros.  On return v holds the stored values (for the column sums).
+template <int EPI, bool FULL>
 __device__ __forceinline__ void epilogue8(const EpiParams& ep, float (&v)[8], const float (&sc)[8],
                                           const float (&bs)[8], bool affine, long off_row, int row, int col,
                                           int ncols, bool zero, const EpiPrefetch<EPI>& pf, int it) {
+  if (zero) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) v[j] = 0.f;
+    if (ep.out_bf16) store_bf16x8<FULL>(ep.out_bf16 + off_row * ep.ldo_bf16 + col, v, ncols);
+    if (ep.out2_bf16) store_bf16x8<FULL>(ep.out2_bf16 + off_row * ep.ldo2_bf16 + col, v, ncols);
+    if (ep.out_f32 && !ep.accumulate) {
+      float* o = ep.out_f32 + off_row * ep.ldo_f32 + col;
+      *reinterpret_cast<float4*>(o) = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (FULL || ncols >= 8) *reinterpret_cast<float4*>(o + 4) = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    return;
+  }
   if (affine) {
 #pragma unroll
     for (int j = 0; j < 8; ++j) v[j] = fmaf(v[j], sc[j], bs[j]);
   }
   if constexpr (EPI == EPI_BF16) {
-    if (zero) {
-#pragma unroll
-      for (int j = 0; j < 8; ++j) v[j] = 0.f;
-    }
-    store_bf16x8(ep.out_bf16 + off_row * ep.ldo_bf16 + col, v, ncols);
+    store_bf16x8<FULL>(ep.out_bf16 + off_row * ep.ldo_bf16 + col, v, ncols);
   } else if constexpr (EPI == EPI_F32) {
-    if (ep.pe && !zero) {
+    if (ep.pe) {
       const float* pe = ep.pe + static_cast<long>(ep.pe_idx[row % ep.row_period - ep.row_skip]) * ep.ldpe + col;
       const float4 a = *reinterpret_cast<const float4*>(pe);
       v[0] += a.x, v[1] += a.y, v[2] += a.z, v[3] += a.w;
-      if (ncols >= 8) {
+      if (FULL || ncols >= 8) {
         const float4 b = *reinterpret_cast<const float4*>(pe + 4);
         v[4] += b.x, v[5] += b.y, v[6] += b.z, v[7] += b.w;
       }
@@ -155,22 +169,15 @@ __device__ __forceinline__ void epilogue8(const EpiParams& ep, float (&v)[8], co
     const float4 r0 = pf.v[it][0], r1 = pf.v[it][1];
     v[0] += r0.x, v[1] += r0.y, v[2] += r0.z, v[3] += r0.w;
     v[4] += r1.x, v[5] += r1.y, v[6] += r1.z, v[7] += r1.w;
-    if (zero) {
-#pragma unroll
-      for (int j = 0; j < 8; ++j) v[j] = 0.f;
-    }
     float* o = ep.out_f32 + off_row * ep.ldo_f32 + col;
     store_f32x4(o, make_float4(v[0], v[1], v[2], v[3]), ep.accumulate != 0);
-    if (ncols >= 8) store_f32x4(o + 4, make_float4(v[4], v[5], v[6], v[7]), ep.accumulate != 0);
+    if (FULL || ncols >= 8) store_f32x4(o + 4, make_float4(v[4], v[5], v[6], v[7]), ep.accumulate != 0);
   } else if constexpr (EPI == EPI_GELU_FWD) {
     float g[8];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      if (zero) v[j] = 0.f;
-      g[j] = gelu_fast(v[j]);
-    }
-    if (ep.out_bf16) store_bf16x8(ep.out_bf16 + off_row * ep.ldo_bf16 + col, v, ncols);
-    if (ep.out2_bf16) store_bf16x8(ep.out2_bf16 + off_row * ep.ldo2_bf16 + col, g, ncols);
+    for (int j = 0; j < 8; ++j) g[j] = gelu_fast(v[j]);
+    store_bf16x8<FULL>(ep.out_bf16 + off_row * ep.ldo_bf16 + col, v, ncols);
+    store_bf16x8<FULL>(ep.out2_bf16 + off_row * ep.ldo2_bf16 + col, g, ncols);
   } else if constexpr (EPI == EPI_GELU_BWD) {
     const uint4 u = pf.v[it];
     const uint32_t w[4] = {u.x, u.y, u.z, u.w};
@@ -180,21 +187,14 @@ __device__ __forceinline__ void epilogue8(const EpiParams& ep, float (&v)[8], co
       v[2 * j] *= gelu_grad_fast(a.x);
       v[2 * j + 1] *= gelu_grad_fast(a.y);
     }
-    if (zero) {
-#pragma unroll
-      for (int j = 0; j < 8; ++j) v[j] = 0.f;
-    }
-    store_bf16x8(ep.out_bf16 + off_row * ep.ldo_bf16 + col, v, ncols);
+    store_bf16x8<FULL>(ep.out_bf16 + off_row * ep.ldo_bf16 + col, v, ncols);
   } else {
     if (ep.act == 1) {
       float g[8];
 #pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        if (zero) v[j] = 0.f;
-        g[j] = gelu_fast(v[j]);
-      }
-      if (ep.out_bf16) store_bf16x8(ep.out_bf16 + off_row * ep.ldo_bf16 + col, v, ncols);
-      if (ep.out2_bf16) store_bf16x8(ep.out2_bf16 + off_row * ep.ldo2_bf16 + col, g, ncols);
+      for (int j = 0; j < 8; ++j) g[j] = gelu_fast(v[j]);
+      if (ep.out_bf16) store_bf16x8<FULL>(ep.out_bf16 + off_row * ep.ldo_bf16 + col, v, ncols);
+      if (ep.out2_bf16) store_bf16x8<FULL>(ep.out2_bf16 + off_row * ep.ldo2_bf16 + col, g, ncols);
       return;
     }
 #pragma unroll
@@ -208,7 +208,7 @@ __device__ __forceinline__ void epilogue8(const EpiParams& ep, float (&v)[8], co
         x[0] *= gelu_grad_fast(a.x), x[1] *= gelu_grad_fast(a.y);
         x[2] *= gelu_grad_fast(b.x), x[3] *= gelu_grad_fast(b.y);
       }
-      if (ep.pe && !zero) {
+      if (ep.pe) {
         const float4 b = *reinterpret_cast<const float4*>(
             ep.pe + static_cast<long>(ep.pe_idx[row % ep.row_period - ep.row_skip]) * ep.ldpe + c4);
         x[0] += b.x, x[1] += b.y, x[2] += b.z, x[3] += b.w;
@@ -217,11 +217,10 @@ __device__ __forceinline__ void epilogue8(const EpiParams& ep, float (&v)[8], co
         const float4 b = *reinterpret_cast<const float4*>(ep.residual + off_row * ep.ldr + c4);
         x[0] += b.x, x[1] += b.y, x[2] += b.z, x[3] += b.w;
       }
-      if (zero) x[0] = x[1] = x[2] = x[3] = 0.f;
       if (ep.out_f32)
         store_f32x4(ep.out_f32 + off_row * ep.ldo_f32 + c4, make_float4(x[0], x[1], x[2], x[3]), ep.accumulate != 0);
     }
-    if (ep.out_bf16) store_bf16x8(ep.out_bf16 + off_row * ep.ldo_bf16 + col, v, ncols);
+    if (ep.out_bf16) store_bf16x8<FULL>(ep.out_bf16 + off_row * ep.ldo_bf16 + col, v, ncols);
   }
 }
 
@@ -335,10 +334,11 @@ __device__ __forceinline__ void epilogue_role(const EpiParams& ep, const GemmSha
       else epi_prefetch<EPI, BN>(pf, ep, sh, t + static_cast<int>(gridDim.x), 0, q, half, lane, total_tiles);
       const int col = col0 + cu * 8;
       const int ncols = sh.N - col;
+      constexpr bool kColsum = (EPI == EPI_GELU_BWD || EPI == EPI_GENERIC);
       float cs[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
       if (live && ncols >= 4) {
         float sc[8], bs[8];
-        const bool scaled = col < ep.col_scale_n;            // warp-uniform per chunk up to the boundary
+        const bool scaled = col < ep.col_scale_n;
         const bool affine = ep.bias != nullptr || col0 < ep.col_scale_n;
         if (affine) {
 #pragma unroll
@@ -355,6 +355,7 @@ __device__ __forceinline__ void epilogue_role(const EpiParams& ep, const GemmSha
             }
           }
         }
+        const bool full = col0 + 32 <= sh.N;  // warp-uniform: the whole chunk is inside the matrix
 #pragma unroll
         for (int it = 0; it < 4; ++it) {
           const int rloc = it * 8 + rsub;
@@ -369,24 +370,32 @@ __device__ __forceinline__ void epilogue_role(const EpiParams& ep, const GemmSha
                        : "r"(a1));
           if (store_mask & (1u << it)) {
             const int row = row0 + it * 8;
-            epilogue8<EPI>(ep, v, sc, bs, affine, static_cast<long>(row), row, col, ncols,
-                           (zero_mask >> it) & 1u, cur, it);
+            if (full)
+              epilogue8<EPI, true>(ep, v, sc, bs, affine, static_cast<long>(row), row, col, 8,
+                                   (zero_mask >> it) & 1u, cur, it);
+            else
+              epilogue8<EPI, false>(ep, v, sc, bs, affine, static_cast<long>(row), row, col, ncols,
+                                    (zero_mask >> it) & 1u, cur, it);
+            if constexpr (kColsum) {
 #pragma unroll
-            for (int j = 0; j < 8; ++j) cs[j] += v[j];
+              for (int j = 0; j < 8; ++j) cs[j] += v[j];
+            }
           }
         }
       }
-      if (ep.colsum != nullptr && live) {  // warp-uniform: fold the 8 row-lanes, one atomic per column
+      if constexpr (kColsum) {
+        if (ep.colsum != nullptr && live) {  // warp-uniform: fold the 8 row-lanes, one atomic per column
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          cs[j] += __shfl_xor_sync(0xffffffffu, cs[j], 4);
-          cs[j] += __shfl_xor_sync(0xffffffffu, cs[j], 8);
-          cs[j] += __shfl_xor_sync(0xffffffffu, cs[j], 16);
-        }
-        if (rsub == 0 && ncols >= 4) {
+          for (int j = 0; j < 8; ++j) {
+            cs[j] += __shfl_xor_sync(0xffffffffu, cs[j], 4);
+            cs[j] += __shfl_xor_sync(0xffffffffu, cs[j], 8);
+            cs[j] += __shfl_xor_sync(0xffffffffu, cs[j], 16);
+          }
+          if (rsub == 0 && ncols >= 4) {
 #pragma unroll
-          for (int j = 0; j < 8; ++j)
-            if (j < ncols) atomicAdd(ep.colsum + col + j, cs[j]);
+            for (int j = 0; j < 8; ++j)
+              if (j < ncols) atomicAdd(ep.colsum + col + j, cs[j]);
+          }
         }
       }
       __syncwarp();
@@ -687,10 +696,10 @@ extern "C" int jm_gemm(const jm_gemm_args* a, void* stream_) {
   int epi = EPI_GENERIC;
   const bool only_bf16 = ep.out_bf16 && !ep.out_f32 && !ep.out2_bf16;
   const bool only_f32 = ep.out_f32 && !ep.out_bf16 && !ep.out2_bf16;
-  if (ep.act == 1 && !ep.out_f32 && !ep.residual && !ep.pe) epi = EPI_GELU_FWD;
+  if (ep.act == 1 && ep.out_bf16 && ep.out2_bf16 && !ep.out_f32 && !ep.residual && !ep.pe) epi = EPI_GELU_FWD;
   else if (ep.act == 2 && only_bf16 && !ep.residual && !ep.pe) epi = EPI_GELU_BWD;
-  else if (ep.act == 0 && only_f32) epi = EPI_F32;
-  else if (ep.act == 0 && only_bf16 && !ep.residual && !ep.pe) epi = EPI_BF16;
+  else if (ep.act == 0 && only_f32 && !ep.colsum) epi = EPI_F32;
+  else if (ep.act == 0 && only_bf16 && !ep.residual && !ep.pe && !ep.colsum) epi = EPI_BF16;
   if (bn == 256) return dispatch_major<256>(amn, bmn, epi, tmA, tmB, sh, ep, grid, stream);
   if (bn == 128) return dispatch_major<128>(amn, bmn, epi, tmA, tmB, sh, ep, grid, stream);
   return dispatch_major<64>(amn, bmn, epi, tmA, tmB, sh, ep, grid, stream);
