@@ -25,9 +25,9 @@ constexpr int BM = 128;
 constexpr int BK = 64;  // 64 bf16 = 128 bytes = one SWIZZLE_128B row
 constexpr int UMMA_K = 16;
 constexpr int kEpiWarp0 = 4;
-constexpr int kEpiWarps = 8;  // two per TMEM lane quarter, each takes half of the tile's columns
+constexpr int kEpiWarps = 16;  // four per TMEM lane quarter, each takes a quarter of the tile's columns
 constexpr int kGemmThreads = (kEpiWarp0 + kEpiWarps) * 32;
-constexpr int kStageRowBytes = 128;                    // 32 f32 columns
+constexpr int kStageRowBytes = 64;                     // 16 f32 columns
 constexpr int kStageBytesPerWarp = 32 * kStageRowBytes;  // 32 rows
 
 struct GemmShape {
@@ -108,16 +108,27 @@ enum : int {
   EPI_GENERIC = 4,
 };
 
+// 32 lanes x 16 consecutive f32 columns: thread t of the warp receives lane (base+t).
+__device__ __forceinline__ void tmem_ld_32x16(uint32_t taddr, uint32_t (&r)[16]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+        "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+      : "r"(taddr)
+      : "memory");
+}
+
 template <int EPI>
-struct EpiPrefetch {  // global operand of one lane for its 4 rows x 8 columns of a 32x32 chunk
+struct EpiPrefetch {  // global operand of one lane for its 2 rows x 8 columns of a 32x16 sub-chunk
 };
 template <>
 struct EpiPrefetch<EPI_F32> {
-  float4 v[4][2];
+  float4 v[2][2];
 };
 template <>
 struct EpiPrefetch<EPI_GELU_BWD> {
-  uint4 v[4];
+  uint4 v[2];
 };
 
 template <bool FULL>
@@ -224,24 +235,19 @@ __device__ __forceinline__ void epilogue8(const EpiParams& ep, float (&v)[8], co
   }
 }
 
-// Issues the global loads one lane needs for chunk (tile t, chunk c) of its warp: the f32 residual
-// (EPI_F32) or the bf16 pre-activation (EPI_GELU_BWD).  Called one chunk ahead so that the HBM
-// latency hides behind the previous chunk's work / the MMA main loop.
-template <int EPI, int BN>
-__device__ __forceinline__ void epi_prefetch(EpiPrefetch<EPI>& pf, const EpiParams& ep, const GemmShape& sh, int t,
-                                             int c, int q, int half, int lane, int total_tiles) {
+// Issues the global loads one lane needs for one 32x16 sub-chunk: the f32 residual (EPI_F32) or the
+// bf16 pre-activation (EPI_GELU_BWD).  Issued before the TMEM load / shared-memory transpose of the
+// sub-chunk (and, for a tile's first sub-chunk, before waiting for the accumulator), so that the HBM
+// latency overlaps with them and with the other epilogue warps of the scheduler.
+template <int EPI>
+__device__ __forceinline__ void epi_prefetch(EpiPrefetch<EPI>& pf, const EpiParams& ep, const GemmShape& sh,
+                                             int row0, int col) {
   if constexpr (EPI == EPI_F32 || EPI == EPI_GELU_BWD) {
-    const int tiles_mn = sh.num_m * sh.num_n;
-    const bool tile_ok = t < total_tiles;
-    const int rem = tile_ok ? t % tiles_mn : 0;
-    const int m_blk = rem / sh.num_n, n_blk = rem - m_blk * sh.num_n;
-    const int col = n_blk * BN + half * (BN / 2) + c * 32 + (lane & 3) * 8;
-    const int row0 = m_blk * BM + q * 32 + (lane >> 2);
     const int ncols = sh.N - col;
 #pragma unroll
-    for (int it = 0; it < 4; ++it) {
-      const int row = row0 + it * 8;
-      const bool ok = tile_ok && ncols >= 4 && row < sh.M;
+    for (int it = 0; it < 2; ++it) {
+      const int row = row0 + it * 16;
+      const bool ok = ncols >= 4 && row < sh.M;
       if constexpr (EPI == EPI_F32) {
         pf.v[it][0] = make_float4(0.f, 0.f, 0.f, 0.f);
         pf.v[it][1] = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -266,37 +272,38 @@ __device__ __forceinline__ void epi_prefetch(EpiPrefetch<EPI>& pf, const EpiPara
   }
 }
 
-// Epilogue warps.  TMEM hands each thread one accumulator ROW (32 consecutive columns); global memory
-// wants a warp to write consecutive COLUMNS.  Each warp transposes 32x32 f32 chunks through a private,
-// XOR-swizzled 4 KB staging tile (conflict-free both ways), then runs the fused epilogue with 4 lanes
-// covering the 128 contiguous bytes of a chunk row (8 columns per lane, 8 rows per warp instruction):
-// all global loads and stores are coalesced 16-byte accesses.
+// Epilogue warps (16: four per TMEM lane quarter, each draining a quarter of the tile's columns).
+// TMEM hands each thread one accumulator ROW; global memory wants lanes on consecutive COLUMNS.  Each warp
+// transposes 32x16 f32 sub-chunks through a private, XOR-swizzled 2 KB staging tile (conflict-free both
+// ways), then runs the fused epilogue with 2 lanes covering the 64 contiguous bytes of a sub-chunk row
+// (8 columns per lane, 16 rows per warp instruction): every global access is a full 16-byte vector.
+// Sixteen warps, not four or eight: one warp retires a long dependent instruction stream per sub-chunk at
+// well under one instruction per cycle, so the drain rate scales with the number of warps per scheduler.
 template <int EPI, int BN>
 __device__ __forceinline__ void epilogue_role(const EpiParams& ep, const GemmShape& sh, uint8_t* sEpi,
                                               uint64_t* tfull, uint64_t* tempty, uint32_t tmem_base, int warp,
                                               int lane, int total_tiles) {
   const int e = warp - kEpiWarp0;
   const int q = e & 3;      // TMEM lane quarter == warp % 4
-  const int half = e >> 2;  // which half of the tile's columns
-  constexpr int HALF_N = BN / 2;
-  constexpr int NCHUNK = HALF_N / 32;
+  const int part = e >> 2;  // which quarter of the tile's columns
+  constexpr int PART_N = BN / 4;
+  constexpr int NSUB = PART_N / 16;
+  constexpr bool kColsum = (EPI == EPI_GELU_BWD || EPI == EPI_GENERIC);
   const uint32_t stage_addr = smem_u32(sEpi + e * kStageBytesPerWarp);
-  const int rsub = lane >> 2, cu = lane & 3;
+  const int rsub = lane >> 1, cu = lane & 1;
   const int tiles_mn = sh.num_m * sh.num_n;
-  EpiPrefetch<EPI> pf;
-  epi_prefetch<EPI, BN>(pf, ep, sh, blockIdx.x, 0, q, half, lane, total_tiles);
   int iter = 0;
   for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++iter) {
     const int rem = t % tiles_mn;
     const int m_blk = rem / sh.num_n, n_blk = rem - m_blk * sh.num_n;
     const int acc = iter & 1;
     const uint32_t acc_phase = (iter >> 1) & 1;
-    // this lane's 4 rows are the same for every chunk of the tile: resolve the row predicates once
+    // this lane's 2 rows are the same for every sub-chunk of the tile: resolve the row predicates once
     const int row0 = m_blk * BM + q * 32 + rsub;
     uint32_t store_mask = 0, zero_mask = 0;
 #pragma unroll
-    for (int it = 0; it < 4; ++it) {
-      const int row = row0 + it * 8;
+    for (int it = 0; it < 2; ++it) {
+      const int row = row0 + it * 16;
       bool st = row < sh.M, zr = false;
       if (ep.row_period > 0 && (row % ep.row_period) < ep.row_skip) {
         if (ep.row_mask_mode == 2) st = false;
@@ -305,36 +312,37 @@ __device__ __forceinline__ void epilogue_role(const EpiParams& ep, const GemmSha
       store_mask |= (st ? 1u : 0u) << it;
       zero_mask |= (zr ? 1u : 0u) << it;
     }
+    const int colp = n_blk * BN + part * PART_N;  // first column of this warp's part
+    EpiPrefetch<EPI> pf;
+    epi_prefetch<EPI>(pf, ep, sh, row0, colp + cu * 8);
     mbar_wait(&tfull[acc], acc_phase);
     tc_fence_after();
-    const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * BN + half * HALF_N;
+    const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * BN + part * PART_N;
 #pragma unroll
-    for (int c = 0; c < NCHUNK; ++c) {
-      const int col0 = n_blk * BN + half * HALF_N + c * 32;
+    for (int c = 0; c < NSUB; ++c) {
+      const int col0 = colp + c * 16;
       const bool live = col0 < sh.N;  // warp-uniform
       if (live) {
-        uint32_t r[32];
-        tmem_ld_32x32(t_addr + c * 32, r);
+        uint32_t r[16];
+        tmem_ld_32x16(t_addr + c * 16, r);
         tmem_ld_wait();
 #pragma unroll
-        for (int u = 0; u < 8; ++u) {
-          const uint32_t a = stage_addr + lane * kStageRowBytes + ((u ^ (lane & 7)) << 4);
+        for (int u = 0; u < 4; ++u) {
+          const uint32_t a = stage_addr + lane * kStageRowBytes + ((u ^ ((lane >> 1) & 3)) << 4);
           asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(r[4 * u]), "r"(r[4 * u + 1]),
                        "r"(r[4 * u + 2]), "r"(r[4 * u + 3])
                        : "memory");
         }
       }
-      if (c == NCHUNK - 1) {  // accumulator fully drained: hand the TMEM buffer back to the MMA warp
+      if (c == NSUB - 1) {  // accumulator fully drained: hand the TMEM buffer back to the MMA warp
         tc_fence_before();
         mbar_arrive(&tempty[acc]);
       }
       __syncwarp();
       const EpiPrefetch<EPI> cur = pf;
-      if (c + 1 < NCHUNK) epi_prefetch<EPI, BN>(pf, ep, sh, t, c + 1, q, half, lane, total_tiles);
-      else epi_prefetch<EPI, BN>(pf, ep, sh, t + static_cast<int>(gridDim.x), 0, q, half, lane, total_tiles);
+      if (c + 1 < NSUB) epi_prefetch<EPI>(pf, ep, sh, row0, col0 + 16 + cu * 8);
       const int col = col0 + cu * 8;
       const int ncols = sh.N - col;
-      constexpr bool kColsum = (EPI == EPI_GELU_BWD || EPI == EPI_GENERIC);
       float cs[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
       if (live && ncols >= 4) {
         float sc[8], bs[8];
@@ -355,13 +363,14 @@ __device__ __forceinline__ void epilogue_role(const EpiParams& ep, const GemmSha
             }
           }
         }
-        const bool full = col0 + 32 <= sh.N;  // warp-uniform: the whole chunk is inside the matrix
+        const bool full = col0 + 16 <= sh.N;  // warp-uniform: the whole sub-chunk is inside the matrix
 #pragma unroll
-        for (int it = 0; it < 4; ++it) {
-          const int rloc = it * 8 + rsub;
+        for (int it = 0; it < 2; ++it) {
+          const int rloc = it * 16 + rsub;
           float v[8];
-          const uint32_t a0 = stage_addr + rloc * kStageRowBytes + (((2 * cu) ^ (rloc & 7)) << 4);
-          const uint32_t a1 = stage_addr + rloc * kStageRowBytes + (((2 * cu + 1) ^ (rloc & 7)) << 4);
+          const uint32_t sw = (rloc >> 1) & 3;
+          const uint32_t a0 = stage_addr + rloc * kStageRowBytes + (((2 * cu) ^ sw) << 4);
+          const uint32_t a1 = stage_addr + rloc * kStageRowBytes + (((2 * cu + 1) ^ sw) << 4);
           asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
                        : "=f"(v[0]), "=f"(v[1]), "=f"(v[2]), "=f"(v[3])
                        : "r"(a0));
@@ -369,7 +378,7 @@ __device__ __forceinline__ void epilogue_role(const EpiParams& ep, const GemmSha
                        : "=f"(v[4]), "=f"(v[5]), "=f"(v[6]), "=f"(v[7])
                        : "r"(a1));
           if (store_mask & (1u << it)) {
-            const int row = row0 + it * 8;
+            const int row = row0 + it * 16;
             if (full)
               epilogue8<EPI, true>(ep, v, sc, bs, affine, static_cast<long>(row), row, col, 8,
                                    (zero_mask >> it) & 1u, cur, it);
@@ -384,9 +393,10 @@ __device__ __forceinline__ void epilogue_role(const EpiParams& ep, const GemmSha
         }
       }
       if constexpr (kColsum) {
-        if (ep.colsum != nullptr && live) {  // warp-uniform: fold the 8 row-lanes, one atomic per column
+        if (ep.colsum != nullptr && live) {  // warp-uniform: fold the 16 row-lanes, one atomic per column
 #pragma unroll
           for (int j = 0; j < 8; ++j) {
+            cs[j] += __shfl_xor_sync(0xffffffffu, cs[j], 2);
             cs[j] += __shfl_xor_sync(0xffffffffu, cs[j], 4);
             cs[j] += __shfl_xor_sync(0xffffffffu, cs[j], 8);
             cs[j] += __shfl_xor_sync(0xffffffffu, cs[j], 16);
