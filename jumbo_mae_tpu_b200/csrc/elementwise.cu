@@ -224,7 +224,7 @@ layernorm_fwd_kernel(const float* __restrict__ x, long ldx, int rows, int D, con
   }
 }
 
-constexpr int kLnBwdMaxBlocks = 444;  // 3 x 148
+constexpr int kLnBwdMaxBlocks = 444;  // 3 x 148 (3 resident CTAs per SM)
 
 // dx = dres + rstd * (dy*g - mean(dy*g) - xhat * mean(dy*g*xhat)); per-block dgamma/dbeta partials
 // are accumulated in shared memory and written to the workspace [block][2][D].
@@ -288,59 +288,71 @@ layernorm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, long lddy, const floa
   for (int c = threadIdx.x; c < 3 * D; c += blockDim.x) out[c] = s_acc[c];
 }
 
-// Fast path for dim <= NV*128: the row and the per-lane dgamma/dbeta partial sums stay in
-// registers (one global read of dy and x per row); shared memory is touched once per block.
+// Fast path for dim <= NV*128.  One warp per row, the row (dy, x-hat) stays in registers between the two
+// passes (one global read per operand).  The dgamma / dbeta / column-sum partials live in a per-warp
+// private shared-memory accumulator that each lane updates with plain float4 read-modify-writes on the
+// columns it owns (no atomics, no conflicts): keeping them in registers costs 3*NV*4 registers per
+// thread and leaves one resident CTA per SM, which starves a kernel that is pure HBM streaming.
+constexpr int kLnBwdWarps = 4;
+
 template <int NV>
-__global__ void __launch_bounds__(kLnWarps * 32)
+__global__ void __launch_bounds__(kLnBwdWarps * 32, 3)
 layernorm_bwd_reg_kernel(const __nv_bfloat16* __restrict__ dy, long lddy, const float* __restrict__ x, long ldx,
                          const float* __restrict__ mean, const float* __restrict__ rstd,
                          const float* __restrict__ gamma, int rows, int D, const float* __restrict__ dres,
                          long lddres, float* __restrict__ dx, long lddx, __nv_bfloat16* __restrict__ dxb, long lddxb,
                          int row_period, int row_skip, float* __restrict__ ws, int want_dcol, int dcol_period,
                          int dcol_skip) {
-  extern __shared__ float s_acc[];  // [3][D]: dgamma, dbeta, column sums of dx
-  for (int c = threadIdx.x; c < 3 * D; c += blockDim.x) s_acc[c] = 0.f;
-  __syncthreads();
+  extern __shared__ __align__(16) float s_acc[];  // [warps][3][D]: dgamma, dbeta, column sums of dx
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  float gm[NV][4], ag[NV][4], ab[NV][4], ac[NV][4];
-#pragma unroll
-  for (int k = 0; k < NV; ++k) {
-    const int c = lane * 4 + k * 128;
-    float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (c < D) g = *reinterpret_cast<const float4*>(gamma + c);
-    gm[k][0] = g.x, gm[k][1] = g.y, gm[k][2] = g.z, gm[k][3] = g.w;
-#pragma unroll
-    for (int j = 0; j < 4; ++j) ag[k][j] = 0.f, ab[k][j] = 0.f, ac[k][j] = 0.f;
-  }
-  for (long row = static_cast<long>(blockIdx.x) * kLnWarps + warp; row < rows;
-       row += static_cast<long>(gridDim.x) * kLnWarps) {
+  float* my = s_acc + static_cast<long>(warp) * 3 * D;
+  for (int c = lane; c < 3 * D; c += 32) my[c] = 0.f;
+  __syncwarp();
+  for (long row = static_cast<long>(blockIdx.x) * kLnBwdWarps + warp; row < rows;
+       row += static_cast<long>(gridDim.x) * kLnBwdWarps) {
     if (row_period > 0 && (row % row_period) < row_skip) continue;
     const bool col_row = want_dcol && !(dcol_period > 0 && (row % dcol_period) < dcol_skip);
     const __nv_bfloat16* dyr = dy + row * lddy;
     const float* xr = x + row * ldx;
     const float mu = mean[row], rs = rstd[row];
     float d[NV][4], xh[NV][4];
+    float4 rres[NV];  // residual gradient, requested together with dy / x so that a row costs ONE memory round trip
     float c1 = 0.f, c2 = 0.f;
+#pragma unroll
+    for (int k = 0; k < NV; ++k) {
+      const int c = lane * 4 + k * 128;
+      rres[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (dres && c < D) rres[k] = *reinterpret_cast<const float4*>(dres + row * lddres + c);
+    }
 #pragma unroll
     for (int k = 0; k < NV; ++k) {
       const int c = lane * 4 + k * 128;
       uint2 u = make_uint2(0u, 0u);
       float4 xv = make_float4(mu, mu, mu, mu);
+      float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
       if (c < D) {
         u = *reinterpret_cast<const uint2*>(dyr + c);
         xv = *reinterpret_cast<const float4*>(xr + c);
+        g = *reinterpret_cast<const float4*>(gamma + c);
       }
       const float2 d01 = unpack_bf16(u.x), d23 = unpack_bf16(u.y);
       d[k][0] = d01.x, d[k][1] = d01.y, d[k][2] = d23.x, d[k][3] = d23.y;
       xh[k][0] = (xv.x - mu) * rs, xh[k][1] = (xv.y - mu) * rs, xh[k][2] = (xv.z - mu) * rs,
       xh[k][3] = (xv.w - mu) * rs;
+      const float gg[4] = {g.x, g.y, g.z, g.w};
+      if (c < D) {  // parameter-gradient partials: this lane owns these columns of the warp's accumulator
+        float4 ag = *reinterpret_cast<float4*>(my + c);
+        float4 ab = *reinterpret_cast<float4*>(my + D + c);
+        ag.x += d[k][0] * xh[k][0], ag.y += d[k][1] * xh[k][1], ag.z += d[k][2] * xh[k][2], ag.w += d[k][3] * xh[k][3];
+        ab.x += d[k][0], ab.y += d[k][1], ab.z += d[k][2], ab.w += d[k][3];
+        *reinterpret_cast<float4*>(my + c) = ag;
+        *reinterpret_cast<float4*>(my + D + c) = ab;
+      }
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
-        const float dg = d[k][j] * gm[k][j];
-        c1 += dg;
-        c2 += dg * xh[k][j];
-        ag[k][j] += d[k][j] * xh[k][j];
-        ab[k][j] += d[k][j];
+        d[k][j] *= gg[j];  // from here on d holds dy * gamma
+        c1 += d[k][j];
+        c2 += d[k][j] * xh[k][j];
       }
     }
     c1 = warp_sum(c1) / D, c2 = warp_sum(c2) / D;
@@ -350,38 +362,29 @@ layernorm_bwd_reg_kernel(const __nv_bfloat16* __restrict__ dy, long lddy, const 
       if (c < D) {
         float o[4];
 #pragma unroll
-        for (int j = 0; j < 4; ++j) o[j] = rs * (d[k][j] * gm[k][j] - c1 - xh[k][j] * c2);
-        if (dres) {
-          const float4 r = *reinterpret_cast<const float4*>(dres + row * lddres + c);
-          o[0] += r.x, o[1] += r.y, o[2] += r.z, o[3] += r.w;
-        }
+        for (int j = 0; j < 4; ++j) o[j] = rs * (d[k][j] - c1 - xh[k][j] * c2);
+        o[0] += rres[k].x, o[1] += rres[k].y, o[2] += rres[k].z, o[3] += rres[k].w;
         if (dx) *reinterpret_cast<float4*>(dx + row * lddx + c) = make_float4(o[0], o[1], o[2], o[3]);
         if (dxb) {
           uint2 w = {pack_bf16(o[0], o[1]), pack_bf16(o[2], o[3])};
           *reinterpret_cast<uint2*>(dxb + row * lddxb + c) = w;
         }
         if (col_row) {
-#pragma unroll
-          for (int j = 0; j < 4; ++j) ac[k][j] += o[j];
+          float4 ac = *reinterpret_cast<float4*>(my + 2 * D + c);
+          ac.x += o[0], ac.y += o[1], ac.z += o[2], ac.w += o[3];
+          *reinterpret_cast<float4*>(my + 2 * D + c) = ac;
         }
-      }
-    }
-  }
-#pragma unroll
-  for (int k = 0; k < NV; ++k) {
-    const int c = lane * 4 + k * 128;
-    if (c < D) {
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        atomicAdd(&s_acc[c + j], ag[k][j]);
-        atomicAdd(&s_acc[D + c + j], ab[k][j]);
-        if (want_dcol) atomicAdd(&s_acc[2 * D + c + j], ac[k][j]);
       }
     }
   }
   __syncthreads();
   float* out = ws + static_cast<long>(blockIdx.x) * 3 * D;
-  for (int c = threadIdx.x; c < 3 * D; c += blockDim.x) out[c] = s_acc[c];
+  for (int c = threadIdx.x; c < 3 * D; c += blockDim.x) {
+    float t = 0.f;
+#pragma unroll
+    for (int w = 0; w < kLnBwdWarps; ++w) t += s_acc[static_cast<long>(w) * 3 * D + c];
+    out[c] = t;
+  }
 }
 
 // out[c] += sum over blocks of ws[block][c]; 32 columns x 8 block-groups per CTA
@@ -691,7 +694,7 @@ extern "C" int jm_layernorm_fwd(const float* x, long ldx, int rows, int dim, con
 }
 
 static int ln_bwd_blocks(int rows) {
-  const int need = (rows + kLnWarps - 1) / kLnWarps;
+  const int need = (rows + 3) / 4;  // 4 rows (warps) per CTA in the register kernel, 8 in the fallback
   return need < kLnBwdMaxBlocks ? need : kLnBwdMaxBlocks;
 }
 
@@ -710,7 +713,7 @@ extern "C" int jm_layernorm_bwd(const jm_bf16* dy, long lddy, const float* x, lo
   if (rows == 0) return 0;
   JM_CHECK(workspace && workspace_bytes >= jm_layernorm_bwd_workspace(rows, dim),
            "jm_layernorm_bwd: workspace too small");
-  const int grid = ln_bwd_blocks(rows);
+  int grid = ln_bwd_blocks(rows);
   const size_t smem = static_cast<size_t>(3) * dim * sizeof(float);
   if (smem > 48 * 1024) {
     JM_CUDA(cudaFuncSetAttribute(layernorm_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
@@ -720,13 +723,23 @@ extern "C" int jm_layernorm_bwd(const jm_bf16* dy, long lddy, const float* x, lo
   reinterpret_cast<const __nv_bfloat16*>(dy), lddy, x, ldx, mean, rstd, gamma, rows, dim, dres, lddres, dx, lddx, \
       reinterpret_cast<__nv_bfloat16*>(dx_bf16), lddxb, row_period, row_skip, static_cast<float*>(workspace), \
       want_dcol, dcol_period, dcol_skip
-  if (dim <= 128) layernorm_bwd_reg_kernel<1><<<grid, kLnWarps * 32, smem, STREAM>>>(JM_LN_BWD_ARGS);
-  else if (dim <= 256) layernorm_bwd_reg_kernel<2><<<grid, kLnWarps * 32, smem, STREAM>>>(JM_LN_BWD_ARGS);
-  else if (dim <= 512) layernorm_bwd_reg_kernel<4><<<grid, kLnWarps * 32, smem, STREAM>>>(JM_LN_BWD_ARGS);
-  else if (dim <= 768) layernorm_bwd_reg_kernel<6><<<grid, kLnWarps * 32, smem, STREAM>>>(JM_LN_BWD_ARGS);
-  else if (dim <= 1024) layernorm_bwd_reg_kernel<8><<<grid, kLnWarps * 32, smem, STREAM>>>(JM_LN_BWD_ARGS);
-  else if (dim <= 1280) layernorm_bwd_reg_kernel<10><<<grid, kLnWarps * 32, smem, STREAM>>>(JM_LN_BWD_ARGS);
-  else layernorm_bwd_kernel<<<grid, kLnWarps * 32, smem, STREAM>>>(JM_LN_BWD_ARGS);
+  const size_t smem_reg = static_cast<size_t>(kLnBwdWarps) * 3 * dim * sizeof(float);
+  const int tr = kLnBwdWarps * 32;
+  if (dim <= 128) layernorm_bwd_reg_kernel<1><<<grid, tr, smem_reg, STREAM>>>(JM_LN_BWD_ARGS);
+  else if (dim <= 256) layernorm_bwd_reg_kernel<2><<<grid, tr, smem_reg, STREAM>>>(JM_LN_BWD_ARGS);
+  else if (dim <= 512) layernorm_bwd_reg_kernel<4><<<grid, tr, smem_reg, STREAM>>>(JM_LN_BWD_ARGS);
+  else if (dim <= 768) layernorm_bwd_reg_kernel<6><<<grid, tr, smem_reg, STREAM>>>(JM_LN_BWD_ARGS);
+  else if (dim <= 1024) {
+    JM_CUDA(cudaFuncSetAttribute(layernorm_bwd_reg_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
+    layernorm_bwd_reg_kernel<8><<<grid, tr, smem_reg, STREAM>>>(JM_LN_BWD_ARGS);
+  } else if (dim <= 1280) {
+    JM_CUDA(cudaFuncSetAttribute(layernorm_bwd_reg_kernel<10>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
+    layernorm_bwd_reg_kernel<10><<<grid, tr, smem_reg, STREAM>>>(JM_LN_BWD_ARGS);
+  } else {
+    const int g8 = (rows + kLnWarps - 1) / kLnWarps < grid ? (rows + kLnWarps - 1) / kLnWarps : grid;
+    grid = g8;
+    layernorm_bwd_kernel<<<grid, kLnWarps * 32, smem, STREAM>>>(JM_LN_BWD_ARGS);
+  }
 #undef JM_LN_BWD_ARGS
   ln_param_reduce_kernel<<<(3 * dim + 31) / 32, 256, 0, STREAM>>>(static_cast<const float*>(workspace), grid, dim,
                                                                   dgamma, dbeta, dcol);
