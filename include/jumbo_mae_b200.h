@@ -150,6 +150,7 @@ typedef struct jm_gemm_args {
   int splits;      /* 0 = choose automatically */
   int block_n;     /* 0 = choose automatically (64, 128 or 256) */
   float* colsum;   /* optional [N]: += column sums of the stored output (fused bias gradient) */
+  int cta_pair;    /* 0 = automatic, 1 = force the 2-SM (cta_group::2) 256x256 kernel, -1 = never use it */
 } jm_gemm_args;
 int jm_gemm(const jm_gemm_args* args, void* stream);
 

@@ -46,6 +46,7 @@ class GemmArgs(ctypes.Structure):
         ("splits", c_int),
         ("block_n", c_int),
         ("colsum", c_void_p),
+        ("cta_pair", c_int),
     ]
 
 

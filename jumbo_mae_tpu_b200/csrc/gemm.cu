@@ -15,6 +15,7 @@
 // Replaces the XLA dot_general behind every Dense/DenseGeneral/Conv of the reference
 // (src/modeling.py:108-148, src/pretraining.py:84-85) and their autodiff transposes.
 #include <cudaTypedefs.h>
+#include <stdlib.h>
 
 #include "../../include/jumbo_mae_b200.h"
 #include "common.cuh"
@@ -33,6 +34,7 @@ constexpr int kStageBytesPerWarp = 32 * kStageRowBytes;  // 32 rows
 struct GemmShape {
   int M, N, K;
   int num_m, num_n, splits, kblocks;
+  int pf_dist, pf_a, pf_b;  // L2 prefetch: k-blocks of lookahead, and which operands are streamed from DRAM
 };
 
 struct EpiParams {
@@ -279,10 +281,10 @@ __device__ __forceinline__ void epi_prefetch(EpiPrefetch<EPI>& pf, const EpiPara
 // (8 columns per lane, 16 rows per warp instruction): every global access is a full 16-byte vector.
 // Sixteen warps, not four or eight: one warp retires a long dependent instruction stream per sub-chunk at
 // well under one instruction per cycle, so the drain rate scales with the number of warps per scheduler.
-template <int EPI, int BN>
+template <int EPI, int BN, int CG>
 __device__ __forceinline__ void epilogue_role(const EpiParams& ep, const GemmShape& sh, uint8_t* sEpi,
                                               uint64_t* tfull, uint64_t* tempty, uint32_t tmem_base, int warp,
-                                              int lane, int total_tiles) {
+                                              int lane, int total_tiles, int tile0, int tile_step, int m_off) {
   const int e = warp - kEpiWarp0;
   const int q = e & 3;      // TMEM lane quarter == warp % 4
   const int part = e >> 2;  // which quarter of the tile's columns
@@ -293,13 +295,13 @@ __device__ __forceinline__ void epilogue_role(const EpiParams& ep, const GemmSha
   const int rsub = lane >> 1, cu = lane & 1;
   const int tiles_mn = sh.num_m * sh.num_n;
   int iter = 0;
-  for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++iter) {
+  for (int t = tile0; t < total_tiles; t += tile_step, ++iter) {
     const int rem = t % tiles_mn;
     const int m_blk = rem / sh.num_n, n_blk = rem - m_blk * sh.num_n;
     const int acc = iter & 1;
     const uint32_t acc_phase = (iter >> 1) & 1;
     // this lane's 2 rows are the same for every sub-chunk of the tile: resolve the row predicates once
-    const int row0 = m_blk * BM + q * 32 + rsub;
+    const int row0 = m_blk * (BM * CG) + m_off + q * 32 + rsub;
     uint32_t store_mask = 0, zero_mask = 0;
 #pragma unroll
     for (int it = 0; it < 2; ++it) {
@@ -336,7 +338,8 @@ __device__ __forceinline__ void epilogue_role(const EpiParams& ep, const GemmSha
       }
       if (c == NSUB - 1) {  // accumulator fully drained: hand the TMEM buffer back to the MMA warp
         tc_fence_before();
-        mbar_arrive(&tempty[acc]);
+        if constexpr (CG == 1) mbar_arrive(&tempty[acc]);
+        else mbar_arrive_cluster(mapa_shared(smem_u32(&tempty[acc]), 0));  // the leader CTA issues the MMAs
       }
       __syncwarp();
       const EpiPrefetch<EPI> cur = pf;
@@ -463,6 +466,44 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     if (elect_one()) {
       int stage = 0;
       uint32_t phase = 0;
+      // L2 prefetch cursor: runs kPfDist k-blocks ahead of the load cursor through this CTA's (tile, k-block)
+      // sequence, so that a streamed operand is already in L2 when the ring asks for it.
+      const int pf_dist = sh.pf_dist;
+      int pt = blockIdx.x, pkb = -1, pkb1 = 0, pm = 0, pn = 0, ahead = 0;
+      auto pf_tile = [&]() {
+        if (pt < total_tiles) {
+          const int split = pt / tiles_mn;
+          const int rem = pt - split * tiles_mn;
+          pm = rem / sh.num_n, pn = rem - pm * sh.num_n;
+          pkb = static_cast<int>(static_cast<long>(sh.kblocks) * split / sh.splits);
+          pkb1 = static_cast<int>(static_cast<long>(sh.kblocks) * (split + 1) / sh.splits);
+        }
+      };
+      auto pf_step = [&]() {  // prefetch one k-block and advance the cursor
+        if (pt >= total_tiles) return;
+        if (sh.pf_a) {
+          if (!A_MN) tma_prefetch_2d(&tmA, pkb * BK, pm * BM);
+          else {
+#pragma unroll
+            for (int i = 0; i < BM / 64; ++i) tma_prefetch_2d(&tmA, pm * BM + i * 64, pkb * BK);
+          }
+        }
+        if (sh.pf_b) {
+          if (!B_MN) tma_prefetch_2d(&tmB, pkb * BK, pn * BN);
+          else {
+#pragma unroll
+            for (int i = 0; i < BN / 64; ++i) tma_prefetch_2d(&tmB, pn * BN + i * 64, pkb * BK);
+          }
+        }
+        if (++pkb == pkb1) {
+          pt += gridDim.x;
+          pf_tile();
+        }
+      };
+      if (pf_dist > 0) {
+        pf_tile();
+        for (; ahead < pf_dist; ++ahead) pf_step();
+      }
       for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
         const int split = t / tiles_mn;
         const int rem = t - split * tiles_mn;
@@ -470,6 +511,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         const int kb0 = static_cast<int>(static_cast<long>(sh.kblocks) * split / sh.splits);
         const int kb1 = static_cast<int>(static_cast<long>(sh.kblocks) * (split + 1) / sh.splits);
         for (int kb = kb0; kb < kb1; ++kb) {
+          if (pf_dist > 0) pf_step();
           mbar_wait(&empty[stage], phase ^ 1);
           mbar_arrive_expect_tx(&full[stage], Cfg::STAGE_BYTES);
           uint8_t* a_dst = sA + stage * Cfg::A_BYTES;
@@ -530,12 +572,172 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       }
     }
   } else if (warp >= kEpiWarp0) {
-    epilogue_role<EPI, BN>(ep, sh, sEpi, tfull, tempty, tmem_base, warp, lane, total_tiles);
+    epilogue_role<EPI, BN, 1>(ep, sh, sEpi, tfull, tempty, tmem_base, warp, lane, total_tiles, blockIdx.x,
+                              gridDim.x, 0);
   }
 
   tc_fence_before();
   __syncthreads();
   if (warp == 2) tmem_dealloc<Cfg::TMEM_COLS>(tmem_base);
+}
+
+// ---------------------------------------------------------------- CTA-pair (cta_group::2) kernel
+// One 256 x 256 output tile per pair of CTAs on neighbouring SMs.  Each CTA stages its own 128 rows of A and
+// only HALF of the B tile (128 columns); one tcgen05.mma.cta_group::2 issued by the leader CTA drives both
+// tensor cores, each reading its local A and both halves of B.  Per CTA and k-block that is 32 KB of TMA
+// writes and 32 KB of operand reads instead of 48 + 48: the single-CTA kernel is bound by exactly that
+// shared-memory / L2-to-SM traffic (a 128 x 256 x 16 MMA consumes 96 B/clk of operands at full rate).
+// Barriers: `full` lives in the leader (both producers arrive, both CTAs' TMA bytes complete on it);
+// `empty` and `tfull` are signalled in both CTAs by multicast commits; `tempty` lives in the leader and is
+// arrived on by the epilogue threads of both CTAs.
+struct Gemm2Cfg {
+  static constexpr int BN = 256;
+  static constexpr int A_BYTES = BM * BK * 2;         // this CTA's 128 rows
+  static constexpr int B_BYTES = (BN / 2) * BK * 2;   // this CTA's 128 of the 256 columns
+  static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+  static constexpr int STAGES = 6;
+  static constexpr int TMEM_COLS = 2 * BN;
+  static constexpr int BAR_BYTES = (2 * STAGES + 4) * 8 + 16;
+  static constexpr int EPI_BYTES = kEpiWarps * kStageBytesPerWarp;
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + EPI_BYTES + BAR_BYTES + 1024;
+};
+
+template <bool A_MN, bool B_MN, int EPI>
+__global__ void __launch_bounds__(kGemmThreads, 1)
+gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmShape sh,
+             const EpiParams ep) {
+  using Cfg = Gemm2Cfg;
+  constexpr int STAGES = Cfg::STAGES;
+  constexpr int BN = Cfg::BN;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+  uint8_t* sA = smem;
+  uint8_t* sB = smem + STAGES * Cfg::A_BYTES;
+  uint8_t* sEpi = smem + STAGES * Cfg::STAGE_BYTES;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sEpi + Cfg::EPI_BYTES);
+  uint64_t* full = bars;
+  uint64_t* empty = bars + STAGES;
+  uint64_t* tfull = bars + 2 * STAGES;
+  uint64_t* tempty = bars + 2 * STAGES + 2;
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 4);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int rank = static_cast<int>(cluster_ctarank());
+  const int pair = blockIdx.x >> 1, npairs = gridDim.x >> 1;
+#ifdef JM_DEBUG_SMID
+  if (threadIdx.x == 0 && blockIdx.x < 8) {
+    uint32_t smid;
+    asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+    printf("block %d rank %d smid %u\n", blockIdx.x, rank, smid);
+  }
+#endif
+
+  if (warp == 0 && elect_one()) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+  }
+  if (warp == 1 && elect_one()) {
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(&full[s], 2);   // one arrive per CTA's producer (the leader's carries the byte count)
+      mbar_init(&empty[s], 1);  // one multicast commit
+    }
+    for (int a = 0; a < 2; ++a) {
+      mbar_init(&tfull[a], 1);
+      mbar_init(&tempty[a], 2 * kEpiWarps * 32);
+    }
+    fence_barrier_init();
+  }
+  if (warp == 2) tmem_alloc2<Cfg::TMEM_COLS>(tmem_ptr);
+  tc_fence_before();
+  cluster_sync_all();  // peer barriers initialised, TMEM allocated in both CTAs
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr;
+
+  const int tiles_mn = sh.num_m * sh.num_n;  // num_m counts 256-row pair tiles here
+  const int total_tiles = tiles_mn * sh.splits;
+
+  if (warp == 0) {
+    if (elect_one()) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int t = pair; t < total_tiles; t += npairs) {
+        const int split = t / tiles_mn;
+        const int rem = t - split * tiles_mn;
+        const int m_blk = rem / sh.num_n, n_blk = rem - m_blk * sh.num_n;
+        const int kb0 = static_cast<int>(static_cast<long>(sh.kblocks) * split / sh.splits);
+        const int kb1 = static_cast<int>(static_cast<long>(sh.kblocks) * (split + 1) / sh.splits);
+        const int m0 = m_blk * 2 * BM + rank * BM;
+        const int n0 = n_blk * BN + rank * (BN / 2);
+        for (int kb = kb0; kb < kb1; ++kb) {
+          mbar_wait(&empty[stage], phase ^ 1);
+          if (rank == 0) mbar_arrive_expect_tx(&full[stage], 2 * Cfg::STAGE_BYTES);
+          else mbar_arrive_cluster(mapa_shared(smem_u32(&full[stage]), 0));
+          uint8_t* a_dst = sA + stage * Cfg::A_BYTES;
+          uint8_t* b_dst = sB + stage * Cfg::B_BYTES;
+          if (!A_MN) {
+            tma_load_2d_pair(&tmA, &full[stage], a_dst, kb * BK, m0);
+          } else {
+#pragma unroll
+            for (int i = 0; i < BM / 64; ++i)
+              tma_load_2d_pair(&tmA, &full[stage], a_dst + i * (BK * 128), m0 + i * 64, kb * BK);
+          }
+          if (!B_MN) {
+            tma_load_2d_pair(&tmB, &full[stage], b_dst, kb * BK, n0);
+          } else {
+#pragma unroll
+            for (int i = 0; i < (BN / 2) / 64; ++i)
+              tma_load_2d_pair(&tmB, &full[stage], b_dst + i * (BK * 128), n0 + i * 64, kb * BK);
+          }
+          if (++stage == STAGES) stage = 0, phase ^= 1;
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (rank == 0) {
+      constexpr uint32_t idesc = make_idesc_bf16(2 * BM, BN, A_MN ? 1 : 0, B_MN ? 1 : 0);
+      int stage = 0;
+      uint32_t phase = 0;
+      int iter = 0;
+      for (int t = pair; t < total_tiles; t += npairs, ++iter) {
+        const int split = t / tiles_mn;
+        const int kb0 = static_cast<int>(static_cast<long>(sh.kblocks) * split / sh.splits);
+        const int kb1 = static_cast<int>(static_cast<long>(sh.kblocks) * (split + 1) / sh.splits);
+        const int acc = iter & 1;
+        const uint32_t acc_phase = (iter >> 1) & 1;
+        mbar_wait(&tempty[acc], acc_phase ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + acc * BN;
+        for (int kb = kb0; kb < kb1; ++kb) {
+          mbar_wait(&full[stage], phase);
+          tc_fence_after();
+          if (elect_one()) {
+            const uint32_t a_addr = smem_u32(sA + stage * Cfg::A_BYTES);
+            const uint32_t b_addr = smem_u32(sB + stage * Cfg::B_BYTES);
+#pragma unroll
+            for (int k = 0; k < BK / UMMA_K; ++k) {
+              const uint64_t da = A_MN ? make_smem_desc_sw128(a_addr + k * (UMMA_K * 128), BK * 128, 1024)
+                                       : make_smem_desc_sw128(a_addr + k * (UMMA_K * 2), 0, 1024);
+              const uint64_t db = B_MN ? make_smem_desc_sw128(b_addr + k * (UMMA_K * 128), BK * 128, 1024)
+                                       : make_smem_desc_sw128(b_addr + k * (UMMA_K * 2), 0, 1024);
+              umma2_bf16(d_tmem, da, db, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+            }
+            umma2_commit_mc(&empty[stage]);
+            if (kb == kb1 - 1) umma2_commit_mc(&tfull[acc]);
+          }
+          __syncwarp();
+          if (++stage == STAGES) stage = 0, phase ^= 1;
+        }
+      }
+    }
+  } else if (warp >= kEpiWarp0) {
+    epilogue_role<EPI, BN, 2>(ep, sh, sEpi, tfull, tempty, tmem_base, warp, lane, total_tiles, pair, npairs,
+                              rank * BM);
+  }
+
+  tc_fence_before();
+  cluster_sync_all();  // no CTA may exit (or free TMEM) while its peer can still signal it or read its operands
+  if (warp == 2) tmem_dealloc2<Cfg::TMEM_COLS>(tmem_base);
 }
 
 // ---------------------------------------------------------------- host side
@@ -583,6 +785,64 @@ static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const Gem
   kern<<<grid, kGemmThreads, GemmCfg<BN>::SMEM_BYTES, stream>>>(tmA, tmB, sh, ep);
   JM_AFTER_LAUNCH();
   return 0;
+}
+
+template <bool A_MN, bool B_MN, int EPI>
+static int launch_gemm2(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmShape& sh, const EpiParams& ep,
+                        int grid, cudaStream_t stream) {
+  auto kern = gemm2_kernel<A_MN, B_MN, EPI>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    JM_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Gemm2Cfg::SMEM_BYTES));
+    attr_set = true;
+  }
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(kGemmThreads);
+  cfg.dynamicSmemBytes = Gemm2Cfg::SMEM_BYTES;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[2];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 2;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  static int policy = -1;
+  if (policy < 0) {
+    const char* e = getenv("JM_PAIR_POLICY");
+    policy = e ? atoi(e) : 0;
+  }
+  if (policy > 0) {
+    attr[1].id = cudaLaunchAttributeClusterSchedulingPolicyPreference;
+    attr[1].val.clusterSchedulingPolicyPreference =
+        policy == 1 ? cudaClusterSchedulingPolicySpread : cudaClusterSchedulingPolicyLoadBalancing;
+    cfg.numAttrs = 2;
+  }
+  JM_CUDA(cudaLaunchKernelEx(&cfg, kern, tmA, tmB, sh, ep));
+  count_launch();
+  return 0;
+}
+
+template <bool A_MN, bool B_MN>
+static int dispatch_epi2(int epi, const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmShape& sh,
+                         const EpiParams& ep, int grid, cudaStream_t stream) {
+  switch (epi) {
+    case EPI_BF16: return launch_gemm2<A_MN, B_MN, EPI_BF16>(tmA, tmB, sh, ep, grid, stream);
+    case EPI_F32: return launch_gemm2<A_MN, B_MN, EPI_F32>(tmA, tmB, sh, ep, grid, stream);
+    case EPI_GELU_FWD: return launch_gemm2<A_MN, B_MN, EPI_GELU_FWD>(tmA, tmB, sh, ep, grid, stream);
+    case EPI_GELU_BWD: return launch_gemm2<A_MN, B_MN, EPI_GELU_BWD>(tmA, tmB, sh, ep, grid, stream);
+    default: return launch_gemm2<A_MN, B_MN, EPI_GENERIC>(tmA, tmB, sh, ep, grid, stream);
+  }
+}
+
+// Pair kernel instantiations: forward (A K-major, B MN-major), input gradient (K, K), weight gradient (MN, MN).
+static int dispatch_pair(bool a_mn, bool b_mn, int epi, const CUtensorMap& tmA, const CUtensorMap& tmB,
+                         const GemmShape& sh, const EpiParams& ep, int grid, cudaStream_t stream) {
+  if (!a_mn && !b_mn) return dispatch_epi2<false, false>(epi, tmA, tmB, sh, ep, grid, stream);
+  if (!a_mn && b_mn) return dispatch_epi2<false, true>(epi, tmA, tmB, sh, ep, grid, stream);
+  if (epi == EPI_F32) return launch_gemm2<true, true, EPI_F32>(tmA, tmB, sh, ep, grid, stream);
+  return launch_gemm2<true, true, EPI_GENERIC>(tmA, tmB, sh, ep, grid, stream);
 }
 
 template <int BN, bool A_MN, bool B_MN>
@@ -672,6 +932,28 @@ extern "C" int jm_gemm(const jm_gemm_args* a, void* stream_) {
   JM_CHECK(splits == 1 || can_split, "jm_gemm: split-K needs a pure accumulate epilogue");
   JM_CHECK(splits <= kblocks, "jm_gemm: more splits (%d) than k-blocks (%d)", splits, kblocks);
 
+  // CTA-pair kernel (256 x 256 tiles, cta_group::2) whenever the 256-wide tile was chosen and M fills a pair
+  const bool amn = a->a_mn_major != 0, bmn = a->b_mn_major != 0;
+  // (measured slower than the single-CTA kernel so far, see DESIGN.md: only on request)
+  bool pair = false;
+  if (a->cta_pair > 0) {
+    JM_CHECK(bn == 256 && !(amn && !bmn), "jm_gemm: cta_pair needs block_n 256 and a supported operand layout");
+    pair = true;
+  }
+  int num_m_eff = num_m;
+  if (pair) {
+    num_m_eff = (a->M + 2 * BM - 1) / (2 * BM);
+    if (a->splits <= 0) {
+      splits = 1;
+      if (can_split) {
+        const long tiles2 = static_cast<long>(num_m_eff) * num_n;
+        splits = static_cast<int>((sms / 2) / tiles2);
+        if (splits < 1) splits = 1;
+        if (splits > kblocks / 2) splits = kblocks / 2 > 0 ? kblocks / 2 : 1;
+      }
+    }
+  }
+
   CUtensorMap tmA, tmB;
   if (!a->a_mn_major) {
     if (make_tmap(&tmA, a->A, a->K, a->M, a->lda, BK, BM)) return 1;
@@ -679,12 +961,20 @@ extern "C" int jm_gemm(const jm_gemm_args* a, void* stream_) {
     if (make_tmap(&tmA, a->A, a->M, a->K, a->lda, 64, BK)) return 1;
   }
   if (!a->b_mn_major) {
-    if (make_tmap(&tmB, a->B, a->K, a->N, a->ldb, BK, bn)) return 1;
+    if (make_tmap(&tmB, a->B, a->K, a->N, a->ldb, BK, pair ? bn / 2 : bn)) return 1;
   } else {
     if (make_tmap(&tmB, a->B, a->N, a->K, a->ldb, 64, BK)) return 1;
   }
 
-  GemmShape sh{a->M, a->N, a->K, num_m, num_n, splits, kblocks};
+  // Operands larger than ~a quarter of L2 are streamed from DRAM once: prefetch them into L2 ahead of the ring.
+  static int pf_env = -1;
+  if (pf_env < 0) {
+    const char* e = getenv("JM_GEMM_PF");
+    pf_env = e ? atoi(e) : 0;  // measured: no gain on B200 (the ring is not DRAM-latency bound), off by default
+  }
+  const double a_bytes = 2.0 * a->M * a->K, b_bytes = 2.0 * a->N * a->K;
+  const int pf_a = a_bytes > 24e6 ? 1 : 0, pf_b = b_bytes > 24e6 ? 1 : 0;
+  GemmShape sh{a->M, a->N, a->K, num_m_eff, num_n, splits, kblocks, (pf_a || pf_b) ? pf_env : 0, pf_a, pf_b};
   EpiParams ep;
   ep.out_f32 = a->out_f32, ep.ldo_f32 = a->ldo_f32;
   ep.out_bf16 = reinterpret_cast<__nv_bfloat16*>(a->out_bf16), ep.ldo_bf16 = a->ldo_bf16;
@@ -700,9 +990,9 @@ extern "C" int jm_gemm(const jm_gemm_args* a, void* stream_) {
   ep.colsum = a->colsum;
   JM_CHECK(!a->colsum || a->act != 1, "jm_gemm: colsum is not defined for the GELU-forward epilogue");
 
-  const long total = static_cast<long>(num_m) * num_n * splits;
-  const int grid = static_cast<int>(total < sms ? total : sms);
-  const bool amn = a->a_mn_major != 0, bmn = a->b_mn_major != 0;
+  const long total = static_cast<long>(num_m_eff) * num_n * splits;
+  const int grid = pair ? 2 * static_cast<int>(total < sms / 2 ? total : sms / 2)
+                        : static_cast<int>(total < sms ? total : sms);
   int epi = EPI_GENERIC;
   const bool only_bf16 = ep.out_bf16 && !ep.out_f32 && !ep.out2_bf16;
   const bool only_f32 = ep.out_f32 && !ep.out_bf16 && !ep.out2_bf16;
@@ -710,6 +1000,10 @@ extern "C" int jm_gemm(const jm_gemm_args* a, void* stream_) {
   else if (ep.act == 2 && only_bf16 && !ep.residual && !ep.pe) epi = EPI_GELU_BWD;
   else if (ep.act == 0 && only_f32 && !ep.colsum) epi = EPI_F32;
   else if (ep.act == 0 && only_bf16 && !ep.residual && !ep.pe && !ep.colsum) epi = EPI_BF16;
+  if (pair) {
+    if (amn && epi != EPI_F32) epi = EPI_GENERIC;
+    return dispatch_pair(amn, bmn, epi, tmA, tmB, sh, ep, grid, stream);
+  }
   if (bn == 256) return dispatch_major<256>(amn, bmn, epi, tmA, tmB, sh, ep, grid, stream);
   if (bn == 128) return dispatch_major<128>(amn, bmn, epi, tmA, tmB, sh, ep, grid, stream);
   return dispatch_major<64>(amn, bmn, epi, tmA, tmB, sh, ep, grid, stream);

@@ -7,6 +7,7 @@ PyTorch here: without the CUDA library these functions raise.
 from __future__ import annotations
 
 import ctypes
+import os
 from typing import Optional
 
 import torch
@@ -146,7 +147,7 @@ def gemm(A: torch.Tensor, B: torch.Tensor, M: int, N: int, K: int, *, a_mn: bool
          act: int = 0, col_scale: float = 1.0, col_scale_n: int = 0,
          row_period: int = 0, row_skip: int = 0, row_mask_mode: int = 0,
          accumulate: bool = False, splits: int = 0, block_n: int = 0,
-         colsum: Optional[torch.Tensor] = None) -> None:
+         colsum: Optional[torch.Tensor] = None, cta_pair: int = 0) -> None:
     """D = epilogue(A @ B) through jm_gemm; see include/jumbo_mae_b200.h for the epilogue order."""
     _chk(A, BF16, "A"), _chk(B, BF16, "B"), _chk(out_f32, F32, "out_f32"), _chk(out_bf16, BF16, "out_bf16")
     _chk(out2_bf16, BF16, "out2_bf16"), _chk(bias, F32, "bias"), _chk(residual, F32, "residual")
@@ -168,6 +169,7 @@ def gemm(A: torch.Tensor, B: torch.Tensor, M: int, N: int, K: int, *, a_mn: bool
     a.accumulate, a.splits, a.block_n = int(accumulate), splits, block_n
     _chk(colsum, F32, "colsum")
     a.colsum = ptr(colsum)
+    a.cta_pair = int(os.environ.get("JM_GEMM_PAIR", cta_pair))
     check(_lib.load().jm_gemm(ctypes.byref(a), stream_ptr()))
 
 

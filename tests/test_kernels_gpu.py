@@ -458,3 +458,20 @@ def test_attention_bwd(ops, B, T, H, hd):
     # fused q/k/v bias gradient = column sums (the k part is ~0: softmax shift invariance)
     wb = want.sum(0)
     assert (dbias - 1 - wb).norm().item() <= 2e-2 * wb.norm().item() + 1e-3
+
+
+@pytest.mark.parametrize("M,N,K,a_mn,b_mn", [(256, 256, 64, False, False), (1280, 512, 512, False, True),
+                                             (768, 1024, 3000, True, True), (600, 520, 200, False, True)])
+def test_gemm_cta_pair_kernel(ops, M, N, K, a_mn, b_mn):
+    """The 2-SM (cta_group::2) 256x256 kernel: same results as the single-CTA kernel (it is kept opt-in:
+    measured slower on B200 so far)."""
+    g = torch.Generator(device="cuda").manual_seed(M + N + K)
+    ldn, ldk = (N + 7) // 8 * 8, (K + 7) // 8 * 8
+    A = torch.randn((K, M) if a_mn else (M, ldk), generator=g, device="cuda").to(BF16)
+    A = A if a_mn else A[:, :K]
+    B = torch.randn((K, ldn) if b_mn else (N, ldk), generator=g, device="cuda").to(BF16)
+    B = B[:, :N] if b_mn else B[:, :K]
+    out = torch.full((M, N), float("nan"), device="cuda")
+    ops.gemm(A, B, M, N, K, a_mn=a_mn, b_mn=b_mn, out_f32=out, block_n=256, cta_pair=1)
+    ref = _gemm_ref(A, B, a_mn, b_mn)
+    assert (out - ref).abs().max().item() <= 2e-5 * ref.abs().max().item() * math.sqrt(K)

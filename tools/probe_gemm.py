@@ -21,6 +21,16 @@ CASES = {
     "mnk_big": (384, 256, 328, True, False, 64),
     "tail": (200, 588, 72, False, True, 0),
     "persist": (4096, 2304, 768, False, True, 0),
+    # CTA-pair kernel (JM_GEMM_PAIR=1 in the environment forces it)
+    "pair_kk_256": (256, 256, 64, False, False, 256),
+    "pair_kk_k512": (256, 256, 512, False, False, 256),
+    "pair_kmn_256": (256, 256, 128, False, True, 256),
+    "pair_mnmn_256": (256, 256, 128, True, True, 256),
+    "pair_kk_big": (1024, 768, 576, False, False, 256),
+    "pair_kmn_big": (1280, 512, 512, False, True, 256),
+    "pair_mnmn_big": (768, 1024, 3000, True, True, 256),
+    "pair_tail": (600, 520, 200, False, True, 256),
+    "pair_persist": (26624, 2304, 768, False, True, 256),
 }
 
 
@@ -55,9 +65,15 @@ if __name__ == "__main__":
     if len(sys.argv) > 1 and sys.argv[1] != "all":
         sys.exit(run_case(sys.argv[1]))
     fails = 0
+    only = os.environ.get("PROBE_PREFIX", "")
     for name in CASES:
+        if not name.startswith(only):
+            continue
+        env = dict(os.environ)
+        if name.startswith("pair"):
+            env["JM_GEMM_PAIR"] = "1"
         try:
-            r = subprocess.run([sys.executable, __file__, name], timeout=120, capture_output=True, text=True)
+            r = subprocess.run([sys.executable, __file__, name], timeout=120, capture_output=True, text=True, env=env)
             sys.stdout.write(r.stdout)
             if r.returncode != 0:
                 fails += 1
