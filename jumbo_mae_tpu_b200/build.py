@@ -19,7 +19,8 @@ INCLUDE = os.path.join(os.path.dirname(HERE), "include")
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
     "-Xcompiler", "-fPIC", "-Xptxas", "-v", "--expt-relaxed-constexpr",
-] + (["-DJM_DEBUG_SMID"] if os.environ.get("JM_DEBUG_SMID") else [])
+] + (["-DJM_DEBUG_SMID"] if os.environ.get("JM_DEBUG_SMID") else []) + \
+    (["-DJM_EXP_NO_STORE"] if os.environ.get("JM_EXP_NO_STORE") else [])
 
 
 def _nvcc() -> str:

@@ -475,3 +475,4 @@ def test_gemm_cta_pair_kernel(ops, M, N, K, a_mn, b_mn):
     ops.gemm(A, B, M, N, K, a_mn=a_mn, b_mn=b_mn, out_f32=out, block_n=256, cta_pair=1)
     ref = _gemm_ref(A, B, a_mn, b_mn)
     assert (out - ref).abs().max().item() <= 2e-5 * ref.abs().max().item() * math.sqrt(K)
+

@@ -85,7 +85,8 @@ def run_gemm(name, M, N, K, kind):
     o = torch.empty(M, N, dtype=BF16, device="cuda")
     if kind == "dx_gelu":
         aux = r(M, N)
-        return lambda: ops.gemm(A, W, M, N, K, b_mn=False, out_bf16=o, aux=aux, act=2)
+        cs = torch.zeros(N, device="cuda") if os.environ.get("NO_CS") is None else None
+        return lambda: ops.gemm(A, W, M, N, K, b_mn=False, out_bf16=o, aux=aux, act=2, colsum=cs)
     return lambda: ops.gemm(A, W, M, N, K, b_mn=False, out_bf16=o)
 
 
