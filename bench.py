@@ -211,15 +211,20 @@ def run_ours(args):
     if use_graph:
         eng.capture_graphs()
 
+    if use_graph and reducer is not None:
+        eng.capture_segment_graphs()
+
     def resident_step():
         for i in range(accum):
-            if use_graph:
+            if use_graph and reducer is not None and i == accum - 1:
+                eng.run_graph_overlapped(dev_images[i], dev_noise[counter["micro"] % total_micro], i == 0, reducer)
+            elif use_graph:
                 eng.run_graph(dev_images[i], dev_noise[counter["micro"] % total_micro], zero_grads=(i == 0))
             else:
                 eng.forward(dev_images[i], dev_noise[counter["micro"] % total_micro])
                 eng.backward(zero_grads=(i == 0))
             counter["micro"] += 1
-        if reducer is not None:
+        if reducer is not None and not use_graph:
             reducer.all_reduce_grads()
         eng.adamw_step(counter["step"], lr_schedule(counter["step"], cfg), grad_scale=1.0 / (accum * world))
         counter["step"] += 1
@@ -268,30 +273,37 @@ def run_ours(args):
     h2d = accum * (micro * 3 * cfg.image_size * cfg.image_size + cfg.num_patches * 4)
     d2h = accum * 4
 
-    # ---- roofline of the dominant kernel: the tcgen05 GEMM, at the decoder-FFN shape that holds the
-    # largest share of the step's FLOPs, timed live with CUDA events.
-    from jumbo_mae_tpu_b200.config import flops_per_image
-    M, N, K = micro * (cfg.num_patches + cfg.num_cls_tokens), 4 * cfg.dec_dim, cfg.dec_dim
-    A = torch.randn(M, K, device=dev).to(torch.bfloat16)
+    # ---- roofline of the dominant kernel.  By time share (profiles/r1c_launches_summary.md) that is the tcgen05
+    # GEMM, and its largest instantiation is the weight-gradient product dW += X^T dY (15 % of the step); it is
+    # timed live at the decoder-FFN shape with CUDA events.  The GELU-forward instantiation (12 %), whose epilogue
+    # writes two bf16 tensors and is not hidden behind a K = 512 main loop, is reported next to it.
+    Md_, dd_ = micro * (cfg.num_patches + cfg.num_cls_tokens), cfg.dec_dim
+
+    def time_kernel(fn, reps=30):
+        for _ in range(5):
+            fn()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        a.record()
+        for _ in range(reps):
+            fn()
+        b.record()
+        torch.cuda.synchronize()
+        return a.elapsed_time(b) / reps
+
+    X = torch.randn(Md_, dd_, device=dev).to(torch.bfloat16)
+    dY = torch.randn(Md_, 4 * dd_, device=dev).to(torch.bfloat16)
+    dW = torch.zeros(dd_, 4 * dd_, device=dev)
+    dw_ms = time_kernel(lambda: ops.gemm(X, dY, dd_, 4 * dd_, Md_, a_mn=True, b_mn=True, out_f32=dW, accumulate=True))
+    dw_tflops = 2.0 * dd_ * 4 * dd_ * Md_ / (dw_ms * 1e-3) / 1e12
+    M, N, K = Md_, 4 * dd_, dd_
     W = torch.randn(K, N, device=dev).to(torch.bfloat16)
     bias = torch.zeros(N, device=dev)
     h = torch.empty(M, N, dtype=torch.bfloat16, device=dev)
     g = torch.empty(M, N, dtype=torch.bfloat16, device=dev)
-
-    def one_gemm():
-        ops.gemm(A, W, M, N, K, b_mn=True, out_bf16=h, out2_bf16=g, bias=bias, act=1)
-    for _ in range(5):
-        one_gemm()
-    reps = 30
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    torch.cuda.synchronize()
-    e0.record()
-    for _ in range(reps):
-        one_gemm()
-    e1.record()
-    torch.cuda.synchronize()
-    gemm_ms = e0.elapsed_time(e1) / reps
+    gemm_ms = time_kernel(lambda: ops.gemm(X, W, M, N, K, b_mn=True, out_bf16=h, out2_bf16=g, bias=bias, act=1))
     gemm_tflops = 2.0 * M * N * K / (gemm_ms * 1e-3) / 1e12
+    del X, dY, dW, W, h, g
     fwd_flops, step_flops = flops_per_image(cfg)
     step_tflops_per_gpu = step_flops * args.global_batch / world / (ms_per_step * 1e-3) / 1e12
 
@@ -301,10 +313,22 @@ def run_ours(args):
         "scaling": "strong", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
         "config": workload_config(args, micro, accum, world),
         "roofline": {
-            "bound": "tensor", "kernel": f"gemm_kernel<256> decoder FFN w1+GELU M={M} N={N} K={K}",
+            "bound": "tensor", "kernel": f"gemm_kernel<256,MN,MN,f32-accumulate> dW += X^T dY, decoder FFN w1: "
+                                         f"M={dd_} N={4 * dd_} K={Md_} (tokens)",
+            "achieved": dw_tflops, "peak": peaks["bf16_burst"], "unit": "TFLOP/s",
+            "frac": dw_tflops / peaks["bf16_burst"],
+            # dram__bytes_read.sum + dram__bytes_write.sum of one launch, ncu --set full
+            # (profiles/r1c_gemm_dw_ncu_full.md); algorithmic bytes 2*(M+N)*K + 4*M*N = 525.9 MB
+            "traffic": 530.5e6 if micro == 512 and args.config == "vit_b16" else None,
+            "peak_source": f"{peaks['source']} (burst: kernel timed alone)", "kernel_ms": dw_ms,
+        },
+        "roofline_gelu_fwd": {
+            "bound": "tensor", "kernel": f"gemm_kernel<256,K,MN,GELU> decoder FFN w1 forward M={M} N={N} K={K}",
             "achieved": gemm_tflops, "peak": peaks["bf16_burst"], "unit": "TFLOP/s",
-            "frac": gemm_tflops / peaks["bf16_burst"], "traffic": None,
-            "peak_source": f"{peaks['source']} (burst: kernel timed alone)", "kernel_ms": gemm_ms,
+            "frac": gemm_tflops / peaks["bf16_burst"],
+            "traffic": 888.7e6 if micro == 512 and args.config == "vit_b16" else None,
+            "kernel_ms": gemm_ms,
+            "note": "writes 834 MB (pre-activation + GELU) per launch: 128 us of HBM time against 129 us of MMA time",
         },
         "step_roofline": {
             "bound": "tensor", "achieved": step_tflops_per_gpu, "peak": peaks["bf16_sustained"], "unit": "TFLOP/s",

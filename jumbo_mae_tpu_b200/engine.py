@@ -211,43 +211,83 @@ class MAEEngine:
     # ------------------------------------------------------------------ backward
     def backward(self, zero_grads: bool = True) -> None:
         """Accumulates d loss / d params into store.g (after ``forward(want_grad=True)``)."""
+        for k in range(self.num_bwd_segments()):
+            self.backward_segment(k, zero_grads)
+
+    # The backward pass in segments whose parameter gradients are FINAL when the segment ends, so that a
+    # data-parallel caller can start all-reducing them while the next segment computes (the overlap the
+    # reference gets from XLA scheduling lax.pmean inside the step, src/pretraining.py:150).
+    ENC_LAYERS_PER_SEGMENT = 3
+
+    def num_bwd_segments(self) -> int:
+        n_enc = (self.cfg.layers + self.ENC_LAYERS_PER_SEGMENT - 1) // self.ENC_LAYERS_PER_SEGMENT
+        return 1 + n_enc
+
+    def _enc_segment_layers(self, k: int):
+        """Encoder layers (descending) handled by backward segment k >= 1."""
+        hi = self.cfg.layers - (k - 1) * self.ENC_LAYERS_PER_SEGMENT
+        lo = max(0, hi - self.ENC_LAYERS_PER_SEGMENT)
+        return list(reversed(range(lo, hi)))
+
+    def segment_grad_ranges(self, k: int):
+        """[start, end) ranges of store.g that are final once backward segment k has run."""
+        last = self.num_bwd_segments() - 1
+        if k == 0:
+            sel = lambda n: not n.startswith("model/") or n.startswith("model/norm/")
+        else:
+            layers = self._enc_segment_layers(k)
+            # a layer's ff/w2 bias is produced by the block ABOVE it (LayerNorm-backward column sums), hence
+            # final one block earlier; it is simply reduced together with its own layer's leaves
+            def sel(n, layers=layers, is_last=(k == last)):
+                if any(n.startswith(f"model/layer_{i}/") for i in layers):
+                    return True
+                return is_last and (n.startswith("model/embed/") or n.startswith("model/cls_tokens")
+                                    or n.startswith("model/jumbo_mlp/"))
+        return self.ps.ranges(sel)
+
+    def backward_segment(self, k: int, zero_grads: bool = True) -> None:
         cfg, ps, B = self.cfg, self.ps, self.B
         J, n, N, d, dd, P = cfg.num_cls_tokens, cfg.keep, cfg.num_patches, cfg.dim, cfg.dec_dim, cfg.patch_dim
         Te, Td, Me, Md, Pp = self.Te, self.Td, self.Me, self.Md, self.Pp
-        if zero_grads:
-            ps.g.zero_()
         view = lambda buf, M, w: buf[:M * w].view(M, w)
-        # ---- pixel head
-        dn = view(self.dn16, Md, dd)
-        self._bwd_linear(self.dec_n, self.dpred, Md, "decoder_image_output", P, dd, dX16=dn, dy_ld=Pp)
-        dx, dx16 = view(self.dxA, Md, dd), view(self.dxA16, Md, dd)
-        # (every LayerNorm backward also emits the column sums of the dx it produces: that dx is the
-        #  output gradient of the previous block's ff/w2, i.e. its bias gradient)
-        ops.layernorm_bwd(dn, self.za[cfg.dec_layers], self.meanD, self.rstdD, ps.f("decoder_model/dec_norm/scale"),
-                          None, dx, dx16, ps.grad("decoder_model/dec_norm/scale"),
-                          ps.grad("decoder_model/dec_norm/bias"), self.ln_ws,
-                          dcol=ps.grad(f"decoder_model/dec_layer_{cfg.dec_layers - 1}/ff/w2/bias"))
-        # ---- decoder blocks
-        for i in reversed(range(cfg.dec_layers)):
-            below = ps.grad(f"decoder_model/dec_layer_{i - 1}/ff/w2/bias") if i > 0 else None
-            self._block_bwd(f"decoder_model/dec_layer_{i}", self.dec[i], self.za[i], Md, dd, cfg.dec_heads, Td, False,
-                            below)
-        # ---- decoder input assembly + decoder_proj
-        ops.unshuffle_bwd(dx, self.ids_restore, B, N, n, J, dd, self.dy16, ps.grad("image_mask_embedding"))
-        dn = view(self.dn16, Me, d)
-        self._bwd_linear(self.enc_n, self.dy16, Me, "decoder_proj", dd, d, dX16=dn)
-        dx, dx16 = view(self.dxA, Me, d), view(self.dxA16, Me, d)
-        ops.layernorm_bwd(dn, self.xa[cfg.layers], self.meanF, self.rstdF, ps.f("model/norm/scale"), None, dx, dx16,
-                          ps.grad("model/norm/scale"), ps.grad("model/norm/bias"), self.ln_ws,
-                          dcol=ps.grad(f"model/layer_{cfg.layers - 1}/ff/w2/bias"), dcol_period=Te, dcol_skip=J)
-        # ---- encoder blocks
-        for i in reversed(range(cfg.layers)):
+        if k == 0:
+            if zero_grads:
+                ps.g.zero_()
+            # ---- pixel head
+            dn = view(self.dn16, Md, dd)
+            self._bwd_linear(self.dec_n, self.dpred, Md, "decoder_image_output", P, dd, dX16=dn, dy_ld=Pp)
+            dx, dx16 = view(self.dxA, Md, dd), view(self.dxA16, Md, dd)
+            # (every LayerNorm backward also emits the column sums of the dx it produces: that dx is the
+            #  output gradient of the previous block's ff/w2, i.e. its bias gradient)
+            ops.layernorm_bwd(dn, self.za[cfg.dec_layers], self.meanD, self.rstdD,
+                              ps.f("decoder_model/dec_norm/scale"), None, dx, dx16,
+                              ps.grad("decoder_model/dec_norm/scale"), ps.grad("decoder_model/dec_norm/bias"),
+                              self.ln_ws, dcol=ps.grad(f"decoder_model/dec_layer_{cfg.dec_layers - 1}/ff/w2/bias"))
+            # ---- decoder blocks
+            for i in reversed(range(cfg.dec_layers)):
+                below = ps.grad(f"decoder_model/dec_layer_{i - 1}/ff/w2/bias") if i > 0 else None
+                self._block_bwd(f"decoder_model/dec_layer_{i}", self.dec[i], self.za[i], Md, dd, cfg.dec_heads, Td,
+                                False, below)
+            # ---- decoder input assembly + decoder_proj
+            ops.unshuffle_bwd(dx, self.ids_restore, B, N, n, J, dd, self.dy16, ps.grad("image_mask_embedding"))
+            dn = view(self.dn16, Me, d)
+            self._bwd_linear(self.enc_n, self.dy16, Me, "decoder_proj", dd, d, dX16=dn)
+            dx, dx16 = view(self.dxA, Me, d), view(self.dxA16, Me, d)
+            ops.layernorm_bwd(dn, self.xa[cfg.layers], self.meanF, self.rstdF, ps.f("model/norm/scale"), None, dx,
+                              dx16, ps.grad("model/norm/scale"), ps.grad("model/norm/bias"), self.ln_ws,
+                              dcol=ps.grad(f"model/layer_{cfg.layers - 1}/ff/w2/bias"), dcol_period=Te, dcol_skip=J)
+            return
+        # ---- encoder blocks of this segment
+        for i in self._enc_segment_layers(k):
             below = ps.grad(f"model/layer_{i - 1}/ff/w2/bias") if i > 0 else ps.grad("model/embed/wte/bias")
             self._block_bwd(f"model/layer_{i}", self.enc[i], self.xa[i], Me, d, cfg.heads, Te, True, below)
-        # ---- CLS parameter and patch embedding (its bias gradient came from layer 0's LN1 backward)
-        ops.colsum(dx, B, J * d, ps.grad("model/cls_tokens"), ldx=Te * d)
-        ops.gemm(self.patches, dx16, P, d, Me, a_mn=True, b_mn=True, lda=Pp,
-                 out_f32=ps.grad("model/embed/wte/kernel"), ldo_f32=ps.ld("model/embed/wte/kernel"), accumulate=True)
+        if k == self.num_bwd_segments() - 1:
+            # ---- CLS parameter and patch embedding (its bias gradient came from layer 0's LN1 backward)
+            dx, dx16 = view(self.dxA, Me, d), view(self.dxA16, Me, d)
+            ops.colsum(dx, B, J * d, ps.grad("model/cls_tokens"), ldx=Te * d)
+            ops.gemm(self.patches, dx16, P, d, Me, a_mn=True, b_mn=True, lda=Pp,
+                     out_f32=ps.grad("model/embed/wte/kernel"), ldo_f32=ps.ld("model/embed/wte/kernel"),
+                     accumulate=True)
 
     def _block_bwd(self, name, s: _Block, x_in, M, dim, heads, T, jumbo, dcol_below):
         """In: d/d(block output) in dxA / dxA16.  Out: d/d(block input) in dxA / dxA16.
@@ -319,6 +359,39 @@ class MAEEngine:
             self.graph_launches = lib.jm_launch_count() - l0
             self.graphs[zero] = g
         self.ps.g.zero_()
+
+    def capture_segment_graphs(self) -> None:
+        """Graphs for a data-parallel rank's LAST micro-step of an optimizer step: forward + backward
+        segment 0, then one graph per encoder segment, so gradient all-reduces can start between them."""
+        if not hasattr(self, "graphs"):
+            self.capture_graphs()
+        self.seg_graphs = {}
+        for zero in (True, False):
+            graphs = []
+            for k in range(self.num_bwd_segments()):
+                g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g):
+                    if k == 0:
+                        self.forward(self.images_buf, self.noise_buf)
+                    self.backward_segment(k, zero_grads=zero)
+                graphs.append(g)
+            self.seg_graphs[zero] = graphs
+        self.ps.g.zero_()
+
+    def run_graph_overlapped(self, images: torch.Tensor, noise: torch.Tensor, zero_grads: bool, reducer) -> torch.Tensor:
+        """Last micro-step of a data-parallel optimizer step: every backward segment is followed by the
+        all-reduce of the gradients it finalised, on the reducer's stream, overlapping the next segment."""
+        if not hasattr(self, "seg_graphs"):
+            self.capture_segment_graphs()
+        self.images_buf.copy_(images, non_blocking=True)
+        self.noise_buf.copy_(noise, non_blocking=True)
+        for k, g in enumerate(self.seg_graphs[bool(zero_grads)]):
+            g.replay()
+            ev = torch.cuda.Event()
+            ev.record()
+            reducer.all_reduce_ranges(self.segment_grad_ranges(k), after_event=ev)
+        reducer.join()
+        return self.loss
 
     def run_graph(self, images: torch.Tensor, noise: torch.Tensor, zero_grads: bool) -> torch.Tensor:
         """forward + backward through the captured graph; images may be a pinned host tensor."""

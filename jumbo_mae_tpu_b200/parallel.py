@@ -48,7 +48,8 @@ class GradReducer:
 
     def __init__(self, store, bucket_mb: int = 64):
         self.store = store
-        self.ranges = bucket_ranges(store.total, bucket_mb * (1 << 20) // 4)
+        self.bucket_elems = bucket_mb * (1 << 20) // 4
+        self.ranges = bucket_ranges(store.total, self.bucket_elems)
         self.stream = torch.cuda.Stream() if store.g.is_cuda else None
 
     def all_reduce_grads(self) -> None:
@@ -64,6 +65,30 @@ class GradReducer:
             for s, e in self.ranges:
                 dist.all_reduce(g[s:e])
         torch.cuda.current_stream().wait_stream(self.stream)
+
+    def all_reduce_ranges(self, ranges, after_event=None) -> None:
+        """Sum-all-reduces the given [start, end) ranges of the gradient buffer on the communication stream,
+        after ``after_event`` (recorded on the compute stream when those gradients became final).  The compute
+        stream is NOT blocked: call ``join()`` before the optimizer reads the gradients."""
+        if process_count() == 1:
+            return
+        g = self.store.g
+        if self.stream is None:
+            for s, e in ranges:
+                dist.all_reduce(g[s:e])
+            return
+        if after_event is not None:
+            self.stream.wait_event(after_event)
+        else:
+            self.stream.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(self.stream):
+            for s, e in ranges:
+                for b in range(s, e, self.bucket_elems):
+                    dist.all_reduce(g[b:min(e, b + self.bucket_elems)])
+
+    def join(self) -> None:
+        if self.stream is not None:
+            torch.cuda.current_stream().wait_stream(self.stream)
 
     def mean_scalar(self, t: torch.Tensor) -> None:
         if process_count() == 1:

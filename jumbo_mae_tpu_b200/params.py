@@ -131,6 +131,20 @@ class ParamStore:
     def ld(self, name: str) -> int:
         return self.leaves[name].ld
 
+    def ranges(self, select) -> List[Tuple[int, int]]:
+        """Merged [start, end) element ranges of the flat buffers covering the leaves whose name satisfies
+        ``select(name)`` (padding between consecutive selected leaves is included)."""
+        out: List[Tuple[int, int]] = []
+        for leaf in sorted(self.leaves.values(), key=lambda l: l.offset):
+            if not select(leaf.name):
+                continue
+            start, end = leaf.offset, leaf.offset + _round_up(leaf.size, ALIGN)
+            if out and out[-1][1] == start:
+                out[-1] = (out[-1][0], end)
+            else:
+                out.append((start, end))
+        return out
+
     # ------------------------------------------------------------- Flax-shaped trees
     def tree(self, buf: torch.Tensor | None = None) -> dict:
         """The reference's parameter pytree as views into ``buf`` (default: f32 masters)."""

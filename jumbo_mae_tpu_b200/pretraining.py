@@ -182,7 +182,13 @@ def training_step(state: TrainState, batch, noise=None) -> Tuple[TrainState, Dic
     if state.reducer is None and world > 1:
         state.reducer = GradReducer(state.store)
     first_micro = state.micro_step == 0
-    if USE_CUDA_GRAPH:
+    last_micro = state.micro_step + 1 == accum
+    reduced = False
+    if USE_CUDA_GRAPH and world > 1 and last_micro:
+        # gradient all-reduce overlapped with the backward pass (lax.pmean(grads), :150)
+        loss = eng.run_graph_overlapped(images, nz, first_micro, state.reducer)
+        reduced = True
+    elif USE_CUDA_GRAPH:
         loss = eng.run_graph(images, nz, zero_grads=first_micro)
     else:
         loss = eng.forward(images, nz, want_grad=True)
@@ -193,7 +199,7 @@ def training_step(state: TrainState, batch, noise=None) -> Tuple[TrainState, Dic
     state.micro_step += 1
     lr = lr_schedule(state.step, state.cfg)                          # hyperparams["learning_rate"] (:159)
     if state.micro_step == accum:                                    # :149-158
-        if world > 1:
+        if world > 1 and not reduced:
             state.reducer.all_reduce_grads()                         # lax.pmean(grads) (:150); 1/world below
         eng.adamw_step(state.step, lr, grad_scale=1.0 / (accum * world))
         state.step += 1

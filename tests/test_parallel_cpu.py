@@ -52,7 +52,12 @@ def _worker(rank, world, port, out_dir):
         views[path].copy_(g.float())
     red = GradReducer(store, bucket_mb=1)
     red.ranges = bucket_ranges(store.total, 4096)          # force many buckets
-    red.all_reduce_grads()
+    # reduce in two pieces through the range API (what the overlapped backward uses), then nothing is left
+    half = store.total // 2 // 64 * 64
+    red.bucket_elems = 4096
+    red.all_reduce_ranges([(half, store.total)])
+    red.all_reduce_ranges([(0, half)])
+    red.join()
     loss_t = torch.tensor([float(rank + 1)])
     red.mean_scalar(loss_t)
     torch.save({"g": store.g.clone(), "loss": loss_t}, os.path.join(out_dir, f"rank{rank}.pt"))

@@ -57,3 +57,20 @@ def test_lr_schedule_matches_oracle():
     for count in (0, 1, 100, cfg.warmup_steps - 1, cfg.warmup_steps, cfg.warmup_steps + 1, 250000, cfg.training_steps,
                   cfg.training_steps + 5):
         assert lr_schedule(count, cfg) == O.lr_schedule(count, ocfg)
+
+
+def test_backward_segment_ranges_partition_the_gradient_buffer():
+    """Data-parallel overlap: the per-segment all-reduce ranges are disjoint and cover every leaf once."""
+    from jumbo_mae_tpu_b200.engine import MAEEngine
+    for cfg in (vit_b16(), _pc(O.tiny())):
+        store = ParamStore(cfg, device="meta")
+        eng = MAEEngine.__new__(MAEEngine)          # no device buffers: only the host-side planning is exercised
+        eng.cfg, eng.ps = cfg, store
+        seen = []
+        for k in range(eng.num_bwd_segments()):
+            seen += eng.segment_grad_ranges(k)
+        seen.sort()
+        assert all(a[1] <= b[0] for a, b in zip(seen, seen[1:]))
+        assert sum(e - s for s, e in seen) == store.total
+        layers = [i for k in range(1, eng.num_bwd_segments()) for i in eng._enc_segment_layers(k)]
+        assert layers == list(reversed(range(cfg.layers)))

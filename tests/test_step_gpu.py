@@ -225,3 +225,19 @@ def test_cuda_graph_path_equals_eager():
     assert torch.allclose(store.g, g_e, rtol=1e-4, atol=1e-7)
     eng.run_graph(im, nz, zero_grads=False)
     assert torch.allclose(store.g, 2 * g_e, rtol=1e-4, atol=1e-7)
+
+
+def test_segmented_backward_graphs_equal_whole_backward():
+    """The data-parallel path replays forward + backward as one graph per segment (gradient all-reduces start
+    between them); on one rank it must produce the same gradients as the single-graph path."""
+    from jumbo_mae_tpu_b200.parallel import GradReducer
+    ocfg, cfg, state, images, noise, store, eng = _setup("mid")
+    im, nz = images.cuda(), torch.from_numpy(noise).cuda()
+    eng.run_graph(im, nz, zero_grads=True)
+    g_ref = store.g.clone()
+    red = GradReducer(store)
+    loss = eng.run_graph_overlapped(im, nz, True, red)
+    torch.cuda.synchronize()
+    assert torch.allclose(store.g, g_ref, rtol=1e-4, atol=1e-7)
+    assert torch.isfinite(loss).all()
+    assert eng.num_bwd_segments() == 1 + (cfg.layers + eng.ENC_LAYERS_PER_SEGMENT - 1) // eng.ENC_LAYERS_PER_SEGMENT
