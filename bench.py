@@ -167,6 +167,7 @@ def workload_config(args, micro, accum, world):
 def run_ours(args):
     from jumbo_mae_tpu_b200 import _lib, ops
     from jumbo_mae_tpu_b200 import parallel
+    from jumbo_mae_tpu_b200.config import flops_per_image
     from jumbo_mae_tpu_b200.engine import lr_schedule
     from jumbo_mae_tpu_b200.pretraining import create_train_state, training_step
 
