@@ -198,6 +198,17 @@ __device__ __forceinline__ void tmem_ld_32x32(uint32_t taddr, uint32_t (&r)[32])
 }
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
+// Register re-balancing between warpgroups (4 aligned warps): the data-movement warps give registers back,
+// the epilogue warps take them.  All warps of the warpgroup must execute the instruction.
+template <int N>
+__device__ __forceinline__ void setmaxnreg_inc() {
+  asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(N));
+}
+template <int N>
+__device__ __forceinline__ void setmaxnreg_dec() {
+  asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(N));
+}
+
 // ---- cta_group::2 (CTA pair) variants: one MMA spans two SMs; the leader CTA issues it.
 __device__ __forceinline__ uint32_t cluster_ctarank() {
   uint32_t r;

@@ -1,11 +1,11 @@
 // tcgen05 / TMEM / TMA GEMM for sm_100a with fused epilogues.
 //
-// One persistent CTA per SM, 256 threads, warp-specialised:
-//   warp 0      TMA producer   (one elected lane; cp.async.bulk.tensor into a SWIZZLE_128B ring)
-//   warp 1      MMA issuer     (one elected lane; tcgen05.mma 128 x BN x 16, accumulators in TMEM)
-//   warp 2      TMEM allocator (2 x BN f32 columns: the accumulator is double-buffered so the
-//                               epilogue of tile i overlaps the MMAs of tile i+1)
-//   warps 4..7  epilogue       (tcgen05.ld 32 lanes x 32 columns -> registers -> fused epilogue -> global)
+// One persistent CTA per SM, 18 warps (576 threads: 112 registers each), warp-specialised:
+//   warp 0       TMA producer   (one elected lane; cp.async.bulk.tensor into a SWIZZLE_128B ring)
+//   warp 1       MMA issuer     (one elected lane; tcgen05.mma 128 x BN x 16, accumulators in TMEM) and TMEM
+//                allocator (2 x BN f32 columns: the accumulator is double-buffered so the epilogue of
+//                tile i overlaps the MMAs of tile i+1)
+//   warps 2..17  epilogue       (tcgen05.ld -> registers -> fused epilogue -> staging transpose -> global)
 // Pipelines: smem full/empty mbarriers (TMA <-> MMA), TMEM full/empty mbarriers (MMA <-> epilogue).
 //
 // Operand majors: both A and B may be K-major ([rows, K] row-major) or MN-major ([K, rows]
@@ -25,16 +25,23 @@ namespace jm {
 constexpr int BM = 128;
 constexpr int BK = 64;  // 64 bf16 = 128 bytes = one SWIZZLE_128B row
 constexpr int UMMA_K = 16;
-constexpr int kEpiWarp0 = 4;
+constexpr int kEpiWarp0 = 4;  // warps 0..3 form the warpgroup that hands its registers to the epilogue warps
 constexpr int kEpiWarps = 16;  // four per TMEM lane quarter, each takes a quarter of the tile's columns
 constexpr int kGemmThreads = (kEpiWarp0 + kEpiWarps) * 32;
+// 640 threads launch with 96 registers each (five warps per scheduler share 16 K registers).  Warps 0..3
+// only move data: they shrink, and every scheduler's four epilogue warps grow by what its one warp released
+// (the pool is the CTA's own allocation: 4 x 32 x (INC - 96) <= 32 x (96 - DEC)).
+#ifndef JM_GEMM_REG_DEC
+#define JM_GEMM_REG_DEC 32
+#define JM_GEMM_REG_INC 112
+#endif
+static_assert(4 * (JM_GEMM_REG_INC - 96) <= 96 - JM_GEMM_REG_DEC, "setmaxnreg pool exceeded");
 constexpr int kStageRowBytes = 64;                     // 16 f32 columns
 constexpr int kStageBytesPerWarp = 32 * kStageRowBytes;  // 32 rows
 
 struct GemmShape {
   int M, N, K;
   int num_m, num_n, splits, kblocks;
-  int pf_dist, pf_a, pf_b;  // L2 prefetch: k-blocks of lookahead, and which operands are streamed from DRAM
 };
 
 struct EpiParams {
@@ -286,7 +293,7 @@ __device__ __forceinline__ void epilogue_role(const EpiParams& ep, const GemmSha
                                               uint64_t* tfull, uint64_t* tempty, uint32_t tmem_base, int warp,
                                               int lane, int total_tiles, int tile0, int tile_step, int m_off) {
   const int e = warp - kEpiWarp0;
-  const int q = e & 3;      // TMEM lane quarter == warp % 4
+  const int q = warp & 3;   // TMEM lane quarter == warp % 4 (a hardware rule); (q, part) still enumerates the 16 warps
   const int part = e >> 2;  // which quarter of the tile's columns
   constexpr int PART_N = BN / 4;
   constexpr int NSUB = PART_N / 16;
@@ -416,6 +423,229 @@ __device__ __forceinline__ void epilogue_role(const EpiParams& ep, const GemmSha
   }
 }
 
+// Row-register epilogue for the kinds whose only per-element output is bf16 (EPI_BF16, EPI_GELU_FWD,
+// EPI_GELU_BWD).  The arithmetic runs in the TMEM layout (one thread = one accumulator row, 32 columns at a
+// time), the results are packed to bf16 and only then transposed through the warp's 2 KB staging tile
+// (32 rows x 64 bytes, XOR-swizzled 16-byte chunks), so that
+//   * a warp store instruction covers 8 rows x 64 contiguous bytes (8 L1 tags instead of the 32 of a
+//     32 x 16 sub-chunk: the store rate, not DRAM, bounded the old path),
+//   * the dependent chain per 32 columns is TMEM load -> FMA/pack -> STS -> LDS -> STG with no global load
+//     in it: the bias of the warp's columns sits one value per lane in a register (loaded before the
+//     accumulator wait) and is broadcast with shuffles; the GELU-backward pre-activations are loaded
+//     coalesced before the wait and handed to the row threads through the same staging tile,
+//   * the second TMEM load of a 64-column part is in flight while the first half is stored.
+template <int EPI, int BN, int CG>
+__device__ __forceinline__ void epilogue_rows(const EpiParams& ep, const GemmShape& sh, uint8_t* sEpi,
+                                              uint64_t* tfull, uint64_t* tempty, uint32_t tmem_base, int warp,
+                                              int lane, int total_tiles, int tile0, int tile_step, int m_off) {
+  constexpr int NH = (BN == 256) ? 2 : 1;   // 32-column halves per warp
+  constexpr int PARTS = BN / (32 * NH);     // column parts per tile: 4, 4, 2 (BN = 64: half the warps idle)
+  constexpr uint32_t kFull = 0xffffffffu;
+  const int e = warp - kEpiWarp0;
+  const int q = warp & 3;   // TMEM lane quarter == warp % 4 (a hardware rule); (q, part) still enumerates the 16 warps
+  const int part = e >> 2;
+  const uint32_t stage_addr = smem_u32(sEpi + e * kStageBytesPerWarp);
+  // row view: lane = row, chunk j at ((j ^ sw) << 4); coalesced view: 4 lanes per row, 8 rows per instruction
+  const uint32_t own_addr = stage_addr + lane * 64;
+  const uint32_t own_sw = (lane >> 1) & 3;
+  const int crow = lane >> 2, cch = lane & 3;
+  const uint32_t co_addr = stage_addr + crow * 64 + ((cch ^ ((crow >> 1) & 3)) << 4);  // + i * 512 for row 8 i + crow
+  const int tiles_mn = sh.num_m * sh.num_n;
+  const bool has_bias = ep.bias != nullptr;
+  int iter = 0;
+  for (int t = tile0; t < total_tiles; t += tile_step, ++iter) {
+    const int rem = t % tiles_mn;
+    const int m_blk = rem / sh.num_n, n_blk = rem - m_blk * sh.num_n;
+    const int acc = iter & 1;
+    const uint32_t acc_phase = (iter >> 1) & 1;
+    auto release = [&]() {
+      tc_fence_before();
+      if constexpr (CG == 1) mbar_arrive(&tempty[acc]);
+      else mbar_arrive_cluster(mapa_shared(smem_u32(&tempty[acc]), 0));  // the leader CTA issues the MMAs
+    };
+    if constexpr (PARTS < 4) {
+      if (part >= PARTS) {  // keep in lock-step with the accumulator hand-over
+        mbar_wait(&tfull[acc], acc_phase);
+        tc_fence_after();
+        release();
+        continue;
+      }
+    }
+    const int row_base = m_blk * (BM * CG) + m_off + q * 32;
+    const int colp = n_blk * BN + part * (32 * NH);
+    uint32_t zmask = 0xffffffffu;  // 0 for a row that stores zeros (row_mask_mode 1)
+    uint32_t st_mask = 0;
+    {
+      const bool masked = ep.row_period > 0;
+      if (masked && ep.row_mask_mode == 1 && ((row_base + lane) % ep.row_period) < ep.row_skip) zmask = 0u;
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int row = row_base + 8 * i + crow;
+        bool st = row < sh.M;
+        if (masked && ep.row_mask_mode == 2 && (row % ep.row_period) < ep.row_skip) st = false;
+        st_mask |= (st ? 1u : 0u) << i;
+      }
+    }
+    float bs[NH], sc[NH];
+    uint4 ax[4];
+    auto load_aux = [&](int colh) {  // this lane's 4 coalesced 16-byte chunks of the pre-activation
+      const int col = colh + 8 * cch;
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        ax[i] = make_uint4(0u, 0u, 0u, 0u);
+        if (((st_mask >> i) & 1u) && col < sh.N)
+          ax[i] = *reinterpret_cast<const uint4*>(ep.aux + static_cast<long>(row_base + 8 * i + crow) * ep.ldaux + col);
+      }
+    };
+#pragma unroll
+    for (int h = 0; h < NH; ++h) {
+      const int colh = colp + 32 * h;
+      sc[h] = colh < ep.col_scale_n ? ep.col_scale : 1.f;
+      bs[h] = (has_bias && colh + lane < sh.N) ? __ldg(ep.bias + colh + lane) * sc[h] : 0.f;
+    }
+    if constexpr (EPI == EPI_GELU_BWD) load_aux(colp);
+    mbar_wait(&tfull[acc], acc_phase);
+    tc_fence_after();
+    const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * BN + part * (32 * NH);
+    uint32_t r[NH][32];
+    if (colp < sh.N) tmem_ld_32x32(t_addr, r[0]);  // warp-uniform
+    tmem_ld_wait();
+    if constexpr (NH == 1) release();
+#pragma unroll
+    for (int h = 0; h < NH; ++h) {
+      const int colh = colp + 32 * h;
+      const bool live = colh < sh.N;  // warp-uniform
+      uint32_t G[16];
+      if (live) {
+        if constexpr (EPI == EPI_GELU_BWD) {
+          // pre-activations: coalesced registers -> staging -> row threads; results overwrite them in place
+#pragma unroll
+          for (int i = 0; i < 4; ++i)
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(co_addr + i * 512), "r"(ax[i].x),
+                         "r"(ax[i].y), "r"(ax[i].z), "r"(ax[i].w)
+                         : "memory");
+          __syncwarp();
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const uint32_t a = own_addr + ((j ^ own_sw) << 4);
+            uint32_t w[4], o[4];
+            asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];"
+                         : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3])
+                         : "r"(a)
+                         : "memory");
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+              const float2 x = unpack_bf16(w[k]);
+              const float v0 = __uint_as_float(r[h][8 * j + 2 * k]) * gelu_grad_fast(x.x);
+              const float v1 = __uint_as_float(r[h][8 * j + 2 * k + 1]) * gelu_grad_fast(x.y);
+              o[k] = pack_bf16(v0, v1) & zmask;
+            }
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(o[0]), "r"(o[1]), "r"(o[2]),
+                         "r"(o[3])
+                         : "memory");
+          }
+        } else {
+          // branch-free: masked rows are zeroed with an AND, so the 32 columns stay one basic block
+          uint32_t P[16];
+          float v[32];
+          if (has_bias) {  // warp-uniform
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+              v[j] = fmaf(__uint_as_float(r[h][j]), sc[h], __shfl_sync(kFull, bs[h], j));
+          } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[h][j]) * sc[h];
+          }
+#pragma unroll
+          for (int j = 0; j < 16; ++j) {
+            P[j] = pack_bf16(v[2 * j], v[2 * j + 1]) & zmask;
+            if constexpr (EPI == EPI_GELU_FWD) G[j] = pack_bf16(gelu_fast(v[2 * j]), gelu_fast(v[2 * j + 1])) & zmask;
+          }
+#pragma unroll
+          for (int j = 0; j < 4; ++j)
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(own_addr + ((j ^ own_sw) << 4)),
+                         "r"(P[4 * j]), "r"(P[4 * j + 1]), "r"(P[4 * j + 2]), "r"(P[4 * j + 3])
+                         : "memory");
+        }
+      }
+      if constexpr (NH == 2) {
+        if (h == 0 && colp + 32 < sh.N) {  // both in flight during the stores below
+          if constexpr (EPI == EPI_GELU_BWD) load_aux(colp + 32);
+          tmem_ld_32x32(t_addr + 32, r[1]);
+        }
+      }
+      constexpr int NOUT = (EPI == EPI_GELU_FWD) ? 2 : 1;
+#pragma unroll
+      for (int o = 0; o < NOUT; ++o) {
+        if (o == 1 && live) {
+#pragma unroll
+          for (int j = 0; j < 4; ++j)
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(own_addr + ((j ^ own_sw) << 4)),
+                         "r"(G[4 * j]), "r"(G[4 * j + 1]), "r"(G[4 * j + 2]), "r"(G[4 * j + 3])
+                         : "memory");
+        }
+        __syncwarp();
+        if (live) {
+          __nv_bfloat16* out = (o == 0) ? ep.out_bf16 : ep.out2_bf16;
+          const long ldo = (o == 0) ? ep.ldo_bf16 : ep.ldo2_bf16;
+          const int col = colh + 8 * cch;
+          const bool cl = col < sh.N;
+          float cs[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            uint4 v;
+            asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];"
+                         : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+                         : "r"(co_addr + i * 512)
+                         : "memory");
+            if (cl && ((st_mask >> i) & 1u)) {
+              *reinterpret_cast<uint4*>(out + static_cast<long>(row_base + 8 * i + crow) * ldo + col) = v;
+              if constexpr (EPI == EPI_GELU_BWD) {
+                const float2 a = unpack_bf16(v.x), b = unpack_bf16(v.y), c = unpack_bf16(v.z), d = unpack_bf16(v.w);
+                cs[0] += a.x, cs[1] += a.y, cs[2] += b.x, cs[3] += b.y;
+                cs[4] += c.x, cs[5] += c.y, cs[6] += d.x, cs[7] += d.y;
+              }
+            }
+          }
+          if constexpr (EPI == EPI_GELU_BWD) {
+            if (ep.colsum != nullptr) {  // warp-uniform: fold the 8 row-lanes, one atomic per column
+#pragma unroll
+              for (int j = 0; j < 8; ++j) {
+                cs[j] += __shfl_xor_sync(kFull, cs[j], 4);
+                cs[j] += __shfl_xor_sync(kFull, cs[j], 8);
+                cs[j] += __shfl_xor_sync(kFull, cs[j], 16);
+              }
+              if (crow == 0 && cl) {  // two 16-byte vector reductions per lane instead of eight scalar ones
+                atomicAdd(reinterpret_cast<float4*>(ep.colsum + col), make_float4(cs[0], cs[1], cs[2], cs[3]));
+                atomicAdd(reinterpret_cast<float4*>(ep.colsum + col + 4), make_float4(cs[4], cs[5], cs[6], cs[7]));
+              }
+            }
+          }
+        }
+        __syncwarp();
+      }
+      if constexpr (NH == 2) {
+        if (h == 0) {
+          tmem_ld_wait();
+          release();
+        }
+      }
+    }
+  }
+}
+
+template <int EPI, int BN, int CG>
+__device__ __forceinline__ void run_epilogue(const EpiParams& ep, const GemmShape& sh, uint8_t* sEpi,
+                                             uint64_t* tfull, uint64_t* tempty, uint32_t tmem_base, int warp,
+                                             int lane, int total_tiles, int tile0, int tile_step, int m_off) {
+  if constexpr (EPI == EPI_BF16 || EPI == EPI_GELU_FWD || EPI == EPI_GELU_BWD)
+    epilogue_rows<EPI, BN, CG>(ep, sh, sEpi, tfull, tempty, tmem_base, warp, lane, total_tiles, tile0, tile_step,
+                               m_off);
+  else
+    epilogue_role<EPI, BN, CG>(ep, sh, sEpi, tfull, tempty, tmem_base, warp, lane, total_tiles, tile0, tile_step,
+                               m_off);
+}
+
 template <int BN, bool A_MN, bool B_MN, int EPI>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmShape sh,
@@ -442,7 +672,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
   }
-  if (warp == 1 && elect_one()) {
+  if (warp == 0 && elect_one()) {
     for (int s = 0; s < STAGES; ++s) {
       mbar_init(&full[s], 1);
       mbar_init(&empty[s], 1);
@@ -453,7 +683,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     }
     fence_barrier_init();
   }
-  if (warp == 2) tmem_alloc<Cfg::TMEM_COLS>(tmem_ptr);
+  if (warp == 1) tmem_alloc<Cfg::TMEM_COLS>(tmem_ptr);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -462,48 +692,11 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   const int tiles_mn = sh.num_m * sh.num_n;
   const int total_tiles = tiles_mn * sh.splits;
 
+  if (warp < kEpiWarp0) setmaxnreg_dec<JM_GEMM_REG_DEC>();
   if (warp == 0) {
     if (elect_one()) {
       int stage = 0;
       uint32_t phase = 0;
-      // L2 prefetch cursor: runs kPfDist k-blocks ahead of the load cursor through this CTA's (tile, k-block)
-      // sequence, so that a streamed operand is already in L2 when the ring asks for it.
-      const int pf_dist = sh.pf_dist;
-      int pt = blockIdx.x, pkb = -1, pkb1 = 0, pm = 0, pn = 0, ahead = 0;
-      auto pf_tile = [&]() {
-        if (pt < total_tiles) {
-          const int split = pt / tiles_mn;
-          const int rem = pt - split * tiles_mn;
-          pm = rem / sh.num_n, pn = rem - pm * sh.num_n;
-          pkb = static_cast<int>(static_cast<long>(sh.kblocks) * split / sh.splits);
-          pkb1 = static_cast<int>(static_cast<long>(sh.kblocks) * (split + 1) / sh.splits);
-        }
-      };
-      auto pf_step = [&]() {  // prefetch one k-block and advance the cursor
-        if (pt >= total_tiles) return;
-        if (sh.pf_a) {
-          if (!A_MN) tma_prefetch_2d(&tmA, pkb * BK, pm * BM);
-          else {
-#pragma unroll
-            for (int i = 0; i < BM / 64; ++i) tma_prefetch_2d(&tmA, pm * BM + i * 64, pkb * BK);
-          }
-        }
-        if (sh.pf_b) {
-          if (!B_MN) tma_prefetch_2d(&tmB, pkb * BK, pn * BN);
-          else {
-#pragma unroll
-            for (int i = 0; i < BN / 64; ++i) tma_prefetch_2d(&tmB, pn * BN + i * 64, pkb * BK);
-          }
-        }
-        if (++pkb == pkb1) {
-          pt += gridDim.x;
-          pf_tile();
-        }
-      };
-      if (pf_dist > 0) {
-        pf_tile();
-        for (; ahead < pf_dist; ++ahead) pf_step();
-      }
       for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
         const int split = t / tiles_mn;
         const int rem = t - split * tiles_mn;
@@ -511,7 +704,6 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         const int kb0 = static_cast<int>(static_cast<long>(sh.kblocks) * split / sh.splits);
         const int kb1 = static_cast<int>(static_cast<long>(sh.kblocks) * (split + 1) / sh.splits);
         for (int kb = kb0; kb < kb1; ++kb) {
-          if (pf_dist > 0) pf_step();
           mbar_wait(&empty[stage], phase ^ 1);
           mbar_arrive_expect_tx(&full[stage], Cfg::STAGE_BYTES);
           uint8_t* a_dst = sA + stage * Cfg::A_BYTES;
@@ -572,13 +764,14 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       }
     }
   } else if (warp >= kEpiWarp0) {
-    epilogue_role<EPI, BN, 1>(ep, sh, sEpi, tfull, tempty, tmem_base, warp, lane, total_tiles, blockIdx.x,
-                              gridDim.x, 0);
+    setmaxnreg_inc<JM_GEMM_REG_INC>();
+    run_epilogue<EPI, BN, 1>(ep, sh, sEpi, tfull, tempty, tmem_base, warp, lane, total_tiles, blockIdx.x,
+                             gridDim.x, 0);
   }
 
   tc_fence_before();
   __syncthreads();
-  if (warp == 2) tmem_dealloc<Cfg::TMEM_COLS>(tmem_base);
+  if (warp == 1) tmem_dealloc<Cfg::TMEM_COLS>(tmem_base);
 }
 
 // ---------------------------------------------------------------- CTA-pair (cta_group::2) kernel
@@ -637,7 +830,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
   }
-  if (warp == 1 && elect_one()) {
+  if (warp == 0 && elect_one()) {
     for (int s = 0; s < STAGES; ++s) {
       mbar_init(&full[s], 2);   // one arrive per CTA's producer (the leader's carries the byte count)
       mbar_init(&empty[s], 1);  // one multicast commit
@@ -648,7 +841,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
     }
     fence_barrier_init();
   }
-  if (warp == 2) tmem_alloc2<Cfg::TMEM_COLS>(tmem_ptr);
+  if (warp == 1) tmem_alloc2<Cfg::TMEM_COLS>(tmem_ptr);
   tc_fence_before();
   cluster_sync_all();  // peer barriers initialised, TMEM allocated in both CTAs
   tc_fence_after();
@@ -657,6 +850,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
   const int tiles_mn = sh.num_m * sh.num_n;  // num_m counts 256-row pair tiles here
   const int total_tiles = tiles_mn * sh.splits;
 
+  if (warp < kEpiWarp0) setmaxnreg_dec<JM_GEMM_REG_DEC>();
   if (warp == 0) {
     if (elect_one()) {
       int stage = 0;
@@ -731,13 +925,14 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
       }
     }
   } else if (warp >= kEpiWarp0) {
-    epilogue_role<EPI, BN, 2>(ep, sh, sEpi, tfull, tempty, tmem_base, warp, lane, total_tiles, pair, npairs,
+    setmaxnreg_inc<JM_GEMM_REG_INC>();
+    run_epilogue<EPI, 256, 2>(ep, sh, sEpi, tfull, tempty, tmem_base, warp, lane, total_tiles, pair, npairs,
                               rank * BM);
   }
 
   tc_fence_before();
   cluster_sync_all();  // no CTA may exit (or free TMEM) while its peer can still signal it or read its operands
-  if (warp == 2) tmem_dealloc2<Cfg::TMEM_COLS>(tmem_base);
+  if (warp == 1) tmem_dealloc2<Cfg::TMEM_COLS>(tmem_base);
 }
 
 // ---------------------------------------------------------------- host side
@@ -966,15 +1161,7 @@ extern "C" int jm_gemm(const jm_gemm_args* a, void* stream_) {
     if (make_tmap(&tmB, a->B, a->N, a->K, a->ldb, 64, BK)) return 1;
   }
 
-  // Operands larger than ~a quarter of L2 are streamed from DRAM once: prefetch them into L2 ahead of the ring.
-  static int pf_env = -1;
-  if (pf_env < 0) {
-    const char* e = getenv("JM_GEMM_PF");
-    pf_env = e ? atoi(e) : 0;  // measured: no gain on B200 (the ring is not DRAM-latency bound), off by default
-  }
-  const double a_bytes = 2.0 * a->M * a->K, b_bytes = 2.0 * a->N * a->K;
-  const int pf_a = a_bytes > 24e6 ? 1 : 0, pf_b = b_bytes > 24e6 ? 1 : 0;
-  GemmShape sh{a->M, a->N, a->K, num_m_eff, num_n, splits, kblocks, (pf_a || pf_b) ? pf_env : 0, pf_a, pf_b};
+  GemmShape sh{a->M, a->N, a->K, num_m_eff, num_n, splits, kblocks};
   EpiParams ep;
   ep.out_f32 = a->out_f32, ep.ldo_f32 = a->ldo_f32;
   ep.out_bf16 = reinterpret_cast<__nv_bfloat16*>(a->out_bf16), ep.ldo_bf16 = a->ldo_bf16;
@@ -996,10 +1183,15 @@ extern "C" int jm_gemm(const jm_gemm_args* a, void* stream_) {
   int epi = EPI_GENERIC;
   const bool only_bf16 = ep.out_bf16 && !ep.out_f32 && !ep.out2_bf16;
   const bool only_f32 = ep.out_f32 && !ep.out_bf16 && !ep.out2_bf16;
-  if (ep.act == 1 && ep.out_bf16 && ep.out2_bf16 && !ep.out_f32 && !ep.residual && !ep.pe) epi = EPI_GELU_FWD;
-  else if (ep.act == 2 && only_bf16 && !ep.residual && !ep.pe) epi = EPI_GELU_BWD;
+  // the row-register epilogues work on whole 16-byte column chunks and a per-32-column scale
+  const bool rows_ok = a->N % 8 == 0 && ep.col_scale_n % 32 == 0;
+  if (ep.act == 1 && ep.out_bf16 && ep.out2_bf16 && !ep.out_f32 && !ep.residual && !ep.pe && rows_ok)
+    epi = EPI_GELU_FWD;
+  else if (ep.act == 2 && only_bf16 && !ep.residual && !ep.pe && rows_ok && !ep.bias && ep.col_scale_n == 0 &&
+           (reinterpret_cast<uintptr_t>(ep.colsum) & 15) == 0)
+    epi = EPI_GELU_BWD;
   else if (ep.act == 0 && only_f32 && !ep.colsum) epi = EPI_F32;
-  else if (ep.act == 0 && only_bf16 && !ep.residual && !ep.pe && !ep.colsum) epi = EPI_BF16;
+  else if (ep.act == 0 && only_bf16 && !ep.residual && !ep.pe && !ep.colsum && rows_ok) epi = EPI_BF16;
   if (pair) {
     if (amn && epi != EPI_F32) epi = EPI_GENERIC;
     return dispatch_pair(amn, bmn, epi, tmA, tmB, sh, ep, grid, stream);

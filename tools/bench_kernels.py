@@ -11,6 +11,7 @@ from jumbo_mae_tpu_b200 import ops  # noqa: E402
 BF16 = torch.bfloat16
 B = int(os.environ.get("B", "512"))
 ONLY = os.environ.get("ONLY", "")
+BN = int(os.environ.get("BN", "0"))
 
 
 def timeit(fn, reps=20, warm=3):
@@ -72,13 +73,13 @@ def run_gemm(name, M, N, K, kind):
         W = r(K, N)
         if kind == "fwd_bf16":
             o = torch.empty(M, N, dtype=BF16, device="cuda")
-            return lambda: ops.gemm(A, W, M, N, K, b_mn=True, out_bf16=o, bias=bias, col_scale=0.125, col_scale_n=N // 3)
+            return lambda: ops.gemm(A, W, M, N, K, b_mn=True, out_bf16=o, bias=bias, col_scale=0.125, col_scale_n=N // 3, block_n=BN)
         if kind == "fwd_gelu":
             h, g = torch.empty(M, N, dtype=BF16, device="cuda"), torch.empty(M, N, dtype=BF16, device="cuda")
-            return lambda: ops.gemm(A, W, M, N, K, b_mn=True, out_bf16=h, out2_bf16=g, bias=bias, act=1)
+            return lambda: ops.gemm(A, W, M, N, K, b_mn=True, out_bf16=h, out2_bf16=g, bias=bias, act=1, block_n=BN)
         if kind == "fwd_res":
             res, o = torch.zeros(M, N, device="cuda"), torch.empty(M, N, device="cuda")
-            return lambda: ops.gemm(A, W, M, N, K, b_mn=True, out_f32=o, bias=bias, residual=res)
+            return lambda: ops.gemm(A, W, M, N, K, b_mn=True, out_f32=o, bias=bias, residual=res, block_n=BN)
         o = torch.empty(M, N, device="cuda")
         return lambda: ops.gemm(A, W, M, N, K, b_mn=True, out_f32=o, bias=bias)
     W = r(N, K)
@@ -87,7 +88,7 @@ def run_gemm(name, M, N, K, kind):
         aux = r(M, N)
         cs = torch.zeros(N, device="cuda") if os.environ.get("NO_CS") is None else None
         return lambda: ops.gemm(A, W, M, N, K, b_mn=False, out_bf16=o, aux=aux, act=2, colsum=cs)
-    return lambda: ops.gemm(A, W, M, N, K, b_mn=False, out_bf16=o)
+    return lambda: ops.gemm(A, W, M, N, K, b_mn=False, out_bf16=o, block_n=BN)
 
 
 def main():
