@@ -225,8 +225,10 @@ __device__ __forceinline__ uint32_t mapa_shared(uint32_t addr, uint32_t rank) {
   asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank));
   return r;
 }
+// Relaxed: the callers order their tcgen05 / TMEM accesses with tcgen05 fences and publish no generic-memory
+// data through the barrier (a .release arrive at cluster scope compiles to a GPU-wide MEMBAR per call).
 __device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
-  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+  asm volatile("mbarrier.arrive.relaxed.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
 }
 template <uint32_t kCols>
 __device__ __forceinline__ void tmem_alloc2(uint32_t* dst_in_smem) {  // one whole warp in EACH CTA of the pair

@@ -780,7 +780,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
 // tensor cores, each reading its local A and both halves of B.  Per CTA and k-block that is 32 KB of TMA
 // writes and 32 KB of operand reads instead of 48 + 48: the single-CTA kernel is bound by exactly that
 // shared-memory / L2-to-SM traffic (a 128 x 256 x 16 MMA consumes 96 B/clk of operands at full rate).
-// Barriers: `full` lives in the leader (both producers arrive, both CTAs' TMA bytes complete on it);
+// Barriers: `full` lives in the leader (its producer arrives, both CTAs' TMA bytes complete on it);
 // `empty` and `tfull` are signalled in both CTAs by multicast commits; `tempty` lives in the leader and is
 // arrived on by the epilogue threads of both CTAs.
 struct Gemm2Cfg {
@@ -832,7 +832,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
   }
   if (warp == 0 && elect_one()) {
     for (int s = 0; s < STAGES; ++s) {
-      mbar_init(&full[s], 2);   // one arrive per CTA's producer (the leader's carries the byte count)
+      mbar_init(&full[s], 1);   // the leader's producer arrives with the byte count of BOTH CTAs' loads
       mbar_init(&empty[s], 1);  // one multicast commit
     }
     for (int a = 0; a < 2; ++a) {
@@ -865,8 +865,9 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
         const int n0 = n_blk * BN + rank * (BN / 2);
         for (int kb = kb0; kb < kb1; ++kb) {
           mbar_wait(&empty[stage], phase ^ 1);
+          // the peer's bytes may land before this arrive: the transaction count then runs negative until it
+          // does, and the phase cannot complete without the arrival
           if (rank == 0) mbar_arrive_expect_tx(&full[stage], 2 * Cfg::STAGE_BYTES);
-          else mbar_arrive_cluster(mapa_shared(smem_u32(&full[stage]), 0));
           uint8_t* a_dst = sA + stage * Cfg::A_BYTES;
           uint8_t* b_dst = sB + stage * Cfg::B_BYTES;
           if (!A_MN) {
@@ -1014,6 +1015,19 @@ static int launch_gemm2(const CUtensorMap& tmA, const CUtensorMap& tmB, const Ge
         policy == 1 ? cudaClusterSchedulingPolicySpread : cudaClusterSchedulingPolicyLoadBalancing;
     cfg.numAttrs = 2;
   }
+  // A persistent grid must not exceed the clusters the GPU can hold at once (GPCs with an odd SM left over
+  // cannot host a pair there): surplus clusters would run as a second wave.
+  static int max_clusters = 0;
+  if (max_clusters == 0) {
+    int n = 0;
+    JM_CUDA(cudaOccupancyMaxActiveClusters(&n, kern, &cfg));
+    JM_CHECK(n > 0, "jm_gemm: the CTA-pair kernel cannot be scheduled on this device");
+    if (getenv("JM_PAIR_VERBOSE")) fprintf(stderr, "jm: pair kernel max active clusters = %d\n", n);
+    max_clusters = n;
+  }
+  if (grid > 2 * max_clusters) {
+    cfg.gridDim = dim3(2 * max_clusters);
+  }
   JM_CUDA(cudaLaunchKernelEx(&cfg, kern, tmA, tmB, sh, ep));
   count_launch();
   return 0;
@@ -1127,13 +1141,22 @@ extern "C" int jm_gemm(const jm_gemm_args* a, void* stream_) {
   JM_CHECK(splits == 1 || can_split, "jm_gemm: split-K needs a pure accumulate epilogue");
   JM_CHECK(splits <= kblocks, "jm_gemm: more splits (%d) than k-blocks (%d)", splits, kblocks);
 
-  // CTA-pair kernel (256 x 256 tiles, cta_group::2) whenever the 256-wide tile was chosen and M fills a pair
+  // CTA-pair kernel (256 x 256 tiles, cta_group::2): each CTA stages only half of B, which relieves the
+  // shared-memory / L2-to-SM traffic the 128 x 256 single-CTA tile is bound by.  Default whenever the 256-wide
+  // tile was chosen, the operand layout has an instantiation and M spans more than one CTA.
   const bool amn = a->a_mn_major != 0, bmn = a->b_mn_major != 0;
-  // (measured slower than the single-CTA kernel so far, see DESIGN.md: only on request)
+  const bool pair_ok = bn == 256 && !(amn && !bmn) && a->M > BM;
   bool pair = false;
   if (a->cta_pair > 0) {
-    JM_CHECK(bn == 256 && !(amn && !bmn), "jm_gemm: cta_pair needs block_n 256 and a supported operand layout");
+    JM_CHECK(pair_ok, "jm_gemm: cta_pair needs block_n 256, M > 128 and a supported operand layout");
     pair = true;
+  } else if (a->cta_pair == 0) {
+    static int auto_pair = -1;
+    if (auto_pair < 0) {
+      const char* e = getenv("JM_GEMM_PAIR");
+      auto_pair = e ? (atoi(e) != 0) : 1;
+    }
+    pair = pair_ok && auto_pair;
   }
   int num_m_eff = num_m;
   if (pair) {

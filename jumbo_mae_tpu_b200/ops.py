@@ -169,7 +169,7 @@ def gemm(A: torch.Tensor, B: torch.Tensor, M: int, N: int, K: int, *, a_mn: bool
     a.accumulate, a.splits, a.block_n = int(accumulate), splits, block_n
     _chk(colsum, F32, "colsum")
     a.colsum = ptr(colsum)
-    a.cta_pair = int(os.environ.get("JM_GEMM_PAIR", cta_pair))
+    a.cta_pair = int(cta_pair)
     check(_lib.load().jm_gemm(ctypes.byref(a), stream_ptr()))
 
 

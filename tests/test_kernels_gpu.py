@@ -463,8 +463,7 @@ def test_attention_bwd(ops, B, T, H, hd):
 @pytest.mark.parametrize("M,N,K,a_mn,b_mn", [(256, 256, 64, False, False), (1280, 512, 512, False, True),
                                              (768, 1024, 3000, True, True), (600, 520, 200, False, True)])
 def test_gemm_cta_pair_kernel(ops, M, N, K, a_mn, b_mn):
-    """The 2-SM (cta_group::2) 256x256 kernel: same results as the single-CTA kernel (it is kept opt-in:
-    measured slower on B200 so far)."""
+    """The 2-SM (cta_group::2) 256x256 kernel against the reference product."""
     g = torch.Generator(device="cuda").manual_seed(M + N + K)
     ldn, ldk = (N + 7) // 8 * 8, (K + 7) // 8 * 8
     A = torch.randn((K, M) if a_mn else (M, ldk), generator=g, device="cuda").to(BF16)
@@ -476,3 +475,47 @@ def test_gemm_cta_pair_kernel(ops, M, N, K, a_mn, b_mn):
     ref = _gemm_ref(A, B, a_mn, b_mn)
     assert (out - ref).abs().max().item() <= 2e-5 * ref.abs().max().item() * math.sqrt(K)
 
+
+
+@pytest.mark.parametrize("bn,pair", [(64, -1), (128, -1), (256, -1), (256, 1)])
+@pytest.mark.parametrize("M,N,K", [(700, 328, 136), (1300, 512, 64)])
+def test_gemm_bf16_epilogues_every_tile_shape(ops, M, N, K, bn, pair):
+    """The row-register epilogues (plain bf16 with bias and q-scale, GELU forward, GELU backward with the fused
+    column sums) for every tile width and for the CTA-pair kernel: ragged M, N not a multiple of the tile or
+    of 32, zeroed rows (mode 1) and skipped rows (mode 2)."""
+    T, J = 13, 3
+    g = torch.Generator(device="cuda").manual_seed(M + N + bn)
+    A = torch.randn(M, K, generator=g, device="cuda").to(BF16)
+    W = (torch.randn(K, N, generator=g, device="cuda") * 0.2).to(BF16)
+    bias = torch.randn(N, generator=g, device="cuda")
+    rows = torch.arange(M, device="cuda") % T
+    keep = (rows >= J)[:, None]
+    pre = A.float() @ W.float() + bias
+    kw = dict(block_n=bn, cta_pair=pair)
+    # plain bf16: (acc + bias) * scale on the first 32*k columns, rows < J of every period left untouched
+    out = torch.full((M, N), 3.0, dtype=BF16, device="cuda")
+    ops.gemm(A, W, M, N, K, b_mn=True, out_bf16=out, bias=bias, col_scale=0.25, col_scale_n=64, row_period=T,
+             row_skip=J, row_mask_mode=2, **kw)
+    ref = pre.clone()
+    ref[:, :64] *= 0.25
+    ref = torch.where(keep, ref, torch.full_like(ref, 3.0))
+    assert torch.allclose(out.float(), ref, rtol=2 ** -7, atol=1e-3)
+    # GELU forward, masked rows zeroed
+    h = torch.empty(M, N, dtype=BF16, device="cuda")
+    gl = torch.empty(M, N, dtype=BF16, device="cuda")
+    ops.gemm(A, W, M, N, K, b_mn=True, out_bf16=h, out2_bf16=gl, bias=bias, act=1, row_period=T, row_skip=J,
+             row_mask_mode=1, **kw)
+    assert torch.allclose(h.float(), pre * keep, rtol=2 ** -7, atol=1e-3)
+    assert torch.allclose(gl.float(), O.gelu_tanh((pre * keep).cpu()).cuda(), rtol=2 ** -7, atol=2e-3)
+    # GELU backward + fused column sums
+    dY = torch.randn(M, K, generator=g, device="cuda").to(BF16)
+    W2 = (torch.randn(N, K, generator=g, device="cuda") * 0.2).to(BF16)
+    dH = torch.empty(M, N, dtype=BF16, device="cuda")
+    cs = torch.ones(N, device="cuda")
+    ops.gemm(dY, W2, M, N, K, b_mn=False, out_bf16=dH, aux=h, act=2, row_period=T, row_skip=J, row_mask_mode=1,
+             colsum=cs, **kw)
+    hh = h.float().cpu().requires_grad_(True)
+    O.gelu_tanh(hh).sum().backward()
+    ref = (dY.float() @ W2.float().t()) * hh.grad.cuda() * keep
+    assert torch.allclose(dH.float(), ref, rtol=2 ** -6, atol=2e-3)
+    assert torch.allclose(cs - 1, ref.sum(0), rtol=1e-2, atol=0.3)   # sums of bf16-rounded values over M rows
