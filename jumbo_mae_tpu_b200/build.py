@@ -20,7 +20,8 @@ NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
     "-Xcompiler", "-fPIC", "-Xptxas", "-v", "--expt-relaxed-constexpr",
 ] + (["-DJM_DEBUG_SMID"] if os.environ.get("JM_DEBUG_SMID") else []) + \
-    (["-DJM_EXP_NO_STORE"] if os.environ.get("JM_EXP_NO_STORE") else [])
+    (["-DJM_EXP_NO_STORE"] if os.environ.get("JM_EXP_NO_STORE") else []) + \
+    os.environ.get("JM_NVCC_DEFS", "").split()          # experiments: extra -D flags
 
 
 def _nvcc() -> str:

@@ -142,6 +142,22 @@ __device__ __forceinline__ void tma_load_2d(const void* desc, uint64_t* bar, voi
       : "memory");
 }
 
+// 2-D tiled store shared -> global (bulk async-group completion).  The shared-memory writes must have been
+// made visible to the async proxy (fence_proxy_async) and the issuing thread must be ordered after them.
+__device__ __forceinline__ void tma_store_2d(const void* desc, uint32_t smem_addr, int c0, int c1) {
+  asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(
+                   reinterpret_cast<uint64_t>(desc)),
+               "r"(smem_addr), "r"(c0), "r"(c1)
+               : "memory");
+}
+__device__ __forceinline__ void tma_store_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+// all but the newest N groups of this thread have finished READING their shared-memory source
+template <int N>
+__device__ __forceinline__ void tma_store_wait_read() {
+  asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
+}
+__device__ __forceinline__ void tma_store_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+
 // L2 prefetch of a 2-D tile (no shared memory, no completion tracking): hides DRAM latency for operands
 // that are streamed exactly once, so that the smem ring only has to cover the L2 latency.
 __device__ __forceinline__ void tma_prefetch_2d(const void* desc, int c0, int c1) {

@@ -44,6 +44,10 @@ struct GemmShape {
   int num_m, num_n, splits, kblocks;
 };
 
+struct GemmMaps {
+  CUtensorMap a, b, o, o2;  // operands; bf16 outputs of the row-register epilogues (TMA stores)
+};
+
 struct EpiParams {
   float* out_f32;
   long ldo_f32;
@@ -65,6 +69,7 @@ struct EpiParams {
   int row_period, row_skip, row_mask_mode;
   int accumulate;
   float* colsum;  // optional [N]: += column sums of the stored values (bias gradient of the producer Dense)
+  int tma_store;  // row-register epilogues: write the bf16 outputs with TMA stores (maps o / o2)
 };
 
 template <int BN>
@@ -72,10 +77,13 @@ struct GemmCfg {
   static constexpr int A_BYTES = BM * BK * 2;
   static constexpr int B_BYTES = BN * BK * 2;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-  static constexpr int STAGES = (BN == 256) ? 4 : ((BN == 128) ? 6 : 8);
+  // staging tiles per epilogue warp: two where a pipeline stage can be spared for them (TMA stores of one
+  // tile then overlap the arithmetic of the next), one for the 48 KB stages of the 128 x 256 tile
+  static constexpr int EPI_BUFS = (BN == 256) ? 1 : 2;
+  static constexpr int STAGES = (BN == 256) ? 4 : ((BN == 128) ? 5 : 6);
   static constexpr int TMEM_COLS = 2 * BN;
   static constexpr int BAR_BYTES = (2 * STAGES + 4) * 8 + 16;
-  static constexpr int EPI_BYTES = kEpiWarps * kStageBytesPerWarp;  // epilogue transpose staging
+  static constexpr int EPI_BYTES = kEpiWarps * kStageBytesPerWarp * EPI_BUFS;  // epilogue transpose staging
   static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + EPI_BYTES + BAR_BYTES + 1024;  // +1024: alignment
 };
 
@@ -288,7 +296,7 @@ __device__ __forceinline__ void epi_prefetch(EpiPrefetch<EPI>& pf, const EpiPara
 // (8 columns per lane, 16 rows per warp instruction): every global access is a full 16-byte vector.
 // Sixteen warps, not four or eight: one warp retires a long dependent instruction stream per sub-chunk at
 // well under one instruction per cycle, so the drain rate scales with the number of warps per scheduler.
-template <int EPI, int BN, int CG>
+template <int EPI, int BN, int CG, int NBUF>
 __device__ __forceinline__ void epilogue_role(const EpiParams& ep, const GemmShape& sh, uint8_t* sEpi,
                                               uint64_t* tfull, uint64_t* tempty, uint32_t tmem_base, int warp,
                                               int lane, int total_tiles, int tile0, int tile_step, int m_off) {
@@ -298,7 +306,7 @@ __device__ __forceinline__ void epilogue_role(const EpiParams& ep, const GemmSha
   constexpr int PART_N = BN / 4;
   constexpr int NSUB = PART_N / 16;
   constexpr bool kColsum = (EPI == EPI_GELU_BWD || EPI == EPI_GENERIC);
-  const uint32_t stage_addr = smem_u32(sEpi + e * kStageBytesPerWarp);
+  const uint32_t stage_addr = smem_u32(sEpi + e * (kStageBytesPerWarp * NBUF));
   const int rsub = lane >> 1, cu = lane & 1;
   const int tiles_mn = sh.num_m * sh.num_n;
   int iter = 0;
@@ -423,6 +431,45 @@ __device__ __forceinline__ void epilogue_role(const EpiParams& ep, const GemmSha
   }
 }
 
+// Opaque copies: ptxas otherwise re-derives loop-invariant addresses (generic->shared conversion, 64-bit
+// row * stride products) at every use instead of keeping them in a register.
+__device__ __forceinline__ uint32_t opaque(uint32_t x) {
+#ifdef JM_OPAQUE
+  asm volatile("mov.b32 %0, %0;" : "+r"(x));
+#endif
+  return x;
+}
+__device__ __forceinline__ uint64_t opaque(uint64_t x) {
+#ifdef JM_OPAQUE
+  asm volatile("mov.b64 %0, %0;" : "+l"(x));
+#endif
+  return x;
+}
+// 16-byte global store under a predicate (no branch around it)
+__device__ __forceinline__ void stg128_if(uint64_t addr, const uint4& v, uint32_t flag) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "setp.ne.b32 p, %5, 0;\n\t"
+      "@p st.global.v4.b32 [%0], {%1, %2, %3, %4};\n\t"
+      "}\n" ::"l"(addr),
+      "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w), "r"(flag)
+      : "memory");
+}
+// 16-byte shared store of v, or of zeros when `zero` is set (rows that store zeros), without a branch
+__device__ __forceinline__ void sts128_or_zero(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d,
+                                               uint32_t zero) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "setp.ne.b32 p, %5, 0;\n\t"
+      "@!p st.shared.v4.b32 [%0], {%1, %2, %3, %4};\n\t"
+      "@p st.shared.v4.b32 [%0], {%6, %6, %6, %6};\n\t"
+      "}\n" ::"r"(addr),
+      "r"(a), "r"(b), "r"(c), "r"(d), "r"(zero), "r"(0u)
+      : "memory");
+}
+
 // Row-register epilogue for the kinds whose only per-element output is bf16 (EPI_BF16, EPI_GELU_FWD,
 // EPI_GELU_BWD).  The arithmetic runs in the TMEM layout (one thread = one accumulator row, 32 columns at a
 // time), the results are packed to bf16 and only then transposed through the warp's 2 KB staging tile
@@ -434,8 +481,9 @@ __device__ __forceinline__ void epilogue_role(const EpiParams& ep, const GemmSha
 //     accumulator wait) and is broadcast with shuffles; the GELU-backward pre-activations are loaded
 //     coalesced before the wait and handed to the row threads through the same staging tile,
 //   * the second TMEM load of a 64-column part is in flight while the first half is stored.
-template <int EPI, int BN, int CG>
-__device__ __forceinline__ void epilogue_rows(const EpiParams& ep, const GemmShape& sh, uint8_t* sEpi,
+template <int EPI, int BN, int CG, int NBUF>
+__device__ __forceinline__ void epilogue_rows(const EpiParams& ep, const GemmShape& sh, const CUtensorMap* tmO,
+                                              const CUtensorMap* tmO2, uint8_t* sEpi,
                                               uint64_t* tfull, uint64_t* tempty, uint32_t tmem_base, int warp,
                                               int lane, int total_tiles, int tile0, int tile_step, int m_off) {
   constexpr int NH = (BN == 256) ? 2 : 1;   // 32-column halves per warp
@@ -444,14 +492,16 @@ __device__ __forceinline__ void epilogue_rows(const EpiParams& ep, const GemmSha
   const int e = warp - kEpiWarp0;
   const int q = warp & 3;   // TMEM lane quarter == warp % 4 (a hardware rule); (q, part) still enumerates the 16 warps
   const int part = e >> 2;
-  const uint32_t stage_addr = smem_u32(sEpi + e * kStageBytesPerWarp);
+  const uint32_t stage_addr = smem_u32(sEpi + e * (kStageBytesPerWarp * NBUF));
   // row view: lane = row, chunk j at ((j ^ sw) << 4); coalesced view: 4 lanes per row, 8 rows per instruction
-  const uint32_t own_addr = stage_addr + lane * 64;
   const uint32_t own_sw = (lane >> 1) & 3;
+  const uint32_t own_addr = opaque(stage_addr + lane * 64);
   const int crow = lane >> 2, cch = lane & 3;
-  const uint32_t co_addr = stage_addr + crow * 64 + ((cch ^ ((crow >> 1) & 3)) << 4);  // + i * 512 for row 8 i + crow
+  const uint32_t co_addr = opaque(stage_addr + crow * 64 + ((cch ^ ((crow >> 1) & 3)) << 4));  // + i * 512: row 8 i + crow
   const int tiles_mn = sh.num_m * sh.num_n;
   const bool has_bias = ep.bias != nullptr;
+  const bool tma = ep.tma_store != 0;  // kernel-uniform
+  uint32_t buf = 0;                     // byte offset of the staging tile in use (NBUF tiles, used in turn)
   int iter = 0;
   for (int t = tile0; t < total_tiles; t += tile_step, ++iter) {
     const int rem = t % tiles_mn;
@@ -473,11 +523,11 @@ __device__ __forceinline__ void epilogue_rows(const EpiParams& ep, const GemmSha
     }
     const int row_base = m_blk * (BM * CG) + m_off + q * 32;
     const int colp = n_blk * BN + part * (32 * NH);
-    uint32_t zmask = 0xffffffffu;  // 0 for a row that stores zeros (row_mask_mode 1)
+    uint32_t zflag = 0;  // set for a row that stores zeros (row_mask_mode 1)
     uint32_t st_mask = 0;
     {
       const bool masked = ep.row_period > 0;
-      if (masked && ep.row_mask_mode == 1 && ((row_base + lane) % ep.row_period) < ep.row_skip) zmask = 0u;
+      if (masked && ep.row_mask_mode == 1 && ((row_base + lane) % ep.row_period) < ep.row_skip) zflag = 1u;
 #pragma unroll
       for (int i = 0; i < 4; ++i) {
         const int row = row_base + 8 * i + crow;
@@ -485,6 +535,16 @@ __device__ __forceinline__ void epilogue_rows(const EpiParams& ep, const GemmSha
         if (masked && ep.row_mask_mode == 2 && (row % ep.row_period) < ep.row_skip) st = false;
         st_mask |= (st ? 1u : 0u) << i;
       }
+    }
+    // this lane's output addresses (row row_base + crow, first column of the part + its 16-byte chunk); row
+    // 8 i + crow is i * step further, the second 32-column half 64 bytes further
+    const long row0 = row_base + crow;
+    const uint64_t o1 = opaque(reinterpret_cast<uint64_t>(ep.out_bf16 + row0 * ep.ldo_bf16 + colp + 8 * cch));
+    const uint64_t step1 = opaque(static_cast<uint64_t>(ep.ldo_bf16) * 16);
+    uint64_t o2 = 0, step2 = 0;
+    if constexpr (EPI == EPI_GELU_FWD) {
+      o2 = opaque(reinterpret_cast<uint64_t>(ep.out2_bf16 + row0 * ep.ldo2_bf16 + colp + 8 * cch));
+      step2 = opaque(static_cast<uint64_t>(ep.ldo2_bf16) * 16);
     }
     float bs[NH], sc[NH];
     uint4 ax[4];
@@ -515,19 +575,59 @@ __device__ __forceinline__ void epilogue_rows(const EpiParams& ep, const GemmSha
     for (int h = 0; h < NH; ++h) {
       const int colh = colp + 32 * h;
       const bool live = colh < sh.N;  // warp-uniform
+      const int col = colh + 8 * cch;
+      const uint32_t ok = col < sh.N ? st_mask : 0u;
+      // The staging tile goes to global memory either as one TMA store (a SWIZZLE_64B 32 x 32 box: exactly
+      // the staging layout; rows and columns beyond the matrix are clipped by the tensor map) or, when rows
+      // must be skipped, with 16-byte stores in the coalesced view.
+      auto flush = [&](int o) {
+        if (tma) {
+          fence_proxy_async();  // this lane's staging writes -> visible to the async proxy
+          __syncwarp();
+          if (lane == 0) {
+            tma_store_2d(o == 0 ? tmO : tmO2, stage_addr + buf, colh, row_base);
+            tma_store_commit();
+          }
+        } else {
+          __syncwarp();
+          const uint64_t obase = ((o == 0) ? o1 : o2) + 64 * h;
+          const uint64_t ostep = (o == 0) ? step1 : step2;
+          uint4 v[4];
+#pragma unroll
+          for (int i = 0; i < 4; ++i)
+            asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];"
+                         : "=r"(v[i].x), "=r"(v[i].y), "=r"(v[i].z), "=r"(v[i].w)
+                         : "r"(co_addr + buf + i * 512)
+                         : "memory");
+#pragma unroll
+          for (int i = 0; i < 4; ++i) stg128_if(obase + i * ostep, v[i], ok & (1u << i));
+        }
+      };
+      // next staging tile (with two tiles, the store issued from the other one may still be reading it)
+      auto next_buf = [&]() {
+        if constexpr (NBUF == 2) buf ^= kStageBytesPerWarp;
+      };
+      // the previous contents of the staging tile have left it (TMA: the store has read them)
+      auto staging_free = [&]() {
+        if (tma) {
+          if (lane == 0) tma_store_wait_read<NBUF - 1>();
+        }
+        __syncwarp();
+      };
       uint32_t G[16];
       if (live) {
         if constexpr (EPI == EPI_GELU_BWD) {
           // pre-activations: coalesced registers -> staging -> row threads; results overwrite them in place
+          staging_free();
 #pragma unroll
           for (int i = 0; i < 4; ++i)
-            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(co_addr + i * 512), "r"(ax[i].x),
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(co_addr + buf + i * 512), "r"(ax[i].x),
                          "r"(ax[i].y), "r"(ax[i].z), "r"(ax[i].w)
                          : "memory");
           __syncwarp();
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
-            const uint32_t a = own_addr + ((j ^ own_sw) << 4);
+            const uint32_t a = own_addr + buf + ((j ^ own_sw) << 4);
             uint32_t w[4], o[4];
             asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];"
                          : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3])
@@ -538,14 +638,12 @@ __device__ __forceinline__ void epilogue_rows(const EpiParams& ep, const GemmSha
               const float2 x = unpack_bf16(w[k]);
               const float v0 = __uint_as_float(r[h][8 * j + 2 * k]) * gelu_grad_fast(x.x);
               const float v1 = __uint_as_float(r[h][8 * j + 2 * k + 1]) * gelu_grad_fast(x.y);
-              o[k] = pack_bf16(v0, v1) & zmask;
+              o[k] = pack_bf16(v0, v1);
             }
-            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(o[0]), "r"(o[1]), "r"(o[2]),
-                         "r"(o[3])
-                         : "memory");
+            sts128_or_zero(a, o[0], o[1], o[2], o[3], zflag);
           }
         } else {
-          // branch-free: masked rows are zeroed with an AND, so the 32 columns stay one basic block
+          // branch-free (one basic block for the 32 columns); rows that store zeros are handled at the STS
           uint32_t P[16];
           float v[32];
           if (has_bias) {  // warp-uniform
@@ -558,14 +656,17 @@ __device__ __forceinline__ void epilogue_rows(const EpiParams& ep, const GemmSha
           }
 #pragma unroll
           for (int j = 0; j < 16; ++j) {
-            P[j] = pack_bf16(v[2 * j], v[2 * j + 1]) & zmask;
-            if constexpr (EPI == EPI_GELU_FWD) G[j] = pack_bf16(gelu_fast(v[2 * j]), gelu_fast(v[2 * j + 1])) & zmask;
+            P[j] = pack_bf16(v[2 * j], v[2 * j + 1]);
+            if constexpr (EPI == EPI_GELU_FWD) G[j] = pack_bf16(gelu_fast(v[2 * j]), gelu_fast(v[2 * j + 1]));
           }
+          staging_free();
 #pragma unroll
           for (int j = 0; j < 4; ++j)
-            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(own_addr + ((j ^ own_sw) << 4)),
-                         "r"(P[4 * j]), "r"(P[4 * j + 1]), "r"(P[4 * j + 2]), "r"(P[4 * j + 3])
-                         : "memory");
+            sts128_or_zero(own_addr + buf + ((j ^ own_sw) << 4), P[4 * j], P[4 * j + 1], P[4 * j + 2], P[4 * j + 3], zflag);
+          if constexpr (EPI == EPI_GELU_FWD) {
+            flush(0);
+            next_buf();
+          }
         }
       }
       if constexpr (NH == 2) {
@@ -574,55 +675,46 @@ __device__ __forceinline__ void epilogue_rows(const EpiParams& ep, const GemmSha
           tmem_ld_32x32(t_addr + 32, r[1]);
         }
       }
-      constexpr int NOUT = (EPI == EPI_GELU_FWD) ? 2 : 1;
-#pragma unroll
-      for (int o = 0; o < NOUT; ++o) {
-        if (o == 1 && live) {
+      if (live) {
+        if constexpr (EPI == EPI_GELU_FWD) {
+          staging_free();
 #pragma unroll
           for (int j = 0; j < 4; ++j)
-            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(own_addr + ((j ^ own_sw) << 4)),
-                         "r"(G[4 * j]), "r"(G[4 * j + 1]), "r"(G[4 * j + 2]), "r"(G[4 * j + 3])
-                         : "memory");
+            sts128_or_zero(own_addr + buf + ((j ^ own_sw) << 4), G[4 * j], G[4 * j + 1], G[4 * j + 2], G[4 * j + 3], zflag);
+          flush(1);
+        } else {
+          flush(0);
         }
-        __syncwarp();
-        if (live) {
-          __nv_bfloat16* out = (o == 0) ? ep.out_bf16 : ep.out2_bf16;
-          const long ldo = (o == 0) ? ep.ldo_bf16 : ep.ldo2_bf16;
-          const int col = colh + 8 * cch;
-          const bool cl = col < sh.N;
-          float cs[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+        const uint32_t sum_buf = buf;  // (GELU backward: the tile just stored, for the column sums)
+        next_buf();
+        if constexpr (EPI == EPI_GELU_BWD) {
+          if (ep.colsum != nullptr) {  // warp-uniform: column sums of the stored tile, one vector reduction per 4
+            float cs[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-          for (int i = 0; i < 4; ++i) {
-            uint4 v;
-            asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];"
-                         : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
-                         : "r"(co_addr + i * 512)
-                         : "memory");
-            if (cl && ((st_mask >> i) & 1u)) {
-              *reinterpret_cast<uint4*>(out + static_cast<long>(row_base + 8 * i + crow) * ldo + col) = v;
-              if constexpr (EPI == EPI_GELU_BWD) {
+            for (int i = 0; i < 4; ++i) {
+              uint4 v;
+              asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];"
+                           : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+                           : "r"(co_addr + sum_buf + i * 512)
+                           : "memory");
+              if (ok & (1u << i)) {
                 const float2 a = unpack_bf16(v.x), b = unpack_bf16(v.y), c = unpack_bf16(v.z), d = unpack_bf16(v.w);
                 cs[0] += a.x, cs[1] += a.y, cs[2] += b.x, cs[3] += b.y;
                 cs[4] += c.x, cs[5] += c.y, cs[6] += d.x, cs[7] += d.y;
               }
             }
-          }
-          if constexpr (EPI == EPI_GELU_BWD) {
-            if (ep.colsum != nullptr) {  // warp-uniform: fold the 8 row-lanes, one atomic per column
 #pragma unroll
-              for (int j = 0; j < 8; ++j) {
-                cs[j] += __shfl_xor_sync(kFull, cs[j], 4);
-                cs[j] += __shfl_xor_sync(kFull, cs[j], 8);
-                cs[j] += __shfl_xor_sync(kFull, cs[j], 16);
-              }
-              if (crow == 0 && cl) {  // two 16-byte vector reductions per lane instead of eight scalar ones
-                atomicAdd(reinterpret_cast<float4*>(ep.colsum + col), make_float4(cs[0], cs[1], cs[2], cs[3]));
-                atomicAdd(reinterpret_cast<float4*>(ep.colsum + col + 4), make_float4(cs[4], cs[5], cs[6], cs[7]));
-              }
+            for (int j = 0; j < 8; ++j) {
+              cs[j] += __shfl_xor_sync(kFull, cs[j], 4);
+              cs[j] += __shfl_xor_sync(kFull, cs[j], 8);
+              cs[j] += __shfl_xor_sync(kFull, cs[j], 16);
+            }
+            if (crow == 0 && col < sh.N) {
+              atomicAdd(reinterpret_cast<float4*>(ep.colsum + col), make_float4(cs[0], cs[1], cs[2], cs[3]));
+              atomicAdd(reinterpret_cast<float4*>(ep.colsum + col + 4), make_float4(cs[4], cs[5], cs[6], cs[7]));
             }
           }
         }
-        __syncwarp();
       }
       if constexpr (NH == 2) {
         if (h == 0) {
@@ -632,23 +724,29 @@ __device__ __forceinline__ void epilogue_rows(const EpiParams& ep, const GemmSha
       }
     }
   }
+  if (tma) {  // the last stores must have read the staging tile (and landed) before the CTA may go away
+    if (lane == 0) tma_store_wait_all();
+  }
+  __syncwarp();
 }
 
-template <int EPI, int BN, int CG>
-__device__ __forceinline__ void run_epilogue(const EpiParams& ep, const GemmShape& sh, uint8_t* sEpi,
+template <int EPI, int BN, int CG, int NBUF>
+__device__ __forceinline__ void run_epilogue(const EpiParams& ep, const GemmShape& sh, const CUtensorMap* tmO,
+                                             const CUtensorMap* tmO2, uint8_t* sEpi,
                                              uint64_t* tfull, uint64_t* tempty, uint32_t tmem_base, int warp,
                                              int lane, int total_tiles, int tile0, int tile_step, int m_off) {
   if constexpr (EPI == EPI_BF16 || EPI == EPI_GELU_FWD || EPI == EPI_GELU_BWD)
-    epilogue_rows<EPI, BN, CG>(ep, sh, sEpi, tfull, tempty, tmem_base, warp, lane, total_tiles, tile0, tile_step,
+    epilogue_rows<EPI, BN, CG, NBUF>(ep, sh, tmO, tmO2, sEpi, tfull, tempty, tmem_base, warp, lane, total_tiles, tile0, tile_step,
                                m_off);
   else
-    epilogue_role<EPI, BN, CG>(ep, sh, sEpi, tfull, tempty, tmem_base, warp, lane, total_tiles, tile0, tile_step,
+    epilogue_role<EPI, BN, CG, NBUF>(ep, sh, sEpi, tfull, tempty, tmem_base, warp, lane, total_tiles, tile0, tile_step,
                                m_off);
 }
 
 template <int BN, bool A_MN, bool B_MN, int EPI>
 __global__ void __launch_bounds__(kGemmThreads, 1)
-gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmShape sh,
+gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+            const __grid_constant__ CUtensorMap tmO, const __grid_constant__ CUtensorMap tmO2, const GemmShape sh,
             const EpiParams ep) {
   using Cfg = GemmCfg<BN>;
   constexpr int STAGES = Cfg::STAGES;
@@ -765,7 +863,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     }
   } else if (warp >= kEpiWarp0) {
     setmaxnreg_inc<JM_GEMM_REG_INC>();
-    run_epilogue<EPI, BN, 1>(ep, sh, sEpi, tfull, tempty, tmem_base, warp, lane, total_tiles, blockIdx.x,
+    run_epilogue<EPI, BN, 1, Cfg::EPI_BUFS>(ep, sh, &tmO, &tmO2, sEpi, tfull, tempty, tmem_base, warp, lane, total_tiles, blockIdx.x,
                              gridDim.x, 0);
   }
 
@@ -788,16 +886,18 @@ struct Gemm2Cfg {
   static constexpr int A_BYTES = BM * BK * 2;         // this CTA's 128 rows
   static constexpr int B_BYTES = (BN / 2) * BK * 2;   // this CTA's 128 of the 256 columns
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-  static constexpr int STAGES = 6;
+  static constexpr int EPI_BUFS = 2;
+  static constexpr int STAGES = 5;
   static constexpr int TMEM_COLS = 2 * BN;
   static constexpr int BAR_BYTES = (2 * STAGES + 4) * 8 + 16;
-  static constexpr int EPI_BYTES = kEpiWarps * kStageBytesPerWarp;
+  static constexpr int EPI_BYTES = kEpiWarps * kStageBytesPerWarp * EPI_BUFS;
   static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + EPI_BYTES + BAR_BYTES + 1024;
 };
 
 template <bool A_MN, bool B_MN, int EPI>
 __global__ void __launch_bounds__(kGemmThreads, 1)
-gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmShape sh,
+gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+             const __grid_constant__ CUtensorMap tmO, const __grid_constant__ CUtensorMap tmO2, const GemmShape sh,
              const EpiParams ep) {
   using Cfg = Gemm2Cfg;
   constexpr int STAGES = Cfg::STAGES;
@@ -927,7 +1027,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
     }
   } else if (warp >= kEpiWarp0) {
     setmaxnreg_inc<JM_GEMM_REG_INC>();
-    run_epilogue<EPI, 256, 2>(ep, sh, sEpi, tfull, tempty, tmem_base, warp, lane, total_tiles, pair, npairs,
+    run_epilogue<EPI, 256, 2, Cfg::EPI_BUFS>(ep, sh, &tmO, &tmO2, sEpi, tfull, tempty, tmem_base, warp, lane, total_tiles, pair, npairs,
                               rank * BM);
   }
 
@@ -950,9 +1050,10 @@ static PFN_cuTensorMapEncodeTiled_v12000 get_encode_fn() {
   return fn;
 }
 
-// 2-D bf16 tensor [outer, inner] row-major with row stride ld elements, SWIZZLE_128B boxes.
+// 2-D bf16 tensor [outer, inner] row-major with row stride ld elements; operand boxes are SWIZZLE_128B, the
+// epilogue's 32 x 32 output boxes SWIZZLE_64B.
 static int make_tmap(CUtensorMap* map, const void* ptr, long inner, long outer, long ld, int box_inner,
-                     int box_outer) {
+                     int box_outer, CUtensorMapSwizzle swizzle = CU_TENSOR_MAP_SWIZZLE_128B) {
   auto fn = get_encode_fn();
   JM_CHECK(fn != nullptr, "cuTensorMapEncodeTiled not available from the driver");
   JM_CHECK((reinterpret_cast<uintptr_t>(ptr) & 15) == 0, "GEMM operand pointer must be 16-byte aligned");
@@ -962,7 +1063,7 @@ static int make_tmap(CUtensorMap* map, const void* ptr, long inner, long outer, 
   cuuint32_t box[2] = {static_cast<cuuint32_t>(box_inner), static_cast<cuuint32_t>(box_outer)};
   cuuint32_t estr[2] = {1, 1};
   CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, estr,
-                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   JM_CHECK(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed with CUresult %d (inner=%ld outer=%ld ld=%ld)",
            static_cast<int>(r), inner, outer, ld);
@@ -970,7 +1071,7 @@ static int make_tmap(CUtensorMap* map, const void* ptr, long inner, long outer, 
 }
 
 template <int BN, bool A_MN, bool B_MN, int EPI>
-static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmShape& sh, const EpiParams& ep,
+static int launch_gemm(const GemmMaps& tm, const GemmShape& sh, const EpiParams& ep,
                        int grid, cudaStream_t stream) {
   auto kern = gemm_kernel<BN, A_MN, B_MN, EPI>;
   static bool attr_set = false;  // per template instantiation; benign race (idempotent)
@@ -978,13 +1079,13 @@ static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const Gem
     JM_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, GemmCfg<BN>::SMEM_BYTES));
     attr_set = true;
   }
-  kern<<<grid, kGemmThreads, GemmCfg<BN>::SMEM_BYTES, stream>>>(tmA, tmB, sh, ep);
+  kern<<<grid, kGemmThreads, GemmCfg<BN>::SMEM_BYTES, stream>>>(tm.a, tm.b, tm.o, tm.o2, sh, ep);
   JM_AFTER_LAUNCH();
   return 0;
 }
 
 template <bool A_MN, bool B_MN, int EPI>
-static int launch_gemm2(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmShape& sh, const EpiParams& ep,
+static int launch_gemm2(const GemmMaps& tm, const GemmShape& sh, const EpiParams& ep,
                         int grid, cudaStream_t stream) {
   auto kern = gemm2_kernel<A_MN, B_MN, EPI>;
   static bool attr_set = false;
@@ -1028,57 +1129,55 @@ static int launch_gemm2(const CUtensorMap& tmA, const CUtensorMap& tmB, const Ge
   if (grid > 2 * max_clusters) {
     cfg.gridDim = dim3(2 * max_clusters);
   }
-  JM_CUDA(cudaLaunchKernelEx(&cfg, kern, tmA, tmB, sh, ep));
+  JM_CUDA(cudaLaunchKernelEx(&cfg, kern, tm.a, tm.b, tm.o, tm.o2, sh, ep));
   count_launch();
   return 0;
 }
 
 template <bool A_MN, bool B_MN>
-static int dispatch_epi2(int epi, const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmShape& sh,
+static int dispatch_epi2(int epi, const GemmMaps& tm, const GemmShape& sh,
                          const EpiParams& ep, int grid, cudaStream_t stream) {
   switch (epi) {
-    case EPI_BF16: return launch_gemm2<A_MN, B_MN, EPI_BF16>(tmA, tmB, sh, ep, grid, stream);
-    case EPI_F32: return launch_gemm2<A_MN, B_MN, EPI_F32>(tmA, tmB, sh, ep, grid, stream);
-    case EPI_GELU_FWD: return launch_gemm2<A_MN, B_MN, EPI_GELU_FWD>(tmA, tmB, sh, ep, grid, stream);
-    case EPI_GELU_BWD: return launch_gemm2<A_MN, B_MN, EPI_GELU_BWD>(tmA, tmB, sh, ep, grid, stream);
-    default: return launch_gemm2<A_MN, B_MN, EPI_GENERIC>(tmA, tmB, sh, ep, grid, stream);
+    case EPI_BF16: return launch_gemm2<A_MN, B_MN, EPI_BF16>(tm, sh, ep, grid, stream);
+    case EPI_F32: return launch_gemm2<A_MN, B_MN, EPI_F32>(tm, sh, ep, grid, stream);
+    case EPI_GELU_FWD: return launch_gemm2<A_MN, B_MN, EPI_GELU_FWD>(tm, sh, ep, grid, stream);
+    case EPI_GELU_BWD: return launch_gemm2<A_MN, B_MN, EPI_GELU_BWD>(tm, sh, ep, grid, stream);
+    default: return launch_gemm2<A_MN, B_MN, EPI_GENERIC>(tm, sh, ep, grid, stream);
   }
 }
 
 // Pair kernel instantiations: forward (A K-major, B MN-major), input gradient (K, K), weight gradient (MN, MN).
-static int dispatch_pair(bool a_mn, bool b_mn, int epi, const CUtensorMap& tmA, const CUtensorMap& tmB,
-                         const GemmShape& sh, const EpiParams& ep, int grid, cudaStream_t stream) {
-  if (!a_mn && !b_mn) return dispatch_epi2<false, false>(epi, tmA, tmB, sh, ep, grid, stream);
-  if (!a_mn && b_mn) return dispatch_epi2<false, true>(epi, tmA, tmB, sh, ep, grid, stream);
-  if (epi == EPI_F32) return launch_gemm2<true, true, EPI_F32>(tmA, tmB, sh, ep, grid, stream);
-  return launch_gemm2<true, true, EPI_GENERIC>(tmA, tmB, sh, ep, grid, stream);
+static int dispatch_pair(bool a_mn, bool b_mn, int epi, const GemmMaps& tm, const GemmShape& sh, const EpiParams& ep, int grid, cudaStream_t stream) {
+  if (!a_mn && !b_mn) return dispatch_epi2<false, false>(epi, tm, sh, ep, grid, stream);
+  if (!a_mn && b_mn) return dispatch_epi2<false, true>(epi, tm, sh, ep, grid, stream);
+  if (epi == EPI_F32) return launch_gemm2<true, true, EPI_F32>(tm, sh, ep, grid, stream);
+  return launch_gemm2<true, true, EPI_GENERIC>(tm, sh, ep, grid, stream);
 }
 
 template <int BN, bool A_MN, bool B_MN>
-static int dispatch_epi(int epi, const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmShape& sh,
+static int dispatch_epi(int epi, const GemmMaps& tm, const GemmShape& sh,
                         const EpiParams& ep, int grid, cudaStream_t stream) {
   switch (epi) {
-    case EPI_BF16: return launch_gemm<BN, A_MN, B_MN, EPI_BF16>(tmA, tmB, sh, ep, grid, stream);
-    case EPI_F32: return launch_gemm<BN, A_MN, B_MN, EPI_F32>(tmA, tmB, sh, ep, grid, stream);
-    case EPI_GELU_FWD: return launch_gemm<BN, A_MN, B_MN, EPI_GELU_FWD>(tmA, tmB, sh, ep, grid, stream);
-    case EPI_GELU_BWD: return launch_gemm<BN, A_MN, B_MN, EPI_GELU_BWD>(tmA, tmB, sh, ep, grid, stream);
-    default: return launch_gemm<BN, A_MN, B_MN, EPI_GENERIC>(tmA, tmB, sh, ep, grid, stream);
+    case EPI_BF16: return launch_gemm<BN, A_MN, B_MN, EPI_BF16>(tm, sh, ep, grid, stream);
+    case EPI_F32: return launch_gemm<BN, A_MN, B_MN, EPI_F32>(tm, sh, ep, grid, stream);
+    case EPI_GELU_FWD: return launch_gemm<BN, A_MN, B_MN, EPI_GELU_FWD>(tm, sh, ep, grid, stream);
+    case EPI_GELU_BWD: return launch_gemm<BN, A_MN, B_MN, EPI_GELU_BWD>(tm, sh, ep, grid, stream);
+    default: return launch_gemm<BN, A_MN, B_MN, EPI_GENERIC>(tm, sh, ep, grid, stream);
   }
 }
 
 template <int BN>
-static int dispatch_major(bool a_mn, bool b_mn, int epi, const CUtensorMap& tmA, const CUtensorMap& tmB,
-                          const GemmShape& sh, const EpiParams& ep, int grid, cudaStream_t stream) {
-  if (!a_mn && !b_mn) return dispatch_epi<BN, false, false>(epi, tmA, tmB, sh, ep, grid, stream);
-  if (!a_mn && b_mn) return dispatch_epi<BN, false, true>(epi, tmA, tmB, sh, ep, grid, stream);
+static int dispatch_major(bool a_mn, bool b_mn, int epi, const GemmMaps& tm, const GemmShape& sh, const EpiParams& ep, int grid, cudaStream_t stream) {
+  if (!a_mn && !b_mn) return dispatch_epi<BN, false, false>(epi, tm, sh, ep, grid, stream);
+  if (!a_mn && b_mn) return dispatch_epi<BN, false, true>(epi, tm, sh, ep, grid, stream);
   // transposed-A products are weight gradients: f32 accumulate epilogue (anything else: generic)
   if (epi != EPI_F32) epi = EPI_GENERIC;
   if (a_mn && !b_mn) {
-    if (epi == EPI_F32) return launch_gemm<BN, true, false, EPI_F32>(tmA, tmB, sh, ep, grid, stream);
-    return launch_gemm<BN, true, false, EPI_GENERIC>(tmA, tmB, sh, ep, grid, stream);
+    if (epi == EPI_F32) return launch_gemm<BN, true, false, EPI_F32>(tm, sh, ep, grid, stream);
+    return launch_gemm<BN, true, false, EPI_GENERIC>(tm, sh, ep, grid, stream);
   }
-  if (epi == EPI_F32) return launch_gemm<BN, true, true, EPI_F32>(tmA, tmB, sh, ep, grid, stream);
-  return launch_gemm<BN, true, true, EPI_GENERIC>(tmA, tmB, sh, ep, grid, stream);
+  if (epi == EPI_F32) return launch_gemm<BN, true, true, EPI_F32>(tm, sh, ep, grid, stream);
+  return launch_gemm<BN, true, true, EPI_GENERIC>(tm, sh, ep, grid, stream);
 }
 
 }  // namespace jm
@@ -1109,21 +1208,42 @@ extern "C" int jm_gemm(const jm_gemm_args* a, void* stream_) {
   const int kblocks = (a->K + BK - 1) / BK;
   const bool can_split = a->accumulate && a->out_f32 && !a->out_bf16 && !a->out2_bf16 && !a->bias &&
                          !a->residual && !a->pe && a->act == 0;
+  const bool amn = a->a_mn_major != 0, bmn = a->b_mn_major != 0;
+  static int auto_pair = -1;
+  if (auto_pair < 0) {
+    const char* e = getenv("JM_GEMM_PAIR");
+    auto_pair = e ? (atoi(e) != 0) : 1;
+  }
   int bn = a->block_n;
+  bool pair_pick = false;
   if (bn == 0) {
-    // Largest tile that still gives every SM work; 256-wide tiles halve the shared-memory
-    // operand traffic per MMA, which is what a 1-CTA tcgen05.mma needs to run at full rate.
+    // Pick the tile by a small cost model in SM cycles: waves x max(main loop, epilogue) per tile, plus the
+    // last tile's exposed epilogue.  Cycles per 64-deep k-block per CTA are the measured steady-state rates
+    // (the 256-wide tiles halve the operand traffic per MMA, the CTA pair halves the B traffic again).
+    const bool pair_allowed = a->cta_pair >= 0 && (a->cta_pair > 0 || auto_pair) && !(amn && !bmn) && a->M > BM &&
+                              a->N >= 256;
+    double best = 0.0;
     bn = 64;
-    const int cand[3] = {256, 128, 64};
-    for (int i = 0; i < 3; ++i) {
-      const int c = cand[i];
-      if (c > 64 && a->N < c) continue;
-      const long tiles = static_cast<long>(num_m) * ((a->N + c - 1) / c);
-      const long reach = can_split ? tiles * kblocks : tiles;
-      if (reach >= sms || c == 64) {
-        bn = c;
-        break;
+    for (int c = 0; c < 4; ++c) {  // pair 256, single 256, 128, 64: ties keep the earlier (larger) tile
+      const bool pr = c == 0;
+      const int w = c <= 1 ? 256 : (c == 2 ? 128 : 64);
+      if (pr && !pair_allowed) continue;
+      if (!pr && a->cta_pair > 0) continue;
+      if (w > 64 && a->N < w) continue;
+      const long slots = pr ? sms / 2 : sms;
+      const long tiles = (pr ? (a->M + 2 * BM - 1) / (2 * BM) : num_m) * static_cast<long>((a->N + w - 1) / w);
+      long sp = 1;
+      if (a->splits > 0) sp = a->splits;
+      else if (can_split) {
+        sp = slots / tiles;
+        if (sp > kblocks / 2) sp = kblocks / 2;
+        if (sp < 1) sp = 1;
       }
+      const long waves = (tiles * sp + slots - 1) / slots;
+      const double per_kb = pr ? 512.0 : (w == 256 ? 560.0 : (w == 128 ? 350.0 : 260.0));
+      const double main_loop = per_kb * kblocks / sp, epi = 14.0 * w;
+      const double cost = waves * (main_loop > epi ? main_loop : epi) + epi;
+      if (best == 0.0 || cost < best) best = cost, bn = w, pair_pick = pr;
     }
   }
   JM_CHECK(bn == 64 || bn == 128 || bn == 256, "jm_gemm: block_n must be 64, 128 or 256");
@@ -1142,21 +1262,14 @@ extern "C" int jm_gemm(const jm_gemm_args* a, void* stream_) {
   JM_CHECK(splits <= kblocks, "jm_gemm: more splits (%d) than k-blocks (%d)", splits, kblocks);
 
   // CTA-pair kernel (256 x 256 tiles, cta_group::2): each CTA stages only half of B, which relieves the
-  // shared-memory / L2-to-SM traffic the 128 x 256 single-CTA tile is bound by.  Default whenever the 256-wide
-  // tile was chosen, the operand layout has an instantiation and M spans more than one CTA.
-  const bool amn = a->a_mn_major != 0, bmn = a->b_mn_major != 0;
+  // shared-memory / L2-to-SM traffic the 128 x 256 single-CTA tile is bound by.
   const bool pair_ok = bn == 256 && !(amn && !bmn) && a->M > BM;
   bool pair = false;
   if (a->cta_pair > 0) {
     JM_CHECK(pair_ok, "jm_gemm: cta_pair needs block_n 256, M > 128 and a supported operand layout");
     pair = true;
   } else if (a->cta_pair == 0) {
-    static int auto_pair = -1;
-    if (auto_pair < 0) {
-      const char* e = getenv("JM_GEMM_PAIR");
-      auto_pair = e ? (atoi(e) != 0) : 1;
-    }
-    pair = pair_ok && auto_pair;
+    pair = a->block_n == 0 ? pair_pick : (pair_ok && auto_pair);
   }
   int num_m_eff = num_m;
   if (pair) {
@@ -1172,7 +1285,10 @@ extern "C" int jm_gemm(const jm_gemm_args* a, void* stream_) {
     }
   }
 
-  CUtensorMap tmA, tmB;
+  GemmMaps tm;
+  memset(&tm, 0, sizeof(tm));
+  CUtensorMap& tmA = tm.a;
+  CUtensorMap& tmB = tm.b;
   if (!a->a_mn_major) {
     if (make_tmap(&tmA, a->A, a->K, a->M, a->lda, BK, BM)) return 1;
   } else {
@@ -1215,11 +1331,18 @@ extern "C" int jm_gemm(const jm_gemm_args* a, void* stream_) {
     epi = EPI_GELU_BWD;
   else if (ep.act == 0 && only_f32 && !ep.colsum) epi = EPI_F32;
   else if (ep.act == 0 && only_bf16 && !ep.residual && !ep.pe && !ep.colsum && rows_ok) epi = EPI_BF16;
-  if (pair) {
-    if (amn && epi != EPI_F32) epi = EPI_GENERIC;
-    return dispatch_pair(amn, bmn, epi, tmA, tmB, sh, ep, grid, stream);
+  if (amn && epi != EPI_F32) epi = EPI_GENERIC;  // transposed-A products are weight gradients
+  ep.tma_store = 0;
+  if ((epi == EPI_BF16 || epi == EPI_GELU_FWD || epi == EPI_GELU_BWD) &&
+      !(ep.row_period > 0 && ep.row_mask_mode == 2)) {  // skipped rows need per-row predicates: plain stores
+    if (make_tmap(&tm.o, ep.out_bf16, a->N, a->M, ep.ldo_bf16, 32, 32, CU_TENSOR_MAP_SWIZZLE_64B)) return 1;
+    if (epi == EPI_GELU_FWD &&
+        make_tmap(&tm.o2, ep.out2_bf16, a->N, a->M, ep.ldo2_bf16, 32, 32, CU_TENSOR_MAP_SWIZZLE_64B))
+      return 1;
+    ep.tma_store = 1;
   }
-  if (bn == 256) return dispatch_major<256>(amn, bmn, epi, tmA, tmB, sh, ep, grid, stream);
-  if (bn == 128) return dispatch_major<128>(amn, bmn, epi, tmA, tmB, sh, ep, grid, stream);
-  return dispatch_major<64>(amn, bmn, epi, tmA, tmB, sh, ep, grid, stream);
+  if (pair) return dispatch_pair(amn, bmn, epi, tm, sh, ep, grid, stream);
+  if (bn == 256) return dispatch_major<256>(amn, bmn, epi, tm, sh, ep, grid, stream);
+  if (bn == 128) return dispatch_major<128>(amn, bmn, epi, tm, sh, ep, grid, stream);
+  return dispatch_major<64>(amn, bmn, epi, tm, sh, ep, grid, stream);
 }

@@ -1,0 +1,15 @@
+#!/bin/bash
+# Builds experiment variants of the library into exp/lib_<name>.so:  tools/build_variants.sh name1="-DX" name2="-DY -DZ"
+set -e
+cd "$(dirname "$0")/.."
+mkdir -p exp
+cp jumbo_mae_tpu_b200/libjumbo_mae_b200.so /tmp/lib_keep.so 2>/dev/null || true
+for spec in "$@"; do
+  name="${spec%%=*}"; defs="${spec#*=}"
+  touch jumbo_mae_tpu_b200/csrc/gemm.cu
+  JM_NVCC_DEFS="$defs" python -m jumbo_mae_tpu_b200.build > /dev/null 2> exp/build_$name.log
+  cp jumbo_mae_tpu_b200/libjumbo_mae_b200.so exp/lib_$name.so
+  echo "$name: $(grep -A3 'gemm2_kernelILb0ELb1ELi2E' exp/build_$name.log | grep spill)"
+done
+touch jumbo_mae_tpu_b200/csrc/gemm.cu
+python -m jumbo_mae_tpu_b200.build > /dev/null 2>&1
