@@ -150,6 +150,14 @@ __device__ __forceinline__ void tma_store_2d(const void* desc, uint32_t smem_add
                "r"(smem_addr), "r"(c0), "r"(c1)
                : "memory");
 }
+// Same, but the tile is ADDED to global memory (f32 reduction in L2): split-K partial sums and gradient
+// accumulation without reading the destination back into the SM.
+__device__ __forceinline__ void tma_reduce_add_2d(const void* desc, uint32_t smem_addr, int c0, int c1) {
+  asm volatile("cp.reduce.async.bulk.tensor.2d.global.shared::cta.add.tile.bulk_group [%0, {%2, %3}], [%1];" ::"l"(
+                   reinterpret_cast<uint64_t>(desc)),
+               "r"(smem_addr), "r"(c0), "r"(c1)
+               : "memory");
+}
 __device__ __forceinline__ void tma_store_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 // all but the newest N groups of this thread have finished READING their shared-memory source
 template <int N>

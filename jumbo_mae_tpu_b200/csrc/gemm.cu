@@ -82,7 +82,7 @@ struct GemmCfg {
   static constexpr int EPI_BUFS = (BN == 256) ? 1 : 2;
   static constexpr int STAGES = (BN == 256) ? 4 : ((BN == 128) ? 5 : 6);
   static constexpr int TMEM_COLS = 2 * BN;
-  static constexpr int BAR_BYTES = (2 * STAGES + 4) * 8 + 16;
+  static constexpr int BAR_BYTES = (2 * STAGES + 4) * 8 + 16 + kEpiWarps * 2 * 8;  // + residual-load barriers
   static constexpr int EPI_BYTES = kEpiWarps * kStageBytesPerWarp * EPI_BUFS;  // epilogue transpose staging
   static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + EPI_BYTES + BAR_BYTES + 1024;  // +1024: alignment
 };
@@ -730,17 +730,150 @@ __device__ __forceinline__ void epilogue_rows(const EpiParams& ep, const GemmSha
   __syncwarp();
 }
 
+// f32 epilogue through TMA (EPI_F32 without positional embedding / skipped rows): out (=|+=) acc + bias
+// [+ residual].  Per warp and 16-column chunk: the residual tile (32 rows x 64 bytes) arrives in the staging
+// tile by a TMA load that was issued one chunk earlier, every thread adds its accumulator row in place, and
+// the tile leaves by a TMA store -- or a TMA reduce-add for gradient accumulation / split-K, which replaces
+// the read-modify-write (and the atomics) by a reduction in L2.  No global load/store instruction is issued.
+template <int BN, int CG, int NBUF>
+__device__ __forceinline__ void epilogue_f32_tma(const EpiParams& ep, const GemmShape& sh, const CUtensorMap* tmO,
+                                                 const CUtensorMap* tmR, uint8_t* sEpi, uint64_t* rbars,
+                                                 uint64_t* tfull, uint64_t* tempty, uint32_t tmem_base, int warp,
+                                                 int lane, int total_tiles, int tile0, int tile_step, int m_off) {
+  constexpr uint32_t kFull = 0xffffffffu;
+  constexpr int PART_N = BN / 4;
+  constexpr int NC = PART_N / 16;
+  constexpr int NB = (PART_N + 31) / 32;  // bias registers per lane
+  const int e = warp - kEpiWarp0;
+  const int q = warp & 3;
+  const int part = e >> 2;
+  const uint32_t stage_addr = smem_u32(sEpi + e * (kStageBytesPerWarp * NBUF));
+  const uint32_t own_sw = (lane >> 1) & 3;
+  const uint32_t own_addr = stage_addr + lane * 64;
+  uint64_t* rbar = rbars + e * 2;
+  const bool has_res = ep.residual != nullptr, has_bias = ep.bias != nullptr, reduce = ep.accumulate != 0;
+  const int tiles_mn = sh.num_m * sh.num_n;
+  uint32_t buf = 0;      // staging tile in use (index)
+  uint32_t rphase = 0;   // bit b: parity to wait for on rbar[b]
+  uint32_t rissued = 0;  // bit b: a residual load into tile b is in flight
+  auto tile_origin = [&](int t, int& row_base, int& colp) {
+    const int rem = t % tiles_mn;
+    const int m_blk = rem / sh.num_n, n_blk = rem - m_blk * sh.num_n;
+    row_base = m_blk * (BM * CG) + m_off + q * 32;
+    colp = n_blk * BN + part * PART_N;
+  };
+  auto load_res = [&](uint32_t b, int col, int row) {  // warp-uniform call
+    if (has_res && col < sh.N) {
+      if (lane == 0) {
+        mbar_arrive_expect_tx(&rbar[b], kStageBytesPerWarp);
+        tma_load_2d(tmR, &rbar[b], sEpi + e * (kStageBytesPerWarp * NBUF) + b * kStageBytesPerWarp, col, row);
+      }
+      rissued |= 1u << b;
+    }
+  };
+  if (tile0 < total_tiles) {
+    int rb, cp;
+    tile_origin(tile0, rb, cp);
+    load_res(0, cp, rb);
+  }
+  int iter = 0;
+  for (int t = tile0; t < total_tiles; t += tile_step, ++iter) {
+    int row_base, colp;
+    tile_origin(t, row_base, colp);
+    const int acc = iter & 1;
+    const uint32_t acc_phase = (iter >> 1) & 1;
+    float bs[NB];
+#pragma unroll
+    for (int i = 0; i < NB; ++i) {
+      const int col = colp + 32 * i + lane;
+      bs[i] = (has_bias && col < sh.N && 32 * i + lane < PART_N) ? __ldg(ep.bias + col) : 0.f;
+    }
+    mbar_wait(&tfull[acc], acc_phase);
+    tc_fence_after();
+    const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * BN + part * PART_N;
+#pragma unroll
+    for (int c = 0; c < NC; ++c) {
+      const int col0 = colp + 16 * c;
+      const bool live = col0 < sh.N;  // warp-uniform
+      uint32_t r[16];
+      if (live) tmem_ld_32x16(t_addr + 16 * c, r);
+      const uint32_t b = buf;
+      if (rissued & (1u << b)) {  // warp-uniform: the residual tile has landed
+        mbar_wait(&rbar[b], (rphase >> b) & 1u);
+        rphase ^= 1u << b;
+        rissued &= ~(1u << b);
+      }
+      tmem_ld_wait();
+      if (c == NC - 1) {  // accumulator fully drained: hand the TMEM buffer back to the MMA warp
+        tc_fence_before();
+        if constexpr (CG == 1) mbar_arrive(&tempty[acc]);
+        else mbar_arrive_cluster(mapa_shared(smem_u32(&tempty[acc]), 0));
+      }
+      if (live) {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const uint32_t a = own_addr + b * kStageBytesPerWarp + ((j ^ own_sw) << 4);
+          float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (has_res)
+            asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
+                         : "=f"(x.x), "=f"(x.y), "=f"(x.z), "=f"(x.w)
+                         : "r"(a)
+                         : "memory");
+          if (has_bias) {  // warp-uniform
+            const float bsrc = bs[(16 * c) / 32];
+            const int l0 = (16 * c) % 32 + 4 * j;
+            x.x += __shfl_sync(kFull, bsrc, l0), x.y += __shfl_sync(kFull, bsrc, l0 + 1);
+            x.z += __shfl_sync(kFull, bsrc, l0 + 2), x.w += __shfl_sync(kFull, bsrc, l0 + 3);
+          }
+          x.x += __uint_as_float(r[4 * j]), x.y += __uint_as_float(r[4 * j + 1]);
+          x.z += __uint_as_float(r[4 * j + 2]), x.w += __uint_as_float(r[4 * j + 3]);
+          asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(a), "f"(x.x), "f"(x.y), "f"(x.z), "f"(x.w)
+                       : "memory");
+        }
+        fence_proxy_async();
+        __syncwarp();
+        if (lane == 0) {
+          if (reduce) tma_reduce_add_2d(tmO, stage_addr + b * kStageBytesPerWarp, col0, row_base);
+          else tma_store_2d(tmO, stage_addr + b * kStageBytesPerWarp, col0, row_base);
+          tma_store_commit();
+        }
+      }
+      if constexpr (NBUF == 2) buf ^= 1u;
+      // the tile used next: its previous store must have read it; then its residual can be fetched
+      if (lane == 0) tma_store_wait_read<NBUF - 1>();
+      __syncwarp();
+      if (c + 1 < NC) {
+        load_res(buf, col0 + 16, row_base);
+      } else if (t + tile_step < total_tiles) {
+        int rb, cp;
+        tile_origin(t + tile_step, rb, cp);
+        load_res(buf, cp, rb);
+      }
+    }
+  }
+  if (lane == 0) tma_store_wait_all();
+  __syncwarp();
+}
+
 template <int EPI, int BN, int CG, int NBUF>
 __device__ __forceinline__ void run_epilogue(const EpiParams& ep, const GemmShape& sh, const CUtensorMap* tmO,
-                                             const CUtensorMap* tmO2, uint8_t* sEpi,
+                                             const CUtensorMap* tmO2, uint8_t* sEpi, uint64_t* rbars,
                                              uint64_t* tfull, uint64_t* tempty, uint32_t tmem_base, int warp,
                                              int lane, int total_tiles, int tile0, int tile_step, int m_off) {
-  if constexpr (EPI == EPI_BF16 || EPI == EPI_GELU_FWD || EPI == EPI_GELU_BWD)
-    epilogue_rows<EPI, BN, CG, NBUF>(ep, sh, tmO, tmO2, sEpi, tfull, tempty, tmem_base, warp, lane, total_tiles, tile0, tile_step,
-                               m_off);
-  else
+  if constexpr (EPI == EPI_BF16 || EPI == EPI_GELU_FWD || EPI == EPI_GELU_BWD) {
+    epilogue_rows<EPI, BN, CG, NBUF>(ep, sh, tmO, tmO2, sEpi, tfull, tempty, tmem_base, warp, lane, total_tiles, tile0,
+                                     tile_step, m_off);
+  } else {
+    if constexpr (EPI == EPI_F32) {
+      if (ep.tma_store) {  // kernel-uniform
+        epilogue_f32_tma<BN, CG, NBUF>(ep, sh, tmO, tmO2, sEpi, rbars, tfull, tempty, tmem_base, warp, lane,
+                                       total_tiles, tile0, tile_step, m_off);
+        return;
+      }
+    }
     epilogue_role<EPI, BN, CG, NBUF>(ep, sh, sEpi, tfull, tempty, tmem_base, warp, lane, total_tiles, tile0, tile_step,
-                               m_off);
+                                     m_off);
+  }
 }
 
 template <int BN, bool A_MN, bool B_MN, int EPI>
@@ -762,6 +895,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   uint64_t* tfull = bars + 2 * STAGES;
   uint64_t* tempty = bars + 2 * STAGES + 2;
   uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 4);
+  uint64_t* rbars = bars + 2 * STAGES + 6;  // two per epilogue warp: residual tiles arriving by TMA
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -779,6 +913,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       mbar_init(&tfull[a], 1);
       mbar_init(&tempty[a], kEpiWarps * 32);
     }
+    for (int i = 0; i < kEpiWarps * 2; ++i) mbar_init(&rbars[i], 1);
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc<Cfg::TMEM_COLS>(tmem_ptr);
@@ -863,7 +998,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     }
   } else if (warp >= kEpiWarp0) {
     setmaxnreg_inc<JM_GEMM_REG_INC>();
-    run_epilogue<EPI, BN, 1, Cfg::EPI_BUFS>(ep, sh, &tmO, &tmO2, sEpi, tfull, tempty, tmem_base, warp, lane, total_tiles, blockIdx.x,
+    run_epilogue<EPI, BN, 1, Cfg::EPI_BUFS>(ep, sh, &tmO, &tmO2, sEpi, rbars, tfull, tempty, tmem_base, warp, lane, total_tiles, blockIdx.x,
                              gridDim.x, 0);
   }
 
@@ -889,7 +1024,7 @@ struct Gemm2Cfg {
   static constexpr int EPI_BUFS = 2;
   static constexpr int STAGES = 5;
   static constexpr int TMEM_COLS = 2 * BN;
-  static constexpr int BAR_BYTES = (2 * STAGES + 4) * 8 + 16;
+  static constexpr int BAR_BYTES = (2 * STAGES + 4) * 8 + 16 + kEpiWarps * 2 * 8;  // + residual-load barriers
   static constexpr int EPI_BYTES = kEpiWarps * kStageBytesPerWarp * EPI_BUFS;
   static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + EPI_BYTES + BAR_BYTES + 1024;
 };
@@ -913,6 +1048,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
   uint64_t* tfull = bars + 2 * STAGES;
   uint64_t* tempty = bars + 2 * STAGES + 2;
   uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 4);
+  uint64_t* rbars = bars + 2 * STAGES + 6;  // two per epilogue warp: residual tiles arriving by TMA
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -939,6 +1075,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
       mbar_init(&tfull[a], 1);
       mbar_init(&tempty[a], 2 * kEpiWarps * 32);
     }
+    for (int i = 0; i < kEpiWarps * 2; ++i) mbar_init(&rbars[i], 1);
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc2<Cfg::TMEM_COLS>(tmem_ptr);
@@ -1027,7 +1164,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
     }
   } else if (warp >= kEpiWarp0) {
     setmaxnreg_inc<JM_GEMM_REG_INC>();
-    run_epilogue<EPI, 256, 2, Cfg::EPI_BUFS>(ep, sh, &tmO, &tmO2, sEpi, tfull, tempty, tmem_base, warp, lane, total_tiles, pair, npairs,
+    run_epilogue<EPI, 256, 2, Cfg::EPI_BUFS>(ep, sh, &tmO, &tmO2, sEpi, rbars, tfull, tempty, tmem_base, warp, lane, total_tiles, pair, npairs,
                               rank * BM);
   }
 
@@ -1053,18 +1190,19 @@ static PFN_cuTensorMapEncodeTiled_v12000 get_encode_fn() {
 // 2-D bf16 tensor [outer, inner] row-major with row stride ld elements; operand boxes are SWIZZLE_128B, the
 // epilogue's 32 x 32 output boxes SWIZZLE_64B.
 static int make_tmap(CUtensorMap* map, const void* ptr, long inner, long outer, long ld, int box_inner,
-                     int box_outer, CUtensorMapSwizzle swizzle = CU_TENSOR_MAP_SWIZZLE_128B) {
+                     int box_outer, CUtensorMapSwizzle swizzle = CU_TENSOR_MAP_SWIZZLE_128B, bool f32 = false) {
   auto fn = get_encode_fn();
+  const int esize = f32 ? 4 : 2;
   JM_CHECK(fn != nullptr, "cuTensorMapEncodeTiled not available from the driver");
   JM_CHECK((reinterpret_cast<uintptr_t>(ptr) & 15) == 0, "GEMM operand pointer must be 16-byte aligned");
-  JM_CHECK((ld * 2) % 16 == 0, "GEMM operand row stride must be a multiple of 8 elements (got %ld)", ld);
+  JM_CHECK((ld * esize) % 16 == 0, "GEMM operand row stride must be a multiple of 16 bytes (got %ld elements)", ld);
   cuuint64_t dims[2] = {static_cast<cuuint64_t>(inner), static_cast<cuuint64_t>(outer)};
-  cuuint64_t strides[1] = {static_cast<cuuint64_t>(ld) * 2};
+  cuuint64_t strides[1] = {static_cast<cuuint64_t>(ld) * esize};
   cuuint32_t box[2] = {static_cast<cuuint32_t>(box_inner), static_cast<cuuint32_t>(box_outer)};
   cuuint32_t estr[2] = {1, 1};
-  CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, estr,
-                  CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  CUresult r = fn(map, f32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2,
+                  const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle,
+                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   JM_CHECK(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed with CUresult %d (inner=%ld outer=%ld ld=%ld)",
            static_cast<int>(r), inner, outer, ld);
   return 0;
@@ -1338,6 +1476,14 @@ extern "C" int jm_gemm(const jm_gemm_args* a, void* stream_) {
     if (make_tmap(&tm.o, ep.out_bf16, a->N, a->M, ep.ldo_bf16, 32, 32, CU_TENSOR_MAP_SWIZZLE_64B)) return 1;
     if (epi == EPI_GELU_FWD &&
         make_tmap(&tm.o2, ep.out2_bf16, a->N, a->M, ep.ldo2_bf16, 32, 32, CU_TENSOR_MAP_SWIZZLE_64B))
+      return 1;
+    ep.tma_store = 1;
+  }
+  if (epi == EPI_F32 && !ep.pe && !(ep.row_period > 0 && ep.row_mask_mode != 0) && ep.col_scale_n == 0) {
+    // f32 output (and residual) tiles of 32 rows x 16 columns move by TMA; accumulation is a TMA reduce-add
+    if (make_tmap(&tm.o, ep.out_f32, a->N, a->M, ep.ldo_f32, 16, 32, CU_TENSOR_MAP_SWIZZLE_64B, true)) return 1;
+    if (ep.residual &&
+        make_tmap(&tm.o2, ep.residual, a->N, a->M, ep.ldr, 16, 32, CU_TENSOR_MAP_SWIZZLE_64B, true))
       return 1;
     ep.tma_store = 1;
   }

@@ -191,6 +191,15 @@ class MAEEngine:
                          col_scale_n=dim)
         ops.attention_fwd(s.qkv, B, T, heads, hd, s.att, s.lse)
         self._fwd_linear(s.att, M, f"{name}/attn/wo", dim, dim, out_f32=s.xb, residual=x_in)
+        period, skip = (T, J) if jumbo else (0, 0)
+        # patch tokens: x = x_b + ff(LN2(x_b))       (src/modeling.py:166 / :201)
+        ops.layernorm_fwd(s.xb, ps.f(f"{name}/norm2/scale"), ps.f(f"{name}/norm2/bias"), LN_EPS, s.xn2, None,
+                          s.mean2, s.rstd2)
+        self._fwd_linear(s.xn2, M, f"{name}/ff/w1", 4 * dim, dim, out_bf16=s.h, out2_bf16=s.g, act=1,
+                         row_period=period, row_skip=skip, row_mask_mode=1 if jumbo else 0)
+        # (every row is written, so that the output tiles can leave by TMA; the CLS rows of a Jumbo block get
+        #  x_b + bias here -- their h/g rows are zero -- and are overwritten by the Jumbo MLP just below)
+        self._fwd_linear(s.g, M, f"{name}/ff/w2", dim, 4 * dim, out_f32=x_out, residual=s.xb)
         if jumbo:
             Jd = J * dim
             # c = LN3(cls concat); c = c + jumbo_mlp(c)      (src/modeling.py:194-199)
@@ -199,14 +208,6 @@ class MAEEngine:
             self._fwd_linear(s.cn16, B, "model/jumbo_mlp/w1", 4 * Jd, Jd, out_bf16=s.hj, out2_bf16=s.gj, act=1)
             self._fwd_linear(s.gj, B, "model/jumbo_mlp/w2", Jd, 4 * Jd, out_f32=x_out, ldo_f32=T * dim,
                              residual=s.cn)
-        period, skip = (T, J) if jumbo else (0, 0)
-        # patch tokens: x = x_b + ff(LN2(x_b))       (src/modeling.py:166 / :201)
-        ops.layernorm_fwd(s.xb, ps.f(f"{name}/norm2/scale"), ps.f(f"{name}/norm2/bias"), LN_EPS, s.xn2, None,
-                          s.mean2, s.rstd2)
-        self._fwd_linear(s.xn2, M, f"{name}/ff/w1", 4 * dim, dim, out_bf16=s.h, out2_bf16=s.g, act=1,
-                         row_period=period, row_skip=skip, row_mask_mode=1 if jumbo else 0)
-        self._fwd_linear(s.g, M, f"{name}/ff/w2", dim, 4 * dim, out_f32=x_out, residual=s.xb, row_period=period,
-                         row_skip=skip, row_mask_mode=2 if jumbo else 0)
 
     # ------------------------------------------------------------------ backward
     def backward(self, zero_grads: bool = True) -> None:
