@@ -195,6 +195,13 @@ int jm_adamw(float* p, const float* g, float* m, float* v, jm_bf16* p_bf16, long
 
 int jm_cast_bf16(const float* x, jm_bf16* y, long n, void* stream);
 
+/* dst = src + bias (bias optional) over a strided [rows, cols] f32 view (cols, lds, ldd multiples of 4), written
+ * as f32 and/or bf16.  Seeds the output of a split-K GEMM with residual + bias (Jumbo MLP output,
+ * src/modeling.py:199) and converts an f32 gradient for a bf16 consumer.  No reference counterpart: XLA fuses
+ * these adds/converts into their neighbours. */
+int jm_add_bias_cast(const float* src, long lds, int rows, int cols, const float* bias, float* dst_f32, long ldd,
+                     jm_bf16* dst_bf16, long ldd16, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -818,3 +818,39 @@ extern "C" int jm_cast_bf16(const float* x, jm_bf16* y, long n, void* stream) {
   JM_AFTER_LAUNCH();
   return 0;
 }
+
+// dst = src + bias over a strided [rows, cols] f32 view, written as f32 and/or bf16: seeds an output that a
+// split-K GEMM then accumulates into, and hands an f32 result to a bf16 consumer.
+__global__ void add_bias_cast_kernel(const float* __restrict__ src, long lds, int rows, int cols,
+                                     const float* __restrict__ bias, float* __restrict__ dst_f32, long ldd,
+                                     __nv_bfloat16* __restrict__ dst_bf16, long ldd16) {
+  const int c4 = cols >> 2;
+  const long total = static_cast<long>(rows) * c4;
+  for (long i = blockIdx.x * static_cast<long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long>(gridDim.x) * blockDim.x) {
+    const int r = static_cast<int>(i / c4), c = static_cast<int>(i - static_cast<long>(r) * c4) * 4;
+    float4 v = *reinterpret_cast<const float4*>(src + r * lds + c);
+    if (bias) {
+      const float4 b = *reinterpret_cast<const float4*>(bias + c);
+      v.x += b.x, v.y += b.y, v.z += b.z, v.w += b.w;
+    }
+    if (dst_f32) *reinterpret_cast<float4*>(dst_f32 + r * ldd + c) = v;
+    if (dst_bf16) *reinterpret_cast<uint2*>(dst_bf16 + r * ldd16 + c) = make_uint2(pack_bf16(v.x, v.y), pack_bf16(v.z, v.w));
+  }
+}
+
+extern "C" int jm_add_bias_cast(const float* src, long lds, int rows, int cols, const float* bias, float* dst_f32,
+                                long ldd, jm_bf16* dst_bf16, long ldd16, void* stream) {
+  JM_CHECK(src && (dst_f32 || dst_bf16), "jm_add_bias_cast: null argument");
+  JM_CHECK(rows >= 0 && cols >= 0 && cols % 4 == 0 && lds % 4 == 0, "jm_add_bias_cast: cols and lds must be multiples of 4");
+  JM_CHECK((!dst_f32 || ldd % 4 == 0) && (!dst_bf16 || ldd16 % 4 == 0), "jm_add_bias_cast: ldd must be a multiple of 4");
+  if (rows == 0 || cols == 0) return 0;
+  const long total = static_cast<long>(rows) * (cols / 4);
+  long blocks = (total + 255) / 256;
+  const long cap = static_cast<long>(sm_count()) * 8;
+  if (blocks > cap) blocks = cap;
+  add_bias_cast_kernel<<<static_cast<int>(blocks), 256, 0, STREAM>>>(src, lds, rows, cols, bias, dst_f32, ldd,
+                                                                     reinterpret_cast<__nv_bfloat16*>(dst_bf16), ldd16);
+  JM_AFTER_LAUNCH();
+  return 0;
+}

@@ -56,8 +56,8 @@ class _Block:
         if jumbo:
             Jd = J * dim
             self.mean3, self.rstd3 = e(B, dt=F32), e(B, dt=F32)
-            self.cn, self.cn16 = e(B, Jd, dt=F32), e(B, Jd)
-            self.hj, self.gj = e(B, 4 * Jd), e(B, 4 * Jd)
+            self.cn = e(B, Jd, dt=F32)
+            self.hj = e(B, 4 * Jd)              # (cn16, gj, dhj16, dc16: slices of the engine's all-layer buffers)
 
 
 class MAEEngine:
@@ -86,6 +86,16 @@ class MAEEngine:
         # encoder
         self.xa: List[torch.Tensor] = [e(self.Me, d, dt=F32) for _ in range(cfg.layers + 1)]
         self.enc = [_Block(self.Me, d, cfg.heads, B, self.Te, J, True, dev) for _ in range(cfg.layers)]
+        # The Jumbo MLP is ONE set of weights applied in every layer (src/modeling.py:234): its inputs and
+        # output gradients are kept layer after layer in [layers * B, .] buffers, so that each weight gradient
+        # is a single GEMM over K = layers * B at the end of the backward pass instead of one read-modify-write
+        # of the 85 MB gradient per layer.
+        L, Jd = cfg.layers, J * d
+        self.cn16_all, self.gj_all = e(L * B, Jd), e(L * B, 4 * Jd)
+        self.dhj16_all, self.dc16_all = e(L * B, 4 * Jd), e(L * B, Jd)
+        for i, blk in enumerate(self.enc):
+            blk.cn16, blk.gj = self.cn16_all[i * B:(i + 1) * B], self.gj_all[i * B:(i + 1) * B]
+            blk.dhj16, blk.dc16 = self.dhj16_all[i * B:(i + 1) * B], self.dc16_all[i * B:(i + 1) * B]
         self.meanF, self.rstdF = e(self.Me, dt=F32), e(self.Me, dt=F32)
         self.enc_n = e(self.Me, d)
         self.y = e(self.Me, dd, dt=F32)
@@ -109,7 +119,6 @@ class MAEEngine:
         self.datt16 = e(wmax)
         self.delta_ws = e(B * max(cfg.heads * self.Te, cfg.dec_heads * self.Td), dt=F32)
         self.dy16 = e(self.Me, dd)
-        self.dhj16 = e(B, 4 * J * d)
         self.dcn16 = e(B, J * d)
         ln_ws = max(ops.layernorm_bwd_workspace(Mx, max(d, dd)), ops.layernorm_bwd_workspace(B, J * d))
         self.ln_ws = torch.empty(ln_ws, dtype=torch.uint8, device=dev)
@@ -206,8 +215,10 @@ class MAEEngine:
             ops.layernorm_fwd(s.xb, ps.f(f"{name}/norm3/scale"), ps.f(f"{name}/norm3/bias"), LN_EPS, s.cn16, s.cn,
                               s.mean3, s.rstd3, rows=B, dim=Jd, ldx=T * dim, ldy=Jd, ldyf=Jd)
             self._fwd_linear(s.cn16, B, "model/jumbo_mlp/w1", 4 * Jd, Jd, out_bf16=s.hj, out2_bf16=s.gj, act=1)
-            self._fwd_linear(s.gj, B, "model/jumbo_mlp/w2", Jd, 4 * Jd, out_f32=x_out, ldo_f32=T * dim,
-                             residual=s.cn)
+            # w2 has few output tiles and a long K: seed the CLS rows with c + bias, then split-K accumulate
+            ops.add_bias_cast(s.cn, B, Jd, bias=ps.f("model/jumbo_mlp/w2/bias"), dst_f32=x_out, ldd=T * dim)
+            ops.gemm(s.gj, self._W("model/jumbo_mlp/w2/kernel"), B, Jd, 4 * Jd, b_mn=True,
+                     ldb=ps.ld("model/jumbo_mlp/w2/kernel"), out_f32=x_out, ldo_f32=T * dim, accumulate=True)
 
     # ------------------------------------------------------------------ backward
     def backward(self, zero_grads: bool = True) -> None:
@@ -286,6 +297,13 @@ class MAEEngine:
             # ---- CLS parameter and patch embedding (its bias gradient came from layer 0's LN1 backward)
             dx, dx16 = view(self.dxA, Me, d), view(self.dxA16, Me, d)
             ops.colsum(dx, B, J * d, ps.grad("model/cls_tokens"), ldx=Te * d)
+            # shared Jumbo MLP: weight gradients over all layers at once (K = layers * B)
+            L, Jd = cfg.layers, J * d
+            for nm, X, dY, rows, cols in (("w1", self.cn16_all, self.dhj16_all, Jd, 4 * Jd),
+                                          ("w2", self.gj_all, self.dc16_all, 4 * Jd, Jd)):
+                ops.gemm(X, dY, rows, cols, L * B, a_mn=True, b_mn=True,
+                         out_f32=ps.grad(f"model/jumbo_mlp/{nm}/kernel"), ldo_f32=ps.ld(f"model/jumbo_mlp/{nm}/kernel"),
+                         accumulate=True)
             ops.gemm(self.patches, dx16, P, d, Me, a_mn=True, b_mn=True, lda=Pp,
                      out_f32=ps.grad("model/embed/wte/kernel"), ldo_f32=ps.ld("model/embed/wte/kernel"),
                      accumulate=True)
@@ -314,10 +332,16 @@ class MAEEngine:
         if jumbo:
             # ---- Jumbo CLS: c_out = c + w2j(gelu(w1j c)), c = LN3(cls concat); strided [B, J*dim] views
             Jd, ldc = J * dim, T * dim
-            self._bwd_linear(s.gj, dx16, B, "model/jumbo_mlp/w2", Jd, 4 * Jd, dX16=self.dhj16, dy_ld=ldc, act=2,
-                             aux=s.hj, colsum=ps.grad("model/jumbo_mlp/w1/bias"))
-            self._bwd_linear(s.cn16, self.dhj16, B, "model/jumbo_mlp/w1", 4 * Jd, Jd, dX16=self.dcn16, bias=False,
-                             residual=dx, ldr=ldc)
+            # output gradient of w2 = the CLS rows of dx: bias gradient now, a bf16 copy for the batched dW
+            ops.colsum(dx16, B, Jd, ps.grad("model/jumbo_mlp/w2/bias"), ldx=ldc)
+            ops.add_bias_cast(dx, B, Jd, dst_bf16=s.dc16, lds=ldc)
+            ops.gemm(dx16, self._W("model/jumbo_mlp/w2/kernel"), B, 4 * Jd, Jd, b_mn=False, lda=ldc,
+                     ldb=ps.ld("model/jumbo_mlp/w2/kernel"), out_bf16=s.dhj16, act=2, aux=s.hj,
+                     colsum=ps.grad("model/jumbo_mlp/w1/bias"))
+            # d c = d c_out + dh W1^T: split-K accumulate into the CLS rows of dx (f32), bf16 copy for LN3 backward
+            ops.gemm(s.dhj16, self._W("model/jumbo_mlp/w1/kernel"), B, Jd, 4 * Jd, b_mn=False,
+                     ldb=ps.ld("model/jumbo_mlp/w1/kernel"), out_f32=dx, ldo_f32=ldc, accumulate=True)
+            ops.add_bias_cast(dx, B, Jd, dst_bf16=self.dcn16, lds=ldc)
             ops.layernorm_bwd(self.dcn16, s.xb, s.mean3, s.rstd3, ps.f(f"{name}/norm3/scale"), None, dxb, dxb16,
                               ps.grad(f"{name}/norm3/scale"), ps.grad(f"{name}/norm3/bias"), self.ln_ws, rows=B,
                               dim=Jd, ldx=ldc, lddx=ldc, lddxb=ldc)

@@ -240,3 +240,19 @@ def adamw(p: torch.Tensor, g: torch.Tensor, m: torch.Tensor, v: torch.Tensor, p_
 def cast_bf16(x: torch.Tensor, y: torch.Tensor) -> None:
     _chk(x, F32, "x"), _chk(y, BF16, "y")
     check(_lib.load().jm_cast_bf16(ptr(x), ptr(y), x.numel(), stream_ptr()))
+
+
+def add_bias_cast(src: torch.Tensor, rows: int, cols: int, bias: Optional[torch.Tensor] = None,
+                  dst_f32: Optional[torch.Tensor] = None, dst_bf16: Optional[torch.Tensor] = None,
+                  lds: Optional[int] = None, ldd: Optional[int] = None, ldd16: Optional[int] = None) -> None:
+    """dst = src + bias over a strided [rows, cols] f32 view, as f32 and/or bf16 (jm_add_bias_cast)."""
+    _chk(src, F32, "src")
+    if bias is not None:
+        _chk(bias, F32, "bias")
+    if dst_f32 is not None:
+        _chk(dst_f32, F32, "dst_f32")
+    if dst_bf16 is not None:
+        _chk(dst_bf16, BF16, "dst_bf16")
+    check(_lib.load().jm_add_bias_cast(ptr(src), lds if lds is not None else cols, rows, cols, ptr(bias), ptr(dst_f32),
+                                       ldd if ldd is not None else cols, ptr(dst_bf16),
+                                       ldd16 if ldd16 is not None else cols, stream_ptr()))

@@ -519,3 +519,19 @@ def test_gemm_bf16_epilogues_every_tile_shape(ops, M, N, K, bn, pair):
     ref = (dY.float() @ W2.float().t()) * hh.grad.cuda() * keep
     assert torch.allclose(dH.float(), ref, rtol=2 ** -6, atol=2e-3)
     assert torch.allclose(cs - 1, ref.sum(0), rtol=1e-2, atol=0.3)   # sums of bf16-rounded values over M rows
+
+
+def test_add_bias_cast_strided(ops):
+    """jm_add_bias_cast: dst = src + bias over strided views, f32 and bf16 destinations."""
+    g = torch.Generator(device="cuda").manual_seed(5)
+    rows, cols, lds, ldd, ldd16 = 37, 24, 40, 56, 32
+    src = torch.randn(rows, lds, generator=g, device="cuda")
+    bias = torch.randn(cols, generator=g, device="cuda")
+    d32 = torch.full((rows, ldd), 9.0, device="cuda")
+    d16 = torch.full((rows, ldd16), 9.0, dtype=BF16, device="cuda")
+    ops.add_bias_cast(src, rows, cols, bias=bias, dst_f32=d32, dst_bf16=d16, lds=lds, ldd=ldd, ldd16=ldd16)
+    want = src[:, :cols] + bias
+    assert torch.equal(d32[:, :cols], want) and torch.equal(d32[:, cols:], torch.full_like(d32[:, cols:], 9.0))
+    assert torch.equal(d16[:, :cols], want.to(BF16)) and torch.equal(d16[:, cols:], torch.full_like(d16[:, cols:], 9.0))
+    ops.add_bias_cast(src, rows, cols, dst_bf16=d16, lds=lds, ldd16=ldd16)
+    assert torch.equal(d16[:, :cols], src[:, :cols].to(BF16))

@@ -220,11 +220,13 @@ def test_cuda_graph_path_equals_eager():
     g_e = store.g.clone()
     loss_g = eng.run_graph(im, nz, zero_grads=True).clone()
     torch.cuda.synchronize()
-    assert loss_e.item() == loss_g.item()
-    # identical kernels; only the f32 atomics of the weight-gradient epilogues may reorder
-    assert torch.allclose(store.g, g_e, rtol=1e-4, atol=1e-7)
+    # identical kernels; only the order of the f32 reductions in L2 (split-K of the Jumbo MLP output in the
+    # forward pass, weight-gradient accumulation in the backward pass) may differ from run to run
+    assert abs(loss_e.item() - loss_g.item()) <= 1e-5 * abs(loss_e.item())
+    # (a last-bit change of a forward value can flip bf16 roundings downstream: compare in the l2 norm)
+    assert (store.g - g_e).norm().item() <= 2e-3 * g_e.norm().item()
     eng.run_graph(im, nz, zero_grads=False)
-    assert torch.allclose(store.g, 2 * g_e, rtol=1e-4, atol=1e-7)
+    assert (store.g - 2 * g_e).norm().item() <= 4e-3 * g_e.norm().item()
 
 
 def test_segmented_backward_graphs_equal_whole_backward():
@@ -238,6 +240,6 @@ def test_segmented_backward_graphs_equal_whole_backward():
     red = GradReducer(store)
     loss = eng.run_graph_overlapped(im, nz, True, red)
     torch.cuda.synchronize()
-    assert torch.allclose(store.g, g_ref, rtol=1e-4, atol=1e-7)
+    assert (store.g - g_ref).norm().item() <= 2e-3 * g_ref.norm().item()   # L2 reduction order, see above
     assert torch.isfinite(loss).all()
     assert eng.num_bwd_segments() == 1 + (cfg.layers + eng.ENC_LAYERS_PER_SEGMENT - 1) // eng.ENC_LAYERS_PER_SEGMENT
