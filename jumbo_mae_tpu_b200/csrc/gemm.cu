@@ -116,6 +116,52 @@ __device__ __forceinline__ float gelu_grad_fast(float x) {
   return fmaf(a, du, fmaf(0.5f, t, 0.5f));
 }
 
+// Packed f32x2 arithmetic (sm_100: one FFMA2 issue slot does two FMAs).  The epilogues are bound by
+// instruction issue, not by the FMA pipe, so the polynomial parts of GELU run on column pairs.
+typedef unsigned long long f32x2;
+__device__ __forceinline__ f32x2 pack2(float a, float b) {
+  f32x2 r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(a), "f"(b));
+  return r;
+}
+__device__ __forceinline__ void unpack2(f32x2 v, float& a, float& b) {
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(v));
+}
+__device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) {
+  f32x2 r;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+  return r;
+}
+__device__ __forceinline__ f32x2 mul2(f32x2 a, f32x2 b) {
+  f32x2 r;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+// gelu_fast / gelu_grad_fast on a pair (identical arithmetic, element-wise)
+__device__ __forceinline__ f32x2 gelu_fast2(f32x2 x) {
+  const f32x2 c1 = pack2(0.0356774081f, 0.0356774081f), c0 = pack2(0.7978845608f, 0.7978845608f);
+  const f32x2 half = pack2(0.5f, 0.5f);
+  const f32x2 u = mul2(x, fma2(mul2(x, x), c1, c0));
+  float u0, u1;
+  unpack2(u, u0, u1);
+  const f32x2 t = pack2(tanh_fast(u0), tanh_fast(u1));
+  const f32x2 hx = mul2(x, half);
+  return fma2(hx, t, hx);
+}
+__device__ __forceinline__ f32x2 gelu_grad_fast2(f32x2 x) {
+  const f32x2 c1 = pack2(0.0356774081f, 0.0356774081f), c0 = pack2(0.7978845608f, 0.7978845608f);
+  const f32x2 c3 = pack2(0.1070322243f, 0.1070322243f), half = pack2(0.5f, 0.5f), one = pack2(1.0f, 1.0f);
+  const f32x2 x2 = mul2(x, x);
+  const f32x2 u = mul2(x, fma2(x2, c1, c0));
+  float u0, u1;
+  unpack2(u, u0, u1);
+  const float t0 = tanh_fast(u0), t1 = tanh_fast(u1);
+  const f32x2 t = pack2(t0, t1), nt = pack2(-t0, -t1);
+  const f32x2 du = fma2(x2, c3, c0);
+  const f32x2 a = mul2(mul2(x, half), fma2(nt, t, one));
+  return fma2(a, du, fma2(half, t, half));
+}
+
 // Epilogue specialisations: straight-line code per kind (the generic one keeps every runtime switch).
 enum : int {
   EPI_BF16 = 0,      // out_bf16 = (acc + bias) * scale
@@ -636,8 +682,9 @@ __device__ __forceinline__ void epilogue_rows(const EpiParams& ep, const GemmSha
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
               const float2 x = unpack_bf16(w[k]);
-              const float v0 = __uint_as_float(r[h][8 * j + 2 * k]) * gelu_grad_fast(x.x);
-              const float v1 = __uint_as_float(r[h][8 * j + 2 * k + 1]) * gelu_grad_fast(x.y);
+              const f32x2 a = pack2(__uint_as_float(r[h][8 * j + 2 * k]), __uint_as_float(r[h][8 * j + 2 * k + 1]));
+              float v0, v1;
+              unpack2(mul2(a, gelu_grad_fast2(pack2(x.x, x.y))), v0, v1);
               o[k] = pack_bf16(v0, v1);
             }
             sts128_or_zero(a, o[0], o[1], o[2], o[3], zflag);
@@ -645,19 +692,27 @@ __device__ __forceinline__ void epilogue_rows(const EpiParams& ep, const GemmSha
         } else {
           // branch-free (one basic block for the 32 columns); rows that store zeros are handled at the STS
           uint32_t P[16];
-          float v[32];
+          f32x2 v[16];  // column pairs
+          const f32x2 sc2 = pack2(sc[h], sc[h]);
           if (has_bias) {  // warp-uniform
 #pragma unroll
-            for (int j = 0; j < 32; ++j)
-              v[j] = fmaf(__uint_as_float(r[h][j]), sc[h], __shfl_sync(kFull, bs[h], j));
+            for (int j = 0; j < 16; ++j)
+              v[j] = fma2(pack2(__uint_as_float(r[h][2 * j]), __uint_as_float(r[h][2 * j + 1])), sc2,
+                          pack2(__shfl_sync(kFull, bs[h], 2 * j), __shfl_sync(kFull, bs[h], 2 * j + 1)));
           } else {
 #pragma unroll
-            for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[h][j]) * sc[h];
+            for (int j = 0; j < 16; ++j)
+              v[j] = mul2(pack2(__uint_as_float(r[h][2 * j]), __uint_as_float(r[h][2 * j + 1])), sc2);
           }
 #pragma unroll
           for (int j = 0; j < 16; ++j) {
-            P[j] = pack_bf16(v[2 * j], v[2 * j + 1]);
-            if constexpr (EPI == EPI_GELU_FWD) G[j] = pack_bf16(gelu_fast(v[2 * j]), gelu_fast(v[2 * j + 1]));
+            float a, b;
+            unpack2(v[j], a, b);
+            P[j] = pack_bf16(a, b);
+            if constexpr (EPI == EPI_GELU_FWD) {
+              unpack2(gelu_fast2(v[j]), a, b);
+              G[j] = pack_bf16(a, b);
+            }
           }
           staging_free();
 #pragma unroll

@@ -5,6 +5,6 @@ cp jumbo_mae_tpu_b200/libjumbo_mae_b200.so /tmp/lib_keep.so
 for v in "$@"; do
   cp exp/lib_$v.so jumbo_mae_tpu_b200/libjumbo_mae_b200.so
   echo "== $v"
-  ONLY=gemm timeout 120 python tools/bench_kernels.py 2>&1 | grep -v "timed out" | grep -E "${FILTER:-total}"
+  ONLY=${ONLY:-gemm} timeout 120 python tools/bench_kernels.py 2>&1 | grep -v "timed out" | grep -E "${FILTER:-total}"
 done
 cp /tmp/lib_keep.so jumbo_mae_tpu_b200/libjumbo_mae_b200.so

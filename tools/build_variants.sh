@@ -3,13 +3,12 @@
 set -e
 cd "$(dirname "$0")/.."
 mkdir -p exp
-cp jumbo_mae_tpu_b200/libjumbo_mae_b200.so /tmp/lib_keep.so 2>/dev/null || true
 for spec in "$@"; do
   name="${spec%%=*}"; defs="${spec#*=}"
-  touch jumbo_mae_tpu_b200/csrc/gemm.cu
+  touch jumbo_mae_tpu_b200/csrc/*.cu
   JM_NVCC_DEFS="$defs" python -m jumbo_mae_tpu_b200.build > /dev/null 2> exp/build_$name.log
   cp jumbo_mae_tpu_b200/libjumbo_mae_b200.so exp/lib_$name.so
-  echo "$name: $(grep -A3 'gemm2_kernelILb0ELb1ELi2E' exp/build_$name.log | grep spill)"
+  echo "built $name ($defs)"
 done
-touch jumbo_mae_tpu_b200/csrc/gemm.cu
+touch jumbo_mae_tpu_b200/csrc/*.cu
 python -m jumbo_mae_tpu_b200.build > /dev/null 2>&1

@@ -12,6 +12,10 @@ __global__ void k(float* out, int iters) {
       if (OP == 1) asm volatile("ex2.approx.ftz.f32 %0, %0;" : "+f"(a[i]));
       if (OP == 2) asm volatile("rcp.approx.ftz.f32 %0, %0;" : "+f"(a[i]));
       if (OP == 3) asm volatile("fma.rn.f32 %0, %0, %0, %0;" : "+f"(a[i]));
+      if (OP == 4) {
+        unsigned long long& p = *reinterpret_cast<unsigned long long*>(&a[i & ~1]);
+        asm volatile("fma.rn.f32x2 %0, %0, %0, %0;" : "+l"(p));
+      }
     }
   }
   float s = 0;
@@ -44,5 +48,6 @@ int main() {
   run<1>("ex2.approx");
   run<2>("rcp.approx");
   run<3>("fma");
+  run<4>("fma.f32x2 (instructions; x2 for FMAs)");
   return 0;
 }
