@@ -319,15 +319,15 @@ def run_ours(args):
             "achieved": dw_tflops, "peak": peaks["bf16_burst"], "unit": "TFLOP/s",
             "frac": dw_tflops / peaks["bf16_burst"],
             # dram__bytes_read.sum + dram__bytes_write.sum of one launch, ncu --set full
-            # (profiles/r1c_gemm_dw_ncu_full.md); algorithmic bytes 2*(M+N)*K + 4*M*N = 525.9 MB
-            "traffic": 530.5e6 if micro == 512 and args.config == "vit_b16" else None,
+            # (profiles/r1e_gemm_dw_ncu_full.md); algorithmic bytes 2*(M+N)*K + 4*M*N = 525.9 MB
+            "traffic": 529.8e6 if micro == 512 and args.config == "vit_b16" else None,
             "peak_source": f"{peaks['source']} (burst: kernel timed alone)", "kernel_ms": dw_ms,
         },
         "roofline_gelu_fwd": {
             "bound": "tensor", "kernel": f"gemm2_kernel<K,MN,GELU> (CTA pair, 256x256 tile) decoder FFN w1 forward M={M} N={N} K={K}",
             "achieved": gemm_tflops, "peak": peaks["bf16_burst"], "unit": "TFLOP/s",
             "frac": gemm_tflops / peaks["bf16_burst"],
-            "traffic": 888.7e6 if micro == 512 and args.config == "vit_b16" else None,
+            "traffic": 905.7e6 if micro == 512 and args.config == "vit_b16" else None,
             "kernel_ms": gemm_ms,
             "note": "writes 834 MB (pre-activation + GELU) per launch: 128 us of HBM time against 129 us of MMA time",
         },
