@@ -16,6 +16,13 @@ __device__ __forceinline__ float norm_pixel(uint8_t u, int c) {
   return __fdiv_rn(__fsub_rn(__fdiv_rn(static_cast<float>(u), 255.0f), c_mean[c]), c_std[c]);
 }
 
+// The 768 possible values of norm_pixel, computed once per block with the same IEEE operations (two divisions
+// per element cost ~40 instructions; a row kernel that recomputes them per element is ALU-bound).
+__device__ __forceinline__ void fill_norm_lut(float* lut /* [3][256] in shared memory */) {
+  for (int i = threadIdx.x; i < 768; i += blockDim.x) lut[i] = norm_pixel(static_cast<uint8_t>(i & 255), i >> 8);
+  __syncthreads();
+}
+
 __device__ __forceinline__ float block_sum(float v, float* red /* >= 32 floats */) {
   v = warp_sum(v);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = (blockDim.x + 31) >> 5;
@@ -63,28 +70,63 @@ __global__ void index_sequence_kernel(const float* __restrict__ x, const int* __
 }
 
 // ---------------------------------------------------------------- patchify
-__global__ void patchify_kernel(const uint8_t* __restrict__ images, int S, int p, const int* __restrict__ ids,
-                                int n_sel, int rows_per_image, int row_off, __nv_bfloat16* __restrict__ out,
-                                long ldo) {
-  const int r = blockIdx.x, b = blockIdx.y;
-  __nv_bfloat16* dst = out + (static_cast<long>(b) * rows_per_image + r) * ldo;
-  const int P = p * p * 3;
-  if (r < row_off || r >= row_off + n_sel) {
-    for (int e = threadIdx.x; e < ldo; e += blockDim.x) dst[e] = __float2bfloat16(0.f);
-    return;
-  }
-  const int g = S / p;
-  const int patch = ids ? ids[r - row_off] : (r - row_off);
-  const int gy = patch / g, gx = patch - gy * g;
-  const uint8_t* img = images + static_cast<long>(b) * 3 * S * S;
-  for (int e = threadIdx.x; e < ldo; e += blockDim.x) {
-    float v = 0.f;
-    if (e < P) {
-      const int c = e % 3, pix = e / 3;
-      const int ph = pix / p, pw = pix - ph * p;
-      v = norm_pixel(img[(static_cast<long>(c) * S + gy * p + ph) * S + gx * p + pw], c);
+// Copies one patch (3 planes of p x p uint8) into spix[c][ph][pw] with the lanes of one warp: a run of p
+// contiguous bytes per (plane, row); 16-byte vector copies when p == 16 and the image rows keep them aligned.
+__device__ __forceinline__ void stage_patch(uint8_t* spix, const uint8_t* img, int S, int p, int gy, int gx, int lane) {
+  const int runs = 3 * p;
+  if (p == 16 && (S & 15) == 0) {
+    for (int r = lane; r < runs; r += 32) {
+      const int c = r >> 4, ph = r & 15;
+      *reinterpret_cast<uint4*>(spix + r * 16) =
+          *reinterpret_cast<const uint4*>(img + (static_cast<long>(c) * S + gy * 16 + ph) * S + gx * 16);
     }
-    dst[e] = __float2bfloat16(v);
+  } else {
+    for (int r = lane; r < runs; r += 32) {
+      const int c = r / p, ph = r - c * p;
+      const uint8_t* src = img + (static_cast<long>(c) * S + gy * p + ph) * S + gx * p;
+      for (int i = 0; i < p; ++i) spix[r * p + i] = src[i];
+    }
+  }
+}
+
+
+// One warp per output row, eight rows in flight per block (see patch_loss_kernel for why).
+__global__ void __launch_bounds__(256)
+patchify_kernel(const uint8_t* __restrict__ images, int S, int p, const int* __restrict__ ids, int n_sel,
+                int rows_per_image, int row_off, __nv_bfloat16* __restrict__ out, long ldo, int batch) {
+  __shared__ __align__(16) uint8_t spix_all[8][2048];  // per warp: the patch's 3 planes of p x p bytes (P <= 2048, checked)
+  __shared__ float lut[768];
+  fill_norm_lut(lut);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  uint8_t* spix = spix_all[warp];
+  const int pp = p * p, P = pp * 3, g = S / p;
+  const long rows = static_cast<long>(batch) * rows_per_image;
+  for (long row = static_cast<long>(blockIdx.x) * 8 + warp; row < rows; row += static_cast<long>(gridDim.x) * 8) {
+    const int b = static_cast<int>(row / rows_per_image), r = static_cast<int>(row - static_cast<long>(b) * rows_per_image);
+    __nv_bfloat16* dst = out + row * ldo;
+    if (r < row_off || r >= row_off + n_sel) {
+      for (int e = lane * 4; e < ldo; e += 128) *reinterpret_cast<uint2*>(dst + e) = make_uint2(0u, 0u);
+      continue;
+    }
+    const int patch = ids ? ids[r - row_off] : (r - row_off);
+    const int gy = patch / g, gx = patch - gy * g;
+    const uint8_t* img = images + static_cast<long>(b) * 3 * S * S;
+    __syncwarp();
+    stage_patch(spix, img, S, p, gy, gx, lane);
+    __syncwarp();
+    for (int e0 = lane * 4; e0 < ldo; e0 += 128) {  // ldo is a multiple of 4 (checked)
+      float v[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int e = e0 + j;
+        v[j] = 0.f;
+        if (e < P) {
+          const int pix = e / 3, c = e - pix * 3;
+          v[j] = lut[c * 256 + spix[c * pp + pix]];
+        }
+      }
+      *reinterpret_cast<uint2*>(dst + e0) = make_uint2(pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]));
+    }
   }
 }
 
@@ -105,68 +147,110 @@ __global__ void extract_patches_kernel(const uint8_t* __restrict__ images, int S
 constexpr int kLossThreads = 256;
 constexpr int kLossMaxPer = 8;  // P <= 2048
 
+// One WARP per token row, eight rows in flight per block (a block per row leaves one dependent chain of four
+// global round trips per 256 threads: latency-bound at a seventh of the HBM rate).  The patch's uint8 pixels are
+// staged in the warp's slice of shared memory (3 planes of p x p bytes); every lane then owns groups of 4
+// consecutive elements: one float4 read of the prediction, one 8-byte bf16 write of the gradient.
+constexpr int kLossWarps = kLossThreads / 32;
+static int loss_blocks(int batch, int tokens) {
+  const long want = (static_cast<long>(batch) * tokens + kLossWarps - 1) / kLossWarps;
+  const long cap = static_cast<long>(sm_count()) * 16;
+  return static_cast<int>(want < cap ? want : cap);
+}
+constexpr int kLossMaxP = 2048;
+
+template <int kLossGroups>  // 4-element groups per lane: P <= 128 * kLossGroups
 __global__ void __launch_bounds__(kLossThreads)
 patch_loss_kernel(const float* __restrict__ pred, long ldp, const uint8_t* __restrict__ images,
                   const float* __restrict__ mask_row, int S, int p, int J, int norm_pix, float grad_scale,
                   float* __restrict__ partial, __nv_bfloat16* __restrict__ dpred, long lddp, int batch) {
-  __shared__ float red[32];
-  const int g = S / p, N = g * g, P = p * p * 3;
-  const int t = blockIdx.x;  // token index within the image, 0 .. J+N-1
-  const int b = blockIdx.y;
-  const long row = static_cast<long>(b) * (J + N) + t;
-  const int patch = t - J;
-  const bool masked = patch >= 0 && mask_row[patch] > 0.f;
-  if (!masked) {
-    if (patch >= 0 && threadIdx.x == 0) partial[static_cast<long>(b) * N + patch] = 0.f;
-    if (dpred)
-      for (int e = threadIdx.x; e < P; e += blockDim.x) dpred[row * lddp + e] = __float2bfloat16(0.f);
-    return;
-  }
+  __shared__ __align__(16) uint8_t spix_all[kLossWarps][kLossMaxP];
+  __shared__ float lut[768];
+  fill_norm_lut(lut);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  uint8_t* spix = spix_all[warp];
+  const int g = S / p, N = g * g, pp = p * p, P = pp * 3, T = J + N;
   float cnt = 0.f;
-  for (int i = threadIdx.x; i < N; i += blockDim.x) cnt += mask_row[i] > 0.f ? 1.f : 0.f;
-  const float num_masked = block_sum(cnt, red);
-
-  const int gy = patch / g, gx = patch - gy * g;
-  const uint8_t* img = images + static_cast<long>(b) * 3 * S * S;
-  float tv[kLossMaxPer];
-  float s = 0.f;
-#pragma unroll
-  for (int k = 0; k < kLossMaxPer; ++k) {
-    const int e = threadIdx.x + k * kLossThreads;
-    tv[k] = 0.f;
-    if (e < P) {
-      const int c = e % 3, pix = e / 3;
-      const int ph = pix / p, pw = pix - ph * p;
-      tv[k] = norm_pixel(img[(static_cast<long>(c) * S + gy * p + ph) * S + gx * p + pw], c);
-      s += tv[k];
-    }
-  }
-  if (norm_pix) {  // src/pretraining.py:115-118, jnp.var is the biased variance
-    const float mean = block_sum(s, red) / P;
-    float ss = 0.f;
-#pragma unroll
-    for (int k = 0; k < kLossMaxPer; ++k) {
-      const int e = threadIdx.x + k * kLossThreads;
-      if (e < P) ss += (tv[k] - mean) * (tv[k] - mean);
-    }
-    const float var = block_sum(ss, red) / P;
-    const float inv = 1.0f / sqrtf(var + 1e-6f);
-#pragma unroll
-    for (int k = 0; k < kLossMaxPer; ++k) tv[k] = (tv[k] - mean) * inv;
-  }
+  for (int i = lane; i < N; i += 32) cnt += mask_row[i] > 0.f ? 1.f : 0.f;
+  const float num_masked = warp_sum(cnt);
   const float gscale = 2.0f * grad_scale / (static_cast<float>(P) * num_masked * static_cast<float>(batch));
-  float sq = 0.f;
-#pragma unroll
-  for (int k = 0; k < kLossMaxPer; ++k) {
-    const int e = threadIdx.x + k * kLossThreads;
-    if (e < P) {
-      const float d = pred[row * ldp + e] - tv[k];
-      sq += d * d;
-      if (dpred) dpred[row * lddp + e] = __float2bfloat16(d * gscale);
+  const long rows = static_cast<long>(batch) * T;
+  for (long row = static_cast<long>(blockIdx.x) * kLossWarps + warp; row < rows;
+       row += static_cast<long>(gridDim.x) * kLossWarps) {
+    const int b = static_cast<int>(row / T), t = static_cast<int>(row - static_cast<long>(b) * T);
+    const int patch = t - J;
+    const bool masked = patch >= 0 && mask_row[patch] > 0.f;
+    if (!masked) {
+      if (patch >= 0 && lane == 0) partial[static_cast<long>(b) * N + patch] = 0.f;
+      if (dpred)
+        for (int e = lane * 4; e < P; e += 128) *reinterpret_cast<uint2*>(dpred + row * lddp + e) = make_uint2(0u, 0u);
+      continue;
     }
+    const int gy = patch / g, gx = patch - gy * g;
+    const uint8_t* img = images + static_cast<long>(b) * 3 * S * S;
+    __syncwarp();  // the previous row's readers are done with the staging slice
+    stage_patch(spix, img, S, p, gy, gx, lane);
+    __syncwarp();
+    float tv[kLossGroups][4];
+    float4 pv[kLossGroups];
+    float s = 0.f;
+#pragma unroll
+    for (int k = 0; k < kLossGroups; ++k) {
+      const int e0 = (lane + 32 * k) * 4;
+      pv[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (e0 < P) pv[k] = *reinterpret_cast<const float4*>(pred + row * ldp + e0);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int e = e0 + j;
+        tv[k][j] = 0.f;
+        if (e < P) {
+          const int pix = e / 3, c = e - pix * 3;
+          tv[k][j] = lut[c * 256 + spix[c * pp + pix]];
+          s += tv[k][j];
+        }
+      }
+    }
+    if (norm_pix) {  // src/pretraining.py:115-118, jnp.var is the biased variance
+      const float mean = warp_sum(s) / P;
+      float ss = 0.f;
+#pragma unroll
+      for (int k = 0; k < kLossGroups; ++k)
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+          if ((lane + 32 * k) * 4 + j < P) ss += (tv[k][j] - mean) * (tv[k][j] - mean);
+      const float var = warp_sum(ss) / P;
+      const float inv = 1.0f / sqrtf(var + 1e-6f);
+#pragma unroll
+      for (int k = 0; k < kLossGroups; ++k)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) tv[k][j] = (tv[k][j] - mean) * inv;
+    }
+    float sq = 0.f;
+#pragma unroll
+    for (int k = 0; k < kLossGroups; ++k) {
+      const int e0 = (lane + 32 * k) * 4;
+      if (e0 < P) {
+        const float d0 = pv[k].x - tv[k][0], d1 = pv[k].y - tv[k][1], d2 = pv[k].z - tv[k][2], d3 = pv[k].w - tv[k][3];
+        sq += d0 * d0 + d1 * d1 + d2 * d2 + d3 * d3;
+        if (dpred)
+          *reinterpret_cast<uint2*>(dpred + row * lddp + e0) =
+              make_uint2(pack_bf16(d0 * gscale, d1 * gscale), pack_bf16(d2 * gscale, d3 * gscale));
+      }
+    }
+    const float tot = warp_sum(sq);
+    if (lane == 0) partial[static_cast<long>(b) * N + patch] = tot / P;
   }
-  const float tot = block_sum(sq, red);
-  if (threadIdx.x == 0) partial[static_cast<long>(b) * N + patch] = tot / P;
+}
+
+static void launch_patch_loss(const float* pred, long ldp, const uint8_t* images, const float* mask_row, int S, int p,
+                              int J, int norm_pix, float grad_scale, float* partial, __nv_bfloat16* dpred, long lddp,
+                              int batch, int N, int P, cudaStream_t stream) {
+  const int grid = loss_blocks(batch, J + N);
+#define JM_LOSS_ARGS pred, ldp, images, mask_row, S, p, J, norm_pix, grad_scale, partial, dpred, lddp, batch
+  if (P <= 768) patch_loss_kernel<6><<<grid, kLossThreads, 0, stream>>>(JM_LOSS_ARGS);
+  else if (P <= 1024) patch_loss_kernel<8><<<grid, kLossThreads, 0, stream>>>(JM_LOSS_ARGS);
+  else patch_loss_kernel<16><<<grid, kLossThreads, 0, stream>>>(JM_LOSS_ARGS);
+#undef JM_LOSS_ARGS
 }
 
 __global__ void patch_loss_finalize_kernel(const float* __restrict__ partial, const float* __restrict__ mask_row,
@@ -444,7 +528,7 @@ __global__ void unshuffle_fwd_kernel(const float* __restrict__ y, const int* __r
   }
 }
 
-constexpr int kUnshufBwdImgs = 16;
+constexpr int kUnshufBwdImgs = 64;  // images per block: the mask-token rows reduce over them before touching L2
 __global__ void unshuffle_bwd_kernel(const float* __restrict__ dout, const int* __restrict__ ids_restore, int batch,
                                      int N, int n, int J, int dim, __nv_bfloat16* __restrict__ dy,
                                      float* __restrict__ dmask) {
@@ -459,21 +543,27 @@ __global__ void unshuffle_bwd_kernel(const float* __restrict__ dout, const int* 
   }
   for (int c = threadIdx.x * 4; c < dim; c += blockDim.x * 4) {
     float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-    for (int b = b0; b < b1; ++b) {
-      const float4 v = *reinterpret_cast<const float4*>(dout + (static_cast<long>(b) * (J + N) + t) * dim + c);
-      if (dst_tok >= 0) {
-        uint2 u = {pack_bf16(v.x, v.y), pack_bf16(v.z, v.w)};
-        *reinterpret_cast<uint2*>(dy + (static_cast<long>(b) * (J + n) + dst_tok) * dim + c) = u;
-      } else {
-        acc.x += v.x, acc.y += v.y, acc.z += v.z, acc.w += v.w;
+    for (int bb = b0; bb < b1; bb += 8) {  // eight independent loads in flight per thread
+      float4 v[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        v[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (bb + i < b1)
+          v[i] = *reinterpret_cast<const float4*>(dout + (static_cast<long>(bb + i) * (J + N) + t) * dim + c);
+      }
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        if (dst_tok >= 0) {
+          if (bb + i < b1) {
+            uint2 u = {pack_bf16(v[i].x, v[i].y), pack_bf16(v[i].z, v[i].w)};
+            *reinterpret_cast<uint2*>(dy + (static_cast<long>(bb + i) * (J + n) + dst_tok) * dim + c) = u;
+          }
+        } else {
+          acc.x += v[i].x, acc.y += v[i].y, acc.z += v[i].z, acc.w += v[i].w;
+        }
       }
     }
-    if (dst_tok < 0 && dmask) {
-      atomicAdd(dmask + c + 0, acc.x);
-      atomicAdd(dmask + c + 1, acc.y);
-      atomicAdd(dmask + c + 2, acc.z);
-      atomicAdd(dmask + c + 3, acc.w);
-    }
+    if (dst_tok < 0 && dmask) atomicAdd(reinterpret_cast<float4*>(dmask + c), acc);  // one 16-byte reduction
   }
 }
 
@@ -587,9 +677,13 @@ extern "C" int jm_patchify(const uint8_t* images, int batch, int image_size, int
   JM_CHECK(image_size % patch_size == 0, "jm_patchify: image size must be a multiple of the patch size");
   JM_CHECK(ldo >= patch_size * patch_size * 3, "jm_patchify: ldo smaller than the patch dimension");
   JM_CHECK(row_off + n_sel <= rows_per_image, "jm_patchify: rows_per_image too small");
+  JM_CHECK(patch_size * patch_size * 3 <= 2048, "jm_patchify: patch dimension %d too large", patch_size * patch_size * 3);
+  JM_CHECK(ldo % 4 == 0 && (reinterpret_cast<uintptr_t>(out) & 7) == 0, "jm_patchify: ldo must be a multiple of 4");
   if (batch == 0) return 0;
-  patchify_kernel<<<dim3(rows_per_image, batch), 256, 0, STREAM>>>(
-      images, image_size, patch_size, ids, n_sel, rows_per_image, row_off, reinterpret_cast<__nv_bfloat16*>(out), ldo);
+  const long want = (static_cast<long>(batch) * rows_per_image + 7) / 8, cap = static_cast<long>(sm_count()) * 16;
+  patchify_kernel<<<static_cast<int>(want < cap ? want : cap), 256, 0, STREAM>>>(
+      images, image_size, patch_size, ids, n_sel, rows_per_image, row_off, reinterpret_cast<__nv_bfloat16*>(out), ldo,
+      batch);
   JM_AFTER_LAUNCH();
   return 0;
 }
@@ -613,12 +707,14 @@ extern "C" int jm_patch_loss(const float* pred, long ldp, const uint8_t* images,
                              jm_bf16* dpred, long lddp, void* workspace, size_t workspace_bytes, void* stream) {
   const int g = image_size / patch_size, N = g * g, P = patch_size * patch_size * 3;
   JM_CHECK(P <= kLossThreads * kLossMaxPer, "jm_patch_loss: patch dimension %d too large", P);
+  JM_CHECK(P % 4 == 0 && ldp % 4 == 0 && (!dpred || lddp % 4 == 0) && (reinterpret_cast<uintptr_t>(pred) & 15) == 0 &&
+               (reinterpret_cast<uintptr_t>(dpred) & 7) == 0,
+           "jm_patch_loss: P, ldp, lddp must be multiples of 4 and the buffers 16/8-byte aligned");
   JM_CHECK(batch > 0, "jm_patch_loss: empty batch");
   JM_CHECK(workspace && workspace_bytes >= jm_patch_loss_workspace(batch, N), "jm_patch_loss: workspace too small");
   float* partial = static_cast<float*>(workspace);
-  patch_loss_kernel<<<dim3(num_cls + N, batch), kLossThreads, 0, STREAM>>>(
-      pred, ldp, images, mask_row, image_size, patch_size, num_cls, norm_pix, grad_scale, partial,
-      reinterpret_cast<__nv_bfloat16*>(dpred), lddp, batch);
+  launch_patch_loss(pred, ldp, images, mask_row, image_size, patch_size, num_cls, norm_pix, grad_scale, partial,
+                    reinterpret_cast<__nv_bfloat16*>(dpred), lddp, batch, N, P, STREAM);
   JM_AFTER_LAUNCH();
   patch_loss_finalize_kernel<<<1, 1024, 0, STREAM>>>(partial, mask_row, N, batch, loss);
   JM_AFTER_LAUNCH();
@@ -659,6 +755,9 @@ extern "C" int jm_patch_loss_static(const float* pred, long ldp, const uint8_t* 
            "jm_patch_loss_static: image size must be a positive multiple of the patch size");
   const int g = image_size / patch_size, N = g * g, P = patch_size * patch_size * 3;
   JM_CHECK(P <= kLossThreads * kLossMaxPer, "jm_patch_loss_static: patch dimension %d too large", P);
+  JM_CHECK(P % 4 == 0 && ldp % 4 == 0 && (!dpred || lddp % 4 == 0) && (reinterpret_cast<uintptr_t>(pred) & 15) == 0 &&
+               (reinterpret_cast<uintptr_t>(dpred) & 7) == 0,
+           "jm_patch_loss_static: P, ldp, lddp must be multiples of 4 and the buffers 16/8-byte aligned");
   JM_CHECK(batch > 0, "jm_patch_loss_static: empty batch");
   const long need = static_cast<long>(batch) * N;
   JM_CHECK(need <= JM_PATCH_LOSS_STATIC_MAX,
@@ -669,9 +768,8 @@ extern "C" int jm_patch_loss_static(const float* pred, long ldp, const uint8_t* 
   if (patch_loss_static_scratch(&partial)) return 1;
   // Every entry [0, batch * N) is overwritten by the first kernel (zero for visible patches), so the
   // previous call's contents never leak into this one and nothing has to be cleared first.
-  patch_loss_kernel<<<dim3(num_cls + N, batch), kLossThreads, 0, STREAM>>>(
-      pred, ldp, images, mask_row, image_size, patch_size, num_cls, norm_pix, grad_scale, partial,
-      reinterpret_cast<__nv_bfloat16*>(dpred), lddp, batch);
+  launch_patch_loss(pred, ldp, images, mask_row, image_size, patch_size, num_cls, norm_pix, grad_scale, partial,
+                    reinterpret_cast<__nv_bfloat16*>(dpred), lddp, batch, N, P, STREAM);
   JM_AFTER_LAUNCH();
   patch_loss_finalize_kernel<<<1, 1024, 0, STREAM>>>(partial, mask_row, N, batch, loss);
   JM_AFTER_LAUNCH();
@@ -767,6 +865,7 @@ extern "C" int jm_unshuffle_fwd(const float* y, const int32_t* ids_restore, cons
 extern "C" int jm_unshuffle_bwd(const float* dout, const int32_t* ids_restore, int batch, int N, int n, int J,
                                 int dim, jm_bf16* dy, float* dmask_emb, void* stream) {
   JM_CHECK(dim % 4 == 0, "jm_unshuffle_bwd: dim must be a multiple of 4");
+  JM_CHECK((reinterpret_cast<uintptr_t>(dmask_emb) & 15) == 0, "jm_unshuffle_bwd: dmask_emb must be 16-byte aligned");
   if (batch == 0) return 0;
   unshuffle_bwd_kernel<<<dim3(J + N, (batch + kUnshufBwdImgs - 1) / kUnshufBwdImgs), 128, 0, STREAM>>>(
       dout, ids_restore, batch, N, n, J, dim, reinterpret_cast<__nv_bfloat16*>(dy), dmask_emb);

@@ -136,6 +136,29 @@ def main():
             print(f"colsum [{M}x{D}] {cs * 1e3:.0f} us ({M * D * 2 / cs / 1e6:.0f} GB/s)")
         print(f"layernorm total per micro-step: {ln_ms:.2f} ms")
         total_ms += ln_ms
+    if ONLY in ("", "misc"):
+        N, n, J, P, dd = 196, 49, 3, 768, 512
+        images = torch.randint(0, 256, (B, 3, 224, 224), dtype=torch.uint8, device="cuda")
+        noise = torch.rand(N, device="cuda")
+        ids_shuffle = torch.argsort(noise).to(torch.int32)
+        ids_restore = torch.argsort(ids_shuffle.long()).to(torch.int32)
+        mask_row = (ids_restore >= n).float()
+        pred = torch.randn(B * (J + N), P, device="cuda")
+        dpred = torch.empty(B * (J + N), P, dtype=BF16, device="cuda")
+        loss = torch.zeros(1, device="cuda")
+        ws = torch.empty(ops.patch_loss_workspace(B, N), dtype=torch.uint8, device="cuda")
+        t = timeit(lambda: ops.patch_loss(pred, images, mask_row, 16, J, False, 1.0, loss, dpred, ws))
+        by = pred.numel() * 4 * 0.75 + dpred.numel() * 2 + images.numel() * 0.75
+        print(f"patch_loss: {t * 1e3:.0f} us ({by / t / 1e6:.0f} GB/s)")
+        patches = torch.empty(B * (J + n), P, dtype=BF16, device="cuda")
+        t2 = timeit(lambda: ops.patchify(images, 16, ids_shuffle, n, J + n, J, patches))
+        print(f"patchify: {t2 * 1e3:.0f} us ({(patches.numel() * 2 + images.numel() * 0.25) / t2 / 1e6:.0f} GB/s)")
+        dout = torch.randn(B * (J + N), dd, device="cuda")
+        dy = torch.empty(B * (J + n), dd, dtype=BF16, device="cuda")
+        dm = torch.zeros(dd, device="cuda")
+        t3 = timeit(lambda: ops.unshuffle_bwd(dout, ids_restore, B, N, n, J, dd, dy, dm))
+        print(f"unshuffle_bwd: {t3 * 1e3:.0f} us ({(dout.numel() * 4 + dy.numel() * 2) / t3 / 1e6:.0f} GB/s)")
+        total_ms += t + t2 + t3
     print(f"sum of timed kernels per micro-step: {total_ms:.2f} ms -> {B / total_ms * 1e3:.0f} images/s upper bound")
 
 
