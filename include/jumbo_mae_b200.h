@@ -161,8 +161,9 @@ int jm_gemm(const jm_gemm_args* args, void* stream);
 int jm_attention_fwd(const jm_bf16* qkv, long ldqkv, int batch, int T, int heads, int head_dim, jm_bf16* out,
                      long ldo, float* lse, void* stream);
 /* dqkv (same layout as qkv) from dout; the q part is multiplied by q_scale so that it
- * is the gradient w.r.t. the un-scaled projection.  delta_ws: caller-owned scratch of
- * batch*heads*T floats (receives rowsum(dout * out)).  dbias (optional, [3*heads*hd], +=)
+ * is the gradient w.r.t. the un-scaled projection.  delta_ws: unused (rowsum(dout * out)
+ * is computed inside the kernel since round 1; kept in the signature, may be NULL).
+ * dbias (optional, [3*heads*hd], +=)
  * receives the column sums of dqkv, i.e. the gradient of the fused q/k/v bias. */
 int jm_attention_bwd(const jm_bf16* qkv, long ldqkv, const jm_bf16* out, long ldo, const jm_bf16* dout, long lddo,
                      const float* lse, float* delta_ws, int batch, int T, int heads, int head_dim, float q_scale,

@@ -151,8 +151,14 @@ __device__ __forceinline__ void fwd_chunk(const uint32_t (&qf)[HD / 16][4], uint
   }
 }
 
+#ifndef JM_ATTN_FWD64_CTAS
+#define JM_ATTN_FWD64_CTAS 2  // measured: 79 -> 61 us at T=52 (128 registers, twice the resident CTAs)
+#endif
+#ifndef JM_ATTN_BWD64_CTAS
+#define JM_ATTN_BWD64_CTAS 2  // 180 -> 170 us
+#endif
 template <int HD>
-__global__ void __launch_bounds__(256, HD == 32 ? 3 : 1)
+__global__ void __launch_bounds__(256, HD == 32 ? 3 : (HD == 64 ? JM_ATTN_FWD64_CTAS : 1))
 attn_fwd_kernel(const __nv_bfloat16* __restrict__ qkv, long ldqkv, int T, int heads,
                                 __nv_bfloat16* __restrict__ out, long ldo, float* __restrict__ lse) {
   constexpr int LDS = HD + 8;
@@ -356,10 +362,10 @@ __device__ __forceinline__ void bwd_kv_chunk(const uint32_t (&kf)[HD / 16][4], c
 #define JM_ATTN_BWD_CTAS 2
 #endif
 template <int HD>
-__global__ void __launch_bounds__(256, HD == 32 ? JM_ATTN_BWD_CTAS : 1)
+__global__ void __launch_bounds__(256, HD == 32 ? JM_ATTN_BWD_CTAS : (HD == 64 ? JM_ATTN_BWD64_CTAS : 1))
 attn_bwd_kernel(const __nv_bfloat16* __restrict__ qkv, long ldqkv,
                                 const __nv_bfloat16* __restrict__ dout, long lddo, const float* __restrict__ lse,
-                                const float* __restrict__ delta, int T, int heads, float q_scale,
+                                const __nv_bfloat16* __restrict__ out, long ldo, int T, int heads, float q_scale,
                                 __nv_bfloat16* __restrict__ dqkv, long lddqkv, float* __restrict__ dbias) {
   constexpr int LDS = HD + 8;
   extern __shared__ __align__(16) uint8_t smem_raw[];
@@ -379,13 +385,44 @@ attn_bwd_kernel(const __nv_bfloat16* __restrict__ qkv, long ldqkv,
   load_head<HD, LDS>(base + d, ldqkv, T, Tk, sK);
   load_head<HD, LDS>(base + 2 * d, ldqkv, T, Tk, sV);
   load_head<HD, LDS>(dout + static_cast<long>(b) * T * lddo + h * HD, lddo, T, Tk, sdO);
-  // saved log-sum-exp and D = rowsum(dO * O); padded rows get lse = +big so that their P is exactly 0
+  // saved log-sum-exp; padded rows get lse = +big so that their P is exactly 0
   for (int row = threadIdx.x; row < Tk; row += blockDim.x) {
     const long i = (static_cast<long>(b) * heads + h) * T + row;
     sL2[row] = row < T ? lse[i] * kLog2e : 1e30f;
-    sD[row] = row < T ? delta[i] : 0.f;
   }
-  cp_async_wait_all();
+  // D = rowsum(dO * O), one thread per row: the O row is requested from global memory now (its latency
+  // overlaps the cp.async fills above), the dO row is read from shared memory once it has landed
+  for (int row0 = 0; row0 < Tk; row0 += blockDim.x) {
+    const int row = row0 + threadIdx.x;
+    uint4 ov[HD / 8];
+#pragma unroll
+    for (int c = 0; c < HD / 8; ++c) ov[c] = make_uint4(0u, 0u, 0u, 0u);
+    if (row < T) {
+      const __nv_bfloat16* orow = out + (static_cast<long>(b) * T + row) * ldo + h * HD;
+#pragma unroll
+      for (int c = 0; c < HD / 8; ++c) ov[c] = *reinterpret_cast<const uint4*>(orow + c * 8);
+    }
+    if (row0 == 0) {  // first pass: this is where everybody waits for the tiles
+      cp_async_wait_all();
+      __syncthreads();
+    }
+    if (row < Tk) {
+      float acc = 0.f;
+      const __nv_bfloat16* drow = sdO + row * LDS;
+#pragma unroll
+      for (int c = 0; c < HD / 8; ++c) {
+        const uint4 dv = *reinterpret_cast<const uint4*>(drow + c * 8);
+        const uint32_t ow[4] = {ov[c].x, ov[c].y, ov[c].z, ov[c].w}, dw[4] = {dv.x, dv.y, dv.z, dv.w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const float2 a = unpack_bf16(ow[j]), bb = unpack_bf16(dw[j]);
+          acc = fmaf(a.x, bb.x, acc);
+          acc = fmaf(a.y, bb.y, acc);
+        }
+      }
+      sD[row] = acc;  // padded rows: O was not read, 0
+    }
+  }
   __syncthreads();
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -554,14 +591,10 @@ static int launch_bwd(const jm_bf16* qkv, long ldqkv, const jm_bf16* out, long l
   int warps = 0;
   if (pick_warps(reinterpret_cast<const void*>(kern), T, &warps)) return 1;
   const int threads = warps * 32;
-  const long total = static_cast<long>(batch) * T * heads;
-  attn_delta_kernel<<<static_cast<int>((total + 255) / 256), 256, 0, stream>>>(
-      reinterpret_cast<const __nv_bfloat16*>(out), ldo, reinterpret_cast<const __nv_bfloat16*>(dout), lddo, batch, T,
-      heads, HD, delta);
-  JM_AFTER_LAUNCH();
+  (void)delta;  // D = rowsum(dO * O) is computed inside the backward kernel
   kern<<<batch * heads, threads, smem, stream>>>(
       reinterpret_cast<const __nv_bfloat16*>(qkv), ldqkv, reinterpret_cast<const __nv_bfloat16*>(dout), lddo, lse,
-      delta, T, heads, q_scale, reinterpret_cast<__nv_bfloat16*>(dqkv), lddqkv, dbias);
+      reinterpret_cast<const __nv_bfloat16*>(out), ldo, T, heads, q_scale, reinterpret_cast<__nv_bfloat16*>(dqkv), lddqkv, dbias);
   JM_AFTER_LAUNCH();
   return 0;
 }
@@ -596,7 +629,6 @@ extern "C" int jm_attention_bwd(const jm_bf16* qkv, long ldqkv, const jm_bf16* o
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   if (check_attn("jm_attention_bwd", batch, T, heads, head_dim, ldqkv, lddqkv)) return 1;
   JM_CHECK(ldo % 8 == 0 && lddo % 8 == 0, "jm_attention_bwd: row strides must be multiples of 8 elements");
-  JM_CHECK(delta_ws != nullptr, "jm_attention_bwd: delta workspace (batch*heads*T floats) is required");
   JM_CHECK(bwd_smem(T, head_dim) <= 227 * 1024, "jm_attention_bwd: T=%d hd=%d does not fit shared memory", T,
            head_dim);
   if (head_dim == 32)
