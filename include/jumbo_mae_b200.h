@@ -126,6 +126,8 @@ int jm_layernorm_bwd(const jm_bf16* dy, long lddy, const float* x, long ldx, con
  *   v += bias[col]; if (col < col_scale_n) v *= col_scale;
  *   act == 1 (GELU-tanh, src/modeling.py:148): out_bf16 <- v (pre-activation), out2_bf16 <- gelu(v)
  *   act == 2 (GELU backward): v *= gelu'(aux[row, col])
+ *   act == 3: as 1, but out_bf16 <- gelu'(v): the derivative is saved instead of the pre-activation ...
+ *   act == 4: ... and the backward epilogue is v *= aux[row, col] (no tanh in the backward pass)
  *   v += pe[pe_idx[(row % row_period) - row_skip], col]   (positional embedding, modeling.py:123)
  *   v += residual[row, col]
  *   rows with (row % row_period) < row_skip: row_mask_mode 1 -> zeros are stored,

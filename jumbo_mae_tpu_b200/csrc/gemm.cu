@@ -162,6 +162,22 @@ __device__ __forceinline__ f32x2 gelu_grad_fast2(f32x2 x) {
   return fma2(a, du, fma2(half, t, half));
 }
 
+// gelu(x) and gelu'(x) of a pair from one tanh: with s = (1 + t) / 2, gelu = x s and gelu' = s + x s (1 - t) du.
+__device__ __forceinline__ void gelu_both2(f32x2 x, f32x2& g, f32x2& d) {
+  const f32x2 c1 = pack2(0.0356774081f, 0.0356774081f), c0 = pack2(0.7978845608f, 0.7978845608f);
+  const f32x2 c3 = pack2(0.1070322243f, 0.1070322243f), half = pack2(0.5f, 0.5f), one = pack2(1.0f, 1.0f);
+  const f32x2 x2 = mul2(x, x);
+  const f32x2 u = mul2(x, fma2(x2, c1, c0));
+  float u0, u1;
+  unpack2(u, u0, u1);
+  const float t0 = tanh_fast(u0), t1 = tanh_fast(u1);
+  const f32x2 t = pack2(t0, t1), nt = pack2(-t0, -t1);
+  const f32x2 s = fma2(half, t, half);
+  g = mul2(x, s);
+  d = fma2(mul2(g, fma2(nt, one, one)), fma2(x2, c3, c0), s);
+}
+__device__ __forceinline__ float gelu_grad_of(float x) { return gelu_grad_fast(x); }
+
 // Epilogue specialisations: straight-line code per kind (the generic one keeps every runtime switch).
 enum : int {
   EPI_BF16 = 0,      // out_bf16 = (acc + bias) * scale
@@ -258,15 +274,19 @@ __device__ __forceinline__ void epilogue8(const EpiParams& ep, float (&v)[8], co
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
       const float2 a = unpack_bf16(w[j]);
-      v[2 * j] *= gelu_grad_fast(a.x);
-      v[2 * j + 1] *= gelu_grad_fast(a.y);
+      v[2 * j] *= ep.act == 4 ? a.x : gelu_grad_fast(a.x);
+      v[2 * j + 1] *= ep.act == 4 ? a.y : gelu_grad_fast(a.y);
     }
     store_bf16x8<FULL>(ep.out_bf16 + off_row * ep.ldo_bf16 + col, v, ncols);
   } else {
-    if (ep.act == 1) {
+    if (ep.act == 1 || ep.act == 3) {
       float g[8];
 #pragma unroll
       for (int j = 0; j < 8; ++j) g[j] = gelu_fast(v[j]);
+      if (ep.act == 3) {  // the derivative is saved instead of the pre-activation
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v[j] = gelu_grad_fast(v[j]);
+      }
       if (ep.out_bf16) store_bf16x8<FULL>(ep.out_bf16 + off_row * ep.ldo_bf16 + col, v, ncols);
       if (ep.out2_bf16) store_bf16x8<FULL>(ep.out2_bf16 + off_row * ep.ldo2_bf16 + col, g, ncols);
       return;
@@ -276,11 +296,15 @@ __device__ __forceinline__ void epilogue8(const EpiParams& ep, float (&v)[8], co
       if (hh * 4 >= ncols) break;
       const int c4 = col + hh * 4;
       float* x = v + hh * 4;
-      if (ep.act == 2) {
+      if (ep.act == 2 || ep.act == 4) {
         const uint2 u = *reinterpret_cast<const uint2*>(ep.aux + off_row * ep.ldaux + c4);
         const float2 a = unpack_bf16(u.x), b = unpack_bf16(u.y);
-        x[0] *= gelu_grad_fast(a.x), x[1] *= gelu_grad_fast(a.y);
-        x[2] *= gelu_grad_fast(b.x), x[3] *= gelu_grad_fast(b.y);
+        if (ep.act == 2) {
+          x[0] *= gelu_grad_fast(a.x), x[1] *= gelu_grad_fast(a.y);
+          x[2] *= gelu_grad_fast(b.x), x[3] *= gelu_grad_fast(b.y);
+        } else {
+          x[0] *= a.x, x[1] *= a.y, x[2] *= b.x, x[3] *= b.y;
+        }
       }
       if (ep.pe) {
         const float4 b = *reinterpret_cast<const float4*>(
@@ -547,6 +571,7 @@ __device__ __forceinline__ void epilogue_rows(const EpiParams& ep, const GemmSha
   const int tiles_mn = sh.num_m * sh.num_n;
   const bool has_bias = ep.bias != nullptr;
   const bool tma = ep.tma_store != 0;  // kernel-uniform
+  const bool saved_grad = ep.act >= 3;  // acts 3 / 4: the GELU derivative is stored / consumed directly
   uint32_t buf = 0;                     // byte offset of the staging tile in use (NBUF tiles, used in turn)
   int iter = 0;
   for (int t = tile0; t < total_tiles; t += tile_step, ++iter) {
@@ -684,7 +709,8 @@ __device__ __forceinline__ void epilogue_rows(const EpiParams& ep, const GemmSha
               const float2 x = unpack_bf16(w[k]);
               const f32x2 a = pack2(__uint_as_float(r[h][8 * j + 2 * k]), __uint_as_float(r[h][8 * j + 2 * k + 1]));
               float v0, v1;
-              unpack2(mul2(a, gelu_grad_fast2(pack2(x.x, x.y))), v0, v1);
+              // aux holds the pre-activation (act 2) or the saved derivative itself (act 4, kernel-uniform)
+              unpack2(mul2(a, saved_grad ? pack2(x.x, x.y) : gelu_grad_fast2(pack2(x.x, x.y))), v0, v1);
               o[k] = pack_bf16(v0, v1);
             }
             sts128_or_zero(a, o[0], o[1], o[2], o[3], zflag);
@@ -710,8 +736,17 @@ __device__ __forceinline__ void epilogue_rows(const EpiParams& ep, const GemmSha
             unpack2(v[j], a, b);
             P[j] = pack_bf16(a, b);
             if constexpr (EPI == EPI_GELU_FWD) {
-              unpack2(gelu_fast2(v[j]), a, b);
-              G[j] = pack_bf16(a, b);
+              if (saved_grad) {  // act 3 (kernel-uniform): out <- gelu'(v) instead of v
+                f32x2 gg, dd;
+                gelu_both2(v[j], gg, dd);
+                unpack2(dd, a, b);
+                P[j] = pack_bf16(a, b);
+                unpack2(gg, a, b);
+                G[j] = pack_bf16(a, b);
+              } else {
+                unpack2(gelu_fast2(v[j]), a, b);
+                G[j] = pack_bf16(a, b);
+              }
             }
           }
           staging_free();
@@ -1400,7 +1435,8 @@ extern "C" int jm_gemm(const jm_gemm_args* a, void* stream_) {
   JM_CHECK(a->N % 4 == 0, "jm_gemm: N must be a multiple of 4 (got %d)", a->N);
   JM_CHECK(a->A && a->B, "jm_gemm: null operand");
   JM_CHECK(a->out_f32 || a->out_bf16 || a->out2_bf16, "jm_gemm: no output");
-  JM_CHECK(a->act != 2 || a->aux, "jm_gemm: act=2 needs aux");
+  JM_CHECK(a->act >= 0 && a->act <= 4, "jm_gemm: act must be 0..4");
+  JM_CHECK((a->act != 2 && a->act != 4) || a->aux, "jm_gemm: act=2/4 needs aux");
   JM_CHECK(!a->pe || (a->pe_idx && a->row_period > 0), "jm_gemm: pe needs pe_idx and row_period");
   JM_CHECK(!a->out_f32 || a->ldo_f32 % 4 == 0, "jm_gemm: ldo_f32 must be a multiple of 4");
   JM_CHECK(!a->out_bf16 || a->ldo_bf16 % 8 == 0, "jm_gemm: ldo_bf16 must be a multiple of 8");
@@ -1516,7 +1552,7 @@ extern "C" int jm_gemm(const jm_gemm_args* a, void* stream_) {
   ep.row_period = a->row_period, ep.row_skip = a->row_skip, ep.row_mask_mode = a->row_mask_mode;
   ep.accumulate = (a->accumulate || splits > 1) ? 1 : 0;
   ep.colsum = a->colsum;
-  JM_CHECK(!a->colsum || a->act != 1, "jm_gemm: colsum is not defined for the GELU-forward epilogue");
+  JM_CHECK(!a->colsum || (a->act != 1 && a->act != 3), "jm_gemm: colsum is not defined for the GELU-forward epilogue");
 
   const long total = static_cast<long>(num_m_eff) * num_n * splits;
   const int grid = pair ? 2 * static_cast<int>(total < sms / 2 ? total : sms / 2)
@@ -1526,9 +1562,10 @@ extern "C" int jm_gemm(const jm_gemm_args* a, void* stream_) {
   const bool only_f32 = ep.out_f32 && !ep.out_bf16 && !ep.out2_bf16;
   // the row-register epilogues work on whole 16-byte column chunks and a per-32-column scale
   const bool rows_ok = a->N % 8 == 0 && ep.col_scale_n % 32 == 0;
-  if (ep.act == 1 && ep.out_bf16 && ep.out2_bf16 && !ep.out_f32 && !ep.residual && !ep.pe && rows_ok)
+  if ((ep.act == 1 || ep.act == 3) && ep.out_bf16 && ep.out2_bf16 && !ep.out_f32 && !ep.residual && !ep.pe && rows_ok)
     epi = EPI_GELU_FWD;
-  else if (ep.act == 2 && only_bf16 && !ep.residual && !ep.pe && rows_ok && !ep.bias && ep.col_scale_n == 0 &&
+  else if ((ep.act == 2 || ep.act == 4) && only_bf16 && !ep.residual && !ep.pe && rows_ok && !ep.bias &&
+           ep.col_scale_n == 0 &&
            (reinterpret_cast<uintptr_t>(ep.colsum) & 15) == 0)
     epi = EPI_GELU_BWD;
   else if (ep.act == 0 && only_f32 && !ep.colsum) epi = EPI_F32;

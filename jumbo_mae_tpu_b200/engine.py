@@ -17,6 +17,8 @@ throughout; BASELINE.json's "bf16" is this compute dtype).
 """
 from __future__ import annotations
 
+import os
+
 import math
 from typing import Dict, List, Optional
 
@@ -28,6 +30,9 @@ from .params import ParamStore
 
 F32, BF16 = torch.float32, torch.bfloat16
 LN_EPS = 1e-6   # flax.linen.LayerNorm default
+# jm_gemm activation codes used by the step: the forward FFN GEMM saves gelu'(h) (not h) next to gelu(h), so that
+# the backward epilogue is a single multiply
+GELU_FWD, GELU_BWD = (3, 4) if os.environ.get("JM_GELU_SAVED", "1") != "0" else (1, 2)
 
 
 def fixed_sincos2d_embeddings(ncols: int, nrows: int, dim: int) -> torch.Tensor:
@@ -52,7 +57,7 @@ class _Block:
         self.lse = e(B, heads, T, dt=F32)
         self.att = e(M, dim)
         self.xb = e(M, dim, dt=F32)            # residual stream after the attention branch
-        self.h, self.g = e(M, 4 * dim), e(M, 4 * dim)
+        self.h, self.g = e(M, 4 * dim), e(M, 4 * dim)   # h: gelu'(pre-activation), g: gelu(pre-activation)
         if jumbo:
             Jd = J * dim
             self.mean3, self.rstd3 = e(B, dt=F32), e(B, dt=F32)
@@ -204,7 +209,7 @@ class MAEEngine:
         # patch tokens: x = x_b + ff(LN2(x_b))       (src/modeling.py:166 / :201)
         ops.layernorm_fwd(s.xb, ps.f(f"{name}/norm2/scale"), ps.f(f"{name}/norm2/bias"), LN_EPS, s.xn2, None,
                           s.mean2, s.rstd2)
-        self._fwd_linear(s.xn2, M, f"{name}/ff/w1", 4 * dim, dim, out_bf16=s.h, out2_bf16=s.g, act=1,
+        self._fwd_linear(s.xn2, M, f"{name}/ff/w1", 4 * dim, dim, out_bf16=s.h, out2_bf16=s.g, act=GELU_FWD,
                          row_period=period, row_skip=skip, row_mask_mode=1 if jumbo else 0)
         # (every row is written, so that the output tiles can leave by TMA; the CLS rows of a Jumbo block get
         #  x_b + bias here -- their h/g rows are zero -- and are overwritten by the Jumbo MLP just below)
@@ -214,7 +219,7 @@ class MAEEngine:
             # c = LN3(cls concat); c = c + jumbo_mlp(c)      (src/modeling.py:194-199)
             ops.layernorm_fwd(s.xb, ps.f(f"{name}/norm3/scale"), ps.f(f"{name}/norm3/bias"), LN_EPS, s.cn16, s.cn,
                               s.mean3, s.rstd3, rows=B, dim=Jd, ldx=T * dim, ldy=Jd, ldyf=Jd)
-            self._fwd_linear(s.cn16, B, "model/jumbo_mlp/w1", 4 * Jd, Jd, out_bf16=s.hj, out2_bf16=s.gj, act=1)
+            self._fwd_linear(s.cn16, B, "model/jumbo_mlp/w1", 4 * Jd, Jd, out_bf16=s.hj, out2_bf16=s.gj, act=GELU_FWD)
             # w2 has few output tiles and a long K: seed the CLS rows with c + bias, then split-K accumulate
             ops.add_bias_cast(s.cn, B, Jd, bias=ps.f("model/jumbo_mlp/w2/bias"), dst_f32=x_out, ldd=T * dim)
             ops.gemm(s.gj, self._W("model/jumbo_mlp/w2/kernel"), B, Jd, 4 * Jd, b_mn=True,
@@ -322,7 +327,7 @@ class MAEEngine:
         period, skip = (T, J) if jumbo else (0, 0)
         mode = 1 if jumbo else 0
         # ---- patch FFN: y = x_b + w2(gelu(w1 LN2(x_b)))
-        self._bwd_linear(s.g, dx16, M, f"{name}/ff/w2", dim, 4 * dim, dX16=dh, bias=False, act=2, aux=s.h,
+        self._bwd_linear(s.g, dx16, M, f"{name}/ff/w2", dim, 4 * dim, dX16=dh, bias=False, act=GELU_BWD, aux=s.h,
                          row_period=period, row_skip=skip, row_mask_mode=mode,
                          colsum=ps.grad(f"{name}/ff/w1/bias"))
         self._bwd_linear(s.xn2, dh, M, f"{name}/ff/w1", 4 * dim, dim, dX16=dn, bias=False)
@@ -336,7 +341,7 @@ class MAEEngine:
             ops.colsum(dx16, B, Jd, ps.grad("model/jumbo_mlp/w2/bias"), ldx=ldc)
             ops.add_bias_cast(dx, B, Jd, dst_bf16=s.dc16, lds=ldc)
             ops.gemm(dx16, self._W("model/jumbo_mlp/w2/kernel"), B, 4 * Jd, Jd, b_mn=False, lda=ldc,
-                     ldb=ps.ld("model/jumbo_mlp/w2/kernel"), out_bf16=s.dhj16, act=2, aux=s.hj,
+                     ldb=ps.ld("model/jumbo_mlp/w2/kernel"), out_bf16=s.dhj16, act=GELU_BWD, aux=s.hj,
                      colsum=ps.grad("model/jumbo_mlp/w1/bias"))
             # d c = d c_out + dh W1^T: split-K accumulate into the CLS rows of dx (f32), bf16 copy for LN3 backward
             ops.gemm(s.dhj16, self._W("model/jumbo_mlp/w1/kernel"), B, Jd, 4 * Jd, b_mn=False,

@@ -519,6 +519,22 @@ def test_gemm_bf16_epilogues_every_tile_shape(ops, M, N, K, bn, pair):
     ref = (dY.float() @ W2.float().t()) * hh.grad.cuda() * keep
     assert torch.allclose(dH.float(), ref, rtol=2 ** -6, atol=2e-3)
     assert torch.allclose(cs - 1, ref.sum(0), rtol=1e-2, atol=0.3)   # sums of bf16-rounded values over M rows
+    # acts 3 / 4: the forward saves gelu'(pre) instead of pre, the backward multiplies by it
+    dsave = torch.empty(M, N, dtype=BF16, device="cuda")
+    gl2 = torch.empty(M, N, dtype=BF16, device="cuda")
+    ops.gemm(A, W, M, N, K, b_mn=True, out_bf16=dsave, out2_bf16=gl2, bias=bias, act=3, row_period=T, row_skip=J,
+             row_mask_mode=1, **kw)
+    pp = (pre * keep).cpu().requires_grad_(True)
+    O.gelu_tanh(pp).sum().backward()
+    assert torch.allclose(dsave.float(), pp.grad.cuda() * keep, rtol=2 ** -7, atol=3e-3)
+    assert torch.allclose(gl2.float(), gl.float(), rtol=2 ** -7, atol=2e-3)
+    dH2 = torch.empty(M, N, dtype=BF16, device="cuda")
+    cs2 = torch.zeros(N, device="cuda")
+    ops.gemm(dY, W2, M, N, K, b_mn=False, out_bf16=dH2, aux=dsave, act=4, row_period=T, row_skip=J, row_mask_mode=1,
+             colsum=cs2, **kw)
+    ref2 = (dY.float() @ W2.float().t()) * dsave.float() * keep
+    assert torch.allclose(dH2.float(), ref2, rtol=2 ** -6, atol=2e-3)
+    assert torch.allclose(cs2, ref2.sum(0), rtol=1e-2, atol=0.3)
 
 
 def test_add_bias_cast_strided(ops):

@@ -12,6 +12,7 @@ BF16 = torch.bfloat16
 B = int(os.environ.get("B", "512"))
 ONLY = os.environ.get("ONLY", "")
 BN = int(os.environ.get("BN", "0"))
+SAVED = os.environ.get("SAVED_GRAD", "1") != "0"   # acts 3/4 (what the engine uses) instead of 1/2
 
 
 def timeit(fn, reps=20, warm=3):
@@ -76,7 +77,7 @@ def run_gemm(name, M, N, K, kind):
             return lambda: ops.gemm(A, W, M, N, K, b_mn=True, out_bf16=o, bias=bias, col_scale=0.125, col_scale_n=N // 3, block_n=BN)
         if kind == "fwd_gelu":
             h, g = torch.empty(M, N, dtype=BF16, device="cuda"), torch.empty(M, N, dtype=BF16, device="cuda")
-            return lambda: ops.gemm(A, W, M, N, K, b_mn=True, out_bf16=h, out2_bf16=g, bias=bias, act=1, block_n=BN)
+            return lambda: ops.gemm(A, W, M, N, K, b_mn=True, out_bf16=h, out2_bf16=g, bias=bias, act=3 if SAVED else 1, block_n=BN)
         if kind == "fwd_res":
             res, o = torch.zeros(M, N, device="cuda"), torch.empty(M, N, device="cuda")
             return lambda: ops.gemm(A, W, M, N, K, b_mn=True, out_f32=o, bias=bias, residual=res, block_n=BN)
@@ -87,7 +88,7 @@ def run_gemm(name, M, N, K, kind):
     if kind == "dx_gelu":
         aux = r(M, N)
         cs = torch.zeros(N, device="cuda") if os.environ.get("NO_CS") is None else None
-        return lambda: ops.gemm(A, W, M, N, K, b_mn=False, out_bf16=o, aux=aux, act=2, colsum=cs)
+        return lambda: ops.gemm(A, W, M, N, K, b_mn=False, out_bf16=o, aux=aux, act=4 if SAVED else 2, colsum=cs)
     return lambda: ops.gemm(A, W, M, N, K, b_mn=False, out_bf16=o, block_n=BN)
 
 
