@@ -161,6 +161,8 @@ template <int HD>
 __global__ void __launch_bounds__(256, HD == 32 ? 3 : (HD == 64 ? JM_ATTN_FWD64_CTAS : 1))
 attn_fwd_kernel(const __nv_bfloat16* __restrict__ qkv, long ldqkv, int T, int heads,
                                 __nv_bfloat16* __restrict__ out, long ldo, float* __restrict__ lse) {
+  pdl_wait();  // programmatic dependent launch: nothing above touches global memory
+  pdl_launch_dependents();
   constexpr int LDS = HD + 8;
   extern __shared__ __align__(16) uint8_t smem_raw[];
   __nv_bfloat16* sK = reinterpret_cast<__nv_bfloat16*>(smem_raw);
@@ -367,6 +369,8 @@ attn_bwd_kernel(const __nv_bfloat16* __restrict__ qkv, long ldqkv,
                                 const __nv_bfloat16* __restrict__ dout, long lddo, const float* __restrict__ lse,
                                 const __nv_bfloat16* __restrict__ out, long ldo, int T, int heads, float q_scale,
                                 __nv_bfloat16* __restrict__ dqkv, long lddqkv, float* __restrict__ dbias) {
+  pdl_wait();  // programmatic dependent launch: nothing above touches global memory
+  pdl_launch_dependents();
   constexpr int LDS = HD + 8;
   extern __shared__ __align__(16) uint8_t smem_raw[];
   const int Tk = (T + 15) / 16 * 16;
@@ -574,7 +578,7 @@ static int launch_fwd(const jm_bf16* qkv, long ldqkv, int batch, int T, int head
   int warps = 0;
   if (pick_warps(reinterpret_cast<const void*>(kern), T, &warps)) return 1;
   const int threads = warps * 32;
-  kern<<<batch * heads, threads, smem, stream>>>(reinterpret_cast<const __nv_bfloat16*>(qkv), ldqkv, T, heads,
+  JM_LAUNCH_PDL(kern, batch * heads, threads, smem, stream, reinterpret_cast<const __nv_bfloat16*>(qkv), ldqkv, T, heads,
                                                  reinterpret_cast<__nv_bfloat16*>(out), ldo, lse);
   JM_AFTER_LAUNCH();
   return 0;
@@ -592,7 +596,7 @@ static int launch_bwd(const jm_bf16* qkv, long ldqkv, const jm_bf16* out, long l
   if (pick_warps(reinterpret_cast<const void*>(kern), T, &warps)) return 1;
   const int threads = warps * 32;
   (void)delta;  // D = rowsum(dO * O) is computed inside the backward kernel
-  kern<<<batch * heads, threads, smem, stream>>>(
+  JM_LAUNCH_PDL(kern, batch * heads, threads, smem, stream,
       reinterpret_cast<const __nv_bfloat16*>(qkv), ldqkv, reinterpret_cast<const __nv_bfloat16*>(dout), lddo, lse,
       reinterpret_cast<const __nv_bfloat16*>(out), ldo, T, heads, q_scale, reinterpret_cast<__nv_bfloat16*>(dqkv), lddqkv, dbias);
   JM_AFTER_LAUNCH();

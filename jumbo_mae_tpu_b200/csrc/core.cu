@@ -1,5 +1,6 @@
 // Error reporting and device queries shared by every entry point.
 #include <stdarg.h>
+#include <stdlib.h>
 
 #include <atomic>
 
@@ -27,6 +28,15 @@ int fail(const char* fmt, ...) {
 static std::atomic<long long> g_launches{0};
 void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
 long long launches() { return g_launches.load(std::memory_order_relaxed); }
+
+bool pdl_enabled() {
+  static int on = -1;
+  if (on < 0) {
+    const char* e = getenv("JM_PDL");
+    on = e ? (atoi(e) != 0) : 0;  // measured on B200: no gain without the early trigger, -2 % with it
+  }
+  return on != 0;
+}
 
 int sm_count() {
   static int cached[64];

@@ -273,6 +273,8 @@ __global__ void __launch_bounds__(kLnWarps * 32)
 layernorm_fwd_kernel(const float* __restrict__ x, long ldx, int rows, int D, const float* __restrict__ gamma,
                      const float* __restrict__ beta, float eps, __nv_bfloat16* __restrict__ yb, long ldy,
                      float* __restrict__ yf, long ldyf, float* __restrict__ mean_out, float* __restrict__ rstd_out) {
+  pdl_wait();  // programmatic dependent launch: nothing above touches global memory
+  pdl_launch_dependents();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const long row = static_cast<long>(blockIdx.x) * kLnWarps + warp;
   if (row >= rows) return;
@@ -318,6 +320,8 @@ layernorm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, long lddy, const floa
                      int rows, int D, const float* __restrict__ dres, long lddres, float* __restrict__ dx, long lddx,
                      __nv_bfloat16* __restrict__ dxb, long lddxb, int row_period, int row_skip,
                      float* __restrict__ ws, int /*want_dcol*/, int /*dcol_period*/, int /*dcol_skip*/) {
+  pdl_wait();  // programmatic dependent launch: nothing above touches global memory
+  pdl_launch_dependents();
   extern __shared__ float s_acc[];  // [3][D] (the dcol part is not produced by this fallback)
   for (int c = threadIdx.x; c < 3 * D; c += blockDim.x) s_acc[c] = 0.f;
   __syncthreads();
@@ -387,6 +391,8 @@ layernorm_bwd_reg_kernel(const __nv_bfloat16* __restrict__ dy, long lddy, const 
                          long lddres, float* __restrict__ dx, long lddx, __nv_bfloat16* __restrict__ dxb, long lddxb,
                          int row_period, int row_skip, float* __restrict__ ws, int want_dcol, int dcol_period,
                          int dcol_skip) {
+  pdl_wait();  // programmatic dependent launch: nothing above touches global memory
+  pdl_launch_dependents();
   extern __shared__ __align__(16) float s_acc[];  // [warps][3][D]: dgamma, dbeta, column sums of dx
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   float* my = s_acc + static_cast<long>(warp) * 3 * D;
@@ -482,6 +488,8 @@ layernorm_bwd_pipe_kernel(const __nv_bfloat16* __restrict__ dy, long lddy, const
                          long lddres, float* __restrict__ dx, long lddx, __nv_bfloat16* __restrict__ dxb, long lddxb,
                          int row_period, int row_skip, float* __restrict__ ws, int want_dcol, int dcol_period,
                          int dcol_skip) {
+  pdl_wait();  // programmatic dependent launch: nothing above touches global memory
+  pdl_launch_dependents();
   extern __shared__ __align__(16) float s_acc[];  // [warps][3][D]: dgamma, dbeta, column sums of dx
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   float* my = s_acc + static_cast<long>(warp) * 3 * D;
@@ -596,6 +604,8 @@ layernorm_bwd_pipe_kernel(const __nv_bfloat16* __restrict__ dy, long lddy, const
 __global__ void __launch_bounds__(256)
 ln_param_reduce_kernel(const float* __restrict__ ws, int nblocks, int D, float* __restrict__ dgamma,
                        float* __restrict__ dbeta, float* __restrict__ dcol) {
+  pdl_wait();  // programmatic dependent launch: nothing above touches global memory
+  pdl_launch_dependents();
   __shared__ float red[8][33];
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
   const int c = blockIdx.x * 32 + tx;
@@ -693,6 +703,8 @@ template <bool F32>
 __global__ void __launch_bounds__(256)
 colsum_kernel(const void* __restrict__ xv, long ldx, int rows, int cols, int row_period, int row_skip,
               int row_invert, int rows_per_block, float* __restrict__ out) {
+  pdl_wait();  // programmatic dependent launch: nothing above touches global memory
+  pdl_launch_dependents();
   __shared__ float4 s_part[4][64];
   const int tx = threadIdx.x & 63, ty = threadIdx.x >> 6;
   const int c = (blockIdx.x * 64 + tx) * 4;
@@ -905,7 +917,7 @@ extern "C" int jm_layernorm_fwd(const float* x, long ldx, int rows, int dim, con
   JM_CHECK(!y_f32 || ldyf % 4 == 0, "jm_layernorm_fwd: ldyf must be a multiple of 4");
   if (rows == 0) return 0;
   const int grid = (rows + kLnWarps - 1) / kLnWarps;
-  layernorm_fwd_kernel<<<grid, kLnWarps * 32, 0, STREAM>>>(x, ldx, rows, dim, gamma, beta, eps,
+  JM_LAUNCH_PDL(layernorm_fwd_kernel, grid, kLnWarps * 32, 0, STREAM, x, ldx, rows, dim, gamma, beta, eps,
                                                            reinterpret_cast<__nv_bfloat16*>(y_bf16), ldy, y_f32, ldyf,
                                                            mean, rstd);
   JM_AFTER_LAUNCH();
@@ -944,23 +956,23 @@ extern "C" int jm_layernorm_bwd(const jm_bf16* dy, long lddy, const float* x, lo
       want_dcol, dcol_period, dcol_skip
   const size_t smem_reg = static_cast<size_t>(kLnBwdWarps) * 3 * dim * sizeof(float);
   const int tr = kLnBwdWarps * 32;
-  if (dim <= 128) layernorm_bwd_pipe_kernel<1><<<grid, tr, smem_reg, STREAM>>>(JM_LN_BWD_ARGS);
-  else if (dim <= 256) layernorm_bwd_pipe_kernel<2><<<grid, tr, smem_reg, STREAM>>>(JM_LN_BWD_ARGS);
-  else if (dim <= 512) layernorm_bwd_pipe_kernel<4><<<grid, tr, smem_reg, STREAM>>>(JM_LN_BWD_ARGS);
-  else if (dim <= 768) layernorm_bwd_reg_kernel<6><<<grid, tr, smem_reg, STREAM>>>(JM_LN_BWD_ARGS);
+  if (dim <= 128) JM_LAUNCH_PDL(layernorm_bwd_pipe_kernel<1>, grid, tr, smem_reg, STREAM, JM_LN_BWD_ARGS);
+  else if (dim <= 256) JM_LAUNCH_PDL(layernorm_bwd_pipe_kernel<2>, grid, tr, smem_reg, STREAM, JM_LN_BWD_ARGS);
+  else if (dim <= 512) JM_LAUNCH_PDL(layernorm_bwd_pipe_kernel<4>, grid, tr, smem_reg, STREAM, JM_LN_BWD_ARGS);
+  else if (dim <= 768) JM_LAUNCH_PDL(layernorm_bwd_reg_kernel<6>, grid, tr, smem_reg, STREAM, JM_LN_BWD_ARGS);
   else if (dim <= 1024) {
     JM_CUDA(cudaFuncSetAttribute(layernorm_bwd_reg_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
-    layernorm_bwd_reg_kernel<8><<<grid, tr, smem_reg, STREAM>>>(JM_LN_BWD_ARGS);
+    JM_LAUNCH_PDL(layernorm_bwd_reg_kernel<8>, grid, tr, smem_reg, STREAM, JM_LN_BWD_ARGS);
   } else if (dim <= 1280) {
     JM_CUDA(cudaFuncSetAttribute(layernorm_bwd_reg_kernel<10>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
-    layernorm_bwd_reg_kernel<10><<<grid, tr, smem_reg, STREAM>>>(JM_LN_BWD_ARGS);
+    JM_LAUNCH_PDL(layernorm_bwd_reg_kernel<10>, grid, tr, smem_reg, STREAM, JM_LN_BWD_ARGS);
   } else {
     const int g8 = (rows + kLnWarps - 1) / kLnWarps < grid ? (rows + kLnWarps - 1) / kLnWarps : grid;
     grid = g8;
-    layernorm_bwd_kernel<<<grid, kLnWarps * 32, smem, STREAM>>>(JM_LN_BWD_ARGS);
+    JM_LAUNCH_PDL(layernorm_bwd_kernel, grid, kLnWarps * 32, smem, STREAM, JM_LN_BWD_ARGS);
   }
 #undef JM_LN_BWD_ARGS
-  ln_param_reduce_kernel<<<(3 * dim + 31) / 32, 256, 0, STREAM>>>(static_cast<const float*>(workspace), grid, dim,
+  JM_LAUNCH_PDL(ln_param_reduce_kernel, (3 * dim + 31) / 32, 256, 0, STREAM, static_cast<const float*>(workspace), grid, dim,
                                                                   dgamma, dbeta, dcol);
   JM_AFTER_LAUNCH();
   return 0;
@@ -1005,10 +1017,10 @@ extern "C" int jm_colsum(const void* x, int is_f32, long ldx, int rows, int cols
   if (rows_per_block < 32) rows_per_block = 32;
   gy = (rows + rows_per_block - 1) / rows_per_block;
   if (is_f32)
-    colsum_kernel<true><<<dim3(gx, gy), 256, 0, STREAM>>>(x, ldx, rows, cols, row_period, row_skip, row_invert,
+    JM_LAUNCH_PDL(colsum_kernel<true>, dim3(gx, gy), 256, 0, STREAM, x, ldx, rows, cols, row_period, row_skip, row_invert,
                                                           rows_per_block, out);
   else
-    colsum_kernel<false><<<dim3(gx, gy), 256, 0, STREAM>>>(x, ldx, rows, cols, row_period, row_skip, row_invert,
+    JM_LAUNCH_PDL(colsum_kernel<false>, dim3(gx, gy), 256, 0, STREAM, x, ldx, rows, cols, row_period, row_skip, row_invert,
                                                            rows_per_block, out);
   JM_AFTER_LAUNCH();
   return 0;
@@ -1044,6 +1056,8 @@ extern "C" int jm_cast_bf16(const float* x, jm_bf16* y, long n, void* stream) {
 __global__ void add_bias_cast_kernel(const float* __restrict__ src, long lds, int rows, int cols,
                                      const float* __restrict__ bias, float* __restrict__ dst_f32, long ldd,
                                      __nv_bfloat16* __restrict__ dst_bf16, long ldd16) {
+  pdl_wait();  // programmatic dependent launch: nothing above touches global memory
+  pdl_launch_dependents();
   const int c4 = cols >> 2;
   const long total = static_cast<long>(rows) * c4;
   for (long i = blockIdx.x * static_cast<long>(blockDim.x) + threadIdx.x; i < total;
@@ -1069,7 +1083,7 @@ extern "C" int jm_add_bias_cast(const float* src, long lds, int rows, int cols, 
   long blocks = (total + 255) / 256;
   const long cap = static_cast<long>(sm_count()) * 8;
   if (blocks > cap) blocks = cap;
-  add_bias_cast_kernel<<<static_cast<int>(blocks), 256, 0, STREAM>>>(src, lds, rows, cols, bias, dst_f32, ldd,
+  JM_LAUNCH_PDL(add_bias_cast_kernel, static_cast<int>(blocks), 256, 0, STREAM, src, lds, rows, cols, bias, dst_f32, ldd,
                                                                      reinterpret_cast<__nv_bfloat16*>(dst_bf16), ldd16);
   JM_AFTER_LAUNCH();
   return 0;

@@ -1011,6 +1011,10 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr;
+  // programmatic dependent launch: the prologue above (barriers, TMEM) ran while the previous kernel drained;
+  // its results are needed from here on
+  pdl_wait();
+  pdl_launch_dependents();
 
   const int tiles_mn = sh.num_m * sh.num_n;
   const int total_tiles = tiles_mn * sh.splits;
@@ -1173,6 +1177,8 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
   cluster_sync_all();  // peer barriers initialised, TMEM allocated in both CTAs
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr;
+  pdl_wait();  // (see gemm_kernel)
+  pdl_launch_dependents();
 
   const int tiles_mn = sh.num_m * sh.num_n;  // num_m counts 256-row pair tiles here
   const int total_tiles = tiles_mn * sh.splits;
@@ -1307,7 +1313,7 @@ static int launch_gemm(const GemmMaps& tm, const GemmShape& sh, const EpiParams&
     JM_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, GemmCfg<BN>::SMEM_BYTES));
     attr_set = true;
   }
-  kern<<<grid, kGemmThreads, GemmCfg<BN>::SMEM_BYTES, stream>>>(tm.a, tm.b, tm.o, tm.o2, sh, ep);
+  JM_LAUNCH_PDL(kern, grid, kGemmThreads, GemmCfg<BN>::SMEM_BYTES, stream, tm.a, tm.b, tm.o, tm.o2, sh, ep);
   JM_AFTER_LAUNCH();
   return 0;
 }
@@ -1326,23 +1332,25 @@ static int launch_gemm2(const GemmMaps& tm, const GemmShape& sh, const EpiParams
   cfg.blockDim = dim3(kGemmThreads);
   cfg.dynamicSmemBytes = Gemm2Cfg::SMEM_BYTES;
   cfg.stream = stream;
-  cudaLaunchAttribute attr[2];
+  cudaLaunchAttribute attr[3];
   attr[0].id = cudaLaunchAttributeClusterDimension;
   attr[0].val.clusterDim.x = 2;
   attr[0].val.clusterDim.y = 1;
   attr[0].val.clusterDim.z = 1;
+  attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[1].val.programmaticStreamSerializationAllowed = pdl_enabled() ? 1 : 0;
   cfg.attrs = attr;
-  cfg.numAttrs = 1;
+  cfg.numAttrs = 2;
   static int policy = -1;
   if (policy < 0) {
     const char* e = getenv("JM_PAIR_POLICY");
     policy = e ? atoi(e) : 0;
   }
   if (policy > 0) {
-    attr[1].id = cudaLaunchAttributeClusterSchedulingPolicyPreference;
-    attr[1].val.clusterSchedulingPolicyPreference =
+    attr[2].id = cudaLaunchAttributeClusterSchedulingPolicyPreference;
+    attr[2].val.clusterSchedulingPolicyPreference =
         policy == 1 ? cudaClusterSchedulingPolicySpread : cudaClusterSchedulingPolicyLoadBalancing;
-    cfg.numAttrs = 2;
+    cfg.numAttrs = 3;
   }
   // A persistent grid must not exceed the clusters the GPU can hold at once (GPCs with an odd SM left over
   // cannot host a pair there): surplus clusters would run as a second wave.
