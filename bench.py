@@ -7,8 +7,8 @@
 
 Workload (BASELINE.json configs[1]): ViT-B/16, 224 px, mask 0.75, decoder 8 x 512 (16 heads),
 Jumbo CLS J = 3, bf16 compute, GLOBAL batch 4096 synthetic uint8 images per optimizer step,
-run as micro-batches of 512 per GPU with the reference's gradient-accumulation semantics
-(4096 / (512 * N) micro-steps per rank, one gradient all-reduce and one AdamW per step).
+run as micro-batches of min(1024, 4096 / N) per GPU with the reference's gradient-accumulation semantics
+(4096 / (micro * N) micro-steps per rank, one gradient all-reduce and one AdamW per step).
 One "step" = one optimizer step = forward + backward of 4096 images + all-reduce + AdamW.
 
 Prints ONE JSON line (rank 0).  `value` is whole-job images/s with inputs resident in HBM;
@@ -159,7 +159,7 @@ def workload_config(args, micro, accum, world):
                     f"synthetic uint8 (BASELINE.json configs[1])",
         "global_batch": args.global_batch, "micro_batch": micro, "grad_accum": accum, "parallelism": f"dp{world}",
         "norm_pix_loss": False,
-        "l2": "inputs larger than L2: every micro-batch streams >20 GB of activations through a 126 MB L2",
+        "l2": "inputs larger than L2: every micro-batch streams tens of GB of activations through a 126 MB L2",
     }
 
 
@@ -319,17 +319,18 @@ def run_ours(args):
             "achieved": dw_tflops, "peak": peaks["bf16_burst"], "unit": "TFLOP/s",
             "frac": dw_tflops / peaks["bf16_burst"],
             # dram__bytes_read.sum + dram__bytes_write.sum of one launch, ncu --set full
-            # (profiles/r1e_gemm_dw_ncu_full.md); algorithmic bytes 2*(M+N)*K + 4*M*N = 525.9 MB
-            "traffic": 529.8e6 if micro == 512 and args.config == "vit_b16" else None,
+            # (profiles/r1e_gemm_dw_ncu_full.md, r1f_* at micro-batch 1024); algorithmic bytes 2*(M+N)*K + 4*M*N = 525.9 MB
+            "traffic": {512: 529.8e6, 1024: 1141.3e6}.get(micro) if args.config == "vit_b16" else None,
             "peak_source": f"{peaks['source']} (burst: kernel timed alone)", "kernel_ms": dw_ms,
         },
         "roofline_gelu_fwd": {
             "bound": "tensor", "kernel": f"gemm2_kernel<K,MN,GELU> (CTA pair, 256x256 tile) decoder FFN w1 forward M={M} N={N} K={K}",
             "achieved": gemm_tflops, "peak": peaks["bf16_burst"], "unit": "TFLOP/s",
             "frac": gemm_tflops / peaks["bf16_burst"],
-            "traffic": 905.7e6 if micro == 512 and args.config == "vit_b16" else None,
+            "traffic": {512: 905.7e6, 1024: 1865.9e6}.get(micro) if args.config == "vit_b16" else None,
             "kernel_ms": gemm_ms,
-            "note": "writes 834 MB (pre-activation + GELU) per launch: 128 us of HBM time against 129 us of MMA time",
+            "note": "epilogue-bound: writes 1.6 bytes per FLOP-byte of input (gelu'(h) + gelu(h), bf16, TMA stores); "
+                    "see DESIGN.md section 4",
         },
         "step_roofline": {
             "bound": "tensor", "achieved": step_tflops_per_gpu, "peak": peaks["bf16_sustained"], "unit": "TFLOP/s",
@@ -361,7 +362,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--config", default="vit_b16", choices=["vit_b16", "vit_l16", "vit_h14"])
     ap.add_argument("--global-batch", type=int, default=4096)
-    ap.add_argument("--micro-batch", type=int, default=512)
+    ap.add_argument("--micro-batch", type=int, default=1024)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     if args.impl == "reference":

@@ -12,6 +12,14 @@ __global__ void k(float* out, int iters) {
       if (OP == 1) asm volatile("ex2.approx.ftz.f32 %0, %0;" : "+f"(a[i]));
       if (OP == 2) asm volatile("rcp.approx.ftz.f32 %0, %0;" : "+f"(a[i]));
       if (OP == 3) asm volatile("fma.rn.f32 %0, %0, %0, %0;" : "+f"(a[i]));
+      if (OP == 5) {
+        unsigned r;
+        asm volatile("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(a[i]), "f"(a[(i + 1) & 7]));
+        a[i] = __uint_as_float(r | 0x3f000000u);
+      }
+      if (OP == 6) {
+        asm volatile("shfl.sync.idx.b32 %0, %0, 3, 31, 0xffffffff;" : "+f"(a[i]));
+      }
       if (OP == 4) {
         unsigned long long& p = *reinterpret_cast<unsigned long long*>(&a[i & ~1]);
         asm volatile("fma.rn.f32x2 %0, %0, %0, %0;" : "+l"(p));
@@ -49,5 +57,7 @@ int main() {
   run<2>("rcp.approx");
   run<3>("fma");
   run<4>("fma.f32x2 (instructions; x2 for FMAs)");
+  run<5>("cvt.rn.bf16x2.f32 (+1 LOP3)");
+  run<6>("shfl.idx");
   return 0;
 }
