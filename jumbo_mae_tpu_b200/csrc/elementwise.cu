@@ -384,7 +384,10 @@ layernorm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, long lddy, const floa
 constexpr int kLnBwdWarps = 4;
 
 template <int NV>
-__global__ void __launch_bounds__(kLnBwdWarps * 32, 3)
+#ifndef JM_LN_REG_CTAS
+#define JM_LN_REG_CTAS 4  // dim 768: 127 registers without spills, four resident CTAs: 81 -> 77 us at the encoder shape
+#endif
+__global__ void __launch_bounds__(kLnBwdWarps * 32, NV == 6 ? JM_LN_REG_CTAS : 3)
 layernorm_bwd_reg_kernel(const __nv_bfloat16* __restrict__ dy, long lddy, const float* __restrict__ x, long ldx,
                          const float* __restrict__ mean, const float* __restrict__ rstd,
                          const float* __restrict__ gamma, int rows, int D, const float* __restrict__ dres,
@@ -481,7 +484,10 @@ layernorm_bwd_reg_kernel(const __nv_bfloat16* __restrict__ dy, long lddy, const 
 // registers allow it: 193 -> 138 us at the decoder shape (93 % of the HBM rate).  Wider rows were measured
 // slower with it and keep the kernel above.
 template <int NV>
-__global__ void __launch_bounds__(kLnBwdWarps * 32, 3)
+#ifndef JM_LN_PIPE_CTAS
+#define JM_LN_PIPE_CTAS 3
+#endif
+__global__ void __launch_bounds__(kLnBwdWarps * 32, JM_LN_PIPE_CTAS)
 layernorm_bwd_pipe_kernel(const __nv_bfloat16* __restrict__ dy, long lddy, const float* __restrict__ x, long ldx,
                          const float* __restrict__ mean, const float* __restrict__ rstd,
                          const float* __restrict__ gamma, int rows, int D, const float* __restrict__ dres,
@@ -924,13 +930,14 @@ extern "C" int jm_layernorm_fwd(const float* x, long ldx, int rows, int dim, con
   return 0;
 }
 
-static int ln_bwd_blocks(int rows) {
+static int ln_bwd_blocks(int rows, int dim) {
   const int need = (rows + 3) / 4;  // 4 rows (warps) per CTA in the register kernel, 8 in the fallback
-  return need < kLnBwdMaxBlocks ? need : kLnBwdMaxBlocks;
+  const int cap = (dim > 512 && dim <= 768) ? kLnBwdMaxBlocks / 3 * JM_LN_REG_CTAS : kLnBwdMaxBlocks;
+  return need < cap ? need : cap;
 }
 
 extern "C" size_t jm_layernorm_bwd_workspace(int rows, int dim) {
-  return static_cast<size_t>(ln_bwd_blocks(rows)) * 3 * dim * sizeof(float);
+  return static_cast<size_t>(ln_bwd_blocks(rows, dim)) * 3 * dim * sizeof(float);
 }
 
 extern "C" int jm_layernorm_bwd(const jm_bf16* dy, long lddy, const float* x, long ldx, const float* mean,
@@ -944,7 +951,7 @@ extern "C" int jm_layernorm_bwd(const jm_bf16* dy, long lddy, const float* x, lo
   if (rows == 0) return 0;
   JM_CHECK(workspace && workspace_bytes >= jm_layernorm_bwd_workspace(rows, dim),
            "jm_layernorm_bwd: workspace too small");
-  int grid = ln_bwd_blocks(rows);
+  int grid = ln_bwd_blocks(rows, dim);
   const size_t smem = static_cast<size_t>(3) * dim * sizeof(float);
   if (smem > 48 * 1024) {
     JM_CUDA(cudaFuncSetAttribute(layernorm_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
@@ -959,7 +966,11 @@ extern "C" int jm_layernorm_bwd(const jm_bf16* dy, long lddy, const float* x, lo
   if (dim <= 128) JM_LAUNCH_PDL(layernorm_bwd_pipe_kernel<1>, grid, tr, smem_reg, STREAM, JM_LN_BWD_ARGS);
   else if (dim <= 256) JM_LAUNCH_PDL(layernorm_bwd_pipe_kernel<2>, grid, tr, smem_reg, STREAM, JM_LN_BWD_ARGS);
   else if (dim <= 512) JM_LAUNCH_PDL(layernorm_bwd_pipe_kernel<4>, grid, tr, smem_reg, STREAM, JM_LN_BWD_ARGS);
+#ifdef JM_LN_PIPE6
+  else if (dim <= 768) JM_LAUNCH_PDL(layernorm_bwd_pipe_kernel<6>, grid, tr, smem_reg, STREAM, JM_LN_BWD_ARGS);
+#else
   else if (dim <= 768) JM_LAUNCH_PDL(layernorm_bwd_reg_kernel<6>, grid, tr, smem_reg, STREAM, JM_LN_BWD_ARGS);
+#endif
   else if (dim <= 1024) {
     JM_CUDA(cudaFuncSetAttribute(layernorm_bwd_reg_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
     JM_LAUNCH_PDL(layernorm_bwd_reg_kernel<8>, grid, tr, smem_reg, STREAM, JM_LN_BWD_ARGS);
