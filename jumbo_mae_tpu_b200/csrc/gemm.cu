@@ -540,6 +540,16 @@ __device__ __forceinline__ void sts128_or_zero(uint32_t addr, uint32_t a, uint32
       : "memory");
 }
 
+// Optional cycle accounting of the row-register epilogue (build with -DJM_EPI_PROF; block 0, first epilogue warp
+// prints one line per launch): where an epilogue warp's time goes.
+#ifdef JM_EPI_PROF
+#define EPI_T(var) const long long var = clock64()
+#define EPI_ACC(sum, t0) sum += clock64() - (t0)
+#else
+#define EPI_T(var)
+#define EPI_ACC(sum, t0)
+#endif
+
 // Row-register epilogue for the kinds whose only per-element output is bf16 (EPI_BF16, EPI_GELU_FWD,
 // EPI_GELU_BWD).  The arithmetic runs in the TMEM layout (one thread = one accumulator row, 32 columns at a
 // time), the results are packed to bf16 and only then transposed through the warp's 2 KB staging tile
@@ -573,6 +583,10 @@ __device__ __forceinline__ void epilogue_rows(const EpiParams& ep, const GemmSha
   const bool tma = ep.tma_store != 0;  // kernel-uniform
   const bool saved_grad = ep.act >= 3;  // acts 3 / 4: the GELU derivative is stored / consumed directly
   uint32_t buf = 0;                     // byte offset of the staging tile in use (NBUF tiles, used in turn)
+#ifdef JM_EPI_PROF
+  long long pt_tfull = 0, pt_ld = 0, pt_math = 0, pt_flush = 0, pt_free = 0, pt_setup = 0, pt_sts = 0, pt_rel = 0, pt_ldi = 0, pt_half = 0;
+  const long long pt_begin = clock64();
+#endif
   int iter = 0;
   for (int t = tile0; t < total_tiles; t += tile_step, ++iter) {
     const int rem = t % tiles_mn;
@@ -580,9 +594,11 @@ __device__ __forceinline__ void epilogue_rows(const EpiParams& ep, const GemmSha
     const int acc = iter & 1;
     const uint32_t acc_phase = (iter >> 1) & 1;
     auto release = [&]() {
+      EPI_T(pr0);
       tc_fence_before();
       if constexpr (CG == 1) mbar_arrive(&tempty[acc]);
       else mbar_arrive_cluster(mapa_shared(smem_u32(&tempty[acc]), 0));  // the leader CTA issues the MMAs
+      EPI_ACC(pt_rel, pr0);
     };
     if constexpr (PARTS < 4) {
       if (part >= PARTS) {  // keep in lock-step with the accumulator hand-over
@@ -592,6 +608,7 @@ __device__ __forceinline__ void epilogue_rows(const EpiParams& ep, const GemmSha
         continue;
       }
     }
+    EPI_T(psu);
     const int row_base = m_blk * (BM * CG) + m_off + q * 32;
     const int colp = n_blk * BN + part * (32 * NH);
     uint32_t zflag = 0;  // set for a row that stores zeros (row_mask_mode 1)
@@ -635,13 +652,21 @@ __device__ __forceinline__ void epilogue_rows(const EpiParams& ep, const GemmSha
       bs[h] = (has_bias && colh + lane < sh.N) ? __ldg(ep.bias + colh + lane) * sc[h] : 0.f;
     }
     if constexpr (EPI == EPI_GELU_BWD) load_aux(colp);
+    EPI_ACC(pt_setup, psu);
+    EPI_T(pt0);
     mbar_wait(&tfull[acc], acc_phase);
+    EPI_ACC(pt_tfull, pt0);
     tc_fence_after();
     const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * BN + part * (32 * NH);
     uint32_t r[NH][32];
+    EPI_T(pl0);
     if (colp < sh.N) tmem_ld_32x32(t_addr, r[0]);  // warp-uniform
+    EPI_ACC(pt_ldi, pl0);
+    EPI_T(pt1);
     tmem_ld_wait();
+    EPI_ACC(pt_ld, pt1);
     if constexpr (NH == 1) release();
+    EPI_T(ph0);
 #pragma unroll
     for (int h = 0; h < NH; ++h) {
       const int colh = colp + 32 * h;
@@ -652,6 +677,7 @@ __device__ __forceinline__ void epilogue_rows(const EpiParams& ep, const GemmSha
       // the staging layout; rows and columns beyond the matrix are clipped by the tensor map) or, when rows
       // must be skipped, with 16-byte stores in the coalesced view.
       auto flush = [&](int o) {
+        EPI_T(pf0);
         if (tma) {
           fence_proxy_async();  // this lane's staging writes -> visible to the async proxy
           __syncwarp();
@@ -673,6 +699,7 @@ __device__ __forceinline__ void epilogue_rows(const EpiParams& ep, const GemmSha
 #pragma unroll
           for (int i = 0; i < 4; ++i) stg128_if(obase + i * ostep, v[i], ok & (1u << i));
         }
+        EPI_ACC(pt_flush, pf0);
       };
       // next staging tile (with two tiles, the store issued from the other one may still be reading it)
       auto next_buf = [&]() {
@@ -680,10 +707,12 @@ __device__ __forceinline__ void epilogue_rows(const EpiParams& ep, const GemmSha
       };
       // the previous contents of the staging tile have left it (TMA: the store has read them)
       auto staging_free = [&]() {
+        EPI_T(ps0);
         if (tma) {
           if (lane == 0) tma_store_wait_read<NBUF - 1>();
         }
         __syncwarp();
+        EPI_ACC(pt_free, ps0);
       };
       uint32_t G[16];
       if (live) {
@@ -717,6 +746,7 @@ __device__ __forceinline__ void epilogue_rows(const EpiParams& ep, const GemmSha
           }
         } else {
           // branch-free (one basic block for the 32 columns); rows that store zeros are handled at the STS
+          EPI_T(pm0);
           uint32_t P[16];
           f32x2 v[16];  // column pairs
           const f32x2 sc2 = pack2(sc[h], sc[h]);
@@ -749,10 +779,13 @@ __device__ __forceinline__ void epilogue_rows(const EpiParams& ep, const GemmSha
               }
             }
           }
+          EPI_ACC(pt_math, pm0);
           staging_free();
+          EPI_T(pq0);
 #pragma unroll
           for (int j = 0; j < 4; ++j)
             sts128_or_zero(own_addr + buf + ((j ^ own_sw) << 4), P[4 * j], P[4 * j + 1], P[4 * j + 2], P[4 * j + 3], zflag);
+          EPI_ACC(pt_sts, pq0);
           if constexpr (EPI == EPI_GELU_FWD) {
             flush(0);
             next_buf();
@@ -762,7 +795,9 @@ __device__ __forceinline__ void epilogue_rows(const EpiParams& ep, const GemmSha
       if constexpr (NH == 2) {
         if (h == 0 && colp + 32 < sh.N) {  // both in flight during the stores below
           if constexpr (EPI == EPI_GELU_BWD) load_aux(colp + 32);
+          EPI_T(pl1);
           tmem_ld_32x32(t_addr + 32, r[1]);
+          EPI_ACC(pt_ldi, pl1);
         }
       }
       if (live) {
@@ -808,16 +843,27 @@ __device__ __forceinline__ void epilogue_rows(const EpiParams& ep, const GemmSha
       }
       if constexpr (NH == 2) {
         if (h == 0) {
+          EPI_T(pt2);
           tmem_ld_wait();
+          EPI_ACC(pt_ld, pt2);
           release();
         }
       }
     }
+    EPI_ACC(pt_half, ph0);
   }
   if (tma) {  // the last stores must have read the staging tile (and landed) before the CTA may go away
     if (lane == 0) tma_store_wait_all();
   }
   __syncwarp();
+#ifdef JM_EPI_PROF
+  if (blockIdx.x == 0 && e == 0 && lane == 0) {
+    const long long tot = clock64() - pt_begin;
+    printf("epi prof: tiles %d total %lld  setup %lld  tfull %lld  ld_issue %lld  tmem_ld %lld  release %lld  math %lld  sts %lld  flush %lld  staging_free %lld  half_loop %lld  rest %lld\n", iter, tot,
+           pt_setup, pt_tfull, pt_ldi, pt_ld, pt_rel, pt_math, pt_sts, pt_flush, pt_free, pt_half,
+           tot - pt_setup - pt_tfull - pt_ldi - pt_ld - pt_rel - pt_math - pt_sts - pt_flush - pt_free);
+  }
+#endif
 }
 
 // f32 epilogue through TMA (EPI_F32 without positional embedding / skipped rows): out (=|+=) acc + bias
@@ -1110,13 +1156,19 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
 // Barriers: `full` lives in the leader (its producer arrives, both CTAs' TMA bytes complete on it);
 // `empty` and `tfull` are signalled in both CTAs by multicast commits; `tempty` lives in the leader and is
 // arrived on by the epilogue threads of both CTAs.
+#ifndef JM_PAIR_BF16_BUFS
+#define JM_PAIR_BF16_BUFS 1  // measured 1-3 % faster on the plain bf16 GEMMs than two tiles + 5 stages
+#endif
+template <int EPI>
 struct Gemm2Cfg {
   static constexpr int BN = 256;
   static constexpr int A_BYTES = BM * BK * 2;         // this CTA's 128 rows
   static constexpr int B_BYTES = (BN / 2) * BK * 2;   // this CTA's 128 of the 256 columns
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-  static constexpr int EPI_BUFS = 2;
-  static constexpr int STAGES = 5;
+  // Two staging tiles per epilogue warp (5 pipeline stages) where the epilogue is heavy; the light plain-bf16
+  // epilogue can run with one tile and a sixth stage (JM_PAIR_BF16_BUFS).
+  static constexpr int EPI_BUFS = (EPI == EPI_BF16) ? JM_PAIR_BF16_BUFS : 2;
+  static constexpr int STAGES = EPI_BUFS == 2 ? 5 : 6;
   static constexpr int TMEM_COLS = 2 * BN;
   static constexpr int BAR_BYTES = (2 * STAGES + 4) * 8 + 16 + kEpiWarps * 2 * 8;  // + residual-load barriers
   static constexpr int EPI_BYTES = kEpiWarps * kStageBytesPerWarp * EPI_BUFS;
@@ -1128,7 +1180,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
              const __grid_constant__ CUtensorMap tmO, const __grid_constant__ CUtensorMap tmO2, const GemmShape sh,
              const EpiParams ep) {
-  using Cfg = Gemm2Cfg;
+  using Cfg = Gemm2Cfg<EPI>;
   constexpr int STAGES = Cfg::STAGES;
   constexpr int BN = Cfg::BN;
   extern __shared__ uint8_t smem_raw[];
@@ -1324,13 +1376,13 @@ static int launch_gemm2(const GemmMaps& tm, const GemmShape& sh, const EpiParams
   auto kern = gemm2_kernel<A_MN, B_MN, EPI>;
   static bool attr_set = false;
   if (!attr_set) {
-    JM_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Gemm2Cfg::SMEM_BYTES));
+    JM_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Gemm2Cfg<EPI>::SMEM_BYTES));
     attr_set = true;
   }
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(grid);
   cfg.blockDim = dim3(kGemmThreads);
-  cfg.dynamicSmemBytes = Gemm2Cfg::SMEM_BYTES;
+  cfg.dynamicSmemBytes = Gemm2Cfg<EPI>::SMEM_BYTES;
   cfg.stream = stream;
   cudaLaunchAttribute attr[3];
   attr[0].id = cudaLaunchAttributeClusterDimension;
