@@ -158,6 +158,9 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   if (mbar_try_wait(bar, parity)) return;
   const long long t0 = clock64();
   while (!mbar_try_wait(bar, parity)) {
+#ifdef JM_WAIT_SLEEP
+    __nanosleep(JM_WAIT_SLEEP);
+#endif
     if (clock64() - t0 > 4000000000LL) {
       printf("jm: mbarrier wait timed out (block %d thread %d)\n", blockIdx.x, threadIdx.x);
       __trap();
