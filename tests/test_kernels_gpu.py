@@ -141,7 +141,11 @@ def test_layernorm_fwd_strided_rows(ops):
 
 
 @pytest.mark.parametrize("rows,D,period,skip", [(64, 64, 0, 0), (500, 512, 0, 0), (260, 768, 52, 3),
-                                                (12, 2304, 0, 0), (40, 1280, 0, 0)])
+                                                (12, 2304, 0, 0), (40, 1280, 0, 0),
+                                                # several rows per warp: the software-pipelined kernel (dim <= 512)
+                                                # with and without skipped rows, and the dim-768 kernel
+                                                (5000, 512, 13, 3), (7000, 256, 7, 2), (4001, 128, 0, 0),
+                                                (6000, 768, 52, 3)])
 def test_layernorm_bwd(ops, rows, D, period, skip):
     g = torch.Generator().manual_seed(D + rows)
     x = (torch.randn(rows, D, generator=g) * 2 + 0.5).requires_grad_(True)
