@@ -121,18 +121,33 @@ __device__ __forceinline__ void fwd_chunk(const uint32_t (&qf)[HD / 16][4], uint
     mneg[r] = -mn;
     l[r] *= alpha[r];
   }
+  // packed f32x2 arithmetic on the (e0, e1) / (e2, e3) pairs, which share a row: the kernel is bound by
+  // instruction issue, and one FFMA2 slot does two of the scale-and-shift / sum / rescale operations
+  {
+    const f32x2 k2 = pack2(kLog2e, kLog2e);
+    const f32x2 mn2[2] = {pack2(mneg[0], mneg[0]), pack2(mneg[1], mneg[1])};
+    f32x2 l2[2] = {pack2(0.f, 0.f), pack2(0.f, 0.f)};
 #pragma unroll
-  for (int nt = 0; nt < NT; ++nt)
+    for (int nt = 0; nt < NT; ++nt)
 #pragma unroll
-    for (int e = 0; e < 4; ++e) {
-      const float p = ex2f(fmaf(s[nt][e], kLog2e, mneg[e >> 1]));
-      s[nt][e] = p;
-      l[e >> 1] += p;
+      for (int r = 0; r < 2; ++r) {
+        float x0, x1;
+        unpack2(fma2(pack2(s[nt][2 * r], s[nt][2 * r + 1]), k2, mn2[r]), x0, x1);
+        const float p0 = ex2f(x0), p1 = ex2f(x1);
+        s[nt][2 * r] = p0, s[nt][2 * r + 1] = p1;
+        l2[r] = add2(l2[r], pack2(p0, p1));
+      }
+#pragma unroll
+    for (int r = 0; r < 2; ++r) {
+      float a, b;
+      unpack2(l2[r], a, b);
+      l[r] += a + b;
     }
+    const f32x2 al2[2] = {pack2(alpha[0], alpha[0]), pack2(alpha[1], alpha[1])};
 #pragma unroll
-  for (int i = 0; i < HD / 8; ++i) {
-    o[i][0] *= alpha[0], o[i][1] *= alpha[0];
-    o[i][2] *= alpha[1], o[i][3] *= alpha[1];
+    for (int i = 0; i < HD / 8; ++i)
+#pragma unroll
+      for (int r = 0; r < 2; ++r) unpack2(mul2(pack2(o[i][2 * r], o[i][2 * r + 1]), al2[r]), o[i][2 * r], o[i][2 * r + 1]);
   }
 #pragma unroll
   for (int kk = 0; kk < NT / 2; ++kk) {
@@ -273,17 +288,26 @@ __device__ __forceinline__ void bwd_q_chunk(const uint32_t (&qf)[HD / 16][4], co
       mma_bf16(dp[2 * np + 1], dof[ks], vb[2], vb[3]);
     }
   }
+  {  // packed f32x2 arithmetic on the (e0, e1) / (e2, e3) pairs (same query row)
+    const f32x2 k2 = pack2(kLog2e, kLog2e);
+    const f32x2 nl2[2] = {pack2(-Lr2[0], -Lr2[0]), pack2(-Lr2[1], -Lr2[1])};
+    const f32x2 nd2[2] = {pack2(-Dr[0], -Dr[0]), pack2(-Dr[1], -Dr[1])};
 #pragma unroll
-  for (int nt = 0; nt < NT; ++nt)
+    for (int nt = 0; nt < NT; ++nt)
 #pragma unroll
-    for (int e = 0; e < 4; ++e) {
-      float p = ex2f(fmaf(s[nt][e], kLog2e, -Lr2[e >> 1]));
-      if (TAIL) {
-        const int key = kc + nt * 8 + 2 * t4 + (e & 1);
-        if (key >= T) p = 0.f;
+      for (int r = 0; r < 2; ++r) {
+        float x0, x1;
+        unpack2(fma2(pack2(s[nt][2 * r], s[nt][2 * r + 1]), k2, nl2[r]), x0, x1);
+        float p0 = ex2f(x0), p1 = ex2f(x1);
+        if (TAIL) {
+          const int key = kc + nt * 8 + 2 * t4;
+          if (key >= T) p0 = 0.f;
+          if (key + 1 >= T) p1 = 0.f;
+        }
+        const f32x2 ds = mul2(pack2(p0, p1), add2(pack2(dp[nt][2 * r], dp[nt][2 * r + 1]), nd2[r]));  // dS
+        unpack2(ds, s[nt][2 * r], s[nt][2 * r + 1]);
       }
-      s[nt][e] = p * (dp[nt][e] - Dr[e >> 1]);  // dS
-    }
+  }
 #pragma unroll
   for (int kk = 0; kk < NT / 2; ++kk) {
     uint32_t a[4];
@@ -334,11 +358,16 @@ __device__ __forceinline__ void bwd_kv_chunk(const uint32_t (&kf)[HD / 16][4], c
     const float2 L2 = *reinterpret_cast<const float2*>(sL2 + q0);
     const float2 D2 = *reinterpret_cast<const float2*>(sD + q0);
     float p[4], ds[4];
+    {  // packed f32x2: the pair (e0, e1) (and (e2, e3)) is the query pair (q0, q0 + 1)
+      const f32x2 k2 = pack2(kLog2e, kLog2e), nl = pack2(-L2.x, -L2.y), nd = pack2(-D2.x, -D2.y);
 #pragma unroll
-    for (int e = 0; e < 4; ++e) {
-      const float L = (e & 1) ? L2.y : L2.x, D = (e & 1) ? D2.y : D2.x;
-      p[e] = ex2f(fmaf(st[nt][e], kLog2e, -L));
-      ds[e] = p[e] * (dpt[nt][e] - D);
+      for (int r = 0; r < 2; ++r) {
+        float x0, x1;
+        unpack2(fma2(pack2(st[nt][2 * r], st[nt][2 * r + 1]), k2, nl), x0, x1);
+        p[2 * r] = ex2f(x0), p[2 * r + 1] = ex2f(x1);
+        unpack2(mul2(pack2(p[2 * r], p[2 * r + 1]), add2(pack2(dpt[nt][2 * r], dpt[nt][2 * r + 1]), nd)), ds[2 * r],
+                ds[2 * r + 1]);
+      }
     }
     pa[nt >> 1][(nt & 1) * 2 + 0] = pack_bf16(p[0], p[1]);
     pa[nt >> 1][(nt & 1) * 2 + 1] = pack_bf16(p[2], p[3]);

@@ -116,27 +116,6 @@ __device__ __forceinline__ float gelu_grad_fast(float x) {
   return fmaf(a, du, fmaf(0.5f, t, 0.5f));
 }
 
-// Packed f32x2 arithmetic (sm_100: one FFMA2 issue slot does two FMAs).  The epilogues are bound by
-// instruction issue, not by the FMA pipe, so the polynomial parts of GELU run on column pairs.
-typedef unsigned long long f32x2;
-__device__ __forceinline__ f32x2 pack2(float a, float b) {
-  f32x2 r;
-  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(a), "f"(b));
-  return r;
-}
-__device__ __forceinline__ void unpack2(f32x2 v, float& a, float& b) {
-  asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(v));
-}
-__device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) {
-  f32x2 r;
-  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
-  return r;
-}
-__device__ __forceinline__ f32x2 mul2(f32x2 a, f32x2 b) {
-  f32x2 r;
-  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
-  return r;
-}
 // gelu_fast / gelu_grad_fast on a pair (identical arithmetic, element-wise)
 __device__ __forceinline__ f32x2 gelu_fast2(f32x2 x) {
   const f32x2 c1 = pack2(0.0356774081f, 0.0356774081f), c0 = pack2(0.7978845608f, 0.7978845608f);
