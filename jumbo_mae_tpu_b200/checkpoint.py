@@ -1,0 +1,129 @@
+"""Parameter checkpoints in the reference's wire format (Flax msgpack).
+
+The reference saves ``msgpack_serialize(unreplicate(state.params))`` to ``<name>-last.msgpack`` /
+``<name>-best.msgpack`` (src/main_pretrain.py:80-88, src/utils.py:55-63) and fine-tuning reads such a file back
+with ``flax.serialization.msgpack_restore`` (src/utils.py:150-152).  Flax is not importable here, so this module
+restates the published wire format of ``flax.serialization`` (flax 0.8.x, unchanged since 0.3):
+
+  * the pytree is a msgpack map of str -> (map | leaf);
+  * an ndarray leaf is ``ExtType(1, packb((shape, dtype.name, C-order bytes), use_bin_type=True))``;
+  * numpy scalars are ``ExtType(3, <same triple>)``, Python complex ``ExtType(2, packb((re, im)))``;
+  * arrays above 2**30 bytes are split into a map
+    ``{"__msgpack_chunked_array__": True, "shape": [...], "chunks": {"0": ext, "1": ext, ...}}`` of flat pieces.
+
+With it, weights move between the reference and this build in both directions: ``state.params`` has the Flax
+names and shapes (params.ParamStore.tree).  SURVEY.md section 8(f) rank 2; host-side only, no kernel involved.
+"""
+from __future__ import annotations
+
+from typing import Any, Dict
+
+import msgpack
+import numpy as np
+
+EXT_NDARRAY, EXT_NATIVE_COMPLEX, EXT_NPSCALAR = 1, 2, 3
+MAX_CHUNK_SIZE = 2 ** 30
+_CHUNKED = "__msgpack_chunked_array__"
+
+
+def _ndarray_to_bytes(arr: np.ndarray) -> bytes:
+    if arr.dtype.hasobject or arr.dtype.isalignedstruct:
+        raise ValueError("object and structured arrays cannot be serialised")
+    return msgpack.packb((list(arr.shape), arr.dtype.name, arr.tobytes("C")), use_bin_type=True)
+
+
+def _ndarray_from_bytes(data: bytes) -> np.ndarray:
+    shape, dtype_name, buffer = msgpack.unpackb(data, raw=True)
+    name = dtype_name.decode() if isinstance(dtype_name, bytes) else dtype_name
+    if name == "bfloat16":
+        raise ValueError("bfloat16 leaves are not supported by this reader (the reference stores f32 parameters)")
+    return np.frombuffer(buffer, dtype=np.dtype(name)).reshape(shape).copy()
+
+
+def _ext_pack(x: Any):
+    if isinstance(x, np.ndarray):
+        return msgpack.ExtType(EXT_NDARRAY, _ndarray_to_bytes(x))
+    if isinstance(x, np.generic):
+        return msgpack.ExtType(EXT_NPSCALAR, _ndarray_to_bytes(np.asarray(x)))
+    if isinstance(x, complex):
+        return msgpack.ExtType(EXT_NATIVE_COMPLEX, msgpack.packb((x.real, x.imag)))
+    return x
+
+
+def _ext_unpack(code: int, data: bytes):
+    if code == EXT_NDARRAY:
+        return _ndarray_from_bytes(data)
+    if code == EXT_NATIVE_COMPLEX:
+        re, im = msgpack.unpackb(data)
+        return complex(re, im)
+    if code == EXT_NPSCALAR:
+        return _ndarray_from_bytes(data)[()]
+    return msgpack.ExtType(code, data)
+
+
+def _tuple_to_dict(tpl) -> Dict[str, Any]:
+    return {str(i): v for i, v in enumerate(tpl)}
+
+
+def _dict_to_tuple(d: Dict[str, Any]):
+    return tuple(d[str(i)] for i in range(len(d)))
+
+
+def _chunk(arr: np.ndarray) -> Dict[str, Any]:
+    chunksize = max(1, int(MAX_CHUNK_SIZE / arr.dtype.itemsize))
+    flat = arr.reshape(-1)
+    chunks = [flat[i:i + chunksize] for i in range(0, flat.size, chunksize)]
+    return {_CHUNKED: True, "shape": _tuple_to_dict(arr.shape), "chunks": _tuple_to_dict(chunks)}
+
+
+def _prepare(tree: Any) -> Any:
+    """torch tensors / array-likes -> C-contiguous numpy leaves, oversize leaves chunked."""
+    if isinstance(tree, dict):
+        return {str(k): _prepare(v) for k, v in tree.items()}
+    if hasattr(tree, "detach"):                      # torch.Tensor (possibly a strided device view)
+        tree = tree.detach().to("cpu").contiguous().numpy()
+    if isinstance(tree, np.ndarray):
+        arr = tree if tree.flags.c_contiguous else np.ascontiguousarray(tree)   # (ascontiguousarray makes 0-d 1-d)
+        return _chunk(arr) if arr.size * arr.dtype.itemsize > MAX_CHUNK_SIZE else arr
+    return tree
+
+
+def _unchunk(tree: Any) -> Any:
+    if isinstance(tree, dict):
+        if tree.get(_CHUNKED, False):
+            shape = _dict_to_tuple(tree["shape"])
+            return np.concatenate(_dict_to_tuple(tree["chunks"])).reshape(shape)
+        return {k: _unchunk(v) for k, v in tree.items()}
+    return tree
+
+
+def msgpack_serialize(pytree: Any) -> bytes:
+    """flax.serialization.msgpack_serialize for dict pytrees of arrays (src/main_pretrain.py:83)."""
+    return msgpack.packb(_prepare(pytree), default=_ext_pack, strict_types=True)
+
+
+def msgpack_restore(encoded: bytes) -> Any:
+    """flax.serialization.msgpack_restore (src/utils.py:151): nested dicts of numpy arrays."""
+    return _unchunk(msgpack.unpackb(encoded, ext_hook=_ext_unpack, raw=False, strict_map_key=False))
+
+
+# ----------------------------------------------------------------------------- train-state helpers
+def save_params(state, path: str) -> None:
+    """Writes ``state.params`` as the reference does (``<name>-last.msgpack``, src/utils.py:55-63)."""
+    data = msgpack_serialize(state.params)
+    with open(path, "wb") as f:
+        f.write(data)
+
+
+def load_params(state, path: str) -> None:
+    """Loads a parameter file written by the reference (or by ``save_params``) into ``state``: every leaf of the
+    model must be present with the Flax shape; the bf16 compute copy is refreshed."""
+    with open(path, "rb") as f:
+        tree = msgpack_restore(f.read())
+    if set(tree.keys()) == {"params"}:               # a whole Flax variable dict rather than its "params" entry
+        tree = tree["params"]
+    import torch
+
+    def to_torch(t):
+        return {k: to_torch(v) for k, v in t.items()} if isinstance(t, dict) else torch.from_numpy(np.asarray(t))
+    state.store.load_tree(to_torch(tree))
