@@ -96,6 +96,51 @@ class TrainState:
             self.engines[batch] = MAEEngine(self.cfg, self.store, batch)
         return self.engines[batch]
 
+    def prefetch(self, batch):
+        """Starts the host-to-device copy of the NEXT batch on a copy stream, so that it overlaps the step that
+        is running (the reference's ``shard(batch)`` + XLA's asynchronous dispatch give it
+        the same overlap, src/main_pretrain.py:61-64).  ``batch`` is ``(images,)`` with uint8 images in pinned
+        host memory; returns the device-side ``(images,)`` to hand to ``training_step``.  Two staging buffers
+        alternate; a buffer is rewritten only after the step that consumed it has copied it out."""
+        images = batch[0] if isinstance(batch, (tuple, list)) else batch
+        if images.is_cuda:
+            return (images,)
+        dev = self.store.device
+        if not hasattr(self, "_stage"):
+            self._stage = {"stream": torch.cuda.Stream(device=dev), "bufs": {}, "next": 0, "ready": {}, "freed": {}}
+        st = self._stage
+        key = (tuple(images.shape), st["next"])
+        st["next"] ^= 1
+        if key not in st["bufs"]:
+            st["bufs"][key] = torch.empty(images.shape, dtype=torch.uint8, device=dev)
+        buf = st["bufs"][key]
+        with torch.cuda.stream(st["stream"]):
+            freed = st["freed"].pop(buf.data_ptr(), None)
+            if freed is not None:
+                st["stream"].wait_event(freed)          # the step that read this buffer has copied it out
+            buf.copy_(images, non_blocking=True)
+            ev = torch.cuda.Event()
+            ev.record(st["stream"])
+        st["ready"][buf.data_ptr()] = ev
+        return (buf,)
+
+    def _consume_prefetched(self, images: torch.Tensor) -> None:
+        """Orders the compute stream after the copy that filled a prefetched buffer."""
+        st = getattr(self, "_stage", None)
+        if st is None:
+            return
+        ev = st["ready"].pop(images.data_ptr(), None)
+        if ev is not None:
+            torch.cuda.current_stream().wait_event(ev)
+
+    def _release_prefetched(self, images: torch.Tensor) -> None:
+        st = getattr(self, "_stage", None)
+        if st is None or not any(b.data_ptr() == images.data_ptr() for b in st["bufs"].values()):
+            return
+        ev = torch.cuda.Event()
+        ev.record()
+        st["freed"][images.data_ptr()] = ev
+
 
 def create_train_state(args: argparse.Namespace) -> TrainState:
     """src/pretraining.py:170-270: builds the modules from the CLI namespace, initialises the
@@ -177,6 +222,7 @@ def training_step(state: TrainState, batch, noise=None) -> Tuple[TrainState, Dic
     nz = torch.from_numpy(np.ascontiguousarray(nz, dtype=np.float32)) if isinstance(nz, np.ndarray) else nz
     nz = nz.to(device=state.store.device, dtype=torch.float32, non_blocking=True)
     eng = state.engine(images.shape[0])
+    state._consume_prefetched(images)
     world = process_count()
     accum = state.micro_in_mini
     if state.reducer is None and world > 1:
@@ -193,6 +239,7 @@ def training_step(state: TrainState, batch, noise=None) -> Tuple[TrainState, Dic
     else:
         loss = eng.forward(images, nz, want_grad=True)
         eng.backward(zero_grads=first_micro)
+    state._release_prefetched(images)
     metrics_loss = loss.clone()
     if world > 1:
         state.reducer.mean_scalar(metrics_loss)                      # lax.pmean(metrics) (:144)

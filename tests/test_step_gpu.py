@@ -243,3 +243,31 @@ def test_segmented_backward_graphs_equal_whole_backward():
     assert (store.g - g_ref).norm().item() <= 2e-3 * g_ref.norm().item()   # L2 reduction order, see above
     assert torch.isfinite(loss).all()
     assert eng.num_bwd_segments() == 1 + (cfg.layers + eng.ENC_LAYERS_PER_SEGMENT - 1) // eng.ENC_LAYERS_PER_SEGMENT
+
+
+def test_prefetched_batches_give_the_same_step():
+    """TrainState.prefetch (copy stream + staging buffers) feeds training_step the same data as a direct call."""
+    from jumbo_mae_tpu_b200.pretraining import create_train_state, training_step
+    ocfg = O.tiny()
+    ostate = O.create_state(ocfg, seed=0, randomize_all=True)
+    images, noise = O.synthetic_batch(ocfg, 4, seed=5, noise_seed=6)
+    host = [images.pin_memory(), torch.flip(images, dims=[0]).contiguous().pin_memory(), images.pin_memory()]
+
+    def run(prefetch):
+        state = create_train_state(_tiny_args()).replicate()
+        state.store.load_tree(ostate.params)
+        losses = []
+        nxt = state.prefetch((host[0],)) if prefetch else (host[0],)
+        for i in range(len(host)):
+            cur = nxt
+            state, m = training_step(state, cur, noise=noise)
+            if i + 1 < len(host):
+                nxt = state.prefetch((host[i + 1],)) if prefetch else (host[i + 1],)
+            losses.append(m["loss"].item())
+        return losses, state.store.p.clone()
+
+    want, p_want = run(False)
+    got, p_got = run(True)
+    for a, b in zip(want, got):
+        assert abs(a - b) <= 1e-5 * abs(a)
+    assert (p_got - p_want).norm().item() <= 1e-3 * p_want.norm().item() * 1e-2 + 1e-6
