@@ -198,6 +198,12 @@ int jm_adamw(float* p, const float* g, float* m, float* v, jm_bf16* p_bf16, long
 
 int jm_cast_bf16(const float* x, jm_bf16* y, long n, void* stream);
 
+/* optax.clip_by_global_norm in front of the optimizer (src/pretraining.py:243-244, --clip-grad > 0): with
+ * norm = pre_scale * ||g||_2 over the whole flat gradient buffer (pre_scale = 1/(accum*world), the factor the
+ * caller folds into jm_adamw), g is left unchanged if norm < max_norm and multiplied by max_norm / norm
+ * otherwise.  sumsq: one device float, receives sum(g^2) of the unscaled buffer. */
+int jm_clip_by_global_norm(float* g, long n, float pre_scale, float max_norm, float* sumsq, void* stream);
+
 /* dst = src + bias (bias optional) over a strided [rows, cols] f32 view (cols, lds, ldd multiples of 4), written
  * as f32 and/or bf16.  Seeds the output of a split-K GEMM with residual + bias (Jumbo MLP output,
  * src/modeling.py:199) and converts an f32 gradient for a bf16 consumer.  No reference counterpart: XLA fuses

@@ -1099,3 +1099,52 @@ extern "C" int jm_add_bias_cast(const float* src, long lds, int rows, int cols, 
   JM_AFTER_LAUNCH();
   return 0;
 }
+
+// ---------------------------------------------------------------- gradient clipping
+// optax.clip_by_global_norm (src/pretraining.py:243-244) over the flat gradient buffer: one pass for the sum
+// of squares, one pass that rescales in place if the norm (of pre_scale * g) reaches max_norm.
+namespace jm {
+__global__ void __launch_bounds__(256)
+sumsq_kernel(const float* __restrict__ g, long n4, float* __restrict__ out) {
+  __shared__ float red[32];
+  float acc = 0.f;
+  for (long i = blockIdx.x * static_cast<long>(blockDim.x) + threadIdx.x; i < n4;
+       i += static_cast<long>(gridDim.x) * blockDim.x) {
+    const float4 v = reinterpret_cast<const float4*>(g)[i];
+    acc += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
+  }
+  const float tot = block_sum(acc, red);
+  if (threadIdx.x == 0) atomicAdd(out, tot);
+}
+
+__global__ void __launch_bounds__(256)
+clip_scale_kernel(float* __restrict__ g, long n4, const float* __restrict__ sumsq, float pre_scale, float max_norm) {
+  const float norm = sqrtf(*sumsq) * pre_scale;
+  if (norm < max_norm) return;  // optax: unchanged below the threshold
+  const float f = max_norm / norm;
+  for (long i = blockIdx.x * static_cast<long>(blockDim.x) + threadIdx.x; i < n4;
+       i += static_cast<long>(gridDim.x) * blockDim.x) {
+    float4 v = reinterpret_cast<float4*>(g)[i];
+    v.x *= f, v.y *= f, v.z *= f, v.w *= f;
+    reinterpret_cast<float4*>(g)[i] = v;
+  }
+}
+}  // namespace jm
+
+extern "C" int jm_clip_by_global_norm(float* g, long n, float pre_scale, float max_norm, float* sumsq, void* stream) {
+  using namespace jm;
+  JM_CHECK(g && sumsq, "jm_clip_by_global_norm: null argument");
+  JM_CHECK(n % 4 == 0 && (reinterpret_cast<uintptr_t>(g) & 15) == 0, "jm_clip_by_global_norm: n must be a multiple of 4, g 16-byte aligned");
+  JM_CHECK(max_norm > 0.f && pre_scale > 0.f, "jm_clip_by_global_norm: max_norm and pre_scale must be positive");
+  if (n == 0) return 0;
+  const long n4 = n / 4;
+  long blocks = (n4 + 255) / 256;
+  const long cap = static_cast<long>(sm_count()) * 8;
+  if (blocks > cap) blocks = cap;
+  JM_CUDA(cudaMemsetAsync(sumsq, 0, sizeof(float), STREAM));
+  sumsq_kernel<<<static_cast<int>(blocks), 256, 0, STREAM>>>(g, n4, sumsq);
+  JM_AFTER_LAUNCH();
+  clip_scale_kernel<<<static_cast<int>(blocks), 256, 0, STREAM>>>(g, n4, sumsq, pre_scale, max_norm);
+  JM_AFTER_LAUNCH();
+  return 0;
+}

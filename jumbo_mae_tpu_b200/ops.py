@@ -256,3 +256,9 @@ def add_bias_cast(src: torch.Tensor, rows: int, cols: int, bias: Optional[torch.
     check(_lib.load().jm_add_bias_cast(ptr(src), lds if lds is not None else cols, rows, cols, ptr(bias), ptr(dst_f32),
                                        ldd if ldd is not None else cols, ptr(dst_bf16),
                                        ldd16 if ldd16 is not None else cols, stream_ptr()))
+
+
+def clip_by_global_norm(g: torch.Tensor, pre_scale: float, max_norm: float, sumsq: torch.Tensor) -> None:
+    """In-place optax.clip_by_global_norm of the flat gradient buffer (jm_clip_by_global_norm)."""
+    _chk(g, F32, "g"), _chk(sumsq, F32, "sumsq")
+    check(_lib.load().jm_clip_by_global_norm(ptr(g), g.numel(), pre_scale, max_norm, ptr(sumsq), stream_ptr()))

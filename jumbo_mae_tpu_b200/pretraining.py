@@ -18,7 +18,7 @@ from typing import Any, Dict, Optional, Tuple
 import numpy as np
 import torch
 
-from . import _lib
+from . import _lib, ops
 from .config import MAEConfig
 from .engine import MAEEngine, lr_schedule
 from .modeling import MAEDecoder, ViT
@@ -63,6 +63,7 @@ class TrainState:
     engines: Dict[int, MAEEngine] = field(default_factory=dict)
     reducer: Optional[GradReducer] = None
     _noise_gen: Optional[np.random.Generator] = None
+    clip_grad: float = 0.0      # --clip-grad: optax.clip_by_global_norm in front of adamw (src/pretraining.py:243-244)
 
     @property
     def params(self) -> dict:
@@ -149,8 +150,8 @@ def create_train_state(args: argparse.Namespace) -> TrainState:
     _lib.require_device()
     if getattr(args, "optimizer", "adamw") != "adamw":
         raise NotImplementedError("only --optimizer adamw (both pre-training presets) is on the hot path")
-    if getattr(args, "lr_decay", 1.0) < 1.0 or getattr(args, "clip_grad", 0.0) > 0:
-        raise NotImplementedError("--lr-decay < 1 and --clip-grad > 0 are inactive at the pre-training presets")
+    if getattr(args, "lr_decay", 1.0) < 1.0:
+        raise NotImplementedError("--lr-decay < 1 (layer-wise decay, a fine-tuning option) is not built")
     for nm in ("dropout", "droppath", "dec_dropout", "dec_droppath"):
         if getattr(args, nm, 0.0) != 0.0:
             raise NotImplementedError(f"--{nm.replace('_', '-')} > 0 is not built (0.0 in both presets)")
@@ -175,7 +176,7 @@ def create_train_state(args: argparse.Namespace) -> TrainState:
                       mixup_rng=getattr(args, "mixup_seed", 0) + process_index(),
                       dropout_rng=getattr(args, "dropout_seed", 0) + process_index(),
                       noise_rng=getattr(args, "noise_seed", 0) + process_index(),
-                      micro_step=0, micro_in_mini=cfg.grad_accum)
+                      micro_step=0, micro_in_mini=cfg.grad_accum, clip_grad=float(getattr(args, "clip_grad", 0.0)))
 
 
 def init_params_(store: ParamStore, seed: int) -> None:
@@ -248,6 +249,10 @@ def training_step(state: TrainState, batch, noise=None) -> Tuple[TrainState, Dic
     if state.micro_step == accum:                                    # :149-158
         if world > 1 and not reduced:
             state.reducer.all_reduce_grads()                         # lax.pmean(grads) (:150); 1/world below
+        if state.clip_grad > 0:                                      # chain(clip_by_global_norm, adamw) (:243-244)
+            if not hasattr(state, "_sumsq"):
+                state._sumsq = torch.zeros(1, dtype=torch.float32, device=state.store.device)
+            ops.clip_by_global_norm(state.store.g, 1.0 / (accum * world), state.clip_grad, state._sumsq)
         eng.adamw_step(state.step, lr, grad_scale=1.0 / (accum * world))
         state.step += 1
         state.micro_step = 0

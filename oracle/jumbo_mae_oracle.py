@@ -59,6 +59,7 @@ class MAEConfig:
     learning_rate: float = 1.5e-4
     train_batch_size: int = 4096
     weight_decay: float = 0.05
+    clip_grad: float = 0.0           # optax.clip_by_global_norm in front of adamw when > 0 (src/pretraining.py:243-244)
     adam_b1: float = 0.9
     adam_b2: float = 0.95
     adam_eps: float = 1e-8
@@ -528,6 +529,11 @@ def training_step(state: OracleState, images_u8, noise, grads_override: Tree | N
     if grads_override is not None:
         grads = grads_override
     lr = lr_schedule(state.step, cfg)
+    if cfg.clip_grad > 0:
+        # optax.clip_by_global_norm: g unchanged if ||g|| < max_norm, else g / ||g|| * max_norm (all leaves together)
+        g_norm = torch.sqrt(sum((g.double() ** 2).sum() for _, g in tree_leaves(grads))).float()
+        if not bool(g_norm < cfg.clip_grad):
+            grads = tree_map(lambda g: (g / g_norm) * cfg.clip_grad, grads)
     new_p, new_m, new_v = {}, {}, {}
 
     def upd(p, g, m, v, path):

@@ -555,3 +555,21 @@ def test_add_bias_cast_strided(ops):
     assert torch.equal(d16[:, :cols], want.to(BF16)) and torch.equal(d16[:, cols:], torch.full_like(d16[:, cols:], 9.0))
     ops.add_bias_cast(src, rows, cols, dst_bf16=d16, lds=lds, ldd16=ldd16)
     assert torch.equal(d16[:, :cols], src[:, :cols].to(BF16))
+
+
+@pytest.mark.parametrize("max_norm", [0.5, 1e6])
+def test_clip_by_global_norm(ops, max_norm):
+    """jm_clip_by_global_norm against optax's rule: unchanged below the threshold, g / ||g|| * max_norm above."""
+    g = torch.Generator(device="cuda").manual_seed(3)
+    x = torch.randn(1 << 20, generator=g, device="cuda")
+    pre = 0.25
+    want_norm = (x.double() * pre).norm().item()
+    y = x.clone()
+    ss = torch.full((1,), 7.0, device="cuda")
+    ops.clip_by_global_norm(y, pre, max_norm, ss)
+    assert abs(ss.item() - (x.double() ** 2).sum().item()) <= 1e-5 * ss.item()
+    if want_norm < max_norm:
+        assert torch.equal(y, x)
+    else:
+        assert torch.allclose(y, x * (max_norm / want_norm), rtol=1e-5, atol=0)
+        assert abs((y.double() * pre).norm().item() - max_norm) <= 1e-5 * max_norm

@@ -271,3 +271,32 @@ def test_prefetched_batches_give_the_same_step():
     for a, b in zip(want, got):
         assert abs(a - b) <= 1e-5 * abs(a)
     assert (p_got - p_want).norm().item() <= 1e-3 * p_want.norm().item() * 1e-2 + 1e-6
+
+
+def test_training_step_with_gradient_clipping_matches_oracle():
+    """--clip-grad > 0: chain(clip_by_global_norm, adamw) (src/pretraining.py:243-244), threshold low enough to bind."""
+    import dataclasses
+    from jumbo_mae_tpu_b200.pretraining import create_train_state, training_step
+    from jumbo_mae_tpu_b200.params import tree_leaves
+    ocfg = dataclasses.replace(O.tiny(), clip_grad=0.05)
+    ostate = O.create_state(ocfg, seed=0, randomize_all=True)
+    images, noise = O.synthetic_batch(ocfg, 4, seed=5, noise_seed=6)
+    _, grads = O.loss_and_grads(ostate.params, images, noise, ocfg)
+    gnorm = torch.sqrt(sum((g.double() ** 2).sum() for _, g in O.tree_leaves(grads))).item()
+    assert gnorm > 2 * ocfg.clip_grad                       # the clip is active in this test
+    want_state, _, _ = O.training_step(ostate, images, noise)
+    unclipped_state, _, _ = O.training_step(dataclasses.replace(ostate, cfg=dataclasses.replace(ocfg, clip_grad=0.0)),
+                                            images, noise)
+    state = create_train_state(_tiny_args(clip_grad=0.05)).replicate()
+    state.store.load_tree(ostate.params)
+    state, _ = training_step(state, (images.pin_memory(),), noise=noise)
+    assert abs(state._sumsq.sqrt().item() - gnorm) <= 3e-2 * gnorm
+    # Adam's first step moves every parameter by ~lr * sign(g) whatever the gradient scale, so the parameters barely
+    # see the clip; the first moment does: mu = (1 - b1) * clipped g
+    got_mu = dict(tree_leaves(state.opt_state["mu"]))
+    leaves = [(p, w) for p, w in O.tree_leaves(want_state.mu) if p[-2:] != ("wk", "bias")]
+    want = torch.cat([w.flatten() for _, w in leaves])
+    got = torch.cat([got_mu[p].detach().cpu().reshape(w.shape).flatten() for p, w in leaves])
+    unclipped = torch.cat([dict(O.tree_leaves(unclipped_state.mu))[p].flatten() for p, _ in leaves])
+    assert _rel(got, want) <= 3e-2
+    assert _rel(unclipped, want) > 0.5                      # and the oracle without the clip is far away
