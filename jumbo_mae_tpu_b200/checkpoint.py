@@ -127,3 +127,67 @@ def load_params(state, path: str) -> None:
     def to_torch(t):
         return {k: to_torch(v) for k, v in t.items()} if isinstance(t, dict) else torch.from_numpy(np.asarray(t))
     state.store.load_tree(to_torch(tree))
+
+
+def save_state(state, path: str) -> None:
+    """Everything a run needs to resume (the reference saves parameters only and cannot): parameters, both Adam
+    moments, the step / micro-step counters, an in-flight gradient accumulator and the RNG stream seeds, as
+    one msgpack file in the same leaf encoding."""
+    tree = {
+        "params": state.params,
+        "opt_state": {"mu": state.opt_state["mu"], "nu": state.opt_state["nu"]},
+        "step": np.int64(state.step), "micro_step": np.int64(state.micro_step),
+        "rngs": {"mixup": np.int64(state.mixup_rng), "dropout": np.int64(state.dropout_rng),
+                 "noise": np.int64(state.noise_rng)},
+    }
+    if state.micro_step > 0:
+        tree["grad_accum"] = state.store.tree(state.store.g)
+    noise_gen = getattr(state, "_noise_gen", None)
+    if noise_gen is not None:                      # position of this rank's mask-noise stream (Philox counter state)
+        st = noise_gen.bit_generator.state
+        tree["noise_stream"] = {"counter": np.asarray(st["state"]["counter"], dtype=np.uint64),
+                                "key": np.asarray(st["state"]["key"], dtype=np.uint64),
+                                "buffer": np.asarray(st["buffer"], dtype=np.uint64),
+                                "buffer_pos": np.int64(st["buffer_pos"]), "has_uint32": np.int64(st["has_uint32"]),
+                                "uinteger": np.int64(st["uinteger"])}
+    with open(path, "wb") as f:
+        f.write(msgpack_serialize(tree))
+
+
+def load_state(state, path: str) -> None:
+    """Inverse of ``save_state`` into a state built by ``create_train_state`` with the same arguments."""
+    import torch
+    with open(path, "rb") as f:
+        tree = msgpack_restore(f.read())
+
+    def to_torch(t):
+        return {k: to_torch(v) for k, v in t.items()} if isinstance(t, dict) else torch.from_numpy(np.asarray(t))
+
+    store = state.store
+    store.load_tree(to_torch(tree["params"]))
+
+    def fill(buf, src):
+        def walk(dst, s):
+            for k, v in dst.items():
+                if isinstance(v, dict):
+                    walk(v, s[k])
+                else:
+                    v.copy_(torch.from_numpy(np.asarray(s[k])).to(v.device).reshape(v.shape))
+        walk(store.tree(buf), src)
+    fill(store.m, tree["opt_state"]["mu"])
+    fill(store.v, tree["opt_state"]["nu"])
+    state.step, state.micro_step = int(tree["step"]), int(tree["micro_step"])
+    if "grad_accum" in tree:
+        fill(store.g, tree["grad_accum"])
+    state.mixup_rng, state.dropout_rng = int(tree["rngs"]["mixup"]), int(tree["rngs"]["dropout"])
+    state.noise_rng = int(tree["rngs"]["noise"])
+    if "noise_stream" in tree:
+        ns = tree["noise_stream"]
+        gen = np.random.Generator(np.random.Philox(key=0))
+        st = gen.bit_generator.state
+        st["state"]["counter"] = np.asarray(ns["counter"], dtype=np.uint64)
+        st["state"]["key"] = np.asarray(ns["key"], dtype=np.uint64)
+        st["buffer"] = np.asarray(ns["buffer"], dtype=np.uint64)
+        st["buffer_pos"], st["has_uint32"], st["uinteger"] = int(ns["buffer_pos"]), int(ns["has_uint32"]), int(ns["uinteger"])
+        gen.bit_generator.state = st
+        state._noise_gen = gen

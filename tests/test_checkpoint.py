@@ -78,3 +78,34 @@ def test_train_state_save_and_load(tmp_path):
     tree = C.msgpack_restore(open(path, "rb").read())
     assert tree["model"]["layer_0"]["attn"]["wq"]["kernel"].shape == (64, 2, 32)        # Flax DenseGeneral shapes
     assert tree["model"]["embed"]["wte"]["kernel"].shape == (16, 16, 3, 64)
+
+
+@pytest.mark.gpu
+def test_resume_reproduces_the_run(tmp_path):
+    """save_state / load_state: a run resumed after 2 steps continues exactly like the uninterrupted one (same
+    parameters, moments, step counter and mask-noise stream)."""
+    import bench
+    from jumbo_mae_tpu_b200.pretraining import create_train_state, training_step
+    args = bench.preset_args("vit_b16", 8)
+    args.layers, args.dim, args.heads, args.dec_layers, args.dec_dim, args.dec_heads = 2, 64, 2, 1, 64, 2
+    g = torch.Generator().manual_seed(0)
+    batches = [torch.randint(0, 256, (8, 3, 224, 224), generator=g, dtype=torch.uint8) for _ in range(4)]
+    a = create_train_state(args).replicate()
+    for b in batches[:2]:
+        a, _ = training_step(a, (b,))
+    path = str(tmp_path / "resume.msgpack")
+    C.save_state(a, path)
+    losses_a = []
+    for b in batches[2:]:
+        a, m = training_step(a, (b,))
+        losses_a.append(m["loss"].item())
+    r = create_train_state(args).replicate()
+    C.load_state(r, path)
+    assert r.step == 2
+    losses_r = []
+    for b in batches[2:]:
+        r, m = training_step(r, (b,))
+        losses_r.append(m["loss"].item())
+    for x, y in zip(losses_a, losses_r):
+        assert abs(x - y) <= 1e-4 * abs(x)            # same masks (noise stream restored), same weights
+    assert (a.store.p - r.store.p).norm().item() <= 1e-4 * a.store.p.norm().item()
