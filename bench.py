@@ -216,9 +216,16 @@ def run_ours(args):
         eng.capture_segment_graphs()
 
     def resident_step():
+        updated = False
         for i in range(accum):
             if use_graph and reducer is not None and i == accum - 1:
-                eng.run_graph_overlapped(dev_images[i], dev_noise[counter["micro"] % total_micro], i == 0, reducer)
+                # as training_step does: all-reduce AND AdamW of each backward segment overlap the next segment
+                cnt, lr_now = counter["step"], lr_schedule(counter["step"], cfg)
+                hook = ((lambda ranges: eng.adamw_ranges(ranges, cnt, lr_now, grad_scale=1.0 / (accum * world)))
+                        if reducer.stream is not None else None)
+                eng.run_graph_overlapped(dev_images[i], dev_noise[counter["micro"] % total_micro], i == 0, reducer,
+                                         after_reduce=hook)
+                updated = hook is not None
             elif use_graph:
                 eng.run_graph(dev_images[i], dev_noise[counter["micro"] % total_micro], zero_grads=(i == 0))
             else:
@@ -227,7 +234,8 @@ def run_ours(args):
             counter["micro"] += 1
         if reducer is not None and not use_graph:
             reducer.all_reduce_grads()
-        eng.adamw_step(counter["step"], lr_schedule(counter["step"], cfg), grad_scale=1.0 / (accum * world))
+        if not updated:
+            eng.adamw_step(counter["step"], lr_schedule(counter["step"], cfg), grad_scale=1.0 / (accum * world))
         counter["step"] += 1
 
     def timed(fn, steps):

@@ -408,7 +408,8 @@ class MAEEngine:
             self.seg_graphs[zero] = graphs
         self.ps.g.zero_()
 
-    def run_graph_overlapped(self, images: torch.Tensor, noise: torch.Tensor, zero_grads: bool, reducer) -> torch.Tensor:
+    def run_graph_overlapped(self, images: torch.Tensor, noise: torch.Tensor, zero_grads: bool, reducer,
+                             after_reduce=None) -> torch.Tensor:
         """Last micro-step of a data-parallel optimizer step: every backward segment is followed by the
         all-reduce of the gradients it finalised, on the reducer's stream, overlapping the next segment."""
         if not hasattr(self, "seg_graphs"):
@@ -419,7 +420,11 @@ class MAEEngine:
             g.replay()
             ev = torch.cuda.Event()
             ev.record()
-            reducer.all_reduce_ranges(self.segment_grad_ranges(k), after_event=ev)
+            ranges = self.segment_grad_ranges(k)
+            reducer.all_reduce_ranges(ranges, after_event=ev)
+            if after_reduce is not None and reducer.stream is not None:
+                with torch.cuda.stream(reducer.stream):      # e.g. the optimizer update of exactly these ranges
+                    after_reduce(ranges)
         reducer.join()
         return self.loss
 
@@ -439,6 +444,17 @@ class MAEEngine:
         t = count + 1
         ops.adamw(ps.p, ps.g, ps.m, ps.v, ps.p16, ps.n_decay, lr, cfg.adam_b1, cfg.adam_b2, cfg.adam_eps,
                   cfg.weight_decay, 1.0 - cfg.adam_b1 ** t, 1.0 - cfg.adam_b2 ** t, grad_scale)
+
+    def adamw_ranges(self, ranges, count: int, lr: float, grad_scale: float = 1.0) -> None:
+        """The same update restricted to [start, end) ranges of the flat buffers (multiples of 64 elements): lets
+        a data-parallel step update the parameters of a backward segment as soon as its gradients are reduced,
+        while the remaining segments still compute (they no longer read those parameters)."""
+        cfg, ps = self.cfg, self.ps
+        t = count + 1
+        for s, e in ranges:
+            nd = min(max(ps.n_decay - s, 0), e - s)
+            ops.adamw(ps.p[s:e], ps.g[s:e], ps.m[s:e], ps.v[s:e], ps.p16[s:e], nd, lr, cfg.adam_b1, cfg.adam_b2,
+                      cfg.adam_eps, cfg.weight_decay, 1.0 - cfg.adam_b1 ** t, 1.0 - cfg.adam_b2 ** t, grad_scale)
 
     # ------------------------------------------------------------------ accounting
     def activation_bytes(self) -> int:

@@ -230,10 +230,16 @@ def training_step(state: TrainState, batch, noise=None) -> Tuple[TrainState, Dic
         state.reducer = GradReducer(state.store)
     first_micro = state.micro_step == 0
     last_micro = state.micro_step + 1 == accum
-    reduced = False
+    reduced = updated = False
     if USE_CUDA_GRAPH and world > 1 and last_micro:
-        # gradient all-reduce overlapped with the backward pass (lax.pmean(grads), :150)
-        loss = eng.run_graph_overlapped(images, nz, first_micro, state.reducer)
+        # gradient all-reduce overlapped with the backward pass (lax.pmean(grads), :150); without gradient clipping
+        # (which needs the global norm) each segment's parameters are also updated as soon as its sum has arrived
+        hook = None
+        if state.clip_grad == 0 and state.reducer.stream is not None:
+            lr_now, cnt = lr_schedule(state.step, state.cfg), state.step
+            hook = lambda ranges: eng.adamw_ranges(ranges, cnt, lr_now, grad_scale=1.0 / (accum * world))
+            updated = True
+        loss = eng.run_graph_overlapped(images, nz, first_micro, state.reducer, after_reduce=hook)
         reduced = True
     elif USE_CUDA_GRAPH:
         loss = eng.run_graph(images, nz, zero_grads=first_micro)
@@ -253,7 +259,8 @@ def training_step(state: TrainState, batch, noise=None) -> Tuple[TrainState, Dic
             if not hasattr(state, "_sumsq"):
                 state._sumsq = torch.zeros(1, dtype=torch.float32, device=state.store.device)
             ops.clip_by_global_norm(state.store.g, 1.0 / (accum * world), state.clip_grad, state._sumsq)
-        eng.adamw_step(state.step, lr, grad_scale=1.0 / (accum * world))
+        if not updated:
+            eng.adamw_step(state.step, lr, grad_scale=1.0 / (accum * world))
         state.step += 1
         state.micro_step = 0
     return state, {"loss": metrics_loss[0], "learning_rate": lr}

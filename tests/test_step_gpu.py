@@ -300,3 +300,23 @@ def test_training_step_with_gradient_clipping_matches_oracle():
     unclipped = torch.cat([dict(O.tree_leaves(unclipped_state.mu))[p].flatten() for p, _ in leaves])
     assert _rel(got, want) <= 3e-2
     assert _rel(unclipped, want) > 0.5                      # and the oracle without the clip is far away
+
+
+def test_adamw_by_segment_ranges_equals_whole_buffer_update():
+    """engine.adamw_ranges over the backward segments' ranges (what a data-parallel step runs as each segment's
+    all-reduce finishes) is the same update as one adamw_step over the flat buffers."""
+    ocfg, cfg, state, images, noise, store, eng = _setup("mid")
+    eng.forward(images.cuda(), torch.from_numpy(noise).cuda())
+    eng.backward()
+    p0, m0, v0 = store.p.clone(), store.m.clone(), store.v.clone()
+    eng.adamw_step(3, 1e-3, grad_scale=0.5)
+    want = (store.p.clone(), store.m.clone(), store.v.clone(), store.p16.clone())
+    store.p.copy_(p0), store.m.copy_(m0), store.v.copy_(v0)
+    covered = 0
+    for k in range(eng.num_bwd_segments()):
+        ranges = eng.segment_grad_ranges(k)
+        covered += sum(e - s for s, e in ranges)
+        eng.adamw_ranges(ranges, 3, 1e-3, grad_scale=0.5)
+    assert covered == store.total
+    for a, b in zip(want, (store.p, store.m, store.v, store.p16)):
+        assert torch.equal(a, b)
