@@ -81,7 +81,12 @@ class ClockSampler:
 
     def _read(self):
         for line in self.proc.stdout:
-            self.lines.append(line.strip())
+            self.lines.append((time.time(), line.strip()))
+
+    def mark(self):
+        """Start of a timed region: summary() uses the samples taken from here on (nvidia-smi needs ~0.3 s to
+        deliver its first line, so the sampler itself is started once, before the warm-up steps)."""
+        self.t_mark = time.time()
 
     def stop(self):
         if self.proc is None:
@@ -95,7 +100,11 @@ class ClockSampler:
     def summary(self):
         sm, mx, reasons = [], [], set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for line in self.lines:
+        t_mark = getattr(self, "t_mark", 0.0)
+        lines = [l for t, l in self.lines if t >= t_mark]
+        if not lines:            # region shorter than the sampling period: the latest sample (taken under warm-up load)
+            lines = [l for _, l in self.lines[-1:]]
+        for line in lines:
             parts = [p.strip() for p in line.split(",")]
             if len(parts) < 7:
                 continue
@@ -240,8 +249,7 @@ def run_ours(args):
 
     def timed(fn, steps):
         barrier()
-        sampler = ClockSampler(local)
-        sampler.start()
+        sampler.mark()
         l0 = lib.jm_launch_count()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
@@ -253,13 +261,14 @@ def run_ours(args):
         if use_graph:     # kernels inside a replayed graph are not re-counted by the library: add them
             launches += steps * accum * eng.graph_launches
         ms = e0.elapsed_time(e1)
-        sampler.stop()
         barrier()
         t = torch.tensor([ms], device=dev)
         if world > 1:
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return t.item(), launches, sampler.summary()
 
+    sampler = ClockSampler(local)
+    sampler.start()
     for _ in range(args.warmup):
         resident_step()
     ms, launches, clocks = timed(resident_step, args.steps)
@@ -362,6 +371,7 @@ def run_ours(args):
         line["cpu_baseline"] = {"value": ips, "unit": "images/s", "cores": cores, "kind": "port",
                                 "sample": f"{args.config} MAE step, batch 8, 1 warm-up + 3 timed steps of the f32 "
                                           f"torch-CPU port in oracle/ ({sec:.2f} s/step)"}
+    sampler.stop()
     if rank == 0:
         print(json.dumps(line), flush=True)
     if world > 1:
