@@ -166,6 +166,9 @@ __device__ __forceinline__ void fwd_chunk(const uint32_t (&qf)[HD / 16][4], uint
   }
 }
 
+#ifndef JM_ATTN_FWD32_CTAS
+#define JM_ATTN_FWD32_CTAS 3
+#endif
 #ifndef JM_ATTN_FWD64_CTAS
 #define JM_ATTN_FWD64_CTAS 2  // measured: 79 -> 61 us at T=52 (128 registers, twice the resident CTAs)
 #endif
@@ -173,7 +176,7 @@ __device__ __forceinline__ void fwd_chunk(const uint32_t (&qf)[HD / 16][4], uint
 #define JM_ATTN_BWD64_CTAS 2  // 180 -> 170 us
 #endif
 template <int HD>
-__global__ void __launch_bounds__(256, HD == 32 ? 3 : (HD == 64 ? JM_ATTN_FWD64_CTAS : 1))
+__global__ void __launch_bounds__(256, HD == 32 ? JM_ATTN_FWD32_CTAS : (HD == 64 ? JM_ATTN_FWD64_CTAS : 1))
 attn_fwd_kernel(const __nv_bfloat16* __restrict__ qkv, long ldqkv, int T, int heads,
                                 __nv_bfloat16* __restrict__ out, long ldo, float* __restrict__ lse) {
   pdl_wait();  // programmatic dependent launch: nothing above touches global memory
