@@ -542,7 +542,7 @@ __device__ __forceinline__ void sts128_or_zero(uint32_t addr, uint32_t a, uint32
 //   * the second TMEM load of a 64-column part is in flight while the first half is stored.
 template <int EPI, int BN, int CG, int NBUF>
 __device__ __forceinline__ void epilogue_rows(const EpiParams& ep, const GemmShape& sh, const CUtensorMap* tmO,
-                                              const CUtensorMap* tmO2, uint8_t* sEpi,
+                                              const CUtensorMap* tmO2, uint8_t* sEpi, uint64_t* rbars,
                                               uint64_t* tfull, uint64_t* tempty, uint32_t tmem_base, int warp,
                                               int lane, int total_tiles, int tile0, int tile_step, int m_off) {
   constexpr int NH = (BN == 256) ? 2 : 1;   // 32-column halves per warp
@@ -562,6 +562,31 @@ __device__ __forceinline__ void epilogue_rows(const EpiParams& ep, const GemmSha
   const bool tma = ep.tma_store != 0;  // kernel-uniform
   const bool saved_grad = ep.act >= 3;  // acts 3 / 4: the GELU derivative is stored / consumed directly
   uint32_t buf = 0;                     // byte offset of the staging tile in use (NBUF tiles, used in turn)
+  // GELU backward with TMA stores: the pre-activation (or saved-derivative) tile of each 32-column half arrives in
+  // the staging tile by a TMA load through map o2, issued one half ahead (no global-load instructions at all)
+  const bool tma_aux = (EPI == EPI_GELU_BWD) && tma;
+  uint64_t* rbar = rbars + e * 2;
+  uint32_t rphase = 0, rissued = 0;     // per staging tile: parity to wait for / a load is in flight
+  auto issue_aux = [&](uint32_t bi, int col, int row) {  // warp-uniform
+    if (col < sh.N) {
+      if (lane == 0) {
+        mbar_arrive_expect_tx(&rbar[bi], kStageBytesPerWarp);
+        tma_load_2d(tmO2, &rbar[bi], sEpi + e * (kStageBytesPerWarp * NBUF) + bi * kStageBytesPerWarp, col, row);
+      }
+      rissued |= 1u << bi;
+    }
+  };
+  auto half_origin = [&](int t, int& row_base, int& colp) {
+    const int rem = t % tiles_mn;
+    const int m_blk = rem / sh.num_n, n_blk = rem - m_blk * sh.num_n;
+    row_base = m_blk * (BM * CG) + m_off + q * 32;
+    colp = n_blk * BN + part * (32 * NH);
+  };
+  if (tma_aux && part < PARTS && tile0 < total_tiles) {
+    int rb, cp;
+    half_origin(tile0, rb, cp);
+    issue_aux(0, cp, rb);
+  }
 #ifdef JM_EPI_PROF
   long long pt_tfull = 0, pt_ld = 0, pt_math = 0, pt_flush = 0, pt_free = 0, pt_setup = 0, pt_sts = 0, pt_rel = 0, pt_ldi = 0, pt_half = 0;
   const long long pt_begin = clock64();
@@ -630,7 +655,9 @@ __device__ __forceinline__ void epilogue_rows(const EpiParams& ep, const GemmSha
       sc[h] = colh < ep.col_scale_n ? ep.col_scale : 1.f;
       bs[h] = (has_bias && colh + lane < sh.N) ? __ldg(ep.bias + colh + lane) * sc[h] : 0.f;
     }
-    if constexpr (EPI == EPI_GELU_BWD) load_aux(colp);
+    if constexpr (EPI == EPI_GELU_BWD) {
+      if (!tma_aux) load_aux(colp);
+    }
     EPI_ACC(pt_setup, psu);
     EPI_T(pt0);
     mbar_wait(&tfull[acc], acc_phase);
@@ -694,16 +721,41 @@ __device__ __forceinline__ void epilogue_rows(const EpiParams& ep, const GemmSha
         EPI_ACC(pt_free, ps0);
       };
       uint32_t G[16];
+      if constexpr (EPI == EPI_GELU_BWD) {
+        if (tma_aux) {
+          const uint32_t bi = buf / kStageBytesPerWarp;
+          if (rissued & (1u << bi)) {  // warp-uniform: this half's tile has landed in staging tile bi
+            mbar_wait(&rbar[bi], (rphase >> bi) & 1u);
+            rphase ^= 1u << bi;
+            rissued &= ~(1u << bi);
+          }
+          if constexpr (NBUF == 2) {
+            // fetch the NEXT half's tile into the other staging tile, once the store that last used it has read it
+            if (lane == 0) tma_store_wait_read<0>();
+            __syncwarp();
+            const uint32_t nb = live ? (bi ^ 1u) : bi;  // (a half beyond N uses no tile and does not toggle)
+            if (NH == 2 && h == 0) {
+              issue_aux(nb, colp + 32, row_base);
+            } else if (t + tile_step < total_tiles) {
+              int rb, cp;
+              half_origin(t + tile_step, rb, cp);
+              issue_aux(nb, cp, rb);
+            }
+          }
+        }
+      }
       if (live) {
         if constexpr (EPI == EPI_GELU_BWD) {
-          // pre-activations: coalesced registers -> staging -> row threads; results overwrite them in place
-          staging_free();
+          // pre-activations: (coalesced registers ->) staging -> row threads; results overwrite them in place
+          if (!tma_aux) {
+            staging_free();
 #pragma unroll
-          for (int i = 0; i < 4; ++i)
-            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(co_addr + buf + i * 512), "r"(ax[i].x),
-                         "r"(ax[i].y), "r"(ax[i].z), "r"(ax[i].w)
-                         : "memory");
-          __syncwarp();
+            for (int i = 0; i < 4; ++i)
+              asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(co_addr + buf + i * 512), "r"(ax[i].x),
+                           "r"(ax[i].y), "r"(ax[i].z), "r"(ax[i].w)
+                           : "memory");
+            __syncwarp();
+          }
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
             const uint32_t a = own_addr + buf + ((j ^ own_sw) << 4);
@@ -773,7 +825,9 @@ __device__ __forceinline__ void epilogue_rows(const EpiParams& ep, const GemmSha
       }
       if constexpr (NH == 2) {
         if (h == 0 && colp + 32 < sh.N) {  // both in flight during the stores below
-          if constexpr (EPI == EPI_GELU_BWD) load_aux(colp + 32);
+          if constexpr (EPI == EPI_GELU_BWD) {
+            if (!tma_aux) load_aux(colp + 32);
+          }
           EPI_T(pl1);
           tmem_ld_32x32(t_addr + 32, r[1]);
           EPI_ACC(pt_ldi, pl1);
@@ -817,6 +871,19 @@ __device__ __forceinline__ void epilogue_rows(const EpiParams& ep, const GemmSha
               atomicAdd(reinterpret_cast<float4*>(ep.colsum + col), make_float4(cs[0], cs[1], cs[2], cs[3]));
               atomicAdd(reinterpret_cast<float4*>(ep.colsum + col + 4), make_float4(cs[4], cs[5], cs[6], cs[7]));
             }
+          }
+        }
+      }
+      if constexpr (EPI == EPI_GELU_BWD && NBUF == 1) {
+        if (tma_aux) {  // one staging tile: the next half's tile can only be fetched once this store has read it
+          if (lane == 0) tma_store_wait_read<0>();
+          __syncwarp();
+          if (NH == 2 && h == 0) {
+            issue_aux(0, colp + 32, row_base);
+          } else if (t + tile_step < total_tiles) {
+            int rb, cp;
+            half_origin(t + tile_step, rb, cp);
+            issue_aux(0, cp, rb);
           }
         }
       }
@@ -976,7 +1043,7 @@ __device__ __forceinline__ void run_epilogue(const EpiParams& ep, const GemmShap
                                              uint64_t* tfull, uint64_t* tempty, uint32_t tmem_base, int warp,
                                              int lane, int total_tiles, int tile0, int tile_step, int m_off) {
   if constexpr (EPI == EPI_BF16 || EPI == EPI_GELU_FWD || EPI == EPI_GELU_BWD) {
-    epilogue_rows<EPI, BN, CG, NBUF>(ep, sh, tmO, tmO2, sEpi, tfull, tempty, tmem_base, warp, lane, total_tiles, tile0,
+    epilogue_rows<EPI, BN, CG, NBUF>(ep, sh, tmO, tmO2, sEpi, rbars, tfull, tempty, tmem_base, warp, lane, total_tiles, tile0,
                                      tile_step, m_off);
   } else {
     if constexpr (EPI == EPI_F32) {
@@ -1616,6 +1683,9 @@ extern "C" int jm_gemm(const jm_gemm_args* a, void* stream_) {
     if (make_tmap(&tm.o, ep.out_bf16, a->N, a->M, ep.ldo_bf16, 32, 32, CU_TENSOR_MAP_SWIZZLE_64B)) return 1;
     if (epi == EPI_GELU_FWD &&
         make_tmap(&tm.o2, ep.out2_bf16, a->N, a->M, ep.ldo2_bf16, 32, 32, CU_TENSOR_MAP_SWIZZLE_64B))
+      return 1;
+    if (epi == EPI_GELU_BWD &&  // the pre-activation / saved-derivative tiles come in by TMA as well
+        make_tmap(&tm.o2, ep.aux, a->N, a->M, ep.ldaux, 32, 32, CU_TENSOR_MAP_SWIZZLE_64B))
       return 1;
     ep.tma_store = 1;
   }
