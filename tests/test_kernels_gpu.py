@@ -573,3 +573,33 @@ def test_clip_by_global_norm(ops, max_norm):
     else:
         assert torch.allclose(y, x * (max_norm / want_norm), rtol=1e-5, atol=0)
         assert abs((y.double() * pre).norm().item() - max_norm) <= 1e-5 * max_norm
+
+
+@pytest.mark.parametrize("M,N,K", [(300, 328, 72), (130, 264, 200)])
+def test_gemm_outputs_stay_inside_their_views(ops, M, N, K):
+    """Ragged problems through the TMA-store / TMA-reduce epilogues: nothing outside the [M, N] view of a larger,
+    sentinel-filled buffer is written (rows beyond M, columns beyond N, the gap between row ends and the stride)."""
+    g = torch.Generator(device="cuda").manual_seed(M * N + K)
+    A = torch.randn(M, K, generator=g, device="cuda").to(BF16)
+    W = (torch.randn(K, N, generator=g, device="cuda") * 0.2).to(BF16)
+    bias = torch.randn(N, generator=g, device="cuda")
+    ref = A.float() @ W.float() + bias
+    pad_r, ld = 5, N + 24
+    # bf16 output (TMA store of 32x32 tiles)
+    big = torch.full((M + 2 * pad_r, ld), 7.0, dtype=BF16, device="cuda")
+    out = big[pad_r:pad_r + M, :N]
+    ops.gemm(A, W, M, N, K, b_mn=True, out_bf16=out, bias=bias)
+    assert torch.allclose(out.float(), ref, rtol=2 ** -7, atol=1e-3)
+    mask = torch.ones_like(big, dtype=torch.bool)
+    mask[pad_r:pad_r + M, :N] = False
+    assert torch.all(big[mask] == 7.0)
+    # f32 output with residual (TMA load + store of 32x16 tiles), then accumulation (TMA reduce-add)
+    res = torch.randn(M, N, generator=g, device="cuda")
+    big32 = torch.full((M + 2 * pad_r, ld), 7.0, device="cuda")
+    out32 = big32[pad_r:pad_r + M, :N]
+    ops.gemm(A, W, M, N, K, b_mn=True, out_f32=out32, bias=bias, residual=res)
+    assert torch.allclose(out32, ref + res, rtol=1e-5, atol=1e-4)
+    assert torch.all(big32[mask] == 7.0)
+    ops.gemm(A, W, M, N, K, b_mn=True, out_f32=out32, accumulate=True)
+    assert torch.allclose(out32, ref + res + (ref - bias), rtol=1e-5, atol=2e-4)
+    assert torch.all(big32[mask] == 7.0)
