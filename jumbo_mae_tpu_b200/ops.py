@@ -186,10 +186,7 @@ def attention_bwd(qkv: torch.Tensor, out: torch.Tensor, dout: torch.Tensor, lse:
                   delta_ws: Optional[torch.Tensor] = None, dbias: Optional[torch.Tensor] = None) -> None:
     _chk(qkv, BF16, "qkv"), _chk(out, BF16, "out"), _chk(dout, BF16, "dout"), _chk(lse, F32, "lse")
     _chk(dqkv, BF16, "dqkv"), _chk(delta_ws, F32, "delta_ws"), _chk(dbias, F32, "dbias")
-    if delta_ws is None:
-        delta_ws = torch.empty(batch * heads * T, dtype=F32, device=qkv.device)
-    if delta_ws.numel() < batch * heads * T:
-        raise _lib.JmError("attention_bwd: delta_ws too small")
+    # (delta_ws is unused since the kernel computes rowsum(dout * out) itself; accepted for compatibility)
     check(_lib.load().jm_attention_bwd(ptr(qkv), _ld(qkv), ptr(out), _ld(out), ptr(dout), _ld(dout), ptr(lse),
                                        ptr(delta_ws), batch, T, heads, head_dim, q_scale, ptr(dqkv), _ld(dqkv),
                                        ptr(dbias), stream_ptr()))

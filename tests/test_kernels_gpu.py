@@ -603,3 +603,22 @@ def test_gemm_outputs_stay_inside_their_views(ops, M, N, K):
     ops.gemm(A, W, M, N, K, b_mn=True, out_f32=out32, accumulate=True)
     assert torch.allclose(out32, ref + res + (ref - bias), rtol=1e-5, atol=2e-4)
     assert torch.all(big32[mask] == 7.0)
+
+
+@pytest.mark.parametrize("T,H,hd", [(199, 2, 32), (52, 2, 64), (67, 1, 80)])
+def test_attention_outputs_stay_inside_their_buffers(ops, T, H, hd):
+    """Sequence lengths that are not multiples of the 16-row strips: the padded rows of the last strip and the
+    last image never reach memory (sentinel rows after the end of out / lse / dqkv stay intact)."""
+    B, d, guard = 3, H * hd, 24
+    g = torch.Generator(device="cuda").manual_seed(T)
+    qkv = (torch.randn(B * T + guard, 3 * d, generator=g, device="cuda") * 0.5).to(BF16)
+    dout = torch.randn(B * T + guard, d, generator=g, device="cuda").to(BF16)
+    out = torch.full((B * T + guard, d), 5.0, dtype=BF16, device="cuda")
+    lse = torch.full((B * H * T + guard,), 5.0, device="cuda")
+    dqkv = torch.full((B * T + guard, 3 * d), 5.0, dtype=BF16, device="cuda")
+    ops.attention_fwd(qkv[:B * T], B, T, H, hd, out[:B * T], lse[:B * H * T].view(B, H, T))
+    ops.attention_bwd(qkv[:B * T], out[:B * T], dout[:B * T], lse[:B * H * T].view(B, H, T), B, T, H, hd, hd ** -0.5,
+                      dqkv[:B * T])
+    torch.cuda.synchronize()
+    assert torch.all(out[B * T:] == 5.0) and torch.all(lse[B * H * T:] == 5.0) and torch.all(dqkv[B * T:] == 5.0)
+    assert torch.isfinite(out[:B * T].float()).all() and torch.isfinite(dqkv[:B * T].float()).all()
