@@ -191,46 +191,32 @@ patch_loss_kernel(const float* __restrict__ pred, long ldp, const uint8_t* __res
     __syncwarp();  // the previous row's readers are done with the staging slice
     stage_patch(spix, img, S, p, gy, gx, lane);
     __syncwarp();
-    float tv[kLossGroups][4];
-    float4 pv[kLossGroups];
-    float s = 0.f;
-#pragma unroll
-    for (int k = 0; k < kLossGroups; ++k) {
-      const int e0 = (lane + 32 * k) * 4;
-      pv[k] = make_float4(0.f, 0.f, 0.f, 0.f);
-      if (e0 < P) pv[k] = *reinterpret_cast<const float4*>(pred + row * ldp + e0);
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        const int e = e0 + j;
-        tv[k][j] = 0.f;
-        if (e < P) {
-          const int pix = e / 3, c = e - pix * 3;
-          tv[k][j] = lut[c * 256 + spix[c * pp + pix]];
-          s += tv[k][j];
-        }
-      }
-    }
-    if (norm_pix) {  // src/pretraining.py:115-118, jnp.var is the biased variance
-      const float mean = warp_sum(s) / P;
+    // target pixel e of the patch: element (pix = e / 3, channel = e % 3) of the staged planes
+    auto target = [&](int e) {
+      const int pix = e / 3, c = e - pix * 3;
+      return lut[c * 256 + spix[c * pp + pix]];
+    };
+    float mean = 0.f, inv = 1.f;
+    if (norm_pix) {  // src/pretraining.py:115-118, jnp.var is the biased variance: two cheap passes over the staged bytes
+      float s = 0.f;
+      for (int e = lane; e < P; e += 32) s += target(e);
+      mean = warp_sum(s) / P;
       float ss = 0.f;
-#pragma unroll
-      for (int k = 0; k < kLossGroups; ++k)
-#pragma unroll
-        for (int j = 0; j < 4; ++j)
-          if ((lane + 32 * k) * 4 + j < P) ss += (tv[k][j] - mean) * (tv[k][j] - mean);
-      const float var = warp_sum(ss) / P;
-      const float inv = 1.0f / sqrtf(var + 1e-6f);
-#pragma unroll
-      for (int k = 0; k < kLossGroups; ++k)
-#pragma unroll
-        for (int j = 0; j < 4; ++j) tv[k][j] = (tv[k][j] - mean) * inv;
+      for (int e = lane; e < P; e += 32) {
+        const float d = target(e) - mean;
+        ss += d * d;
+      }
+      inv = 1.0f / sqrtf(warp_sum(ss) / P + 1e-6f);
     }
     float sq = 0.f;
-#pragma unroll
-    for (int k = 0; k < kLossGroups; ++k) {
+#pragma unroll 2
+    for (int k = 0; k < kLossGroups; ++k) {  // one group in flight at a time: few registers, many resident warps
       const int e0 = (lane + 32 * k) * 4;
       if (e0 < P) {
-        const float d0 = pv[k].x - tv[k][0], d1 = pv[k].y - tv[k][1], d2 = pv[k].z - tv[k][2], d3 = pv[k].w - tv[k][3];
+        const float4 pv = *reinterpret_cast<const float4*>(pred + row * ldp + e0);
+        float t0 = target(e0), t1 = target(e0 + 1), t2 = target(e0 + 2), t3 = target(e0 + 3);
+        if (norm_pix) t0 = (t0 - mean) * inv, t1 = (t1 - mean) * inv, t2 = (t2 - mean) * inv, t3 = (t3 - mean) * inv;
+        const float d0 = pv.x - t0, d1 = pv.y - t1, d2 = pv.z - t2, d3 = pv.w - t3;
         sq += d0 * d0 + d1 * d1 + d2 * d2 + d3 * d3;
         if (dpred)
           *reinterpret_cast<uint2*>(dpred + row * lddp + e0) =
