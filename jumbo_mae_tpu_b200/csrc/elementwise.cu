@@ -369,6 +369,15 @@ layernorm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, long lddy, const floa
 // thread and leaves one resident CTA per SM, which starves a kernel that is pure HBM streaming.
 constexpr int kLnBwdWarps = 4;
 
+// Where a block's parameter-gradient partials go: straight into dgamma / dbeta / dcol with 16-byte vector
+// reductions (on != 0), or into the per-block workspace that ln_param_reduce_kernel sums afterwards.
+struct LnDirect {
+  float* dgamma;
+  float* dbeta;
+  float* dcol;
+  int on;
+};
+
 template <int NV>
 #ifndef JM_LN_REG_CTAS
 #define JM_LN_REG_CTAS 4  // dim 768: 127 registers without spills, four resident CTAs: 81 -> 77 us at the encoder shape
@@ -379,7 +388,7 @@ layernorm_bwd_reg_kernel(const __nv_bfloat16* __restrict__ dy, long lddy, const 
                          const float* __restrict__ gamma, int rows, int D, const float* __restrict__ dres,
                          long lddres, float* __restrict__ dx, long lddx, __nv_bfloat16* __restrict__ dxb, long lddxb,
                          int row_period, int row_skip, float* __restrict__ ws, int want_dcol, int dcol_period,
-                         int dcol_skip) {
+                         int dcol_skip, LnDirect direct) {
   pdl_wait();  // programmatic dependent launch: nothing above touches global memory
   pdl_launch_dependents();
   extern __shared__ __align__(16) float s_acc[];  // [warps][3][D]: dgamma, dbeta, column sums of dx
@@ -457,6 +466,20 @@ layernorm_bwd_reg_kernel(const __nv_bfloat16* __restrict__ dy, long lddy, const 
     }
   }
   __syncthreads();
+  if (direct.on) {  // one 16-byte reduction per 4 columns and block (D is a multiple of 4, so is every section)
+    for (int c = threadIdx.x * 4; c < 3 * D; c += blockDim.x * 4) {
+      float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+      for (int w = 0; w < kLnBwdWarps; ++w) {
+        const float4 a = *reinterpret_cast<const float4*>(s_acc + static_cast<long>(w) * 3 * D + c);
+        t.x += a.x, t.y += a.y, t.z += a.z, t.w += a.w;
+      }
+      float* dst = c < D ? direct.dgamma : (c < 2 * D ? direct.dbeta : direct.dcol);
+      const int cc = c < D ? c : (c < 2 * D ? c - D : c - 2 * D);
+      if (dst) atomicAdd(reinterpret_cast<float4*>(dst + cc), t);
+    }
+    return;
+  }
   float* out = ws + static_cast<long>(blockIdx.x) * 3 * D;
   for (int c = threadIdx.x; c < 3 * D; c += blockDim.x) {
     float t = 0.f;
@@ -479,7 +502,7 @@ layernorm_bwd_pipe_kernel(const __nv_bfloat16* __restrict__ dy, long lddy, const
                          const float* __restrict__ gamma, int rows, int D, const float* __restrict__ dres,
                          long lddres, float* __restrict__ dx, long lddx, __nv_bfloat16* __restrict__ dxb, long lddxb,
                          int row_period, int row_skip, float* __restrict__ ws, int want_dcol, int dcol_period,
-                         int dcol_skip) {
+                         int dcol_skip, LnDirect direct) {
   pdl_wait();  // programmatic dependent launch: nothing above touches global memory
   pdl_launch_dependents();
   extern __shared__ __align__(16) float s_acc[];  // [warps][3][D]: dgamma, dbeta, column sums of dx
@@ -583,6 +606,20 @@ layernorm_bwd_pipe_kernel(const __nv_bfloat16* __restrict__ dy, long lddy, const
     row = nrow;
   }
   __syncthreads();
+  if (direct.on) {  // one 16-byte reduction per 4 columns and block (D is a multiple of 4, so is every section)
+    for (int c = threadIdx.x * 4; c < 3 * D; c += blockDim.x * 4) {
+      float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+      for (int w = 0; w < kLnBwdWarps; ++w) {
+        const float4 a = *reinterpret_cast<const float4*>(s_acc + static_cast<long>(w) * 3 * D + c);
+        t.x += a.x, t.y += a.y, t.z += a.z, t.w += a.w;
+      }
+      float* dst = c < D ? direct.dgamma : (c < 2 * D ? direct.dbeta : direct.dcol);
+      const int cc = c < D ? c : (c < 2 * D ? c - D : c - 2 * D);
+      if (dst) atomicAdd(reinterpret_cast<float4*>(dst + cc), t);
+    }
+    return;
+  }
   float* out = ws + static_cast<long>(blockIdx.x) * 3 * D;
   for (int c = threadIdx.x; c < 3 * D; c += blockDim.x) {
     float t = 0.f;
@@ -949,29 +986,45 @@ extern "C" int jm_layernorm_bwd(const jm_bf16* dy, long lddy, const float* x, lo
       want_dcol, dcol_period, dcol_skip
   const size_t smem_reg = static_cast<size_t>(kLnBwdWarps) * 3 * dim * sizeof(float);
   const int tr = kLnBwdWarps * 32;
-  if (dim <= 128) JM_LAUNCH_PDL(layernorm_bwd_pipe_kernel<1>, grid, tr, smem_reg, STREAM, JM_LN_BWD_ARGS);
-  else if (dim <= 256) JM_LAUNCH_PDL(layernorm_bwd_pipe_kernel<2>, grid, tr, smem_reg, STREAM, JM_LN_BWD_ARGS);
-  else if (dim <= 512) JM_LAUNCH_PDL(layernorm_bwd_pipe_kernel<4>, grid, tr, smem_reg, STREAM, JM_LN_BWD_ARGS);
+  // register kernels: the blocks reduce their partials straight into the gradients (no second launch) when the
+  // destinations allow 16-byte vector reductions; JM_LN_DIRECT=0 keeps the workspace + reduce-kernel path
+  static int direct_env = -1;
+  if (direct_env < 0) {
+    const char* e = getenv("JM_LN_DIRECT");
+    direct_env = e ? (atoi(e) != 0) : 1;
+  }
+  LnDirect direct{dgamma, dbeta, dcol, 0};
+  direct.on = direct_env && dim <= 1280 &&
+              ((reinterpret_cast<uintptr_t>(dgamma) | reinterpret_cast<uintptr_t>(dbeta) |
+                reinterpret_cast<uintptr_t>(dcol)) & 15) == 0;
+#define JM_LN_BWD_ARGS_D JM_LN_BWD_ARGS, direct
+  if (dim <= 128) JM_LAUNCH_PDL(layernorm_bwd_pipe_kernel<1>, grid, tr, smem_reg, STREAM, JM_LN_BWD_ARGS_D);
+  else if (dim <= 256) JM_LAUNCH_PDL(layernorm_bwd_pipe_kernel<2>, grid, tr, smem_reg, STREAM, JM_LN_BWD_ARGS_D);
+  else if (dim <= 512) JM_LAUNCH_PDL(layernorm_bwd_pipe_kernel<4>, grid, tr, smem_reg, STREAM, JM_LN_BWD_ARGS_D);
 #ifdef JM_LN_PIPE6
-  else if (dim <= 768) JM_LAUNCH_PDL(layernorm_bwd_pipe_kernel<6>, grid, tr, smem_reg, STREAM, JM_LN_BWD_ARGS);
+  else if (dim <= 768) JM_LAUNCH_PDL(layernorm_bwd_pipe_kernel<6>, grid, tr, smem_reg, STREAM, JM_LN_BWD_ARGS_D);
 #else
-  else if (dim <= 768) JM_LAUNCH_PDL(layernorm_bwd_reg_kernel<6>, grid, tr, smem_reg, STREAM, JM_LN_BWD_ARGS);
+  else if (dim <= 768) JM_LAUNCH_PDL(layernorm_bwd_reg_kernel<6>, grid, tr, smem_reg, STREAM, JM_LN_BWD_ARGS_D);
 #endif
   else if (dim <= 1024) {
     JM_CUDA(cudaFuncSetAttribute(layernorm_bwd_reg_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
-    JM_LAUNCH_PDL(layernorm_bwd_reg_kernel<8>, grid, tr, smem_reg, STREAM, JM_LN_BWD_ARGS);
+    JM_LAUNCH_PDL(layernorm_bwd_reg_kernel<8>, grid, tr, smem_reg, STREAM, JM_LN_BWD_ARGS_D);
   } else if (dim <= 1280) {
     JM_CUDA(cudaFuncSetAttribute(layernorm_bwd_reg_kernel<10>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
-    JM_LAUNCH_PDL(layernorm_bwd_reg_kernel<10>, grid, tr, smem_reg, STREAM, JM_LN_BWD_ARGS);
+    JM_LAUNCH_PDL(layernorm_bwd_reg_kernel<10>, grid, tr, smem_reg, STREAM, JM_LN_BWD_ARGS_D);
   } else {
     const int g8 = (rows + kLnWarps - 1) / kLnWarps < grid ? (rows + kLnWarps - 1) / kLnWarps : grid;
     grid = g8;
     JM_LAUNCH_PDL(layernorm_bwd_kernel, grid, kLnWarps * 32, smem, STREAM, JM_LN_BWD_ARGS);
   }
+#undef JM_LN_BWD_ARGS_D
 #undef JM_LN_BWD_ARGS
-  JM_LAUNCH_PDL(ln_param_reduce_kernel, (3 * dim + 31) / 32, 256, 0, STREAM, static_cast<const float*>(workspace), grid, dim,
-                                                                  dgamma, dbeta, dcol);
   JM_AFTER_LAUNCH();
+  if (!direct.on) {
+    JM_LAUNCH_PDL(ln_param_reduce_kernel, (3 * dim + 31) / 32, 256, 0, STREAM, static_cast<const float*>(workspace),
+                  grid, dim, dgamma, dbeta, dcol);
+    JM_AFTER_LAUNCH();
+  }
   return 0;
 }
 
