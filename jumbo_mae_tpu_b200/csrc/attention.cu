@@ -392,11 +392,14 @@ __device__ __forceinline__ void bwd_kv_chunk(const uint32_t (&kf)[HD / 16][4], c
   }
 }
 
+#ifndef JM_ATTN_BWD_THREADS
+#define JM_ATTN_BWD_THREADS 256
+#endif
 #ifndef JM_ATTN_BWD_CTAS
 #define JM_ATTN_BWD_CTAS 2
 #endif
 template <int HD>
-__global__ void __launch_bounds__(256, HD == 32 ? JM_ATTN_BWD_CTAS : (HD == 64 ? JM_ATTN_BWD64_CTAS : 1))
+__global__ void __launch_bounds__(JM_ATTN_BWD_THREADS, HD == 32 ? JM_ATTN_BWD_CTAS : (HD == 64 ? JM_ATTN_BWD64_CTAS : 1))
 attn_bwd_kernel(const __nv_bfloat16* __restrict__ qkv, long ldqkv,
                                 const __nv_bfloat16* __restrict__ dout, long lddo, const float* __restrict__ lse,
                                 const __nv_bfloat16* __restrict__ out, long ldo, int T, int heads, float q_scale,
