@@ -211,6 +211,22 @@ int jm_clip_by_global_norm(float* g, long n, float pre_scale, float max_norm, fl
 int jm_add_bias_cast(const float* src, long lds, int rows, int cols, const float* bias, float* dst_f32, long ldd,
                      jm_bf16* dst_bf16, long ldd16, void* stream);
 
+/* Classification loss of the fine-tune step (src/finetuning.py:90-106), one launch:
+ *   labels  = one_hot(labels_idx, C) or labels_soft                         (finetuning.py:90-91)
+ *   labels  = (1 - label_smoothing) * labels + label_smoothing / C          (optax.smooth_labels, :94)
+ *   labels  = ratio * labels + (1 - ratio) * labels[perm]   if perm != NULL (Mixup / CutMix label side,
+ *                                                                            src/utils.py:70-71,82-83)
+ *   loss[b] = -sum_c labels * log_softmax(logits)                           (optax.softmax_cross_entropy, :98)
+ *   acc1[b] = labels[top1] == max(labels);  acc5[b] = any over top_k(logits, 5), ties to the lower index (:99-106)
+ *   dlogits = grad_scale * (softmax(logits) * sum_c labels - labels)        (d sum_b loss[b] / d logits, scaled)
+ * Exactly one of labels_soft [B, C] f32 and labels_idx [B] int32 is given.  loss_rows / acc1 / acc5 [B] f32,
+ * metrics [3] f32 (batch means of the three, accumulated with atomics after being zeroed here) and
+ * dlogits [B, C] f32 may each be NULL.  Evaluation (det=True) passes label_smoothing = 0 and perm = NULL.
+ * 1 <= C <= 8192. */
+int jm_softmax_ce(const float* logits, const float* labels_soft, const int* labels_idx, const int* perm,
+                  float ratio, double label_smoothing, int B, int C, float grad_scale, float* loss_rows,
+                  float* acc1, float* acc5, float* metrics, float* dlogits, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -27,6 +27,11 @@ def _chk(t: Optional[torch.Tensor], dtype, name: str) -> None:
         raise _lib.JmError(f"{name} must be {dtype}, got {t.dtype}")
 
 
+def _expect(cond: bool, msg: str) -> None:
+    if not cond:
+        raise _lib.JmError(msg)
+
+
 def _ld(t: Optional[torch.Tensor]) -> int:
     """Row stride (elements) of a 2-D view whose last dim is contiguous."""
     if t is None:
@@ -259,3 +264,38 @@ def clip_by_global_norm(g: torch.Tensor, pre_scale: float, max_norm: float, sums
     """In-place optax.clip_by_global_norm of the flat gradient buffer (jm_clip_by_global_norm)."""
     _chk(g, F32, "g"), _chk(sumsq, F32, "sumsq")
     check(_lib.load().jm_clip_by_global_norm(ptr(g), g.numel(), pre_scale, max_norm, ptr(sumsq), stream_ptr()))
+
+
+def softmax_ce(logits: torch.Tensor, labels: torch.Tensor, *, label_smoothing: float = 0.0,
+               perm: Optional[torch.Tensor] = None, ratio: float = 1.0, grad_scale: Optional[float] = None,
+               want_grad: bool = True):
+    """Classification loss of the fine-tune step (jm_softmax_ce; src/finetuning.py:90-106): label smoothing, the
+    Mixup / CutMix label mix ``ratio * labels + (1 - ratio) * labels[perm]``, softmax cross-entropy, top-1 / top-5
+    hits and the gradient with respect to the logits, in one launch.
+
+    ``labels`` is int32 ``[B]`` (class indices) or f32 ``[B, C]`` (soft labels).  Returns
+    ``(metrics [3] = mean loss, acc1, acc5; loss_rows [B]; acc1 [B]; acc5 [B]; dlogits [B, C] or None)``;
+    ``dlogits`` is d(mean loss)/d(logits) unless ``grad_scale`` is given."""
+    _chk(logits, F32, "logits")
+    if logits.dim() != 2 or not logits.is_contiguous():
+        raise _lib.JmError("logits must be a contiguous [B, C] tensor")
+    B, C = logits.shape
+    soft = idx = None
+    if labels.dim() == 1:
+        _chk(labels, I32, "labels"), _expect(labels.shape[0] == B and labels.is_contiguous(), "labels must be [B]")
+        idx = labels
+    else:
+        _chk(labels, F32, "labels")
+        _expect(tuple(labels.shape) == (B, C) and labels.is_contiguous(), "soft labels must be contiguous [B, C]")
+        soft = labels
+    if perm is not None:
+        _chk(perm, I32, "perm"), _expect(perm.shape == (B,) and perm.is_contiguous(), "perm must be int32 [B]")
+    dev = logits.device
+    metrics = torch.empty(3, dtype=F32, device=dev)
+    rows = torch.empty(3, B, dtype=F32, device=dev)
+    dlogits = torch.empty_like(logits) if want_grad else None
+    scale = (1.0 / max(B, 1)) if grad_scale is None else grad_scale
+    check(_lib.load().jm_softmax_ce(ptr(logits), ptr(soft), ptr(idx), ptr(perm), ratio, float(label_smoothing), B, C,
+                                    scale, ptr(rows[0]), ptr(rows[1]), ptr(rows[2]), ptr(metrics), ptr(dlogits),
+                                    stream_ptr()))
+    return metrics, rows[0], rows[1], rows[2], dlogits

@@ -550,6 +550,65 @@ def training_step(state: OracleState, images_u8, noise, grads_override: Tree | N
     new_state = OracleState(new_p, new_m, new_v, state.step + 1, cfg)
     return new_state, {"loss": float(loss), "learning_rate": lr}, grads
 
+# ----------------------------------------------------------------------------
+# fine-tune step, classification loss (src/finetuning.py:84-106; SURVEY.md 8(f) rank 1, first piece)
+# ----------------------------------------------------------------------------
+def smooth_labels(labels: np.ndarray, alpha: float) -> np.ndarray:
+    """optax.smooth_labels (src/finetuning.py:94): ``(1.0 - alpha) * labels + alpha / num_categories`` with
+    Python-float constants meeting an f32 array (third-party, restated from its published definition)."""
+    labels = np.asarray(labels, dtype=np.float32)
+    return np.float32(1.0 - alpha) * labels + np.float32(alpha / labels.shape[-1])
+
+
+def mix_labels(labels: np.ndarray, perm: np.ndarray, ratio) -> np.ndarray:
+    """Label side of Mixup.apply_mixup / apply_cutmix (src/utils.py:70-71,82-83): ``ratio`` is the beta sample
+    (mixup) or the mean of the box mask (cutmix), an f32 scalar either way."""
+    r = np.float32(ratio)
+    return r * labels + (np.float32(1) - r) * labels[perm]
+
+
+def softmax_cross_entropy(logits: np.ndarray, labels: np.ndarray) -> np.ndarray:
+    """optax.softmax_cross_entropy (src/finetuning.py:40,98): ``-sum(labels * log_softmax(logits), -1)`` with
+    jax.nn.log_softmax = shifted - log(sum(exp(shifted))), shifted = logits - max(logits)."""
+    logits = np.asarray(logits, dtype=np.float32)
+    shifted = logits - logits.max(-1, keepdims=True)
+    logp = shifted - np.log(np.exp(shifted).sum(-1, keepdims=True, dtype=np.float32))
+    return -(labels * logp).sum(-1, dtype=np.float32)
+
+
+def top_k_indices(logits: np.ndarray, k: int) -> np.ndarray:
+    """jax.lax.top_k(...)[1]: descending values, the lower index first among equal values."""
+    return np.argsort(-np.asarray(logits, dtype=np.float32), axis=-1, kind="stable")[..., :k]
+
+
+def finetune_metrics(logits, labels, num_labels: int, label_smoothing: float = 0.0, perm=None, ratio=1.0,
+                     det: bool = False):
+    """FinetuneModule.__call__ after the model (src/finetuning.py:90-106): per-row loss, acc1, acc5 and the label
+    matrix the loss saw.  ``labels``: int [B] class indices or f32 [B, C]."""
+    labels = np.asarray(labels)
+    if labels.ndim == 1:                                          # nn.one_hot (:90)
+        labels = np.eye(num_labels, dtype=np.float32)[labels]
+    labels = labels.astype(np.float32)
+    if not det:                                                   # :93-95
+        labels = smooth_labels(labels, label_smoothing)
+        if perm is not None:
+            labels = mix_labels(labels, np.asarray(perm), ratio)
+    loss = softmax_cross_entropy(logits, labels)                  # :98
+    hot = labels == labels.max(-1, keepdims=True)                 # :99
+    preds = top_k_indices(logits, min(5, labels.shape[-1]))       # :105
+    accs = np.take_along_axis(hot, preds, axis=-1)                # :106
+    return {"loss": loss, "acc1": accs[:, 0].astype(np.float32), "acc5": accs.any(-1).astype(np.float32),
+            "labels": labels}
+
+
+def softmax_ce_grad(logits: np.ndarray, labels: np.ndarray) -> np.ndarray:
+    """d mean_b(loss) / d logits = (softmax * sum(labels) - labels) / B, the closed form jax.grad arrives at."""
+    logits = np.asarray(logits, dtype=np.float64)
+    p = np.exp(logits - logits.max(-1, keepdims=True))
+    p /= p.sum(-1, keepdims=True)
+    return ((p * labels.sum(-1, keepdims=True) - labels) / logits.shape[0]).astype(np.float32)
+
+
 
 def synthetic_batch(cfg: MAEConfig, batch: int, seed: int = 0, noise_seed: int = 1000):
     """SURVEY.md section 8d synthetic inputs: uint8 images, f32 uniform noise."""

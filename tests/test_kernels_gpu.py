@@ -622,3 +622,55 @@ def test_attention_outputs_stay_inside_their_buffers(ops, T, H, hd):
     torch.cuda.synchronize()
     assert torch.all(out[B * T:] == 5.0) and torch.all(lse[B * H * T:] == 5.0) and torch.all(dqkv[B * T:] == 5.0)
     assert torch.isfinite(out[:B * T].float()).all() and torch.isfinite(dqkv[:B * T].float()).all()
+
+
+# ------------------------------------------------------------------ fine-tune classification loss (8(f) rank 1)
+@pytest.mark.parametrize("B,C,soft,mix,alpha", [
+    (64, 1000, False, False, 0.1), (64, 1000, False, True, 0.1), (33, 1000, True, True, 0.0),
+    (8, 3, False, True, 0.1), (5, 8192, False, False, 0.0), (1, 1, False, False, 0.0), (16, 37, True, False, 0.2),
+])
+def test_softmax_ce_matches_oracle(ops, B, C, soft, mix, alpha):
+    """jm_softmax_ce against the numpy restatement of src/finetuning.py:90-106.  Labels and hit flags: bit exact.
+    Loss: rel 1e-5 (f32 exp/log of CUDA vs numpy).  Gradient: atol 1e-7 + rel 1e-4 against the f64 closed form."""
+    rng = np.random.default_rng(B * 7919 + C)
+    logits = (rng.standard_normal((B, C)) * 3).astype(np.float32)
+    if C >= 8:
+        logits[0, 5] = logits[0, 2] = logits[0].max() + 1       # a tie for the first place: index 2 must win
+    idx = rng.integers(0, C, B).astype(np.int32)
+    if soft:
+        labels = rng.random((B, C), dtype=np.float32)
+        labels /= labels.sum(-1, keepdims=True)
+    else:
+        labels = idx
+    perm = rng.permutation(B).astype(np.int32) if mix else None
+    ratio = float(np.float32(rng.beta(0.8, 0.8))) if mix else 1.0
+    want = O.finetune_metrics(logits, labels, C, alpha, perm=perm, ratio=ratio)
+    metrics, loss, acc1, acc5, dlogits = ops.softmax_ce(
+        dev(torch.from_numpy(logits)), dev(torch.from_numpy(labels)), label_smoothing=alpha,
+        perm=None if perm is None else dev(torch.from_numpy(perm)), ratio=ratio)
+    assert np.allclose(loss.cpu().numpy(), want["loss"], rtol=1e-5, atol=1e-6)
+    assert np.array_equal(acc1.cpu().numpy(), want["acc1"])
+    assert np.array_equal(acc5.cpu().numpy(), want["acc5"])
+    got_m = metrics.cpu().numpy()
+    assert np.allclose(got_m, [want["loss"].mean(), want["acc1"].mean(), want["acc5"].mean()], rtol=1e-5, atol=1e-6)
+    g = O.softmax_ce_grad(logits, want["labels"])
+    assert np.allclose(dlogits.cpu().numpy(), g, rtol=1e-4, atol=1e-7)
+
+
+def test_softmax_ce_eval_mode_and_errors(ops):
+    """Evaluation: no smoothing, no mixing, no gradient buffer; bad arguments are refused with a message."""
+    from jumbo_mae_tpu_b200._lib import JmError
+    rng = np.random.default_rng(11)
+    logits = rng.standard_normal((32, 1000)).astype(np.float32)
+    idx = rng.integers(0, 1000, 32).astype(np.int32)
+    idx[:8] = logits[:8].argmax(-1)                              # eight certain top-1 hits
+    want = O.finetune_metrics(logits, idx, 1000, 0.1, det=True)
+    metrics, loss, acc1, acc5, dlogits = ops.softmax_ce(dev(torch.from_numpy(logits)), dev(torch.from_numpy(idx)),
+                                                        want_grad=False)
+    assert dlogits is None and acc1[:8].sum().item() == 8
+    assert np.allclose(loss.cpu().numpy(), want["loss"], rtol=1e-5)
+    assert np.array_equal(acc5.cpu().numpy(), want["acc5"])
+    with pytest.raises(JmError, match="label_smoothing"):
+        ops.softmax_ce(dev(torch.from_numpy(logits)), dev(torch.from_numpy(idx)), label_smoothing=1.5)
+    with pytest.raises(JmError, match="8192"):
+        ops.softmax_ce(torch.zeros(2, 9000, device="cuda"), torch.zeros(2, dtype=torch.int32, device="cuda"))

@@ -221,3 +221,36 @@ def test_f32_oracle_close_to_f64_golden():
     for path, g in O.tree_leaves(grads):
         want = torch.from_numpy(z["tiny/grads/" + "/".join(path)])
         assert (g - want).norm() <= 1e-4 * want.norm() + 1e-7
+
+
+# ------------------------------------------------------------------ fine-tune classification loss (8(f) rank 1)
+def test_softmax_ce_known_answers():
+    """Uniform logits give log C for any label distribution that sums to one; a dominant correct logit gives ~0."""
+    C = 1000
+    lab = np.eye(C, dtype=np.float32)[[3, 7]]
+    assert np.allclose(O.softmax_cross_entropy(np.zeros((2, C), np.float32), lab), math.log(C), rtol=1e-6)
+    lg = np.zeros((2, C), np.float32)
+    lg[0, 3] = lg[1, 7] = 50.0
+    assert np.all(O.softmax_cross_entropy(lg, lab) < 1e-6)
+
+
+def test_smooth_labels_is_optax_rule():
+    out = O.smooth_labels(np.eye(4, dtype=np.float32)[[1]], 0.1)
+    assert np.allclose(out, [[0.025, 0.925, 0.025, 0.025]], atol=1e-7) and abs(out.sum() - 1) < 1e-6
+
+
+def test_top_k_ties_go_to_the_lower_index():
+    assert O.top_k_indices(np.array([[1.0, 3.0, 3.0, 0.0, 3.0, 2.0]], np.float32), 5).tolist() == [[1, 2, 4, 5, 0]]
+
+
+def test_finetune_metrics_mixup_and_eval_modes():
+    """acc counts a prediction inside the arg-max label SET (src/finetuning.py:99-106): with ratio 0.5 both mixed
+    classes count; evaluation (det=True) ignores smoothing and mixing."""
+    lg = np.zeros((2, 6), np.float32)
+    lg[0, 4], lg[1, 0] = 2.0, 2.0
+    m = O.finetune_metrics(lg, np.array([1, 4]), 6, 0.1, perm=np.array([1, 0]), ratio=0.5)
+    assert m["acc1"].tolist() == [1.0, 0.0] and m["acc5"].tolist() == [1.0, 1.0]
+    e = O.finetune_metrics(lg, np.array([1, 4]), 6, 0.1, perm=np.array([1, 0]), ratio=0.5, det=True)
+    assert np.array_equal(e["labels"], np.eye(6, dtype=np.float32)[[1, 4]])
+    g = O.softmax_ce_grad(lg, m["labels"])
+    assert np.allclose(g.sum(-1), 0, atol=1e-7)      # labels sum to one -> every gradient row sums to zero
