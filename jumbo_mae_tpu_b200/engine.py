@@ -236,30 +236,37 @@ class MAEEngine:
     # reference gets from XLA scheduling lax.pmean inside the step, src/pretraining.py:150).
     ENC_LAYERS_PER_SEGMENT = 3
 
+    def _segment_plan(self):
+        """Decoder segment, encoder segments of ENC_LAYERS_PER_SEGMENT layers (layers L-1 .. 1), then the shared
+        Jumbo MLP on its own and a tail.  The Jumbo gradients (the largest leaves, 28 % of ViT-B) are final as soon
+        as layer 0's Jumbo branch has run: that branch and the batched Jumbo weight-gradient GEMMs form one
+        segment, so the all-reduce of the layers before it overlaps those GEMMs and the Jumbo all-reduce overlaps
+        the tail (layer 0's patch-FFN and attention branches, the patch embedding)."""
+        upper = list(reversed(range(1, self.cfg.layers)))
+        n = self.ENC_LAYERS_PER_SEGMENT
+        return [("dec", [])] + [("enc", upper[i:i + n]) for i in range(0, len(upper), n)] + [("jumbo", [0]), ("tail", [0])]
+
     def num_bwd_segments(self) -> int:
-        n_enc = (self.cfg.layers + self.ENC_LAYERS_PER_SEGMENT - 1) // self.ENC_LAYERS_PER_SEGMENT
-        return 1 + n_enc
+        return len(self._segment_plan())
 
     def _enc_segment_layers(self, k: int):
-        """Encoder layers (descending) handled by backward segment k >= 1."""
-        hi = self.cfg.layers - (k - 1) * self.ENC_LAYERS_PER_SEGMENT
-        lo = max(0, hi - self.ENC_LAYERS_PER_SEGMENT)
-        return list(reversed(range(lo, hi)))
+        """Encoder layers (descending) that backward segment k >= 1 works on."""
+        return self._segment_plan()[k][1]
 
     def segment_grad_ranges(self, k: int):
         """[start, end) ranges of store.g that are final once backward segment k has run."""
-        last = self.num_bwd_segments() - 1
-        if k == 0:
+        kind, layers = self._segment_plan()[k]
+        if kind == "dec":
             sel = lambda n: not n.startswith("model/") or n.startswith("model/norm/")
+        elif kind == "jumbo":
+            sel = lambda n: n.startswith("model/jumbo_mlp/")
+        elif kind == "tail":
+            sel = lambda n: (n.startswith("model/layer_0/") or n.startswith("model/embed/")
+                             or n.startswith("model/cls_tokens"))
         else:
-            layers = self._enc_segment_layers(k)
             # a layer's ff/w2 bias is produced by the block ABOVE it (LayerNorm-backward column sums), hence
             # final one block earlier; it is simply reduced together with its own layer's leaves
-            def sel(n, layers=layers, is_last=(k == last)):
-                if any(n.startswith(f"model/layer_{i}/") for i in layers):
-                    return True
-                return is_last and (n.startswith("model/embed/") or n.startswith("model/cls_tokens")
-                                    or n.startswith("model/jumbo_mlp/"))
+            sel = lambda n, layers=layers: any(n.startswith(f"model/layer_{i}/") for i in layers)
         return self.ps.ranges(sel)
 
     def backward_segment(self, k: int, zero_grads: bool = True) -> None:
@@ -294,27 +301,36 @@ class MAEEngine:
                               dx16, ps.grad("model/norm/scale"), ps.grad("model/norm/bias"), self.ln_ws,
                               dcol=ps.grad(f"model/layer_{cfg.layers - 1}/ff/w2/bias"), dcol_period=Te, dcol_skip=J)
             return
-        # ---- encoder blocks of this segment
-        for i in self._enc_segment_layers(k):
-            below = ps.grad(f"model/layer_{i - 1}/ff/w2/bias") if i > 0 else ps.grad("model/embed/wte/bias")
-            self._block_bwd(f"model/layer_{i}", self.enc[i], self.xa[i], Me, d, cfg.heads, Te, True, below)
-        if k == self.num_bwd_segments() - 1:
-            # ---- CLS parameter and patch embedding (its bias gradient came from layer 0's LN1 backward)
-            dx, dx16 = view(self.dxA, Me, d), view(self.dxA16, Me, d)
-            ops.colsum(dx, B, J * d, ps.grad("model/cls_tokens"), ldx=Te * d)
-            # shared Jumbo MLP: weight gradients over all layers at once (K = layers * B)
+        kind, layers = self._segment_plan()[k]
+        if kind == "enc":
+            for i in layers:
+                self._block_bwd(f"model/layer_{i}", self.enc[i], self.xa[i], Me, d, cfg.heads, Te, True,
+                                ps.grad(f"model/layer_{i - 1}/ff/w2/bias"))
+        if kind == "jumbo":
+            # layer 0's Jumbo branch alone (its patch-FFN and attention branches do not touch the CLS rows'
+            # incoming gradient and run in the tail), then the shared Jumbo MLP's weight gradients over all
+            # layers at once (K = layers * B)
+            self._block_bwd("model/layer_0", self.enc[0], self.xa[0], Me, d, cfg.heads, Te, True, None, part="jumbo")
             L, Jd = cfg.layers, J * d
             for nm, X, dY, rows, cols in (("w1", self.cn16_all, self.dhj16_all, Jd, 4 * Jd),
                                           ("w2", self.gj_all, self.dc16_all, 4 * Jd, Jd)):
                 ops.gemm(X, dY, rows, cols, L * B, a_mn=True, b_mn=True,
                          out_f32=ps.grad(f"model/jumbo_mlp/{nm}/kernel"), ldo_f32=ps.ld(f"model/jumbo_mlp/{nm}/kernel"),
                          accumulate=True)
+        if kind == "tail":
+            self._block_bwd("model/layer_0", self.enc[0], self.xa[0], Me, d, cfg.heads, Te, True,
+                            ps.grad("model/embed/wte/bias"), part="rest")
+            # ---- CLS parameter and patch embedding (its bias gradient came from layer 0's LN1 backward)
+            dx, dx16 = view(self.dxA, Me, d), view(self.dxA16, Me, d)
+            ops.colsum(dx, B, J * d, ps.grad("model/cls_tokens"), ldx=Te * d)
             ops.gemm(self.patches, dx16, P, d, Me, a_mn=True, b_mn=True, lda=Pp,
                      out_f32=ps.grad("model/embed/wte/kernel"), ldo_f32=ps.ld("model/embed/wte/kernel"),
                      accumulate=True)
 
-    def _block_bwd(self, name, s: _Block, x_in, M, dim, heads, T, jumbo, dcol_below):
+    def _block_bwd(self, name, s: _Block, x_in, M, dim, heads, T, jumbo, dcol_below, part="all"):
         """In: d/d(block output) in dxA / dxA16.  Out: d/d(block input) in dxA / dxA16.
+        ``part``: "all", or the block in two steps, "jumbo" (the Jumbo CLS branch alone: it reads and writes only
+        the CLS rows, which the patch FFN branch leaves alone) followed by "rest".
         Bias gradients are produced where their dY is produced (LayerNorm backward, GELU-backward GEMM
         epilogue, attention backward); ``dcol_below`` is the ff/w2 (or patch-embed) bias gradient of the
         block below, whose output gradient this block's LN1 backward emits."""
@@ -326,15 +342,16 @@ class MAEEngine:
         dh, dn = view(self.dh16, 4 * dim), view(self.dn16, dim)
         period, skip = (T, J) if jumbo else (0, 0)
         mode = 1 if jumbo else 0
-        # ---- patch FFN: y = x_b + w2(gelu(w1 LN2(x_b)))
-        self._bwd_linear(s.g, dx16, M, f"{name}/ff/w2", dim, 4 * dim, dX16=dh, bias=False, act=GELU_BWD, aux=s.h,
-                         row_period=period, row_skip=skip, row_mask_mode=mode,
-                         colsum=ps.grad(f"{name}/ff/w1/bias"))
-        self._bwd_linear(s.xn2, dh, M, f"{name}/ff/w1", 4 * dim, dim, dX16=dn, bias=False)
-        ops.layernorm_bwd(dn, s.xb, s.mean2, s.rstd2, ps.f(f"{name}/norm2/scale"), dx, dxb, dxb16,
-                          ps.grad(f"{name}/norm2/scale"), ps.grad(f"{name}/norm2/bias"), self.ln_ws,
-                          row_period=period, row_skip=skip, dcol=ps.grad(f"{name}/attn/wo/bias"))
-        if jumbo:
+        if part != "jumbo":
+            # ---- patch FFN: y = x_b + w2(gelu(w1 LN2(x_b)))
+            self._bwd_linear(s.g, dx16, M, f"{name}/ff/w2", dim, 4 * dim, dX16=dh, bias=False, act=GELU_BWD, aux=s.h,
+                             row_period=period, row_skip=skip, row_mask_mode=mode,
+                             colsum=ps.grad(f"{name}/ff/w1/bias"))
+            self._bwd_linear(s.xn2, dh, M, f"{name}/ff/w1", 4 * dim, dim, dX16=dn, bias=False)
+            ops.layernorm_bwd(dn, s.xb, s.mean2, s.rstd2, ps.f(f"{name}/norm2/scale"), dx, dxb, dxb16,
+                              ps.grad(f"{name}/norm2/scale"), ps.grad(f"{name}/norm2/bias"), self.ln_ws,
+                              row_period=period, row_skip=skip, dcol=ps.grad(f"{name}/attn/wo/bias"))
+        if jumbo and part != "rest":
             # ---- Jumbo CLS: c_out = c + w2j(gelu(w1j c)), c = LN3(cls concat); strided [B, J*dim] views
             Jd, ldc = J * dim, T * dim
             # output gradient of w2 = the CLS rows of dx: bias gradient now, a bf16 copy for the batched dW
@@ -352,6 +369,8 @@ class MAEEngine:
                               dim=Jd, ldx=ldc, lddx=ldc, lddxb=ldc)
             # wo bias: LN2 backward covered the patch rows, add the CLS rows LN3 backward just wrote
             ops.colsum(dxb16, M, dim, ps.grad(f"{name}/attn/wo/bias"), row_period=T, row_skip=J, row_invert=True)
+        if part == "jumbo":
+            return
         # ---- attention branch: x_b = x + wo(attn(wqkv LN1(x)))
         datt, dqkv = view(self.datt16, dim), view(self.dqkv16, 3 * dim)
         self._bwd_linear(s.att, dxb16, M, f"{name}/attn/wo", dim, dim, dX16=datt, bias=False)

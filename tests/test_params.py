@@ -72,5 +72,10 @@ def test_backward_segment_ranges_partition_the_gradient_buffer():
         seen.sort()
         assert all(a[1] <= b[0] for a, b in zip(seen, seen[1:]))
         assert sum(e - s for s, e in seen) == store.total
-        layers = [i for k in range(1, eng.num_bwd_segments()) for i in eng._enc_segment_layers(k)]
+        last = eng.num_bwd_segments() - 1
+        layers = [i for k in range(1, last) for i in eng._enc_segment_layers(k)]
         assert layers == list(reversed(range(cfg.layers)))
+        # the shared Jumbo MLP is a segment of its own, layer 0 and the patch embedding go with the tail
+        names = lambda k: {n for n, l in store.leaves.items() if any(s <= l.offset < e for s, e in eng.segment_grad_ranges(k))}
+        assert names(last - 1) and all(n.startswith("model/jumbo_mlp/") for n in names(last - 1))
+        assert all(n.startswith(("model/layer_0/", "model/embed/", "model/cls_tokens")) for n in names(last))

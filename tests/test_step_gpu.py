@@ -242,7 +242,8 @@ def test_segmented_backward_graphs_equal_whole_backward():
     torch.cuda.synchronize()
     assert (store.g - g_ref).norm().item() <= 2e-3 * g_ref.norm().item()   # L2 reduction order, see above
     assert torch.isfinite(loss).all()
-    assert eng.num_bwd_segments() == 1 + (cfg.layers + eng.ENC_LAYERS_PER_SEGMENT - 1) // eng.ENC_LAYERS_PER_SEGMENT
+    # decoder segment + encoder segments (layers L-1 .. 1) + the Jumbo segment + the tail (rest of layer 0, embedding)
+    assert eng.num_bwd_segments() == 3 + (cfg.layers - 1 + eng.ENC_LAYERS_PER_SEGMENT - 1) // eng.ENC_LAYERS_PER_SEGMENT
 
 
 def test_prefetched_batches_give_the_same_step():
