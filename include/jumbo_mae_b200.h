@@ -57,6 +57,17 @@ int jm_index_sequence(const float* x, const int32_t* ids, int batch, int length_
 int jm_patchify(const uint8_t* images, int batch, int image_size, int patch_size, const int32_t* ids, int n_sel,
                 int rows_per_image, int row_off, jm_bf16* out, long ldo, void* stream);
 
+/* jm_patchify with Mixup / CutMix on the normalised pixels (fine-tune input path, SURVEY.md 8(f) rank 1;
+ * src/finetuning.py:87-88,95 and Mixup in src/utils.py:67-90).  perm [batch] int32 = the batch permutation.
+ *   mode 1 (apply_mixup):  pixel = ratio * a + (1 - ratio) * b,  b = images[perm[image]]
+ *   mode 2 (apply_cutmix): pixel = b inside the box, a outside; xmask [image_size], ymask [image_size] uint8 are the
+ *                          box's column / row membership (random_bounding_box, src/utils.py:85-92, evaluated by the
+ *                          caller: 2 x image_size bytes), ratio unused.
+ * perm[i] must be in [0, batch).  Everything else as jm_patchify. */
+int jm_patchify_mix(const uint8_t* images, int batch, int image_size, int patch_size, const int32_t* ids, int n_sel,
+                    int rows_per_image, int row_off, jm_bf16* out, long ldo, const int32_t* perm, int mode,
+                    float ratio, const uint8_t* xmask, const uint8_t* ymask, void* stream);
+
 /* extract_patches on the normalised image as f32 (reference signature; tests only). */
 int jm_extract_patches(const uint8_t* images, int batch, int image_size, int patch_size, float* out, void* stream);
 

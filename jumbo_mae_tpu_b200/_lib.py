@@ -20,7 +20,7 @@ EXPORTS = [
     "jm_extract_patches", "jm_patch_loss_workspace", "jm_patch_loss", "jm_patch_loss_static", "jm_layernorm_fwd",
     "jm_layernorm_bwd_workspace", "jm_layernorm_bwd", "jm_gemm", "jm_attention_fwd", "jm_attention_bwd",
     "jm_fill_cls", "jm_unshuffle_fwd", "jm_unshuffle_bwd", "jm_colsum", "jm_adamw", "jm_cast_bf16",
-    "jm_add_bias_cast", "jm_clip_by_global_norm", "jm_softmax_ce",
+    "jm_add_bias_cast", "jm_clip_by_global_norm", "jm_softmax_ce", "jm_patchify_mix",
 ]
 
 
@@ -93,6 +93,7 @@ def load() -> ctypes.CDLL:
         "jm_cast_bf16": [P, P, c_long, P],
         "jm_add_bias_cast": [P, c_long, c_int, c_int, P, P, c_long, P, c_long, P],
         "jm_clip_by_global_norm": [P, c_long, c_float, c_float, P, P],
+        "jm_patchify_mix": [P, c_int, c_int, c_int, P, c_int, c_int, c_int, P, c_long, P, c_int, c_float, P, P, P],
         "jm_softmax_ce": [P, P, P, P, c_float, ctypes.c_double, c_int, c_int, c_float, P, P, P, P, P, P],
     }
     for name, argtypes in sig.items():

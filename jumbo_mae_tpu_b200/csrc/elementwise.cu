@@ -130,6 +130,61 @@ patchify_kernel(const uint8_t* __restrict__ images, int S, int p, const int* __r
   }
 }
 
+// Fine-tune input path: patchify with Mixup / CutMix applied to the NORMALISED pixels
+// (src/finetuning.py:87-88,95; src/utils.py:67-90), one warp per output row as above, both source patches staged.
+//   mode 1 (Mixup.apply_mixup):  v = ratio * a + (1 - ratio) * b      (separate roundings, as the f32 array ops)
+//   mode 2 (Mixup.apply_cutmix): v = inside_box(y, x) ? b : a         (image_mask * a + (1 - image_mask) * b with a
+//                                                                     0/1 mask), inside = xmask[x] & ymask[y]
+// with b = images[perm[image]].
+__global__ void __launch_bounds__(256)
+patchify_mix_kernel(const uint8_t* __restrict__ images, int S, int p, const int* __restrict__ ids, int n_sel,
+                    int rows_per_image, int row_off, __nv_bfloat16* __restrict__ out, long ldo, int batch,
+                    const int* __restrict__ perm, int mode, float ratio, const uint8_t* __restrict__ xmask,
+                    const uint8_t* __restrict__ ymask) {
+  __shared__ __align__(16) uint8_t spix_all[8][2][2048];
+  __shared__ float lut[768];
+  fill_norm_lut(lut);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  uint8_t* spa = spix_all[warp][0];
+  uint8_t* spb = spix_all[warp][1];
+  const int pp = p * p, P = pp * 3, g = S / p;
+  const float one_minus_r = __fsub_rn(1.f, ratio);
+  const long rows = static_cast<long>(batch) * rows_per_image;
+  for (long row = static_cast<long>(blockIdx.x) * 8 + warp; row < rows; row += static_cast<long>(gridDim.x) * 8) {
+    const int b = static_cast<int>(row / rows_per_image), r = static_cast<int>(row - static_cast<long>(b) * rows_per_image);
+    __nv_bfloat16* dst = out + row * ldo;
+    if (r < row_off || r >= row_off + n_sel) {
+      for (int e = lane * 4; e < ldo; e += 128) *reinterpret_cast<uint2*>(dst + e) = make_uint2(0u, 0u);
+      continue;
+    }
+    const int patch = ids ? ids[r - row_off] : (r - row_off);
+    const int gy = patch / g, gx = patch - gy * g;
+    __syncwarp();
+    stage_patch(spa, images + static_cast<long>(b) * 3 * S * S, S, p, gy, gx, lane);
+    stage_patch(spb, images + static_cast<long>(perm[b]) * 3 * S * S, S, p, gy, gx, lane);
+    __syncwarp();
+    for (int e0 = lane * 4; e0 < ldo; e0 += 128) {
+      float v[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int e = e0 + j;
+        v[j] = 0.f;
+        if (e < P) {
+          const int pix = e / 3, c = e - pix * 3;
+          const float a = lut[c * 256 + spa[c * pp + pix]], o = lut[c * 256 + spb[c * pp + pix]];
+          if (mode == 1) {
+            v[j] = __fadd_rn(__fmul_rn(ratio, a), __fmul_rn(one_minus_r, o));
+          } else {
+            const int ph = pix / p, pw = pix - ph * p;
+            v[j] = (xmask[gx * p + pw] & ymask[gy * p + ph]) ? o : a;
+          }
+        }
+      }
+      *reinterpret_cast<uint2*>(dst + e0) = make_uint2(pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]));
+    }
+  }
+}
+
 __global__ void extract_patches_kernel(const uint8_t* __restrict__ images, int S, int p, float* __restrict__ out) {
   const int patch = blockIdx.x, b = blockIdx.y;
   const int P = p * p * 3, g = S / p;
@@ -846,6 +901,26 @@ extern "C" int jm_patchify(const uint8_t* images, int batch, int image_size, int
   patchify_kernel<<<static_cast<int>(want < cap ? want : cap), 256, 0, STREAM>>>(
       images, image_size, patch_size, ids, n_sel, rows_per_image, row_off, reinterpret_cast<__nv_bfloat16*>(out), ldo,
       batch);
+  JM_AFTER_LAUNCH();
+  return 0;
+}
+
+extern "C" int jm_patchify_mix(const uint8_t* images, int batch, int image_size, int patch_size, const int32_t* ids,
+                               int n_sel, int rows_per_image, int row_off, jm_bf16* out, long ldo, const int32_t* perm,
+                               int mode, float ratio, const uint8_t* xmask, const uint8_t* ymask, void* stream) {
+  JM_CHECK(mode == 1 || mode == 2, "jm_patchify_mix: mode must be 1 (mixup) or 2 (cutmix); use jm_patchify without mixing");
+  JM_CHECK(images && out && perm, "jm_patchify_mix: null argument");
+  JM_CHECK(mode == 1 || (xmask && ymask), "jm_patchify_mix: cutmix needs xmask [image_size] and ymask [image_size]");
+  JM_CHECK(image_size % patch_size == 0, "jm_patchify_mix: image size must be a multiple of the patch size");
+  JM_CHECK(ldo >= patch_size * patch_size * 3, "jm_patchify_mix: ldo smaller than the patch dimension");
+  JM_CHECK(row_off + n_sel <= rows_per_image, "jm_patchify_mix: rows_per_image too small");
+  JM_CHECK(patch_size * patch_size * 3 <= 2048, "jm_patchify_mix: patch dimension %d too large", patch_size * patch_size * 3);
+  JM_CHECK(ldo % 4 == 0 && (reinterpret_cast<uintptr_t>(out) & 7) == 0, "jm_patchify_mix: ldo must be a multiple of 4");
+  if (batch == 0) return 0;
+  const long want = (static_cast<long>(batch) * rows_per_image + 7) / 8, cap = static_cast<long>(sm_count()) * 16;
+  patchify_mix_kernel<<<static_cast<int>(want < cap ? want : cap), 256, 0, STREAM>>>(
+      images, image_size, patch_size, ids, n_sel, rows_per_image, row_off, reinterpret_cast<__nv_bfloat16*>(out), ldo,
+      batch, perm, mode, ratio, xmask, ymask);
   JM_AFTER_LAUNCH();
   return 0;
 }

@@ -76,6 +76,25 @@ def patchify(images: torch.Tensor, patch_size: int, ids: Optional[torch.Tensor],
     return out
 
 
+def patchify_mix(images: torch.Tensor, patch_size: int, ids: Optional[torch.Tensor], n_sel: int, rows_per_image: int,
+                 row_off: int, out: torch.Tensor, perm: torch.Tensor, *, ratio: float = 1.0,
+                 xmask: Optional[torch.Tensor] = None, ymask: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """patchify with Mixup (``xmask is None``: ratio * a + (1 - ratio) * a[perm]) or CutMix (uint8 ``xmask`` /
+    ``ymask`` [image_size]: a[perm] inside the box) on the normalised pixels (jm_patchify_mix; src/utils.py:67-90)."""
+    _chk(images, U8, "images"), _chk(ids, I32, "ids"), _chk(out, BF16, "out"), _chk(perm, I32, "perm")
+    _chk(xmask, U8, "xmask"), _chk(ymask, U8, "ymask")
+    B, C, H, W = images.shape
+    _expect(C == 3 and H == W and images.is_contiguous(), "images must be contiguous [B, 3, S, S]")
+    _expect(perm.shape == (B,) and perm.is_contiguous(), "perm must be int32 [B]")
+    _expect((xmask is None) == (ymask is None), "give both xmask and ymask (cutmix) or neither (mixup)")
+    if xmask is not None:
+        _expect(xmask.numel() == W and ymask.numel() == H, "xmask / ymask must have image_size entries")
+    check(_lib.load().jm_patchify_mix(ptr(images), B, H, patch_size, ptr(ids), n_sel, rows_per_image, row_off, ptr(out),
+                                      _ld(out), ptr(perm), 1 if xmask is None else 2, ratio, ptr(xmask), ptr(ymask),
+                                      stream_ptr()))
+    return out
+
+
 def extract_patches_u8(images: torch.Tensor, patch_size: int) -> torch.Tensor:
     _chk(images, U8, "images")
     B, C, H, W = images.shape

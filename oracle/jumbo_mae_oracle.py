@@ -567,6 +567,36 @@ def mix_labels(labels: np.ndarray, perm: np.ndarray, ratio) -> np.ndarray:
     return r * labels + (np.float32(1) - r) * labels[perm]
 
 
+def apply_mixup(images: np.ndarray, labels: np.ndarray, ratio, perm) -> Tuple[np.ndarray, np.ndarray]:
+    """Mixup.apply_mixup (src/utils.py:67-72) on normalised NHWC f32 images with the beta sample ``ratio`` and the
+    batch permutation given (the reference draws both from the ``mixup`` RNG stream: RNG parity is not attempted)."""
+    r, perm = np.float32(ratio), np.asarray(perm)
+    images = r * images + (np.float32(1) - r) * images[perm]
+    return images, mix_labels(labels, perm, r)
+
+
+def random_bounding_box(ratio, xstart, ystart, width: int, height: int):
+    """Mixup.random_bounding_box (src/utils.py:85-92) with the two uniform draws given: column / row membership of
+    the box and the image mask (True OUTSIDE the box) of shape [1, height, width, 1]."""
+    size = np.float32((np.float32(1) - np.float32(ratio)) ** np.float32(0.5))
+    xs, ys, half = np.float32(xstart), np.float32(ystart), np.float32(0.5)
+    xr, yr = np.linspace(0, 1, width, dtype=np.float32), np.linspace(0, 1, height, dtype=np.float32)
+    xmask = (xs - half * size <= xr) & (xr < xs + half * size)
+    ymask = (ys - half * size <= yr) & (yr < ys + half * size)
+    return xmask, ymask, ~(xmask[None, None, :, None] & ymask[None, :, None, None])
+
+
+def apply_cutmix(images: np.ndarray, labels: np.ndarray, ratio, xstart, ystart, perm):
+    """Mixup.apply_cutmix (src/utils.py:74-83): the box of images[perm] pasted in, labels mixed by the box area."""
+    perm = np.asarray(perm)
+    _, _, image_mask = random_bounding_box(ratio, xstart, ystart, images.shape[2], images.shape[1])
+    label_mask = image_mask.mean((1, 2), dtype=np.float32)          # [1, 1]
+    m = image_mask.astype(np.float32)
+    images = m * images + (np.float32(1) - m) * images[perm]
+    labels = label_mask * labels + (np.float32(1) - label_mask) * labels[perm]
+    return images, labels
+
+
 def softmax_cross_entropy(logits: np.ndarray, labels: np.ndarray) -> np.ndarray:
     """optax.softmax_cross_entropy (src/finetuning.py:40,98): ``-sum(labels * log_softmax(logits), -1)`` with
     jax.nn.log_softmax = shifted - log(sum(exp(shifted))), shifted = logits - max(logits)."""

@@ -674,3 +674,33 @@ def test_softmax_ce_eval_mode_and_errors(ops):
         ops.softmax_ce(dev(torch.from_numpy(logits)), dev(torch.from_numpy(idx)), label_smoothing=1.5)
     with pytest.raises(JmError, match="8192"):
         ops.softmax_ce(torch.zeros(2, 9000, device="cuda"), torch.zeros(2, dtype=torch.int32, device="cuda"))
+
+
+@pytest.mark.parametrize("mode", ["mixup", "cutmix"])
+def test_patchify_mix_matches_oracle(ops, mode):
+    """jm_patchify_mix against Mixup.apply_mixup / apply_cutmix of the oracle on the normalised images, followed by
+    extract_patches: exact after the same bf16 rounding (the mix is done in f32 with the array ops' roundings)."""
+    S, p, J, B = 32, 8, 3, 5
+    N, P, ld = (S // p) ** 2, p * p * 3, 200
+    g = torch.Generator().manual_seed(4)
+    images = torch.randint(0, 256, (B, 3, S, S), generator=g, dtype=torch.uint8)
+    perm = np.array([3, 0, 4, 1, 2], dtype=np.int32)
+    norm = O.preprocess(images).numpy()
+    lab = np.eye(B, dtype=np.float32)
+    out = torch.full((B * (J + N), ld), 7.0, dtype=BF16, device="cuda")
+    if mode == "mixup":
+        ratio = 0.3
+        mixed, _ = O.apply_mixup(norm, lab, ratio, perm)
+        ops.patchify_mix(dev(images), p, None, N, J + N, J, out, dev(torch.from_numpy(perm)), ratio=ratio)
+    else:
+        xm, ym, _ = O.random_bounding_box(0.6, 0.4, 0.7, S, S)
+        assert 0 < xm.sum() < S and 0 < ym.sum() < S
+        mixed, _ = O.apply_cutmix(norm, lab, 0.6, 0.4, 0.7, perm)
+        ops.patchify_mix(dev(images), p, None, N, J + N, J, out, dev(torch.from_numpy(perm)),
+                         xmask=dev(torch.from_numpy(xm.astype(np.uint8))), ymask=dev(torch.from_numpy(ym.astype(np.uint8))))
+    want = O.extract_patches(torch.from_numpy(mixed), p)
+    got = out.float().cpu().reshape(B, J + N, ld)
+    assert torch.equal(got[:, :J], torch.zeros(B, J, ld))
+    assert torch.equal(got[:, J:, P:], torch.zeros(B, N, ld - P))
+    assert torch.equal(got[:, J:, :P], want.to(BF16).float())
+    assert not torch.equal(got[:, J:, :P], O.extract_patches(torch.from_numpy(norm), p).to(BF16).float())

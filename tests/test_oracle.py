@@ -254,3 +254,18 @@ def test_finetune_metrics_mixup_and_eval_modes():
     assert np.array_equal(e["labels"], np.eye(6, dtype=np.float32)[[1, 4]])
     g = O.softmax_ce_grad(lg, m["labels"])
     assert np.allclose(g.sum(-1), 0, atol=1e-7)      # labels sum to one -> every gradient row sums to zero
+
+
+def test_cutmix_box_and_label_ratio():
+    """random_bounding_box (src/utils.py:85-92): ratio 0.75 -> a box of half the side; the label weight of the pasted
+    image is the box's share of the pixels; mixup with ratio 1 is the identity."""
+    xm, ym, mask = O.random_bounding_box(0.75, 0.5, 0.5, 9, 9)
+    assert xm.tolist() == [False, False, True, True, True, True, False, False, False]      # 0.25 <= x/8 < 0.75
+    assert mask.shape == (1, 9, 9, 1) and (~mask).sum() == 16
+    img = np.arange(2 * 9 * 9 * 3, dtype=np.float32).reshape(2, 9, 9, 3)
+    lab = np.eye(2, dtype=np.float32)
+    out, l2 = O.apply_cutmix(img, lab, 0.75, 0.5, 0.5, [1, 0])
+    assert np.array_equal(out[0, 3, 3], img[1, 3, 3]) and np.array_equal(out[0, 0, 0], img[0, 0, 0])
+    assert np.allclose(l2[0], [1 - 16 / 81, 16 / 81], atol=1e-6)
+    same, l3 = O.apply_mixup(img, lab, 1.0, [1, 0])
+    assert np.array_equal(same, img) and np.array_equal(l3, lab)
