@@ -26,7 +26,7 @@ import torch
 
 from . import _lib, ops
 from .config import MAEConfig
-from .params import ParamStore
+from .params import ParamStore, get_layer_index
 
 F32, BF16 = torch.float32, torch.bfloat16
 LN_EPS = 1e-6   # flax.linen.LayerNorm default
@@ -457,9 +457,16 @@ class MAEEngine:
         return self.loss
 
     # ------------------------------------------------------------------ optimizer
-    def adamw_step(self, count: int, lr: float, grad_scale: float = 1.0) -> None:
-        """optax.adamw update number ``count`` (0-based) over the flat buffers (src/pretraining.py:223-234)."""
+    def adamw_step(self, count: int, lr: float, grad_scale: float = 1.0, lr_decay: float = 1.0) -> None:
+        """optax.adamw update number ``count`` (0-based) over the flat buffers (src/pretraining.py:223-234).
+        ``lr_decay < 1``: the layer-wise scale table chained behind it (:235-242) — the leaves of label i
+        (params.get_layer_index) take the step with ``lr * lr_decay ** (layers - i)``, one range list per label."""
         cfg, ps = self.cfg, self.ps
+        if lr_decay < 1.0:
+            for i in range(cfg.layers + 1):
+                ranges = ps.ranges(lambda n, i=i: get_layer_index(n, cfg.layers) == i)
+                self.adamw_ranges(ranges, count, lr * lr_decay ** (cfg.layers - i), grad_scale)
+            return
         t = count + 1
         ops.adamw(ps.p, ps.g, ps.m, ps.v, ps.p16, ps.n_decay, lr, cfg.adam_b1, cfg.adam_b2, cfg.adam_eps,
                   cfg.weight_decay, 1.0 - cfg.adam_b1 ** t, 1.0 - cfg.adam_b2 ** t, grad_scale)

@@ -16,6 +16,7 @@ Layout rules
 """
 from __future__ import annotations
 
+import re
 from dataclasses import dataclass
 from typing import Dict, List, Tuple
 
@@ -88,6 +89,19 @@ def _leaves(cfg: MAEConfig) -> List[Leaf]:
     kernel("decoder_image_output/kernel", dd, P)
     vec("decoder_image_output/bias", P)
     return out
+
+
+def get_layer_index(name: str, num_layers: int) -> int:
+    """get_layer_index_fn (src/utils.py:142-147) on a '/'-joined leaf path: ``model/layer_k/...`` -> k + 1,
+    ``model/embed/...`` -> 0, every other leaf (CLS tokens, shared Jumbo MLP, final norm, decoder, heads) ->
+    ``num_layers``.  Label i is updated with the learning rate times ``lr_decay ** (num_layers - i)``
+    (src/pretraining.py:235-242, src/finetuning.py:241-248)."""
+    parts = name.split("/")
+    if parts[0] == "model" and len(parts) > 1 and parts[1].startswith("layer_"):
+        return int(re.match(r"layer_(\d+)", parts[1]).group(1)) + 1
+    if parts[0] == "model" and len(parts) > 1 and parts[1] == "embed":
+        return 0
+    return num_layers
 
 
 class ParamStore:

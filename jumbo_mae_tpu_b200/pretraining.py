@@ -63,6 +63,7 @@ class TrainState:
     engines: Dict[int, MAEEngine] = field(default_factory=dict)
     reducer: Optional[GradReducer] = None
     _noise_gen: Optional[np.random.Generator] = None
+    lr_decay: float = 1.0       # --lr-decay: layer-wise learning-rate scale table behind adamw (src/pretraining.py:235-242)
     clip_grad: float = 0.0      # --clip-grad: optax.clip_by_global_norm in front of adamw (src/pretraining.py:243-244)
 
     @property
@@ -150,8 +151,6 @@ def create_train_state(args: argparse.Namespace) -> TrainState:
     _lib.require_device()
     if getattr(args, "optimizer", "adamw") != "adamw":
         raise NotImplementedError("only --optimizer adamw (both pre-training presets) is on the hot path")
-    if getattr(args, "lr_decay", 1.0) < 1.0:
-        raise NotImplementedError("--lr-decay < 1 (layer-wise decay, a fine-tuning option) is not built")
     for nm in ("dropout", "droppath", "dec_dropout", "dec_droppath"):
         if getattr(args, nm, 0.0) != 0.0:
             raise NotImplementedError(f"--{nm.replace('_', '-')} > 0 is not built (0.0 in both presets)")
@@ -176,7 +175,8 @@ def create_train_state(args: argparse.Namespace) -> TrainState:
                       mixup_rng=getattr(args, "mixup_seed", 0) + process_index(),
                       dropout_rng=getattr(args, "dropout_seed", 0) + process_index(),
                       noise_rng=getattr(args, "noise_seed", 0) + process_index(),
-                      micro_step=0, micro_in_mini=cfg.grad_accum, clip_grad=float(getattr(args, "clip_grad", 0.0)))
+                      micro_step=0, micro_in_mini=cfg.grad_accum, clip_grad=float(getattr(args, "clip_grad", 0.0)),
+                      lr_decay=float(getattr(args, "lr_decay", 1.0)))
 
 
 def init_params_(store: ParamStore, seed: int) -> None:
@@ -235,7 +235,7 @@ def training_step(state: TrainState, batch, noise=None) -> Tuple[TrainState, Dic
         # gradient all-reduce overlapped with the backward pass (lax.pmean(grads), :150); without gradient clipping
         # (which needs the global norm) each segment's parameters are also updated as soon as its sum has arrived
         hook = None
-        if state.clip_grad == 0 and state.reducer.stream is not None:
+        if state.clip_grad == 0 and state.lr_decay >= 1.0 and state.reducer.stream is not None:
             lr_now, cnt = lr_schedule(state.step, state.cfg), state.step
             hook = lambda ranges: eng.adamw_ranges(ranges, cnt, lr_now, grad_scale=1.0 / (accum * world))
             updated = True
@@ -260,7 +260,7 @@ def training_step(state: TrainState, batch, noise=None) -> Tuple[TrainState, Dic
                 state._sumsq = torch.zeros(1, dtype=torch.float32, device=state.store.device)
             ops.clip_by_global_norm(state.store.g, 1.0 / (accum * world), state.clip_grad, state._sumsq)
         if not updated:
-            eng.adamw_step(state.step, lr, grad_scale=1.0 / (accum * world))
+            eng.adamw_step(state.step, lr, grad_scale=1.0 / (accum * world), lr_decay=state.lr_decay)
         state.step += 1
         state.micro_step = 0
     return state, {"loss": metrics_loss[0], "learning_rate": lr}

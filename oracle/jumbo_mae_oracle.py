@@ -59,6 +59,7 @@ class MAEConfig:
     learning_rate: float = 1.5e-4
     train_batch_size: int = 4096
     weight_decay: float = 0.05
+    lr_decay: float = 1.0            # < 1: layer-wise lr scale lr_decay ** (layers - label) behind adamw (src/pretraining.py:235-242)
     clip_grad: float = 0.0           # optax.clip_by_global_norm in front of adamw when > 0 (src/pretraining.py:243-244)
     adam_b1: float = 0.9
     adam_b2: float = 0.95
@@ -465,6 +466,23 @@ def lr_schedule(count: int, cfg: MAEConfig) -> float:
     return peak * ((1.0 - alpha) * cosine + alpha)
 
 
+def get_layer_index(path: Tuple[str, ...], num_layers: int) -> int:
+    """get_layer_index_fn, src/utils.py:142-147: ``model/layer_k`` -> k + 1, ``model/embed`` -> 0, else num_layers."""
+    if path[0] == "model" and path[1].startswith("layer_"):
+        return int(path[1][len("layer_"):]) + 1
+    if path[0] == "model" and path[1] == "embed":
+        return 0
+    return num_layers
+
+
+def layerwise_scale(path: Tuple[str, ...], cfg: MAEConfig) -> float:
+    """optax.multi_transform(layerwise_scales, label_fn) chained behind adamw (src/pretraining.py:235-242): the final
+    update of a leaf is multiplied by ``lr_decay ** (layers - label)``; 1.0 when --lr-decay is 1."""
+    if cfg.lr_decay >= 1.0:
+        return 1.0
+    return cfg.lr_decay ** (cfg.layers - get_layer_index(path, cfg.layers))
+
+
 def adamw_leaf(p, g, m, v, count: int, lr: float, cfg: MAEConfig, decay: bool):
     """One optax.adamw leaf update, ``count`` = number of updates already applied.
 
@@ -537,7 +555,7 @@ def training_step(state: OracleState, images_u8, noise, grads_override: Tree | N
     new_p, new_m, new_v = {}, {}, {}
 
     def upd(p, g, m, v, path):
-        return adamw_leaf(p, g, m, v, state.step, lr, cfg, decay=(path[-1] == "kernel"))
+        return adamw_leaf(p, g, m, v, state.step, lr * layerwise_scale(path, cfg), cfg, decay=(path[-1] == "kernel"))
 
     def walk(pt, gt, mt, vt, np_, nm, nv, prefix=()):
         for k in pt.keys():

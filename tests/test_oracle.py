@@ -269,3 +269,24 @@ def test_cutmix_box_and_label_ratio():
     assert np.allclose(l2[0], [1 - 16 / 81, 16 / 81], atol=1e-6)
     same, l3 = O.apply_mixup(img, lab, 1.0, [1, 0])
     assert np.array_equal(same, img) and np.array_equal(l3, lab)
+
+
+def test_layer_index_labels_and_scales():
+    """get_layer_index_fn (src/utils.py:142-147) and the scale table of src/pretraining.py:235-242."""
+    import dataclasses
+    cfg = dataclasses.replace(O.vit_b16(), lr_decay=0.75)
+    assert O.get_layer_index(("model", "embed", "wte", "kernel"), 12) == 0
+    assert O.get_layer_index(("model", "layer_0", "attn", "wq", "kernel"), 12) == 1
+    assert O.get_layer_index(("model", "layer_11", "norm3", "scale"), 12) == 12
+    for path in (("model", "jumbo_mlp", "w1", "kernel"), ("model", "cls_tokens"), ("model", "norm", "scale"),
+                 ("decoder_model", "dec_layer_3", "ff", "w2", "bias"), ("image_mask_embedding",), ("decoder_proj", "kernel")):
+        assert O.get_layer_index(path, 12) == 12 and O.layerwise_scale(path, cfg) == 1.0
+    assert O.layerwise_scale(("model", "embed", "wte", "bias"), cfg) == 0.75 ** 12
+    assert O.layerwise_scale(("model", "layer_5", "ff", "w1", "kernel"), cfg) == 0.75 ** 6
+    assert O.layerwise_scale(("model", "embed", "wte", "bias"), O.vit_b16()) == 1.0
+
+
+def test_product_layer_index_matches_oracle():
+    from jumbo_mae_tpu_b200.params import get_layer_index
+    for path, _ in O.tree_leaves(O.init_params(O.tiny())):
+        assert get_layer_index("/".join(path), 7) == O.get_layer_index(path, 7)

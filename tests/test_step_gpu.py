@@ -321,3 +321,71 @@ def test_adamw_by_segment_ranges_equals_whole_buffer_update():
     assert covered == store.total
     for a, b in zip(want, (store.p, store.m, store.v, store.p16)):
         assert torch.equal(a, b)
+
+
+def test_layerwise_lr_decay_scales_every_leaf_by_its_label():
+    """--lr-decay < 1 (src/pretraining.py:235-242): same gradients, same moments, and every leaf's parameter step is
+    the plain AdamW step times lr_decay ** (layers - get_layer_index(leaf)).  The oracle's AdamW with the same
+    gradients gives the same parameters (f32 update arithmetic: rel 1e-6 of the step)."""
+    import dataclasses
+    ocfg, cfg, state, images, noise, store, eng = _setup("mid")
+    eng.forward(images.cuda(), torch.from_numpy(noise).cuda())
+    eng.backward()
+    p0, m0, v0 = store.p.clone(), store.m.clone(), store.v.clone()
+    eng.adamw_step(3, 1e-3, grad_scale=0.5)
+    p1, m1, v1 = store.p.clone(), store.m.clone(), store.v.clone()
+    store.p.copy_(p0), store.m.copy_(m0), store.v.copy_(v0)
+    eng.adamw_step(3, 1e-3, grad_scale=0.5, lr_decay=0.75)
+    assert torch.equal(store.m, m1) and torch.equal(store.v, v1)
+    scales = set()
+    for name, leaf in store.leaves.items():
+        sl = slice(leaf.offset, leaf.offset + leaf.size)
+        scale = O.layerwise_scale(tuple(name.split("/")), dataclasses.replace(ocfg, lr_decay=0.75))
+        scales.add(scale)
+        plain, decayed = (p1[sl] - p0[sl]).double(), (store.p[sl] - p0[sl]).double()
+        # the steps are differences of f32 parameters: compare with an absolute slack of a few ulp of the parameter
+        slack = 4 * torch.finfo(torch.float32).eps * p0[sl].abs().max().item()
+        assert (decayed - scale * plain).abs().max().item() <= slack + 1e-6 * plain.abs().max().item(), name
+        assert torch.equal(store.p16[sl], store.p[sl].to(torch.bfloat16)), name
+    assert len(scales) == ocfg.layers + 1 and min(scales) == 0.75 ** ocfg.layers and max(scales) == 1.0
+    # against the oracle's optimizer with the engine's own gradients
+    from jumbo_mae_tpu_b200.params import tree_leaves
+    grads = {}
+    for path, g in tree_leaves(store.tree(store.g)):
+        node = grads
+        for k in path[:-1]:
+            node = node.setdefault(k, {})
+        node[path[-1]] = g.detach().cpu().clone() * 0.5
+    dcfg = dataclasses.replace(ocfg, lr_decay=0.75)
+    want = {}
+    for path, p in O.tree_leaves(state.params):
+        g = grads
+        for k in path:
+            g = g[k]
+        newp, _, _ = O.adamw_leaf(p, g.reshape(p.shape), torch.zeros_like(p), torch.zeros_like(p), 3,
+                                  1e-3 * O.layerwise_scale(path, dcfg), dcfg, decay=(path[-1] == "kernel"))
+        want[path] = newp
+    got = dict(tree_leaves(store.tree(store.p)))
+    for path, w in want.items():
+        step = (w - dict(O.tree_leaves(state.params))[path]).abs().max().item()
+        assert (got[path].detach().cpu().reshape(w.shape) - w).abs().max().item() <= 1e-3 * step + 1e-7, path
+
+
+def test_training_step_accepts_lr_decay():
+    """create_train_state(--lr-decay 0.75) builds and steps; the embedding moves less than with --lr-decay 1."""
+    from jumbo_mae_tpu_b200.pretraining import create_train_state, training_step
+    ocfg = O.tiny()
+    ostate = O.create_state(ocfg, seed=0, randomize_all=True)
+    images, noise = O.synthetic_batch(ocfg, 4, seed=5, noise_seed=6)
+    moved = {}
+    for decay in (1.0, 0.5):
+        state = create_train_state(_tiny_args(lr_decay=decay)).replicate()
+        state.store.load_tree(ostate.params)
+        before = state.store.f("model/embed/wte/kernel").clone()
+        top = state.store.f("decoder_proj/kernel").clone()
+        state, m = training_step(state, (images.pin_memory(),), noise=noise)
+        moved[decay] = ((state.store.f("model/embed/wte/kernel") - before).norm().item(),
+                        (state.store.f("decoder_proj/kernel") - top).norm().item())
+    L = ocfg.layers
+    assert abs(moved[0.5][0] / moved[1.0][0] - 0.5 ** L) <= 5e-3 * 0.5 ** L      # f32 rounding of p at steps of 1e-6
+    assert abs(moved[0.5][1] / moved[1.0][1] - 1.0) <= 1e-4
