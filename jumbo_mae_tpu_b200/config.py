@@ -33,6 +33,7 @@ class MAEConfig:
     warmup_steps: int = 1281167 * 40 // 4096
     training_steps: int = 1281167 * 1600 // 4096
     grad_accum: int = 1
+    labels: int = 0                    # > 0: classification mode (ViT head, no masking, no decoder; src/modeling.py:239-242,252)
 
     @property
     def grid(self) -> int:
@@ -43,11 +44,15 @@ class MAEConfig:
         return self.grid * self.grid
 
     @property
-    def keep(self) -> int:             # src/modeling.py:255
+    def keep(self) -> int:             # src/modeling.py:255 (MAE mode); every patch in classification mode
+        if self.labels > 0:
+            return self.num_patches
         return int(self.num_patches * (1.0 - self.image_mask_ratio))
 
     @property
     def num_masked(self) -> int:       # src/pretraining.py:101
+        if self.labels > 0:
+            return 0
         return int(self.num_patches * self.image_mask_ratio)
 
     @property

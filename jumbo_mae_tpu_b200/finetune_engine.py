@@ -1,0 +1,144 @@
+"""Fine-tune / classification step on the encoder kernels of the pre-training engine.
+
+``FinetuneModule.__call__`` + ``ViT.__call__`` with ``labels > 0`` (src/finetuning.py:84-106, src/modeling.py:245-274):
+no masking, all ``N`` patches + ``J`` CLS tokens through the JumboLayers, final LayerNorm, ``LinearCLS`` on the
+concatenated CLS tokens, softmax cross-entropy on smoothed / mixed labels, top-1 / top-5 flags.  Everything between
+the patch rows and the logits is the schedule of ``engine.MAEEngine`` at ``T = J + N``; the two ends are
+``jm_patchify`` / ``jm_patchify_mix`` and ``jm_softmax_ce``; the head is one ``jm_gemm`` over the strided CLS rows.
+
+Built: forward, loss, metrics, backward (all parameter gradients), AdamW with the layer-wise lr table
+(``adamw_step(..., lr_decay=0.75)``).  Not built (``create``-time options of the fine-tune recipe): DropPath 0.1,
+BatchNorm in the head (linear probing), LARS / LAMB / SGD; RNG draws (beta sample, permutation, box) are caller data.
+"""
+from __future__ import annotations
+
+from typing import List, Optional
+
+import torch
+
+from . import _lib, ops
+from .config import MAEConfig
+from .engine import BF16, F32, LN_EPS, MAEEngine, _Block, fixed_sincos2d_embeddings
+from .params import ParamStore
+
+HEAD = "model/head/Dense_0"     # LinearCLS is nn.compact around one nn.Dense (src/modeling.py:214-219)
+
+
+class FinetuneEngine(MAEEngine):
+    """Buffers + kernel schedule of the classification step for one per-device batch size."""
+
+    def __init__(self, cfg: MAEConfig, store: ParamStore, batch: int):
+        _lib.require_device()
+        cfg.validate()
+        if cfg.labels <= 0:
+            raise _lib.JmError("FinetuneEngine needs cfg.labels > 0 (classification mode)")
+        if cfg.labels % 8:
+            raise _lib.JmError("labels must be a multiple of 8 (16-byte rows of the bf16 logits gradient)")
+        self.cfg, self.ps, self.B = cfg, store, batch
+        dev = store.device
+        self.dev = dev
+        B, J, N, d, P, C = batch, cfg.num_cls_tokens, cfg.num_patches, cfg.dim, cfg.patch_dim, cfg.labels
+        self.Te = self.Td = J + N
+        self.Me = self.Md = B * self.Te
+        self.Pp = (P + 7) // 8 * 8
+        Me = self.Me
+        e = lambda *s, dt=BF16: torch.empty(*s, dtype=dt, device=dev)
+
+        self.wpe = fixed_sincos2d_embeddings(cfg.grid, cfg.grid, d).reshape(N, d).contiguous().to(dev)
+        self.ids_all = torch.arange(N, dtype=torch.int32, device=dev)
+        self.patches = e(Me, self.Pp)
+        self.xa: List[torch.Tensor] = [e(Me, d, dt=F32) for _ in range(cfg.layers + 1)]
+        self.enc = [_Block(Me, d, cfg.heads, B, self.Te, J, True, dev) for _ in range(cfg.layers)]
+        L, Jd = cfg.layers, J * d
+        self.cn16_all, self.gj_all = e(L * B, Jd), e(L * B, 4 * Jd)
+        self.dhj16_all, self.dc16_all = e(L * B, 4 * Jd), e(L * B, Jd)
+        for i, blk in enumerate(self.enc):
+            blk.cn16, blk.gj = self.cn16_all[i * B:(i + 1) * B], self.gj_all[i * B:(i + 1) * B]
+            blk.dhj16, blk.dc16 = self.dhj16_all[i * B:(i + 1) * B], self.dc16_all[i * B:(i + 1) * B]
+        self.meanF, self.rstdF = e(Me, dt=F32), e(Me, dt=F32)
+        self.enc_n = e(Me, d)
+        # head + loss
+        self.logits = e(B, C, dt=F32)
+        self.dlogits, self.dlog16 = e(B, C, dt=F32), e(B, C)
+        self.loss_rows, self.acc1, self.acc5 = e(B, dt=F32), e(B, dt=F32), e(B, dt=F32)
+        self.metrics = torch.zeros(3, dtype=F32, device=dev)      # mean loss, acc1, acc5
+        self.loss = self.metrics[0:1]
+        # backward scratch
+        w = Me * d
+        self.dxA, self.dxB = e(w, dt=F32), e(w, dt=F32)
+        self.dxA16, self.dxB16 = e(w), e(w)
+        self.dh16, self.dn16, self.dqkv16, self.datt16 = e(4 * w), e(w), e(3 * w), e(w)
+        self.delta_ws = None
+        self.dcn16 = e(B, Jd)
+        ln_ws = max(ops.layernorm_bwd_workspace(Me, d), ops.layernorm_bwd_workspace(B, Jd))
+        self.ln_ws = torch.empty(ln_ws, dtype=torch.uint8, device=dev)
+
+    # ------------------------------------------------------------------ forward
+    def forward(self, images: torch.Tensor, labels: torch.Tensor, *, label_smoothing: float = 0.0,
+                perm: Optional[torch.Tensor] = None, ratio: float = 1.0, label_ratio: Optional[float] = None,
+                xmask: Optional[torch.Tensor] = None, ymask: Optional[torch.Tensor] = None,
+                want_grad: bool = True, grad_scale: float = 1.0) -> torch.Tensor:
+        """images uint8 [B,3,H,W], labels int32 [B] or f32 [B, C] (device) -> mean loss (device tensor [1]);
+        ``metrics`` = (loss, acc1, acc5) batch means, ``logits`` f32 [B, C].
+
+        Training (det=False, src/finetuning.py:93-95): ``label_smoothing`` and, with ``perm``, Mixup
+        (``ratio`` = the beta sample) or CutMix (``xmask`` / ``ymask`` = the box, ``label_ratio`` = the mean of the
+        image mask).  Evaluation: defaults."""
+        cfg, ps, B = self.cfg, self.ps, self.B
+        J, N, d, P, C, Te, Me = cfg.num_cls_tokens, cfg.num_patches, cfg.dim, cfg.patch_dim, cfg.labels, self.Te, self.Me
+        if tuple(images.shape) != (B, 3, cfg.image_size, cfg.image_size):
+            raise _lib.JmError(f"engine built for images {(B, 3, cfg.image_size, cfg.image_size)}, got {tuple(images.shape)}")
+        self.images = images
+        # pre-processing (+ Mixup / CutMix) + patch extraction (src/finetuning.py:87-88,95)
+        if perm is None:
+            ops.patchify(images, cfg.patch_size, None, N, Te, J, self.patches)
+        else:
+            ops.patchify_mix(images, cfg.patch_size, None, N, Te, J, self.patches, perm, ratio=ratio, xmask=xmask,
+                             ymask=ymask)
+        x0 = self.xa[0]
+        ops.fill_cls(x0, B, Te, J, d, ps.f("model/cls_tokens"))
+        self._fwd_linear(self.patches, Me, "model/embed/wte", d, P, lda=self.Pp, out_f32=x0, pe=self.wpe,
+                         pe_idx=self.ids_all, row_period=Te, row_skip=J, row_mask_mode=2)
+        for i in range(cfg.layers):
+            self._block_fwd(f"model/layer_{i}", self.enc[i], self.xa[i], self.xa[i + 1], Me, d, cfg.heads, Te, True)
+        ops.layernorm_fwd(self.xa[cfg.layers], ps.f("model/norm/scale"), ps.f("model/norm/bias"), LN_EPS,
+                          self.enc_n, None, self.meanF, self.rstdF)
+        # LinearCLS on x[:, :J].reshape(B, J*d) (src/modeling.py:272-274): the CLS rows are the first J of every
+        # image's block, i.e. a [B, J*d] view with row stride Te*d
+        ops.gemm(self.enc_n, self._W(f"{HEAD}/kernel"), B, C, J * d, b_mn=True, lda=Te * d,
+                 ldb=ps.ld(f"{HEAD}/kernel"), bias=self._b(f"{HEAD}/bias"), out_f32=self.logits)
+        soft = labels if labels.dim() == 2 else None
+        idx = labels if labels.dim() == 1 else None
+        ops._chk(soft, F32, "labels"), ops._chk(idx, torch.int32, "labels"), ops._chk(perm, torch.int32, "perm")
+        lr = ratio if label_ratio is None else label_ratio
+        _lib.check(_lib.load().jm_softmax_ce(
+            _lib.ptr(self.logits), _lib.ptr(soft), _lib.ptr(idx), _lib.ptr(perm), lr, float(label_smoothing), B, C,
+            grad_scale / B, _lib.ptr(self.loss_rows), _lib.ptr(self.acc1), _lib.ptr(self.acc5), _lib.ptr(self.metrics),
+            _lib.ptr(self.dlogits) if want_grad else None, _lib.stream_ptr()))
+        return self.loss
+
+    # ------------------------------------------------------------------ backward
+    def segment_grad_ranges(self, k: int):
+        if k == 0:
+            return self.ps.ranges(lambda n: n.startswith("model/norm/") or n.startswith("model/head/"))
+        return super().segment_grad_ranges(k)
+
+    def backward_segment(self, k: int, zero_grads: bool = True) -> None:
+        if k != 0:
+            return super().backward_segment(k, zero_grads)
+        cfg, ps, B = self.cfg, self.ps, self.B
+        J, d, C, Te, Me = cfg.num_cls_tokens, cfg.dim, cfg.labels, self.Te, self.Me
+        if zero_grads:
+            ps.g.zero_()
+        # head: dW += cls^T dlogits, db += colsum, d cls = dlogits W^T into the CLS rows; patch rows get no gradient
+        ops.add_bias_cast(self.dlogits, B, C, dst_bf16=self.dlog16)
+        dn = self.dn16[:Me * d].view(Me, d)
+        dn.zero_()
+        self._bwd_linear(self.enc_n, self.dlog16, B, HEAD, C, J * d, dX16=dn, x_ld=Te * d, ldo_bf16=Te * d)
+        dx, dx16 = self.dxA[:Me * d].view(Me, d), self.dxA16[:Me * d].view(Me, d)
+        ops.layernorm_bwd(dn, self.xa[cfg.layers], self.meanF, self.rstdF, ps.f("model/norm/scale"), None, dx, dx16,
+                          ps.grad("model/norm/scale"), ps.grad("model/norm/bias"), self.ln_ws,
+                          dcol=ps.grad(f"model/layer_{cfg.layers - 1}/ff/w2/bias"), dcol_period=Te, dcol_skip=J)
+
+    def capture_graphs(self) -> None:
+        raise NotImplementedError("CUDA-graph capture of the classification step is not built yet: run it eagerly")

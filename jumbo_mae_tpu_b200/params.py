@@ -79,6 +79,11 @@ def _leaves(cfg: MAEConfig) -> List[Leaf]:
         block(f"model/layer_{i}", d, True)
     vec("model/norm/scale", d)
     vec("model/norm/bias", d)
+    if cfg.labels > 0:
+        # classification mode: LinearCLS on the concatenated CLS tokens (src/modeling.py:209-219,236-240), no decoder
+        kernel("model/head/Dense_0/kernel", J * d, cfg.labels)
+        vec("model/head/Dense_0/bias", cfg.labels)
+        return out
     for i in range(cfg.dec_layers):
         block(f"decoder_model/dec_layer_{i}", dd, False)
     vec("decoder_model/dec_norm/scale", dd)
@@ -201,6 +206,9 @@ class ParamStore:
             p = f"model/layer_{i}"
             model[f"layer_{i}"] = {"attn": attn(f"{p}/attn", cfg.dim, cfg.heads), "ff": ff(f"{p}/ff"),
                                    "norm1": ln(f"{p}/norm1"), "norm2": ln(f"{p}/norm2"), "norm3": ln(f"{p}/norm3")}
+        if cfg.labels > 0:
+            model["head"] = {"Dense_0": {"kernel": k("model/head/Dense_0/kernel"), "bias": v("model/head/Dense_0/bias")}}
+            return {"model": model}
         dec = {"dec_norm": ln("decoder_model/dec_norm")}
         for i in range(cfg.dec_layers):
             p = f"decoder_model/dec_layer_{i}"

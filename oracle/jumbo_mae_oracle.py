@@ -55,6 +55,7 @@ class MAEConfig:
     dec_dim: int = 512
     dec_heads: int = 16
     norm_pix_loss: bool = False      # src/main_pretrain.py:139 (off in both presets)
+    labels: int = 0                  # > 0: classification mode of ViT (src/modeling.py:236-242): head, no masking, no decoder
     # optimizer: src/pretraining.py:223-259 with the preset's flags
     learning_rate: float = 1.5e-4
     train_batch_size: int = 4096
@@ -291,6 +292,33 @@ def vit_forward(images_nhwc, p: Tree, cfg: MAEConfig, noise, collect=None):
     return x, mask, ids_restore
 
 
+def vit_classify(images_nhwc, p: Tree, cfg: MAEConfig, collect=None):
+    """ViT.__call__ with a head (labels > 0), src/modeling.py:245-274: no masking, every patch, final LayerNorm,
+    LinearCLS (no BatchNorm: batch_norm is a linear-probing option) on the concatenated CLS tokens -> logits."""
+    J = cfg.num_cls_tokens
+    x = patch_embed(images_nhwc, p["embed"], cfg)
+    bs = x.shape[0]
+    x = torch.cat((p["cls_tokens"].expand(bs, J, cfg.dim), x), dim=1)
+    for i in range(cfg.layers):
+        x = jumbo_layer(x, p[f"layer_{i}"], p["jumbo_mlp"], cfg.heads, J)
+    x = layer_norm(x, p["norm"]["scale"], p["norm"]["bias"])
+    if collect is not None:
+        collect["enc_out"] = x
+    x = x[:, :J, :].reshape(bs, -1)
+    return dense(x, p["head"]["Dense_0"])
+
+
+def finetune_loss_and_grads(params: Tree, images_nhwc, labels_soft, cfg: MAEConfig):
+    """loss_fn of src/finetuning.py:109-124 on already mixed images / prepared labels: mean softmax cross-entropy of
+    FinetuneModule (:98) and its gradient (jax.value_and_grad -> torch.autograd).  Returns (loss, logits, grads)."""
+    leaves = tree_map(lambda t: t.detach().clone().requires_grad_(True), params)
+    logits = vit_classify(torch.as_tensor(images_nhwc), leaves["model"], cfg)
+    lab = torch.as_tensor(labels_soft, dtype=logits.dtype)
+    loss = (-(lab * torch.log_softmax(logits, dim=-1)).sum(-1)).mean()
+    loss.backward()
+    return loss.detach(), logits.detach(), tree_map(lambda t: t.grad if t.grad is not None else torch.zeros_like(t), leaves)
+
+
 def decoder_forward(x, p: Tree, cfg: MAEConfig, collect=None):
     """MAEDecoder.__call__, src/modeling.py:286-298 (always sincos dec_wpe)."""
     J = cfg.num_cls_tokens
@@ -396,6 +424,16 @@ def init_params(cfg: MAEConfig, seed: int = 0, dtype=torch.float32, randomize_al
                                "norm1": _ln_p(d, dtype), "norm2": _ln_p(d, dtype),
                                "norm3": _ln_p(J * d, dtype)}
     model["norm"] = _ln_p(d, dtype)
+    if cfg.labels > 0:               # LinearCLS (src/modeling.py:209-219): nn.compact around one Dense -> "Dense_0"
+        model["head"] = {"Dense_0": _dense_p(gen, J * d, cfg.labels, dtype)}
+        params = {"model": model}
+        if randomize_all:
+            for path, leaf in tree_leaves(params):
+                if path[-1] in ("bias", "cls_tokens"):
+                    leaf.add_(_tn(gen, tuple(leaf.shape), dtype))
+                elif path[-1] == "scale":
+                    leaf.add_(_tn(gen, tuple(leaf.shape), dtype) * 5.0)
+        return params
     dd = cfg.dec_dim
     dec: Tree = {}
     for i in range(cfg.dec_layers):

@@ -1,0 +1,139 @@
+"""GPU parity tests of the classification (fine-tune) step, SURVEY.md 8(f) rank 1: FinetuneEngine against the CPU
+oracle's vit_classify / finetune_loss_and_grads (src/finetuning.py:84-124, src/modeling.py:245-274) on the same
+parameters, images, labels and Mixup / CutMix draws.  Tolerances (bf16 kernels vs f32 oracle) beside each assert."""
+import dataclasses
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import jumbo_mae_oracle as O
+
+pytestmark = pytest.mark.gpu
+
+
+def _rel(a, b):
+    return ((a - b).norm() / (b.norm() + 1e-12)).item()
+
+
+def _cfgs():
+    return {
+        "tiny": (O.tiny(labels=16), 4),
+        "mid": (O.MAEConfig(layers=2, dim=256, heads=4, patch_size=16, image_size=64, labels=40, warmup_steps=10,
+                            training_steps=100, train_batch_size=256), 8),
+    }
+
+
+def _setup(name):
+    from jumbo_mae_tpu_b200.config import MAEConfig
+    from jumbo_mae_tpu_b200.finetune_engine import FinetuneEngine
+    from jumbo_mae_tpu_b200.params import ParamStore
+    ocfg, B = _cfgs()[name]
+    cfg = MAEConfig(**{f: getattr(ocfg, f) for f in MAEConfig.__dataclass_fields__ if hasattr(ocfg, f)})
+    params = O.init_params(ocfg, seed=0, randomize_all=True)
+    images, _ = O.synthetic_batch(ocfg, B, seed=1)
+    store = ParamStore(cfg)
+    store.load_tree(params)
+    return ocfg, cfg, params, images, store, FinetuneEngine(cfg, store, B)
+
+
+@pytest.mark.parametrize("name,mode", [("tiny", "plain"), ("tiny", "mixup"), ("tiny", "cutmix"), ("mid", "mixup")])
+def test_classification_step_matches_oracle(name, mode):
+    from jumbo_mae_tpu_b200.params import tree_leaves
+    ocfg, cfg, params, images, store, eng = _setup(name)
+    B, C, S = images.shape[0], ocfg.labels, ocfg.image_size
+    rng = np.random.default_rng(3)
+    idx = rng.integers(0, C, B).astype(np.int32)
+    perm = rng.permutation(B).astype(np.int32)
+    norm = O.preprocess(images).numpy()
+    onehot = O.smooth_labels(np.eye(C, dtype=np.float32)[idx], 0.1)
+    kw = {}
+    if mode == "mixup":
+        x, lab = O.apply_mixup(norm, onehot, 0.35, perm)
+        kw = dict(perm=torch.from_numpy(perm).cuda(), ratio=0.35)
+    elif mode == "cutmix":
+        xm, ym, mask = O.random_bounding_box(0.6, 0.4, 0.7, S, S)
+        x, lab = O.apply_cutmix(norm, onehot, 0.6, 0.4, 0.7, perm)
+        kw = dict(perm=torch.from_numpy(perm).cuda(), xmask=torch.from_numpy(xm.astype(np.uint8)).cuda(),
+                  ymask=torch.from_numpy(ym.astype(np.uint8)).cuda(),
+                  label_ratio=float(mask.mean((1, 2), dtype=np.float32).item()))
+    else:
+        x, lab = norm, onehot
+    want_loss, want_logits, want = O.finetune_loss_and_grads(params, x, lab, ocfg)
+    loss = eng.forward(images.cuda(), torch.from_numpy(idx).cuda(), label_smoothing=0.1, **kw)
+    eng.backward()
+    torch.cuda.synchronize()
+    logits = eng.logits.cpu()
+    assert _rel(logits, want_logits) <= 2e-2                                   # bf16 activations, f32 accumulate
+    assert abs(loss.item() - want_loss.item()) <= 5e-3 * abs(want_loss.item())
+    # metrics of the engine's own logits, exactly (top-k of the oracle's logits may differ by a bf16 near-tie)
+    m = O.finetune_metrics(logits.numpy(), idx, C, 0.1, perm=perm if mode != "plain" else None,
+                           ratio=kw.get("label_ratio", kw.get("ratio", 1.0)))
+    assert np.array_equal(eng.acc1.cpu().numpy(), m["acc1"]) and np.array_equal(eng.acc5.cpu().numpy(), m["acc5"])
+    assert np.allclose(eng.loss_rows.cpu().numpy(), m["loss"], rtol=1e-5, atol=1e-6)
+    assert np.allclose(m["labels"], lab, atol=1e-7)                            # the label matrix the oracle loss saw
+    got = dict(tree_leaves(store.tree(store.g)))
+    ref = dict(O.tree_leaves(want))
+    bad = []
+    for path, w in ref.items():
+        g = got[path].detach().cpu().reshape(w.shape)
+        if path[-2:] == ("wk", "bias"):           # identically zero gradient (softmax shift invariance): noise only
+            scale = ref[path[:-2] + ("wv", "bias")].norm().item()
+            if not (g.norm().item() <= 3e-2 * scale and w.norm().item() <= 1e-3 * scale):
+                bad.append(("/".join(path), g.norm().item(), scale))
+            continue
+        if w.norm().item() == 0.0:
+            # only the CLS rows reach the head: the last layer's patch FFN (and its norm2) has an exactly zero gradient
+            assert path[1] == f"layer_{ocfg.layers - 1}" and path[2] in ("ff", "norm2"), path
+            if g.norm().item() != 0.0:
+                bad.append(("/".join(path), g.norm().item(), 0.0))
+            continue
+        r = _rel(g, w)
+        cos = (g.flatten() @ w.flatten() / (g.norm() * w.norm() + 1e-20)).item()
+        if not (r <= 3e-2 and cos >= 0.999):
+            bad.append(("/".join(path), r, cos))
+    assert not bad, bad
+
+
+def test_classification_eval_mode_and_accumulation():
+    """det=True: no smoothing, no mixing, no gradient buffer written; backward accumulates like the MAE engine."""
+    ocfg, cfg, params, images, store, eng = _setup("tiny")
+    idx = torch.tensor([1, 5, 9, 2], dtype=torch.int32, device="cuda")
+    eng.dlogits.fill_(7.0)
+    loss = eng.forward(images.cuda(), idx, want_grad=False)
+    want = O.vit_classify(O.preprocess(images), params["model"], ocfg)
+    m = O.finetune_metrics(eng.logits.cpu().numpy(), idx.cpu().numpy(), ocfg.labels, det=True)
+    assert _rel(eng.logits.cpu(), want) <= 2e-2
+    assert abs(loss.item() - m["loss"].mean()) <= 1e-5 * abs(loss.item())
+    assert torch.all(eng.dlogits == 7.0)
+    eng.forward(images.cuda(), idx, label_smoothing=0.1)
+    eng.backward()
+    g1 = store.g.clone()
+    eng.forward(images.cuda(), idx, label_smoothing=0.1)
+    eng.backward(zero_grads=False)
+    assert (store.g - 2 * g1).norm().item() <= 4e-3 * g1.norm().item()
+
+
+def test_classification_step_at_vit_b_width():
+    """ViT-B/16 width at 224 px (T = 199 tokens, head_dim 64, 1000 classes), one layer, against the oracle."""
+    from jumbo_mae_tpu_b200.config import MAEConfig
+    from jumbo_mae_tpu_b200.finetune_engine import FinetuneEngine
+    from jumbo_mae_tpu_b200.params import ParamStore
+    ocfg = O.MAEConfig(layers=1, labels=1000, warmup_steps=10, training_steps=100)
+    cfg = MAEConfig(**{f: getattr(ocfg, f) for f in MAEConfig.__dataclass_fields__ if hasattr(ocfg, f)})
+    params = O.init_params(ocfg, seed=0, randomize_all=True)
+    images, _ = O.synthetic_batch(ocfg, 3, seed=2)
+    store = ParamStore(cfg)
+    store.load_tree(params)
+    eng = FinetuneEngine(cfg, store, 3)
+    idx = np.array([3, 999, 500], dtype=np.int32)
+    lab = O.smooth_labels(np.eye(1000, dtype=np.float32)[idx], 0.1)
+    want_loss, want_logits, want = O.finetune_loss_and_grads(params, O.preprocess(images).numpy(), lab, ocfg)
+    loss = eng.forward(images.cuda(), torch.from_numpy(idx).cuda(), label_smoothing=0.1)
+    eng.backward()
+    assert _rel(eng.logits.cpu(), want_logits) <= 2e-2
+    assert abs(loss.item() - want_loss.item()) <= 5e-3 * abs(want_loss.item())
+    gk = store.grad("model/head/Dense_0/kernel")[:, :1000].cpu()
+    assert _rel(gk, want["model"]["head"]["Dense_0"]["kernel"]) <= 3e-2
+    ge = store.grad("model/embed/wte/kernel").cpu().reshape(-1)
+    assert _rel(ge, want["model"]["embed"]["wte"]["kernel"].reshape(-1)) <= 3e-2
