@@ -140,5 +140,48 @@ class FinetuneEngine(MAEEngine):
                           ps.grad("model/norm/scale"), ps.grad("model/norm/bias"), self.ln_ws,
                           dcol=ps.grad(f"model/layer_{cfg.layers - 1}/ff/w2/bias"), dcol_period=Te, dcol_skip=J)
 
-    def capture_graphs(self) -> None:
-        raise NotImplementedError("CUDA-graph capture of the classification step is not built yet: run it eagerly")
+    # ------------------------------------------------------------------ CUDA graphs
+    def capture_graphs(self, label_smoothing: float = 0.0, mixup: bool = False) -> None:
+        """Records forward + backward of one micro-batch into two CUDA graphs (gradients zeroed first / accumulated)
+        over static input buffers: images, class indices and, with ``mixup``, the batch permutation; the Mixup ratio
+        is baked into the graph's kernel arguments, so a training loop that draws a new ratio per step runs eagerly
+        or re-captures (CutMix likewise)."""
+        cfg, B = self.cfg, self.B
+        self.images_buf = torch.empty(B, 3, cfg.image_size, cfg.image_size, dtype=torch.uint8, device=self.dev)
+        self.labels_buf = torch.zeros(B, dtype=torch.int32, device=self.dev)
+        self.perm_buf = torch.arange(B, dtype=torch.int32, device=self.dev).flip(0).contiguous() if mixup else None
+        kw = dict(label_smoothing=label_smoothing, perm=self.perm_buf, ratio=0.5 if mixup else 1.0)
+        side = torch.cuda.Stream(device=self.dev)
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):                  # eager warm-up: one-time function attributes, module load
+            self.images_buf.zero_()
+            self.forward(self.images_buf, self.labels_buf, **kw)
+            self.backward(zero_grads=True)
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+        self.graphs = {}
+        lib = _lib.load()
+        for zero in (True, False):
+            g = torch.cuda.CUDAGraph()
+            l0 = lib.jm_launch_count()
+            with torch.cuda.graph(g):
+                self.forward(self.images_buf, self.labels_buf, **kw)
+                self.backward(zero_grads=zero)
+            self.graph_launches = lib.jm_launch_count() - l0
+            self.graphs[zero] = g
+        self.ps.g.zero_()
+
+    def run_graph(self, images: torch.Tensor, labels: torch.Tensor, zero_grads: bool,
+                  perm: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """forward + backward through the captured graph; images may be a pinned host tensor."""
+        if not hasattr(self, "graphs"):
+            self.capture_graphs()
+        self.images_buf.copy_(images, non_blocking=True)
+        self.labels_buf.copy_(labels, non_blocking=True)
+        if perm is not None and self.perm_buf is not None:
+            self.perm_buf.copy_(perm, non_blocking=True)
+        self.graphs[bool(zero_grads)].replay()
+        return self.loss
+
+    def capture_segment_graphs(self) -> None:
+        raise NotImplementedError("the data-parallel overlap graphs of the classification step are not built yet")
