@@ -137,3 +137,70 @@ def test_classification_step_at_vit_b_width():
     assert _rel(gk, want["model"]["head"]["Dense_0"]["kernel"]) <= 3e-2
     ge = store.grad("model/embed/wte/kernel").cpu().reshape(-1)
     assert _rel(ge, want["model"]["embed"]["wte"]["kernel"].reshape(-1)) <= 3e-2
+
+
+def _ft_args(**kw):
+    import argparse
+    base = dict(layers=2, dim=64, heads=2, labels=16, patch_size=8, image_size=32, init_seed=0, mixup_seed=0,
+                dropout_seed=0, noise_seed=0, optimizer="adamw", criterion="ce", mode="finetune", learning_rate=1e-3,
+                weight_decay=0.05, adam_b1=0.9, adam_b2=0.999, adam_eps=1e-8, lr_decay=0.75, clip_grad=0.0,
+                grad_accum=1, warmup_steps=2, training_steps=50, posemb="sincos2d", dropout=0.0, droppath=0.0,
+                layerscale=False, label_smoothing=0.1, mixup=0.8, cutmix=1.0, pretrained_ckpt=None)
+    base.update(kw)
+    return argparse.Namespace(**base)
+
+
+@pytest.mark.parametrize("box", [None, (0.4, 0.7)])
+def test_finetuning_api_step_matches_oracle(box):
+    """create_train_state / training_step / validation_step (reference names, src/finetuning.py:108-284) with the
+    Mixup / CutMix draws given: loss against the oracle on the state's own parameters, optimizer bookkeeping,
+    validation sums over the rows whose label is not -1."""
+    from jumbo_mae_tpu_b200.finetuning import MixDraw, create_train_state, training_step, validation_step, lr_schedule
+    from jumbo_mae_tpu_b200.params import tree_leaves
+    state = create_train_state(_ft_args()).replicate()
+    ocfg = O.tiny(labels=16)
+    params = O.init_params(ocfg, seed=0, randomize_all=True)
+    state.store.load_tree(params)
+    images, _ = O.synthetic_batch(ocfg, 4, seed=5)
+    idx = np.array([1, 7, 7, 15], dtype=np.int32)
+    perm = np.array([2, 3, 1, 0], dtype=np.int32)
+    norm = O.preprocess(images).numpy()
+    lab0 = O.smooth_labels(np.eye(16, dtype=np.float32)[idx], 0.1)
+    if box is None:
+        x, lab = O.apply_mixup(norm, lab0, 0.3, perm)
+    else:
+        x, lab = O.apply_cutmix(norm, lab0, 0.3, box[0], box[1], perm)
+    want_loss, _, _ = O.finetune_loss_and_grads(params, x, lab, ocfg)
+    before = state.store.p.clone()
+    state, m = training_step(state, (images, torch.from_numpy(idx)), mix=MixDraw(perm=perm, ratio=0.3, box=box))
+    assert abs(m["loss"].item() - want_loss.item()) <= 5e-3 * abs(want_loss.item())
+    assert state.step == 1 and state.micro_step == 0
+    assert m["learning_rate"] == lr_schedule(0, state) and abs(m["learning_rate"] - 1e-6) < 1e-15   # lr(0) = init
+    assert not torch.equal(state.store.p, before)
+    # validation: det=True, one padded row
+    vidx = np.array([1, -1, 7, 15], dtype=np.int32)
+    out = validation_step(state, (images, torch.from_numpy(vidx)))
+    logits = state.engine(4).logits.cpu().numpy()
+    om = O.finetune_metrics(logits, np.where(vidx == -1, 0, vidx), 16, det=True)
+    keep = vidx != -1
+    assert out["num_samples"].item() == 3
+    assert abs(out["loss"].item() - om["loss"][keep].sum()) <= 1e-5 * abs(out["loss"].item())
+    assert out["acc1"].item() == om["acc1"][keep].sum() and out["acc5"].item() == om["acc5"][keep].sum()
+
+
+def test_finetuning_loss_goes_down_and_draws_advance():
+    """A few steps on one batch without mixing reduce the loss; the default Mixup / CutMix draws differ step to step."""
+    from jumbo_mae_tpu_b200.finetuning import create_train_state, training_step
+    state = create_train_state(_ft_args(mixup=0.0, cutmix=0.0, learning_rate=3e-3, warmup_steps=1, lr_decay=1.0)).replicate()
+    ocfg = O.tiny(labels=16)
+    images, _ = O.synthetic_batch(ocfg, 8, seed=9)
+    labels = torch.arange(8, dtype=torch.int32)
+    losses = []
+    for _ in range(12):
+        state, m = training_step(state, (images, labels))
+        losses.append(m["loss"].item())
+    assert losses[-1] < 0.7 * losses[0], losses
+    s2 = create_train_state(_ft_args()).replicate()
+    d1, d2 = s2.draw_mix(8), s2.draw_mix(8)
+    assert d1 is not None and (d1.ratio != d2.ratio or not np.array_equal(d1.perm, d2.perm))
+    assert sorted(d1.perm.tolist()) == list(range(8)) and 0.0 <= d1.ratio <= 1.0
