@@ -129,6 +129,42 @@ def load_params(state, path: str) -> None:
     state.store.load_tree(to_torch(tree))
 
 
+def load_pretrained_params(state, path: str) -> int:
+    """Fine-tuning from a pre-training checkpoint (``--pretrained-ckpt``, src/utils.py:150-202, called at
+    src/finetuning.py:215-217): the leaves of the checkpoint's ``model`` sub-tree that the classification tree also has
+    (patch embedding, CLS tokens, shared Jumbo MLP, every layer, final norm) replace the fresh initialisation; the
+    head keeps its initial values, the checkpoint's decoder leaves are ignored.  (The reference's active code returns
+    the restored tree as it is, which only works for a checkpoint that already has the classification tree; the
+    overlap it prints is what is loaded here.)  Returns the number of ``model`` entries taken over."""
+    import torch
+    with open(path, "rb") as f:
+        new = msgpack_restore(f.read())
+    if set(new.keys()) == {"params"}:
+        new = new["params"]
+    mine = state.store.tree()
+    overlap = sorted(set(new["model"]).intersection(mine["model"]))
+
+    def merge(dst, src, path_):
+        out = {}
+        for k, v in dst.items():
+            if isinstance(v, dict):
+                out[k] = merge(v, src[k], path_ + (k,)) if k in src else v
+            elif k in src:
+                t = torch.from_numpy(np.asarray(src[k]))
+                if tuple(t.shape) != tuple(v.shape):
+                    raise ValueError(f"{'/'.join(path_ + (k,))}: checkpoint shape {tuple(t.shape)} != {tuple(v.shape)}")
+                out[k] = t
+            else:
+                out[k] = v
+        return out
+    merged = dict(mine)
+    merged["model"] = {k: (merge(v, new["model"][k], ("model", k)) if isinstance(v, dict) and k in overlap
+                           else (torch.from_numpy(np.asarray(new["model"][k])) if k in overlap else v))
+                       for k, v in mine["model"].items()}
+    state.store.load_tree(merged)
+    return len(overlap)
+
+
 def save_state(state, path: str) -> None:
     """Everything a run needs to resume (the reference saves parameters only and cannot): parameters, both Adam
     moments, the step / micro-step counters, an in-flight gradient accumulator and the RNG stream seeds, as

@@ -14,7 +14,7 @@ streams never advance: ``updates`` of ``split_rngs()`` is overwritten by the ``b
 src/finetuning.py:136-137,154 -- every step reuses the same key.  That looks unintended and is not reproduced.)
 
 Not built: DropPath / Dropout > 0, BatchNorm head and stop-gradient of linear probing (``--mode linear``), ``bce``,
-LARS / LAMB / SGD, loading a pre-training checkpoint into the classification tree (``load_pretrained_params``).
+LARS / LAMB / SGD.
 """
 from __future__ import annotations
 
@@ -134,9 +134,6 @@ def create_train_state(args: argparse.Namespace) -> TrainState:
             raise NotImplementedError(f"--{nm} > 0 is not built (the fine-tune recipe's DropPath 0.1 is the next item)")
     if getattr(args, "layerscale", False) or getattr(args, "posemb", "sincos2d") != "sincos2d":
         raise NotImplementedError("LayerScale / learnable position embeddings are not built")
-    if getattr(args, "pretrained_ckpt", None) is not None:
-        raise NotImplementedError("load_pretrained_params: load the encoder leaves with checkpoint.msgpack_restore + "
-                                  "store.load_tree on a merged tree; the helper is not built")
     cfg = MAEConfig(layers=args.layers, dim=args.dim, heads=args.heads, patch_size=args.patch_size,
                     image_size=args.image_size, labels=args.labels, weight_decay=args.weight_decay,
                     adam_b1=args.adam_b1, adam_b2=args.adam_b2, adam_eps=args.adam_eps,
@@ -152,6 +149,15 @@ def create_train_state(args: argparse.Namespace) -> TrainState:
         elif name.endswith("/scale"):
             view.fill_(1.0)
     store.refresh_bf16()
+    state = _new_state(args, store, cfg)
+    if getattr(args, "pretrained_ckpt", None) is not None:         # src/finetuning.py:215-217
+        from .checkpoint import load_pretrained_params
+        n = load_pretrained_params(state, args.pretrained_ckpt)
+        print(f"[*] load pretrained params with overlap of {n}/{len(state.params['model'])}")
+    return state
+
+
+def _new_state(args: argparse.Namespace, store: ParamStore, cfg: MAEConfig) -> TrainState:
     return TrainState(step=0, store=store, cfg=cfg, mixup_rng=int(getattr(args, "mixup_seed", 0)),
                       dropout_rng=int(getattr(args, "dropout_seed", 0)), noise_rng=int(getattr(args, "noise_seed", 0)),
                       learning_rate=float(args.learning_rate), warmup_steps=int(args.warmup_steps),

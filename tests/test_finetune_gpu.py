@@ -204,3 +204,28 @@ def test_finetuning_loss_goes_down_and_draws_advance():
     d1, d2 = s2.draw_mix(8), s2.draw_mix(8)
     assert d1 is not None and (d1.ratio != d2.ratio or not np.array_equal(d1.perm, d2.perm))
     assert sorted(d1.perm.tolist()) == list(range(8)) and 0.0 <= d1.ratio <= 1.0
+
+
+def test_load_pretrained_params_takes_the_encoder_and_keeps_the_head(tmp_path):
+    """--pretrained-ckpt (src/finetuning.py:215-217, src/utils.py:150-202): a parameter file written by the
+    pre-training step initialises the classification tree's encoder; head untouched, decoder ignored."""
+    from jumbo_mae_tpu_b200 import checkpoint
+    from jumbo_mae_tpu_b200.finetuning import create_train_state
+    from jumbo_mae_tpu_b200.params import ParamStore, tree_leaves
+    from jumbo_mae_tpu_b200.config import MAEConfig
+    ocfg = O.tiny()
+    pre = ParamStore(MAEConfig(**{f: getattr(ocfg, f) for f in MAEConfig.__dataclass_fields__ if hasattr(ocfg, f)}))
+    pre.load_tree(O.init_params(ocfg, seed=3, randomize_all=True))
+    path = str(tmp_path / "pretrain-last.msgpack")
+    with open(path, "wb") as f:
+        f.write(checkpoint.msgpack_serialize(pre.tree()))
+    fresh = create_train_state(_ft_args())
+    head0 = fresh.store.f("model/head/Dense_0/kernel").clone()
+    state = create_train_state(_ft_args(pretrained_ckpt=path))
+    assert torch.equal(state.store.f("model/head/Dense_0/kernel"), head0)          # same init seed, not overwritten
+    want = dict(tree_leaves(pre.tree()["model"]))
+    got = dict(tree_leaves(state.params["model"]))
+    assert set(want) == {k for k in got if k[0] != "head"}
+    for k, w in want.items():
+        assert torch.equal(got[k], w), k
+    assert torch.equal(state.store.p16, state.store.p.to(torch.bfloat16))          # compute copy refreshed
