@@ -30,6 +30,7 @@ def main():
     ap.add_argument("--batch", type=int, default=128)
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--eager", action="store_true", help="no CUDA graph: every kernel is its own launch (for ncu)")
     args = ap.parse_args()
     _lib.require_device()
     cfg = MAEConfig(labels=1000)
@@ -38,13 +39,19 @@ def main():
     store.p.normal_(0, 0.02, generator=g)
     store.refresh_bf16()
     eng = FinetuneEngine(cfg, store, args.batch)
-    eng.capture_graphs(label_smoothing=0.1, mixup=True)
+    if not args.eager:
+        eng.capture_graphs(label_smoothing=0.1, mixup=True)
+    perm = torch.arange(args.batch, dtype=torch.int32, device="cuda").flip(0).contiguous()
     images = torch.randint(0, 256, (args.batch, 3, 224, 224), dtype=torch.uint8, device="cuda", generator=g)
     labels = torch.randint(0, 1000, (args.batch,), dtype=torch.int32, device="cuda", generator=g)
     lib = _lib.load()
 
     def step(i):
-        eng.run_graph(images, labels, True)
+        if args.eager:
+            eng.forward(images, labels, label_smoothing=0.1, perm=perm, ratio=0.5)
+            eng.backward()
+        else:
+            eng.run_graph(images, labels, True)
         eng.adamw_step(i, 1e-4, grad_scale=1.0, lr_decay=0.75)
 
     for i in range(args.warmup):
@@ -74,7 +81,7 @@ def main():
                    "batch": args.batch},
         "flops_per_image": fstep, "achieved_tflops": tf, "peak_tflops_sustained": peak,
         "frac": (tf / peak) if peak else None,
-        "gpu_launches": (lib.jm_launch_count() - l0) + eng.graph_launches * args.steps,
+        "gpu_launches": (lib.jm_launch_count() - l0) + getattr(eng, "graph_launches", 0) * args.steps,
         "loss": eng.loss.item(), "acc1": eng.metrics[1].item()}))
 
 
