@@ -398,8 +398,14 @@ __device__ __forceinline__ void bwd_kv_chunk(const uint32_t (&kf)[HD / 16][4], c
 #ifndef JM_ATTN_BWD_CTAS
 #define JM_ATTN_BWD_CTAS 2
 #endif
-template <int HD>
-__global__ void __launch_bounds__(JM_ATTN_BWD_THREADS, HD == 32 ? JM_ATTN_BWD_CTAS : (HD == 64 ? JM_ATTN_BWD64_CTAS : 1))
+// MINCTAS = resident CTAs per SM the register allocation is bounded for.  head_dim 64 has two instantiations: 2 CTAs
+// (128 registers, a few spills) wins for the pre-training encoder's short sequences (T = 52: 180 -> 170 us), 1 CTA
+// (207 registers, no spills) for long ones (fine-tune step, T = 199: the step 22.7 -> 21.9 ms); launch_bwd picks by T.
+#ifndef JM_ATTN_BWD64_LONG_T
+#define JM_ATTN_BWD64_LONG_T 96
+#endif
+template <int HD, int MINCTAS>
+__global__ void __launch_bounds__(JM_ATTN_BWD_THREADS, MINCTAS)
 attn_bwd_kernel(const __nv_bfloat16* __restrict__ qkv, long ldqkv,
                                 const __nv_bfloat16* __restrict__ dout, long lddo, const float* __restrict__ lse,
                                 const __nv_bfloat16* __restrict__ out, long ldo, int T, int heads, float q_scale,
@@ -619,12 +625,12 @@ static int launch_fwd(const jm_bf16* qkv, long ldqkv, int batch, int T, int head
   return 0;
 }
 
-template <int HD>
-static int launch_bwd(const jm_bf16* qkv, long ldqkv, const jm_bf16* out, long ldo, const jm_bf16* dout, long lddo,
-                      const float* lse, float* delta, int batch, int T, int heads, float q_scale, jm_bf16* dqkv,
-                      long lddqkv, float* dbias, cudaStream_t stream) {
+template <int HD, int MINCTAS>
+static int launch_bwd_k(const jm_bf16* qkv, long ldqkv, const jm_bf16* out, long ldo, const jm_bf16* dout, long lddo,
+                        const float* lse, float* delta, int batch, int T, int heads, float q_scale, jm_bf16* dqkv,
+                        long lddqkv, float* dbias, cudaStream_t stream) {
   const size_t smem = bwd_smem(T, HD);
-  auto kern = attn_bwd_kernel<HD>;
+  auto kern = attn_bwd_kernel<HD, MINCTAS>;
   if (smem > 48 * 1024) JM_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   JM_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
   int warps = 0;
@@ -636,6 +642,25 @@ static int launch_bwd(const jm_bf16* qkv, long ldqkv, const jm_bf16* out, long l
       reinterpret_cast<const __nv_bfloat16*>(out), ldo, T, heads, q_scale, reinterpret_cast<__nv_bfloat16*>(dqkv), lddqkv, dbias);
   JM_AFTER_LAUNCH();
   return 0;
+}
+
+template <int HD>
+static int launch_bwd(const jm_bf16* qkv, long ldqkv, const jm_bf16* out, long ldo, const jm_bf16* dout, long lddo,
+                      const float* lse, float* delta, int batch, int T, int heads, float q_scale, jm_bf16* dqkv,
+                      long lddqkv, float* dbias, cudaStream_t stream) {
+  if constexpr (HD == 32) {
+    return launch_bwd_k<32, JM_ATTN_BWD_CTAS>(qkv, ldqkv, out, ldo, dout, lddo, lse, delta, batch, T, heads, q_scale,
+                                              dqkv, lddqkv, dbias, stream);
+  } else if constexpr (HD == 64) {
+    if (T > JM_ATTN_BWD64_LONG_T)
+      return launch_bwd_k<64, 1>(qkv, ldqkv, out, ldo, dout, lddo, lse, delta, batch, T, heads, q_scale, dqkv, lddqkv,
+                                 dbias, stream);
+    return launch_bwd_k<64, JM_ATTN_BWD64_CTAS>(qkv, ldqkv, out, ldo, dout, lddo, lse, delta, batch, T, heads, q_scale,
+                                                dqkv, lddqkv, dbias, stream);
+  } else {
+    return launch_bwd_k<HD, 1>(qkv, ldqkv, out, ldo, dout, lddo, lse, delta, batch, T, heads, q_scale, dqkv, lddqkv,
+                               dbias, stream);
+  }
 }
 
 static int check_attn(const char* who, int batch, int T, int heads, int hd, long ld0, long ld1) {
