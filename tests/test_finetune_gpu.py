@@ -229,3 +229,37 @@ def test_load_pretrained_params_takes_the_encoder_and_keeps_the_head(tmp_path):
     for k, w in want.items():
         assert torch.equal(got[k], w), k
     assert torch.equal(state.store.p16, state.store.p.to(torch.bfloat16))          # compute copy refreshed
+
+
+def test_classification_step_against_committed_golden():
+    """FinetuneEngine on the committed fixture tests/golden/tiny_classify.npz (f64 oracle, make_golden_finetune.py):
+    inputs, parameters and expected outputs come from the file, not from an RNG stream."""
+    import os
+    from jumbo_mae_tpu_b200.config import MAEConfig
+    from jumbo_mae_tpu_b200.finetune_engine import FinetuneEngine
+    from jumbo_mae_tpu_b200.params import ParamStore, tree_leaves
+    z = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "tiny_classify.npz"))
+    ocfg = O.golden_tiny(labels=int(z["logits"].shape[1]))
+    cfg = MAEConfig(**{f: getattr(ocfg, f) for f in MAEConfig.__dataclass_fields__ if hasattr(ocfg, f)})
+    params = O.init_params(ocfg, seed=0, randomize_all=True)
+    for path, leaf in O.tree_leaves(params):
+        leaf.copy_(torch.from_numpy(z["params/" + "/".join(path)]).float())
+    store = ParamStore(cfg)
+    store.load_tree(params)
+    eng = FinetuneEngine(cfg, store, z["images"].shape[0])
+    loss = eng.forward(torch.from_numpy(z["images"]).cuda(), torch.from_numpy(z["idx"]).cuda(),
+                       label_smoothing=float(z["smoothing"]), perm=torch.from_numpy(z["perm"]).cuda(),
+                       ratio=float(z["ratio"]))
+    eng.backward()
+    assert _rel(eng.logits.cpu().double(), torch.from_numpy(z["logits"])) <= 2e-2
+    assert abs(loss.item() - float(z["loss"])) <= 5e-3 * float(z["loss"])
+    got = dict(tree_leaves(store.tree(store.g)))
+    for key in [k for k in z.files if k.startswith("grads/")]:
+        path = tuple(key.split("/")[1:])
+        w = torch.from_numpy(z[key])
+        assert _rel(got[path].detach().cpu().reshape(w.shape), w) <= 3e-2, key
+    for key in [k for k in z.files if k.startswith("grad_stats/")]:
+        path = tuple(key.split("/")[1:])
+        if path[-2:] == ("wk", "bias") or z[key][1] == 0.0:
+            continue
+        assert abs(got[path].norm().item() - z[key][1]) <= 3e-2 * z[key][1], key

@@ -290,3 +290,40 @@ def test_product_layer_index_matches_oracle():
     from jumbo_mae_tpu_b200.params import get_layer_index
     for path, _ in O.tree_leaves(O.init_params(O.tiny())):
         assert get_layer_index("/".join(path), 7) == O.get_layer_index(path, 7)
+
+
+GOLDEN_CLASSIFY = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "tiny_classify.npz")
+
+
+def _classify_from_golden(dtype):
+    z = np.load(GOLDEN_CLASSIFY)
+    cfg = O.golden_tiny(labels=int(z["logits"].shape[1]))
+    params = O.init_params(cfg, seed=0, dtype=dtype, randomize_all=True)
+    for path, leaf in O.tree_leaves(params):                  # params come from the fixture, not from torch's RNG
+        leaf.copy_(torch.from_numpy(z["params/" + "/".join(path)]).to(dtype))
+    images, perm, ratio = torch.from_numpy(z["images"]), z["perm"], float(z["ratio"])
+    lab = O.mix_labels(O.smooth_labels(np.eye(cfg.labels, dtype=np.float32)[z["idx"]], float(z["smoothing"])), perm, ratio)
+    norm = O.preprocess(images, dtype=dtype).numpy()
+    r = norm.dtype.type(np.float32(ratio))
+    x = r * norm + (1 - r) * norm[perm]
+    return z, cfg, O.finetune_loss_and_grads(params, torch.as_tensor(x, dtype=dtype), lab, cfg), lab
+
+
+def test_oracle_reproduces_committed_classification_golden():
+    z, cfg, (loss, logits, grads), lab = _classify_from_golden(torch.float64)
+    assert np.array_equal(lab, z["labels"])
+    assert abs(float(loss) - float(z["loss"])) < 1e-10
+    assert np.allclose(logits.numpy(), z["logits"], atol=1e-10)
+    for path, g in O.tree_leaves(grads):
+        s = z["grad_stats/" + "/".join(path)]
+        assert abs(g.sum().item() - s[0]) < 1e-9 + 1e-9 * abs(s[0])
+        assert abs(g.norm().item() - s[1]) < 1e-9 + 1e-9 * abs(s[1])
+
+
+def test_f32_classification_oracle_close_to_f64_golden():
+    z, cfg, (loss, logits, grads), _ = _classify_from_golden(torch.float32)
+    assert abs(float(loss) - float(z["loss"])) < 1e-5
+    assert np.allclose(logits.numpy(), z["logits"], atol=1e-4)
+    for path, g in O.tree_leaves(grads):
+        s = z["grad_stats/" + "/".join(path)]
+        assert abs(g.double().norm().item() - s[1]) <= 1e-4 * s[1] + 1e-7
