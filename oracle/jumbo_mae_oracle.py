@@ -15,6 +15,12 @@ warmup_cosine_decay_schedule, all un-pinned: scripts/setup.sh:26-28).  Every
 assumed third-party default has a named test in tests/test_oracle.py so that a
 wrong assumption is a one-line fix once a JAX install exists.
 
+The fine-tune (classification) step is restated the same way further down
+(src/finetuning.py:84-124, src/utils.py:67-111,142-147: vit_classify, smooth_labels,
+apply_mixup / apply_cutmix / random_bounding_box, softmax_cross_entropy, top_k_indices,
+finetune_metrics, get_layer_index / layerwise_scale), with the RNG draws as arguments;
+equally unpinned, with its own committed fixture tests/golden/tiny_classify.npz.
+
 Every function cites the reference file:line it follows (paths are relative to
 the reference checkout).  The backward pass comes from torch.autograd, the
 analogue of ``jax.value_and_grad`` (src/pretraining.py:143).
