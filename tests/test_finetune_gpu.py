@@ -1,8 +1,6 @@
 """GPU parity tests of the classification (fine-tune) step, SURVEY.md 8(f) rank 1: FinetuneEngine against the CPU
 oracle's vit_classify / finetune_loss_and_grads (src/finetuning.py:84-124, src/modeling.py:245-274) on the same
 parameters, images, labels and Mixup / CutMix draws.  Tolerances (bf16 kernels vs f32 oracle) beside each assert."""
-import dataclasses
-
 import numpy as np
 import pytest
 import torch
