@@ -62,7 +62,7 @@ def test_lr_schedule_matches_oracle():
 def test_backward_segment_ranges_partition_the_gradient_buffer():
     """Data-parallel overlap: the per-segment all-reduce ranges are disjoint and cover every leaf once."""
     from jumbo_mae_tpu_b200.engine import MAEEngine
-    for cfg in (vit_b16(), _pc(O.tiny())):
+    for cfg in (vit_b16(), _pc(O.tiny()), _pc(O.tiny(layers=1)), _pc(O.vit_l16())):
         store = ParamStore(cfg, device="meta")
         eng = MAEEngine.__new__(MAEEngine)          # no device buffers: only the host-side planning is exercised
         eng.cfg, eng.ps = cfg, store
