@@ -79,3 +79,23 @@ def test_backward_segment_ranges_partition_the_gradient_buffer():
         names = lambda k: {n for n, l in store.leaves.items() if any(s <= l.offset < e for s, e in eng.segment_grad_ranges(k))}
         assert names(last - 1) and all(n.startswith("model/jumbo_mlp/") for n in names(last - 1))
         assert all(n.startswith(("model/layer_0/", "model/embed/", "model/cls_tokens")) for n in names(last))
+
+
+def test_classification_tree_and_segment_ranges():
+    """labels > 0: no decoder leaves, LinearCLS head under model/head/Dense_0 (src/modeling.py:209-219,236-240); the
+    classification engine's backward segments still partition the flat gradient buffer."""
+    import dataclasses
+    from jumbo_mae_tpu_b200.finetune_engine import FinetuneEngine
+    cfg = dataclasses.replace(vit_b16(), labels=1000)
+    assert cfg.keep == cfg.num_patches and cfg.num_masked == 0
+    store = ParamStore(cfg, device="meta")
+    names = set(store.leaves)
+    assert {"model/head/Dense_0/kernel", "model/head/Dense_0/bias"} <= names
+    assert not any(n.startswith(("decoder", "image_mask")) for n in names)
+    head = store.leaves["model/head/Dense_0/kernel"]
+    assert (head.rows, head.cols) == (3 * 768, 1000) and head.decay
+    eng = FinetuneEngine.__new__(FinetuneEngine)
+    eng.cfg, eng.ps = cfg, store
+    seen = sorted(r for k in range(eng.num_bwd_segments()) for r in eng.segment_grad_ranges(k))
+    assert all(a[1] <= b[0] for a, b in zip(seen, seen[1:]))
+    assert sum(e - s for s, e in seen) == store.total
