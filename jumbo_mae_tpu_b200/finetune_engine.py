@@ -49,6 +49,7 @@ class FinetuneEngine(MAEEngine):
         self.patches = e(Me, self.Pp)
         self.xa: List[torch.Tensor] = [e(Me, d, dt=F32) for _ in range(cfg.layers + 1)]
         self.enc = [_Block(Me, d, cfg.heads, B, self.Te, J, True, dev) for _ in range(cfg.layers)]
+        self.dec: List[_Block] = []          # no decoder in classification mode (activation_bytes walks both lists)
         L, Jd = cfg.layers, J * d
         self.cn16_all, self.gj_all = e(L * B, Jd), e(L * B, 4 * Jd)
         self.dhj16_all, self.dc16_all = e(L * B, 4 * Jd), e(L * B, Jd)
