@@ -143,7 +143,8 @@ int jm_layernorm_bwd(const jm_bf16* dy, long lddy, const float* x, long ldx, con
  *   v += residual[row, col]
  *   rows with (row % row_period) < row_skip: row_mask_mode 1 -> zeros are stored,
  *   2 -> nothing is stored.
- *   accumulate != 0 -> out_f32 += v (atomic; also used for split-K), else out_f32 = v.
+ *   accumulate != 0 -> out_f32 += v (f32 reduce-add of whole tiles in L2 by TMA, or red.global.add on the
+ *   generic path; also used for split-K), else out_f32 = v.
  */
 typedef struct jm_gemm_args {
   int M, N, K;

@@ -40,6 +40,20 @@ def _stale(target: str, deps) -> bool:
     return any(os.path.getmtime(d) > t for d in deps)
 
 
+def _flag_stamp() -> str:
+    """The compile flags an object was built with are written next to it (``<obj>.flags``): an object built with
+    other -D switches (JM_NVCC_DEFS, JM_DEBUG_SMID, ...) is stale even when its sources did not change."""
+    return " ".join([_nvcc()] + NVCC_FLAGS)
+
+
+def _flags_changed(obj: str) -> bool:
+    try:
+        with open(obj + ".flags") as f:
+            return f.read() != _flag_stamp()
+    except OSError:
+        return True
+
+
 def build(force: bool = False, verbose: bool = False) -> str:
     srcs = sources()
     headers = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cuh", ".h"))]
@@ -49,7 +63,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
 
     def compile_one(src):
         obj = os.path.join(objdir, os.path.basename(src)[:-3] + ".o")
-        if force or _stale(obj, [src] + headers):
+        if force or _stale(obj, [src] + headers) or _flags_changed(obj):
             cmd = [_nvcc()] + NVCC_FLAGS + ["-c", src, "-o", obj]
             res = subprocess.run(cmd, capture_output=True, text=True)
             if res.returncode != 0:
@@ -58,6 +72,8 @@ def build(force: bool = False, verbose: bool = False) -> str:
                 sys.stderr.write(res.stderr)
             with open(obj + ".log", "w") as f:
                 f.write(res.stderr)
+            with open(obj + ".flags", "w") as f:
+                f.write(_flag_stamp())
         return obj
 
     with ThreadPoolExecutor(max_workers=min(8, len(srcs))) as ex:

@@ -8,6 +8,7 @@
 #include <stdint.h>
 #include <stdio.h>
 
+#include <atomic>
 #include <mutex>
 #include <string>
 
@@ -31,6 +32,18 @@ int fail(const char* fmt, ...);
   } while (0)
 
 int sm_count();  // SMs of the current device (cached per device)
+
+// Per-device one-time set-up (function attributes, occupancy queries).  A host may drive several GPUs from one
+// process and call in from one thread per device, so nothing device-specific is cached in a
+// plain static: a DeviceOnce holds one bit per device ordinal; racing first calls repeat an idempotent set-up.
+constexpr int kMaxDevices = 64;
+int current_device();               // ordinal of the current device, -1 on error / >= kMaxDevices
+int env_int(const char* name, int dflt);
+struct DeviceOnce {
+  std::atomic<unsigned long long> bits{0};
+  bool done(int dev) const { return (bits.load(std::memory_order_acquire) >> dev) & 1ull; }
+  void mark(int dev) { bits.fetch_or(1ull << dev, std::memory_order_release); }
+};
 
 // Every kernel launch is followed by this: counts the launch (jm_launch_count) and
 // surfaces launch-configuration errors as a return code.

@@ -29,12 +29,19 @@ static std::atomic<long long> g_launches{0};
 void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
 long long launches() { return g_launches.load(std::memory_order_relaxed); }
 
+int env_int(const char* name, int dflt) {
+  const char* e = getenv(name);
+  return e ? atoi(e) : dflt;
+}
+
+int current_device() {
+  int dev = -1;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= kMaxDevices) return -1;
+  return dev;
+}
+
 bool pdl_enabled() {
-  static int on = -1;
-  if (on < 0) {
-    const char* e = getenv("JM_PDL");
-    on = e ? (atoi(e) != 0) : 0;  // measured on B200: no gain without the early trigger, -2 % with it
-  }
+  static const int on = env_int("JM_PDL", 0);  // measured on B200: no gain without the early trigger, -2 % with it
   return on != 0;
 }
 

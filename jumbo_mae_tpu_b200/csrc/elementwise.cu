@@ -942,6 +942,8 @@ extern "C" size_t jm_patch_loss_workspace(int batch, int num_patches) {
 extern "C" int jm_patch_loss(const float* pred, long ldp, const uint8_t* images, const float* mask_row, int batch,
                              int image_size, int patch_size, int num_cls, int norm_pix, float grad_scale, float* loss,
                              jm_bf16* dpred, long lddp, void* workspace, size_t workspace_bytes, void* stream) {
+  JM_CHECK(patch_size > 0 && image_size > 0 && image_size % patch_size == 0,
+           "jm_patch_loss: image size %d must be a positive multiple of the patch size %d", image_size, patch_size);
   const int g = image_size / patch_size, N = g * g, P = patch_size * patch_size * 3;
   JM_CHECK(P <= kLossThreads * kLossMaxPer, "jm_patch_loss: patch dimension %d too large", P);
   JM_CHECK(P % 4 == 0 && ldp % 4 == 0 && (!dpred || lddp % 4 == 0) && (reinterpret_cast<uintptr_t>(pred) & 15) == 0 &&
@@ -1063,11 +1065,7 @@ extern "C" int jm_layernorm_bwd(const jm_bf16* dy, long lddy, const float* x, lo
   const int tr = kLnBwdWarps * 32;
   // register kernels: the blocks reduce their partials straight into the gradients (no second launch) when the
   // destinations allow 16-byte vector reductions; JM_LN_DIRECT=0 keeps the workspace + reduce-kernel path
-  static int direct_env = -1;
-  if (direct_env < 0) {
-    const char* e = getenv("JM_LN_DIRECT");
-    direct_env = e ? (atoi(e) != 0) : 1;
-  }
+  static const int direct_env = env_int("JM_LN_DIRECT", 1) != 0;  // process-wide, initialised once
   LnDirect direct{dgamma, dbeta, dcol, 0};
   direct.on = direct_env && dim <= 1280 &&
               ((reinterpret_cast<uintptr_t>(dgamma) | reinterpret_cast<uintptr_t>(dbeta) |

@@ -1406,10 +1406,13 @@ template <int BN, bool A_MN, bool B_MN, int EPI>
 static int launch_gemm(const GemmMaps& tm, const GemmShape& sh, const EpiParams& ep,
                        int grid, cudaStream_t stream) {
   auto kern = gemm_kernel<BN, A_MN, B_MN, EPI>;
-  static bool attr_set = false;  // per template instantiation; benign race (idempotent)
-  if (!attr_set) {
+  // function attributes are per device: one bit per device ordinal and template instantiation
+  static DeviceOnce attr_set;
+  const int dev = current_device();
+  JM_CHECK(dev >= 0, "jm_gemm: no current CUDA device");
+  if (!attr_set.done(dev)) {
     JM_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, GemmCfg<BN>::SMEM_BYTES));
-    attr_set = true;
+    attr_set.mark(dev);
   }
   JM_LAUNCH_PDL(kern, grid, kGemmThreads, GemmCfg<BN>::SMEM_BYTES, stream, tm.a, tm.b, tm.o, tm.o2, sh, ep);
   JM_AFTER_LAUNCH();
@@ -1420,10 +1423,12 @@ template <bool A_MN, bool B_MN, int EPI>
 static int launch_gemm2(const GemmMaps& tm, const GemmShape& sh, const EpiParams& ep,
                         int grid, cudaStream_t stream) {
   auto kern = gemm2_kernel<A_MN, B_MN, EPI>;
-  static bool attr_set = false;
-  if (!attr_set) {
+  static DeviceOnce attr_set;
+  const int dev = current_device();
+  JM_CHECK(dev >= 0, "jm_gemm: no current CUDA device");
+  if (!attr_set.done(dev)) {
     JM_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Gemm2Cfg<EPI>::SMEM_BYTES));
-    attr_set = true;
+    attr_set.mark(dev);
   }
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(grid);
@@ -1439,11 +1444,7 @@ static int launch_gemm2(const GemmMaps& tm, const GemmShape& sh, const EpiParams
   attr[1].val.programmaticStreamSerializationAllowed = pdl_enabled() ? 1 : 0;
   cfg.attrs = attr;
   cfg.numAttrs = 2;
-  static int policy = -1;
-  if (policy < 0) {
-    const char* e = getenv("JM_PAIR_POLICY");
-    policy = e ? atoi(e) : 0;
-  }
+  static const int policy = env_int("JM_PAIR_POLICY", 0);  // process-wide, initialised once (thread-safe)
   if (policy > 0) {
     attr[2].id = cudaLaunchAttributeClusterSchedulingPolicyPreference;
     attr[2].val.clusterSchedulingPolicyPreference =
@@ -1452,12 +1453,14 @@ static int launch_gemm2(const GemmMaps& tm, const GemmShape& sh, const EpiParams
   }
   // A persistent grid must not exceed the clusters the GPU can hold at once (GPCs with an odd SM left over
   // cannot host a pair there): surplus clusters would run as a second wave.
-  static int max_clusters = 0;
+  static std::atomic<int> max_clusters_dev[kMaxDevices];  // per device ordinal (zero-initialised)
+  int max_clusters = max_clusters_dev[dev].load(std::memory_order_acquire);
   if (max_clusters == 0) {
     int n = 0;
     JM_CUDA(cudaOccupancyMaxActiveClusters(&n, kern, &cfg));
     JM_CHECK(n > 0, "jm_gemm: the CTA-pair kernel cannot be scheduled on this device");
     if (getenv("JM_PAIR_VERBOSE")) fprintf(stderr, "jm: pair kernel max active clusters = %d\n", n);
+    max_clusters_dev[dev].store(n, std::memory_order_release);
     max_clusters = n;
   }
   if (grid > 2 * max_clusters) {
@@ -1561,11 +1564,7 @@ extern "C" int jm_gemm(const jm_gemm_args* a, void* stream_) {
   const bool can_split = a->accumulate && a->out_f32 && !a->out_bf16 && !a->out2_bf16 && !a->bias &&
                          !a->residual && !a->pe && a->act == 0;
   const bool amn = a->a_mn_major != 0, bmn = a->b_mn_major != 0;
-  static int auto_pair = -1;
-  if (auto_pair < 0) {
-    const char* e = getenv("JM_GEMM_PAIR");
-    auto_pair = e ? (atoi(e) != 0) : 1;
-  }
+  static const int auto_pair = env_int("JM_GEMM_PAIR", 1) != 0;  // process-wide, initialised once (thread-safe)
   int bn = a->block_n;
   bool pair_pick = false;
   if (bn == 0) {

@@ -3,8 +3,9 @@
 Same names and argument meaning: ``create_train_state(args)``, ``training_step(state, batch)`` with
 ``batch = (images uint8 [B,3,H,W], labels int32 [B])`` returning ``(state, {"loss", "acc1", "acc5",
 "learning_rate"})``, ``validation_step(state, batch)`` returning summed ``{"loss", "acc1", "acc5", "num_samples"}``
-over the rows whose label is not -1 (src/finetuning.py:157-165).  Single process; the data-parallel wrapper of the
-pre-training step has not been extended to this step yet.
+over the rows whose label is not -1 (src/finetuning.py:157-165).  One process per GPU: under ``torch.distributed``
+the gradients are sum-all-reduced over NCCL before the update (1/world folded into AdamW), the step metrics are
+averaged and the validation sums are summed over ranks, as ``lax.pmean`` / ``lax.psum`` do (src/finetuning.py:131-165).
 
 RNG: the reference draws the Mixup / CutMix choice, the beta sample, the batch permutation and the box origin from
 its ``mixup`` threefry stream (src/utils.py:67-111); those bits cannot be reproduced without JAX, so the draws are
@@ -29,6 +30,7 @@ import torch
 from . import _lib, ops
 from .config import MAEConfig
 from .finetune_engine import FinetuneEngine
+from .parallel import GradReducer, process_count, process_index
 from .params import ParamStore
 
 
@@ -86,6 +88,7 @@ class TrainState:
     micro_in_mini: int = 1
     batch_stats: Any = None
     engines: Dict[int, FinetuneEngine] = field(default_factory=dict)
+    reducer: Optional[GradReducer] = None
     _mix_gen: Optional[np.random.Generator] = None
 
     @property
@@ -98,7 +101,8 @@ class TrainState:
                 "hyperparams": {"learning_rate": lr_schedule(max(self.step - 1, 0), self)}}
 
     def replicate(self) -> "TrainState":
-        self._mix_gen = np.random.Generator(np.random.Philox(key=self.mixup_rng))
+        # one stream per rank, as shard_prng_key gives every device its own key (src/finetuning.py:71-76)
+        self._mix_gen = np.random.Generator(np.random.Philox(key=self.mixup_rng + 7919 * process_index()))
         return self
 
     def engine(self, batch: int) -> FinetuneEngine:
@@ -190,17 +194,24 @@ def training_step(state: TrainState, batch, mix: Optional[MixDraw] = None):
                                                       state.cfg.image_size)
             kw.update(xmask=torch.from_numpy(xm).to(dev), ymask=torch.from_numpy(ym).to(dev), label_ratio=label_ratio)
     accum = state.micro_in_mini
+    world = process_count()
+    if world > 1 and getattr(state, "reducer", None) is None:
+        state.reducer = GradReducer(state.store)
     eng.forward(images, labels, label_smoothing=state.label_smoothing, **kw)
     eng.backward(zero_grads=(state.micro_step == 0))
     metrics = eng.metrics.clone()
+    if world > 1:                                                  # lax.pmean(metrics) (src/finetuning.py:131)
+        state.reducer.mean_scalar(metrics)
     state.micro_step += 1
     lr = lr_schedule(state.step, state)
     if state.micro_step == accum:
+        if world > 1:                                              # lax.pmean(grads) (:138,144); 1/world below
+            state.reducer.all_reduce_grads()
         if state.clip_grad > 0:
             if not hasattr(state, "_sumsq"):
                 state._sumsq = torch.zeros(1, dtype=torch.float32, device=dev)
-            ops.clip_by_global_norm(state.store.g, 1.0 / accum, state.clip_grad, state._sumsq)
-        eng.adamw_step(state.step, lr, grad_scale=1.0 / accum, lr_decay=state.lr_decay)
+            ops.clip_by_global_norm(state.store.g, 1.0 / (accum * world), state.clip_grad, state._sumsq)
+        eng.adamw_step(state.step, lr, grad_scale=1.0 / (accum * world), lr_decay=state.lr_decay)
         state.step += 1
         state.micro_step = 0
     return state, {"loss": metrics[0], "acc1": metrics[1], "acc5": metrics[2], "learning_rate": lr}
@@ -215,5 +226,8 @@ def validation_step(state: TrainState, batch) -> Dict[str, Any]:
     eng = state.engine(images.shape[0])
     eng.forward(images, torch.where(valid, labels, torch.zeros_like(labels)), want_grad=False)
     v = valid.to(torch.float32)
-    return {"loss": (eng.loss_rows * v).sum(), "acc1": (eng.acc1 * v).sum(), "acc5": (eng.acc5 * v).sum(),
-            "num_samples": v.sum()}
+    sums = torch.stack([(eng.loss_rows * v).sum(), (eng.acc1 * v).sum(), (eng.acc5 * v).sum(), v.sum()])
+    if process_count() > 1:                                        # lax.psum(metrics) (src/finetuning.py:165)
+        import torch.distributed as dist
+        dist.all_reduce(sums)
+    return {"loss": sums[0], "acc1": sums[1], "acc5": sums[2], "num_samples": sums[3]}

@@ -83,10 +83,23 @@ def test_two_rank_allreduce_matches_single_replica(tmp_path):
         assert (g - w).norm() <= 1e-5 * w.norm() + 1e-9, path
 
 
-def test_per_rank_noise_streams_differ():
-    """Each device draws its own mask (shard_prng_key, src/pretraining.py:68-73)."""
+def test_per_rank_noise_streams_differ(monkeypatch):
+    """Each device draws its own mask (shard_prng_key, src/pretraining.py:68-73): TrainState.replicate() derives
+    the rank's noise stream from (noise_rng, process_index); split_rngs() then advances it every step."""
     from jumbo_mae_tpu_b200 import pretraining as P
-    a = np.random.Generator(np.random.Philox(key=0 + 7919 * 0)).random(16, dtype=np.float32)
-    b = np.random.Generator(np.random.Philox(key=0 + 7919 * 1)).random(16, dtype=np.float32)
-    assert not np.array_equal(a, b)
-    assert hasattr(P, "training_step") and hasattr(P, "validation_step") and hasattr(P, "create_train_state")
+    from jumbo_mae_tpu_b200.config import MAEConfig
+    cfg = MAEConfig(layers=1, dim=64, heads=2, patch_size=8, image_size=32, dec_layers=1, dec_dim=64, dec_heads=2)
+
+    def draws(rank, seed=0, n=3):
+        monkeypatch.setattr(P, "process_index", lambda: rank)
+        st = P.TrainState(step=0, store=None, cfg=cfg, module=None, mixup_rng=seed, dropout_rng=seed,
+                          noise_rng=seed).replicate()
+        out = [st.split_rngs()[0]["noise"] for _ in range(n)]
+        assert all(o.shape == (cfg.num_patches,) and o.dtype == np.float32 for o in out)
+        return out
+
+    r0, r1, r0_again = draws(0), draws(1), draws(0)
+    assert all(np.array_equal(a, b) for a, b in zip(r0, r0_again))          # reproducible per (seed, rank)
+    assert not any(np.array_equal(a, b) for a, b in zip(r0, r1))            # ranks draw different masks
+    assert not np.array_equal(r0[0], r0[1])                                 # the stream advances per step
+    assert not np.array_equal(draws(0, seed=1)[0], r0[0])                   # and depends on --noise-seed

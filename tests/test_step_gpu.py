@@ -27,6 +27,13 @@ def _cfgs():
         "vitb_width": (O.MAEConfig(layers=2, dec_layers=2, warmup_steps=10, training_steps=100), 3),
         "vith_patch14": (O.MAEConfig(layers=1, dim=160, heads=2, patch_size=14, image_size=56, dec_layers=1,
                                      dec_dim=64, dec_heads=2, warmup_steps=10, training_steps=100), 5),
+        # BASELINE.json configs[0] exactly: ViT-B/16, 12 + 8 layers, 224 px, batch 8 (error growth over 20 blocks,
+        # the T = 199 / head_dim 32 decoder at depth, the batched Jumbo weight gradient over K = 12 * B)
+        "config1_vitb16": (O.MAEConfig(), 8),
+        # one ViT-H/14 block at its real width: d = 1280, head_dim 80, P = 588 (row pitch padded to 592),
+        # T = 67 / 259, decoder 512 x 16 heads
+        "vith_width": (O.MAEConfig(layers=2, dim=1280, heads=16, patch_size=14, image_size=224, dec_layers=1,
+                                   warmup_steps=10, training_steps=100), 2),
     }
 
 
@@ -52,7 +59,10 @@ def _rel(a, b):
     return ((a - b).norm() / (b.norm() + 1e-12)).item()
 
 
-@pytest.mark.parametrize("name", ["tiny", "tiny_normpix", "mid", "vitb_width", "vith_patch14"])
+ALL = ["tiny", "tiny_normpix", "mid", "vitb_width", "vith_patch14", "config1_vitb16", "vith_width"]
+
+
+@pytest.mark.parametrize("name", ALL)
 def test_forward_loss_and_activations(name):
     ocfg, cfg, state, images, noise, store, eng = _setup(name)
     collect = {}
@@ -75,7 +85,7 @@ def test_forward_loss_and_activations(name):
     assert abs(loss.item() - want) <= 5e-3 * abs(want), (loss.item(), want)
 
 
-@pytest.mark.parametrize("name", ["tiny", "tiny_normpix", "mid", "vitb_width", "vith_patch14"])
+@pytest.mark.parametrize("name", ALL)
 def test_gradients_match_oracle(name):
     from jumbo_mae_tpu_b200.params import tree_leaves
     ocfg, cfg, state, images, noise, store, eng = _setup(name)
@@ -116,13 +126,13 @@ def test_backward_accumulates_and_rezeroes():
     assert torch.allclose(store.g, g1, rtol=1e-4, atol=1e-7)
 
 
-@pytest.mark.parametrize("name", ["tiny", "mid"])
+@pytest.mark.parametrize("name", ["tiny", "mid", "config1_vitb16"])
 def test_k_step_training_matches_oracle(name):
     from jumbo_mae_tpu_b200.engine import lr_schedule
     from jumbo_mae_tpu_b200.params import tree_leaves
     ocfg, cfg, state, images, noise, store, eng = _setup(name)
     im = images.cuda()
-    k = 5
+    k = 3 if name == "config1_vitb16" else 5     # the full-depth oracle step costs seconds on the host
     p0 = dict(O.tree_leaves(state.params))
     losses_o, losses_g = [], []
     for step in range(k):
