@@ -15,6 +15,11 @@
 
 namespace jm {
 
+// attention_tc.cu: the tcgen05 / TMEM kernels (head_dim 32 / 64, T <= 256); everything else runs below
+bool attn_tc_supported(int T, int hd);
+int attn_tc_fwd(const jm_bf16* qkv, long ldqkv, int batch, int T, int heads, int hd, jm_bf16* out, long ldo,
+                float* lse, cudaStream_t stream);
+
 constexpr float kLog2e = 1.4426950408889634f;
 
 __device__ __forceinline__ void ldsm_x4(uint32_t (&r)[4], uint32_t addr) {
@@ -678,6 +683,7 @@ extern "C" int jm_attention_fwd(const jm_bf16* qkv, long ldqkv, int batch, int T
   using namespace jm;
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   if (check_attn("jm_attention_fwd", batch, T, heads, head_dim, ldqkv, ldo)) return 1;
+  if (attn_tc_supported(T, head_dim)) return attn_tc_fwd(qkv, ldqkv, batch, T, heads, head_dim, out, ldo, lse, stream);
   JM_CHECK(fwd_smem(T, head_dim) <= 227 * 1024, "jm_attention_fwd: T=%d hd=%d does not fit shared memory", T,
            head_dim);
   if (head_dim == 32) return launch_fwd<32>(qkv, ldqkv, batch, T, heads, out, ldo, lse, stream);

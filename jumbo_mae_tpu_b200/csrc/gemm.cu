@@ -1381,6 +1381,10 @@ static PFN_cuTensorMapEncodeTiled_v12000 get_encode_fn() {
   return fn;
 }
 
+}  // namespace jm
+void* jm::tmap_encode_fn() { return reinterpret_cast<void*>(jm::get_encode_fn()); }
+namespace jm {
+
 // 2-D bf16 tensor [outer, inner] row-major with row stride ld elements; operand boxes are SWIZZLE_128B, the
 // epilogue's 32 x 32 output boxes SWIZZLE_64B.
 static int make_tmap(CUtensorMap* map, const void* ptr, long inner, long outer, long ld, int box_inner,
