@@ -20,6 +20,11 @@ bool attn_tc_supported(int T, int hd);
 int attn_tc_fwd(const jm_bf16* qkv, long ldqkv, int batch, int T, int heads, int hd, jm_bf16* out, long ldo,
                 float* lse, cudaStream_t stream);
 
+bool attn_tc_bwd_supported(int T, int hd);
+int attn_tc_bwd(const jm_bf16* qkv, long ldqkv, const jm_bf16* out, long ldo, const jm_bf16* dout, long lddo,
+                const float* lse, int batch, int T, int heads, int hd, float q_scale, jm_bf16* dqkv, long lddqkv,
+                float* dbias, cudaStream_t stream);
+
 constexpr float kLog2e = 1.4426950408889634f;
 
 __device__ __forceinline__ void ldsm_x4(uint32_t (&r)[4], uint32_t addr) {
@@ -699,6 +704,9 @@ extern "C" int jm_attention_bwd(const jm_bf16* qkv, long ldqkv, const jm_bf16* o
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   if (check_attn("jm_attention_bwd", batch, T, heads, head_dim, ldqkv, lddqkv)) return 1;
   JM_CHECK(ldo % 8 == 0 && lddo % 8 == 0, "jm_attention_bwd: row strides must be multiples of 8 elements");
+  if (attn_tc_bwd_supported(T, head_dim))
+    return attn_tc_bwd(qkv, ldqkv, out, ldo, dout, lddo, lse, batch, T, heads, head_dim, q_scale, dqkv, lddqkv, dbias,
+                       stream);
   JM_CHECK(bwd_smem(T, head_dim) <= 227 * 1024, "jm_attention_bwd: T=%d hd=%d does not fit shared memory", T,
            head_dim);
   if (head_dim == 32)
