@@ -43,7 +43,8 @@ struct AttnTcShape {
   int q_bytes;      // nq * 128 rows
   int kv_bytes;     // Nk rows, rounded up to 1024
   int stage_bytes;  // Q + K + V (+ dO in the backward)
-  int col_o;        // TMEM column (inside a slot) of O: behind the bf16 P that overwrites S in place
+  int cs;           // key columns [0, cs) belong to softmax half 0, [cs, Nk) to half 1 (multiples of 16)
+  int col_o;        // TMEM column (inside a slot) of O: a range that holds no P
   long ldo;
 };
 
@@ -74,15 +75,76 @@ __device__ __forceinline__ uint32_t ptile_chunk(int row, int kc) {
   return static_cast<uint32_t>((kc >> 3) * 16384 + row * 128 + (((kc & 7) ^ (row & 7)) << 4));
 }
 
+// Optional timeline (build with -DJM_ATTN_TRACE): CTA 0 stamps clock64() at the hand-over points of its first items.
+#ifdef JM_ATTN_TRACE
+__device__ long long g_attn_trace[64 * 16];
+#define JM_TRACE(item, id, cond) \
+  do { if (blockIdx.x == 0 && (item) < 64 && (cond)) g_attn_trace[(item) * 16 + (id)] = clock64(); } while (0)
+#else
+#define JM_TRACE(item, id, cond) do { } while (0)
+#endif
+
 // ------------------------------------------------------------------------------------------------ forward
+// Softmax work on one accumulator tile is split between two groups of four warps by key columns: half 0 owns
+// columns [0, cs), half 1 owns [cs, Nk).  The halves exchange their row maxima (and later their row sums) through
+// shared memory with a named barrier, so that 16 softmax warps (4 per scheduler) are in flight per SM.
+constexpr int kFwdThreads = 640;  // warps 0-3 as above, warps 4-19: [slot 2][half 2][lane quarter 4]
+
+template <int W>
+__device__ __forceinline__ void tmem_ld_w(uint32_t taddr, uint32_t (&r)[W]) {
+  if constexpr (W == 32) tmem_ld_32x32(taddr, r);
+  else tmem_ld_32x16(taddr, r);
+}
+
+// running maximum over W score columns starting at column c0 (columns >= T are padding)
+template <int W>
+__device__ __forceinline__ void fwd_chunk_max(uint32_t t_row, int c0, int T, float& mx) {
+  uint32_t r[W];
+  tmem_ld_w<W>(t_row + c0, r);
+  tmem_ld_wait();
+  if (c0 + W > T) {
+#pragma unroll
+    for (int e = 0; e < W; ++e)
+      if (c0 + e >= T) r[e] = 0xff800000u;  // -inf
+  }
+#pragma unroll
+  for (int e = 0; e < W; e += 2) mx = fmax3(mx, __uint_as_float(r[e]), __uint_as_float(r[e + 1]));
+}
+
+// P = exp2(s log2e - max log2e) for W columns at c0; bf16 pairs go back to tensor memory at column `dst`
+template <int W>
+__device__ __forceinline__ void fwd_chunk_exp(uint32_t t_row, int c0, int dst, int T, f32x2 k2, f32x2 nm2, f32x2& l2) {
+  uint32_t r[W];
+  tmem_ld_w<W>(t_row + c0, r);
+  tmem_ld_wait();
+  if (c0 + W > T) {
+#pragma unroll
+    for (int e = 0; e < W; ++e)
+      if (c0 + e >= T) r[e] = 0xff800000u;
+  }
+  uint32_t w[W / 2];
+#pragma unroll
+  for (int e = 0; e < W; e += 2) {
+    float x0, x1;
+    unpack2(fma2(pack2(__uint_as_float(r[e]), __uint_as_float(r[e + 1])), k2, nm2), x0, x1);
+    const float p0 = ex2_approx(x0), p1 = ex2_approx(x1);
+    l2 = add2(l2, pack2(p0, p1));
+    w[e >> 1] = pack_bf16(p0, p1);
+  }
+  if constexpr (W == 32) tmem_st_32x16(t_row + dst, w);
+  else tmem_st_32x8(t_row + dst, w);
+}
+
 template <int HD>
-__global__ void __launch_bounds__(kTcThreads, 1)
+__global__ void __launch_bounds__(kFwdThreads, 1)
 attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmKV,
                    const AttnTcShape sh, __nv_bfloat16* __restrict__ out, float* __restrict__ lse) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   uint8_t* sStage = smem;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + sh.stages * sh.stage_bytes);
+  float* sXm = reinterpret_cast<float*>(smem + sh.stages * sh.stage_bytes);  // [slot][half][128] row maxima
+  float* sXl = sXm + 512;                                                    // [slot][half][128] row sums
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sXl + 512);
   uint64_t* kv_full = bars;            // [stages]
   uint64_t* kv_empty = bars + 4;       // [stages]
   uint64_t* s_full = bars + 8;         // [2]
@@ -101,9 +163,9 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
     }
     for (int s = 0; s < 2; ++s) {
       mbar_init(&s_full[s], 1);
-      mbar_init(&p_full[s], 128);
+      mbar_init(&p_full[s], 256);
       mbar_init(&o_full[s], 1);
-      mbar_init(&o_empty[s], 128);
+      mbar_init(&o_empty[s], 256);
     }
     fence_barrier_init();
   }
@@ -143,12 +205,16 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
         const int slot = i & 1, j = i / sh.nq, st = j % sh.stages;
         mbar_wait(&p_full[slot], (i >> 1) & 1);
         tc_fence_after();
+        JM_TRACE(i, 8, true);
         const uint32_t v_addr = smem_u32(sStage + st * sh.stage_bytes + sh.q_bytes + sh.kv_bytes);
-        const int ksteps = sh.Nk >> 4;
-        const uint32_t t_p = tmem_base + slot * kSlotCols;  // P: bf16 pairs, 8 columns per 16-key step
+        const int ksteps = sh.Nk >> 4, k_half = sh.cs >> 4;
+        const uint32_t t_p = tmem_base + slot * kSlotCols;
+        // P: bf16 pairs, 8 columns per 16-key step; half 0 packed its keys at [0, cs / 2), half 1 at [cs, ...)
         for (int kk = 0; kk < ksteps; ++kk)
-          umma_bf16_ts(t_p + sh.col_o, t_p + kk * 8, desc_mnmajor<HD>(v_addr, kk), idesc_o, kk > 0 ? 1u : 0u);
+          umma_bf16_ts(t_p + sh.col_o, t_p + (kk < k_half ? kk * 8 : sh.cs + (kk - k_half) * 8),
+                       desc_mnmajor<HD>(v_addr, kk), idesc_o, kk > 0 ? 1u : 0u);
         umma_commit(&o_full[slot]);
+        JM_TRACE(i, 9, true);
         if (i % sh.nq == sh.nq - 1) umma_commit(&kv_empty[st]);  // every MMA that reads this stage has been issued
       };
       for (int i = 0; i < n_items; ++i) {
@@ -161,8 +227,10 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
           mbar_wait(&kv_full[st], (j / sh.stages) & 1);
           tc_fence_after();
         }
+        JM_TRACE(i, 10, true);
         mbar_wait(&o_empty[slot], ((i >> 1) & 1) ^ 1);  // the slot's previous O has been read out
         tc_fence_after();
+        JM_TRACE(i, 11, true);
         const uint32_t q_addr = smem_u32(sStage + st * sh.stage_bytes + qt * 128 * HD * 2);
         const uint32_t k_addr = smem_u32(sStage + st * sh.stage_bytes + sh.q_bytes);
 #pragma unroll
@@ -170,100 +238,94 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
           umma_bf16(tmem_base + slot * kSlotCols, desc_kmajor<HD>(q_addr, ks), desc_kmajor<HD>(k_addr, ks), idesc_s,
                     ks > 0 ? 1u : 0u);
         umma_commit(&s_full[slot]);
+        JM_TRACE(i, 12, true);
         if (i >= 1 && !pv_first) issue_pv(i - 1);
       }
       if (n_items >= 1) issue_pv(n_items - 1);
     }
   } else if (warp >= kTcSoftmaxWarp0) {
-    const int grp = (warp - kTcSoftmaxWarp0) >> 2;  // softmax group == TMEM slot
-    const int q = warp & 3;                         // TMEM lane quarter
-    const int row = q * 32 + lane;                  // row of the 128-query tile
-    const uint32_t t_slot = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + grp * kSlotCols;
-    const int nchunks = (sh.Nk + 31) >> 5;
-    for (int i = grp; i < n_items; i += 2) {
+    const int sw = warp - kTcSoftmaxWarp0;
+    const int slot = sw >> 3;       // TMEM slot == parity of the item
+    const int half = (sw >> 2) & 1; // which key columns of the tile
+    const int q = warp & 3;         // TMEM lane quarter
+    const int row = q * 32 + lane;  // row of the 128-query tile
+    const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + slot * kSlotCols;
+    const int h0 = half == 0 ? 0 : sh.cs, h1 = half == 0 ? sh.cs : sh.Nk;
+    const int n32 = (h1 - h0) >> 5;
+    const bool tail16 = ((h1 - h0) & 16) != 0;
+    float* xm_mine = sXm + (slot * 2 + half) * 128 + row;
+    float* xm_other = sXm + (slot * 2 + (half ^ 1)) * 128 + row;
+    float* xl_mine = sXl + (slot * 2 + half) * 128 + row;
+    float* xl_other = sXl + (slot * 2 + (half ^ 1)) * 128 + row;
+    constexpr int OC = HD / 2;  // output columns drained by this half
+    for (int i = slot; i < n_items; i += 2) {
       const int j = i / sh.nq, qt = i - j * sh.nq;
       const int prob = blockIdx.x + j * gridDim.x;
       const int b = prob / sh.heads, h = prob - b * sh.heads;
       const int tok = qt * 128 + row;
       const bool warp_live = qt * 128 + q * 32 < sh.T;  // warp-uniform: any valid row in this warp's 32
       const uint32_t ph = (i >> 1) & 1;
-      mbar_wait(&s_full[grp], ph);
+      const bool tr = half == 0 && q == 0 && lane == 0;
+      JM_TRACE(i, 0, tr);
+      mbar_wait(&s_full[slot], ph);
       tc_fence_after();
-      float l = 0.f, mx = -INFINITY;
+      JM_TRACE(i, 1, tr);
+      float mx = -INFINITY;
       if (warp_live) {
-        // pass 1: row maximum (columns >= T hold q . 0 = 0 and must not take part)
-        for (int c = 0; c < nchunks; ++c) {
-          uint32_t r[32];
-          tmem_ld_32x32(t_slot + c * 32, r);
-          tmem_ld_wait();
-          if (c * 32 + 32 > sh.T) {
-#pragma unroll
-            for (int e = 0; e < 32; ++e)
-              if (c * 32 + e >= sh.T) r[e] = 0xff800000u;  // -inf
-          }
-#pragma unroll
-          for (int e = 0; e < 32; e += 2) mx = fmax3(mx, __uint_as_float(r[e]), __uint_as_float(r[e + 1]));
-        }
-        // pass 2: P = exp2(s log2e - max log2e), row sum, bf16 P into the swizzled shared-memory tile
+        for (int c = 0; c < n32; ++c) fwd_chunk_max<32>(t_row, h0 + c * 32, sh.T, mx);
+        if (tail16) fwd_chunk_max<16>(t_row, h0 + n32 * 32, sh.T, mx);
+      }
+      *xm_mine = mx;
+      JM_TRACE(i, 2, tr);
+      named_bar_sync(1 + slot, 256);
+      mx = fmaxf(mx, *xm_other);
+      JM_TRACE(i, 3, tr);
+      float l = 0.f;
+      if (warp_live) {
         const float nm = -mx * kLog2eTc;
         const f32x2 k2 = pack2(kLog2eTc, kLog2eTc), nm2 = pack2(nm, nm);
         f32x2 l2 = pack2(0.f, 0.f);
-        for (int c = 0; c < nchunks; ++c) {
-          uint32_t r[32];
-          tmem_ld_32x32(t_slot + c * 32, r);
-          tmem_ld_wait();
-          if (c * 32 + 32 > sh.T) {
-#pragma unroll
-            for (int e = 0; e < 32; ++e)
-              if (c * 32 + e >= sh.T) r[e] = 0xff800000u;
-          }
-          uint32_t w[16];
-#pragma unroll
-          for (int e = 0; e < 32; e += 2) {
-            float x0, x1;
-            unpack2(fma2(pack2(__uint_as_float(r[e]), __uint_as_float(r[e + 1])), k2, nm2), x0, x1);
-            const float p0 = ex2_approx(x0), p1 = ex2_approx(x1);
-            l2 = add2(l2, pack2(p0, p1));
-            w[e >> 1] = pack_bf16(p0, p1);
-          }
-          // P overwrites S in place: the 32 f32 columns just read become 16 columns of bf16 pairs at [16 c, 16 c + 16),
-          // which lie inside columns this thread has already consumed
-          tmem_st_32x16(t_slot + c * 16, w);
-        }
+        // P overwrites S in place inside this half's own columns: chunk [c0, c0 + W) becomes W / 2 columns at
+        // h0 + (c0 - h0) / 2, which this thread has already consumed
+        for (int c = 0; c < n32; ++c) fwd_chunk_exp<32>(t_row, h0 + c * 32, h0 + c * 16, sh.T, k2, nm2, l2);
+        if (tail16) fwd_chunk_exp<16>(t_row, h0 + n32 * 32, h0 + n32 * 16, sh.T, k2, nm2, l2);
         float la, lb;
         unpack2(l2, la, lb);
         l = la + lb;
         tmem_st_wait();
       }
+      *xl_mine = l;
       // P is complete (tensor memory, the A operand of O = P V) and S has been consumed
       tc_fence_before();
-      mbar_arrive(&p_full[grp]);
-      mbar_wait(&o_full[grp], ph);
+      JM_TRACE(i, 4, tr);
+      mbar_arrive(&p_full[slot]);
+      mbar_wait(&o_full[slot], ph);
       tc_fence_after();
+      JM_TRACE(i, 5, tr);
+      named_bar_sync(1 + slot, 256);  // the other half's row sum is visible
+      l += *xl_other;
       if (warp_live) {
         const float inv = 1.0f / l;
-        uint32_t r[32];
+        uint32_t r[OC];
+        tmem_ld_w<OC>(t_row + sh.col_o + half * OC, r);
+        tmem_ld_wait();
+        if (tok < sh.T) {
+          __nv_bfloat16* dst = out + (static_cast<long>(b) * sh.T + tok) * sh.ldo + h * HD + half * OC;
 #pragma unroll
-        for (int c = 0; c < HD / 32; ++c) {
-          tmem_ld_32x32(t_slot + sh.col_o + c * 32, r);
-          tmem_ld_wait();
-          if (tok < sh.T) {
-            __nv_bfloat16* dst = out + (static_cast<long>(b) * sh.T + tok) * sh.ldo + h * HD + c * 32;
-#pragma unroll
-            for (int e = 0; e < 32; e += 8) {
-              uint4 v;
-              v.x = pack_bf16(__uint_as_float(r[e]) * inv, __uint_as_float(r[e + 1]) * inv);
-              v.y = pack_bf16(__uint_as_float(r[e + 2]) * inv, __uint_as_float(r[e + 3]) * inv);
-              v.z = pack_bf16(__uint_as_float(r[e + 4]) * inv, __uint_as_float(r[e + 5]) * inv);
-              v.w = pack_bf16(__uint_as_float(r[e + 6]) * inv, __uint_as_float(r[e + 7]) * inv);
-              *reinterpret_cast<uint4*>(dst + e) = v;
-            }
+          for (int e = 0; e < OC; e += 8) {
+            uint4 v;
+            v.x = pack_bf16(__uint_as_float(r[e]) * inv, __uint_as_float(r[e + 1]) * inv);
+            v.y = pack_bf16(__uint_as_float(r[e + 2]) * inv, __uint_as_float(r[e + 3]) * inv);
+            v.z = pack_bf16(__uint_as_float(r[e + 4]) * inv, __uint_as_float(r[e + 5]) * inv);
+            v.w = pack_bf16(__uint_as_float(r[e + 6]) * inv, __uint_as_float(r[e + 7]) * inv);
+            *reinterpret_cast<uint4*>(dst + e) = v;
           }
+          if (half == 0) lse[(static_cast<long>(b) * sh.heads + h) * sh.T + tok] = mx + logf(l);
         }
-        if (tok < sh.T) lse[(static_cast<long>(b) * sh.heads + h) * sh.T + tok] = mx + logf(l);
       }
       tc_fence_before();
-      mbar_arrive(&o_empty[grp]);
+      JM_TRACE(i, 6, tr);
+      mbar_arrive(&o_empty[slot]);
     }
   }
 
@@ -276,23 +338,27 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
 // Per (image, head) and 128-key tile kt, with TMEM lanes = keys (thread = one key row) and columns = queries:
 //   S^T  = K_kt Q^T      tcgen05.mma  M = 128 keys, N = queries (padded to 16), K = head_dim   -> columns [0, Nq)
 //   dP^T = V_kt dO^T     same shape                                                            -> columns [cP, cP + Nq)
-//   P^T  = exp2(S^T c - lse c),  dS^T = P^T (dP^T - D)        both softmax groups (each half of the query columns);
-//          lse and D = rowsum(dO . O) per query come from shared memory (broadcast reads); bf16 P^T and dS^T go to
-//          two SWIZZLE_128B tiles [key][query]
-//   dV_kt = P^T dO       A = P^T tile (K-major), B = dO rows in place (MN-major)       -> columns [0, hd)   (S is dead)
-//   dK_kt = dS^T Q       A = dS^T tile (K-major), B = Q rows in place (MN-major)       -> columns [cP, cP + hd)
-//   dQ   += dS K_kt      A = the same dS^T tile read MN-major (M = queries), B = K_kt rows (MN-major)
+//   P^T  = exp2(S^T c - lse c),  dS^T = P^T (dP^T - D)        sixteen warps: four per TMEM lane quarter, each a
+//          quarter of the query columns (in units of 16); lse and D = rowsum(dO . O) per query come from shared
+//          memory (broadcast reads).  bf16 P^T and dS^T overwrite S^T and dP^T in place as packed pairs (inside
+//          the column range of the warp that read them); dS^T also goes to a SWIZZLE_128B tile [key][query]
+//   dV_kt = P^T dO       A = P^T from tensor memory, B = dO rows in place (MN-major)          -> columns cV
+//   dK_kt = dS^T Q       A = dS^T from tensor memory, B = Q rows in place (MN-major)          -> columns cK
+//   dQ   += dS K_kt      A = the dS^T tile read MN-major (M = queries), B = K_kt rows (MN-major)
 //                        accumulates over the key tiles in columns [cQ, cQ + nq hd)
-// S and dP are computed once (5 matrix products per tile pair); nothing is recomputed and there are no atomics on
-// the gradients.  The bias gradients (column sums of dq, dk, dv) are reduced in shared memory per problem and added
-// to global memory with 3 hd atomics per problem, as the mma.sync kernel does.
+// S and dP are computed once (5 matrix products per tile); nothing is recomputed and there are no atomics on the
+// gradients.  Bias gradients: sum_q dQ (column sums at the drain), sum_key dV = sum_q dO (rows of P sum to one),
+// sum_key dK = 0 (rows of dS sum to zero); reduced in shared memory, 2 hd global atomics per problem.
+constexpr int kBwdThreads = 640;  // warps 0-3 as in the forward, warps 4-19: [column group 4][lane quarter 4]
+
 struct AttnTcBwdShape {
   int T, Nq, nq, nkt, heads, batch, stages;
   int q_bytes;      // Q (and dO): Nq rows, rounded up to 1024
   int k_bytes;      // K (and V): nkt * 128 rows
   int stage_bytes;  // Q + dO + K + V
-  int t_bytes;      // one P^T / dS^T tile
-  int cP, cQ;       // TMEM columns of dP^T and dQ
+  int t_bytes;      // the dS^T tile
+  int cP, cQ, cV, cK;  // TMEM columns of dP^T, dQ, dV, dK
+  int ustart[5];    // column group g owns the 16-query units [ustart[g], ustart[g + 1])
   long ldo, lddo, lddqkv;
   float q_scale;
 };
@@ -313,7 +379,7 @@ __device__ __forceinline__ float warp_colsum32(float (&v)[32], int lane) {
 }
 
 template <int HD>
-__global__ void __launch_bounds__(kTcThreads, 1)
+__global__ void __launch_bounds__(kBwdThreads, 1)
 attn_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                    const __grid_constant__ CUtensorMap tmdO, const AttnTcBwdShape sh,
                    const __nv_bfloat16* __restrict__ out, const __nv_bfloat16* __restrict__ dout,
@@ -322,19 +388,19 @@ attn_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   uint8_t* sStage = smem;
-  uint8_t* sPt = smem + sh.stages * sh.stage_bytes;
-  uint8_t* sDSt = sPt + sh.t_bytes;
+  uint8_t* sDSt = smem + sh.stages * sh.stage_bytes;
   float* sL2 = reinterpret_cast<float*>(sDSt + sh.t_bytes);  // [256] lse * log2(e) per query (+big for padding)
   float* sD = sL2 + 256;                                     // [256] rowsum(dO . O) per query
-  float* sBias = sD + 256;                                   // [3][HD]
-  uint64_t* bars = reinterpret_cast<uint64_t*>(sBias + 3 * HD);
+  float* sBias = sD + 256;                                   // [2][HD]: dq, dv column sums
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sBias + 2 * HD);
   uint64_t* kv_full = bars;       // [stages]
   uint64_t* kv_empty = bars + 4;  // [stages]
-  uint64_t* s_full = bars + 8;
-  uint64_t* p_full = bars + 9;
-  uint64_t* o_full = bars + 10;
-  uint64_t* t_free = bars + 11;
-  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 12);
+  uint64_t* s_full = bars + 8;    // S^T and dP^T of the tile are in tensor memory
+  uint64_t* p_full = bars + 9;    // P^T, dS^T written (512 arrivals)
+  uint64_t* vk_full = bars + 10;  // dV, dK of the tile are complete
+  uint64_t* q_full = bars + 11;   // dQ contribution of the tile is complete
+  uint64_t* t_free = bars + 12;   // the tile's results have left tensor memory (512 arrivals)
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 13);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   if (warp == 0 && elect_one()) {
@@ -346,12 +412,13 @@ attn_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
       mbar_init(&kv_empty[s], 1);
     }
     mbar_init(s_full, 1);
-    mbar_init(p_full, 256);
-    mbar_init(o_full, 1);
-    mbar_init(t_free, 256);
+    mbar_init(p_full, 512);
+    mbar_init(vk_full, 1);
+    mbar_init(q_full, 1);
+    mbar_init(t_free, 512);
     fence_barrier_init();
   }
-  for (int i = threadIdx.x; i < 3 * HD; i += blockDim.x) sBias[i] = 0.f;
+  for (int i = threadIdx.x; i < 2 * HD; i += blockDim.x) sBias[i] = 0.f;
   if (warp == 1) tmem_alloc<512>(tmem_ptr);
   tc_fence_before();
   __syncthreads();
@@ -382,9 +449,10 @@ attn_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
   } else if (warp == 1) {
     if (elect_one()) {
       const uint32_t idesc_s = make_idesc_bf16(128, sh.Nq, 0, 0);   // K-major A and B
-      const uint32_t idesc_kv = make_idesc_bf16(128, HD, 0, 1);     // K-major A (tile), MN-major B
+      const uint32_t idesc_kv = make_idesc_bf16(128, HD, 0, 1);     // A from tensor memory, MN-major B
       const uint32_t idesc_q = make_idesc_bf16(128, HD, 1, 1);      // MN-major A (tile, M = queries), MN-major B
-      const uint32_t pt_addr = smem_u32(sPt), dst_addr = smem_u32(sDSt);
+      const uint32_t dst_addr = smem_u32(sDSt);
+      constexpr uint64_t kStepMn = (16 * ROWB) >> 4;  // descriptor start-address increment per 16-row k-step
       int t = 0;  // tile counter of this CTA (barrier phases)
       for (int j = 0; j < my_prob; ++j) {
         const int st = j % sh.stages;
@@ -392,11 +460,14 @@ attn_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
         const uint32_t do_addr = q_addr + sh.q_bytes;
         const uint32_t k_addr = q_addr + 2 * sh.q_bytes;
         const uint32_t v_addr = k_addr + sh.k_bytes;
+        JM_TRACE(t, 8, true);
         mbar_wait(&kv_full[st], (j / sh.stages) & 1);
         tc_fence_after();
         for (int kt = 0; kt < sh.nkt; ++kt, ++t) {
+          JM_TRACE(t, 9, true);
           mbar_wait(t_free, (t & 1) ^ 1);  // previous tile's dV / dK (and dQ) have left tensor memory
           tc_fence_after();
+          JM_TRACE(t, 10, true);
 #pragma unroll
           for (int ks = 0; ks < HD / 16; ++ks)
             umma_bf16(tmem_base, desc_kmajor<HD>(k_addr + kt * 128 * ROWB, ks), desc_kmajor<HD>(q_addr, ks), idesc_s,
@@ -406,46 +477,66 @@ attn_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
             umma_bf16(tmem_base + sh.cP, desc_kmajor<HD>(v_addr + kt * 128 * ROWB, ks), desc_kmajor<HD>(do_addr, ks),
                       idesc_s, ks > 0 ? 1u : 0u);
           umma_commit(s_full);
+          JM_TRACE(t, 11, true);
           mbar_wait(p_full, t & 1);
           tc_fence_after();
-          const int qsteps = sh.Nq >> 4;
-          for (int kk = 0; kk < qsteps; ++kk)  // dV = P^T dO
-            umma_bf16(tmem_base, desc_ptile(pt_addr, kk), desc_mnmajor<HD>(do_addr, kk), idesc_kv, kk > 0 ? 1u : 0u);
-          for (int kk = 0; kk < qsteps; ++kk)  // dK = dS^T Q
-            umma_bf16(tmem_base + sh.cP, desc_ptile(dst_addr, kk), desc_mnmajor<HD>(q_addr, kk), idesc_kv,
-                      kk > 0 ? 1u : 0u);
-          for (int mt = 0; mt < sh.nq; ++mt)  // dQ += dS K_kt  (M = 128 queries of tile mt, K = 128 keys)
-            for (int kk = 0; kk < 8; ++kk)
-              umma_bf16(tmem_base + sh.cQ + mt * HD,
-                        make_smem_desc(dst_addr + mt * 2 * 16384 + kk * 2048, 16384, 1024, 2),
-                        desc_mnmajor<HD>(k_addr + kt * 128 * ROWB, kk), idesc_q, (kt > 0 || kk > 0) ? 1u : 0u);
-          umma_commit(o_full);
+          JM_TRACE(t, 12, true);
+          // dV = P^T dO and dK = dS^T Q: k-step kk = 16 queries; group g packed its unit kk at 8 (kk + ustart[g])
+          {
+            uint64_t d_do = desc_mnmajor<HD>(do_addr, 0), d_q = desc_mnmajor<HD>(q_addr, 0);
+            int kk = 0;
+            for (int g = 0; g < 4; ++g)
+              for (; kk < sh.ustart[g + 1]; ++kk, d_do += kStepMn)
+                umma_bf16_ts(tmem_base + sh.cV, tmem_base + 8 * (kk + sh.ustart[g]), d_do, idesc_kv, kk > 0 ? 1u : 0u);
+            kk = 0;
+            for (int g = 0; g < 4; ++g)
+              for (; kk < sh.ustart[g + 1]; ++kk, d_q += kStepMn)
+                umma_bf16_ts(tmem_base + sh.cK, tmem_base + sh.cP + 8 * (kk + sh.ustart[g]), d_q, idesc_kv,
+                             kk > 0 ? 1u : 0u);
+          }
+          umma_commit(vk_full);
+          JM_TRACE(t, 13, true);
+          for (int mt = 0; mt < sh.nq; ++mt) {  // dQ += dS K_kt  (M = 128 queries of tile mt, K = 128 keys)
+            uint64_t d_a = make_smem_desc(dst_addr + mt * 2 * 16384, 16384, 1024, 2);
+            uint64_t d_k = desc_mnmajor<HD>(k_addr + kt * 128 * ROWB, 0);
+#pragma unroll
+            for (int kk = 0; kk < 8; ++kk, d_a += (2048 >> 4), d_k += kStepMn)
+              umma_bf16(tmem_base + sh.cQ + mt * HD, d_a, d_k, idesc_q, (kt > 0 || kk > 0) ? 1u : 0u);
+          }
+          umma_commit(q_full);
+          JM_TRACE(t, 14, true);
           if (kt == sh.nkt - 1) umma_commit(&kv_empty[st]);
         }
       }
     }
   } else if (warp >= kTcSoftmaxWarp0) {
-    const int ctid = threadIdx.x - kTcSoftmaxWarp0 * 32;  // 0..255
-    const int grp = ctid >> 7;                            // half of the query columns
+    const int ctid = threadIdx.x - kTcSoftmaxWarp0 * 32;  // 0..511
+    const int grp = ctid >> 7;                            // column group
     const int q = warp & 3;                               // TMEM lane quarter
     const int krow = q * 32 + lane;                       // key row inside the 128-key tile
     const uint32_t t_lane = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
-    const uint32_t pt_addr = smem_u32(sPt), dst_addr = smem_u32(sDSt);
-    const int nch = (sh.Nq + 31) >> 5;
-    const int ch0 = grp == 0 ? 0 : (nch + 1) / 2, ch1 = grp == 0 ? (nch + 1) / 2 : nch;
+    const uint32_t dst_addr = smem_u32(sDSt);
+    const int u0 = sh.ustart[grp], u1 = sh.ustart[grp + 1];
+    constexpr int DC = HD / 2;  // result columns drained per thread
     int t = 0;
     for (int j = 0; j < my_prob; ++j) {
       const int prob = blockIdx.x + j * gridDim.x;
       const int b = prob / sh.heads, h = prob - b * sh.heads;
       // per-query statistics: lse * log2(e) and D = rowsum(dO . O), one query per thread, rows from global memory
       // (their latency overlaps the TMA fill and the first two matrix products of this problem)
-      {
+      const bool tr = ctid == 0;
+      JM_TRACE(t, 0, tr);
+      if (ctid < 256) {
         float L2 = 1e30f, Dv = 0.f;
-        if (ctid < sh.T) {
+        const bool live = ctid < sh.T;
+        uint4 gv[HD / 8];
+#pragma unroll
+        for (int c = 0; c < HD / 8; ++c) gv[c] = make_uint4(0u, 0u, 0u, 0u);
+        if (live) {
           const long tokr = static_cast<long>(b) * sh.T + ctid;
           const __nv_bfloat16* orow = out + tokr * sh.ldo + h * HD;
           const __nv_bfloat16* grow = dout + tokr * sh.lddo + h * HD;
-          uint4 ov[HD / 8], gv[HD / 8];
+          uint4 ov[HD / 8];
 #pragma unroll
           for (int c = 0; c < HD / 8; ++c) {
             ov[c] = *reinterpret_cast<const uint4*>(orow + c * 8);
@@ -465,26 +556,49 @@ attn_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
         }
         sL2[ctid] = L2;
         sD[ctid] = Dv;
+        if (dbias != nullptr && (ctid & ~31) < sh.T) {  // warp-uniform: this warp holds at least one live query
+          // bias gradient of v: sum over keys of dV = sum over queries of dO (every row of P sums to one)
+#pragma unroll
+          for (int c = 0; c < HD / 32; ++c) {
+            float v[32];
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              const uint4 u4 = gv[c * 4 + e];
+              const uint32_t gw[4] = {u4.x, u4.y, u4.z, u4.w};
+#pragma unroll
+              for (int k = 0; k < 4; ++k) {
+                const float2 g2 = unpack_bf16(gw[k]);
+                v[e * 8 + 2 * k] = g2.x, v[e * 8 + 2 * k + 1] = g2.y;
+              }
+            }
+            const float cs = warp_colsum32(v, lane);
+            atomicAdd(&sBias[HD + c * 32 + lane], cs);
+          }
+        }
       }
-      named_bar_sync(1, 256);
+      named_bar_sync(1, 512);
+      JM_TRACE(t, 1, tr);
       for (int kt = 0; kt < sh.nkt; ++kt, ++t) {
         const int key = kt * 128 + krow;
         const bool key_ok = key < sh.T;
         const bool warp_live = kt * 128 + q * 32 < sh.T;
+        JM_TRACE(t, 2, tr);
         mbar_wait(s_full, t & 1);
         tc_fence_after();
+        JM_TRACE(t, 3, tr);
         const f32x2 k2 = pack2(kLog2eTc, kLog2eTc);
-        for (int c = ch0; c < ch1; ++c) {
-          uint32_t wp[16], wd[16];
+        for (int u = u0; u < u1; ++u) {
+          const int c0 = u * 16;
+          uint32_t wd[8];
           if (warp_live) {
-            uint32_t rs[32], rp[32];
-            tmem_ld_32x32(t_lane + c * 32, rs);
-            tmem_ld_32x32(t_lane + sh.cP + c * 32, rp);
+            uint32_t rs[16], rp[16], wp[8];
+            tmem_ld_32x16(t_lane + c0, rs);
+            tmem_ld_32x16(t_lane + sh.cP + c0, rp);
             tmem_ld_wait();
 #pragma unroll
-            for (int e = 0; e < 32; e += 4) {
-              const float4 l4 = *reinterpret_cast<const float4*>(sL2 + c * 32 + e);
-              const float4 d4 = *reinterpret_cast<const float4*>(sD + c * 32 + e);
+            for (int e = 0; e < 16; e += 4) {
+              const float4 l4 = *reinterpret_cast<const float4*>(sL2 + c0 + e);
+              const float4 d4 = *reinterpret_cast<const float4*>(sD + c0 + e);
               float x0, x1, x2, x3;
               unpack2(fma2(pack2(__uint_as_float(rs[e]), __uint_as_float(rs[e + 1])), k2, pack2(-l4.x, -l4.y)), x0, x1);
               unpack2(fma2(pack2(__uint_as_float(rs[e + 2]), __uint_as_float(rs[e + 3])), k2, pack2(-l4.z, -l4.w)), x2, x3);
@@ -496,90 +610,87 @@ attn_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
               wp[e >> 1] = pack_bf16(p0, p1), wp[(e >> 1) + 1] = pack_bf16(p2, p3);
               wd[e >> 1] = pack_bf16(s0, s1), wd[(e >> 1) + 1] = pack_bf16(s2, s3);
             }
+            // packed pairs go back in place, inside this warp's own column range (already consumed)
+            tmem_st_32x8(t_lane + 8 * (u + u0), wp);
+            tmem_st_32x8(t_lane + sh.cP + 8 * (u + u0), wd);
           } else {
 #pragma unroll
-            for (int e = 0; e < 16; ++e) wp[e] = 0u, wd[e] = 0u;
+            for (int e = 0; e < 8; ++e) wd[e] = 0u;
           }
-#pragma unroll
-          for (int jj = 0; jj < 4; ++jj) {
-            const uint32_t off = ptile_chunk(krow, c * 4 + jj);
-            sts128(pt_addr + off, wp[4 * jj], wp[4 * jj + 1], wp[4 * jj + 2], wp[4 * jj + 3]);
-            sts128(dst_addr + off, wd[4 * jj], wd[4 * jj + 1], wd[4 * jj + 2], wd[4 * jj + 3]);
-          }
+          // dS^T also goes to shared memory (dead key rows as zeros: they are contracted over in dQ)
+          sts128(dst_addr + ptile_chunk(krow, 2 * u), wd[0], wd[1], wd[2], wd[3]);
+          sts128(dst_addr + ptile_chunk(krow, 2 * u + 1), wd[4], wd[5], wd[6], wd[7]);
         }
+        if (warp_live) tmem_st_wait();
         tc_fence_before();
         fence_proxy_async();
+        JM_TRACE(t, 4, tr);
         mbar_arrive(p_full);
-        mbar_wait(o_full, t & 1);
+        mbar_wait(vk_full, t & 1);
         tc_fence_after();
-        // drain: group 0 takes dV (columns [0, hd)), group 1 takes dK (columns [cP, cP + hd)); thread = key row
+        JM_TRACE(t, 5, tr);
+        // drain: groups 0, 1 take the two halves of dV's columns, groups 2, 3 of dK's; thread = key row
         if (warp_live) {
-          const uint32_t col0 = grp == 0 ? 0u : static_cast<uint32_t>(sh.cP);
-          __nv_bfloat16* dst = dqkv + (static_cast<long>(b) * sh.T + key) * sh.lddqkv + (grp == 0 ? 2 * d : d) + h * HD;
+          const uint32_t col0 = (grp < 2 ? sh.cV : sh.cK) + (grp & 1) * DC;
+          uint32_t r[DC];
+          tmem_ld_w<DC>(t_lane + col0, r);
+          tmem_ld_wait();
+          if (key_ok) {
+            __nv_bfloat16* dst = dqkv + (static_cast<long>(b) * sh.T + key) * sh.lddqkv + (grp < 2 ? 2 * d : d) + h * HD +
+                                 (grp & 1) * DC;
 #pragma unroll
-          for (int c = 0; c < HD / 32; ++c) {
-            uint32_t r[32];
-            tmem_ld_32x32(t_lane + col0 + c * 32, r);
+            for (int e = 0; e < DC; e += 8) {
+              uint4 w;
+              w.x = pack_bf16(__uint_as_float(r[e]), __uint_as_float(r[e + 1]));
+              w.y = pack_bf16(__uint_as_float(r[e + 2]), __uint_as_float(r[e + 3]));
+              w.z = pack_bf16(__uint_as_float(r[e + 4]), __uint_as_float(r[e + 5]));
+              w.w = pack_bf16(__uint_as_float(r[e + 6]), __uint_as_float(r[e + 7]));
+              *reinterpret_cast<uint4*>(dst + e) = w;
+            }
+          }
+        }
+        if (kt == sh.nkt - 1) {
+          mbar_wait(q_full, t & 1);
+          tc_fence_after();
+          // dQ is complete: groups (2 mt, 2 mt + 1) drain the two column halves of query tile mt; thread = query row
+          const int mt = grp >> 1;
+          if (mt < sh.nq && mt * 128 + q * 32 < sh.T) {
+            const int qrow = mt * 128 + krow;
+            const bool q_ok = qrow < sh.T;
+            uint32_t r[DC];
+            tmem_ld_w<DC>(t_lane + sh.cQ + mt * HD + (grp & 1) * DC, r);
             tmem_ld_wait();
             float v[32];
 #pragma unroll
-            for (int e = 0; e < 32; ++e) v[e] = key_ok ? __uint_as_float(r[e]) : 0.f;
-            if (key_ok) {
+            for (int e = 0; e < 32; ++e) v[e] = (e < DC && q_ok) ? __uint_as_float(r[e < DC ? e : 0]) * sh.q_scale : 0.f;
+            if (q_ok) {
+              __nv_bfloat16* dst = dqkv + (static_cast<long>(b) * sh.T + qrow) * sh.lddqkv + h * HD + (grp & 1) * DC;
 #pragma unroll
-              for (int e = 0; e < 32; e += 8) {
+              for (int e = 0; e < DC; e += 8) {
                 uint4 w;
                 w.x = pack_bf16(v[e], v[e + 1]), w.y = pack_bf16(v[e + 2], v[e + 3]);
                 w.z = pack_bf16(v[e + 4], v[e + 5]), w.w = pack_bf16(v[e + 6], v[e + 7]);
-                *reinterpret_cast<uint4*>(dst + c * 32 + e) = w;
+                *reinterpret_cast<uint4*>(dst + e) = w;
               }
             }
             if (dbias != nullptr) {
               const float cs = warp_colsum32(v, lane);
-              atomicAdd(&sBias[(grp == 0 ? 2 : 1) * HD + c * 32 + lane], cs);
-            }
-          }
-        }
-        if (kt == sh.nkt - 1 && grp < sh.nq) {
-          // dQ of query tile `grp` is complete: thread = query row
-          const int qrow = grp * 128 + krow;
-          const bool q_ok = qrow < sh.T;
-          if (grp * 128 + q * 32 < sh.T) {
-            __nv_bfloat16* dst = dqkv + (static_cast<long>(b) * sh.T + qrow) * sh.lddqkv + h * HD;
-#pragma unroll
-            for (int c = 0; c < HD / 32; ++c) {
-              uint32_t r[32];
-              tmem_ld_32x32(t_lane + sh.cQ + grp * HD + c * 32, r);
-              tmem_ld_wait();
-              float v[32];
-#pragma unroll
-              for (int e = 0; e < 32; ++e) v[e] = q_ok ? __uint_as_float(r[e]) * sh.q_scale : 0.f;
-              if (q_ok) {
-#pragma unroll
-                for (int e = 0; e < 32; e += 8) {
-                  uint4 w;
-                  w.x = pack_bf16(v[e], v[e + 1]), w.y = pack_bf16(v[e + 2], v[e + 3]);
-                  w.z = pack_bf16(v[e + 4], v[e + 5]), w.w = pack_bf16(v[e + 6], v[e + 7]);
-                  *reinterpret_cast<uint4*>(dst + c * 32 + e) = w;
-                }
-              }
-              if (dbias != nullptr) {
-                const float cs = warp_colsum32(v, lane);
-                atomicAdd(&sBias[c * 32 + lane], cs);
-              }
+              if (lane < DC) atomicAdd(&sBias[(grp & 1) * DC + lane], cs);
             }
           }
         }
         tc_fence_before();
+        JM_TRACE(t, 6, tr);
         mbar_arrive(t_free);
       }
       // bias gradients of this (image, head): shared-memory sums -> global atomics, then clear for the next one
-      named_bar_sync(1, 256);
-      if (dbias != nullptr && ctid < 3 * HD) {
-        const int part = ctid / HD, c = ctid - part * HD;
-        atomicAdd(dbias + part * d + h * HD + c, sBias[ctid]);
+      named_bar_sync(1, 512);
+      if (dbias != nullptr && ctid < 2 * HD) {
+        const int part = ctid / HD, c = ctid - part * HD;  // 0: dq, 1: dv
+        atomicAdd(dbias + (part == 0 ? 0 : 2 * d) + h * HD + c, sBias[ctid]);
         sBias[ctid] = 0.f;
       }
-      named_bar_sync(1, 256);
+      named_bar_sync(1, 512);
     }
   }
 
@@ -614,7 +725,16 @@ int fill_shape(AttnTcShape* sh, int batch, int T, int heads, int hd, int tiles_p
   sh->heads = heads, sh->batch = batch;
   sh->q_bytes = sh->nq * 128 * hd * 2;
   sh->kv_bytes = (sh->Nk * hd * 2 + 1023) / 1024 * 1024;
-  sh->col_o = (sh->Nk / 2 + 31) / 32 * 32;
+  // P is packed in place at [0, cs / 2) and [cs, cs + (Nk - cs) / 2).  O goes behind the scores when the 256-column
+  // slot has room, otherwise into the gap [cs / 2, cs) that half 0 leaves (cs is then at least 2 * head_dim).
+  sh->cs = (sh->Nk / 2 + 15) / 16 * 16;
+  const int behind = (sh->Nk + 31) / 32 * 32;
+  if (behind + hd <= kSlotCols) {
+    sh->col_o = behind;
+  } else {
+    if (sh->cs < 2 * hd) sh->cs = 2 * hd;
+    sh->col_o = (sh->cs / 2 + 31) / 32 * 32;
+  }
   (void)tiles_per_stage;
   (void)ptiles;
   return 0;
@@ -627,7 +747,7 @@ int launch_tc_fwd(const jm_bf16* qkv, long ldqkv, int batch, int T, int heads, j
   fill_shape(&sh, batch, T, heads, HD, 0, 0);
   sh.stage_bytes = sh.q_bytes + 2 * sh.kv_bytes;
   sh.ldo = ldo;
-  const int fixed = 1024 + 256;
+  const int fixed = 1024 + 256 + 2 * 512 * 4;
   sh.stages = (kMaxDynSmem - fixed) / sh.stage_bytes;
   if (sh.stages > 3) sh.stages = 3;
   JM_CHECK(sh.stages >= 1, "jm_attention_fwd: T=%d hd=%d does not fit shared memory", T, HD);
@@ -646,9 +766,29 @@ int launch_tc_fwd(const jm_bf16* qkv, long ldqkv, int batch, int T, int heads, j
   }
   const int nprob = batch * heads, sms = sm_count();
   const int grid = nprob < sms ? nprob : sms;
-  JM_LAUNCH_PDL(kern, grid, kTcThreads, smem, stream, tmQ, tmKV, sh, reinterpret_cast<__nv_bfloat16*>(out), lse);
+  JM_LAUNCH_PDL(kern, grid, kFwdThreads, smem, stream, tmQ, tmKV, sh, reinterpret_cast<__nv_bfloat16*>(out), lse);
   JM_AFTER_LAUNCH();
   return 0;
+}
+
+// Tensor-memory and column-group layout of the backward kernel; false when the problem does not fit.
+bool bwd_layout(AttnTcBwdShape* sh, int T, int hd) {
+  sh->T = T, sh->Nq = (T + 15) / 16 * 16, sh->nq = (T + 127) / 128, sh->nkt = sh->nq;
+  const int U = sh->Nq / 16, base = U / 4, rem = U % 4;
+  sh->ustart[0] = 0;
+  for (int g = 0; g < 4; ++g) sh->ustart[g + 1] = sh->ustart[g] + base + (g < rem ? 1 : 0);
+  sh->cP = (sh->Nq + 31) / 32 * 32;
+  sh->cQ = 2 * sh->cP;
+  if (sh->cQ + sh->nq * hd + 2 * hd <= 512) {  // room for dV and dK of their own
+    sh->cV = sh->cQ + sh->nq * hd, sh->cK = sh->cV + hd;
+    return true;
+  }
+  // otherwise dV / dK go into the gap that column group 0 leaves behind its packed pairs: [8 n0, 16 n0) of the
+  // S^T region (and of the dP^T region), n0 = units of group 0
+  const int n0 = sh->ustart[1];
+  if (sh->cQ + sh->nq * hd > 512 || 8 * n0 < hd) return false;
+  sh->cV = 8 * n0, sh->cK = sh->cP + 8 * n0;
+  return true;
 }
 
 template <int HD>
@@ -656,21 +796,18 @@ int launch_tc_bwd(const jm_bf16* qkv, long ldqkv, const jm_bf16* out, long ldo, 
                   const float* lse, int batch, int T, int heads, float q_scale, jm_bf16* dqkv, long lddqkv,
                   float* dbias, cudaStream_t stream) {
   AttnTcBwdShape sh;
-  sh.T = T, sh.Nq = (T + 15) / 16 * 16, sh.nq = (T + 127) / 128, sh.nkt = sh.nq;
+  JM_CHECK(bwd_layout(&sh, T, HD), "jm_attention_bwd: T=%d hd=%d does not fit tensor memory", T, HD);
   sh.heads = heads, sh.batch = batch;
   sh.q_bytes = (sh.Nq * HD * 2 + 1023) / 1024 * 1024;
   sh.k_bytes = sh.nkt * 128 * HD * 2;
   sh.stage_bytes = 2 * sh.q_bytes + 2 * sh.k_bytes;
   const int blocks = (sh.Nq + 63) / 64;
   sh.t_bytes = (blocks > 2 * sh.nq ? blocks : 2 * sh.nq) * 16384;  // dQ's M = 128 reads two 64-query blocks per tile
-  sh.cP = (sh.Nq + 31) / 32 * 32;
-  if (sh.cP < HD) sh.cP = HD;  // dV / dK reuse the first head_dim columns of the S^T / dP^T regions
-  sh.cQ = 2 * sh.cP;
   sh.ldo = ldo, sh.lddo = lddo, sh.lddqkv = lddqkv, sh.q_scale = q_scale;
-  const int fixed = 1024 + 2 * sh.t_bytes + 2 * 256 * 4 + 3 * HD * 4 + 128;
+  const int fixed = 1024 + sh.t_bytes + 2 * 256 * 4 + 2 * HD * 4 + 128;
   sh.stages = (kMaxDynSmem - fixed) / sh.stage_bytes;
   if (sh.stages > 3) sh.stages = 3;
-  JM_CHECK(sh.stages >= 1 && sh.cQ + sh.nq * HD <= 512, "jm_attention_bwd: T=%d hd=%d does not fit", T, HD);
+  JM_CHECK(sh.stages >= 1, "jm_attention_bwd: T=%d hd=%d does not fit shared memory", T, HD);
   const int smem = fixed + sh.stages * sh.stage_bytes;
   CUtensorMap tmQ, tmK, tmdO;
   const long d = static_cast<long>(heads) * HD;
@@ -687,7 +824,7 @@ int launch_tc_bwd(const jm_bf16* qkv, long ldqkv, const jm_bf16* out, long ldo, 
   }
   const int nprob = batch * heads, sms = sm_count();
   const int grid = nprob < sms ? nprob : sms;
-  JM_LAUNCH_PDL(kern, grid, kTcThreads, smem, stream, tmQ, tmK, tmdO, sh, reinterpret_cast<const __nv_bfloat16*>(out),
+  JM_LAUNCH_PDL(kern, grid, kBwdThreads, smem, stream, tmQ, tmK, tmdO, sh, reinterpret_cast<const __nv_bfloat16*>(out),
                 reinterpret_cast<const __nv_bfloat16*>(dout), lse, reinterpret_cast<__nv_bfloat16*>(dqkv), dbias);
   JM_AFTER_LAUNCH();
   return 0;
@@ -697,13 +834,18 @@ int launch_tc_bwd(const jm_bf16* qkv, long ldqkv, const jm_bf16* out, long ldo, 
 
 bool attn_tc_supported(int T, int hd);
 
+#ifdef JM_ATTN_TRACE
+extern "C" int jm_debug_attn_trace(long long* host_buf) {  // 64 items x 16 stamps
+  JM_CUDA(cudaMemcpyFromSymbol(host_buf, g_attn_trace, sizeof(long long) * 64 * 16));
+  return 0;
+}
+#endif
+
 bool attn_tc_bwd_supported(int T, int hd) {
   static const int on = env_int("JM_ATTN_TC_BWD", 1);
   if (!on || !attn_tc_supported(T, hd)) return false;
-  const int Nq = (T + 15) / 16 * 16, nq = (T + 127) / 128;
-  int cP = (Nq + 31) / 32 * 32;
-  if (cP < hd) cP = hd;
-  return 2 * cP + nq * hd <= 512;  // S^T, dP^T and dQ must fit the 512 TMEM columns
+  AttnTcBwdShape sh;
+  return bwd_layout(&sh, T, hd);
 }
 
 int attn_tc_bwd(const jm_bf16* qkv, long ldqkv, const jm_bf16* out, long ldo, const jm_bf16* dout, long lddo,
