@@ -166,6 +166,26 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
       : "memory");
   return ok != 0;
 }
+// Non-blocking test of a phase (try_wait may suspend the thread for a while before it reports failure, which is
+// wrong for a loop that polls several barriers).
+__device__ __forceinline__ bool mbar_test_wait(uint64_t* bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t"
+      "}\n"
+      : "=r"(ok)
+      : "r"(smem_u32(bar)), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
+// Warp-uniform poll (all 32 lanes call it): true only when every lane has observed the phase as complete, so that
+// the warp never diverges on it and every lane has acquired what the barrier published.
+__device__ __forceinline__ bool mbar_try_wait_warp(uint64_t* bar, uint32_t parity) {
+  return __all_sync(0xffffffffu, mbar_test_wait(bar, parity));
+}
 // Bounded wait: a pipeline bug must trap (and surface as a CUDA error) instead of
 // hanging the GPU.  ~4e9 cycles is seconds; a healthy wait is microseconds.
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
@@ -235,6 +255,13 @@ __device__ __forceinline__ void tma_reduce_add_2d(const void* desc, uint32_t sme
   asm volatile("cp.reduce.async.bulk.tensor.2d.global.shared::cta.add.tile.bulk_group [%0, {%2, %3}], [%1];" ::"l"(
                    reinterpret_cast<uint64_t>(desc)),
                "r"(smem_addr), "r"(c0), "r"(c1)
+               : "memory");
+}
+// 3-D tiled store shared -> global (rows outside the tensor are clipped by the TMA unit).
+__device__ __forceinline__ void tma_store_3d(const void* desc, uint32_t smem_addr, int c0, int c1, int c2) {
+  asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];" ::"l"(
+                   reinterpret_cast<uint64_t>(desc)),
+               "r"(smem_addr), "r"(c0), "r"(c1), "r"(c2)
                : "memory");
 }
 __device__ __forceinline__ void tma_store_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }

@@ -27,8 +27,8 @@ if what == "fwd":
              "mma:P seen", "mma:PV issued", "mma:item top", "mma:slot free", "mma:S issued"]
     t0 = t[0][10]
 else:
-    names = ["cp:prob top", "cp:stats done", "cp:tile top", "cp:S ready", "cp:P done", "cp:dVdK ready", "cp:drained", "",
-             "mma:prob top", "mma:tile top", "mma:tmem free", "mma:S issued", "mma:P seen", "mma:dVdK issd", "mma:dQ issued"]
+    names = ["cp:top", "cp:S ready", "", "", "", "cp:P written", "cp:grads done", "", "",
+             "mma:S issued", "", "", "mma:P seen", "", "mma:grads issd"]
     t0 = t[0][9]
 print("item " + " ".join(f"{n:>13s}" for n in names if n))
 for i in range(4, 20):
