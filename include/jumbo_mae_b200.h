@@ -82,6 +82,15 @@ int jm_patch_loss(const float* pred, long ldp, const uint8_t* images, const floa
                   int image_size, int patch_size, int num_cls, int norm_pix, float grad_scale, float* loss,
                   jm_bf16* dpred, long lddp, void* workspace, size_t workspace_bytes, void* stream);
 
+/* patch_mse_loss(patch_output, patch_target, valid=None) with explicit targets, exactly src/utils_mae.py:51-64:
+ * mean over images of [ mean_L( valid > 0 ? mean_c (target - output)^2 : 0 ) / (sum(valid) / L) ].
+ * patch_output / patch_target are [batch*L, P] f32 with row strides ldo / ldt; valid is [batch, L] f32 or NULL
+ * (all ones).  An image without any valid patch gives 0/0 = NaN, as in the reference.
+ * workspace: jm_patch_loss_workspace(batch, L) bytes. */
+int jm_patch_mse_loss(const float* patch_output, long ldo, const float* patch_target, long ldt, const float* valid,
+                      int batch, int num_patches, int patch_dim, float* loss, void* workspace, size_t workspace_bytes,
+                      void* stream);
+
 /* jm_patch_loss without a workspace argument and without any allocation.  It has no counterpart
  * in the reference; it exists for hosts that are not allowed to allocate device memory around the
  * call: an XLA-FFI handler (XLA owns every device buffer and a handler must not call cudaMalloc),

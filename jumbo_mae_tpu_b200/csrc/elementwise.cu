@@ -307,6 +307,41 @@ __global__ void patch_loss_finalize_kernel(const float* __restrict__ partial, co
   if (threadIdx.x == 0) loss[0] = tot / (num_masked * static_cast<float>(batch));
 }
 
+// patch_mse_loss with explicit targets (src/utils_mae.py:51-64): one warp per (image, patch) row -> mean_c (t - o)^2
+__global__ void patch_mse_rows_kernel(const float* __restrict__ out, long ldo, const float* __restrict__ tgt, long ldt,
+                                      long rows, int P, float* __restrict__ rowmse) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const long row = static_cast<long>(blockIdx.x) * (blockDim.x >> 5) + warp;
+  if (row >= rows) return;
+  const float* o = out + row * ldo;
+  const float* t = tgt + row * ldt;
+  float acc = 0.f;
+  for (int c = lane; c < P; c += 32) {
+    const float dlt = t[c] - o[c];
+    acc = fmaf(dlt, dlt, acc);
+  }
+  acc = warp_sum(acc);
+  if (lane == 0) rowmse[row] = acc / static_cast<float>(P);
+}
+// ... then per image: mean_L(where(valid > 0, mse, 0)) / (sum(valid) / L), and the batch mean (one block, fixed order)
+__global__ void patch_mse_finalize_kernel(const float* __restrict__ rowmse, const float* __restrict__ valid, int L,
+                                          int batch, float* __restrict__ loss) {
+  __shared__ float red[32];
+  float total = 0.f;
+  for (int b = 0; b < batch; ++b) {
+    float num = 0.f, den = 0.f;
+    for (int i = threadIdx.x; i < L; i += blockDim.x) {
+      const float v = valid ? valid[static_cast<long>(b) * L + i] : 1.f;
+      num += v > 0.f ? rowmse[static_cast<long>(b) * L + i] : 0.f;
+      den += v;
+    }
+    num = block_sum(num, red);
+    den = block_sum(den, red);
+    total += (num / static_cast<float>(L)) / (den / static_cast<float>(L));
+  }
+  if (threadIdx.x == 0) loss[0] = total / static_cast<float>(batch);
+}
+
 // ---------------------------------------------------------------- LayerNorm
 constexpr int kLnWarps = 8;
 
@@ -956,6 +991,23 @@ extern "C" int jm_patch_loss(const float* pred, long ldp, const uint8_t* images,
                     reinterpret_cast<__nv_bfloat16*>(dpred), lddp, batch, N, P, STREAM);
   JM_AFTER_LAUNCH();
   patch_loss_finalize_kernel<<<1, 1024, 0, STREAM>>>(partial, mask_row, N, batch, loss);
+  JM_AFTER_LAUNCH();
+  return 0;
+}
+
+extern "C" int jm_patch_mse_loss(const float* patch_output, long ldo, const float* patch_target, long ldt,
+                                 const float* valid, int batch, int num_patches, int patch_dim, float* loss,
+                                 void* workspace, size_t workspace_bytes, void* stream) {
+  JM_CHECK(batch > 0 && num_patches > 0 && patch_dim > 0, "jm_patch_mse_loss: empty problem");
+  JM_CHECK(patch_output && patch_target && loss, "jm_patch_mse_loss: null argument");
+  JM_CHECK(workspace && workspace_bytes >= jm_patch_loss_workspace(batch, num_patches),
+           "jm_patch_mse_loss: workspace too small (jm_patch_loss_workspace(batch, num_patches) bytes)");
+  const long rows = static_cast<long>(batch) * num_patches;
+  float* rowmse = static_cast<float*>(workspace);
+  patch_mse_rows_kernel<<<static_cast<unsigned>((rows + 7) / 8), 256, 0, STREAM>>>(patch_output, ldo, patch_target, ldt,
+                                                                                  rows, patch_dim, rowmse);
+  JM_AFTER_LAUNCH();
+  patch_mse_finalize_kernel<<<1, 1024, 0, STREAM>>>(rowmse, valid, num_patches, batch, loss);
   JM_AFTER_LAUNCH();
   return 0;
 }

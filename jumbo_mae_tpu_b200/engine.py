@@ -157,10 +157,19 @@ class MAEEngine:
     # ------------------------------------------------------------------ forward
     def forward(self, images: torch.Tensor, noise: torch.Tensor, want_grad: bool = True,
                 grad_scale: float = 1.0) -> torch.Tensor:
-        """images uint8 [B,3,H,W] (device), noise f32 [N] (device) -> loss (device scalar tensor [1])."""
+        """images uint8 [B,3,H,W] (device), noise f32 [N] (device) -> loss (device scalar tensor [1]).
+        PretrainModule.__call__ (src/pretraining.py:87-122) = encoder, decoder input assembly, decoder, head + loss."""
+        self.forward_encoder(images, noise)
+        self.forward_decoder_input()
+        self.forward_decoder_stack()
+        return self.forward_head_and_loss(want_grad, grad_scale)
+
+    def forward_encoder(self, images: torch.Tensor, noise: torch.Tensor) -> None:
+        """ViT.__call__ in MAE mode (src/modeling.py:245-267) incl. the pixel normalisation of
+        src/pretraining.py:90-91: fills ids_restore / mask_row, xa[0..L] and the normalised output enc_n."""
         cfg, ps, B = self.cfg, self.ps, self.B
-        J, n, N, d, dd, P = cfg.num_cls_tokens, cfg.keep, cfg.num_patches, cfg.dim, cfg.dec_dim, cfg.patch_dim
-        Te, Td, Me, Md = self.Te, self.Td, self.Me, self.Md
+        J, n, N, d, P = cfg.num_cls_tokens, cfg.keep, cfg.num_patches, cfg.dim, cfg.patch_dim
+        Te, Me = self.Te, self.Me
         if tuple(images.shape) != (B, 3, cfg.image_size, cfg.image_size):
             raise _lib.JmError(f"engine built for images {(B, 3, cfg.image_size, cfg.image_size)}, got {tuple(images.shape)}")
         self.images = images
@@ -180,19 +189,31 @@ class MAEEngine:
             self._block_fwd(f"model/layer_{i}", self.enc[i], self.xa[i], self.xa[i + 1], Me, d, cfg.heads, Te, True)
         ops.layernorm_fwd(self.xa[cfg.layers], ps.f("model/norm/scale"), ps.f("model/norm/bias"), LN_EPS,
                           self.enc_n, None, self.meanF, self.rstdF)
-        # decoder_proj + mask tokens + unshuffle + dec_wpe (src/pretraining.py:95-106, modeling.py:289-292)
-        self._fwd_linear(self.enc_n, Me, "decoder_proj", dd, d, out_f32=self.y)
+
+    def forward_decoder_input(self) -> None:
+        """decoder_proj + mask tokens + unshuffle + dec_wpe (src/pretraining.py:95-106, modeling.py:289-292) -> za[0]."""
+        cfg, ps, B = self.cfg, self.ps, self.B
+        J, n, N, d, dd = cfg.num_cls_tokens, cfg.keep, cfg.num_patches, cfg.dim, cfg.dec_dim
+        self._fwd_linear(self.enc_n, self.Me, "decoder_proj", dd, d, out_f32=self.y)
         ops.unshuffle_fwd(self.y, self.ids_restore, ps.f("image_mask_embedding"), self.dec_wpe, B, N, n, J, dd,
                           self.za[0])
+
+    def forward_decoder_stack(self) -> None:
+        """MAEDecoder's blocks and final norm (src/modeling.py:293-298) on za[0] (which already carries dec_wpe)."""
+        cfg, ps = self.cfg, self.ps
         for i in range(cfg.dec_layers):
-            self._block_fwd(f"decoder_model/dec_layer_{i}", self.dec[i], self.za[i], self.za[i + 1], Md, dd,
-                            cfg.dec_heads, Td, False)
+            self._block_fwd(f"decoder_model/dec_layer_{i}", self.dec[i], self.za[i], self.za[i + 1], self.Md, cfg.dec_dim,
+                            cfg.dec_heads, self.Td, False)
         ops.layernorm_fwd(self.za[cfg.dec_layers], ps.f("decoder_model/dec_norm/scale"),
                           ps.f("decoder_model/dec_norm/bias"), LN_EPS, self.dec_n, None, self.meanD, self.rstdD)
+
+    def forward_head_and_loss(self, want_grad: bool = True, grad_scale: float = 1.0) -> torch.Tensor:
+        """decoder_image_output + extract_patches + (norm-pix) + patch_mse_loss (src/pretraining.py:110-120)."""
+        cfg = self.cfg
         # pixel head on every token row; CLS / visible rows are ignored by the loss
-        self._fwd_linear(self.dec_n, Md, "decoder_image_output", P, dd, out_f32=self.pred)
-        ops.patch_loss(self.pred, images, self.mask_row, cfg.patch_size, J, cfg.norm_pix_loss, grad_scale, self.loss,
-                       self.dpred if want_grad else None, self.loss_ws)
+        self._fwd_linear(self.dec_n, self.Md, "decoder_image_output", cfg.patch_dim, cfg.dec_dim, out_f32=self.pred)
+        ops.patch_loss(self.pred, self.images, self.mask_row, cfg.patch_size, cfg.num_cls_tokens, cfg.norm_pix_loss,
+                       grad_scale, self.loss, self.dpred if want_grad else None, self.loss_ws)
         return self.loss
 
     def _block_fwd(self, name, s: _Block, x_in, x_out, M, dim, heads, T, jumbo):

@@ -74,26 +74,77 @@ class MAEDecoderBase:
         return (self.image_size // self.patch_size,) * 2
 
 
-@dataclass
-class ViT(ViTBase):
-    """ViT with the Jumbo CLS token, MAE branch (src/modeling.py:221-267).
+class _Bound:
+    """What ``flax.linen.Module.bind(variables, rngs=...)`` gives the reference's modules: parameters (here the flat
+    device ``ParamStore``) and RNG streams (here the uniform mask noise itself, f32 [num_patches], because the
+    Flax/threefry stream cannot be reproduced outside JAX).  Engines (activation buffers) are cached per batch size."""
 
-    ``encode(store, images, noise)`` runs PatchEmbed + CLS + random_masking + JumboLayer x L + norm
-    and returns ``(x [B, J+keep, dim] f32, mask [B, L] f32, ids_restore [L] i32)`` like
-    ``ViT.__call__`` in MAE mode (``labels <= 0``).  images are the uint8 NCHW batch: the pixel
-    normalisation of PretrainModule (src/pretraining.py:90-91) is fused into the patch loader."""
+    def bind(self, store, rngs=None):
+        import copy
+        m = copy.copy(self)
+        m._store, m._rngs, m._engines = store, dict(rngs or {}), {}
+        return m
+
+    def _need_store(self):
+        if getattr(self, "_store", None) is None:
+            raise _lib.JmError(f"{type(self).__name__} is unbound: call .bind(store, rngs={{'noise': ...}}) first")
+        return self._store
+
+    def _noise(self, device):
+        nz = self._rngs.get("noise")
+        if nz is None:
+            raise _lib.JmError("rngs['noise'] (f32 [num_patches] uniform noise) is required for random masking")
+        if not isinstance(nz, torch.Tensor):
+            import numpy as np
+            nz = torch.from_numpy(np.ascontiguousarray(nz, dtype=np.float32))
+        return nz.to(device=device, dtype=torch.float32).contiguous()
+
+    def _engine(self, batch: int):
+        store = self._need_store()
+        if batch not in self._engines:
+            if store.cfg.labels > 0:
+                from .finetune_engine import FinetuneEngine
+                self._engines[batch] = FinetuneEngine(store.cfg, store, batch)
+            else:
+                from .engine import MAEEngine
+                self._engines[batch] = MAEEngine(store.cfg, store, batch)
+        return self._engines[batch]
+
+
+@dataclass
+class ViT(ViTBase, _Bound):
+    """ViT with the Jumbo CLS token (src/modeling.py:221-274).
+
+    ``ViT(...).bind(store, rngs={"noise": noise})(x, det=True)`` mirrors ``ViT.__call__(x, det=True)`` (:245):
+    MAE mode (``labels`` None or <= 0) returns ``(x [B, J+keep, dim] f32, mask [B, L] f32, ids_restore [L] i32)``,
+    classification mode returns the logits ``[B, labels]``.  ``x`` is the uint8 NCHW batch: the pixel normalisation
+    of PretrainModule (src/pretraining.py:90-91) is fused into the patch loader, the f32 NHWC image never exists."""
     num_cls_tokens: int = 3
 
     def __post_init__(self):
-        if self.labels is not None and self.labels > 0:
-            raise NotImplementedError("classification head (labels > 0) is the fine-tune path, not built yet")
         if self.layerscale or self.dropout or self.droppath or self.posemb != "sincos2d":
             raise NotImplementedError("layerscale / dropout / droppath / learnable posemb are off in the presets")
 
+    def _check(self, cfg):
+        if cfg.dim != self.dim or cfg.layers != self.layers or cfg.heads != self.heads or \
+                cfg.patch_size != self.patch_size or cfg.image_size != self.image_size:
+            raise _lib.JmError("the bound parameter store was built for a different encoder")
+
+    def __call__(self, x: torch.Tensor, det: bool = True):
+        store = self._need_store()
+        self._check(store.cfg)
+        eng = self._engine(x.shape[0])
+        x = x.to(store.device).contiguous()
+        if store.cfg.labels > 0:                                    # classification branch (:269-274)
+            labels = torch.zeros(x.shape[0], dtype=torch.int32, device=store.device)
+            eng.forward(x, labels, want_grad=False)
+            return eng.logits
+        return self.encode(eng, x, self._noise(store.device))
+
     def encode(self, engine, images: torch.Tensor, noise: torch.Tensor):
-        if engine.cfg.dim != self.dim or engine.cfg.layers != self.layers:
-            raise _lib.JmError("engine was built for a different encoder")
-        engine.forward(images, noise, want_grad=False)
+        """MAE branch on a given engine: PatchEmbed + CLS + random_masking + JumboLayer x L + norm (:245-267)."""
+        self._check(engine.cfg)
+        engine.forward_encoder(images, noise)
         B = images.shape[0]
         x = torch.empty(B * engine.Te, self.dim, dtype=torch.float32, device=images.device)
         from . import ops
@@ -104,10 +155,33 @@ class ViT(ViTBase):
 
 
 @dataclass
-class MAEDecoder(MAEDecoderBase):
-    """src/modeling.py:276-298."""
+class MAEDecoder(MAEDecoderBase, _Bound):
+    """src/modeling.py:276-298.  ``MAEDecoder(...).bind(store)(x, det=True)``: ``x`` is the f32 ``[B, J + L, dec_dim]``
+    decoder input (CLS tokens first, mask tokens already inserted and unshuffled, src/pretraining.py:95-106); adds the
+    fixed sincos position embedding to the patch tokens, runs the ``dec_layers`` ViTLayers and ``dec_norm``."""
     num_cls_tokens: int = 3
 
     def __post_init__(self):
         if self.dec_layerscale or self.dec_dropout or self.dec_droppath:
             raise NotImplementedError("decoder layerscale / dropout / droppath are off in the presets")
+
+    def __call__(self, x: torch.Tensor, det: bool = True) -> torch.Tensor:
+        from . import ops
+        store = self._need_store()
+        cfg = store.cfg
+        if cfg.dec_dim != self.dec_dim or cfg.dec_layers != self.dec_layers or cfg.dec_heads != self.dec_heads:
+            raise _lib.JmError("the bound parameter store was built for a different decoder")
+        B, Td, dd = x.shape
+        eng = self._engine(B)
+        if Td != eng.Td or dd != cfg.dec_dim:
+            raise _lib.JmError(f"decoder input must be [B, {eng.Td}, {cfg.dec_dim}], got {tuple(x.shape)}")
+        J, N = cfg.num_cls_tokens, cfg.num_patches
+        xin = x.to(device=store.device, dtype=torch.float32).contiguous().view(B * Td, dd)
+        ids = torch.arange(N, dtype=torch.int32, device=store.device)
+        # x[:, J:] += dec_wpe (:289-292): the unshuffle kernel with the identity permutation and no mask tokens
+        ops.unshuffle_fwd(xin, ids, store.f("image_mask_embedding"), eng.dec_wpe, B, N, N, J, dd, eng.za[0])
+        eng.forward_decoder_stack()
+        out = torch.empty(B * Td, dd, dtype=torch.float32, device=store.device)
+        ops.layernorm_fwd(eng.za[cfg.dec_layers], store.f("decoder_model/dec_norm/scale"),
+                          store.f("decoder_model/dec_norm/bias"), 1e-6, None, out, None, None)
+        return out.view(B, Td, dd)

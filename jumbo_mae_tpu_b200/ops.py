@@ -119,6 +119,16 @@ def patch_loss(pred: torch.Tensor, images: torch.Tensor, mask_row: torch.Tensor,
                                     workspace.numel() * workspace.element_size(), stream_ptr()))
 
 
+def patch_mse_loss(patch_output: torch.Tensor, patch_target: torch.Tensor, valid: Optional[torch.Tensor],
+                   loss: torch.Tensor, workspace: torch.Tensor) -> None:
+    """src/utils_mae.py:51-64 on explicit f32 targets [B, L, P]; valid [B, L] f32 or None."""
+    _chk(patch_output, F32, "patch_output"), _chk(patch_target, F32, "patch_target"), _chk(valid, F32, "valid")
+    _chk(loss, F32, "loss")
+    B, L, P = patch_output.shape
+    check(_lib.load().jm_patch_mse_loss(ptr(patch_output), P, ptr(patch_target), P, ptr(valid), B, L, P, ptr(loss),
+                                        ptr(workspace), workspace.numel() * workspace.element_size(), stream_ptr()))
+
+
 # ------------------------------------------------------------------ LayerNorm
 def layernorm_fwd(x: torch.Tensor, gamma: torch.Tensor, beta: torch.Tensor, eps: float,
                   y_bf16: Optional[torch.Tensor], y_f32: Optional[torch.Tensor], mean: Optional[torch.Tensor],

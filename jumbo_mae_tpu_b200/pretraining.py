@@ -21,7 +21,7 @@ import torch
 from . import _lib, ops
 from .config import MAEConfig
 from .engine import MAEEngine, lr_schedule
-from .modeling import MAEDecoder, ViT
+from .modeling import MAEDecoder, ViT, _Bound
 from .parallel import GradReducer, process_count, process_index
 from .params import ParamStore
 
@@ -30,8 +30,11 @@ from .params import ParamStore
 USE_CUDA_GRAPH = os.environ.get("JM_NO_GRAPH", "0") != "1"
 
 
-class PretrainModule:
-    """PretrainModule (src/pretraining.py:76-122): ViT encoder + MAEDecoder + pixel head."""
+class PretrainModule(_Bound):
+    """PretrainModule (src/pretraining.py:76-122): ViT encoder + MAEDecoder + pixel head.
+
+    ``PretrainModule(...).bind(store, rngs={"noise": noise})(images, det=True)`` returns ``{"loss": scalar}`` like
+    ``PretrainModule.__call__(images, det=True)`` (:87); images are the uint8 NCHW batch."""
 
     def __init__(self, model: ViT, decoder_model: MAEDecoder, image_size: int, norm_pix_loss: bool = False):
         self.model, self.decoder_model = model, decoder_model
@@ -43,6 +46,15 @@ class PretrainModule:
                          image_mask_ratio=m.image_mask_ratio, num_cls_tokens=m.num_cls_tokens,
                          dec_layers=dm.dec_layers, dec_dim=dm.dec_dim, dec_heads=dm.dec_heads,
                          norm_pix_loss=self.norm_pix_loss, **opt)
+
+    def __call__(self, images: torch.Tensor, det: bool = True) -> Dict[str, torch.Tensor]:
+        store = self._need_store()
+        if store.cfg.norm_pix_loss != self.norm_pix_loss or store.cfg.dim != self.model.dim:
+            raise _lib.JmError("the bound parameter store was built for a different module")
+        images = _device_images(images).to(store.device)
+        eng = self._engine(images.shape[0])
+        loss = eng.forward(images, self._noise(store.device), want_grad=False)
+        return {"loss": loss[0].clone()}
 
 
 @dataclass

@@ -38,10 +38,27 @@ def extract_patches(inputs: torch.Tensor, patch_size: int) -> torch.Tensor:
     return ops.extract_patches_u8(inputs, patch_size)
 
 
-def patch_mse_loss(patch_output: torch.Tensor, images: torch.Tensor, valid: torch.Tensor, patch_size: int,
-                   norm_pix: bool = False) -> torch.Tensor:
-    """src/utils_mae.py:51-64 with the target computed from ``images`` (uint8 NCHW) on the fly.
-    patch_output is [B, L, P] f32; valid is the [L] or [B, L] mask (one row is used)."""
+def patch_mse_loss(patch_output: torch.Tensor, patch_target: torch.Tensor, valid: torch.Tensor | None = None
+                   ) -> torch.Tensor:
+    """src/utils_mae.py:51-64, same signature: mean over the batch of the valid patches' mean squared error.
+    patch_output / patch_target are f32 [B, L, P], valid f32 [B, L] (``None``: every patch counts)."""
+    if patch_output.shape != patch_target.shape or patch_output.dim() != 3:
+        raise _lib.JmError("patch_output and patch_target must both be [B, L, P]")
+    B, L, _ = patch_output.shape
+    if valid is not None:
+        valid = valid.to(torch.float32).expand(B, L).contiguous()
+    loss = torch.zeros(1, dtype=torch.float32, device=patch_output.device)
+    ws = torch.empty(ops.patch_loss_workspace(B, L), dtype=torch.uint8, device=patch_output.device)
+    ops.patch_mse_loss(patch_output.to(torch.float32).contiguous(), patch_target.to(torch.float32).contiguous(), valid,
+                       loss, ws)
+    return loss[0]
+
+
+def patch_mse_loss_from_images(patch_output: torch.Tensor, images: torch.Tensor, valid: torch.Tensor, patch_size: int,
+                               norm_pix: bool = False) -> torch.Tensor:
+    """The fused form the training step uses: the target is computed from ``images`` (uint8 NCHW) on the fly
+    (src/pretraining.py:113-118 + src/utils_mae.py:51-64), so the f32 target never exists in memory.
+    patch_output is [B, L, P] f32; valid is the [L] or [B, L] mask (one row: the mask is shared by the batch)."""
     B, L, P = patch_output.shape
     mask_row = (valid[0] if valid.dim() == 2 else valid).to(torch.float32).contiguous()
     loss = torch.zeros(1, dtype=torch.float32, device=patch_output.device)
