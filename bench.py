@@ -147,14 +147,18 @@ def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    batch = 8 if args.steps + args.warmup <= 10 else 4
+    batch = 8                                  # BASELINE.json configs[0] / BASELINE.md section 4: batch 8 on the host cores
     ips, sec, cores, loss = cpu_oracle_rate(args.config, batch, args.steps, args.warmup)
     sample = f"{args.config} MAE step, batch {batch} per step, {args.warmup} warm-up + {args.steps} timed, f32 torch-CPU"
     line = {
         "impl": "reference", "metric": "mae_pretrain_images_per_sec", "value": ips, "unit": "images/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": sec * 1e3,
         "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": workload_config(args, 0, 0, 1),
+        "config": {"workload": f"MAE {args.config} 224px mask 0.75 decoder 8x512 Jumbo CLS J=3, batch {batch} synthetic uint8 "
+                               f"per step on the host cores (BASELINE.json configs[0]; a bounded sample of the GPU arm's "
+                               f"global batch {args.global_batch})",
+                   "global_batch": batch, "micro_batch": batch, "grad_accum": 1, "parallelism": "cpu", "norm_pix_loss": False,
+                   "l2": "n/a (host)"},
         "cpu_baseline": {"value": ips, "unit": "images/s", "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": ips, "unit": "images/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0, "loss": loss,
@@ -280,15 +284,19 @@ def run_ours(args):
     state.step, state.micro_step = counter["step"], 0
     e2e_losses = []
 
+    pending = {"next": None}
+
     def e2e_step():
-        # the input path of a training loop: while a micro-step runs, the next micro-batch is copied from pinned
-        # host memory on a copy stream (TrainState.prefetch); every copy and every loss read is inside the timed region
-        nxt = state.prefetch((host_images[0],))
+        # the input path of a training loop: as soon as a micro-step has been launched, the NEXT micro-batch (of this
+        # optimizer step or of the following one) is copied from pinned host memory on a copy stream
+        # (TrainState.prefetch), so the copy overlaps the running step also when there is one micro-step per
+        # optimizer step; every copy and every loss read is inside the timed region
+        if pending["next"] is None:
+            pending["next"] = state.prefetch((host_images[0],))
         for i in range(accum):
-            cur = nxt
+            cur = pending["next"]
             _, metrics = training_step(state, cur)
-            if i + 1 < accum:
-                nxt = state.prefetch((host_images[i + 1],))
+            pending["next"] = state.prefetch((host_images[(i + 1) % accum],))
             e2e_losses.append(metrics["loss"].item())          # device -> host read of the step's result
 
     e2e_step()                                                  # warm-up of the API path (allocations)
@@ -328,6 +336,32 @@ def run_ours(args):
     gemm_ms = time_kernel(lambda: ops.gemm(X, W, M, N, K, b_mn=True, out_bf16=h, out2_bf16=g, bias=bias, act=1))
     gemm_tflops = 2.0 * M * N * K / (gemm_ms * 1e-3) / 1e12
     del X, dY, dW, W, h, g
+    # ---- every GEMM of one micro-step (forward + backward), each timed alone with CUDA events on its own buffers:
+    # sum of algorithmic FLOPs / sum of times = the time-weighted roofline of the kernel family that dominates the step
+    recorded = []
+    real_gemm = ops.gemm
+
+    def recording_gemm(A, B, M, N, K, **kw):
+        recorded.append((A, B, M, N, K, kw))
+        return real_gemm(A, B, M, N, K, **kw)
+
+    ops.gemm = recording_gemm
+    try:
+        eng.forward(dev_images[0], dev_noise[0])
+        eng.backward(zero_grads=True)
+    finally:
+        ops.gemm = real_gemm
+    torch.cuda.synchronize()
+    gemm_flops = gemm_ms_total = 0.0
+    timed_shapes = {}
+    for A, B, M_, N_, K_, kw in recorded:
+        key = (M_, N_, K_, kw.get("a_mn", False), kw.get("b_mn", False), kw.get("act", 0), kw.get("out_f32") is not None,
+               kw.get("out2_bf16") is not None, kw.get("residual") is not None, bool(kw.get("accumulate", False)))
+        if key not in timed_shapes:
+            timed_shapes[key] = time_kernel(lambda: real_gemm(A, B, M_, N_, K_, **kw), reps=10)
+        gemm_ms_total += timed_shapes[key]
+        gemm_flops += 2.0 * M_ * N_ * K_
+    gemm_weighted_tflops = gemm_flops / (gemm_ms_total * 1e-3) / 1e12
     fwd_flops, step_flops = flops_per_image(cfg)
     step_tflops_per_gpu = step_flops * args.global_batch / world / (ms_per_step * 1e-3) / 1e12
 
@@ -336,21 +370,39 @@ def run_ours(args):
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
         "scaling": "strong", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
         "config": workload_config(args, micro, accum, world),
+        # the number the target is written on: whole-step algorithmic FLOPs over the step time,
+        # against the measured sustained bf16 peak
         "roofline": {
+            "bound": "tensor", "kernel": "whole optimizer step (forward + backward + all-reduce + AdamW), algorithmic FLOPs "
+                                         f"{step_flops / 1e9:.3f} GFLOP/image",
+            "achieved": step_tflops_per_gpu, "peak": peaks["bf16_sustained"], "unit": "TFLOP/s",
+            "frac": step_tflops_per_gpu / peaks["bf16_sustained"], "traffic": None,
+            "flops_per_image": step_flops, "peak_source": f"{peaks['source']} (sustained: long step)",
+        },
+        "roofline_gemm_weighted": {
+            "bound": "tensor", "kernel": f"all {len(recorded)} jm_gemm launches of one micro-step ({len(timed_shapes)} distinct "
+                                         "shapes / epilogues), each timed alone: sum FLOPs / sum time",
+            "achieved": gemm_weighted_tflops, "peak": peaks["bf16_burst"], "unit": "TFLOP/s",
+            "frac": gemm_weighted_tflops / peaks["bf16_burst"], "traffic": None,
+            "peak_source": f"{peaks['source']} (burst: kernels timed alone)", "kernel_ms": gemm_ms_total,
+        },
+        "roofline_gemm_dw": {
             "bound": "tensor", "kernel": f"gemm2_kernel<MN,MN,f32-accumulate> (CTA pair, 256x256 tile) dW += X^T dY, decoder FFN w1: "
-                                         f"M={dd_} N={4 * dd_} K={Md_} (tokens)",
+                                         f"M={dd_} N={4 * dd_} K={Md_} (tokens): the best instance",
             "achieved": dw_tflops, "peak": peaks["bf16_burst"], "unit": "TFLOP/s",
             "frac": dw_tflops / peaks["bf16_burst"],
-            # dram__bytes_read.sum + dram__bytes_write.sum of one launch, ncu --set full
-            # (profiles/r1e_gemm_dw_ncu_full.md, r1f_* at micro-batch 1024); algorithmic bytes 2*(M+N)*K + 4*M*N = 525.9 MB
-            "traffic": {512: 529.8e6, 1024: 1141.3e6}.get(micro) if args.config == "vit_b16" else None,
+            # dram__bytes_read.sum + dram__bytes_write.sum of one launch of THIS shape under ncu --set full in round 1
+            # (profiles/r1f_gemm_b1024_ncu_full.md; algorithmic bytes 2*(M+N)*K + 4*M*N); null for any other shape
+            "traffic": 1141.3e6 if (micro == 1024 and args.config == "vit_b16") else None,
+            "traffic_source": "profiles/r1f_gemm_b1024_ncu_full.md" if (micro == 1024 and args.config == "vit_b16") else None,
             "peak_source": f"{peaks['source']} (burst: kernel timed alone)", "kernel_ms": dw_ms,
         },
         "roofline_gelu_fwd": {
             "bound": "tensor", "kernel": f"gemm2_kernel<K,MN,GELU> (CTA pair, 256x256 tile) decoder FFN w1 forward M={M} N={N} K={K}",
             "achieved": gemm_tflops, "peak": peaks["bf16_burst"], "unit": "TFLOP/s",
             "frac": gemm_tflops / peaks["bf16_burst"],
-            "traffic": {512: 905.7e6, 1024: 1865.9e6}.get(micro) if args.config == "vit_b16" else None,
+            "traffic": 1865.9e6 if (micro == 1024 and args.config == "vit_b16") else None,
+            "traffic_source": "profiles/r1g_gemm_gelu_fwd_ncu_full.md" if (micro == 1024 and args.config == "vit_b16") else None,
             "kernel_ms": gemm_ms,
             "note": "epilogue-bound: writes 1.6 bytes per FLOP-byte of input (gelu'(h) + gelu(h), bf16, TMA stores); "
                     "see DESIGN.md section 4",
