@@ -82,6 +82,13 @@ int jm_patch_loss(const float* pred, long ldp, const uint8_t* images, const floa
                   int image_size, int patch_size, int num_cls, int norm_pix, float grad_scale, float* loss,
                   jm_bf16* dpred, long lddp, void* workspace, size_t workspace_bytes, void* stream);
 
+/* In place x[r, :] *= (r % period < skip ? scale_cls : scale)[r / period] on a bf16 [rows, cols] matrix: the backward
+ * of a DropPath-scaled residual branch (src/modeling.py:157,181-183) -- the gradient entering the branch is the block
+ * output gradient times the image's keep-mask / (1 - p); drop_path3 of the Jumbo CLS rows has its own mask
+ * (scale_cls, may be NULL). */
+int jm_scale_rows_bf16(jm_bf16* x, long ld, long rows, int cols, const float* scale, const float* scale_cls, int period,
+                       int skip, void* stream);
+
 /* patch_mse_loss(patch_output, patch_target, valid=None) with explicit targets, exactly src/utils_mae.py:51-64:
  * mean over images of [ mean_L( valid > 0 ? mean_c (target - output)^2 : 0 ) / (sum(valid) / L) ].
  * patch_output / patch_target are [batch*L, P] f32 with row strides ldo / ldt; valid is [batch, L] f32 or NULL
@@ -149,6 +156,7 @@ int jm_layernorm_bwd(const jm_bf16* dy, long lddy, const float* x, long ldx, con
  *   act == 3: as 1, but out_bf16 <- gelu'(v): the derivative is saved instead of the pre-activation ...
  *   act == 4: ... and the backward epilogue is v *= aux[row, col] (no tanh in the backward pass)
  *   v += pe[pe_idx[(row % row_period) - row_skip], col]   (positional embedding, modeling.py:123)
+ *   v *= row_scale[row / row_scale_period]                (DropPath, f32 output only)
  *   v += residual[row, col]
  *   rows with (row % row_period) < row_skip: row_mask_mode 1 -> zeros are stored,
  *   2 -> nothing is stored.
@@ -174,6 +182,9 @@ typedef struct jm_gemm_args {
   int block_n;     /* 0 = choose automatically (64, 128 or 256) */
   float* colsum;   /* optional [N]: += column sums of the stored output (fused bias gradient) */
   int cta_pair;    /* 0 = automatic, 1 = force the 2-SM (cta_group::2) 256x256 kernel, -1 = never use it */
+  /* optional per-image scale of the branch: out_f32 = row_scale[row / row_scale_period] * (acc + bias) + residual
+   * (DropPath keep-mask / (1 - p) of a residual branch, src/modeling.py:157,181-183,192,199,201); f32 output only */
+  const float* row_scale; int row_scale_period;
 } jm_gemm_args;
 int jm_gemm(const jm_gemm_args* args, void* stream);
 

@@ -307,6 +307,31 @@ __global__ void patch_loss_finalize_kernel(const float* __restrict__ partial, co
   if (threadIdx.x == 0) loss[0] = tot / (num_masked * static_cast<float>(batch));
 }
 
+// x[r, :] *= (r % period < skip ? scale_cls : scale)[r / period]: the transpose of a DropPath-scaled residual branch
+// (the gradient that enters the branch is the block-output gradient times the image's keep-mask / (1 - p))
+__global__ void scale_rows_bf16_kernel(__nv_bfloat16* __restrict__ x, long ld, long rows, int cols,
+                                       const float* __restrict__ scale, const float* __restrict__ scale_cls, int period,
+                                       int skip) {
+  const int chunks = cols >> 3;
+  const long total = rows * chunks;
+  for (long i = static_cast<long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+       i += static_cast<long>(gridDim.x) * blockDim.x) {
+    const long r = i / chunks;
+    const int c = static_cast<int>(i - r * chunks);
+    const long img = r / period;
+    const float s = (scale_cls != nullptr && r - img * period < skip) ? scale_cls[img] : scale[img];
+    uint4* p = reinterpret_cast<uint4*>(x + r * ld + c * 8);
+    uint4 v = *p;
+    uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const float2 f = unpack_bf16(w[k]);
+      w[k] = pack_bf16(f.x * s, f.y * s);
+    }
+    *p = make_uint4(w[0], w[1], w[2], w[3]);
+  }
+}
+
 // patch_mse_loss with explicit targets (src/utils_mae.py:51-64): one warp per (image, patch) row -> mean_c (t - o)^2
 __global__ void patch_mse_rows_kernel(const float* __restrict__ out, long ldo, const float* __restrict__ tgt, long ldt,
                                       long rows, int P, float* __restrict__ rowmse) {
@@ -991,6 +1016,19 @@ extern "C" int jm_patch_loss(const float* pred, long ldp, const uint8_t* images,
                     reinterpret_cast<__nv_bfloat16*>(dpred), lddp, batch, N, P, STREAM);
   JM_AFTER_LAUNCH();
   patch_loss_finalize_kernel<<<1, 1024, 0, STREAM>>>(partial, mask_row, N, batch, loss);
+  JM_AFTER_LAUNCH();
+  return 0;
+}
+
+extern "C" int jm_scale_rows_bf16(jm_bf16* x, long ld, long rows, int cols, const float* scale, const float* scale_cls,
+                                  int period, int skip, void* stream) {
+  JM_CHECK(x && scale && rows > 0 && cols > 0 && period > 0, "jm_scale_rows_bf16: bad arguments");
+  JM_CHECK(cols % 8 == 0 && ld % 8 == 0 && (reinterpret_cast<uintptr_t>(x) & 15) == 0,
+           "jm_scale_rows_bf16: cols and ld must be multiples of 8 and x 16-byte aligned");
+  const long total = rows * (cols / 8);
+  const int blocks = static_cast<int>(total / 256 + 1 < 148L * 16 ? total / 256 + 1 : 148L * 16);
+  scale_rows_bf16_kernel<<<blocks, 256, 0, STREAM>>>(reinterpret_cast<__nv_bfloat16*>(x), ld, rows, cols, scale,
+                                                     scale_cls, period, skip);
   JM_AFTER_LAUNCH();
   return 0;
 }

@@ -70,6 +70,8 @@ struct EpiParams {
   int accumulate;
   float* colsum;  // optional [N]: += column sums of the stored values (bias gradient of the producer Dense)
   int tma_store;  // row-register epilogues: write the bf16 outputs with TMA stores (maps o / o2)
+  const float* row_scale;  // optional [M / row_scale_period]: (acc + bias) of a row is multiplied by its image's entry
+  int row_scale_period;    // before the residual is added (DropPath keep-mask / (1 - p), src/modeling.py:157,181-183)
 };
 
 template <int BN>
@@ -959,6 +961,13 @@ __device__ __forceinline__ void epilogue_f32_tma(const EpiParams& ep, const Gemm
       const int col = colp + 32 * i + lane;
       bs[i] = (has_bias && col < sh.N && 32 * i + lane < PART_N) ? __ldg(ep.bias + col) : 0.f;
     }
+    // optional per-image scale of the branch output (this thread's row), applied before the residual is added
+    const bool has_rs = ep.row_scale != nullptr;
+    float rs = 1.f;
+    if (has_rs) {
+      const int row = row_base + lane;
+      rs = row < sh.M ? __ldg(ep.row_scale + row / ep.row_scale_period) : 0.f;
+    }
     mbar_wait(&tfull[acc], acc_phase);
     tc_fence_after();
     const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * BN + part * PART_N;
@@ -990,14 +999,16 @@ __device__ __forceinline__ void epilogue_f32_tma(const EpiParams& ep, const Gemm
                          : "=f"(x.x), "=f"(x.y), "=f"(x.z), "=f"(x.w)
                          : "r"(a)
                          : "memory");
+          float4 v = make_float4(__uint_as_float(r[4 * j]), __uint_as_float(r[4 * j + 1]), __uint_as_float(r[4 * j + 2]),
+                                 __uint_as_float(r[4 * j + 3]));
           if (has_bias) {  // warp-uniform
             const float bsrc = bs[(16 * c) / 32];
             const int l0 = (16 * c) % 32 + 4 * j;
-            x.x += __shfl_sync(kFull, bsrc, l0), x.y += __shfl_sync(kFull, bsrc, l0 + 1);
-            x.z += __shfl_sync(kFull, bsrc, l0 + 2), x.w += __shfl_sync(kFull, bsrc, l0 + 3);
+            v.x += __shfl_sync(kFull, bsrc, l0), v.y += __shfl_sync(kFull, bsrc, l0 + 1);
+            v.z += __shfl_sync(kFull, bsrc, l0 + 2), v.w += __shfl_sync(kFull, bsrc, l0 + 3);
           }
-          x.x += __uint_as_float(r[4 * j]), x.y += __uint_as_float(r[4 * j + 1]);
-          x.z += __uint_as_float(r[4 * j + 2]), x.w += __uint_as_float(r[4 * j + 3]);
+          if (has_rs) v.x *= rs, v.y *= rs, v.z *= rs, v.w *= rs;  // warp-uniform branch
+          x.x += v.x, x.y += v.y, x.z += v.z, x.w += v.w;
           asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(a), "f"(x.x), "f"(x.y), "f"(x.z), "f"(x.w)
                        : "memory");
         }
@@ -1650,6 +1661,8 @@ extern "C" int jm_gemm(const jm_gemm_args* a, void* stream_) {
   ep.row_period = a->row_period, ep.row_skip = a->row_skip, ep.row_mask_mode = a->row_mask_mode;
   ep.accumulate = (a->accumulate || splits > 1) ? 1 : 0;
   ep.colsum = a->colsum;
+  ep.row_scale = a->row_scale, ep.row_scale_period = a->row_scale_period;
+  JM_CHECK(!a->row_scale || a->row_scale_period > 0, "jm_gemm: row_scale needs row_scale_period > 0");
   JM_CHECK(!a->colsum || (a->act != 1 && a->act != 3), "jm_gemm: colsum is not defined for the GELU-forward epilogue");
 
   const long total = static_cast<long>(num_m_eff) * num_n * splits;
@@ -1689,6 +1702,8 @@ extern "C" int jm_gemm(const jm_gemm_args* a, void* stream_) {
       return 1;
     ep.tma_store = 1;
   }
+  JM_CHECK(!ep.row_scale || (epi == EPI_F32 && ep.tma_store),
+           "jm_gemm: row_scale is built for the f32 output epilogue (out_f32 only, no pe / row mask / col_scale)");
   if (pair) return dispatch_pair(amn, bmn, epi, tm, sh, ep, grid, stream);
   if (bn == 256) return dispatch_major<256>(amn, bmn, epi, tm, sh, ep, grid, stream);
   if (bn == 128) return dispatch_major<128>(amn, bmn, epi, tm, sh, ep, grid, stream);

@@ -127,6 +127,22 @@ class MAEEngine:
         self.dcn16 = e(B, J * d)
         ln_ws = max(ops.layernorm_bwd_workspace(Mx, max(d, dd)), ops.layernorm_bwd_workspace(B, J * d))
         self.ln_ws = torch.empty(ln_ws, dtype=torch.uint8, device=dev)
+        self.drop_masks = None
+
+    # ------------------------------------------------------------------ DropPath (src/modeling.py:157,181-183)
+    def set_droppath(self, masks: Optional[torch.Tensor]) -> None:
+        """Per-image DropPath factors keep / (1 - rate) of every residual branch: f32 [blocks, 3, B] on the device
+        (encoder layers first, then decoder layers; branch 0 attention, 1 patch FFN, 2 Jumbo MLP), or None for the
+        deterministic / rate-0 path.  The buffer is read by the kernels at run time, so a captured CUDA graph keeps
+        working when its CONTENTS change; switching between None and a tensor needs a re-capture."""
+        if masks is not None:
+            nblk = self.cfg.layers + len(self.dec)
+            if tuple(masks.shape) != (nblk, 3, self.B) or masks.dtype != F32 or not masks.is_cuda:
+                raise _lib.JmError(f"drop masks must be f32 [{nblk}, 3, {self.B}] on the device")
+        self.drop_masks = masks
+
+    def _dp(self, block_index: int):
+        return None if self.drop_masks is None else self.drop_masks[block_index]
 
     # ------------------------------------------------------------------ helpers
     def _W(self, name):
@@ -186,7 +202,8 @@ class MAEEngine:
         self._fwd_linear(self.patches, Me, "model/embed/wte", d, P, lda=self.Pp, out_f32=x0, pe=self.wpe,
                          pe_idx=self.ids_shuffle, row_period=Te, row_skip=J, row_mask_mode=2)
         for i in range(cfg.layers):
-            self._block_fwd(f"model/layer_{i}", self.enc[i], self.xa[i], self.xa[i + 1], Me, d, cfg.heads, Te, True)
+            self._block_fwd(f"model/layer_{i}", self.enc[i], self.xa[i], self.xa[i + 1], Me, d, cfg.heads, Te, True,
+                            self._dp(i))
         ops.layernorm_fwd(self.xa[cfg.layers], ps.f("model/norm/scale"), ps.f("model/norm/bias"), LN_EPS,
                           self.enc_n, None, self.meanF, self.rstdF)
 
@@ -203,7 +220,7 @@ class MAEEngine:
         cfg, ps = self.cfg, self.ps
         for i in range(cfg.dec_layers):
             self._block_fwd(f"decoder_model/dec_layer_{i}", self.dec[i], self.za[i], self.za[i + 1], self.Md, cfg.dec_dim,
-                            cfg.dec_heads, self.Td, False)
+                            cfg.dec_heads, self.Td, False, self._dp(cfg.layers + i))
         ops.layernorm_fwd(self.za[cfg.dec_layers], ps.f("decoder_model/dec_norm/scale"),
                           ps.f("decoder_model/dec_norm/bias"), LN_EPS, self.dec_n, None, self.meanD, self.rstdD)
 
@@ -216,35 +233,43 @@ class MAEEngine:
                        grad_scale, self.loss, self.dpred if want_grad else None, self.loss_ws)
         return self.loss
 
-    def _block_fwd(self, name, s: _Block, x_in, x_out, M, dim, heads, T, jumbo):
+    def _block_fwd(self, name, s: _Block, x_in, x_out, M, dim, heads, T, jumbo, dp=None):
+        """One JumboLayer / ViTLayer forward.  ``dp``: [3, B] DropPath factors of the block's branches or None."""
         ps, B, J = self.ps, self.B, self.cfg.num_cls_tokens
         hd = dim // heads
-        # x_b = x + attn(LN1(x))            (src/modeling.py:165 / :192)
+        rs = (lambda k: dict(row_scale=dp[k], row_scale_period=T)) if dp is not None else (lambda k: {})
+        # x_b = x + drop_path1(attn(LN1(x)))            (src/modeling.py:165 / :192)
         ops.layernorm_fwd(x_in, ps.f(f"{name}/norm1/scale"), ps.f(f"{name}/norm1/bias"), LN_EPS, s.xn1, None,
                           s.mean1, s.rstd1)
         self._fwd_linear(s.xn1, M, f"{name}/attn/wqkv", 3 * dim, dim, out_bf16=s.qkv, col_scale=hd ** -0.5,
                          col_scale_n=dim)
         ops.attention_fwd(s.qkv, B, T, heads, hd, s.att, s.lse)
-        self._fwd_linear(s.att, M, f"{name}/attn/wo", dim, dim, out_f32=s.xb, residual=x_in)
+        self._fwd_linear(s.att, M, f"{name}/attn/wo", dim, dim, out_f32=s.xb, residual=x_in, **rs(0))
         period, skip = (T, J) if jumbo else (0, 0)
-        # patch tokens: x = x_b + ff(LN2(x_b))       (src/modeling.py:166 / :201)
+        # patch tokens: x = x_b + drop_path2(ff(LN2(x_b)))       (src/modeling.py:166 / :201)
         ops.layernorm_fwd(s.xb, ps.f(f"{name}/norm2/scale"), ps.f(f"{name}/norm2/bias"), LN_EPS, s.xn2, None,
                           s.mean2, s.rstd2)
         self._fwd_linear(s.xn2, M, f"{name}/ff/w1", 4 * dim, dim, out_bf16=s.h, out2_bf16=s.g, act=GELU_FWD,
                          row_period=period, row_skip=skip, row_mask_mode=1 if jumbo else 0)
         # (every row is written, so that the output tiles can leave by TMA; the CLS rows of a Jumbo block get
         #  x_b + bias here -- their h/g rows are zero -- and are overwritten by the Jumbo MLP just below)
-        self._fwd_linear(s.g, M, f"{name}/ff/w2", dim, 4 * dim, out_f32=x_out, residual=s.xb)
+        self._fwd_linear(s.g, M, f"{name}/ff/w2", dim, 4 * dim, out_f32=x_out, residual=s.xb, **rs(1))
         if jumbo:
             Jd = J * dim
-            # c = LN3(cls concat); c = c + jumbo_mlp(c)      (src/modeling.py:194-199)
+            # c = LN3(cls concat); c = c + drop_path3(jumbo_mlp(c))      (src/modeling.py:194-199)
             ops.layernorm_fwd(s.xb, ps.f(f"{name}/norm3/scale"), ps.f(f"{name}/norm3/bias"), LN_EPS, s.cn16, s.cn,
                               s.mean3, s.rstd3, rows=B, dim=Jd, ldx=T * dim, ldy=Jd, ldyf=Jd)
             self._fwd_linear(s.cn16, B, "model/jumbo_mlp/w1", 4 * Jd, Jd, out_bf16=s.hj, out2_bf16=s.gj, act=GELU_FWD)
-            # w2 has few output tiles and a long K: seed the CLS rows with c + bias, then split-K accumulate
-            ops.add_bias_cast(s.cn, B, Jd, bias=ps.f("model/jumbo_mlp/w2/bias"), dst_f32=x_out, ldd=T * dim)
-            ops.gemm(s.gj, self._W("model/jumbo_mlp/w2/kernel"), B, Jd, 4 * Jd, b_mn=True,
-                     ldb=ps.ld("model/jumbo_mlp/w2/kernel"), out_f32=x_out, ldo_f32=T * dim, accumulate=True)
+            if dp is None:
+                # w2 has few output tiles and a long K: seed the CLS rows with c + bias, then split-K accumulate
+                ops.add_bias_cast(s.cn, B, Jd, bias=ps.f("model/jumbo_mlp/w2/bias"), dst_f32=x_out, ldd=T * dim)
+                ops.gemm(s.gj, self._W("model/jumbo_mlp/w2/kernel"), B, Jd, 4 * Jd, b_mn=True,
+                         ldb=ps.ld("model/jumbo_mlp/w2/kernel"), out_f32=x_out, ldo_f32=T * dim, accumulate=True)
+            else:
+                # with DropPath the branch (bias included) is scaled per image before c is added: one pass over K
+                ops.gemm(s.gj, self._W("model/jumbo_mlp/w2/kernel"), B, Jd, 4 * Jd, b_mn=True,
+                         ldb=ps.ld("model/jumbo_mlp/w2/kernel"), bias=ps.f("model/jumbo_mlp/w2/bias"), residual=s.cn,
+                         ldr=Jd, out_f32=x_out, ldo_f32=T * dim, row_scale=dp[2], row_scale_period=1)
 
     # ------------------------------------------------------------------ backward
     def backward(self, zero_grads: bool = True) -> None:
@@ -304,15 +329,17 @@ class MAEEngine:
             dx, dx16 = view(self.dxA, Md, dd), view(self.dxA16, Md, dd)
             # (every LayerNorm backward also emits the column sums of the dx it produces: that dx is the
             #  output gradient of the previous block's ff/w2, i.e. its bias gradient)
+            dp_on = self.drop_masks is not None     # then every block sums its ff/w2 bias from its scaled gradient copy
             ops.layernorm_bwd(dn, self.za[cfg.dec_layers], self.meanD, self.rstdD,
                               ps.f("decoder_model/dec_norm/scale"), None, dx, dx16,
                               ps.grad("decoder_model/dec_norm/scale"), ps.grad("decoder_model/dec_norm/bias"),
-                              self.ln_ws, dcol=ps.grad(f"decoder_model/dec_layer_{cfg.dec_layers - 1}/ff/w2/bias"))
+                              self.ln_ws,
+                              dcol=None if dp_on else ps.grad(f"decoder_model/dec_layer_{cfg.dec_layers - 1}/ff/w2/bias"))
             # ---- decoder blocks
             for i in reversed(range(cfg.dec_layers)):
                 below = ps.grad(f"decoder_model/dec_layer_{i - 1}/ff/w2/bias") if i > 0 else None
                 self._block_bwd(f"decoder_model/dec_layer_{i}", self.dec[i], self.za[i], Md, dd, cfg.dec_heads, Td,
-                                False, below)
+                                False, below, dp=self._dp(cfg.layers + i))
             # ---- decoder input assembly + decoder_proj
             ops.unshuffle_bwd(dx, self.ids_restore, B, N, n, J, dd, self.dy16, ps.grad("image_mask_embedding"))
             dn = view(self.dn16, Me, d)
@@ -320,18 +347,20 @@ class MAEEngine:
             dx, dx16 = view(self.dxA, Me, d), view(self.dxA16, Me, d)
             ops.layernorm_bwd(dn, self.xa[cfg.layers], self.meanF, self.rstdF, ps.f("model/norm/scale"), None, dx,
                               dx16, ps.grad("model/norm/scale"), ps.grad("model/norm/bias"), self.ln_ws,
-                              dcol=ps.grad(f"model/layer_{cfg.layers - 1}/ff/w2/bias"), dcol_period=Te, dcol_skip=J)
+                              dcol=None if dp_on else ps.grad(f"model/layer_{cfg.layers - 1}/ff/w2/bias"),
+                              dcol_period=Te, dcol_skip=J)
             return
         kind, layers = self._segment_plan()[k]
         if kind == "enc":
             for i in layers:
                 self._block_bwd(f"model/layer_{i}", self.enc[i], self.xa[i], Me, d, cfg.heads, Te, True,
-                                ps.grad(f"model/layer_{i - 1}/ff/w2/bias"))
+                                ps.grad(f"model/layer_{i - 1}/ff/w2/bias"), dp=self._dp(i))
         if kind == "jumbo":
             # layer 0's Jumbo branch alone (its patch-FFN and attention branches do not touch the CLS rows'
             # incoming gradient and run in the tail), then the shared Jumbo MLP's weight gradients over all
             # layers at once (K = layers * B)
-            self._block_bwd("model/layer_0", self.enc[0], self.xa[0], Me, d, cfg.heads, Te, True, None, part="jumbo")
+            self._block_bwd("model/layer_0", self.enc[0], self.xa[0], Me, d, cfg.heads, Te, True, None, part="jumbo",
+                            dp=self._dp(0))
             L, Jd = cfg.layers, J * d
             for nm, X, dY, rows, cols in (("w1", self.cn16_all, self.dhj16_all, Jd, 4 * Jd),
                                           ("w2", self.gj_all, self.dc16_all, 4 * Jd, Jd)):
@@ -340,7 +369,7 @@ class MAEEngine:
                          accumulate=True)
         if kind == "tail":
             self._block_bwd("model/layer_0", self.enc[0], self.xa[0], Me, d, cfg.heads, Te, True,
-                            ps.grad("model/embed/wte/bias"), part="rest")
+                            ps.grad("model/embed/wte/bias"), part="rest", dp=self._dp(0), below_is_branch=False)
             # ---- CLS parameter and patch embedding (its bias gradient came from layer 0's LN1 backward)
             dx, dx16 = view(self.dxA, Me, d), view(self.dxA16, Me, d)
             ops.colsum(dx, B, J * d, ps.grad("model/cls_tokens"), ldx=Te * d)
@@ -348,13 +377,19 @@ class MAEEngine:
                      out_f32=ps.grad("model/embed/wte/kernel"), ldo_f32=ps.ld("model/embed/wte/kernel"),
                      accumulate=True)
 
-    def _block_bwd(self, name, s: _Block, x_in, M, dim, heads, T, jumbo, dcol_below, part="all"):
+    def _block_bwd(self, name, s: _Block, x_in, M, dim, heads, T, jumbo, dcol_below, part="all", dp=None,
+                   below_is_branch=True):
         """In: d/d(block output) in dxA / dxA16.  Out: d/d(block input) in dxA / dxA16.
         ``part``: "all", or the block in two steps, "jumbo" (the Jumbo CLS branch alone: it reads and writes only
         the CLS rows, which the patch FFN branch leaves alone) followed by "rest".
         Bias gradients are produced where their dY is produced (LayerNorm backward, GELU-backward GEMM
         epilogue, attention backward); ``dcol_below`` is the ff/w2 (or patch-embed) bias gradient of the
-        block below, whose output gradient this block's LN1 backward emits."""
+        block below, whose output gradient this block's LN1 backward emits.
+        ``dp``: [3, B] DropPath factors of this block's branches (or None).  The gradient that enters a branch is the
+        block-output gradient times its image's factor, so the bf16 gradient copies are scaled in place before the
+        branch's products, and the bias gradients that LayerNorm backward would fuse (column sums of the UNscaled
+        gradient) are taken from the scaled copies instead.  ``below_is_branch``: dcol_below is the bias of a
+        DropPath-scaled branch of the block below (false for the patch embedding)."""
         ps, B, J = self.ps, self.B, self.cfg.num_cls_tokens
         hd = dim // heads
         view = lambda buf, w: buf[:M * w].view(M, w)
@@ -363,6 +398,13 @@ class MAEEngine:
         dh, dn = view(self.dh16, 4 * dim), view(self.dn16, dim)
         period, skip = (T, J) if jumbo else (0, 0)
         mode = 1 if jumbo else 0
+        any_dp = self.drop_masks is not None
+        if dp is not None and part != "rest":
+            # dY of ff/w2 (patch rows, drop_path2) and of the Jumbo w2 (CLS rows, drop_path3)
+            ops.scale_rows_bf16(dx16, M, dim, dp[1], T, scale_cls=dp[2] if jumbo else None, skip=J if jumbo else 0)
+        if dp is not None and part != "jumbo":
+            # ff/w2 bias: column sums of the scaled gradient over the rows the branch produced
+            ops.colsum(dx16, M, dim, ps.grad(f"{name}/ff/w2/bias"), row_period=period, row_skip=skip)
         if part != "jumbo":
             # ---- patch FFN: y = x_b + w2(gelu(w1 LN2(x_b)))
             self._bwd_linear(s.g, dx16, M, f"{name}/ff/w2", dim, 4 * dim, dX16=dh, bias=False, act=GELU_BWD, aux=s.h,
@@ -371,13 +413,16 @@ class MAEEngine:
             self._bwd_linear(s.xn2, dh, M, f"{name}/ff/w1", 4 * dim, dim, dX16=dn, bias=False)
             ops.layernorm_bwd(dn, s.xb, s.mean2, s.rstd2, ps.f(f"{name}/norm2/scale"), dx, dxb, dxb16,
                               ps.grad(f"{name}/norm2/scale"), ps.grad(f"{name}/norm2/bias"), self.ln_ws,
-                              row_period=period, row_skip=skip, dcol=ps.grad(f"{name}/attn/wo/bias"))
+                              row_period=period, row_skip=skip,
+                              dcol=None if dp is not None else ps.grad(f"{name}/attn/wo/bias"))
         if jumbo and part != "rest":
             # ---- Jumbo CLS: c_out = c + w2j(gelu(w1j c)), c = LN3(cls concat); strided [B, J*dim] views
             Jd, ldc = J * dim, T * dim
             # output gradient of w2 = the CLS rows of dx: bias gradient now, a bf16 copy for the batched dW
             ops.colsum(dx16, B, Jd, ps.grad("model/jumbo_mlp/w2/bias"), ldx=ldc)
             ops.add_bias_cast(dx, B, Jd, dst_bf16=s.dc16, lds=ldc)
+            if dp is not None:
+                ops.scale_rows_bf16(s.dc16, B, Jd, dp[2], 1)
             ops.gemm(dx16, self._W("model/jumbo_mlp/w2/kernel"), B, 4 * Jd, Jd, b_mn=False, lda=ldc,
                      ldb=ps.ld("model/jumbo_mlp/w2/kernel"), out_bf16=s.dhj16, act=GELU_BWD, aux=s.hj,
                      colsum=ps.grad("model/jumbo_mlp/w1/bias"))
@@ -388,16 +433,22 @@ class MAEEngine:
             ops.layernorm_bwd(self.dcn16, s.xb, s.mean3, s.rstd3, ps.f(f"{name}/norm3/scale"), None, dxb, dxb16,
                               ps.grad(f"{name}/norm3/scale"), ps.grad(f"{name}/norm3/bias"), self.ln_ws, rows=B,
                               dim=Jd, ldx=ldc, lddx=ldc, lddxb=ldc)
-            # wo bias: LN2 backward covered the patch rows, add the CLS rows LN3 backward just wrote
-            ops.colsum(dxb16, M, dim, ps.grad(f"{name}/attn/wo/bias"), row_period=T, row_skip=J, row_invert=True)
+            if dp is None:
+                # wo bias: LN2 backward covered the patch rows, add the CLS rows LN3 backward just wrote
+                ops.colsum(dxb16, M, dim, ps.grad(f"{name}/attn/wo/bias"), row_period=T, row_skip=J, row_invert=True)
         if part == "jumbo":
             return
         # ---- attention branch: x_b = x + wo(attn(wqkv LN1(x)))
+        if dp is not None:
+            ops.scale_rows_bf16(dxb16, M, dim, dp[0], T)
+            ops.colsum(dxb16, M, dim, ps.grad(f"{name}/attn/wo/bias"))
         datt, dqkv = view(self.datt16, dim), view(self.dqkv16, 3 * dim)
         self._bwd_linear(s.att, dxb16, M, f"{name}/attn/wo", dim, dim, dX16=datt, bias=False)
         ops.attention_bwd(s.qkv, s.att, datt, s.lse, B, T, heads, hd, hd ** -0.5, dqkv, self.delta_ws,
                           dbias=ps.grad(f"{name}/attn/wqkv/bias"))
         self._bwd_linear(s.xn1, dqkv, M, f"{name}/attn/wqkv", 3 * dim, dim, dX16=dn, bias=False)
+        if any_dp and below_is_branch:
+            dcol_below = None       # the block below takes its ff/w2 bias from its own scaled gradient copy
         ops.layernorm_bwd(dn, x_in, s.mean1, s.rstd1, ps.f(f"{name}/norm1/scale"), dxb, dx, dx16,
                           ps.grad(f"{name}/norm1/scale"), ps.grad(f"{name}/norm1/bias"), self.ln_ws,
                           dcol=dcol_below, dcol_period=period, dcol_skip=skip)

@@ -73,6 +73,7 @@ class FinetuneEngine(MAEEngine):
         self.dcn16 = e(B, Jd)
         ln_ws = max(ops.layernorm_bwd_workspace(Me, d), ops.layernorm_bwd_workspace(B, Jd))
         self.ln_ws = torch.empty(ln_ws, dtype=torch.uint8, device=dev)
+        self.drop_masks = None
 
     # ------------------------------------------------------------------ forward
     def forward(self, images: torch.Tensor, labels: torch.Tensor, *, label_smoothing: float = 0.0,
@@ -101,7 +102,8 @@ class FinetuneEngine(MAEEngine):
         self._fwd_linear(self.patches, Me, "model/embed/wte", d, P, lda=self.Pp, out_f32=x0, pe=self.wpe,
                          pe_idx=self.ids_all, row_period=Te, row_skip=J, row_mask_mode=2)
         for i in range(cfg.layers):
-            self._block_fwd(f"model/layer_{i}", self.enc[i], self.xa[i], self.xa[i + 1], Me, d, cfg.heads, Te, True)
+            self._block_fwd(f"model/layer_{i}", self.enc[i], self.xa[i], self.xa[i + 1], Me, d, cfg.heads, Te, True,
+                            self._dp(i))
         ops.layernorm_fwd(self.xa[cfg.layers], ps.f("model/norm/scale"), ps.f("model/norm/bias"), LN_EPS,
                           self.enc_n, None, self.meanF, self.rstdF)
         # LinearCLS on x[:, :J].reshape(B, J*d) (src/modeling.py:272-274): the CLS rows are the first J of every
@@ -139,7 +141,8 @@ class FinetuneEngine(MAEEngine):
         dx, dx16 = self.dxA[:Me * d].view(Me, d), self.dxA16[:Me * d].view(Me, d)
         ops.layernorm_bwd(dn, self.xa[cfg.layers], self.meanF, self.rstdF, ps.f("model/norm/scale"), None, dx, dx16,
                           ps.grad("model/norm/scale"), ps.grad("model/norm/bias"), self.ln_ws,
-                          dcol=ps.grad(f"model/layer_{cfg.layers - 1}/ff/w2/bias"), dcol_period=Te, dcol_skip=J)
+                          dcol=None if self.drop_masks is not None else ps.grad(f"model/layer_{cfg.layers - 1}/ff/w2/bias"),
+                          dcol_period=Te, dcol_skip=J)
 
     # ------------------------------------------------------------------ CUDA graphs
     def capture_graphs(self, label_smoothing: float = 0.0, mixup: bool = False) -> None:
@@ -184,5 +187,3 @@ class FinetuneEngine(MAEEngine):
         self.graphs[bool(zero_grads)].replay()
         return self.loss
 
-    def capture_segment_graphs(self) -> None:
-        raise NotImplementedError("the data-parallel overlap graphs of the classification step are not built yet")

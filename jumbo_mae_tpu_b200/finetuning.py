@@ -14,7 +14,12 @@ come from a Philox stream seeded with ``--mixup-seed`` that advances every step.
 streams never advance: ``updates`` of ``split_rngs()`` is overwritten by the ``batch_stats`` updates,
 src/finetuning.py:136-137,154 -- every step reuses the same key.  That looks unintended and is not reproduced.)
 
-Not built: DropPath / Dropout > 0, BatchNorm head and stop-gradient of linear probing (``--mode linear``), ``bce``,
+DropPath (``--droppath``, 0.1 in the recipe, config/ft.sh): one Bernoulli draw per image and residual branch
+(src/modeling.py:181-183) from this rank's "dropout" Philox stream, or supplied by the caller
+(``training_step(..., drop_keep=...)``: bool [layers, 3, B]); the factors keep / (1 - rate) scale the branch outputs in the
+GEMM epilogues and the branch gradients in the backward pass.
+
+Not built: Dropout > 0, BatchNorm head and stop-gradient of linear probing (``--mode linear``), ``bce``,
 LARS / LAMB / SGD.
 """
 from __future__ import annotations
@@ -84,11 +89,13 @@ class TrainState:
     cutmix: float = 1.0
     lr_decay: float = 1.0
     clip_grad: float = 0.0
+    droppath: float = 0.0
     micro_step: int = 0
     micro_in_mini: int = 1
     batch_stats: Any = None
     engines: Dict[int, FinetuneEngine] = field(default_factory=dict)
     reducer: Optional[GradReducer] = None
+    _drop_gen: Optional[np.random.Generator] = None
     _mix_gen: Optional[np.random.Generator] = None
 
     @property
@@ -103,7 +110,16 @@ class TrainState:
     def replicate(self) -> "TrainState":
         # one stream per rank, as shard_prng_key gives every device its own key (src/finetuning.py:71-76)
         self._mix_gen = np.random.Generator(np.random.Philox(key=self.mixup_rng + 7919 * process_index()))
+        self._drop_gen = np.random.Generator(np.random.Philox(key=self.dropout_rng + 7919 * process_index() + 15485863))
         return self
+
+    def draw_drop_keep(self, batch: int) -> Optional[np.ndarray]:
+        """This step's DropPath keep bits, bool [layers, 3, B] (drop_path1 / 2 / 3 of every JumboLayer)."""
+        if self.droppath <= 0:
+            return None
+        if self._drop_gen is None:
+            self.replicate()
+        return self._drop_gen.random((self.cfg.layers, 3, batch)) >= self.droppath
 
     def engine(self, batch: int) -> FinetuneEngine:
         if batch not in self.engines:
@@ -133,9 +149,10 @@ def create_train_state(args: argparse.Namespace) -> TrainState:
         raise NotImplementedError("only --criterion ce is built")
     if getattr(args, "mode", "finetune") == "linear":
         raise NotImplementedError("--mode linear (BatchNorm head, stop-gradient) is not built")
-    for nm in ("dropout", "droppath"):
-        if getattr(args, nm, 0.0) != 0.0:
-            raise NotImplementedError(f"--{nm} > 0 is not built (the fine-tune recipe's DropPath 0.1 is the next item)")
+    if getattr(args, "dropout", 0.0) != 0.0:
+        raise NotImplementedError("--dropout > 0 is not built (0.0 in the fine-tune recipe)")
+    if not 0.0 <= float(getattr(args, "droppath", 0.0)) < 1.0:
+        raise ValueError("--droppath must be in [0, 1)")
     if getattr(args, "layerscale", False) or getattr(args, "posemb", "sincos2d") != "sincos2d":
         raise NotImplementedError("LayerScale / learnable position embeddings are not built")
     cfg = MAEConfig(layers=args.layers, dim=args.dim, heads=args.heads, patch_size=args.patch_size,
@@ -168,7 +185,8 @@ def _new_state(args: argparse.Namespace, store: ParamStore, cfg: MAEConfig) -> T
                       training_steps=int(args.training_steps),
                       label_smoothing=float(getattr(args, "label_smoothing", 0.1)), mixup=float(getattr(args, "mixup", 0.8)),
                       cutmix=float(getattr(args, "cutmix", 1.0)), lr_decay=float(getattr(args, "lr_decay", 1.0)),
-                      clip_grad=float(getattr(args, "clip_grad", 0.0)), micro_in_mini=int(getattr(args, "grad_accum", 1)))
+                      clip_grad=float(getattr(args, "clip_grad", 0.0)), micro_in_mini=int(getattr(args, "grad_accum", 1)),
+                      droppath=float(getattr(args, "droppath", 0.0)))
 
 
 def _to_device(t, dev, dtype):
@@ -178,8 +196,22 @@ def _to_device(t, dev, dtype):
     return t.to(dev, non_blocking=True).contiguous()
 
 
-def training_step(state: TrainState, batch, mix: Optional[MixDraw] = None):
-    """src/finetuning.py:108-154: forward with label smoothing + Mixup / CutMix, backward, (accumulated) AdamW."""
+def _set_droppath(state: TrainState, eng: FinetuneEngine, keep) -> None:
+    """keep bits [layers, 3, B] -> the engine's per-image factors keep / (1 - rate) (a persistent device buffer)."""
+    if keep is None:
+        eng.set_droppath(None)
+        return
+    fac = torch.from_numpy(np.ascontiguousarray(keep, dtype=np.float32) / np.float32(1.0 - state.droppath))
+    buf = getattr(eng, "_drop_buf", None)
+    if buf is None:
+        buf = eng._drop_buf = torch.empty(fac.shape, dtype=torch.float32, device=state.store.device)
+    buf.copy_(fac, non_blocking=True)
+    eng.set_droppath(buf)
+
+
+def training_step(state: TrainState, batch, mix: Optional[MixDraw] = None, drop_keep=None):
+    """src/finetuning.py:108-154: forward with label smoothing + Mixup / CutMix + DropPath, backward, (accumulated)
+    AdamW.  ``drop_keep`` (bool [layers, 3, B]) overrides this step's DropPath draws (parity tests)."""
     dev = state.store.device
     images, labels = _to_device(batch[0], dev, torch.uint8), _to_device(batch[1], dev, torch.int32)
     B = images.shape[0]
@@ -197,6 +229,7 @@ def training_step(state: TrainState, batch, mix: Optional[MixDraw] = None):
     world = process_count()
     if world > 1 and getattr(state, "reducer", None) is None:
         state.reducer = GradReducer(state.store)
+    _set_droppath(state, eng, drop_keep if drop_keep is not None else state.draw_drop_keep(B))
     eng.forward(images, labels, label_smoothing=state.label_smoothing, **kw)
     eng.backward(zero_grads=(state.micro_step == 0))
     metrics = eng.metrics.clone()
@@ -224,6 +257,7 @@ def validation_step(state: TrainState, batch) -> Dict[str, Any]:
     images, labels = _to_device(batch[0], dev, torch.uint8), _to_device(batch[1], dev, torch.int32)
     valid = (labels != -1)
     eng = state.engine(images.shape[0])
+    eng.set_droppath(None)                                         # det=True (src/finetuning.py:159)
     eng.forward(images, torch.where(valid, labels, torch.zeros_like(labels)), want_grad=False)
     v = valid.to(torch.float32)
     sums = torch.stack([(eng.loss_rows * v).sum(), (eng.acc1 * v).sum(), (eng.acc5 * v).sum(), v.sum()])

@@ -119,6 +119,14 @@ def patch_loss(pred: torch.Tensor, images: torch.Tensor, mask_row: torch.Tensor,
                                     workspace.numel() * workspace.element_size(), stream_ptr()))
 
 
+def scale_rows_bf16(x: torch.Tensor, rows: int, cols: int, scale: torch.Tensor, period: int,
+                    scale_cls: Optional[torch.Tensor] = None, skip: int = 0, ld: Optional[int] = None) -> None:
+    """In place x[r] *= (r % period < skip ? scale_cls : scale)[r // period] (DropPath backward)."""
+    _chk(x, BF16, "x"), _chk(scale, F32, "scale"), _chk(scale_cls, F32, "scale_cls")
+    check(_lib.load().jm_scale_rows_bf16(ptr(x), _ld(x) if ld is None else ld, rows, cols, ptr(scale), ptr(scale_cls),
+                                         period, skip, stream_ptr()))
+
+
 def patch_mse_loss(patch_output: torch.Tensor, patch_target: torch.Tensor, valid: Optional[torch.Tensor],
                    loss: torch.Tensor, workspace: torch.Tensor) -> None:
     """src/utils_mae.py:51-64 on explicit f32 targets [B, L, P]; valid [B, L] f32 or None."""
@@ -181,7 +189,8 @@ def gemm(A: torch.Tensor, B: torch.Tensor, M: int, N: int, K: int, *, a_mn: bool
          act: int = 0, col_scale: float = 1.0, col_scale_n: int = 0,
          row_period: int = 0, row_skip: int = 0, row_mask_mode: int = 0,
          accumulate: bool = False, splits: int = 0, block_n: int = 0,
-         colsum: Optional[torch.Tensor] = None, cta_pair: int = 0) -> None:
+         colsum: Optional[torch.Tensor] = None, cta_pair: int = 0,
+         row_scale: Optional[torch.Tensor] = None, row_scale_period: int = 0) -> None:
     """D = epilogue(A @ B) through jm_gemm; see include/jumbo_mae_b200.h for the epilogue order."""
     _chk(A, BF16, "A"), _chk(B, BF16, "B"), _chk(out_f32, F32, "out_f32"), _chk(out_bf16, BF16, "out_bf16")
     _chk(out2_bf16, BF16, "out2_bf16"), _chk(bias, F32, "bias"), _chk(residual, F32, "residual")
@@ -204,6 +213,8 @@ def gemm(A: torch.Tensor, B: torch.Tensor, M: int, N: int, K: int, *, a_mn: bool
     _chk(colsum, F32, "colsum")
     a.colsum = ptr(colsum)
     a.cta_pair = int(cta_pair)
+    _chk(row_scale, F32, "row_scale")
+    a.row_scale, a.row_scale_period = ptr(row_scale), int(row_scale_period)
     check(_lib.load().jm_gemm(ctypes.byref(a), stream_ptr()))
 
 

@@ -248,25 +248,37 @@ def feed_forward(x, p: Tree):
     return dense(gelu_tanh(dense(x, p["w1"])), p["w2"])
 
 
-def vit_layer(x, p: Tree, heads: int):
-    """ViTLayer (decoder block), src/modeling.py:150-167; scale1=scale2=1.0,
-    DropPath identity at the recipe's rate 0.0."""
-    x = x + attention(layer_norm(x, p["norm1"]["scale"], p["norm1"]["bias"]), p["attn"], heads)
-    x = x + feed_forward(layer_norm(x, p["norm2"]["scale"], p["norm2"]["bias"]), p["ff"])
+def drop_path(y, scale):
+    """nn.Dropout(rate, broadcast_dims=(1, 2)) / (1,) on a residual branch (src/modeling.py:157,181-183): one draw per
+    image, kept branches are divided by (1 - rate).  ``scale`` is that per-image factor, keep / (1 - rate), f32 [B]
+    (the Bernoulli draws come from the Flax "dropout" stream and are data at this boundary); None = deterministic."""
+    if scale is None:
+        return y
+    return y * torch.as_tensor(scale, dtype=y.dtype).reshape((-1,) + (1,) * (y.dim() - 1))
+
+
+def vit_layer(x, p: Tree, heads: int, drop=None):
+    """ViTLayer (decoder block), src/modeling.py:150-167; scale1=scale2=1.0.  ``drop`` = (scale1, scale2) per-image
+    DropPath factors of the two branches (the SAME nn.Dropout module is applied twice, with two draws), or None."""
+    d1, d2 = drop if drop is not None else (None, None)
+    x = x + drop_path(attention(layer_norm(x, p["norm1"]["scale"], p["norm1"]["bias"]), p["attn"], heads), d1)
+    x = x + drop_path(feed_forward(layer_norm(x, p["norm2"]["scale"], p["norm2"]["bias"]), p["ff"]), d2)
     return x
 
 
-def jumbo_layer(x, p: Tree, jumbo_mlp: Tree, heads: int, J: int):
+def jumbo_layer(x, p: Tree, jumbo_mlp: Tree, heads: int, J: int, drop=None):
     """JumboLayer, src/modeling.py:191-206.  Note (:197-199) that the CLS
-    residual is taken from the post-norm3 value."""
-    x = x + attention(layer_norm(x, p["norm1"]["scale"], p["norm1"]["bias"]), p["attn"], heads)
+    residual is taken from the post-norm3 value.  ``drop`` = per-image DropPath factors (drop_path1, drop_path2,
+    drop_path3), each f32 [B], or None."""
+    d1, d2, d3 = drop if drop is not None else (None, None, None)
+    x = x + drop_path(attention(layer_norm(x, p["norm1"]["scale"], p["norm1"]["bias"]), p["attn"], heads), d1)
     cls_tokens, patch_tokens = x[:, :J, :], x[:, J:, :]
     bs = cls_tokens.shape[0]
     c = cls_tokens.reshape(bs, -1)
     c = layer_norm(c, p["norm3"]["scale"], p["norm3"]["bias"])
-    c = c + feed_forward(c, jumbo_mlp)
-    patch_tokens = patch_tokens + feed_forward(
-        layer_norm(patch_tokens, p["norm2"]["scale"], p["norm2"]["bias"]), p["ff"])
+    c = c + drop_path(feed_forward(c, jumbo_mlp), d3)
+    patch_tokens = patch_tokens + drop_path(feed_forward(
+        layer_norm(patch_tokens, p["norm2"]["scale"], p["norm2"]["bias"]), p["ff"]), d2)
     return torch.cat([c.reshape(bs, J, -1), patch_tokens], dim=1)
 
 
@@ -298,15 +310,15 @@ def vit_forward(images_nhwc, p: Tree, cfg: MAEConfig, noise, collect=None):
     return x, mask, ids_restore
 
 
-def vit_classify(images_nhwc, p: Tree, cfg: MAEConfig, collect=None):
+def vit_classify(images_nhwc, p: Tree, cfg: MAEConfig, collect=None, drop=None):
     """ViT.__call__ with a head (labels > 0), src/modeling.py:245-274: no masking, every patch, final LayerNorm,
     LinearCLS (no BatchNorm: batch_norm is a linear-probing option) on the concatenated CLS tokens -> logits."""
     J = cfg.num_cls_tokens
     x = patch_embed(images_nhwc, p["embed"], cfg)
     bs = x.shape[0]
     x = torch.cat((p["cls_tokens"].expand(bs, J, cfg.dim), x), dim=1)
-    for i in range(cfg.layers):
-        x = jumbo_layer(x, p[f"layer_{i}"], p["jumbo_mlp"], cfg.heads, J)
+    for i in range(cfg.layers):                                       # drop: [layers, 3, B] DropPath factors or None
+        x = jumbo_layer(x, p[f"layer_{i}"], p["jumbo_mlp"], cfg.heads, J, None if drop is None else drop[i])
     x = layer_norm(x, p["norm"]["scale"], p["norm"]["bias"])
     if collect is not None:
         collect["enc_out"] = x
@@ -314,11 +326,11 @@ def vit_classify(images_nhwc, p: Tree, cfg: MAEConfig, collect=None):
     return dense(x, p["head"]["Dense_0"])
 
 
-def finetune_loss_and_grads(params: Tree, images_nhwc, labels_soft, cfg: MAEConfig):
+def finetune_loss_and_grads(params: Tree, images_nhwc, labels_soft, cfg: MAEConfig, drop=None):
     """loss_fn of src/finetuning.py:109-124 on already mixed images / prepared labels: mean softmax cross-entropy of
     FinetuneModule (:98) and its gradient (jax.value_and_grad -> torch.autograd).  Returns (loss, logits, grads)."""
     leaves = tree_map(lambda t: t.detach().clone().requires_grad_(True), params)
-    logits = vit_classify(torch.as_tensor(images_nhwc), leaves["model"], cfg)
+    logits = vit_classify(torch.as_tensor(images_nhwc), leaves["model"], cfg, drop=drop)
     lab = torch.as_tensor(labels_soft, dtype=logits.dtype)
     loss = (-(lab * torch.log_softmax(logits, dim=-1)).sum(-1)).mean()
     loss.backward()

@@ -261,3 +261,71 @@ def test_classification_step_against_committed_golden():
         if path[-2:] == ("wk", "bias") or z[key][1] == 0.0:
             continue
         assert abs(got[path].norm().item() - z[key][1]) <= 3e-2 * z[key][1], key
+
+
+@pytest.mark.parametrize("name", ["tiny", "mid"])
+def test_droppath_matches_oracle(name):
+    """DropPath (src/modeling.py:181-183,192,199,201; 0.1 in config/ft.sh) with the keep bits as data: some images lose
+    a branch entirely, the others see it scaled by 1 / (1 - rate).  Logits, loss and every gradient leaf, same
+    tolerances as the deterministic step."""
+    from jumbo_mae_tpu_b200.params import tree_leaves
+    ocfg, cfg, params, images, store, eng = _setup(name)
+    B, C, rate = images.shape[0], ocfg.labels, 0.25
+    rng = np.random.default_rng(11)
+    keep = rng.random((ocfg.layers, 3, B)) >= rate
+    keep[0, 0, 0] = keep[0, 1, 1] = keep[-1, 2, 2 % B] = False           # every branch kind is dropped somewhere
+    fac = keep.astype(np.float32) / np.float32(1.0 - rate)
+    idx = rng.integers(0, C, B).astype(np.int32)
+    lab = O.smooth_labels(np.eye(C, dtype=np.float32)[idx], 0.1)
+    want_loss, want_logits, want = O.finetune_loss_and_grads(params, O.preprocess(images).numpy(), lab, ocfg,
+                                                            drop=torch.from_numpy(fac))
+    eng.set_droppath(torch.from_numpy(fac).cuda())
+    loss = eng.forward(images.cuda(), torch.from_numpy(idx).cuda(), label_smoothing=0.1)
+    eng.backward()
+    torch.cuda.synchronize()
+    assert _rel(eng.logits.cpu(), want_logits) <= 2e-2
+    assert abs(loss.item() - want_loss.item()) <= 5e-3 * abs(want_loss.item())
+    got = dict(tree_leaves(store.tree(store.g)))
+    bad = []
+    ref = dict(O.tree_leaves(want))
+    for path, w in ref.items():
+        g = got[path].detach().cpu().reshape(w.shape)
+        if path[-2:] == ("wk", "bias") or w.norm().item() == 0.0:
+            continue                                                     # covered by the deterministic test
+        r = _rel(g, w)
+        cos = (g.flatten() @ w.flatten() / (g.norm() * w.norm() + 1e-20)).item()
+        if not (r <= 3e-2 and cos >= 0.999):
+            bad.append(("/".join(path), r, cos))
+    assert not bad, bad
+    # and the deterministic path is untouched once the masks are removed
+    eng.set_droppath(None)
+    eng.forward(images.cuda(), torch.from_numpy(idx).cuda(), label_smoothing=0.1, want_grad=False)
+    det = O.vit_classify(O.preprocess(images), params["model"], ocfg)
+    assert _rel(eng.logits.cpu(), det) <= 2e-2
+
+
+def test_finetune_training_step_with_droppath_draws():
+    """training_step with --droppath: the keep bits come from the rank's dropout stream, advance every step, and a
+    caller-supplied draw reproduces the oracle's loss."""
+    import argparse
+    from jumbo_mae_tpu_b200.finetuning import create_train_state, training_step
+    args = argparse.Namespace(layers=2, dim=64, heads=2, patch_size=8, image_size=32, labels=16, weight_decay=0.05,
+                              adam_b1=0.9, adam_b2=0.999, adam_eps=1e-8, learning_rate=1e-3, warmup_steps=2,
+                              training_steps=10, label_smoothing=0.1, mixup=0.0, cutmix=0.0, droppath=0.5, init_seed=0,
+                              dropout_seed=3)
+    state = create_train_state(args).replicate()
+    a, b = state.draw_drop_keep(4), state.draw_drop_keep(4)
+    assert a.shape == (2, 3, 4) and a.dtype == bool and not np.array_equal(a, b)
+    images = torch.randint(0, 256, (4, 3, 32, 32), dtype=torch.uint8, generator=torch.Generator().manual_seed(0))
+    labels = torch.tensor([1, 2, 3, 4], dtype=torch.int32)
+    keep = np.ones((2, 3, 4), dtype=bool)
+    keep[1, :, 0] = False
+    ocfg = O.tiny(labels=16)
+    params = O.tree_map(lambda t: t.detach().cpu().clone(), state.params)
+    lab = O.smooth_labels(np.eye(16, dtype=np.float32)[labels.numpy()], 0.1)
+    want, _, _ = O.finetune_loss_and_grads(params, O.preprocess(images).numpy(), lab, ocfg,
+                                           drop=torch.from_numpy(keep.astype(np.float32) / 0.5))
+    state, m = training_step(state, (images, labels), drop_keep=keep)
+    assert abs(m["loss"].item() - want.item()) <= 5e-3 * abs(want.item())
+    state, m = training_step(state, (images, labels))                       # draws from the stream
+    assert np.isfinite(m["loss"].item())

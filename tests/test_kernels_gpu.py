@@ -704,3 +704,30 @@ def test_patchify_mix_matches_oracle(ops, mode):
     assert torch.equal(got[:, J:, P:], torch.zeros(B, N, ld - P))
     assert torch.equal(got[:, J:, :P], want.to(BF16).float())
     assert not torch.equal(got[:, J:, :P], O.extract_patches(torch.from_numpy(norm), p).to(BF16).float())
+
+
+def test_gemm_row_scale_epilogue(ops):
+    """out = row_scale[row // period] * (A W + bias) + residual: the DropPath-scaled residual branch (f32 epilogue),
+    also as a split-free accumulate into a strided output (the Jumbo CLS rows)."""
+    g = torch.Generator(device="cuda").manual_seed(5)
+    M, N, K, T = 12 * 52, 768, 512, 52
+    A = torch.randn(M, K, generator=g, device="cuda").to(BF16)
+    W = torch.randn(K, N, generator=g, device="cuda").to(BF16)
+    bias = torch.randn(N, generator=g, device="cuda")
+    res = torch.randn(M, N, generator=g, device="cuda")
+    scale = torch.tensor([0.0, 1.25] * 6, device="cuda")
+    out = torch.empty(M, N, device="cuda")
+    ops.gemm(A, W, M, N, K, b_mn=True, bias=bias, residual=res, out_f32=out, row_scale=scale, row_scale_period=T)
+    want = scale.repeat_interleave(T)[:, None] * (A.float() @ W.float() + bias) + res
+    assert (out - want).abs().max().item() <= 2e-5 * K ** 0.5 * want.abs().max().item()
+    assert torch.equal(out[:T], res[:T])                                       # a dropped image keeps its residual exactly
+
+
+def test_scale_rows_bf16(ops):
+    x = torch.randn(3 * 7, 64, device="cuda").to(BF16)
+    a, b = torch.tensor([2.0, 0.0, 0.5], device="cuda"), torch.tensor([0.0, 3.0, 1.0], device="cuda")
+    want = x.float().clone().view(3, 7, 64)
+    want[:, :2] *= b[:, None, None]
+    want[:, 2:] *= a[:, None, None]
+    ops.scale_rows_bf16(x, 21, 64, a, 7, scale_cls=b, skip=2)
+    assert torch.equal(x.float(), want.view(21, 64).to(BF16).float())
