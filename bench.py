@@ -354,14 +354,14 @@ def run_ours(args):
     torch.cuda.synchronize()
     gemm_flops = gemm_ms_total = 0.0
     timed_shapes = {}
-    for A, B, M_, N_, K_, kw in recorded:
+    for A, B, M_, N_, K_, kw in ([] if args.no_kernel_timings else recorded):
         key = (M_, N_, K_, kw.get("a_mn", False), kw.get("b_mn", False), kw.get("act", 0), kw.get("out_f32") is not None,
                kw.get("out2_bf16") is not None, kw.get("residual") is not None, bool(kw.get("accumulate", False)))
         if key not in timed_shapes:
             timed_shapes[key] = time_kernel(lambda: real_gemm(A, B, M_, N_, K_, **kw), reps=10)
         gemm_ms_total += timed_shapes[key]
         gemm_flops += 2.0 * M_ * N_ * K_
-    gemm_weighted_tflops = gemm_flops / (gemm_ms_total * 1e-3) / 1e12
+    gemm_weighted_tflops = gemm_flops / (gemm_ms_total * 1e-3) / 1e12 if gemm_ms_total > 0 else 0.0
     fwd_flops, step_flops = flops_per_image(cfg)
     step_tflops_per_gpu = step_flops * args.global_batch / world / (ms_per_step * 1e-3) / 1e12
 
@@ -430,6 +430,138 @@ def run_ours(args):
         dist.destroy_process_group()
 
 
+# ---------------------------------------------------------------------------------------------
+def run_finetune(args):
+    """--workload finetune: BASELINE.json configs[4], the ViT-B/16 Jumbo-CLS classification step at the fine-tune
+    recipe (config/ft.sh): global batch 1024, label smoothing 0.1, Mixup, DropPath 0.1, AdamW with lr_decay 0.75.
+    One step = forward + backward of 1024 images + gradient all-reduce + AdamW; same JSON contract."""
+    from jumbo_mae_tpu_b200 import _lib, parallel
+    from jumbo_mae_tpu_b200.config import MAEConfig, flops_per_image
+    from jumbo_mae_tpu_b200.finetune_engine import FinetuneEngine
+    from jumbo_mae_tpu_b200 import finetuning as FT
+    from jumbo_mae_tpu_b200.params import ParamStore
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    parallel.init_from_env("nccl")
+    import torch.distributed as dist
+    _lib.require_device()
+    lib = _lib.load()
+    peaks = measured_peaks()
+    dev = torch.device("cuda", local)
+    gb = 1024 if args.global_batch == 4096 else args.global_batch
+    micro = min(256, gb // world)
+    accum = gb // (micro * world)
+    droppath = 0.1
+    ns = argparse.Namespace(layers=12, dim=768, heads=12, patch_size=16, image_size=224, labels=1000, weight_decay=0.05,
+                            adam_b1=0.9, adam_b2=0.999, adam_eps=1e-8, learning_rate=3.0e-3, lr_decay=0.75, clip_grad=0.0,
+                            grad_accum=accum, warmup_steps=1281167 * 10 // 1024, training_steps=1281167 * 110 // 1024,
+                            label_smoothing=0.1, mixup=0.8, cutmix=1.0, droppath=droppath, init_seed=1, mixup_seed=1,
+                            dropout_seed=1, optimizer="adamw", criterion="ce", mode="finetune")
+    state = FT.create_train_state(ns).replicate()
+    cfg, store = state.cfg, state.store
+    eng = state.engine(micro)
+    reducer = parallel.GradReducer(store) if world > 1 else None
+    state.reducer = reducer
+    gen = torch.Generator().manual_seed(rank)
+    host_images = [torch.randint(0, 256, (micro, 3, 224, 224), generator=gen, dtype=torch.uint8).pin_memory()
+                   for _ in range(accum)]
+    host_labels = [torch.randint(0, 1000, (micro,), generator=gen, dtype=torch.int32).pin_memory() for _ in range(accum)]
+    dev_images, dev_labels = [h.to(dev) for h in host_images], [h.to(dev) for h in host_labels]
+    # DropPath factors live in a device buffer the captured graph reads; fresh draws are copied in every micro-step
+    dgen = np.random.Generator(np.random.Philox(key=77 + rank))
+    drop_buf = torch.ones(cfg.layers, 3, micro, device=dev)
+    eng.set_droppath(drop_buf)
+    eng.capture_graphs(label_smoothing=0.1, mixup=True)
+    perm = torch.arange(micro, dtype=torch.int32, device=dev).flip(0).contiguous()
+    counter = {"step": 0}
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def resident_step():
+        for i in range(accum):
+            keep = dgen.random((cfg.layers, 3, micro)) >= droppath
+            drop_buf.copy_(torch.from_numpy(keep.astype(np.float32) / np.float32(1 - droppath)), non_blocking=True)
+            eng.run_graph(dev_images[i], dev_labels[i], i == 0, perm=perm)
+        if reducer is not None:
+            reducer.all_reduce_grads()
+        eng.adamw_step(counter["step"], FT.lr_schedule(counter["step"], state), grad_scale=1.0 / (accum * world),
+                       lr_decay=0.75)
+        counter["step"] += 1
+
+    sampler = ClockSampler(local)
+    sampler.start()
+
+    def timed(fn, steps):
+        barrier()
+        sampler.mark()
+        l0 = lib.jm_launch_count()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        launches = lib.jm_launch_count() - l0
+        ms = e0.elapsed_time(e1)
+        barrier()
+        t = torch.tensor([ms], device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return t.item(), launches, sampler.summary()
+
+    for _ in range(args.warmup):
+        resident_step()
+    ms, launches, clocks = timed(resident_step, args.steps)
+    launches += args.steps * accum * eng.graph_launches
+    ms_per_step = ms / args.steps
+    value = gb / (ms_per_step / 1e3)
+    final_loss = eng.loss.item()
+
+    # e2e through the public API (finetuning.training_step: eager launches, fresh Mixup / CutMix / DropPath draws,
+    # host images and labels copied in, metrics read back)
+    state.step, state.micro_step = counter["step"], 0
+
+    def e2e_step():
+        for i in range(accum):
+            _, m = FT.training_step(state, (host_images[i], host_labels[i]))
+            m["loss"].item()
+
+    e2e_step()
+    ms_e2e, _, _ = timed(e2e_step, max(1, args.steps // 2))
+    e2e_value = gb / (ms_e2e / max(1, args.steps // 2) / 1e3)
+    _, step_flops = flops_per_image(cfg)
+    tf = step_flops * gb / world / (ms_per_step * 1e-3) / 1e12
+    line = {
+        "metric": "finetune_images_per_sec", "value": value, "unit": "images/s", "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong",
+        "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+        "config": {"workload": "ViT-B/16 Jumbo CLS fine-tune step, 224 px, 196 + 3 tokens, 1000 classes, label smoothing 0.1, "
+                               "Mixup, DropPath 0.1, AdamW lr_decay 0.75, global batch 1024 (BASELINE.json configs[4], "
+                               "config/ft.sh)",
+                   "global_batch": gb, "micro_batch": micro, "grad_accum": accum, "parallelism": f"dp{world}",
+                   "l2": "inputs larger than L2: every micro-batch streams GBs of activations through a 126 MB L2"},
+        "roofline": {"bound": "tensor", "kernel": "whole optimizer step, algorithmic FLOPs "
+                                                   f"{step_flops / 1e9:.3f} GFLOP/image (SURVEY.md section 8d)",
+                     "achieved": tf, "peak": peaks["bf16_sustained"], "unit": "TFLOP/s", "frac": tf / peaks["bf16_sustained"],
+                     "traffic": None, "peak_source": f"{peaks['source']} (sustained: long step)"},
+        "e2e": {"value": e2e_value, "unit": "images/s",
+                "h2d_bytes_per_step": accum * (micro * 3 * 224 * 224 + micro * 4 + cfg.layers * 3 * micro * 4),
+                "d2h_bytes_per_step": accum * 4, "note": "public API finetuning.training_step: eager launches"},
+        "gpu_launches": int(launches), "clocks": clocks, "loss": final_loss,
+    }
+    sampler.stop()
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -440,9 +572,14 @@ def main():
     ap.add_argument("--global-batch", type=int, default=4096)
     ap.add_argument("--micro-batch", type=int, default=1024)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--workload", default="pretrain", choices=["pretrain", "finetune"],
+                    help="pretrain: BASELINE.json configs[1..3] (the headline); finetune: configs[4]")
+    ap.add_argument("--no-kernel-timings", action="store_true", help="skip the isolated GEMM re-timings (profiling runs)")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)
+    elif args.workload == "finetune":
+        run_finetune(args)
     else:
         run_ours(args)
 

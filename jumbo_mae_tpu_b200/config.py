@@ -105,6 +105,12 @@ def vit_h14(**kw) -> MAEConfig:
 def flops_per_image(cfg: MAEConfig):
     """Algorithmic (forward, full step) FLOPs per image: SURVEY.md section 8d / BASELINE.md section 3.
     Counts the patch embedding on the kept patches and the pixel head on the masked rows only."""
+    if cfg.labels > 0:   # classification step (BASELINE.json configs[4]): every patch, no decoder, LinearCLS head
+        N, J, d, L, P = cfg.num_patches, cfg.num_cls_tokens, cfg.dim, cfg.layers, cfg.patch_dim
+        T = N + J
+        fwd = 2.0 * (N * P * d + L * (4 * T * d * d + 2 * T * T * d + 8 * N * d * d + 8 * J * J * d * d)
+                     + J * d * cfg.labels)
+        return fwd, 3.0 * fwd - 2.0 * N * P * d
     n, m, N = cfg.keep, cfg.num_masked, cfg.num_patches
     J, d, L, P = cfg.num_cls_tokens, cfg.dim, cfg.layers, cfg.patch_dim
     Te, Td, dd, dl = n + J, N + J, cfg.dec_dim, cfg.dec_layers

@@ -6,9 +6,10 @@ concatenated CLS tokens, softmax cross-entropy on smoothed / mixed labels, top-1
 the patch rows and the logits is the schedule of ``engine.MAEEngine`` at ``T = J + N``; the two ends are
 ``jm_patchify`` / ``jm_patchify_mix`` and ``jm_softmax_ce``; the head is one ``jm_gemm`` over the strided CLS rows.
 
-Built: forward, loss, metrics, backward (all parameter gradients), AdamW with the layer-wise lr table
-(``adamw_step(..., lr_decay=0.75)``).  Not built (``create``-time options of the fine-tune recipe): DropPath 0.1,
-BatchNorm in the head (linear probing), LARS / LAMB / SGD; RNG draws (beta sample, permutation, box) are caller data.
+Built: forward, loss, metrics, backward (all parameter gradients), DropPath (``set_droppath``: per-image factors of
+the three branches of every JumboLayer), AdamW with the layer-wise lr table (``adamw_step(..., lr_decay=0.75)``).
+Not built (``create``-time options of the fine-tune recipe): BatchNorm in the head (linear probing), LARS / LAMB / SGD;
+RNG draws (beta sample, permutation, box, DropPath keep bits) are caller data.
 """
 from __future__ import annotations
 
@@ -187,3 +188,8 @@ class FinetuneEngine(MAEEngine):
         self.graphs[bool(zero_grads)].replay()
         return self.loss
 
+    def capture_segment_graphs(self) -> None:
+        """The classification step all-reduces its gradients after the last micro-step (finetuning.training_step,
+        bench.py --workload finetune): its backward segments exist (segment_grad_ranges) but are not captured one by
+        one -- the per-segment overlap of the pre-training step is not wired into this engine."""
+        raise NotImplementedError("per-segment CUDA graphs are not wired into the classification engine")
