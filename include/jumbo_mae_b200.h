@@ -82,6 +82,21 @@ int jm_patch_loss(const float* pred, long ldp, const uint8_t* images, const floa
                   int image_size, int patch_size, int num_cls, int norm_pix, float grad_scale, float* loss,
                   jm_bf16* dpred, long lddp, void* workspace, size_t workspace_bytes, void* stream);
 
+/* RandomResizedCrop (bicubic) + horizontal flip of the pre-training recipe on the device (src/dataset.py:56-58,70-71:
+ * T.RandomResizedCrop(S, scale=(0.2, 1.0), interpolation=3), T.RandomHorizontalFlip, T.PILToTensor).  Bit-exact
+ * with PIL's crop(box).resize((S, S), BICUBIC) [+ FLIP_LEFT_RIGHT]: Pillow's two-pass fixed-point resampling.
+ *   src      decoded images, uint8 HWC (RGB), packed in one buffer; image b starts at byte src_off[b]
+ *   src_hw   [batch, 2] (height, width) of each source image
+ *   boxes    [batch, 4] crop (top, left, height, width), drawn by the host (RandomResizedCrop.get_params);
+ *            every height and width must be <= max_crop
+ *   flips    [batch] 0 / 1 or NULL
+ *   out      [batch, 3, S, S] uint8 (the batch the training step takes)
+ * workspace: jm_rrc_flip_workspace(batch, max_crop, S) bytes (coefficient tables + the intermediate image). */
+size_t jm_rrc_flip_workspace(int batch, int max_crop, int out_size);
+int jm_rrc_flip(const uint8_t* src, const long* src_off, const int* src_hw, const int* boxes, const uint8_t* flips,
+                int batch, int max_crop, int out_size, uint8_t* out, void* workspace, size_t workspace_bytes,
+                void* stream);
+
 /* In place x[r, :] *= (r % period < skip ? scale_cls : scale)[r / period] on a bf16 [rows, cols] matrix: the backward
  * of a DropPath-scaled residual branch (src/modeling.py:157,181-183) -- the gradient entering the branch is the block
  * output gradient times the image's keep-mask / (1 - p); drop_path3 of the Jumbo CLS rows has its own mask
