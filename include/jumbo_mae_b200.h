@@ -97,6 +97,12 @@ int jm_rrc_flip(const uint8_t* src, const long* src_off, const int* src_hw, cons
                 int batch, int max_crop, int out_size, uint8_t* out, void* workspace, size_t workspace_bytes,
                 void* stream);
 
+/* Gradient of a learnable position embedding (--posemb learnable, src/modeling.py:115-118,123):
+ * dwpe[ids[i], :] += sum over the batch of dx[b*T + J + i, :] for the n kept patches i (ids = ids_shuffle, or NULL for
+ * the identity when every patch is kept).  dx is the f32 gradient of the encoder input, [batch*T, dim], stride ldx. */
+int jm_posemb_grad(const float* dx, long ldx, int batch, int T, int J, int n, const int32_t* ids, int dim, float* dwpe,
+                   void* stream);
+
 /* In place x[r, :] *= (r % period < skip ? scale_cls : scale)[r / period] on a bf16 [rows, cols] matrix: the backward
  * of a DropPath-scaled residual branch (src/modeling.py:157,181-183) -- the gradient entering the branch is the block
  * output gradient times the image's keep-mask / (1 - p); drop_path3 of the Jumbo CLS rows has its own mask

@@ -33,6 +33,7 @@ class MAEConfig:
     warmup_steps: int = 1281167 * 40 // 4096
     training_steps: int = 1281167 * 1600 // 4096
     grad_accum: int = 1
+    posemb: str = "sincos2d"           # "learnable": model/embed/wpe is a trained parameter (src/modeling.py:115-118)
     labels: int = 0                    # > 0: classification mode (ViT head, no masking, no decoder; src/modeling.py:239-242,252)
 
     @property
@@ -76,6 +77,8 @@ class MAEConfig:
             raise ValueError("head_dim must be 32, 64 or 80 (attention kernel instantiations)")
         if self.dim % 8 or self.dec_dim % 8:
             raise ValueError("dim and dec_dim must be multiples of 8")
+        if self.posemb not in ("sincos2d", "learnable"):
+            raise ValueError("posemb must be 'sincos2d' or 'learnable'")
         if self.keep + self.num_masked != self.num_patches:
             raise ValueError("keep + masked != patches for this mask ratio (the reference's concat would fail too)")
 

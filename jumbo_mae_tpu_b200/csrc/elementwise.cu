@@ -307,6 +307,24 @@ __global__ void patch_loss_finalize_kernel(const float* __restrict__ partial, co
   if (threadIdx.x == 0) loss[0] = tot / (num_masked * static_cast<float>(batch));
 }
 
+// gradient of a learnable position embedding (src/modeling.py:115-118,123): dwpe[ids[i], :] += sum_b dx[b, J + i, :]
+// (one block row per kept patch i, threads over 4-column groups, the batch summed in a fixed order)
+__global__ void posemb_grad_kernel(const float* __restrict__ dx, long ldx, int batch, int T, int J, int n,
+                                   const int* __restrict__ ids, int dim, float* __restrict__ dwpe) {
+  const int i = blockIdx.x;
+  const int c = (blockIdx.y * blockDim.x + threadIdx.x) * 4;
+  if (c >= dim) return;
+  float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+  for (int b = 0; b < batch; ++b) {
+    const float4 v = *reinterpret_cast<const float4*>(dx + (static_cast<long>(b) * T + J + i) * ldx + c);
+    acc.x += v.x, acc.y += v.y, acc.z += v.z, acc.w += v.w;
+  }
+  float4* dst = reinterpret_cast<float4*>(dwpe + static_cast<long>(ids ? ids[i] : i) * dim + c);
+  float4 o = *dst;
+  o.x += acc.x, o.y += acc.y, o.z += acc.z, o.w += acc.w;
+  *dst = o;
+}
+
 // x[r, :] *= (r % period < skip ? scale_cls : scale)[r / period]: the transpose of a DropPath-scaled residual branch
 // (the gradient that enters the branch is the block-output gradient times the image's keep-mask / (1 - p))
 __global__ void scale_rows_bf16_kernel(__nv_bfloat16* __restrict__ x, long ld, long rows, int cols,
@@ -1016,6 +1034,16 @@ extern "C" int jm_patch_loss(const float* pred, long ldp, const uint8_t* images,
                     reinterpret_cast<__nv_bfloat16*>(dpred), lddp, batch, N, P, STREAM);
   JM_AFTER_LAUNCH();
   patch_loss_finalize_kernel<<<1, 1024, 0, STREAM>>>(partial, mask_row, N, batch, loss);
+  JM_AFTER_LAUNCH();
+  return 0;
+}
+
+extern "C" int jm_posemb_grad(const float* dx, long ldx, int batch, int T, int J, int n, const int32_t* ids, int dim,
+                              float* dwpe, void* stream) {
+  JM_CHECK(dx && dwpe && batch > 0 && n > 0 && T >= J + n && dim > 0, "jm_posemb_grad: bad arguments");
+  JM_CHECK(dim % 4 == 0 && ldx % 4 == 0 && ((reinterpret_cast<uintptr_t>(dx) | reinterpret_cast<uintptr_t>(dwpe)) & 15) == 0,
+           "jm_posemb_grad: dim and ldx must be multiples of 4 and the buffers 16-byte aligned");
+  posemb_grad_kernel<<<dim3(n, (dim / 4 + 127) / 128), 128, 0, STREAM>>>(dx, ldx, batch, T, J, n, ids, dim, dwpe);
   JM_AFTER_LAUNCH();
   return 0;
 }

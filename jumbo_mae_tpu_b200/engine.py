@@ -141,6 +141,13 @@ class MAEEngine:
                 raise _lib.JmError(f"drop masks must be f32 [{nblk}, 3, {self.B}] on the device")
         self.drop_masks = masks
 
+    def _wpe_table(self) -> torch.Tensor:
+        """[N, d] position embedding added to the patch tokens: the fixed sincos table, or the trained parameter
+        model/embed/wpe with --posemb learnable (src/modeling.py:115-120)."""
+        if self.cfg.posemb == "learnable":
+            return self.ps.f("model/embed/wpe").view(self.cfg.num_patches, self.cfg.dim)
+        return self.wpe
+
     def _dp(self, block_index: int):
         return None if self.drop_masks is None else self.drop_masks[block_index]
 
@@ -199,7 +206,7 @@ class MAEEngine:
         ops.patchify(images, cfg.patch_size, self.ids_shuffle, n, Te, J, self.patches)
         x0 = self.xa[0]
         ops.fill_cls(x0, B, Te, J, d, ps.f("model/cls_tokens"))
-        self._fwd_linear(self.patches, Me, "model/embed/wte", d, P, lda=self.Pp, out_f32=x0, pe=self.wpe,
+        self._fwd_linear(self.patches, Me, "model/embed/wte", d, P, lda=self.Pp, out_f32=x0, pe=self._wpe_table(),
                          pe_idx=self.ids_shuffle, row_period=Te, row_skip=J, row_mask_mode=2)
         for i in range(cfg.layers):
             self._block_fwd(f"model/layer_{i}", self.enc[i], self.xa[i], self.xa[i + 1], Me, d, cfg.heads, Te, True,
@@ -373,6 +380,9 @@ class MAEEngine:
             # ---- CLS parameter and patch embedding (its bias gradient came from layer 0's LN1 backward)
             dx, dx16 = view(self.dxA, Me, d), view(self.dxA16, Me, d)
             ops.colsum(dx, B, J * d, ps.grad("model/cls_tokens"), ldx=Te * d)
+            if cfg.posemb == "learnable":      # d wpe = the patch rows of the encoder-input gradient, summed over the batch
+                ops.posemb_grad(dx, B, Te, J, Te - J, self.ids_shuffle if cfg.labels <= 0 else None, d,
+                                ps.grad("model/embed/wpe"))
             ops.gemm(self.patches, dx16, P, d, Me, a_mn=True, b_mn=True, lda=Pp,
                      out_f32=ps.grad("model/embed/wte/kernel"), ldo_f32=ps.ld("model/embed/wte/kernel"),
                      accumulate=True)

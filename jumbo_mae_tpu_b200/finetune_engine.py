@@ -100,7 +100,7 @@ class FinetuneEngine(MAEEngine):
                              ymask=ymask)
         x0 = self.xa[0]
         ops.fill_cls(x0, B, Te, J, d, ps.f("model/cls_tokens"))
-        self._fwd_linear(self.patches, Me, "model/embed/wte", d, P, lda=self.Pp, out_f32=x0, pe=self.wpe,
+        self._fwd_linear(self.patches, Me, "model/embed/wte", d, P, lda=self.Pp, out_f32=x0, pe=self._wpe_table(),
                          pe_idx=self.ids_all, row_period=Te, row_skip=J, row_mask_mode=2)
         for i in range(cfg.layers):
             self._block_fwd(f"model/layer_{i}", self.enc[i], self.xa[i], self.xa[i + 1], Me, d, cfg.heads, Te, True,

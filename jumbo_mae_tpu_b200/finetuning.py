@@ -153,12 +153,12 @@ def create_train_state(args: argparse.Namespace) -> TrainState:
         raise NotImplementedError("--dropout > 0 is not built (0.0 in the fine-tune recipe)")
     if not 0.0 <= float(getattr(args, "droppath", 0.0)) < 1.0:
         raise ValueError("--droppath must be in [0, 1)")
-    if getattr(args, "layerscale", False) or getattr(args, "posemb", "sincos2d") != "sincos2d":
-        raise NotImplementedError("LayerScale / learnable position embeddings are not built")
+    if getattr(args, "layerscale", False):
+        raise NotImplementedError("LayerScale is not built")
     cfg = MAEConfig(layers=args.layers, dim=args.dim, heads=args.heads, patch_size=args.patch_size,
                     image_size=args.image_size, labels=args.labels, weight_decay=args.weight_decay,
                     adam_b1=args.adam_b1, adam_b2=args.adam_b2, adam_eps=args.adam_eps,
-                    grad_accum=getattr(args, "grad_accum", 1))
+                    grad_accum=getattr(args, "grad_accum", 1), posemb=getattr(args, "posemb", "sincos2d"))
     store = ParamStore(cfg)
     gen = torch.Generator(device="cpu").manual_seed(int(getattr(args, "init_seed", 0)))
     for name, leaf in store.leaves.items():           # truncated_normal(0.02) kernels, LN scales 1, the rest 0

@@ -119,6 +119,13 @@ def patch_loss(pred: torch.Tensor, images: torch.Tensor, mask_row: torch.Tensor,
                                     workspace.numel() * workspace.element_size(), stream_ptr()))
 
 
+def posemb_grad(dx: torch.Tensor, batch: int, T: int, J: int, n: int, ids: Optional[torch.Tensor], dim: int,
+                dwpe: torch.Tensor) -> None:
+    """dwpe[ids[i]] += sum_b dx[b*T + J + i] (learnable position embedding, src/modeling.py:115-118,123)."""
+    _chk(dx, F32, "dx"), _chk(ids, I32, "ids"), _chk(dwpe, F32, "dwpe")
+    check(_lib.load().jm_posemb_grad(ptr(dx), _ld(dx), batch, T, J, n, ptr(ids), dim, ptr(dwpe), stream_ptr()))
+
+
 def scale_rows_bf16(x: torch.Tensor, rows: int, cols: int, scale: torch.Tensor, period: int,
                     scale_cls: Optional[torch.Tensor] = None, skip: int = 0, ld: Optional[int] = None) -> None:
     """In place x[r] *= (r % period < skip ? scale_cls : scale)[r // period] (DropPath backward)."""

@@ -70,6 +70,8 @@ def _leaves(cfg: MAEConfig) -> List[Leaf]:
 
     kernel("model/embed/wte/kernel", P, d)
     vec("model/embed/wte/bias", d)
+    if cfg.posemb == "learnable":       # [grid, grid, d] parameter named "wpe": no weight decay (mask = leaf name "kernel")
+        vec("model/embed/wpe", cfg.num_patches * d)
     vec("model/cls_tokens", J * d)
     kernel("model/jumbo_mlp/w1/kernel", J * d, 4 * J * d)
     vec("model/jumbo_mlp/w1/bias", 4 * J * d)
@@ -202,6 +204,8 @@ class ParamStore:
             "jumbo_mlp": ff("model/jumbo_mlp"),
             "norm": ln("model/norm"),
         }
+        if cfg.posemb == "learnable":
+            model["embed"]["wpe"] = v("model/embed/wpe").view(cfg.grid, cfg.grid, cfg.dim)
         for i in range(cfg.layers):
             p = f"model/layer_{i}"
             model[f"layer_{i}"] = {"attn": attn(f"{p}/attn", cfg.dim, cfg.heads), "ff": ff(f"{p}/ff"),

@@ -163,15 +163,14 @@ def create_train_state(args: argparse.Namespace) -> TrainState:
     _lib.require_device()
     if getattr(args, "optimizer", "adamw") != "adamw":
         raise NotImplementedError("only --optimizer adamw (both pre-training presets) is on the hot path")
-    for nm in ("dropout", "droppath", "dec_dropout", "dec_droppath"):
+    for nm in ("dropout", "dec_dropout"):
         if getattr(args, nm, 0.0) != 0.0:
             raise NotImplementedError(f"--{nm.replace('_', '-')} > 0 is not built (0.0 in both presets)")
     if getattr(args, "layerscale", False) or getattr(args, "dec_layerscale", False):
         raise NotImplementedError("LayerScale is off in both presets and not built")
-    if getattr(args, "posemb", "sincos2d") != "sincos2d":
-        raise NotImplementedError("only --posemb sincos2d (both presets) is built")
+    posemb = getattr(args, "posemb", "sincos2d")
     model = ViT(layers=args.layers, dim=args.dim, heads=args.heads, labels=getattr(args, "labels", 0),
-                patch_size=args.patch_size, image_size=args.image_size, posemb="sincos2d",
+                patch_size=args.patch_size, image_size=args.image_size, posemb=posemb,
                 image_mask_ratio=args.image_mask_ratio)
     decoder = MAEDecoder(dec_layers=args.dec_layers, dec_dim=args.dec_dim, dec_heads=args.dec_heads,
                          patch_size=args.patch_size, image_size=args.image_size)
@@ -179,7 +178,7 @@ def create_train_state(args: argparse.Namespace) -> TrainState:
     cfg = module.config(learning_rate=args.learning_rate, train_batch_size=args.train_batch_size,
                         weight_decay=args.weight_decay, adam_b1=args.adam_b1, adam_b2=args.adam_b2,
                         adam_eps=args.adam_eps, warmup_steps=args.warmup_steps, training_steps=args.training_steps,
-                        grad_accum=getattr(args, "grad_accum", 1))
+                        grad_accum=getattr(args, "grad_accum", 1), posemb=posemb)
     cfg.validate()
     store = ParamStore(cfg, device=torch.device("cuda", torch.cuda.current_device()))
     init_params_(store, getattr(args, "init_seed", 0))
@@ -202,7 +201,7 @@ def init_params_(store: ParamStore, seed: int) -> None:
             val = node[key]
             if isinstance(val, dict):
                 walk(val, path + (key,))
-            elif key == "kernel" or key == "image_mask_embedding":
+            elif key in ("kernel", "image_mask_embedding", "wpe"):     # truncated_normal(0.02) (src/modeling.py:116)
                 t = torch.empty(tuple(val.shape), dtype=torch.float32)
                 torch.nn.init.trunc_normal_(t, mean=0.0, std=1.0, a=-2.0, b=2.0, generator=gen)
                 val.copy_((t * 0.02).to(val.device))

@@ -61,6 +61,7 @@ class MAEConfig:
     dec_dim: int = 512
     dec_heads: int = 16
     norm_pix_loss: bool = False      # src/main_pretrain.py:139 (off in both presets)
+    posemb: str = "sincos2d"         # "learnable": embed/wpe is a parameter, truncated_normal(0.02) (src/modeling.py:115-118)
     labels: int = 0                  # > 0: classification mode of ViT (src/modeling.py:236-242): head, no masking, no decoder
     # optimizer: src/pretraining.py:223-259 with the preset's flags
     learning_rate: float = 1.5e-4
@@ -288,7 +289,10 @@ def patch_embed(images_nhwc, p: Tree, cfg: MAEConfig):
     patches = extract_patches(images_nhwc, cfg.patch_size)           # (ph, pw, c) order == HWI flatten
     w = p["wte"]["kernel"].reshape(-1, cfg.dim)
     x = patches @ w + p["wte"]["bias"]
-    wpe = fixed_sincos2d_embeddings(cfg.grid, cfg.grid, cfg.dim, dtype=x.dtype)
+    if cfg.posemb == "learnable":
+        wpe = p["wpe"]                                                 # [grid, grid, dim] parameter (:115-118)
+    else:
+        wpe = fixed_sincos2d_embeddings(cfg.grid, cfg.grid, cfg.dim, dtype=x.dtype)
     return x + wpe.reshape(1, -1, cfg.dim)
 
 
@@ -442,6 +446,8 @@ def init_params(cfg: MAEConfig, seed: int = 0, dtype=torch.float32, randomize_al
                                "norm1": _ln_p(d, dtype), "norm2": _ln_p(d, dtype),
                                "norm3": _ln_p(J * d, dtype)}
     model["norm"] = _ln_p(d, dtype)
+    if cfg.posemb == "learnable":    # drawn last, so that the sincos configurations keep their parameter values
+        model["embed"]["wpe"] = _tn(torch.Generator().manual_seed(seed + 7919), (cfg.grid, cfg.grid, d), dtype)
     if cfg.labels > 0:               # LinearCLS (src/modeling.py:209-219): nn.compact around one Dense -> "Dense_0"
         model["head"] = {"Dense_0": _dense_p(gen, J * d, cfg.labels, dtype)}
         params = {"model": model}

@@ -17,6 +17,7 @@ def _rel(a, b):
 def _cfgs():
     return {
         "tiny": (O.tiny(labels=16), 4),
+        "tiny_wpe": (O.tiny(labels=16, posemb="learnable"), 4),
         "mid": (O.MAEConfig(layers=2, dim=256, heads=4, patch_size=16, image_size=64, labels=40, warmup_steps=10,
                             training_steps=100, train_batch_size=256), 8),
     }
@@ -35,7 +36,8 @@ def _setup(name):
     return ocfg, cfg, params, images, store, FinetuneEngine(cfg, store, B)
 
 
-@pytest.mark.parametrize("name,mode", [("tiny", "plain"), ("tiny", "mixup"), ("tiny", "cutmix"), ("mid", "mixup")])
+@pytest.mark.parametrize("name,mode", [("tiny", "plain"), ("tiny", "mixup"), ("tiny", "cutmix"), ("mid", "mixup"),
+                                       ("tiny_wpe", "plain")])
 def test_classification_step_matches_oracle(name, mode):
     from jumbo_mae_tpu_b200.params import tree_leaves
     ocfg, cfg, params, images, store, eng = _setup(name)

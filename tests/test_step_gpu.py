@@ -32,6 +32,8 @@ def _cfgs():
         "config1_vitb16": (O.MAEConfig(), 8),
         # one ViT-H/14 block at its real width: d = 1280, head_dim 80, P = 588 (row pitch padded to 592),
         # T = 67 / 259, decoder 512 x 16 heads
+        # --posemb learnable (src/modeling.py:115-118): embed/wpe is a trained [grid, grid, dim] parameter
+        "tiny_learnable_wpe": (O.tiny(posemb="learnable"), 4),
         "vith_width": (O.MAEConfig(layers=2, dim=1280, heads=16, patch_size=14, image_size=224, dec_layers=1,
                                    warmup_steps=10, training_steps=100), 2),
     }
@@ -59,7 +61,8 @@ def _rel(a, b):
     return ((a - b).norm() / (b.norm() + 1e-12)).item()
 
 
-ALL = ["tiny", "tiny_normpix", "mid", "vitb_width", "vith_patch14", "config1_vitb16", "vith_width"]
+ALL = ["tiny", "tiny_normpix", "mid", "vitb_width", "vith_patch14", "config1_vitb16", "vith_width",
+       "tiny_learnable_wpe"]
 
 
 @pytest.mark.parametrize("name", ALL)
@@ -126,7 +129,7 @@ def test_backward_accumulates_and_rezeroes():
     assert torch.allclose(store.g, g1, rtol=1e-4, atol=1e-7)
 
 
-@pytest.mark.parametrize("name", ["tiny", "mid", "config1_vitb16"])
+@pytest.mark.parametrize("name", ["tiny", "mid", "config1_vitb16", "tiny_learnable_wpe"])
 def test_k_step_training_matches_oracle(name):
     from jumbo_mae_tpu_b200.engine import lr_schedule
     from jumbo_mae_tpu_b200.params import tree_leaves
