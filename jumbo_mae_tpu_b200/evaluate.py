@@ -7,7 +7,7 @@ i.e. total over total -- so a ragged or padded last batch is weighted by its siz
 from __future__ import annotations
 
 from collections import defaultdict
-from typing import Callable, Dict, Iterable, List, Sequence
+from typing import Callable, Dict, Iterable, Sequence
 
 import numpy as np
 
@@ -19,21 +19,30 @@ def _to_float(v) -> float:
 
 
 class AverageMeter:
-    """src/utils.py:34-50: buffers every update; ``summary`` returns the mean (or the latest value for the keys in
-    ``use_latest``) under ``prefix`` and clears the buffer."""
+    """Same contract as the reference's metric accumulator (src/utils.py:34-50): ``update(**metrics)`` once per step,
+    ``summary(prefix)`` reports, per key, the mean of the values seen since the last summary -- or the most recent one
+    for the keys named in ``use_latest`` (the learning rate) -- and starts over.  Kept as running sums instead of
+    lists of samples: a log interval of thousands of steps costs two floats per key."""
 
     def __init__(self, use_latest: Sequence[str] = ()):
-        self.buffer: Dict[str, List] = defaultdict(list)
-        self.use_latest = list(use_latest)
+        self.use_latest = set(use_latest)
+        self._sum: Dict[str, float] = defaultdict(float)
+        self._count: Dict[str, int] = defaultdict(int)
+        self._last: Dict[str, float] = {}
 
     def update(self, **kwargs) -> None:
-        for k, v in kwargs.items():
-            self.buffer[k].append(_to_float(v))
+        for key, value in kwargs.items():
+            x = _to_float(value)
+            self._sum[key] += x
+            self._count[key] += 1
+            self._last[key] = x
 
     def summary(self, prefix: str = "") -> Dict[str, float]:
-        buffer = {k: np.array(v) for k, v in self.buffer.items()}
-        self.buffer.clear()
-        return {f"{prefix}{k}": (v[-1] if k in self.use_latest else np.mean(v)) for k, v in buffer.items()}
+        out = {}
+        for key, last in self._last.items():
+            out[f"{prefix}{key}"] = last if key in self.use_latest else self._sum[key] / self._count[key]
+        self._sum.clear(), self._count.clear(), self._last.clear()
+        return out
 
 
 def evaluate(state, dataloader: Iterable, validation_step: Callable) -> Dict[str, float]:

@@ -106,7 +106,13 @@ class TrainState:
         return {"noise": noise}, {}
 
     def engine(self, batch: int) -> MAEEngine:
+        """Activation buffers (and CUDA graphs) exist per per-rank batch size: keep it fixed, as the reference's loader
+        does (it pads / drops the ragged last batch).  At most two engines are kept (training + validation batch size);
+        an older one-off shape is released when a third appears."""
         if batch not in self.engines:
+            if len(self.engines) >= 2:
+                oldest = next(iter(self.engines))
+                del self.engines[oldest]
             self.engines[batch] = MAEEngine(self.cfg, self.store, batch)
         return self.engines[batch]
 
@@ -223,6 +229,13 @@ def _device_images(images) -> torch.Tensor:
     return images.contiguous()
 
 
+def _device_noise(nz, device) -> torch.Tensor:
+    """The mask noise (numpy array, host or device tensor) as an f32 device vector."""
+    if isinstance(nz, np.ndarray):
+        nz = torch.from_numpy(np.ascontiguousarray(nz, dtype=np.float32))
+    return nz.to(device=device, dtype=torch.float32, non_blocking=True).contiguous()
+
+
 def training_step(state: TrainState, batch, noise=None) -> Tuple[TrainState, Dict[str, Any]]:
     """src/pretraining.py:125-159.  ``batch`` is the 1-tuple ``(images,)`` the reference splats
     into ``apply_fn``; images are this rank's uint8 [B, 3, H, W] shard (host or device).
@@ -230,9 +243,7 @@ def training_step(state: TrainState, batch, noise=None) -> Tuple[TrainState, Dic
     Returns (state, {"loss": device scalar, "learning_rate": float})."""
     images = _device_images(batch[0] if isinstance(batch, (tuple, list)) else batch)
     rngs, _ = state.split_rngs() if noise is None else ({"noise": noise}, {})
-    nz = rngs["noise"]
-    nz = torch.from_numpy(np.ascontiguousarray(nz, dtype=np.float32)) if isinstance(nz, np.ndarray) else nz
-    nz = nz.to(device=state.store.device, dtype=torch.float32, non_blocking=True)
+    nz = _device_noise(rngs["noise"], state.store.device)
     eng = state.engine(images.shape[0])
     state._consume_prefetched(images)
     world = process_count()
@@ -282,11 +293,13 @@ def validation_step(state: TrainState, batch, noise=None) -> Dict[str, Any]:
     returns psum-ed {"loss", "num_samples"}."""
     images = _device_images(batch[0] if isinstance(batch, (tuple, list)) else batch)
     if noise is None:
-        gen = np.random.Generator(np.random.Philox(key=state.noise_rng + 7919 * process_index() + 104729))
-        noise = gen.random(state.cfg.num_patches, dtype=np.float32)
+        # freshly split, not stored (src/pretraining.py:164): one validation stream per rank, advanced per call
+        if getattr(state, "_val_gen", None) is None:
+            state._val_gen = np.random.Generator(np.random.Philox(key=state.noise_rng + 7919 * process_index() + 104729))
+        noise = state._val_gen.random(state.cfg.num_patches, dtype=np.float32)
     dev = state.store.device
     images = images.to(dev, non_blocking=True)
-    nz = torch.from_numpy(np.ascontiguousarray(noise, dtype=np.float32)).to(dev)
+    nz = _device_noise(noise, dev)
     eng = state.engine(images.shape[0])
     loss = eng.forward(images, nz, want_grad=False).clone()
     num = torch.tensor([float(images.shape[0])], device=dev)
