@@ -161,6 +161,14 @@ int jm_layernorm_bwd(const jm_bf16* dy, long lddy, const float* x, long ldx, con
                      float* dcol, int dcol_period, int dcol_skip, void* workspace, size_t workspace_bytes,
                      void* stream);
 
+/* jm_layernorm_bwd with the incoming residual gradient in bf16 (dres_bf16, may be NULL) and dx optional (NULL: only the
+ * bf16 copy dx_bf16 is written): the decoder's gradient stream kept in bf16 only, 10 instead of 16 bytes per element
+ * (dim <= 512).  Same arithmetic otherwise; no row skipping. */
+int jm_layernorm_bwd_lowp(const jm_bf16* dy, long lddy, const float* x, long ldx, const float* mean, const float* rstd,
+                          const float* gamma, int rows, int dim, const jm_bf16* dres_bf16, long lddres, float* dx,
+                          long lddx, jm_bf16* dx_bf16, long lddxb, float* dgamma, float* dbeta, float* dcol,
+                          void* workspace, size_t workspace_bytes, void* stream);
+
 /* ---------------------------------------------------------------- GEMM
  * D = epilogue(A * B), bf16 operands, f32 accumulation in tensor memory
  * (tcgen05.mma fed by TMA).  Replaces every Dense / DenseGeneral / Conv contraction

@@ -20,7 +20,7 @@ EXPORTS = [
     "jm_extract_patches", "jm_patch_loss_workspace", "jm_patch_loss", "jm_patch_loss_static", "jm_layernorm_fwd",
     "jm_layernorm_bwd_workspace", "jm_layernorm_bwd", "jm_gemm", "jm_attention_fwd", "jm_attention_bwd",
     "jm_fill_cls", "jm_unshuffle_fwd", "jm_unshuffle_bwd", "jm_colsum", "jm_adamw", "jm_cast_bf16",
-    "jm_add_bias_cast", "jm_clip_by_global_norm", "jm_softmax_ce", "jm_patchify_mix", "jm_patch_mse_loss", "jm_scale_rows_bf16", "jm_rrc_flip_workspace", "jm_rrc_flip", "jm_posemb_grad",
+    "jm_add_bias_cast", "jm_clip_by_global_norm", "jm_softmax_ce", "jm_patchify_mix", "jm_patch_mse_loss", "jm_scale_rows_bf16", "jm_rrc_flip_workspace", "jm_rrc_flip", "jm_posemb_grad", "jm_layernorm_bwd_lowp",
 ]
 
 
@@ -80,6 +80,8 @@ def load() -> ctypes.CDLL:
         "jm_patchify": [P, c_int, c_int, c_int, P, c_int, c_int, c_int, P, c_long, P],
         "jm_extract_patches": [P, c_int, c_int, c_int, P, P],
         "jm_patch_loss": [P, c_long, P, P, c_int, c_int, c_int, c_int, c_int, c_float, P, P, c_long, P, c_size_t, P],
+        "jm_layernorm_bwd_lowp": [P, c_long, P, c_long, P, P, P, c_int, c_int, P, c_long, P, c_long, P, c_long, P, P, P, P,
+                                  c_size_t, P],
         "jm_posemb_grad": [P, c_long, c_int, c_int, c_int, c_int, P, c_int, P, P],
         "jm_rrc_flip": [P, P, P, P, P, c_int, c_int, c_int, P, P, c_size_t, P],
         "jm_scale_rows_bf16": [P, c_long, c_long, c_int, P, P, c_int, c_int, P],

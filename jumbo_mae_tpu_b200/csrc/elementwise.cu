@@ -635,7 +635,7 @@ layernorm_bwd_pipe_kernel(const __nv_bfloat16* __restrict__ dy, long lddy, const
                          const float* __restrict__ gamma, int rows, int D, const float* __restrict__ dres,
                          long lddres, float* __restrict__ dx, long lddx, __nv_bfloat16* __restrict__ dxb, long lddxb,
                          int row_period, int row_skip, float* __restrict__ ws, int want_dcol, int dcol_period,
-                         int dcol_skip, LnDirect direct) {
+                         int dcol_skip, LnDirect direct, int res_bf16) {
   pdl_wait();  // programmatic dependent launch: nothing above touches global memory
   pdl_launch_dependents();
   extern __shared__ __align__(16) float s_acc[];  // [warps][3][D]: dgamma, dbeta, column sums of dx
@@ -665,7 +665,15 @@ layernorm_bwd_pipe_kernel(const __nv_bfloat16* __restrict__ dy, long lddy, const
       w.x[k] = make_float4(w.mu, w.mu, w.mu, w.mu);
       w.dy[k] = make_uint2(0u, 0u);
       if (c < D) {
-        if (dres) w.res[k] = *reinterpret_cast<const float4*>(dres + r * lddres + c);
+        if (dres) {
+          if (res_bf16) {  // the residual gradient stream kept in bf16 only (lddres in bf16 elements); the raw
+                           // bits travel in .x/.y and are unpacked at the use, so that the load stays in flight
+            const uint2 u = *reinterpret_cast<const uint2*>(reinterpret_cast<const __nv_bfloat16*>(dres) + r * lddres + c);
+            w.res[k].x = __uint_as_float(u.x), w.res[k].y = __uint_as_float(u.y);
+          } else {
+            w.res[k] = *reinterpret_cast<const float4*>(dres + r * lddres + c);
+          }
+        }
         w.dy[k] = *reinterpret_cast<const uint2*>(dy + r * lddy + c);
         w.x[k] = *reinterpret_cast<const float4*>(x + r * ldx + c);
       }
@@ -689,6 +697,10 @@ layernorm_bwd_pipe_kernel(const __nv_bfloat16* __restrict__ dy, long lddy, const
     for (int k = 0; k < NV; ++k) {
       const int c = lane * 4 + k * 128;
       rres[k] = cur.res[k];
+      if (res_bf16) {
+        const float2 a = unpack_bf16(__float_as_uint(rres[k].x)), b = unpack_bf16(__float_as_uint(rres[k].y));
+        rres[k] = make_float4(a.x, a.y, b.x, b.y);
+      }
       const uint2 u = cur.dy[k];
       const float4 xv = cur.x[k];
       float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -1158,12 +1170,14 @@ extern "C" size_t jm_layernorm_bwd_workspace(int rows, int dim) {
   return static_cast<size_t>(ln_bwd_blocks(rows, dim)) * 3 * dim * sizeof(float);
 }
 
-extern "C" int jm_layernorm_bwd(const jm_bf16* dy, long lddy, const float* x, long ldx, const float* mean,
-                                const float* rstd, const float* gamma, int rows, int dim, const float* dres,
-                                long lddres, float* dx, long lddx, jm_bf16* dx_bf16, long lddxb, int row_period,
-                                int row_skip, float* dgamma, float* dbeta, float* dcol, int dcol_period,
-                                int dcol_skip, void* workspace, size_t workspace_bytes, void* stream) {
+static int layernorm_bwd_impl(const jm_bf16* dy, long lddy, const float* x, long ldx, const float* mean,
+                              const float* rstd, const float* gamma, int rows, int dim, const float* dres,
+                              long lddres, int res_bf16, float* dx, long lddx, jm_bf16* dx_bf16, long lddxb,
+                              int row_period, int row_skip, float* dgamma, float* dbeta, float* dcol, int dcol_period,
+                              int dcol_skip, void* workspace, size_t workspace_bytes, void* stream) {
   JM_CHECK(dim % 4 == 0 && ldx % 4 == 0 && lddy % 4 == 0, "jm_layernorm_bwd: dim/ld must be multiples of 4");
+  JM_CHECK(!res_bf16 || (dim <= 512 && lddres % 4 == 0),
+           "jm_layernorm_bwd_lowp: the bf16 residual-gradient input is built for dim <= 512");
   JM_CHECK(dim * 3 * sizeof(float) <= 96 * 1024, "jm_layernorm_bwd: dim %d too large", dim);
   JM_CHECK(dcol == nullptr || dim <= 1280, "jm_layernorm_bwd: dcol is only produced for dim <= 1280");
   if (rows == 0) return 0;
@@ -1189,11 +1203,11 @@ extern "C" int jm_layernorm_bwd(const jm_bf16* dy, long lddy, const float* x, lo
               ((reinterpret_cast<uintptr_t>(dgamma) | reinterpret_cast<uintptr_t>(dbeta) |
                 reinterpret_cast<uintptr_t>(dcol)) & 15) == 0;
 #define JM_LN_BWD_ARGS_D JM_LN_BWD_ARGS, direct
-  if (dim <= 128) JM_LAUNCH_PDL(layernorm_bwd_pipe_kernel<1>, grid, tr, smem_reg, STREAM, JM_LN_BWD_ARGS_D);
-  else if (dim <= 256) JM_LAUNCH_PDL(layernorm_bwd_pipe_kernel<2>, grid, tr, smem_reg, STREAM, JM_LN_BWD_ARGS_D);
-  else if (dim <= 512) JM_LAUNCH_PDL(layernorm_bwd_pipe_kernel<4>, grid, tr, smem_reg, STREAM, JM_LN_BWD_ARGS_D);
+  if (dim <= 128) JM_LAUNCH_PDL(layernorm_bwd_pipe_kernel<1>, grid, tr, smem_reg, STREAM, JM_LN_BWD_ARGS_D, res_bf16);
+  else if (dim <= 256) JM_LAUNCH_PDL(layernorm_bwd_pipe_kernel<2>, grid, tr, smem_reg, STREAM, JM_LN_BWD_ARGS_D, res_bf16);
+  else if (dim <= 512) JM_LAUNCH_PDL(layernorm_bwd_pipe_kernel<4>, grid, tr, smem_reg, STREAM, JM_LN_BWD_ARGS_D, res_bf16);
 #ifdef JM_LN_PIPE6
-  else if (dim <= 768) JM_LAUNCH_PDL(layernorm_bwd_pipe_kernel<6>, grid, tr, smem_reg, STREAM, JM_LN_BWD_ARGS_D);
+  else if (dim <= 768) JM_LAUNCH_PDL(layernorm_bwd_pipe_kernel<6>, grid, tr, smem_reg, STREAM, JM_LN_BWD_ARGS_D, 0);
 #else
   else if (dim <= 768) JM_LAUNCH_PDL(layernorm_bwd_reg_kernel<6>, grid, tr, smem_reg, STREAM, JM_LN_BWD_ARGS_D);
 #endif
@@ -1217,6 +1231,25 @@ extern "C" int jm_layernorm_bwd(const jm_bf16* dy, long lddy, const float* x, lo
     JM_AFTER_LAUNCH();
   }
   return 0;
+}
+
+extern "C" int jm_layernorm_bwd(const jm_bf16* dy, long lddy, const float* x, long ldx, const float* mean,
+                                const float* rstd, const float* gamma, int rows, int dim, const float* dres,
+                                long lddres, float* dx, long lddx, jm_bf16* dx_bf16, long lddxb, int row_period,
+                                int row_skip, float* dgamma, float* dbeta, float* dcol, int dcol_period,
+                                int dcol_skip, void* workspace, size_t workspace_bytes, void* stream) {
+  return layernorm_bwd_impl(dy, lddy, x, ldx, mean, rstd, gamma, rows, dim, dres, lddres, 0, dx, lddx, dx_bf16, lddxb,
+                            row_period, row_skip, dgamma, dbeta, dcol, dcol_period, dcol_skip, workspace,
+                            workspace_bytes, stream);
+}
+
+extern "C" int jm_layernorm_bwd_lowp(const jm_bf16* dy, long lddy, const float* x, long ldx, const float* mean,
+                                     const float* rstd, const float* gamma, int rows, int dim, const jm_bf16* dres_bf16,
+                                     long lddres, float* dx, long lddx, jm_bf16* dx_bf16, long lddxb, float* dgamma,
+                                     float* dbeta, float* dcol, void* workspace, size_t workspace_bytes, void* stream) {
+  return layernorm_bwd_impl(dy, lddy, x, ldx, mean, rstd, gamma, rows, dim, reinterpret_cast<const float*>(dres_bf16),
+                            lddres, dres_bf16 != nullptr ? 1 : 0, dx, lddx, dx_bf16, lddxb, 0, 0, dgamma, dbeta, dcol,
+                            0, 0, workspace, workspace_bytes, stream);
 }
 
 extern "C" int jm_fill_cls(float* x, int batch, int T, int J, int dim, const float* cls, void* stream) {

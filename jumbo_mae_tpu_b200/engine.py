@@ -128,6 +128,8 @@ class MAEEngine:
         ln_ws = max(ops.layernorm_bwd_workspace(Mx, max(d, dd)), ops.layernorm_bwd_workspace(B, J * d))
         self.ln_ws = torch.empty(ln_ws, dtype=torch.uint8, device=dev)
         self.drop_masks = None
+        # decoder residual-gradient stream in bf16 alone (LayerNorm backward's dim <= 512 kernel); JM_DEC_LOWP=0: f32
+        self.dec_lowp = dd <= 512 and os.environ.get("JM_DEC_LOWP", "1") != "0"
 
     # ------------------------------------------------------------------ DropPath (src/modeling.py:157,181-183)
     def set_droppath(self, masks: Optional[torch.Tensor]) -> None:
@@ -337,8 +339,12 @@ class MAEEngine:
             # (every LayerNorm backward also emits the column sums of the dx it produces: that dx is the
             #  output gradient of the previous block's ff/w2, i.e. its bias gradient)
             dp_on = self.drop_masks is not None     # then every block sums its ff/w2 bias from its scaled gradient copy
+            # The decoder's residual-gradient stream is carried in bf16 alone (like the reference's bf16 activations):
+            # its LayerNorm backwards move 10 instead of 16 bytes per element.  Only the gradient that leaves the
+            # decoder (layer 0's input, scattered back to the encoder's tokens) is also written in f32.
+            lowp = self.dec_lowp and not dp_on
             ops.layernorm_bwd(dn, self.za[cfg.dec_layers], self.meanD, self.rstdD,
-                              ps.f("decoder_model/dec_norm/scale"), None, dx, dx16,
+                              ps.f("decoder_model/dec_norm/scale"), None, None if lowp else dx, dx16,
                               ps.grad("decoder_model/dec_norm/scale"), ps.grad("decoder_model/dec_norm/bias"),
                               self.ln_ws,
                               dcol=None if dp_on else ps.grad(f"decoder_model/dec_layer_{cfg.dec_layers - 1}/ff/w2/bias"))
@@ -346,7 +352,7 @@ class MAEEngine:
             for i in reversed(range(cfg.dec_layers)):
                 below = ps.grad(f"decoder_model/dec_layer_{i - 1}/ff/w2/bias") if i > 0 else None
                 self._block_bwd(f"decoder_model/dec_layer_{i}", self.dec[i], self.za[i], Md, dd, cfg.dec_heads, Td,
-                                False, below, dp=self._dp(cfg.layers + i))
+                                False, below, dp=self._dp(cfg.layers + i), lowp=(1 + (i == 0)) if lowp else 0)
             # ---- decoder input assembly + decoder_proj
             ops.unshuffle_bwd(dx, self.ids_restore, B, N, n, J, dd, self.dy16, ps.grad("image_mask_embedding"))
             dn = view(self.dn16, Me, d)
@@ -388,7 +394,7 @@ class MAEEngine:
                      accumulate=True)
 
     def _block_bwd(self, name, s: _Block, x_in, M, dim, heads, T, jumbo, dcol_below, part="all", dp=None,
-                   below_is_branch=True):
+                   below_is_branch=True, lowp=0):
         """In: d/d(block output) in dxA / dxA16.  Out: d/d(block input) in dxA / dxA16.
         ``part``: "all", or the block in two steps, "jumbo" (the Jumbo CLS branch alone: it reads and writes only
         the CLS rows, which the patch FFN branch leaves alone) followed by "rest".
@@ -399,7 +405,9 @@ class MAEEngine:
         block-output gradient times its image's factor, so the bf16 gradient copies are scaled in place before the
         branch's products, and the bias gradients that LayerNorm backward would fuse (column sums of the UNscaled
         gradient) are taken from the scaled copies instead.  ``below_is_branch``: dcol_below is the bias of a
-        DropPath-scaled branch of the block below (false for the patch embedding)."""
+        DropPath-scaled branch of the block below (false for the patch embedding).
+        ``lowp`` (plain blocks without DropPath): 1 = the gradient arrives and leaves in dxA16 alone (bf16), 2 = it
+        arrives in bf16 and leaves in both dxA (f32) and dxA16."""
         ps, B, J = self.ps, self.B, self.cfg.num_cls_tokens
         hd = dim // heads
         view = lambda buf, w: buf[:M * w].view(M, w)
@@ -421,10 +429,15 @@ class MAEEngine:
                              row_period=period, row_skip=skip, row_mask_mode=mode,
                              colsum=ps.grad(f"{name}/ff/w1/bias"))
             self._bwd_linear(s.xn2, dh, M, f"{name}/ff/w1", 4 * dim, dim, dX16=dn, bias=False)
-            ops.layernorm_bwd(dn, s.xb, s.mean2, s.rstd2, ps.f(f"{name}/norm2/scale"), dx, dxb, dxb16,
-                              ps.grad(f"{name}/norm2/scale"), ps.grad(f"{name}/norm2/bias"), self.ln_ws,
-                              row_period=period, row_skip=skip,
-                              dcol=None if dp is not None else ps.grad(f"{name}/attn/wo/bias"))
+            if lowp:
+                ops.layernorm_bwd_lowp(dn, s.xb, s.mean2, s.rstd2, ps.f(f"{name}/norm2/scale"), dx16, None, dxb16,
+                                       ps.grad(f"{name}/norm2/scale"), ps.grad(f"{name}/norm2/bias"), self.ln_ws,
+                                       dcol=ps.grad(f"{name}/attn/wo/bias"))
+            else:
+                ops.layernorm_bwd(dn, s.xb, s.mean2, s.rstd2, ps.f(f"{name}/norm2/scale"), dx, dxb, dxb16,
+                                  ps.grad(f"{name}/norm2/scale"), ps.grad(f"{name}/norm2/bias"), self.ln_ws,
+                                  row_period=period, row_skip=skip,
+                                  dcol=None if dp is not None else ps.grad(f"{name}/attn/wo/bias"))
         if jumbo and part != "rest":
             # ---- Jumbo CLS: c_out = c + w2j(gelu(w1j c)), c = LN3(cls concat); strided [B, J*dim] views
             Jd, ldc = J * dim, T * dim
@@ -459,6 +472,11 @@ class MAEEngine:
         self._bwd_linear(s.xn1, dqkv, M, f"{name}/attn/wqkv", 3 * dim, dim, dX16=dn, bias=False)
         if any_dp and below_is_branch:
             dcol_below = None       # the block below takes its ff/w2 bias from its own scaled gradient copy
+        if lowp:
+            ops.layernorm_bwd_lowp(dn, x_in, s.mean1, s.rstd1, ps.f(f"{name}/norm1/scale"), dxb16,
+                                   dx if lowp == 2 else None, dx16, ps.grad(f"{name}/norm1/scale"),
+                                   ps.grad(f"{name}/norm1/bias"), self.ln_ws, dcol=dcol_below)
+            return
         ops.layernorm_bwd(dn, x_in, s.mean1, s.rstd1, ps.f(f"{name}/norm1/scale"), dxb, dx, dx16,
                           ps.grad(f"{name}/norm1/scale"), ps.grad(f"{name}/norm1/bias"), self.ln_ws,
                           dcol=dcol_below, dcol_period=period, dcol_skip=skip)

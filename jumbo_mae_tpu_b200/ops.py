@@ -183,6 +183,21 @@ def layernorm_bwd(dy: torch.Tensor, x: torch.Tensor, mean: torch.Tensor, rstd: t
         workspace.numel() * workspace.element_size(), stream_ptr()))
 
 
+def layernorm_bwd_lowp(dy: torch.Tensor, x: torch.Tensor, mean: torch.Tensor, rstd: torch.Tensor, gamma: torch.Tensor,
+                       dres_bf16: Optional[torch.Tensor], dx: Optional[torch.Tensor], dx_bf16: torch.Tensor,
+                       dgamma: torch.Tensor, dbeta: torch.Tensor, workspace: torch.Tensor,
+                       dcol: Optional[torch.Tensor] = None) -> None:
+    """LayerNorm backward with the residual gradient read (and written) in bf16 only (dim <= 512)."""
+    _chk(dy, BF16, "dy"), _chk(x, F32, "x"), _chk(mean, F32, "mean"), _chk(rstd, F32, "rstd"), _chk(gamma, F32, "gamma")
+    _chk(dres_bf16, BF16, "dres_bf16"), _chk(dx, F32, "dx"), _chk(dx_bf16, BF16, "dx_bf16"), _chk(dcol, F32, "dcol")
+    _chk(dgamma, F32, "dgamma"), _chk(dbeta, F32, "dbeta")
+    rows, dim = x.shape[0], x.shape[-1]
+    check(_lib.load().jm_layernorm_bwd_lowp(
+        ptr(dy), _ld(dy), ptr(x), _ld(x), ptr(mean), ptr(rstd), ptr(gamma), rows, dim, ptr(dres_bf16), _ld(dres_bf16),
+        ptr(dx), _ld(dx), ptr(dx_bf16), _ld(dx_bf16), ptr(dgamma), ptr(dbeta), ptr(dcol), ptr(workspace),
+        workspace.numel() * workspace.element_size(), stream_ptr()))
+
+
 # ------------------------------------------------------------------ GEMM
 def gemm(A: torch.Tensor, B: torch.Tensor, M: int, N: int, K: int, *, a_mn: bool = False, b_mn: bool = False,
          lda: Optional[int] = None, ldb: Optional[int] = None,

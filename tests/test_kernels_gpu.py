@@ -183,6 +183,44 @@ def test_layernorm_bwd(ops, rows, D, period, skip):
     assert torch.allclose(dbeta.cpu() - 1, beta.grad, rtol=1e-4, atol=1e-4 * scale)
 
 
+@pytest.mark.parametrize("rows,D,with_f32", [(257, 512, False), (130, 256, True), (1000, 128, False)])
+def test_layernorm_bwd_lowp(ops, rows, D, with_f32):
+    """jm_layernorm_bwd_lowp: the residual gradient read from bf16, dx written in bf16 (and f32 on request) --
+    same arithmetic as jm_layernorm_bwd fed the same (bf16-rounded) residual gradient."""
+    g = torch.Generator().manual_seed(D + rows)
+    x = (torch.randn(rows, D, generator=g) * 2 + 0.5).requires_grad_(True)
+    gamma = torch.randn(D, generator=g).requires_grad_(True)
+    beta = torch.randn(D, generator=g).requires_grad_(True)
+    dy = torch.randn(rows, D, generator=g).to(BF16)
+    dres = torch.randn(rows, D, generator=g).to(BF16)
+    y = O.layer_norm(x, gamma, beta)
+    (y * dy.float()).sum().backward()
+    want_dx = x.grad + dres.float()
+    mean = x.detach().mean(-1)
+    var = torch.clamp((x.detach() ** 2).mean(-1) - mean ** 2, min=0)
+    rstd = torch.rsqrt(var + 1e-6)
+    dx = torch.full((rows, D), 5.0, device="cuda") if with_f32 else None
+    dxb = torch.full((rows, D), 5.0, dtype=BF16, device="cuda")
+    dgamma, dbeta, dcol = (torch.ones(D, device="cuda") for _ in range(3))
+    ws = torch.empty(ops.layernorm_bwd_workspace(rows, D), dtype=torch.uint8, device="cuda")
+    ops.layernorm_bwd_lowp(dev(dy), dev(x.detach()), dev(mean), dev(rstd), dev(gamma.detach()), dev(dres), dx, dxb,
+                           dgamma, dbeta, ws, dcol=dcol)
+    scale = max(1.0, math.sqrt(rows))
+    if with_f32:
+        assert torch.allclose(dx.cpu(), want_dx, rtol=1e-4, atol=1e-4)
+    assert torch.allclose(dxb.float().cpu(), want_dx, rtol=2 ** -7, atol=1e-3)
+    assert torch.allclose(dcol.cpu() - 1, want_dx.sum(0), rtol=1e-4, atol=1e-3 * scale)
+    assert torch.allclose(dgamma.cpu() - 1, gamma.grad, rtol=1e-4, atol=1e-4 * scale)
+    assert torch.allclose(dbeta.cpu() - 1, beta.grad, rtol=1e-4, atol=1e-4 * scale)
+    with pytest.raises(RuntimeError):        # the wide-row kernels do not have the bf16 input
+        ops.layernorm_bwd_lowp(torch.zeros(4, 768, dtype=BF16, device="cuda"), torch.zeros(4, 768, device="cuda"),
+                               torch.zeros(4, device="cuda"), torch.ones(4, device="cuda"),
+                               torch.ones(768, device="cuda"), torch.zeros(4, 768, dtype=BF16, device="cuda"), None,
+                               torch.zeros(4, 768, dtype=BF16, device="cuda"), torch.zeros(768, device="cuda"),
+                               torch.zeros(768, device="cuda"),
+                               torch.empty(ops.layernorm_bwd_workspace(4, 768), dtype=torch.uint8, device="cuda"))
+
+
 # ------------------------------------------------------------------ token assembly
 def test_fill_cls_and_unshuffle(ops):
     B, N, n, J, d = 3, 16, 4, 3, 32
