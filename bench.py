@@ -362,6 +362,19 @@ def run_ours(args):
         gemm_ms_total += timed_shapes[key]
         gemm_flops += 2.0 * M_ * N_ * K_
     gemm_weighted_tflops = gemm_flops / (gemm_ms_total * 1e-3) / 1e12 if gemm_ms_total > 0 else 0.0
+    if os.environ.get("JM_BENCH_GEMM_TABLE") and rank == 0:     # per-shape table (stderr): where the GEMM time goes
+        counts = {}
+        for A, B, M_, N_, K_, kw in recorded:
+            key = (M_, N_, K_, kw.get("a_mn", False), kw.get("b_mn", False), kw.get("act", 0),
+                   kw.get("out_f32") is not None, kw.get("out2_bf16") is not None, kw.get("residual") is not None,
+                   bool(kw.get("accumulate", False)))
+            counts[key] = counts.get(key, 0) + 1
+        print("count  M N K a_mn b_mn act f32 out2 res acc : ms each, TFLOP/s, share of GEMM time", file=sys.stderr)
+        for key, n in sorted(counts.items(), key=lambda kv: -kv[1] * timed_shapes.get(kv[0], 0.0)):
+            t = timed_shapes.get(key, 0.0)
+            tf = 2.0 * key[0] * key[1] * key[2] / (t * 1e-3) / 1e12 if t > 0 else 0.0
+            print(f"{n:4d} {key} : {t:.4f} ms, {tf:7.1f}, {100 * n * t / max(gemm_ms_total, 1e-9):5.1f} %",
+                  file=sys.stderr)
     fwd_flops, step_flops = flops_per_image(cfg)
     step_tflops_per_gpu = step_flops * args.global_batch / world / (ms_per_step * 1e-3) / 1e12
 

@@ -42,7 +42,22 @@ constexpr int kStageBytesPerWarp = 32 * kStageRowBytes;  // 32 rows
 struct GemmShape {
   int M, N, K;
   int num_m, num_n, splits, kblocks;
+  int group_m;  // tile order: n fastest within bands of group_m tile rows, m fastest inside a band (1: plain n fastest)
+  int quad;     // CTA-pair kernel in clusters of two pairs: 0 off, 1 the pairs share A (tiles adjacent in n), 2 share B
 };
+
+// Tile index within one split -> tile coordinates.
+__device__ __forceinline__ void tile_mn(const GemmShape& sh, int rem, int& m_blk, int& n_blk) {
+  if (sh.group_m <= 1) {
+    m_blk = rem / sh.num_n, n_blk = rem - m_blk * sh.num_n;
+    return;
+  }
+  const int per = sh.group_m * sh.num_n;
+  const int g = rem / per, r = rem - g * per;
+  const int m0 = g * sh.group_m;
+  const int gm = min(sh.group_m, sh.num_m - m0);
+  n_blk = r / gm, m_blk = m0 + (r - n_blk * gm);
+}
 
 struct GemmMaps {
   CUtensorMap a, b, o, o2;  // operands; bf16 outputs of the row-register epilogues (TMA stores)
@@ -352,7 +367,8 @@ __device__ __forceinline__ void epilogue_role(const EpiParams& ep, const GemmSha
   int iter = 0;
   for (int t = tile0; t < total_tiles; t += tile_step, ++iter) {
     const int rem = t % tiles_mn;
-    const int m_blk = rem / sh.num_n, n_blk = rem - m_blk * sh.num_n;
+    int m_blk, n_blk;
+    tile_mn(sh, rem, m_blk, n_blk);
     const int acc = iter & 1;
     const uint32_t acc_phase = (iter >> 1) & 1;
     // this lane's 2 rows are the same for every sub-chunk of the tile: resolve the row predicates once
@@ -394,7 +410,7 @@ __device__ __forceinline__ void epilogue_role(const EpiParams& ep, const GemmSha
       if (c == NSUB - 1) {  // accumulator fully drained: hand the TMEM buffer back to the MMA warp
         tc_fence_before();
         if constexpr (CG == 1) mbar_arrive(&tempty[acc]);
-        else mbar_arrive_cluster(mapa_shared(smem_u32(&tempty[acc]), 0));  // the leader CTA issues the MMAs
+        else mbar_arrive_cluster(mapa_shared(smem_u32(&tempty[acc]), cluster_ctarank() & ~1u));  // the leader CTA issues the MMAs
       }
       __syncwarp();
       const EpiPrefetch<EPI> cur = pf;
@@ -569,7 +585,8 @@ __device__ __forceinline__ void epilogue_rows(const EpiParams& ep, const GemmSha
   };
   auto half_origin = [&](int t, int& row_base, int& colp) {
     const int rem = t % tiles_mn;
-    const int m_blk = rem / sh.num_n, n_blk = rem - m_blk * sh.num_n;
+    int m_blk, n_blk;
+    tile_mn(sh, rem, m_blk, n_blk);
     row_base = m_blk * (BM * CG) + m_off + q * 32;
     colp = n_blk * BN + part * (32 * NH);
   };
@@ -585,14 +602,15 @@ __device__ __forceinline__ void epilogue_rows(const EpiParams& ep, const GemmSha
   int iter = 0;
   for (int t = tile0; t < total_tiles; t += tile_step, ++iter) {
     const int rem = t % tiles_mn;
-    const int m_blk = rem / sh.num_n, n_blk = rem - m_blk * sh.num_n;
+    int m_blk, n_blk;
+    tile_mn(sh, rem, m_blk, n_blk);
     const int acc = iter & 1;
     const uint32_t acc_phase = (iter >> 1) & 1;
     auto release = [&]() {
       EPI_T(pr0);
       tc_fence_before();
       if constexpr (CG == 1) mbar_arrive(&tempty[acc]);
-      else mbar_arrive_cluster(mapa_shared(smem_u32(&tempty[acc]), 0));  // the leader CTA issues the MMAs
+      else mbar_arrive_cluster(mapa_shared(smem_u32(&tempty[acc]), cluster_ctarank() & ~1u));  // the leader CTA issues the MMAs
       EPI_ACC(pt_rel, pr0);
     };
     if constexpr (PARTS < 4) {
@@ -678,7 +696,11 @@ __device__ __forceinline__ void epilogue_rows(const EpiParams& ep, const GemmSha
         if (tma) {
           fence_proxy_async();  // this lane's staging writes -> visible to the async proxy
           __syncwarp();
+#ifdef JM_EXP_NO_STORE
+          if (lane == 0 && colh < 0) {
+#else
           if (lane == 0) {
+#endif
             tma_store_2d(o == 0 ? tmO : tmO2, stage_addr + buf, colh, row_base);
             tma_store_commit();
           }
@@ -790,7 +812,11 @@ __device__ __forceinline__ void epilogue_rows(const EpiParams& ep, const GemmSha
             if constexpr (EPI == EPI_GELU_FWD) {
               if (saved_grad) {  // act 3 (kernel-uniform): out <- gelu'(v) instead of v
                 f32x2 gg, dd;
+#ifdef JM_EXP_NO_GELU
+                gg = v[j], dd = mul2(v[j], v[j]);
+#else
                 gelu_both2(v[j], gg, dd);
+#endif
                 unpack2(dd, a, b);
                 P[j] = pack_bf16(a, b);
                 unpack2(gg, a, b);
@@ -931,7 +957,8 @@ __device__ __forceinline__ void epilogue_f32_tma(const EpiParams& ep, const Gemm
   uint32_t rissued = 0;  // bit b: a residual load into tile b is in flight
   auto tile_origin = [&](int t, int& row_base, int& colp) {
     const int rem = t % tiles_mn;
-    const int m_blk = rem / sh.num_n, n_blk = rem - m_blk * sh.num_n;
+    int m_blk, n_blk;
+    tile_mn(sh, rem, m_blk, n_blk);
     row_base = m_blk * (BM * CG) + m_off + q * 32;
     colp = n_blk * BN + part * PART_N;
   };
@@ -987,7 +1014,7 @@ __device__ __forceinline__ void epilogue_f32_tma(const EpiParams& ep, const Gemm
       if (c == NC - 1) {  // accumulator fully drained: hand the TMEM buffer back to the MMA warp
         tc_fence_before();
         if constexpr (CG == 1) mbar_arrive(&tempty[acc]);
-        else mbar_arrive_cluster(mapa_shared(smem_u32(&tempty[acc]), 0));
+        else mbar_arrive_cluster(mapa_shared(smem_u32(&tempty[acc]), cluster_ctarank() & ~1u));
       }
       if (live) {
 #pragma unroll
@@ -1119,7 +1146,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
         const int split = t / tiles_mn;
         const int rem = t - split * tiles_mn;
-        const int m_blk = rem / sh.num_n, n_blk = rem - m_blk * sh.num_n;
+        int m_blk, n_blk;
+    tile_mn(sh, rem, m_blk, n_blk);
         const int kb0 = static_cast<int>(static_cast<long>(sh.kblocks) * split / sh.splits);
         const int kb1 = static_cast<int>(static_cast<long>(sh.kblocks) * (split + 1) / sh.splits);
         for (int kb = kb0; kb < kb1; ++kb) {
@@ -1205,35 +1233,49 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
 #ifndef JM_PAIR_BF16_BUFS
 #define JM_PAIR_BF16_BUFS 1  // measured 1-3 % faster on the plain bf16 GEMMs than two tiles + 5 stages
 #endif
-template <int EPI>
+#ifndef JM_BRES_BUFS
+#define JM_BRES_BUFS 1
+#endif
+#ifndef JM_BRES_STAGES
+#define JM_BRES_STAGES 4
+#endif
+// BRES ("B resident", K <= 512): the pair's B tile stays in shared memory over all its k-blocks (8 x 16 KB per CTA) and
+// is loaded once per column tile; only A streams through the ring.  Measured on the long-K weight-gradient GEMM: a
+// k-block costs 605 cycles with no operand loads at all, 734 with one operand's and 906 with both -- the TMA fills
+// share the shared-memory port with the MMA's operand reads and add to them instead of hiding behind them -- so a
+// K = 512 product whose pairs keep their column tile saves one of the two fills.
+template <int EPI, bool BRES = false>
 struct Gemm2Cfg {
   static constexpr int BN = 256;
   static constexpr int A_BYTES = BM * BK * 2;         // this CTA's 128 rows
   static constexpr int B_BYTES = (BN / 2) * BK * 2;   // this CTA's 128 of the 256 columns
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+  static constexpr int RES_KB = 8;                    // k-blocks of B that stay resident (BRES)
   // Two staging tiles per epilogue warp (5 pipeline stages) where the epilogue is heavy; the light plain-bf16
   // epilogue can run with one tile and a sixth stage (JM_PAIR_BF16_BUFS).
-  static constexpr int EPI_BUFS = (EPI == EPI_BF16) ? JM_PAIR_BF16_BUFS : 2;
-  static constexpr int STAGES = EPI_BUFS == 2 ? 5 : 6;
+  static constexpr int EPI_BUFS = BRES ? JM_BRES_BUFS : ((EPI == EPI_BF16) ? JM_PAIR_BF16_BUFS : 2);
+  static constexpr int STAGES = BRES ? JM_BRES_STAGES : (EPI_BUFS == 2 ? 5 : 6);
+  static constexpr int OPER_BYTES = BRES ? STAGES * A_BYTES + RES_KB * B_BYTES : STAGES * STAGE_BYTES;
   static constexpr int TMEM_COLS = 2 * BN;
-  static constexpr int BAR_BYTES = (2 * STAGES + 4) * 8 + 16 + kEpiWarps * 2 * 8;  // + residual-load barriers
+  static constexpr int BAR_BYTES = (2 * STAGES + 4) * 8 + 16 + kEpiWarps * 2 * 8 + 16;  // + residual-load barriers, bfull
   static constexpr int EPI_BYTES = kEpiWarps * kStageBytesPerWarp * EPI_BUFS;
-  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + EPI_BYTES + BAR_BYTES + 1024;
+  static constexpr int SMEM_BYTES = OPER_BYTES + EPI_BYTES + BAR_BYTES + 1024;
+  static_assert(SMEM_BYTES <= 232448, "shared memory budget");
 };
 
-template <bool A_MN, bool B_MN, int EPI>
+template <bool A_MN, bool B_MN, int EPI, bool BRES = false>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
              const __grid_constant__ CUtensorMap tmO, const __grid_constant__ CUtensorMap tmO2, const GemmShape sh,
              const EpiParams ep) {
-  using Cfg = Gemm2Cfg<EPI>;
+  using Cfg = Gemm2Cfg<EPI, BRES>;
   constexpr int STAGES = Cfg::STAGES;
   constexpr int BN = Cfg::BN;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   uint8_t* sA = smem;
   uint8_t* sB = smem + STAGES * Cfg::A_BYTES;
-  uint8_t* sEpi = smem + STAGES * Cfg::STAGE_BYTES;
+  uint8_t* sEpi = smem + Cfg::OPER_BYTES;
   uint64_t* bars = reinterpret_cast<uint64_t*>(sEpi + Cfg::EPI_BYTES);
   uint64_t* full = bars;
   uint64_t* empty = bars + STAGES;
@@ -1241,11 +1283,19 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
   uint64_t* tempty = bars + 2 * STAGES + 2;
   uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 4);
   uint64_t* rbars = bars + 2 * STAGES + 6;  // two per epilogue warp: residual tiles arriving by TMA
+  uint64_t* bfull = rbars + kEpiWarps * 2;  // BRES: the resident B tile has landed (in the leader, like `full`)
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
-  const int rank = static_cast<int>(cluster_ctarank());
-  const int pair = blockIdx.x >> 1, npairs = gridDim.x >> 1;
+  // Clusters of one pair, or (sh.quad) of two pairs that work on neighbouring tiles in lock-step and share one operand:
+  // each CTA loads half of the shared operand's rows and the TMA multicasts it to the CTA of the same rank in the other
+  // pair, so a k-block costs 24 KB of L2 reads per CTA instead of 32 (the L2 -> SM rate is what bounds these GEMMs).
+  const int crank = static_cast<int>(cluster_ctarank());
+  const int rank = crank & 1;  // within the pair
+  const int sub = crank >> 1;  // which pair of the cluster
+  const int quad = sh.quad;    // kernel-uniform
+  const int pair = quad ? 2 * (blockIdx.x >> 2) + sub : blockIdx.x >> 1;
+  const int npairs = quad ? 2 * (gridDim.x >> 2) : gridDim.x >> 1;
 #ifdef JM_DEBUG_SMID
   if (threadIdx.x == 0 && blockIdx.x < 8) {
     uint32_t smid;
@@ -1261,13 +1311,14 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
   if (warp == 0 && elect_one()) {
     for (int s = 0; s < STAGES; ++s) {
       mbar_init(&full[s], 1);   // the leader's producer arrives with the byte count of BOTH CTAs' loads
-      mbar_init(&empty[s], 1);  // one multicast commit
+      mbar_init(&empty[s], quad ? 2 : 1);  // one multicast commit per pair that reads (or writes into) the stage
     }
     for (int a = 0; a < 2; ++a) {
       mbar_init(&tfull[a], 1);
       mbar_init(&tempty[a], 2 * kEpiWarps * 32);
     }
     for (int i = 0; i < kEpiWarps * 2; ++i) mbar_init(&rbars[i], 1);
+    mbar_init(bfull, 1);
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc2<Cfg::TMEM_COLS>(tmem_ptr);
@@ -1286,29 +1337,83 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
     if (elect_one()) {
       int stage = 0;
       uint32_t phase = 0;
+      const uint16_t mc_mask = static_cast<uint16_t>((1u << crank) | (1u << (crank ^ 2)));
+      int res_n = -1;                      // BRES: the column tile whose B is resident
+      int last_stage = 0;
+      uint32_t last_phase = 0;             // ring position of the last k-block issued
       for (int t = pair; t < total_tiles; t += npairs) {
         const int split = t / tiles_mn;
         const int rem = t - split * tiles_mn;
-        const int m_blk = rem / sh.num_n, n_blk = rem - m_blk * sh.num_n;
+        int m_blk, n_blk;
+        tile_mn(sh, rem, m_blk, n_blk);
         const int kb0 = static_cast<int>(static_cast<long>(sh.kblocks) * split / sh.splits);
         const int kb1 = static_cast<int>(static_cast<long>(sh.kblocks) * (split + 1) / sh.splits);
         const int m0 = m_blk * 2 * BM + rank * BM;
         const int n0 = n_blk * BN + rank * (BN / 2);
+        if constexpr (BRES) {
+          if (n_blk != res_n) {  // (host: splits == 1, kblocks <= RES_KB)
+            // the MMAs of the previous tile were the last readers of the resident tile: they have retired when the
+            // stage of its last k-block has been handed back
+            if (res_n >= 0) mbar_wait(&empty[last_stage], last_phase);
+            if (rank == 0) mbar_arrive_expect_tx(bfull, 2 * (kb1 - kb0) * Cfg::B_BYTES);
+            for (int kb = kb0; kb < kb1; ++kb) {
+              uint8_t* b_dst = sB + (kb - kb0) * Cfg::B_BYTES;
+              if (!B_MN) {
+                tma_load_2d_pair(&tmB, bfull, b_dst, kb * BK, n0);
+              } else {
+#pragma unroll
+                for (int i = 0; i < (BN / 2) / 64; ++i)
+                  tma_load_2d_pair(&tmB, bfull, b_dst + i * (BK * 128), n0 + i * 64, kb * BK);
+              }
+            }
+            res_n = n_blk;
+          }
+        }
         for (int kb = kb0; kb < kb1; ++kb) {
           mbar_wait(&empty[stage], phase ^ 1);
+          last_stage = stage, last_phase = phase;
+          if constexpr (BRES) {
+            if (rank == 0) mbar_arrive_expect_tx(&full[stage], 2 * Cfg::A_BYTES);
+            tma_load_2d_pair(&tmA, &full[stage], sA + stage * Cfg::A_BYTES, kb * BK, m0);
+            if (++stage == STAGES) stage = 0, phase ^= 1;
+            continue;
+          }
           // the peer's bytes may land before this arrive: the transaction count then runs negative until it
           // does, and the phase cannot complete without the arrival
+#ifdef JM_EXP_TMA_MODE  // experiments: 1 no operand loads at all, 2 only A, 3 only B (results are garbage)
+          {
+          if (rank == 0)
+            mbar_arrive_expect_tx(&full[stage], JM_EXP_TMA_MODE == 1 ? 0 : (JM_EXP_TMA_MODE == 2 ? 2 * Cfg::A_BYTES : 2 * Cfg::B_BYTES));
+          uint8_t* a_dst = sA + stage * Cfg::A_BYTES;
+          uint8_t* b_dst = sB + stage * Cfg::B_BYTES;
+          if (JM_EXP_TMA_MODE == 2 && !A_MN) tma_load_2d_pair(&tmA, &full[stage], a_dst, kb * BK, m0);
+          if (JM_EXP_TMA_MODE == 3 && !B_MN) tma_load_2d_pair(&tmB, &full[stage], b_dst, kb * BK, n0);
+          if (JM_EXP_TMA_MODE == 3 && B_MN) {
+            for (int i = 0; i < (BN / 2) / 64; ++i)
+              tma_load_2d_pair(&tmB, &full[stage], b_dst + i * (BK * 128), n0 + i * 64, kb * BK);
+          }
+          if (++stage == STAGES) stage = 0, phase ^= 1;
+          continue;
+          }
+#endif
           if (rank == 0) mbar_arrive_expect_tx(&full[stage], 2 * Cfg::STAGE_BYTES);
           uint8_t* a_dst = sA + stage * Cfg::A_BYTES;
           uint8_t* b_dst = sB + stage * Cfg::B_BYTES;
-          if (!A_MN) {
+          // shared operand: this CTA's 64 of the 128 rows (8 KB, the same bytes either major), to both pairs
+          if (quad == 1) {
+            if (!A_MN) tma_load_2d_pair_mc(&tmA, &full[stage], a_dst + sub * 8192, kb * BK, m0 + sub * 64, mc_mask);
+            else tma_load_2d_pair_mc(&tmA, &full[stage], a_dst + sub * 8192, m0 + sub * 64, kb * BK, mc_mask);
+          } else if (!A_MN) {
             tma_load_2d_pair(&tmA, &full[stage], a_dst, kb * BK, m0);
           } else {
 #pragma unroll
             for (int i = 0; i < BM / 64; ++i)
               tma_load_2d_pair(&tmA, &full[stage], a_dst + i * (BK * 128), m0 + i * 64, kb * BK);
           }
-          if (!B_MN) {
+          if (quad == 2) {
+            if (!B_MN) tma_load_2d_pair_mc(&tmB, &full[stage], b_dst + sub * 8192, kb * BK, n0 + sub * 64, mc_mask);
+            else tma_load_2d_pair_mc(&tmB, &full[stage], b_dst + sub * 8192, n0 + sub * 64, kb * BK, mc_mask);
+          } else if (!B_MN) {
             tma_load_2d_pair(&tmB, &full[stage], b_dst, kb * BK, n0);
           } else {
 #pragma unroll
@@ -1325,6 +1430,10 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
       int stage = 0;
       uint32_t phase = 0;
       int iter = 0;
+      // a stage is free when both pairs have read it (its shared half was written by the other pair's CTA)
+      const uint16_t pair_mask = static_cast<uint16_t>(3u << (2 * sub)), empty_mask = quad ? 0xF : pair_mask;
+      int res_n = -1;
+      uint32_t res_phase = 0;  // BRES: resident column tile / parity of its next arrival
       for (int t = pair; t < total_tiles; t += npairs, ++iter) {
         const int split = t / tiles_mn;
         const int kb0 = static_cast<int>(static_cast<long>(sh.kblocks) * split / sh.splits);
@@ -1334,12 +1443,20 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
         mbar_wait(&tempty[acc], acc_phase ^ 1);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + acc * BN;
+        if constexpr (BRES) {
+          int m_blk, n_blk;
+          tile_mn(sh, t - split * tiles_mn, m_blk, n_blk);
+          if (n_blk != res_n) {
+            mbar_wait(bfull, res_phase);
+            res_phase ^= 1, res_n = n_blk;
+          }
+        }
         for (int kb = kb0; kb < kb1; ++kb) {
           mbar_wait(&full[stage], phase);
           tc_fence_after();
           if (elect_one()) {
             const uint32_t a_addr = smem_u32(sA + stage * Cfg::A_BYTES);
-            const uint32_t b_addr = smem_u32(sB + stage * Cfg::B_BYTES);
+            const uint32_t b_addr = smem_u32(sB + (BRES ? kb - kb0 : stage) * Cfg::B_BYTES);
 #pragma unroll
             for (int k = 0; k < BK / UMMA_K; ++k) {
               const uint64_t da = A_MN ? make_smem_desc_sw128(a_addr + k * (UMMA_K * 128), BK * 128, 1024)
@@ -1348,8 +1465,8 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
                                        : make_smem_desc_sw128(b_addr + k * (UMMA_K * 2), 0, 1024);
               umma2_bf16(d_tmem, da, db, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
             }
-            umma2_commit_mc(&empty[stage]);
-            if (kb == kb1 - 1) umma2_commit_mc(&tfull[acc]);
+            umma2_commit_mask(&empty[stage], empty_mask);
+            if (kb == kb1 - 1) umma2_commit_mask(&tfull[acc], pair_mask);
           }
           __syncwarp();
           if (++stage == STAGES) stage = 0, phase ^= 1;
@@ -1423,25 +1540,27 @@ static int launch_gemm(const GemmMaps& tm, const GemmShape& sh, const EpiParams&
   return 0;
 }
 
-template <bool A_MN, bool B_MN, int EPI>
+template <bool A_MN, bool B_MN, int EPI, bool BRES = false>
 static int launch_gemm2(const GemmMaps& tm, const GemmShape& sh, const EpiParams& ep,
                         int grid, cudaStream_t stream) {
-  auto kern = gemm2_kernel<A_MN, B_MN, EPI>;
+  auto kern = gemm2_kernel<A_MN, B_MN, EPI, BRES>;
+  constexpr int kSmem = Gemm2Cfg<EPI, BRES>::SMEM_BYTES;
   static DeviceOnce attr_set;
   const int dev = current_device();
   JM_CHECK(dev >= 0, "jm_gemm: no current CUDA device");
   if (!attr_set.done(dev)) {
-    JM_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Gemm2Cfg<EPI>::SMEM_BYTES));
+    JM_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
     attr_set.mark(dev);
   }
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(grid);
   cfg.blockDim = dim3(kGemmThreads);
-  cfg.dynamicSmemBytes = Gemm2Cfg<EPI>::SMEM_BYTES;
+  cfg.dynamicSmemBytes = kSmem;
   cfg.stream = stream;
   cudaLaunchAttribute attr[3];
+  const int csize = sh.quad ? 4 : 2;
   attr[0].id = cudaLaunchAttributeClusterDimension;
-  attr[0].val.clusterDim.x = 2;
+  attr[0].val.clusterDim.x = csize;
   attr[0].val.clusterDim.y = 1;
   attr[0].val.clusterDim.z = 1;
   attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
@@ -1457,22 +1576,35 @@ static int launch_gemm2(const GemmMaps& tm, const GemmShape& sh, const EpiParams
   }
   // A persistent grid must not exceed the clusters the GPU can hold at once (GPCs with an odd SM left over
   // cannot host a pair there): surplus clusters would run as a second wave.
-  static std::atomic<int> max_clusters_dev[kMaxDevices];  // per device ordinal (zero-initialised)
-  int max_clusters = max_clusters_dev[dev].load(std::memory_order_acquire);
+  static std::atomic<int> max_clusters_dev[2][kMaxDevices];  // per cluster size and device ordinal (zero-initialised)
+  std::atomic<int>& cached = max_clusters_dev[sh.quad ? 1 : 0][dev];
+  int max_clusters = cached.load(std::memory_order_acquire);
   if (max_clusters == 0) {
     int n = 0;
     JM_CUDA(cudaOccupancyMaxActiveClusters(&n, kern, &cfg));
     JM_CHECK(n > 0, "jm_gemm: the CTA-pair kernel cannot be scheduled on this device");
-    if (getenv("JM_PAIR_VERBOSE")) fprintf(stderr, "jm: pair kernel max active clusters = %d\n", n);
-    max_clusters_dev[dev].store(n, std::memory_order_release);
+    if (getenv("JM_PAIR_VERBOSE")) fprintf(stderr, "jm: pair kernel max active clusters of %d = %d\n", csize, n);
+    cached.store(n, std::memory_order_release);
     max_clusters = n;
   }
-  if (grid > 2 * max_clusters) {
-    cfg.gridDim = dim3(2 * max_clusters);
+  if (grid > csize * max_clusters) {
+    cfg.gridDim = dim3(csize * max_clusters);
   }
   JM_CUDA(cudaLaunchKernelEx(&cfg, kern, tm.a, tm.b, tm.o, tm.o2, sh, ep));
   count_launch();
   return 0;
+}
+
+// B-resident instantiations (K <= 512, A K-major): the four TMA-fed epilogues
+template <bool B_MN>
+static int dispatch_bres(int epi, const GemmMaps& tm, const GemmShape& sh, const EpiParams& ep, int grid,
+                         cudaStream_t stream) {
+  switch (epi) {
+    case EPI_BF16: return launch_gemm2<false, B_MN, EPI_BF16, true>(tm, sh, ep, grid, stream);
+    case EPI_F32: return launch_gemm2<false, B_MN, EPI_F32, true>(tm, sh, ep, grid, stream);
+    case EPI_GELU_FWD: return launch_gemm2<false, B_MN, EPI_GELU_FWD, true>(tm, sh, ep, grid, stream);
+    default: return launch_gemm2<false, B_MN, EPI_GELU_BWD, true>(tm, sh, ep, grid, stream);
+  }
 }
 
 template <bool A_MN, bool B_MN>
@@ -1488,7 +1620,8 @@ static int dispatch_epi2(int epi, const GemmMaps& tm, const GemmShape& sh,
 }
 
 // Pair kernel instantiations: forward (A K-major, B MN-major), input gradient (K, K), weight gradient (MN, MN).
-static int dispatch_pair(bool a_mn, bool b_mn, int epi, const GemmMaps& tm, const GemmShape& sh, const EpiParams& ep, int grid, cudaStream_t stream) {
+static int dispatch_pair(bool a_mn, bool b_mn, int epi, const GemmMaps& tm, const GemmShape& sh, const EpiParams& ep, int grid, cudaStream_t stream, bool bres) {
+  if (bres) return b_mn ? dispatch_bres<true>(epi, tm, sh, ep, grid, stream) : dispatch_bres<false>(epi, tm, sh, ep, grid, stream);
   if (!a_mn && !b_mn) return dispatch_epi2<false, false>(epi, tm, sh, ep, grid, stream);
   if (!a_mn && b_mn) return dispatch_epi2<false, true>(epi, tm, sh, ep, grid, stream);
   if (epi == EPI_F32) return launch_gemm2<true, true, EPI_F32>(tm, sh, ep, grid, stream);
@@ -1538,6 +1671,43 @@ static int pick_splits(long tiles, long slots, int kblocks) {
     if (best == 0.0 || cost < best * 0.98) best = cost, best_s = s;
   }
   return best_s;
+}
+
+// How many 4-CTA clusters of the pair kernel the current device holds at once (GPCs whose SM count is not a multiple of
+// four leave SMs over: 33 clusters = 132 of 148 SMs on B200); cached per device ordinal.
+static int quad_cluster_capacity() {
+  static std::atomic<int> cap[jm::kMaxDevices];
+  const int dev = jm::current_device();
+  if (dev < 0) return 0;
+  int n = cap[dev].load(std::memory_order_acquire);
+  if (n == 0) {
+    auto kern = jm::gemm2_kernel<false, true, jm::EPI_GELU_FWD>;  // the largest shared-memory footprint
+    cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, jm::Gemm2Cfg<jm::EPI_GELU_FWD>::SMEM_BYTES);
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(4 * 64), cfg.blockDim = dim3(jm::kGemmThreads);
+    cfg.dynamicSmemBytes = jm::Gemm2Cfg<jm::EPI_GELU_FWD>::SMEM_BYTES;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 4, attr[0].val.clusterDim.y = 1, attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr, cfg.numAttrs = 1;
+    if (cudaOccupancyMaxActiveClusters(&n, kern, &cfg) != cudaSuccess || n <= 0) {
+      cudaGetLastError();
+      n = -1;
+    }
+    cap[dev].store(n, std::memory_order_release);
+  }
+  return n > 0 ? n : 0;
+}
+
+// True when p points into an ordinary device allocation of the current device (not host, managed, or a mapping of
+// another GPU's memory).
+static bool operand_is_local(const void* p) {
+  cudaPointerAttributes at;
+  if (cudaPointerGetAttributes(&at, p) != cudaSuccess) {
+    cudaGetLastError();
+    return false;
+  }
+  return at.type == cudaMemoryTypeDevice && at.device == jm::current_device();
 }
 
 extern "C" int jm_gemm(const jm_gemm_args* a, void* stream_) {
@@ -1632,22 +1802,42 @@ extern "C" int jm_gemm(const jm_gemm_args* a, void* stream_) {
     }
   }
 
+  // Two pairs per cluster that share one operand by TMA multicast, where the tile grid pairs up evenly: neighbours in
+  // n share A, else neighbours in m share B (tile rows then run in bands of 8, m fastest, so that the two are
+  // neighbours in the tile order as well).  TMA multicast loads here read only this GPU's memory, since on B200 a TMA
+  // multicast load from another GPU's memory hung the GPU: the kernel is picked only when both operands are plain
+  // device allocations of the current device.
+  static const int auto_quad = env_int("JM_GEMM_QUAD", 0);  // process-wide, initialised once (thread-safe)
+  int quad = 0, group_m = 1;
+  if (pair && (auto_quad || a->cta_pair == 4) && a->cta_pair != 2) {  // cta_pair 2: plain pairs, 4: ask for this
+    if (num_n % 2 == 0) quad = 1;
+    else if (num_m_eff % 2 == 0) quad = 2, group_m = num_m_eff < 8 ? num_m_eff : 8;
+    if (auto_quad == 2 && quad == 1 && num_m_eff % 2 == 0) quad = 2, group_m = num_m_eff < 8 ? num_m_eff : 8;
+    if (quad && !(operand_is_local(a->A) && operand_is_local(a->B))) quad = 0, group_m = 1;
+    if (quad && quad_cluster_capacity() <= 0) quad = 0, group_m = 1;
+  }
+  const int quad_slots = quad ? quad_cluster_capacity() : 0;
+  if (quad && a->splits <= 0) {
+    splits = 1;
+    if (can_split) splits = pick_splits(static_cast<long>(num_m_eff) * num_n / 2, quad_slots, kblocks);
+  }
+
   GemmMaps tm;
   memset(&tm, 0, sizeof(tm));
   CUtensorMap& tmA = tm.a;
   CUtensorMap& tmB = tm.b;
   if (!a->a_mn_major) {
-    if (make_tmap(&tmA, a->A, a->K, a->M, a->lda, BK, BM)) return 1;
+    if (make_tmap(&tmA, a->A, a->K, a->M, a->lda, BK, quad == 1 ? BM / 2 : BM)) return 1;
   } else {
     if (make_tmap(&tmA, a->A, a->M, a->K, a->lda, 64, BK)) return 1;
   }
   if (!a->b_mn_major) {
-    if (make_tmap(&tmB, a->B, a->K, a->N, a->ldb, BK, pair ? bn / 2 : bn)) return 1;
+    if (make_tmap(&tmB, a->B, a->K, a->N, a->ldb, BK, pair ? (quad == 2 ? bn / 4 : bn / 2) : bn)) return 1;
   } else {
     if (make_tmap(&tmB, a->B, a->N, a->K, a->ldb, 64, BK)) return 1;
   }
 
-  GemmShape sh{a->M, a->N, a->K, num_m_eff, num_n, splits, kblocks};
+  GemmShape sh{a->M, a->N, a->K, num_m_eff, num_n, splits, kblocks, group_m, quad};
   EpiParams ep;
   ep.out_f32 = a->out_f32, ep.ldo_f32 = a->ldo_f32;
   ep.out_bf16 = reinterpret_cast<__nv_bfloat16*>(a->out_bf16), ep.ldo_bf16 = a->ldo_bf16;
@@ -1666,8 +1856,9 @@ extern "C" int jm_gemm(const jm_gemm_args* a, void* stream_) {
   JM_CHECK(!a->colsum || (a->act != 1 && a->act != 3), "jm_gemm: colsum is not defined for the GELU-forward epilogue");
 
   const long total = static_cast<long>(num_m_eff) * num_n * splits;
-  const int grid = pair ? 2 * static_cast<int>(total < sms / 2 ? total : sms / 2)
-                        : static_cast<int>(total < sms ? total : sms);
+  const int grid = quad ? 4 * static_cast<int>(total / 2 < quad_slots ? total / 2 : quad_slots)
+                   : pair ? 2 * static_cast<int>(total < sms / 2 ? total : sms / 2)
+                          : static_cast<int>(total < sms ? total : sms);
   int epi = EPI_GENERIC;
   const bool only_bf16 = ep.out_bf16 && !ep.out_f32 && !ep.out2_bf16;
   const bool only_f32 = ep.out_f32 && !ep.out_bf16 && !ep.out2_bf16;
@@ -1704,7 +1895,18 @@ extern "C" int jm_gemm(const jm_gemm_args* a, void* stream_) {
   }
   JM_CHECK(!ep.row_scale || (epi == EPI_F32 && ep.tma_store),
            "jm_gemm: row_scale is built for the f32 output epilogue (out_f32 only, no pe / row mask / col_scale)");
-  if (pair) return dispatch_pair(amn, bmn, epi, tm, sh, ep, grid, stream);
+  if (pair) {
+    // K <= 512 with A K-major: B resident in shared memory.  The tile order is n fastest, so with a number of pairs
+    // that is a multiple of the column-tile count every pair keeps its column tile (B is loaded once per CTA) while
+    // the pairs of one tile row run side by side (A is read from HBM once).
+    static const int auto_bres = env_int("JM_GEMM_BRES", 1);  // process-wide, initialised once (thread-safe)
+    const bool bres = (auto_bres || a->cta_pair == 5) && !quad && !amn && splits == 1 && kblocks <= Gemm2Cfg<EPI_BF16, true>::RES_KB &&
+                      a->cta_pair != 2 && num_n <= sms / 2 && total >= sms / 2 &&
+                      (epi == EPI_BF16 || epi == EPI_GELU_FWD || epi == EPI_GELU_BWD || epi == EPI_F32) && ep.tma_store;
+    int g = grid;
+    if (bres && a->cta_pair != 5) g = 2 * ((sms / 2) / num_n) * num_n;  // (5: test hook, column tiles change)
+    return dispatch_pair(amn, bmn, epi, tm, sh, ep, g, stream, bres);
+  }
   if (bn == 256) return dispatch_major<256>(amn, bmn, epi, tm, sh, ep, grid, stream);
   if (bn == 128) return dispatch_major<128>(amn, bmn, epi, tm, sh, ep, grid, stream);
   return dispatch_major<64>(amn, bmn, epi, tm, sh, ep, grid, stream);

@@ -519,6 +519,55 @@ def test_gemm_cta_pair_kernel(ops, M, N, K, a_mn, b_mn):
 
 
 
+@pytest.mark.parametrize("variant", [1, 2, 4, 5])
+@pytest.mark.parametrize("M,N,K,b_mn", [(10100, 520, 504, True), (20480, 1024, 512, False), (9000, 768, 136, True)])
+def test_gemm_pair_kernel_variants(ops, M, N, K, b_mn, variant):
+    """The CTA-pair kernel's variants on problems with more tiles than CTA pairs: plain (2), automatic (1: K <= 512
+    keeps B resident in shared memory), two pairs per cluster sharing an operand by TMA multicast (4), resident B with
+    column-tile changes (5) -- bf16, f32 + bias + residual, GELU forward / backward epilogues against torch."""
+    g = torch.Generator(device="cuda").manual_seed(M + N + K)
+    A = torch.randn(M, K, generator=g, device="cuda").to(BF16)
+    W = (torch.randn((K, N) if b_mn else (N, K), generator=g, device="cuda") * 0.2).to(BF16)
+    bias = torch.randn(N, generator=g, device="cuda")
+    pre = A.float() @ (W.float() if b_mn else W.float().t())
+    kw = dict(b_mn=b_mn, cta_pair=variant)
+    out = torch.empty(M, N, dtype=BF16, device="cuda")
+    ops.gemm(A, W, M, N, K, out_bf16=out, bias=bias, **kw)
+    assert torch.allclose(out.float(), pre + bias, rtol=2 ** -7, atol=2e-3)
+    res = torch.randn(M, N, generator=g, device="cuda")
+    o32 = torch.empty(M, N, device="cuda")
+    ops.gemm(A, W, M, N, K, out_f32=o32, bias=bias, residual=res, **kw)
+    assert torch.allclose(o32, pre + bias + res, rtol=1e-4, atol=2e-3)
+    dsave = torch.empty(M, N, dtype=BF16, device="cuda")
+    gl = torch.empty(M, N, dtype=BF16, device="cuda")
+    ops.gemm(A, W, M, N, K, out_bf16=dsave, out2_bf16=gl, bias=bias, act=3, **kw)
+    pp = (pre + bias).cpu().requires_grad_(True)
+    O.gelu_tanh(pp).sum().backward()
+    assert torch.allclose(dsave.float(), pp.grad.cuda(), rtol=2 ** -7, atol=3e-3)
+    assert torch.allclose(gl.float(), O.gelu_tanh(pp.detach()).cuda(), rtol=2 ** -7, atol=2e-3)
+    dH = torch.empty(M, N, dtype=BF16, device="cuda")
+    cs = torch.zeros(N, device="cuda")
+    ops.gemm(A, W, M, N, K, out_bf16=dH, aux=dsave, act=4, colsum=cs, **kw)
+    ref = pre * dsave.float()
+    assert torch.allclose(dH.float(), ref, rtol=2 ** -6, atol=2e-3)
+    assert torch.allclose(cs, ref.sum(0), rtol=1e-2, atol=0.5)
+    # twice in a row into the same output: the second launch must not depend on shared-memory leftovers
+    ops.gemm(A, W, M, N, K, out_bf16=out, bias=bias, **kw)
+    assert torch.allclose(out.float(), pre + bias, rtol=2 ** -7, atol=2e-3)
+
+
+@pytest.mark.parametrize("M,N,K,a_mn", [(768, 1024, 40000, True), (1024, 768, 40000, True)])
+def test_gemm_weight_gradient_quad_clusters(ops, M, N, K, a_mn):
+    """dW += X^T dY in 4-CTA clusters (cta_pair=4): pairs neighbouring in n share A, in m share B."""
+    g = torch.Generator(device="cuda").manual_seed(M + K)
+    X = torch.randn(K, M, generator=g, device="cuda").to(BF16)
+    dY = (torch.randn(K, N, generator=g, device="cuda") * 0.1).to(BF16)
+    out = torch.ones(M, N, device="cuda")
+    ops.gemm(X, dY, M, N, K, a_mn=True, b_mn=True, out_f32=out, accumulate=True, cta_pair=4)
+    ref = X.float().t() @ dY.float() + 1
+    assert (out - ref).abs().max().item() <= 2e-5 * ref.abs().max().item() * math.sqrt(K)
+
+
 @pytest.mark.parametrize("bn,pair", [(64, -1), (128, -1), (256, -1), (256, 1)])
 @pytest.mark.parametrize("M,N,K", [(700, 328, 136), (1300, 512, 64)])
 def test_gemm_bf16_epilogues_every_tile_shape(ops, M, N, K, bn, pair):
