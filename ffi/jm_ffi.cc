@@ -144,6 +144,63 @@ XLA_FFI_DEFINE_HANDLER_SYMBOL(JmDense, Dense,
                               ffi::Ffi::Bind().Ctx<Stream>().Arg<BF16>().Arg<BF16>().Arg<F32>().Attr<int32_t>("act")
                                   .Attr<float>("col_scale").Attr<int32_t>("col_scale_n").Ret<BF16>().Ret<BF16>());
 
+// ---- pixel head with the loss in its epilogue, on the masked rows only (src/pretraining.py:110-120): targets of the
+// masked patches, dec_norm gathered through row_map, then act = 5 of jm_gemm and the ordered sum of its row partials
+static ffi::Error MaskedTargets(cudaStream_t s, U8 images, S32 ids, int32_t patch_size, int32_t num_cls, int32_t norm_pix,
+                                RU8 targets, RF32 stats, RS32 row_map) {
+  const auto d = images.dimensions();  // [B, 3, S, S]
+  return Rc(jm_masked_targets(images.typed_data(), static_cast<int>(d[0]), static_cast<int>(d[3]), patch_size,
+                              ids.typed_data(), static_cast<int>(ids.element_count()), num_cls, norm_pix,
+                              targets->typed_data(), last_dim(targets->dimensions()), stats->typed_data(),
+                              row_map->typed_data(), s));
+}
+XLA_FFI_DEFINE_HANDLER_SYMBOL(JmMaskedTargets, MaskedTargets,
+                              ffi::Ffi::Bind().Ctx<Stream>().Arg<U8>().Arg<S32>().Attr<int32_t>("patch_size")
+                                  .Attr<int32_t>("num_cls").Attr<int32_t>("norm_pix").Ret<U8>().Ret<F32>().Ret<S32>());
+
+static ffi::Error LayerNormFwdRows(cudaStream_t s, F32 x, S32 row_map, F32 gamma, F32 beta, float eps, RBF16 y, RF32 mean,
+                                   RF32 rstd) {
+  const long dim = last_dim(x.dimensions());
+  return Rc(jm_layernorm_fwd_rows(x.typed_data(), dim, row_map.typed_data(), static_cast<int>(row_map.element_count()),
+                                  static_cast<int>(dim), gamma.typed_data(), beta.typed_data(), eps, bf(y), dim,
+                                  mean->typed_data(), rstd->typed_data(), s));
+}
+XLA_FFI_DEFINE_HANDLER_SYMBOL(JmLayerNormFwdRows, LayerNormFwdRows,
+                              ffi::Ffi::Bind().Ctx<Stream>().Arg<F32>().Arg<S32>().Arg<F32>().Arg<F32>().Attr<float>("eps")
+                                  .Ret<BF16>().Ret<F32>().Ret<F32>());
+
+static ffi::Error LayerNormBwdRows(cudaStream_t s, BF16 dy, F32 x, S32 row_map, F32 mean, F32 rstd, F32 gamma,
+                                   F32 dgamma_in, F32 dbeta_in, RF32 dx, RBF16 dx16, RF32 dgamma, RF32 dbeta, RU8 scratch) {
+  (void)dgamma_in, (void)dbeta_in;  // aliased to the results by input_output_aliases
+  const long dim = last_dim(x.dimensions());
+  return Rc(jm_layernorm_bwd_rows(bf(dy), dim, x.typed_data(), dim, row_map.typed_data(), mean.typed_data(),
+                                  rstd.typed_data(), gamma.typed_data(), static_cast<int>(row_map.element_count()),
+                                  static_cast<int>(dim), static_cast<long>(x.element_count() / dim), dx->typed_data(), dim,
+                                  bf(dx16), dim, dgamma->typed_data(), dbeta->typed_data(), nullptr,
+                                  scratch->untyped_data(), scratch->size_bytes(), s));
+}
+XLA_FFI_DEFINE_HANDLER_SYMBOL(JmLayerNormBwdRows, LayerNormBwdRows,
+                              ffi::Ffi::Bind().Ctx<Stream>().Arg<BF16>().Arg<F32>().Arg<S32>().Arg<F32>().Arg<F32>()
+                                  .Arg<F32>().Arg<F32>().Arg<F32>().Ret<F32>().Ret<BF16>().Ret<F32>().Ret<F32>().Ret<U8>());
+
+static ffi::Error HeadLoss(cudaStream_t s, BF16 a, BF16 w, F32 bias, U8 targets, F32 stats, int32_t norm_pix,
+                           float loss_scale, float mean_scale, RF32 loss, RBF16 dpred, RF32 row_loss, RU8 scratch) {
+  jm_gemm_args g = {};
+  g.K = static_cast<int>(a.dimensions().back()), g.M = static_cast<int>(a.element_count() / g.K);
+  g.N = static_cast<int>(w.dimensions().back());
+  g.A = bf(a), g.lda = g.K, g.B = bf(w), g.ldb = g.N, g.b_mn_major = 1, g.bias = bias.typed_data(), g.act = 5;
+  g.out_bf16 = bf(dpred), g.ldo_bf16 = last_dim(dpred->dimensions());
+  g.loss_target = targets.typed_data(), g.ld_target = last_dim(targets.dimensions());
+  g.loss_stats = norm_pix ? stats.typed_data() : nullptr, g.row_loss = row_loss->typed_data(), g.loss_scale = loss_scale;
+  if (int rc = jm_gemm(&g, s)) return Rc(rc);
+  return Rc(jm_row_loss_finalize(row_loss->typed_data(), static_cast<long>(row_loss->element_count()), mean_scale,
+                                 loss->typed_data(), scratch->untyped_data(), scratch->size_bytes(), s));
+}
+XLA_FFI_DEFINE_HANDLER_SYMBOL(JmHeadLoss, HeadLoss,
+                              ffi::Ffi::Bind().Ctx<Stream>().Arg<BF16>().Arg<BF16>().Arg<F32>().Arg<U8>().Arg<F32>()
+                                  .Attr<int32_t>("norm_pix").Attr<float>("loss_scale").Attr<float>("mean_scale")
+                                  .Ret<F32>().Ret<BF16>().Ret<F32>().Ret<U8>());
+
 // ---- Dense forward into the f32 residual stream: out = A @ W + bias + residual (src/modeling.py:165-166,192,201)
 static ffi::Error DenseResidual(cudaStream_t s, BF16 a, BF16 w, F32 bias, F32 residual, RF32 out) {
   jm_gemm_args g = {};

@@ -12,7 +12,8 @@ import os
 
 TARGETS = [
     "JmMaskSort", "JmIndexSequence", "JmPatchify", "JmExtractPatches", "JmPatchLoss", "JmPatchMseLoss", "JmLayerNormFwd",
-    "JmLayerNormBwd", "JmDense", "JmDenseResidual", "JmDenseBwd", "JmAttentionFwd", "JmAttentionBwd", "JmFillCls",
+    "JmLayerNormBwd", "JmDense", "JmMaskedTargets", "JmLayerNormFwdRows", "JmLayerNormBwdRows", "JmHeadLoss",
+    "JmDenseResidual", "JmDenseBwd", "JmAttentionFwd", "JmAttentionBwd", "JmFillCls",
     "JmUnshuffleFwd", "JmUnshuffleBwd", "JmColsum", "JmAdamW", "JmClipByGlobalNorm", "JmCastBf16", "JmSoftmaxCe",
 ]
 

@@ -169,6 +169,32 @@ int jm_layernorm_bwd_lowp(const jm_bf16* dy, long lddy, const float* x, long ldx
                           long lddx, jm_bf16* dx_bf16, long lddxb, float* dgamma, float* dbeta, float* dcol,
                           void* workspace, size_t workspace_bytes, void* stream);
 
+/* LayerNorm over a subset of rows: output row r (compact) is LayerNorm(x[row_map[r], :]); mean / rstd are compact too.
+ * jm_layernorm_bwd_rows is its backward: dy, mean, rstd compact [rows], x and dx / dx_bf16 scattered through row_map;
+ * dx / dx_bf16 [total_rows, dim] are zeroed first (rows outside row_map get no gradient through this LayerNorm).
+ * dim <= 512.  Used for decoder_model/dec_norm on the masked rows only (src/modeling.py:296, src/pretraining.py:110). */
+int jm_layernorm_fwd_rows(const float* x, long ldx, const int32_t* row_map, int rows, int dim, const float* gamma,
+                          const float* beta, float eps, jm_bf16* y_bf16, long ldy, float* mean, float* rstd,
+                          void* stream);
+int jm_layernorm_bwd_rows(const jm_bf16* dy, long lddy, const float* x, long ldx, const int32_t* row_map,
+                          const float* mean, const float* rstd, const float* gamma, int rows, int dim, long total_rows,
+                          float* dx, long lddx, jm_bf16* dx_bf16, long lddxb, float* dgamma, float* dbeta, float* dcol,
+                          void* workspace, size_t workspace_bytes, void* stream);
+
+/* Targets of the selected (masked) patches for the loss epilogue of jm_gemm (act = 5): targets [batch * n_sel, ldt]
+ * uint8 = the patch's pixels in extract_patches order (src/utils_mae.py:67-76), stats [batch * n_sel, 2] = mean and
+ * 1 / sqrt(biased var + 1e-6) of the normalised patch (written when norm_pix; src/pretraining.py:115-118), row_map
+ * (optional) [batch * n_sel] = image * (num_cls + N) + num_cls + ids[k], the decoder row of each target.
+ * ids [n_sel] are shared by the batch (src/utils_mae.py:88-96). */
+int jm_masked_targets(const uint8_t* images, int batch, int image_size, int patch_size, const int32_t* ids, int n_sel,
+                      int num_cls, int norm_pix, uint8_t* targets, long ldt, float* stats, int32_t* row_map,
+                      void* stream);
+
+/* loss[0] = scale * sum(row_loss[0 .. count)), summed in a fixed order.  workspace: jm_row_loss_workspace() bytes. */
+size_t jm_row_loss_workspace(void);
+int jm_row_loss_finalize(const float* row_loss, long count, float scale, float* loss, void* workspace,
+                         size_t workspace_bytes, void* stream);
+
 /* ---------------------------------------------------------------- GEMM
  * D = epilogue(A * B), bf16 operands, f32 accumulation in tensor memory
  * (tcgen05.mma fed by TMA).  Replaces every Dense / DenseGeneral / Conv contraction
@@ -217,6 +243,13 @@ typedef struct jm_gemm_args {
   /* optional per-image scale of the branch: out_f32 = row_scale[row / row_scale_period] * (acc + bias) + residual
    * (DropPath keep-mask / (1 - p) of a residual branch, src/modeling.py:157,181-183,192,199,201); f32 output only */
   const float* row_scale; int row_scale_period;
+  /* act = 5, the loss epilogue of the pixel head (src/pretraining.py:110-120, src/utils_mae.py:51-64): with
+   * d = acc + bias - target, out_bf16 (optional) = d * loss_scale and row_loss[row, col / 16] = sum of d^2 over the 16
+   * columns (row_loss is [M, ceil(N / 16)] f32, every entry written once; jm_row_loss_finalize sums it).  target =
+   * normalised pixel of byte loss_target[row, col] (channel col % 3, ImageNet statistics), then (t - stats[row, 0]) *
+   * stats[row, 1] when loss_stats != NULL (norm_pix_loss).  jm_masked_targets produces loss_target / loss_stats.
+   * A K-major, B MN-major, no other epilogue option; ld_target a multiple of 16 >= N, ldo_bf16 >= N rounded up to 8. */
+  const uint8_t* loss_target; long ld_target; const float* loss_stats; float* row_loss; float loss_scale;
 } jm_gemm_args;
 int jm_gemm(const jm_gemm_args* args, void* stream);
 

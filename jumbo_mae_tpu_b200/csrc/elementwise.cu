@@ -130,6 +130,78 @@ patchify_kernel(const uint8_t* __restrict__ images, int S, int p, const int* __r
   }
 }
 
+// Targets of the masked patches for the loss epilogue of the pixel-head GEMM (src/pretraining.py:113-118): the raw
+// bytes of each selected patch in patch-vector order (pixel-major, channel fastest: extract_patches'), one compact row
+// per (image, selected patch), plus -- for norm_pix_loss -- the patch's mean and 1/sqrt(biased var + 1e-6) over its
+// normalised pixels, and the decoder row each target belongs to.  One warp per row.
+__global__ void __launch_bounds__(256)
+masked_targets_kernel(const uint8_t* __restrict__ images, int S, int p, const int* __restrict__ ids, int n_sel, int J,
+                      int batch, int norm_pix, uint8_t* __restrict__ tgt, long ldt, float* __restrict__ stats,
+                      int* __restrict__ row_map) {
+  __shared__ __align__(16) uint8_t spix_all[8][2048];
+  __shared__ float lut[768];
+  fill_norm_lut(lut);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  uint8_t* spix = spix_all[warp];
+  const int pp = p * p, P = pp * 3, g = S / p, N = g * g;
+  const long rows = static_cast<long>(batch) * n_sel;
+  for (long row = static_cast<long>(blockIdx.x) * 8 + warp; row < rows; row += static_cast<long>(gridDim.x) * 8) {
+    const int b = static_cast<int>(row / n_sel), k = static_cast<int>(row - static_cast<long>(b) * n_sel);
+    const int patch = ids[k];
+    const int gy = patch / g, gx = patch - gy * g;
+    if (row_map && lane == 0) row_map[row] = b * (J + N) + J + patch;
+    __syncwarp();
+    stage_patch(spix, images + static_cast<long>(b) * 3 * S * S, S, p, gy, gx, lane);
+    __syncwarp();
+    uint8_t* dst = tgt + row * ldt;
+    for (int e0 = lane * 4; e0 < P; e0 += 128) {  // P and ldt are multiples of 4 (checked)
+      uint32_t w = 0;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int e = e0 + j, pix = e / 3, c = e - pix * 3;
+        w |= static_cast<uint32_t>(spix[c * pp + pix]) << (8 * j);
+      }
+      *reinterpret_cast<uint32_t*>(dst + e0) = w;
+    }
+    if (norm_pix) {  // same two passes, in the same order, as patch_loss_kernel
+      auto target = [&](int e) {
+        const int pix = e / 3, c = e - pix * 3;
+        return lut[c * 256 + spix[c * pp + pix]];
+      };
+      float s_ = 0.f;
+      for (int e = lane; e < P; e += 32) s_ += target(e);
+      const float mean = warp_sum(s_) / P;
+      float ss = 0.f;
+      for (int e = lane; e < P; e += 32) {
+        const float d = target(e) - mean;
+        ss += d * d;
+      }
+      const float inv = 1.0f / sqrtf(warp_sum(ss) / P + 1e-6f);
+      if (lane == 0) stats[2 * row] = mean, stats[2 * row + 1] = inv;
+    }
+  }
+}
+
+// Sum of a [rows, parts] matrix of per-row loss partials, in a fixed order: per-block partial sums, then one block.
+__global__ void __launch_bounds__(256) row_loss_partial_kernel(const float* __restrict__ row_loss, long total,
+                                                               float* __restrict__ partial) {
+  __shared__ float red[32];
+  const long per = (total + gridDim.x - 1) / gridDim.x;
+  const long lo = per * blockIdx.x, hi = lo + per < total ? lo + per : total;
+  float s_ = 0.f;
+  for (long i = lo + threadIdx.x; i < hi; i += blockDim.x) s_ += row_loss[i];
+  const float t = block_sum(s_, red);
+  if (threadIdx.x == 0) partial[blockIdx.x] = t;
+}
+__global__ void __launch_bounds__(256) row_loss_final_kernel(const float* __restrict__ partial, int n, float scale,
+                                                             float* __restrict__ loss) {
+  __shared__ float red[32];
+  float s_ = 0.f;
+  for (int i = threadIdx.x; i < n; i += blockDim.x) s_ += partial[i];
+  const float t = block_sum(s_, red);
+  if (threadIdx.x == 0) loss[0] = t * scale;
+}
+
 // Fine-tune input path: patchify with Mixup / CutMix applied to the NORMALISED pixels
 // (src/finetuning.py:87-88,95; src/utils.py:67-90), one warp per output row as above, both source patches staged.
 //   mode 1 (Mixup.apply_mixup):  v = ratio * a + (1 - ratio) * b      (separate roundings, as the f32 array ops)
@@ -391,13 +463,14 @@ constexpr int kLnWarps = 8;
 __global__ void __launch_bounds__(kLnWarps * 32)
 layernorm_fwd_kernel(const float* __restrict__ x, long ldx, int rows, int D, const float* __restrict__ gamma,
                      const float* __restrict__ beta, float eps, __nv_bfloat16* __restrict__ yb, long ldy,
-                     float* __restrict__ yf, long ldyf, float* __restrict__ mean_out, float* __restrict__ rstd_out) {
+                     float* __restrict__ yf, long ldyf, float* __restrict__ mean_out, float* __restrict__ rstd_out,
+                     const int* __restrict__ row_map) {
   pdl_wait();  // programmatic dependent launch: nothing above touches global memory
   pdl_launch_dependents();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const long row = static_cast<long>(blockIdx.x) * kLnWarps + warp;
   if (row >= rows) return;
-  const float* xr = x + row * ldx;
+  const float* xr = x + (row_map ? static_cast<long>(row_map[row]) : row) * ldx;  // gather: output rows stay compact
   float s = 0.f, ss = 0.f;
   for (int c = lane * 4; c < D; c += 128) {
     const float4 v = *reinterpret_cast<const float4*>(xr + c);
@@ -635,7 +708,7 @@ layernorm_bwd_pipe_kernel(const __nv_bfloat16* __restrict__ dy, long lddy, const
                          const float* __restrict__ gamma, int rows, int D, const float* __restrict__ dres,
                          long lddres, float* __restrict__ dx, long lddx, __nv_bfloat16* __restrict__ dxb, long lddxb,
                          int row_period, int row_skip, float* __restrict__ ws, int want_dcol, int dcol_period,
-                         int dcol_skip, LnDirect direct, int res_bf16) {
+                         int dcol_skip, LnDirect direct, int res_bf16, const int* __restrict__ row_map) {
   pdl_wait();  // programmatic dependent launch: nothing above touches global memory
   pdl_launch_dependents();
   extern __shared__ __align__(16) float s_acc[];  // [warps][3][D]: dgamma, dbeta, column sums of dx
@@ -650,6 +723,7 @@ layernorm_bwd_pipe_kernel(const __nv_bfloat16* __restrict__ dy, long lddy, const
     float4 res[NV], x[NV];
     uint2 dy[NV];
     float mu, rs;
+    long xrow;  // row of x / dx (row_map: dy, mean and rstd are compact, x and dx are scattered)
   };
   const long stride = static_cast<long>(gridDim.x) * kLnBwdWarps;
   auto next_valid = [&](long r) {
@@ -658,6 +732,7 @@ layernorm_bwd_pipe_kernel(const __nv_bfloat16* __restrict__ dy, long lddy, const
   };
   auto load_row = [&](long r, Raw& w) {
     w.mu = mean[r], w.rs = rstd[r];
+    w.xrow = row_map ? static_cast<long>(row_map[r]) : r;
 #pragma unroll
     for (int k = 0; k < NV; ++k) {
       const int c = lane * 4 + k * 128;
@@ -675,7 +750,7 @@ layernorm_bwd_pipe_kernel(const __nv_bfloat16* __restrict__ dy, long lddy, const
           }
         }
         w.dy[k] = *reinterpret_cast<const uint2*>(dy + r * lddy + c);
-        w.x[k] = *reinterpret_cast<const float4*>(x + r * ldx + c);
+        w.x[k] = *reinterpret_cast<const float4*>(x + w.xrow * ldx + c);
       }
     }
   };
@@ -734,10 +809,10 @@ layernorm_bwd_pipe_kernel(const __nv_bfloat16* __restrict__ dy, long lddy, const
 #pragma unroll
         for (int j = 0; j < 4; ++j) o[j] = rs * (d[k][j] - c1 - xh[k][j] * c2);
         o[0] += rres[k].x, o[1] += rres[k].y, o[2] += rres[k].z, o[3] += rres[k].w;
-        if (dx) *reinterpret_cast<float4*>(dx + row * lddx + c) = make_float4(o[0], o[1], o[2], o[3]);
+        if (dx) *reinterpret_cast<float4*>(dx + cur.xrow * lddx + c) = make_float4(o[0], o[1], o[2], o[3]);
         if (dxb) {
           uint2 w = {pack_bf16(o[0], o[1]), pack_bf16(o[2], o[3])};
-          *reinterpret_cast<uint2*>(dxb + row * lddxb + c) = w;
+          *reinterpret_cast<uint2*>(dxb + cur.xrow * lddxb + c) = w;
         }
         if (col_row) {
           float4 ac = *reinterpret_cast<float4*>(my + 2 * D + c);
@@ -1155,7 +1230,21 @@ extern "C" int jm_layernorm_fwd(const float* x, long ldx, int rows, int dim, con
   const int grid = (rows + kLnWarps - 1) / kLnWarps;
   JM_LAUNCH_PDL(layernorm_fwd_kernel, grid, kLnWarps * 32, 0, STREAM, x, ldx, rows, dim, gamma, beta, eps,
                                                            reinterpret_cast<__nv_bfloat16*>(y_bf16), ldy, y_f32, ldyf,
-                                                           mean, rstd);
+                                                           mean, rstd, static_cast<const int*>(nullptr));
+  JM_AFTER_LAUNCH();
+  return 0;
+}
+
+extern "C" int jm_layernorm_fwd_rows(const float* x, long ldx, const int32_t* row_map, int rows, int dim,
+                                     const float* gamma, const float* beta, float eps, jm_bf16* y_bf16, long ldy,
+                                     float* mean, float* rstd, void* stream) {
+  JM_CHECK(x && row_map && y_bf16 && gamma && beta, "jm_layernorm_fwd_rows: null argument");
+  JM_CHECK(dim % 4 == 0 && ldx % 4 == 0 && ldy % 4 == 0, "jm_layernorm_fwd_rows: dim/ld must be multiples of 4");
+  if (rows == 0) return 0;
+  const int grid = (rows + kLnWarps - 1) / kLnWarps;
+  JM_LAUNCH_PDL(layernorm_fwd_kernel, grid, kLnWarps * 32, 0, STREAM, x, ldx, rows, dim, gamma, beta, eps,
+                reinterpret_cast<__nv_bfloat16*>(y_bf16), ldy, static_cast<float*>(nullptr), 0L, mean, rstd,
+                static_cast<const int*>(row_map));
   JM_AFTER_LAUNCH();
   return 0;
 }
@@ -1174,8 +1263,10 @@ static int layernorm_bwd_impl(const jm_bf16* dy, long lddy, const float* x, long
                               const float* rstd, const float* gamma, int rows, int dim, const float* dres,
                               long lddres, int res_bf16, float* dx, long lddx, jm_bf16* dx_bf16, long lddxb,
                               int row_period, int row_skip, float* dgamma, float* dbeta, float* dcol, int dcol_period,
-                              int dcol_skip, void* workspace, size_t workspace_bytes, void* stream) {
+                              int dcol_skip, void* workspace, size_t workspace_bytes, void* stream,
+                              const int32_t* row_map = nullptr) {
   JM_CHECK(dim % 4 == 0 && ldx % 4 == 0 && lddy % 4 == 0, "jm_layernorm_bwd: dim/ld must be multiples of 4");
+  JM_CHECK(!row_map || dim <= 512, "jm_layernorm_bwd_rows: the scattered variant is built for dim <= 512");
   JM_CHECK(!res_bf16 || (dim <= 512 && lddres % 4 == 0),
            "jm_layernorm_bwd_lowp: the bf16 residual-gradient input is built for dim <= 512");
   JM_CHECK(dim * 3 * sizeof(float) <= 96 * 1024, "jm_layernorm_bwd: dim %d too large", dim);
@@ -1203,11 +1294,11 @@ static int layernorm_bwd_impl(const jm_bf16* dy, long lddy, const float* x, long
               ((reinterpret_cast<uintptr_t>(dgamma) | reinterpret_cast<uintptr_t>(dbeta) |
                 reinterpret_cast<uintptr_t>(dcol)) & 15) == 0;
 #define JM_LN_BWD_ARGS_D JM_LN_BWD_ARGS, direct
-  if (dim <= 128) JM_LAUNCH_PDL(layernorm_bwd_pipe_kernel<1>, grid, tr, smem_reg, STREAM, JM_LN_BWD_ARGS_D, res_bf16);
-  else if (dim <= 256) JM_LAUNCH_PDL(layernorm_bwd_pipe_kernel<2>, grid, tr, smem_reg, STREAM, JM_LN_BWD_ARGS_D, res_bf16);
-  else if (dim <= 512) JM_LAUNCH_PDL(layernorm_bwd_pipe_kernel<4>, grid, tr, smem_reg, STREAM, JM_LN_BWD_ARGS_D, res_bf16);
+  if (dim <= 128) JM_LAUNCH_PDL(layernorm_bwd_pipe_kernel<1>, grid, tr, smem_reg, STREAM, JM_LN_BWD_ARGS_D, res_bf16, static_cast<const int*>(row_map));
+  else if (dim <= 256) JM_LAUNCH_PDL(layernorm_bwd_pipe_kernel<2>, grid, tr, smem_reg, STREAM, JM_LN_BWD_ARGS_D, res_bf16, static_cast<const int*>(row_map));
+  else if (dim <= 512) JM_LAUNCH_PDL(layernorm_bwd_pipe_kernel<4>, grid, tr, smem_reg, STREAM, JM_LN_BWD_ARGS_D, res_bf16, static_cast<const int*>(row_map));
 #ifdef JM_LN_PIPE6
-  else if (dim <= 768) JM_LAUNCH_PDL(layernorm_bwd_pipe_kernel<6>, grid, tr, smem_reg, STREAM, JM_LN_BWD_ARGS_D, 0);
+  else if (dim <= 768) JM_LAUNCH_PDL(layernorm_bwd_pipe_kernel<6>, grid, tr, smem_reg, STREAM, JM_LN_BWD_ARGS_D, 0, static_cast<const int*>(nullptr));
 #else
   else if (dim <= 768) JM_LAUNCH_PDL(layernorm_bwd_reg_kernel<6>, grid, tr, smem_reg, STREAM, JM_LN_BWD_ARGS_D);
 #endif
@@ -1250,6 +1341,51 @@ extern "C" int jm_layernorm_bwd_lowp(const jm_bf16* dy, long lddy, const float* 
   return layernorm_bwd_impl(dy, lddy, x, ldx, mean, rstd, gamma, rows, dim, reinterpret_cast<const float*>(dres_bf16),
                             lddres, dres_bf16 != nullptr ? 1 : 0, dx, lddx, dx_bf16, lddxb, 0, 0, dgamma, dbeta, dcol,
                             0, 0, workspace, workspace_bytes, stream);
+}
+
+extern "C" int jm_layernorm_bwd_rows(const jm_bf16* dy, long lddy, const float* x, long ldx, const int32_t* row_map,
+                                     const float* mean, const float* rstd, const float* gamma, int rows, int dim,
+                                     long total_rows, float* dx, long lddx, jm_bf16* dx_bf16, long lddxb, float* dgamma,
+                                     float* dbeta, float* dcol, void* workspace, size_t workspace_bytes, void* stream) {
+  JM_CHECK(row_map && (dx || dx_bf16), "jm_layernorm_bwd_rows: null argument");
+  // rows that are not in row_map receive no gradient through this LayerNorm: zero first, then scatter
+  if (dx) JM_CUDA(cudaMemset2DAsync(dx, lddx * sizeof(float), 0, dim * sizeof(float), total_rows, STREAM));
+  if (dx_bf16)
+    JM_CUDA(cudaMemset2DAsync(dx_bf16, lddxb * sizeof(jm_bf16), 0, dim * sizeof(jm_bf16), total_rows, STREAM));
+  return layernorm_bwd_impl(dy, lddy, x, ldx, mean, rstd, gamma, rows, dim, nullptr, 0, 0, dx, lddx, dx_bf16, lddxb, 0, 0,
+                            dgamma, dbeta, dcol, 0, 0, workspace, workspace_bytes, stream, row_map);
+}
+
+extern "C" int jm_masked_targets(const uint8_t* images, int batch, int image_size, int patch_size, const int32_t* ids,
+                                 int n_sel, int num_cls, int norm_pix, uint8_t* targets, long ldt, float* stats,
+                                 int32_t* row_map, void* stream) {
+  JM_CHECK(images && ids && targets, "jm_masked_targets: null argument");
+  JM_CHECK(image_size % patch_size == 0, "jm_masked_targets: image size must be a multiple of the patch size");
+  const int P = patch_size * patch_size * 3;
+  JM_CHECK(P <= 2048 && P % 4 == 0, "jm_masked_targets: patch dimension %d must be a multiple of 4, at most 2048", P);
+  JM_CHECK(ldt >= P && ldt % 16 == 0 && (reinterpret_cast<uintptr_t>(targets) & 15) == 0,
+           "jm_masked_targets: ldt must be a multiple of 16 bytes, at least the patch dimension");
+  JM_CHECK(!norm_pix || stats, "jm_masked_targets: norm_pix needs stats [batch * n_sel, 2]");
+  if (batch == 0 || n_sel == 0) return 0;
+  const long want = (static_cast<long>(batch) * n_sel + 7) / 8, cap = static_cast<long>(sm_count()) * 16;
+  masked_targets_kernel<<<static_cast<int>(want < cap ? want : cap), 256, 0, STREAM>>>(
+      images, image_size, patch_size, ids, n_sel, num_cls, batch, norm_pix, targets, ldt, stats, row_map);
+  JM_AFTER_LAUNCH();
+  return 0;
+}
+
+extern "C" size_t jm_row_loss_workspace(void) { return 1024 * sizeof(float); }
+
+extern "C" int jm_row_loss_finalize(const float* row_loss, long count, float scale, float* loss, void* workspace,
+                                    size_t workspace_bytes, void* stream) {
+  JM_CHECK(row_loss && loss && count > 0, "jm_row_loss_finalize: null or empty argument");
+  JM_CHECK(workspace && workspace_bytes >= jm_row_loss_workspace(), "jm_row_loss_finalize: workspace too small");
+  const int blocks = static_cast<int>(count / 4096 + 1 < 1024 ? count / 4096 + 1 : 1024);
+  row_loss_partial_kernel<<<blocks, 256, 0, STREAM>>>(row_loss, count, static_cast<float*>(workspace));
+  JM_AFTER_LAUNCH();
+  row_loss_final_kernel<<<1, 256, 0, STREAM>>>(static_cast<const float*>(workspace), blocks, scale, loss);
+  JM_AFTER_LAUNCH();
+  return 0;
 }
 
 extern "C" int jm_fill_cls(float* x, int batch, int T, int J, int dim, const float* cls, void* stream) {

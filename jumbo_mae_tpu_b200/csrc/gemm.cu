@@ -87,6 +87,12 @@ struct EpiParams {
   int tma_store;  // row-register epilogues: write the bf16 outputs with TMA stores (maps o / o2)
   const float* row_scale;  // optional [M / row_scale_period]: (acc + bias) of a row is multiplied by its image's entry
   int row_scale_period;    // before the residual is added (DropPath keep-mask / (1 - p), src/modeling.py:157,181-183)
+  // loss epilogue (act 5): d = acc + bias - target; out_bf16 = d * loss_scale; row_loss[row, col / 16] = sum d^2
+  const uint8_t* loss_target;  // [M, ld] raw pixel bytes in patch-vector order (channel = col % 3)
+  long ld_target;
+  const float* loss_stats;     // optional [M, 2]: norm_pix mean and 1 / sqrt(var + eps) of the row's normalised target
+  float* row_loss;             // [M, ceil(N / 16)]
+  float loss_scale;
 };
 
 template <int BN>
@@ -181,6 +187,7 @@ enum : int {
   EPI_GELU_FWD = 2,  // out_bf16 = h = acc + bias, out2_bf16 = gelu(h)
   EPI_GELU_BWD = 3,  // out_bf16 = acc * gelu'(aux)                             (aux prefetched)
   EPI_GENERIC = 4,
+  EPI_LOSS = 5,      // out_bf16 = (acc + bias - target) * scale, row_loss = per-row partial sums of the squared error
 };
 
 template <int EPI>
@@ -1064,12 +1071,107 @@ __device__ __forceinline__ void epilogue_f32_tma(const EpiParams& ep, const Gemm
   __syncwarp();
 }
 
+// Loss epilogue of the pixel head (act 5; src/pretraining.py:110-120, src/utils_mae.py:51-64): the accumulator row IS
+// the predicted patch, so the squared error against the target patch and its gradient are formed here and the f32
+// prediction never exists in memory.  Thread = row (TMEM layout), 16 columns at a time: 16 target bytes per thread
+// (one 16-byte load from the compact byte targets jm_masked_targets wrote), normalised with one FMA per pixel
+// ((u / 255 - mean_c) / std_c = u * a_c + b_c; channel = column % 3), optional norm_pix; d = acc + bias - t;
+// out_bf16 = d * loss_scale straight from the row registers (32 contiguous bytes per thread), and the 16-column sum
+// of d^2 goes to row_loss[row, col / 16]: every entry is written exactly once, so the loss is a deterministic sum.
+// The pixel head is 0.9 % of the step's FLOPs; nothing here is tuned beyond "no shared-memory round trip".
+template <int BN, int CG>
+__device__ __forceinline__ void epilogue_loss(const EpiParams& ep, const GemmShape& sh, uint64_t* tfull,
+                                              uint64_t* tempty, uint32_t tmem_base, int warp, int lane,
+                                              int total_tiles, int tile0, int tile_step, int m_off) {
+  constexpr int PART_N = BN / 4;
+  constexpr int NC = PART_N / 16;
+  const int e = warp - kEpiWarp0;
+  const int q = warp & 3;
+  const int part = e >> 2;
+  const int tiles_mn = sh.num_m * sh.num_n;
+  const int parts = (sh.N + 15) / 16;
+  // ImageNet statistics of src/pretraining.py:90-91 as one FMA per pixel
+  const float a3[3] = {1.0f / (255.0f * 0.229f), 1.0f / (255.0f * 0.224f), 1.0f / (255.0f * 0.225f)};
+  const float b3[3] = {-0.485f / 0.229f, -0.456f / 0.224f, -0.406f / 0.225f};
+  int iter = 0;
+  for (int t = tile0; t < total_tiles; t += tile_step, ++iter) {
+    const int rem = t % tiles_mn;
+    int m_blk, n_blk;
+    tile_mn(sh, rem, m_blk, n_blk);
+    const int row = m_blk * (BM * CG) + m_off + q * 32 + lane;
+    const int colp = n_blk * BN + part * PART_N;
+    const bool row_ok = row < sh.M;
+    const int acc = iter & 1;
+    const uint32_t acc_phase = (iter >> 1) & 1;
+    float mu = 0.f, inv = 1.f;
+    if (ep.loss_stats != nullptr && row_ok) mu = ep.loss_stats[2 * static_cast<long>(row)], inv = ep.loss_stats[2 * static_cast<long>(row) + 1];
+    // this row's target bytes of the warp's columns, fetched before the accumulator is waited for
+    uint4 tb[NC];
+#pragma unroll
+    for (int c = 0; c < NC; ++c) {
+      const int col0 = colp + 16 * c;
+      tb[c] = make_uint4(0u, 0u, 0u, 0u);
+      if (row_ok && col0 < sh.N)  // (N is a multiple of 4 and ld_target of 16: a ragged last chunk stays inside the row)
+        tb[c] = *reinterpret_cast<const uint4*>(ep.loss_target + static_cast<long>(row) * ep.ld_target + col0);
+    }
+    mbar_wait(&tfull[acc], acc_phase);
+    tc_fence_after();
+    const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * BN + part * PART_N;
+#pragma unroll
+    for (int c = 0; c < NC; ++c) {
+      const int col0 = colp + 16 * c;
+      const bool live = col0 < sh.N;  // warp-uniform
+      uint32_t r[16];
+      if (live) tmem_ld_32x16(t_addr + 16 * c, r);
+      tmem_ld_wait();
+      if (c == NC - 1) {  // accumulator drained: hand the TMEM buffer back to the MMA warp
+        tc_fence_before();
+        if constexpr (CG == 1) mbar_arrive(&tempty[acc]);
+        else mbar_arrive_cluster(mapa_shared(smem_u32(&tempty[acc]), cluster_ctarank() & ~1u));
+      }
+      if (!live) continue;
+      const int ch0 = col0 % 3;
+      const uint32_t words[4] = {tb[c].x, tb[c].y, tb[c].z, tb[c].w};
+      float sq = 0.f;
+      uint32_t o[8];
+#pragma unroll
+      for (int j = 0; j < 16; j += 2) {
+        float d[2];
+#pragma unroll
+        for (int k = 0; k < 2; ++k) {
+          const int jj = j + k;
+          const int col = col0 + jj;
+          int ch = ch0 + (jj % 3);
+          ch = ch >= 3 ? ch - 3 : ch;
+          const float u = static_cast<float>((words[jj >> 2] >> (8 * (jj & 3))) & 0xffu);
+          float tv = fmaf(u, ch == 0 ? a3[0] : (ch == 1 ? a3[1] : a3[2]), ch == 0 ? b3[0] : (ch == 1 ? b3[1] : b3[2]));
+          tv = (tv - mu) * inv;
+          const float bias = (ep.bias != nullptr && col < sh.N) ? __ldg(ep.bias + col) : 0.f;
+          d[k] = col < sh.N ? __uint_as_float(r[jj]) + bias - tv : 0.f;
+          sq = fmaf(d[k], d[k], sq);
+        }
+        o[j >> 1] = pack_bf16(d[0] * ep.loss_scale, d[1] * ep.loss_scale);
+      }
+      if (row_ok) {
+        ep.row_loss[static_cast<long>(row) * parts + (col0 >> 4)] = sq;
+        if (ep.out_bf16 != nullptr) {  // (ldo_bf16 is a multiple of 8 and covers the padded last chunk: checked on the host)
+          uint4* dst = reinterpret_cast<uint4*>(ep.out_bf16 + static_cast<long>(row) * ep.ldo_bf16 + col0);
+          dst[0] = make_uint4(o[0], o[1], o[2], o[3]);
+          if (col0 + 8 < sh.N) dst[1] = make_uint4(o[4], o[5], o[6], o[7]);
+        }
+      }
+    }
+  }
+}
+
 template <int EPI, int BN, int CG, int NBUF>
 __device__ __forceinline__ void run_epilogue(const EpiParams& ep, const GemmShape& sh, const CUtensorMap* tmO,
                                              const CUtensorMap* tmO2, uint8_t* sEpi, uint64_t* rbars,
                                              uint64_t* tfull, uint64_t* tempty, uint32_t tmem_base, int warp,
                                              int lane, int total_tiles, int tile0, int tile_step, int m_off) {
-  if constexpr (EPI == EPI_BF16 || EPI == EPI_GELU_FWD || EPI == EPI_GELU_BWD) {
+  if constexpr (EPI == EPI_LOSS) {
+    epilogue_loss<BN, CG>(ep, sh, tfull, tempty, tmem_base, warp, lane, total_tiles, tile0, tile_step, m_off);
+  } else if constexpr (EPI == EPI_BF16 || EPI == EPI_GELU_FWD || EPI == EPI_GELU_BWD) {
     epilogue_rows<EPI, BN, CG, NBUF>(ep, sh, tmO, tmO2, sEpi, rbars, tfull, tempty, tmem_base, warp, lane, total_tiles, tile0,
                                      tile_step, m_off);
   } else {
@@ -1621,6 +1723,7 @@ static int dispatch_epi2(int epi, const GemmMaps& tm, const GemmShape& sh,
 
 // Pair kernel instantiations: forward (A K-major, B MN-major), input gradient (K, K), weight gradient (MN, MN).
 static int dispatch_pair(bool a_mn, bool b_mn, int epi, const GemmMaps& tm, const GemmShape& sh, const EpiParams& ep, int grid, cudaStream_t stream, bool bres) {
+  if (epi == EPI_LOSS) return launch_gemm2<false, true, EPI_LOSS>(tm, sh, ep, grid, stream);
   if (bres) return b_mn ? dispatch_bres<true>(epi, tm, sh, ep, grid, stream) : dispatch_bres<false>(epi, tm, sh, ep, grid, stream);
   if (!a_mn && !b_mn) return dispatch_epi2<false, false>(epi, tm, sh, ep, grid, stream);
   if (!a_mn && b_mn) return dispatch_epi2<false, true>(epi, tm, sh, ep, grid, stream);
@@ -1642,6 +1745,7 @@ static int dispatch_epi(int epi, const GemmMaps& tm, const GemmShape& sh,
 
 template <int BN>
 static int dispatch_major(bool a_mn, bool b_mn, int epi, const GemmMaps& tm, const GemmShape& sh, const EpiParams& ep, int grid, cudaStream_t stream) {
+  if (epi == EPI_LOSS) return launch_gemm<BN, false, true, EPI_LOSS>(tm, sh, ep, grid, stream);
   if (!a_mn && !b_mn) return dispatch_epi<BN, false, false>(epi, tm, sh, ep, grid, stream);
   if (!a_mn && b_mn) return dispatch_epi<BN, false, true>(epi, tm, sh, ep, grid, stream);
   // transposed-A products are weight gradients: f32 accumulate epilogue (anything else: generic)
@@ -1717,8 +1821,18 @@ extern "C" int jm_gemm(const jm_gemm_args* a, void* stream_) {
   JM_CHECK(a->M > 0 && a->N > 0 && a->K > 0, "jm_gemm: empty problem M=%d N=%d K=%d", a->M, a->N, a->K);
   JM_CHECK(a->N % 4 == 0, "jm_gemm: N must be a multiple of 4 (got %d)", a->N);
   JM_CHECK(a->A && a->B, "jm_gemm: null operand");
-  JM_CHECK(a->out_f32 || a->out_bf16 || a->out2_bf16, "jm_gemm: no output");
-  JM_CHECK(a->act >= 0 && a->act <= 4, "jm_gemm: act must be 0..4");
+  JM_CHECK(a->out_f32 || a->out_bf16 || a->out2_bf16 || a->act == 5, "jm_gemm: no output");
+  JM_CHECK(a->act >= 0 && a->act <= 5, "jm_gemm: act must be 0..5");
+  if (a->act == 5) {
+    JM_CHECK(a->loss_target && a->row_loss && !a->a_mn_major && a->b_mn_major,
+             "jm_gemm: the loss epilogue needs loss_target, row_loss, A K-major and B MN-major");
+    JM_CHECK(a->ld_target % 16 == 0 && a->ld_target >= a->N && (reinterpret_cast<uintptr_t>(a->loss_target) & 15) == 0,
+             "jm_gemm: ld_target must be a multiple of 16 and at least N, loss_target 16-byte aligned");
+    JM_CHECK(!a->out_f32 && !a->out2_bf16 && !a->residual && !a->pe && !a->colsum && !a->aux && !a->row_scale &&
+                 a->row_period == 0 && a->col_scale_n == 0 && !a->accumulate && a->splits <= 1,
+             "jm_gemm: the loss epilogue takes no other epilogue option");
+    JM_CHECK(!a->out_bf16 || a->ldo_bf16 >= (a->N + 7) / 8 * 8, "jm_gemm: ldo_bf16 must cover N rounded up to 8");
+  }
   JM_CHECK((a->act != 2 && a->act != 4) || a->aux, "jm_gemm: act=2/4 needs aux");
   JM_CHECK(!a->pe || (a->pe_idx && a->row_period > 0), "jm_gemm: pe needs pe_idx and row_period");
   JM_CHECK(!a->out_f32 || a->ldo_f32 % 4 == 0, "jm_gemm: ldo_f32 must be a multiple of 4");
@@ -1852,6 +1966,8 @@ extern "C" int jm_gemm(const jm_gemm_args* a, void* stream_) {
   ep.accumulate = (a->accumulate || splits > 1) ? 1 : 0;
   ep.colsum = a->colsum;
   ep.row_scale = a->row_scale, ep.row_scale_period = a->row_scale_period;
+  ep.loss_target = a->loss_target, ep.ld_target = a->ld_target, ep.loss_stats = a->loss_stats;
+  ep.row_loss = a->row_loss, ep.loss_scale = a->loss_scale;
   JM_CHECK(!a->row_scale || a->row_scale_period > 0, "jm_gemm: row_scale needs row_scale_period > 0");
   JM_CHECK(!a->colsum || (a->act != 1 && a->act != 3), "jm_gemm: colsum is not defined for the GELU-forward epilogue");
 
@@ -1872,6 +1988,7 @@ extern "C" int jm_gemm(const jm_gemm_args* a, void* stream_) {
     epi = EPI_GELU_BWD;
   else if (ep.act == 0 && only_f32 && !ep.colsum) epi = EPI_F32;
   else if (ep.act == 0 && only_bf16 && !ep.residual && !ep.pe && !ep.colsum && rows_ok) epi = EPI_BF16;
+  if (ep.act == 5) epi = EPI_LOSS;
   if (amn && epi != EPI_F32) epi = EPI_GENERIC;  // transposed-A products are weight gradients
   ep.tma_store = 0;
   if ((epi == EPI_BF16 || epi == EPI_GELU_FWD || epi == EPI_GELU_BWD) &&

@@ -32,6 +32,7 @@ F32, BF16 = torch.float32, torch.bfloat16
 LN_EPS = 1e-6   # flax.linen.LayerNorm default
 # jm_gemm activation codes used by the step: the forward FFN GEMM saves gelu'(h) (not h) next to gelu(h), so that
 # the backward epilogue is a single multiply
+LOSS_EPI = 5   # jm_gemm act: loss epilogue of the pixel head
 GELU_FWD, GELU_BWD = (3, 4) if os.environ.get("JM_GELU_SAVED", "1") != "0" else (1, 2)
 
 
@@ -68,7 +69,7 @@ class _Block:
 class MAEEngine:
     """Buffers + kernel schedule for one per-device batch size."""
 
-    def __init__(self, cfg: MAEConfig, store: ParamStore, batch: int):
+    def __init__(self, cfg: MAEConfig, store: ParamStore, batch: int, fused_head: Optional[bool] = None):
         _lib.require_device()
         cfg.validate()
         self.cfg, self.ps, self.B = cfg, store, batch
@@ -107,15 +108,33 @@ class MAEEngine:
         # decoder
         self.za: List[torch.Tensor] = [e(self.Md, dd, dt=F32) for _ in range(cfg.dec_layers + 1)]
         self.dec = [_Block(self.Md, dd, cfg.dec_heads, B, self.Td, J, False, dev) for _ in range(cfg.dec_layers)]
-        self.meanD, self.rstdD = e(self.Md, dt=F32), e(self.Md, dt=F32)
-        self.dec_n = e(self.Md, dd)
-        self.pred = e(self.Md, P, dt=F32)
+        # Pixel head + loss (src/pretraining.py:110-120).  Fused (default for dec_dim <= 512): dec_norm and the head run on
+        # the N - keep masked rows of every image only, gathered into compact [B * n_mask, .] buffers, and the head GEMM's
+        # epilogue forms the squared error against the byte targets and its gradient -- the f32 prediction never exists.
+        # Unfused (fused_head=False / JM_HEAD_FUSED=0): head on all rows -> pred f32 -> jm_patch_loss.
+        if fused_head is None:
+            fused_head = os.environ.get("JM_HEAD_FUSED", "1") != "0"
+        self.fused_head = bool(fused_head) and dd <= 512 and cfg.labels <= 0
+        self.n_mask = N - n
+        self.Mh = B * self.n_mask if self.fused_head else self.Md
+        self.meanD, self.rstdD = e(self.Mh, dt=F32), e(self.Mh, dt=F32)
+        self.dec_n = e(self.Mh, dd)
         self.loss = torch.zeros(1, dtype=F32, device=dev)
-        self.loss_ws = torch.empty(ops.patch_loss_workspace(B, N), dtype=torch.uint8, device=dev)
+        if self.fused_head:
+            self.pred = None
+            self.Pt = (P + 15) // 16 * 16
+            self.tgt_u8 = e(self.Mh, self.Pt, dt=torch.uint8)
+            self.tgt_stats = e(self.Mh, 2, dt=F32) if cfg.norm_pix_loss else None
+            self.row_map = e(self.Mh, dt=torch.int32)
+            self.row_loss = e(self.Mh, (P + 15) // 16, dt=F32)
+            self.loss_ws = torch.empty(ops.row_loss_workspace(), dtype=torch.uint8, device=dev)
+        else:
+            self.pred = e(self.Md, P, dt=F32)
+            self.loss_ws = torch.empty(ops.patch_loss_workspace(B, N), dtype=torch.uint8, device=dev)
         # backward scratch, shared by both stacks (sized for the larger one)
         Mx = max(self.Me, self.Md)
         wmax = max(self.Me * d, self.Md * dd)
-        self.dpred = torch.zeros(self.Md, self.Pp, dtype=BF16, device=dev)     # pad columns stay zero
+        self.dpred = torch.zeros(self.Mh, self.Pp, dtype=BF16, device=dev)     # pad columns stay zero
         self.dxA, self.dxB = e(wmax, dt=F32), e(wmax, dt=F32)
         self.dxA16, self.dxB16 = e(wmax), e(wmax)
         self.dh16 = e(4 * wmax)
@@ -230,12 +249,27 @@ class MAEEngine:
         for i in range(cfg.dec_layers):
             self._block_fwd(f"decoder_model/dec_layer_{i}", self.dec[i], self.za[i], self.za[i + 1], self.Md, cfg.dec_dim,
                             cfg.dec_heads, self.Td, False, self._dp(cfg.layers + i))
+        if self.fused_head:
+            return                       # dec_norm runs on the masked rows only, in forward_head_and_loss
         ops.layernorm_fwd(self.za[cfg.dec_layers], ps.f("decoder_model/dec_norm/scale"),
                           ps.f("decoder_model/dec_norm/bias"), LN_EPS, self.dec_n, None, self.meanD, self.rstdD)
 
     def forward_head_and_loss(self, want_grad: bool = True, grad_scale: float = 1.0) -> torch.Tensor:
         """decoder_image_output + extract_patches + (norm-pix) + patch_mse_loss (src/pretraining.py:110-120)."""
-        cfg = self.cfg
+        cfg, ps = self.cfg, self.ps
+        if self.fused_head:
+            P, n_mask = cfg.patch_dim, self.n_mask
+            ops.masked_targets(self.images, cfg.patch_size, self.ids_shuffle[cfg.keep:], cfg.num_cls_tokens,
+                               cfg.norm_pix_loss, self.tgt_u8, self.tgt_stats, self.row_map)
+            ops.layernorm_fwd_rows(self.za[cfg.dec_layers], self.row_map, ps.f("decoder_model/dec_norm/scale"),
+                                   ps.f("decoder_model/dec_norm/bias"), LN_EPS, self.dec_n, self.meanD, self.rstdD)
+            denom = float(P) * n_mask * self.B            # mean over images of mean over masked patches of mean_c
+            ops.gemm(self.dec_n, self._W("decoder_image_output/kernel"), self.Mh, P, cfg.dec_dim, b_mn=True,
+                     ldb=ps.ld("decoder_image_output/kernel"), bias=ps.f("decoder_image_output/bias"), act=LOSS_EPI,
+                     out_bf16=self.dpred if want_grad else None, ldo_bf16=self.Pp, loss_target=self.tgt_u8,
+                     loss_stats=self.tgt_stats, row_loss=self.row_loss, loss_scale=2.0 * grad_scale / denom)
+            ops.row_loss_finalize(self.row_loss, 1.0 / denom, self.loss, self.loss_ws)
+            return self.loss
         # pixel head on every token row; CLS / visible rows are ignored by the loss
         self._fwd_linear(self.dec_n, self.Md, "decoder_image_output", cfg.patch_dim, cfg.dec_dim, out_f32=self.pred)
         ops.patch_loss(self.pred, self.images, self.mask_row, cfg.patch_size, cfg.num_cls_tokens, cfg.norm_pix_loss,
@@ -333,8 +367,9 @@ class MAEEngine:
             if zero_grads:
                 ps.g.zero_()
             # ---- pixel head
-            dn = view(self.dn16, Md, dd)
-            self._bwd_linear(self.dec_n, self.dpred, Md, "decoder_image_output", P, dd, dX16=dn, dy_ld=Pp)
+            Mh = self.Mh
+            dn = view(self.dn16, Mh, dd)
+            self._bwd_linear(self.dec_n, self.dpred, Mh, "decoder_image_output", P, dd, dX16=dn, dy_ld=Pp)
             dx, dx16 = view(self.dxA, Md, dd), view(self.dxA16, Md, dd)
             # (every LayerNorm backward also emits the column sums of the dx it produces: that dx is the
             #  output gradient of the previous block's ff/w2, i.e. its bias gradient)
@@ -343,11 +378,17 @@ class MAEEngine:
             # its LayerNorm backwards move 10 instead of 16 bytes per element.  Only the gradient that leaves the
             # decoder (layer 0's input, scattered back to the encoder's tokens) is also written in f32.
             lowp = self.dec_lowp and not dp_on
-            ops.layernorm_bwd(dn, self.za[cfg.dec_layers], self.meanD, self.rstdD,
-                              ps.f("decoder_model/dec_norm/scale"), None, None if lowp else dx, dx16,
-                              ps.grad("decoder_model/dec_norm/scale"), ps.grad("decoder_model/dec_norm/bias"),
-                              self.ln_ws,
-                              dcol=None if dp_on else ps.grad(f"decoder_model/dec_layer_{cfg.dec_layers - 1}/ff/w2/bias"))
+            dcol = None if dp_on else ps.grad(f"decoder_model/dec_layer_{cfg.dec_layers - 1}/ff/w2/bias")
+            if self.fused_head:          # the gradient exists on the masked rows only: scattered into a zeroed dx
+                ops.layernorm_bwd_rows(dn, self.za[cfg.dec_layers], self.row_map, self.meanD, self.rstdD,
+                                       ps.f("decoder_model/dec_norm/scale"), None if lowp else dx, dx16,
+                                       ps.grad("decoder_model/dec_norm/scale"), ps.grad("decoder_model/dec_norm/bias"),
+                                       self.ln_ws, dcol=dcol)
+            else:
+                ops.layernorm_bwd(dn, self.za[cfg.dec_layers], self.meanD, self.rstdD,
+                                  ps.f("decoder_model/dec_norm/scale"), None, None if lowp else dx, dx16,
+                                  ps.grad("decoder_model/dec_norm/scale"), ps.grad("decoder_model/dec_norm/bias"),
+                                  self.ln_ws, dcol=dcol)
             # ---- decoder blocks
             for i in reversed(range(cfg.dec_layers)):
                 below = ps.grad(f"decoder_model/dec_layer_{i - 1}/ff/w2/bias") if i > 0 else None

@@ -198,6 +198,50 @@ def layernorm_bwd_lowp(dy: torch.Tensor, x: torch.Tensor, mean: torch.Tensor, rs
         workspace.numel() * workspace.element_size(), stream_ptr()))
 
 
+def layernorm_fwd_rows(x: torch.Tensor, row_map: torch.Tensor, gamma: torch.Tensor, beta: torch.Tensor, eps: float,
+                       y_bf16: torch.Tensor, mean: torch.Tensor, rstd: torch.Tensor) -> None:
+    """y[r] = LayerNorm(x[row_map[r]]): the rows that matter, compact (dec_norm in front of the pixel head)."""
+    _chk(x, F32, "x"), _chk(row_map, I32, "row_map"), _chk(gamma, F32, "gamma"), _chk(beta, F32, "beta")
+    _chk(y_bf16, BF16, "y_bf16"), _chk(mean, F32, "mean"), _chk(rstd, F32, "rstd")
+    check(_lib.load().jm_layernorm_fwd_rows(ptr(x), _ld(x), ptr(row_map), row_map.numel(), x.shape[-1], ptr(gamma),
+                                            ptr(beta), eps, ptr(y_bf16), _ld(y_bf16), ptr(mean), ptr(rstd),
+                                            stream_ptr()))
+
+
+def layernorm_bwd_rows(dy: torch.Tensor, x: torch.Tensor, row_map: torch.Tensor, mean: torch.Tensor,
+                       rstd: torch.Tensor, gamma: torch.Tensor, dx: Optional[torch.Tensor],
+                       dx_bf16: Optional[torch.Tensor], dgamma: torch.Tensor, dbeta: torch.Tensor,
+                       workspace: torch.Tensor, dcol: Optional[torch.Tensor] = None) -> None:
+    """Backward of layernorm_fwd_rows: dx / dx_bf16 [all rows, dim] zeroed, then the mapped rows scattered."""
+    _chk(dy, BF16, "dy"), _chk(x, F32, "x"), _chk(row_map, I32, "row_map"), _chk(mean, F32, "mean")
+    _chk(rstd, F32, "rstd"), _chk(gamma, F32, "gamma"), _chk(dx, F32, "dx"), _chk(dx_bf16, BF16, "dx_bf16")
+    _chk(dgamma, F32, "dgamma"), _chk(dbeta, F32, "dbeta"), _chk(dcol, F32, "dcol")
+    check(_lib.load().jm_layernorm_bwd_rows(
+        ptr(dy), _ld(dy), ptr(x), _ld(x), ptr(row_map), ptr(mean), ptr(rstd), ptr(gamma), row_map.numel(), x.shape[-1],
+        x.shape[0], ptr(dx), _ld(dx), ptr(dx_bf16), _ld(dx_bf16), ptr(dgamma), ptr(dbeta), ptr(dcol), ptr(workspace),
+        workspace.numel() * workspace.element_size(), stream_ptr()))
+
+
+def masked_targets(images: torch.Tensor, patch_size: int, ids: torch.Tensor, num_cls: int, norm_pix: bool,
+                   targets: torch.Tensor, stats: Optional[torch.Tensor], row_map: Optional[torch.Tensor]) -> None:
+    """Byte targets (+ norm-pix statistics, + decoder rows) of the patches ``ids`` for the loss epilogue of gemm(act=5)."""
+    _chk(images, torch.uint8, "images"), _chk(ids, I32, "ids"), _chk(targets, torch.uint8, "targets")
+    _chk(stats, F32, "stats"), _chk(row_map, I32, "row_map")
+    check(_lib.load().jm_masked_targets(ptr(images), images.shape[0], images.shape[-1], patch_size, ptr(ids), ids.numel(),
+                                        num_cls, int(norm_pix), ptr(targets), _ld(targets), ptr(stats), ptr(row_map),
+                                        stream_ptr()))
+
+
+def row_loss_workspace() -> int:
+    return int(_lib.load().jm_row_loss_workspace())
+
+
+def row_loss_finalize(row_loss: torch.Tensor, scale: float, loss: torch.Tensor, workspace: torch.Tensor) -> None:
+    _chk(row_loss, F32, "row_loss"), _chk(loss, F32, "loss")
+    check(_lib.load().jm_row_loss_finalize(ptr(row_loss), row_loss.numel(), scale, ptr(loss), ptr(workspace),
+                                           workspace.numel() * workspace.element_size(), stream_ptr()))
+
+
 # ------------------------------------------------------------------ GEMM
 def gemm(A: torch.Tensor, B: torch.Tensor, M: int, N: int, K: int, *, a_mn: bool = False, b_mn: bool = False,
          lda: Optional[int] = None, ldb: Optional[int] = None,
@@ -212,7 +256,9 @@ def gemm(A: torch.Tensor, B: torch.Tensor, M: int, N: int, K: int, *, a_mn: bool
          row_period: int = 0, row_skip: int = 0, row_mask_mode: int = 0,
          accumulate: bool = False, splits: int = 0, block_n: int = 0,
          colsum: Optional[torch.Tensor] = None, cta_pair: int = 0,
-         row_scale: Optional[torch.Tensor] = None, row_scale_period: int = 0) -> None:
+         row_scale: Optional[torch.Tensor] = None, row_scale_period: int = 0,
+         loss_target: Optional[torch.Tensor] = None, loss_stats: Optional[torch.Tensor] = None,
+         row_loss: Optional[torch.Tensor] = None, loss_scale: float = 0.0) -> None:
     """D = epilogue(A @ B) through jm_gemm; see include/jumbo_mae_b200.h for the epilogue order."""
     _chk(A, BF16, "A"), _chk(B, BF16, "B"), _chk(out_f32, F32, "out_f32"), _chk(out_bf16, BF16, "out_bf16")
     _chk(out2_bf16, BF16, "out2_bf16"), _chk(bias, F32, "bias"), _chk(residual, F32, "residual")
@@ -237,6 +283,9 @@ def gemm(A: torch.Tensor, B: torch.Tensor, M: int, N: int, K: int, *, a_mn: bool
     a.cta_pair = int(cta_pair)
     _chk(row_scale, F32, "row_scale")
     a.row_scale, a.row_scale_period = ptr(row_scale), int(row_scale_period)
+    _chk(loss_target, torch.uint8, "loss_target"), _chk(loss_stats, F32, "loss_stats"), _chk(row_loss, F32, "row_loss")
+    a.loss_target, a.ld_target = ptr(loss_target), _ld(loss_target)
+    a.loss_stats, a.row_loss, a.loss_scale = ptr(loss_stats), ptr(row_loss), float(loss_scale)
     check(_lib.load().jm_gemm(ctypes.byref(a), stream_ptr()))
 
 

@@ -112,6 +112,94 @@ def test_patch_loss_and_grad(ops, norm_pix):
     assert torch.allclose(got[:, J:], pr.grad, rtol=2 ** -7, atol=1e-9)
 
 
+@pytest.mark.parametrize("S,p,keep,B,dd,norm_pix", [(32, 8, 4, 3, 64, False), (32, 8, 4, 3, 64, True),
+                                                      (56, 14, 5, 5, 128, True), (224, 16, 49, 2, 512, True)])
+def test_pixel_head_loss_epilogue(ops, S, p, keep, B, dd, norm_pix):
+    """jm_masked_targets + jm_gemm(act=5) + jm_row_loss_finalize = decoder_image_output + extract_patches + norm-pix +
+    patch_mse_loss on the masked rows (src/pretraining.py:110-120, src/utils_mae.py:51-64), and d loss / d prediction;
+    P = 192, 588 (ViT-H/14: N not a multiple of 16) and 768."""
+    N, P, J = (S // p) ** 2, p * p * 3, 3
+    g = torch.Generator().manual_seed(S + p + B)
+    images = torch.randint(0, 256, (B, 3, S, S), generator=g, dtype=torch.uint8)
+    noise = torch.rand(N, generator=g).numpy()
+    ids_shuffle, _, mask_row = O.masking_from_noise(noise, keep)
+    ids = torch.from_numpy(np.asarray(ids_shuffle)).to(torch.int32)
+    n_mask = N - keep
+    Mh = B * n_mask
+    X = (torch.randn(Mh, dd, generator=g)).to(BF16)
+    W_full = (torch.randn(dd, (P + 7) // 8 * 8, generator=g) * 0.1).to(BF16)        # row stride padded to 16 bytes
+    W = W_full[:, :P]
+    bias = torch.randn(P, generator=g)
+    # oracle: prediction of the masked rows, targets of the same patches
+    pred = (X.float() @ W.float() + bias).reshape(B, n_mask, P).clone().requires_grad_(True)
+    tgt = O.extract_patches(O.preprocess(images), p)[:, ids[keep:].long()]
+    if norm_pix:
+        tgt = (tgt - tgt.mean(-1, keepdim=True)) / torch.sqrt(tgt.var(-1, keepdim=True, unbiased=False) + 1e-6)
+    want = O.patch_mse_loss(pred, tgt, torch.ones(B, n_mask))
+    want.backward()
+    # kernels
+    Pt, Pp = (P + 15) // 16 * 16, (P + 7) // 8 * 8
+    t8 = torch.empty(Mh, Pt, dtype=torch.uint8, device="cuda")
+    stats = torch.empty(Mh, 2, device="cuda") if norm_pix else None
+    row_map = torch.empty(Mh, dtype=torch.int32, device="cuda")
+    ops.masked_targets(dev(images), p, dev(ids)[keep:], J, norm_pix, t8, stats, row_map)
+    want_rows = (torch.arange(B)[:, None] * (J + N) + J + ids[keep:][None, :].long()).reshape(-1)
+    assert torch.equal(row_map.cpu().long(), want_rows)
+    raw = O.extract_patches(images.permute(0, 2, 3, 1).float(), p)[:, ids[keep:].long()].reshape(Mh, P)   # patch-vector order
+    assert torch.equal(t8[:, :P].cpu().float(), raw)
+    row_loss = torch.full((Mh, (P + 15) // 16), float("nan"), device="cuda")
+    dpred = torch.full((Mh, Pp), 9.0, dtype=BF16, device="cuda")
+    loss = torch.zeros(1, device="cuda")
+    ws = torch.empty(ops.row_loss_workspace(), dtype=torch.uint8, device="cuda")
+    denom = float(P) * n_mask * B
+    ops.gemm(dev(X), dev(W_full)[:, :P], Mh, P, dd, b_mn=True, bias=dev(bias), act=5, out_bf16=dpred, loss_target=t8,
+             loss_stats=stats, row_loss=row_loss, loss_scale=2.0 / denom)
+    ops.row_loss_finalize(row_loss, 1.0 / denom, loss, ws)
+    assert abs(loss.item() - want.item()) < 2e-5 * abs(want.item())
+    got = dpred.float().cpu()
+    assert torch.allclose(got[:, :P], pred.grad.reshape(Mh, P), rtol=2 ** -7, atol=1e-9)
+    assert torch.equal(got[:, P:], torch.zeros(Mh, Pp - P))          # pad columns written as zeros
+    # validation form: no gradient output
+    row_loss.fill_(float("nan"))
+    ops.gemm(dev(X), dev(W_full)[:, :P], Mh, P, dd, b_mn=True, bias=dev(bias), act=5, loss_target=t8, loss_stats=stats,
+             row_loss=row_loss, loss_scale=0.0)
+    loss2 = torch.zeros(1, device="cuda")
+    ops.row_loss_finalize(row_loss, 1.0 / denom, loss2, ws)
+    assert loss2.item() == loss.item()                                # deterministic, same order
+
+
+@pytest.mark.parametrize("rows,D,total", [(37, 64, 100), (300, 512, 1000)])
+def test_layernorm_rows_gather_scatter(ops, rows, D, total):
+    """jm_layernorm_fwd_rows / jm_layernorm_bwd_rows: LayerNorm of a subset of rows (compact output), backward scattered
+    into a zeroed dx."""
+    g = torch.Generator().manual_seed(D + rows)
+    x = (torch.randn(total, D, generator=g) * 2 + 0.5)
+    gamma, beta = torch.randn(D, generator=g), torch.randn(D, generator=g)
+    row_map = torch.randperm(total, generator=g)[:rows].to(torch.int32)
+    xs = x[row_map.long()].clone().requires_grad_(True)
+    gm, bt = gamma.clone().requires_grad_(True), beta.clone().requires_grad_(True)
+    y = O.layer_norm(xs, gm, bt)
+    dy = torch.randn(rows, D, generator=g).to(BF16)
+    (y * dy.float()).sum().backward()
+    yb = torch.empty(rows, D, dtype=BF16, device="cuda")
+    mean, rstd = torch.empty(rows, device="cuda"), torch.empty(rows, device="cuda")
+    ops.layernorm_fwd_rows(dev(x), dev(row_map), dev(gamma), dev(beta), 1e-6, yb, mean, rstd)
+    assert torch.allclose(yb.float().cpu(), y.detach(), rtol=2 ** -7, atol=1e-3)
+    dx = torch.full((total, D), 5.0, device="cuda")
+    dxb = torch.full((total, D), 5.0, dtype=BF16, device="cuda")
+    dgamma, dbeta, dcol = (torch.zeros(D, device="cuda") for _ in range(3))
+    ws = torch.empty(ops.layernorm_bwd_workspace(total, D), dtype=torch.uint8, device="cuda")
+    ops.layernorm_bwd_rows(dev(dy), dev(x), dev(row_map), mean, rstd, dev(gamma), dx, dxb, dgamma, dbeta, ws, dcol=dcol)
+    want = torch.zeros(total, D)
+    want[row_map.long()] = xs.grad
+    assert torch.allclose(dx.cpu(), want, rtol=1e-4, atol=1e-4)
+    assert torch.allclose(dxb.float().cpu(), want, rtol=2 ** -7, atol=1e-3)
+    scale = max(1.0, math.sqrt(rows))
+    assert torch.allclose(dgamma.cpu(), gm.grad, rtol=1e-4, atol=1e-4 * scale)
+    assert torch.allclose(dbeta.cpu(), bt.grad, rtol=1e-4, atol=1e-4 * scale)
+    assert torch.allclose(dcol.cpu(), want.sum(0), rtol=1e-4, atol=1e-3 * scale)
+
+
 # ------------------------------------------------------------------ LayerNorm
 @pytest.mark.parametrize("rows,D", [(37, 64), (300, 512), (260, 768), (16, 2304), (9, 1280)])
 def test_layernorm_fwd(ops, rows, D):

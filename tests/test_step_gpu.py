@@ -44,7 +44,7 @@ def _product_cfg(ocfg):
     return MAEConfig(**{f: getattr(ocfg, f) for f in MAEConfig.__dataclass_fields__ if hasattr(ocfg, f)})
 
 
-def _setup(name):
+def _setup(name, fused_head=None):
     from jumbo_mae_tpu_b200.engine import MAEEngine
     from jumbo_mae_tpu_b200.params import ParamStore
     ocfg, B = _cfgs()[name]
@@ -53,7 +53,7 @@ def _setup(name):
     images, noise = O.synthetic_batch(ocfg, B, seed=1, noise_seed=1001)
     store = ParamStore(cfg)
     store.load_tree(state.params)
-    eng = MAEEngine(cfg, store, B)
+    eng = MAEEngine(cfg, store, B, fused_head=fused_head)
     return ocfg, cfg, state, images, noise, store, eng
 
 
@@ -65,9 +65,13 @@ ALL = ["tiny", "tiny_normpix", "mid", "vitb_width", "vith_patch14", "config1_vit
        "tiny_learnable_wpe"]
 
 
+@pytest.mark.parametrize("fused_head", [True, False])
 @pytest.mark.parametrize("name", ALL)
-def test_forward_loss_and_activations(name):
-    ocfg, cfg, state, images, noise, store, eng = _setup(name)
+def test_forward_loss_and_activations(name, fused_head):
+    """fused_head: dec_norm + pixel head on the masked rows only with the loss in the GEMM epilogue (the default);
+    False: head on every row -> f32 prediction -> jm_patch_loss."""
+    ocfg, cfg, state, images, noise, store, eng = _setup(name, fused_head)
+    assert eng.fused_head == fused_head
     collect = {}
     want = O.pretrain_forward(state.params, images, noise, ocfg, collect)["loss"].item()
     loss = eng.forward(images.cuda(), torch.from_numpy(noise).cuda(), want_grad=False)
@@ -83,15 +87,16 @@ def test_forward_loss_and_activations(name):
         w = collect[key]
         r = _rel(got.cpu().reshape(w.shape), w)
         assert r <= (1e-2 if key.startswith("enc") else 3e-2), f"{key}: rel l2 {r}"
-    pred = eng.pred.cpu().reshape(B, -1, ocfg.patch_dim)[:, 3:]
-    assert _rel(pred, collect["image_output"]) <= 3e-2
+    if not fused_head:
+        pred = eng.pred.cpu().reshape(B, -1, ocfg.patch_dim)[:, 3:]
+        assert _rel(pred, collect["image_output"]) <= 3e-2
     assert abs(loss.item() - want) <= 5e-3 * abs(want), (loss.item(), want)
 
 
-@pytest.mark.parametrize("name", ALL)
-def test_gradients_match_oracle(name):
+@pytest.mark.parametrize("name,fused_head", [(n, True) for n in ALL] + [("tiny_normpix", False), ("vith_patch14", False)])
+def test_gradients_match_oracle(name, fused_head):
     from jumbo_mae_tpu_b200.params import tree_leaves
-    ocfg, cfg, state, images, noise, store, eng = _setup(name)
+    ocfg, cfg, state, images, noise, store, eng = _setup(name, fused_head)
     want_loss, want = O.loss_and_grads(state.params, images, noise, ocfg)
     eng.forward(images.cuda(), torch.from_numpy(noise).cuda())
     eng.backward()
