@@ -237,9 +237,8 @@ typedef struct jm_gemm_args {
   int block_n;     /* 0 = choose automatically (64, 128 or 256) */
   float* colsum;   /* optional [N]: += column sums of the stored output (fused bias gradient) */
   int cta_pair;    /* 0 = automatic, 1 = force the 2-SM (cta_group::2) 256x256 kernel, -1 = never use it;
-                    * 2 = the plain pair kernel (no resident B, no 4-CTA clusters), 4 = pairs in 4-CTA clusters that
-                    * share an operand by TMA multicast where the tile grid allows (else as 1), 5 = as 1 with the default pair
-                    * count (the resident-B kernel then reloads B when a pair's column tile changes: a test hook) */
+                    * 2 = the plain pair kernel (B streamed, not resident), 5 = as 1 with the default pair count (the
+                    * resident-B kernel then reloads B when a pair's column tile changes: a test hook) */
   /* optional per-image scale of the branch: out_f32 = row_scale[row / row_scale_period] * (acc + bias) + residual
    * (DropPath keep-mask / (1 - p) of a residual branch, src/modeling.py:157,181-183,192,199,201); f32 output only */
   const float* row_scale; int row_scale_period;

@@ -391,26 +391,6 @@ __device__ __forceinline__ void umma2_commit_mc(uint64_t* bar) {
       "h"(mask)
       : "memory");
 }
-__device__ __forceinline__ void umma2_commit_mask(uint64_t* bar, uint16_t mask) {  // same, in the CTAs of `mask`
-  asm volatile(
-      "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(
-          smem_u32(bar)),
-      "h"(mask)
-      : "memory");
-}
-// 2-D tiled load written to the same shared-memory offset in every CTA of `mask` (cluster ranks); in each of them the
-// bytes complete on the mbarrier of that CTA's pair leader.  Callers pass tensor maps over this GPU's memory only: TMA
-// multicast loads here read only this GPU's memory, since on B200 a TMA multicast load from another GPU's memory hung
-// the GPU (jm_gemm checks where its operands live before it picks the kernel that uses this).
-__device__ __forceinline__ void tma_load_2d_pair_mc(const void* desc, uint64_t* bar, void* smem, int c0, int c1,
-                                                    uint16_t mask) {
-  const uint32_t leader_bar = smem_u32(bar) & 0xFEFFFFFFu;
-  asm volatile(
-      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster "
-      "[%0], [%1, {%4, %5}], [%2], %3;" ::"r"(smem_u32(smem)),
-      "l"(reinterpret_cast<uint64_t>(desc)), "r"(leader_bar), "h"(mask), "r"(c0), "r"(c1)
-      : "memory");
-}
 // 2-D tiled load issued by either CTA of a pair into ITS OWN shared memory, completing on the LEADER's mbarrier
 // (the barrier address with the CTA-rank bit cleared).
 __device__ __forceinline__ void tma_load_2d_pair(const void* desc, uint64_t* bar, void* smem, int c0, int c1) {

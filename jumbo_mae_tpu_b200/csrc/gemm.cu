@@ -43,7 +43,6 @@ struct GemmShape {
   int M, N, K;
   int num_m, num_n, splits, kblocks;
   int group_m;  // tile order: n fastest within bands of group_m tile rows, m fastest inside a band (1: plain n fastest)
-  int quad;     // CTA-pair kernel in clusters of two pairs: 0 off, 1 the pairs share A (tiles adjacent in n), 2 share B
 };
 
 // Tile index within one split -> tile coordinates.
@@ -1389,15 +1388,8 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
-  // Clusters of one pair, or (sh.quad) of two pairs that work on neighbouring tiles in lock-step and share one operand:
-  // each CTA loads half of the shared operand's rows and the TMA multicasts it to the CTA of the same rank in the other
-  // pair, so a k-block costs 24 KB of L2 reads per CTA instead of 32 (the L2 -> SM rate is what bounds these GEMMs).
-  const int crank = static_cast<int>(cluster_ctarank());
-  const int rank = crank & 1;  // within the pair
-  const int sub = crank >> 1;  // which pair of the cluster
-  const int quad = sh.quad;    // kernel-uniform
-  const int pair = quad ? 2 * (blockIdx.x >> 2) + sub : blockIdx.x >> 1;
-  const int npairs = quad ? 2 * (gridDim.x >> 2) : gridDim.x >> 1;
+  const int rank = static_cast<int>(cluster_ctarank());  // within the pair
+  const int pair = blockIdx.x >> 1, npairs = gridDim.x >> 1;
 #ifdef JM_DEBUG_SMID
   if (threadIdx.x == 0 && blockIdx.x < 8) {
     uint32_t smid;
@@ -1413,7 +1405,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
   if (warp == 0 && elect_one()) {
     for (int s = 0; s < STAGES; ++s) {
       mbar_init(&full[s], 1);   // the leader's producer arrives with the byte count of BOTH CTAs' loads
-      mbar_init(&empty[s], quad ? 2 : 1);  // one multicast commit per pair that reads (or writes into) the stage
+      mbar_init(&empty[s], 1);  // one multicast commit
     }
     for (int a = 0; a < 2; ++a) {
       mbar_init(&tfull[a], 1);
@@ -1439,7 +1431,6 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
     if (elect_one()) {
       int stage = 0;
       uint32_t phase = 0;
-      const uint16_t mc_mask = static_cast<uint16_t>((1u << crank) | (1u << (crank ^ 2)));
       int res_n = -1;                      // BRES: the column tile whose B is resident
       int last_stage = 0;
       uint32_t last_phase = 0;             // ring position of the last k-block issued
@@ -1501,21 +1492,14 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
           if (rank == 0) mbar_arrive_expect_tx(&full[stage], 2 * Cfg::STAGE_BYTES);
           uint8_t* a_dst = sA + stage * Cfg::A_BYTES;
           uint8_t* b_dst = sB + stage * Cfg::B_BYTES;
-          // shared operand: this CTA's 64 of the 128 rows (8 KB, the same bytes either major), to both pairs
-          if (quad == 1) {
-            if (!A_MN) tma_load_2d_pair_mc(&tmA, &full[stage], a_dst + sub * 8192, kb * BK, m0 + sub * 64, mc_mask);
-            else tma_load_2d_pair_mc(&tmA, &full[stage], a_dst + sub * 8192, m0 + sub * 64, kb * BK, mc_mask);
-          } else if (!A_MN) {
+          if (!A_MN) {
             tma_load_2d_pair(&tmA, &full[stage], a_dst, kb * BK, m0);
           } else {
 #pragma unroll
             for (int i = 0; i < BM / 64; ++i)
               tma_load_2d_pair(&tmA, &full[stage], a_dst + i * (BK * 128), m0 + i * 64, kb * BK);
           }
-          if (quad == 2) {
-            if (!B_MN) tma_load_2d_pair_mc(&tmB, &full[stage], b_dst + sub * 8192, kb * BK, n0 + sub * 64, mc_mask);
-            else tma_load_2d_pair_mc(&tmB, &full[stage], b_dst + sub * 8192, n0 + sub * 64, kb * BK, mc_mask);
-          } else if (!B_MN) {
+          if (!B_MN) {
             tma_load_2d_pair(&tmB, &full[stage], b_dst, kb * BK, n0);
           } else {
 #pragma unroll
@@ -1532,8 +1516,6 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
       int stage = 0;
       uint32_t phase = 0;
       int iter = 0;
-      // a stage is free when both pairs have read it (its shared half was written by the other pair's CTA)
-      const uint16_t pair_mask = static_cast<uint16_t>(3u << (2 * sub)), empty_mask = quad ? 0xF : pair_mask;
       int res_n = -1;
       uint32_t res_phase = 0;  // BRES: resident column tile / parity of its next arrival
       for (int t = pair; t < total_tiles; t += npairs, ++iter) {
@@ -1567,8 +1549,8 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
                                        : make_smem_desc_sw128(b_addr + k * (UMMA_K * 2), 0, 1024);
               umma2_bf16(d_tmem, da, db, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
             }
-            umma2_commit_mask(&empty[stage], empty_mask);
-            if (kb == kb1 - 1) umma2_commit_mask(&tfull[acc], pair_mask);
+            umma2_commit_mc(&empty[stage]);
+            if (kb == kb1 - 1) umma2_commit_mc(&tfull[acc]);
           }
           __syncwarp();
           if (++stage == STAGES) stage = 0, phase ^= 1;
@@ -1660,7 +1642,7 @@ static int launch_gemm2(const GemmMaps& tm, const GemmShape& sh, const EpiParams
   cfg.dynamicSmemBytes = kSmem;
   cfg.stream = stream;
   cudaLaunchAttribute attr[3];
-  const int csize = sh.quad ? 4 : 2;
+  const int csize = 2;
   attr[0].id = cudaLaunchAttributeClusterDimension;
   attr[0].val.clusterDim.x = csize;
   attr[0].val.clusterDim.y = 1;
@@ -1679,7 +1661,7 @@ static int launch_gemm2(const GemmMaps& tm, const GemmShape& sh, const EpiParams
   // A persistent grid must not exceed the clusters the GPU can hold at once (GPCs with an odd SM left over
   // cannot host a pair there): surplus clusters would run as a second wave.
   static std::atomic<int> max_clusters_dev[2][kMaxDevices];  // per cluster size and device ordinal (zero-initialised)
-  std::atomic<int>& cached = max_clusters_dev[sh.quad ? 1 : 0][dev];
+  std::atomic<int>& cached = max_clusters_dev[0][dev];
   int max_clusters = cached.load(std::memory_order_acquire);
   if (max_clusters == 0) {
     int n = 0;
@@ -1775,43 +1757,6 @@ static int pick_splits(long tiles, long slots, int kblocks) {
     if (best == 0.0 || cost < best * 0.98) best = cost, best_s = s;
   }
   return best_s;
-}
-
-// How many 4-CTA clusters of the pair kernel the current device holds at once (GPCs whose SM count is not a multiple of
-// four leave SMs over: 33 clusters = 132 of 148 SMs on B200); cached per device ordinal.
-static int quad_cluster_capacity() {
-  static std::atomic<int> cap[jm::kMaxDevices];
-  const int dev = jm::current_device();
-  if (dev < 0) return 0;
-  int n = cap[dev].load(std::memory_order_acquire);
-  if (n == 0) {
-    auto kern = jm::gemm2_kernel<false, true, jm::EPI_GELU_FWD>;  // the largest shared-memory footprint
-    cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, jm::Gemm2Cfg<jm::EPI_GELU_FWD>::SMEM_BYTES);
-    cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3(4 * 64), cfg.blockDim = dim3(jm::kGemmThreads);
-    cfg.dynamicSmemBytes = jm::Gemm2Cfg<jm::EPI_GELU_FWD>::SMEM_BYTES;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeClusterDimension;
-    attr[0].val.clusterDim.x = 4, attr[0].val.clusterDim.y = 1, attr[0].val.clusterDim.z = 1;
-    cfg.attrs = attr, cfg.numAttrs = 1;
-    if (cudaOccupancyMaxActiveClusters(&n, kern, &cfg) != cudaSuccess || n <= 0) {
-      cudaGetLastError();
-      n = -1;
-    }
-    cap[dev].store(n, std::memory_order_release);
-  }
-  return n > 0 ? n : 0;
-}
-
-// True when p points into an ordinary device allocation of the current device (not host, managed, or a mapping of
-// another GPU's memory).
-static bool operand_is_local(const void* p) {
-  cudaPointerAttributes at;
-  if (cudaPointerGetAttributes(&at, p) != cudaSuccess) {
-    cudaGetLastError();
-    return false;
-  }
-  return at.type == cudaMemoryTypeDevice && at.device == jm::current_device();
 }
 
 extern "C" int jm_gemm(const jm_gemm_args* a, void* stream_) {
@@ -1916,42 +1861,22 @@ extern "C" int jm_gemm(const jm_gemm_args* a, void* stream_) {
     }
   }
 
-  // Two pairs per cluster that share one operand by TMA multicast, where the tile grid pairs up evenly: neighbours in
-  // n share A, else neighbours in m share B (tile rows then run in bands of 8, m fastest, so that the two are
-  // neighbours in the tile order as well).  TMA multicast loads here read only this GPU's memory, since on B200 a TMA
-  // multicast load from another GPU's memory hung the GPU: the kernel is picked only when both operands are plain
-  // device allocations of the current device.
-  static const int auto_quad = env_int("JM_GEMM_QUAD", 0);  // process-wide, initialised once (thread-safe)
-  int quad = 0, group_m = 1;
-  if (pair && (auto_quad || a->cta_pair == 4) && a->cta_pair != 2) {  // cta_pair 2: plain pairs, 4: ask for this
-    if (num_n % 2 == 0) quad = 1;
-    else if (num_m_eff % 2 == 0) quad = 2, group_m = num_m_eff < 8 ? num_m_eff : 8;
-    if (auto_quad == 2 && quad == 1 && num_m_eff % 2 == 0) quad = 2, group_m = num_m_eff < 8 ? num_m_eff : 8;
-    if (quad && !(operand_is_local(a->A) && operand_is_local(a->B))) quad = 0, group_m = 1;
-    if (quad && quad_cluster_capacity() <= 0) quad = 0, group_m = 1;
-  }
-  const int quad_slots = quad ? quad_cluster_capacity() : 0;
-  if (quad && a->splits <= 0) {
-    splits = 1;
-    if (can_split) splits = pick_splits(static_cast<long>(num_m_eff) * num_n / 2, quad_slots, kblocks);
-  }
-
   GemmMaps tm;
   memset(&tm, 0, sizeof(tm));
   CUtensorMap& tmA = tm.a;
   CUtensorMap& tmB = tm.b;
   if (!a->a_mn_major) {
-    if (make_tmap(&tmA, a->A, a->K, a->M, a->lda, BK, quad == 1 ? BM / 2 : BM)) return 1;
+    if (make_tmap(&tmA, a->A, a->K, a->M, a->lda, BK, BM)) return 1;
   } else {
     if (make_tmap(&tmA, a->A, a->M, a->K, a->lda, 64, BK)) return 1;
   }
   if (!a->b_mn_major) {
-    if (make_tmap(&tmB, a->B, a->K, a->N, a->ldb, BK, pair ? (quad == 2 ? bn / 4 : bn / 2) : bn)) return 1;
+    if (make_tmap(&tmB, a->B, a->K, a->N, a->ldb, BK, pair ? bn / 2 : bn)) return 1;
   } else {
     if (make_tmap(&tmB, a->B, a->N, a->K, a->ldb, 64, BK)) return 1;
   }
 
-  GemmShape sh{a->M, a->N, a->K, num_m_eff, num_n, splits, kblocks, group_m, quad};
+  GemmShape sh{a->M, a->N, a->K, num_m_eff, num_n, splits, kblocks, 1};
   EpiParams ep;
   ep.out_f32 = a->out_f32, ep.ldo_f32 = a->ldo_f32;
   ep.out_bf16 = reinterpret_cast<__nv_bfloat16*>(a->out_bf16), ep.ldo_bf16 = a->ldo_bf16;
@@ -1972,9 +1897,8 @@ extern "C" int jm_gemm(const jm_gemm_args* a, void* stream_) {
   JM_CHECK(!a->colsum || (a->act != 1 && a->act != 3), "jm_gemm: colsum is not defined for the GELU-forward epilogue");
 
   const long total = static_cast<long>(num_m_eff) * num_n * splits;
-  const int grid = quad ? 4 * static_cast<int>(total / 2 < quad_slots ? total / 2 : quad_slots)
-                   : pair ? 2 * static_cast<int>(total < sms / 2 ? total : sms / 2)
-                          : static_cast<int>(total < sms ? total : sms);
+  const int grid = pair ? 2 * static_cast<int>(total < sms / 2 ? total : sms / 2)
+                        : static_cast<int>(total < sms ? total : sms);
   int epi = EPI_GENERIC;
   const bool only_bf16 = ep.out_bf16 && !ep.out_f32 && !ep.out2_bf16;
   const bool only_f32 = ep.out_f32 && !ep.out_bf16 && !ep.out2_bf16;
@@ -2017,7 +1941,7 @@ extern "C" int jm_gemm(const jm_gemm_args* a, void* stream_) {
     // that is a multiple of the column-tile count every pair keeps its column tile (B is loaded once per CTA) while
     // the pairs of one tile row run side by side (A is read from HBM once).
     static const int auto_bres = env_int("JM_GEMM_BRES", 1);  // process-wide, initialised once (thread-safe)
-    const bool bres = (auto_bres || a->cta_pair == 5) && !quad && !amn && splits == 1 && kblocks <= Gemm2Cfg<EPI_BF16, true>::RES_KB &&
+    const bool bres = (auto_bres || a->cta_pair == 5) && !amn && splits == 1 && kblocks <= Gemm2Cfg<EPI_BF16, true>::RES_KB &&
                       a->cta_pair != 2 && num_n <= sms / 2 && total >= sms / 2 &&
                       (epi == EPI_BF16 || epi == EPI_GELU_FWD || epi == EPI_GELU_BWD || epi == EPI_F32) && ep.tma_store;
     int g = grid;

@@ -607,12 +607,12 @@ def test_gemm_cta_pair_kernel(ops, M, N, K, a_mn, b_mn):
 
 
 
-@pytest.mark.parametrize("variant", [1, 2, 4, 5])
+@pytest.mark.parametrize("variant", [1, 2, 5])
 @pytest.mark.parametrize("M,N,K,b_mn", [(10100, 520, 504, True), (20480, 1024, 512, False), (9000, 768, 136, True)])
 def test_gemm_pair_kernel_variants(ops, M, N, K, b_mn, variant):
     """The CTA-pair kernel's variants on problems with more tiles than CTA pairs: plain (2), automatic (1: K <= 512
-    keeps B resident in shared memory), two pairs per cluster sharing an operand by TMA multicast (4), resident B with
-    column-tile changes (5) -- bf16, f32 + bias + residual, GELU forward / backward epilogues against torch."""
+    keeps B resident in shared memory), resident B with column-tile changes (5) -- bf16, f32 + bias + residual, GELU
+    forward / backward epilogues against torch."""
     g = torch.Generator(device="cuda").manual_seed(M + N + K)
     A = torch.randn(M, K, generator=g, device="cuda").to(BF16)
     W = (torch.randn((K, N) if b_mn else (N, K), generator=g, device="cuda") * 0.2).to(BF16)
@@ -642,18 +642,6 @@ def test_gemm_pair_kernel_variants(ops, M, N, K, b_mn, variant):
     # twice in a row into the same output: the second launch must not depend on shared-memory leftovers
     ops.gemm(A, W, M, N, K, out_bf16=out, bias=bias, **kw)
     assert torch.allclose(out.float(), pre + bias, rtol=2 ** -7, atol=2e-3)
-
-
-@pytest.mark.parametrize("M,N,K,a_mn", [(768, 1024, 40000, True), (1024, 768, 40000, True)])
-def test_gemm_weight_gradient_quad_clusters(ops, M, N, K, a_mn):
-    """dW += X^T dY in 4-CTA clusters (cta_pair=4): pairs neighbouring in n share A, in m share B."""
-    g = torch.Generator(device="cuda").manual_seed(M + K)
-    X = torch.randn(K, M, generator=g, device="cuda").to(BF16)
-    dY = (torch.randn(K, N, generator=g, device="cuda") * 0.1).to(BF16)
-    out = torch.ones(M, N, device="cuda")
-    ops.gemm(X, dY, M, N, K, a_mn=True, b_mn=True, out_f32=out, accumulate=True, cta_pair=4)
-    ref = X.float().t() @ dY.float() + 1
-    assert (out - ref).abs().max().item() <= 2e-5 * ref.abs().max().item() * math.sqrt(K)
 
 
 @pytest.mark.parametrize("bn,pair", [(64, -1), (128, -1), (256, -1), (256, 1)])

@@ -1,4 +1,4 @@
-"""CTA-pair GEMM alone (cta_pair=2) against two pairs per cluster sharing an operand by TMA multicast (cta_pair=1):
+"""The plain CTA-pair GEMM (cta_pair=2) against the automatic choice (cta_pair=1: resident B for K <= 512):
 correctness against torch and time per launch, at the shapes of the ViT-B step."""
 import sys, torch
 sys.path.insert(0, ".")
