@@ -34,6 +34,7 @@ class MAEConfig:
     training_steps: int = 1281167 * 1600 // 4096
     grad_accum: int = 1
     posemb: str = "sincos2d"           # "learnable": model/embed/wpe is a trained parameter (src/modeling.py:115-118)
+    grad_ckpt: bool = False            # nn.remat of every layer (src/modeling.py:232,280): activations are recomputed in backward
     labels: int = 0                    # > 0: classification mode (ViT head, no masking, no decoder; src/modeling.py:239-242,252)
 
     @property

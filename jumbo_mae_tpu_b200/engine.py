@@ -17,6 +17,7 @@ throughout; BASELINE.json's "bf16" is this compute dtype).
 """
 from __future__ import annotations
 
+import copy
 import os
 
 import math
@@ -66,6 +67,16 @@ class _Block:
             self.hj = e(B, 4 * Jd)              # (cn16, gj, dhj16, dc16: slices of the engine's all-layer buffers)
 
 
+def make_blocks(count: int, M: int, dim: int, heads: int, B: int, T: int, J: int, jumbo: bool, dev, share: bool):
+    """The saved activations of ``count`` blocks.  ``share`` (grad_ckpt, the reference's nn.remat of every layer,
+    src/modeling.py:232,280): all blocks use ONE set of buffers -- the forward pass keeps only the block inputs
+    (the f32 residual stream) and the backward pass recomputes a block's activations right before it needs them."""
+    if not share or count <= 1:
+        return [_Block(M, dim, heads, B, T, J, jumbo, dev) for _ in range(count)]
+    first = _Block(M, dim, heads, B, T, J, jumbo, dev)
+    return [first] + [copy.copy(first) for _ in range(count - 1)]     # (per-layer attributes are set on the copies)
+
+
 class MAEEngine:
     """Buffers + kernel schedule for one per-device batch size."""
 
@@ -91,7 +102,8 @@ class MAEEngine:
         self.patches = e(self.Me, self.Pp)
         # encoder
         self.xa: List[torch.Tensor] = [e(self.Me, d, dt=F32) for _ in range(cfg.layers + 1)]
-        self.enc = [_Block(self.Me, d, cfg.heads, B, self.Te, J, True, dev) for _ in range(cfg.layers)]
+        self.remat = bool(getattr(cfg, "grad_ckpt", False))
+        self.enc = make_blocks(cfg.layers, self.Me, d, cfg.heads, B, self.Te, J, True, dev, self.remat)
         # The Jumbo MLP is ONE set of weights applied in every layer (src/modeling.py:234): its inputs and
         # output gradients are kept layer after layer in [layers * B, .] buffers, so that each weight gradient
         # is a single GEMM over K = layers * B at the end of the backward pass instead of one read-modify-write
@@ -107,7 +119,7 @@ class MAEEngine:
         self.y = e(self.Me, dd, dt=F32)
         # decoder
         self.za: List[torch.Tensor] = [e(self.Md, dd, dt=F32) for _ in range(cfg.dec_layers + 1)]
-        self.dec = [_Block(self.Md, dd, cfg.dec_heads, B, self.Td, J, False, dev) for _ in range(cfg.dec_layers)]
+        self.dec = make_blocks(cfg.dec_layers, self.Md, dd, cfg.dec_heads, B, self.Td, J, False, dev, self.remat)
         # Pixel head + loss (src/pretraining.py:110-120).  Fused (default for dec_dim <= 512): dec_norm and the head run on
         # the N - keep masked rows of every image only, gathered into compact [B * n_mask, .] buffers, and the head GEMM's
         # epilogue forms the squared error against the byte targets and its gradient -- the f32 prediction never exists.
@@ -392,6 +404,9 @@ class MAEEngine:
             # ---- decoder blocks
             for i in reversed(range(cfg.dec_layers)):
                 below = ps.grad(f"decoder_model/dec_layer_{i - 1}/ff/w2/bias") if i > 0 else None
+                if self.remat:
+                    self._block_fwd(f"decoder_model/dec_layer_{i}", self.dec[i], self.za[i], self.za[i + 1], Md, dd,
+                                    cfg.dec_heads, Td, False, self._dp(cfg.layers + i))
                 self._block_bwd(f"decoder_model/dec_layer_{i}", self.dec[i], self.za[i], Md, dd, cfg.dec_heads, Td,
                                 False, below, dp=self._dp(cfg.layers + i), lowp=(1 + (i == 0)) if lowp else 0)
             # ---- decoder input assembly + decoder_proj
@@ -407,12 +422,18 @@ class MAEEngine:
         kind, layers = self._segment_plan()[k]
         if kind == "enc":
             for i in layers:
+                if self.remat:
+                    self._block_fwd(f"model/layer_{i}", self.enc[i], self.xa[i], self.xa[i + 1], Me, d, cfg.heads, Te,
+                                    True, self._dp(i))
                 self._block_bwd(f"model/layer_{i}", self.enc[i], self.xa[i], Me, d, cfg.heads, Te, True,
                                 ps.grad(f"model/layer_{i - 1}/ff/w2/bias"), dp=self._dp(i))
         if kind == "jumbo":
             # layer 0's Jumbo branch alone (its patch-FFN and attention branches do not touch the CLS rows'
             # incoming gradient and run in the tail), then the shared Jumbo MLP's weight gradients over all
             # layers at once (K = layers * B)
+            if self.remat:      # (the "rest" part of layer 0 follows in the tail segment and finds the same activations)
+                self._block_fwd("model/layer_0", self.enc[0], self.xa[0], self.xa[1], Me, d, cfg.heads, Te, True,
+                                self._dp(0))
             self._block_bwd("model/layer_0", self.enc[0], self.xa[0], Me, d, cfg.heads, Te, True, None, part="jumbo",
                             dp=self._dp(0))
             L, Jd = cfg.layers, J * d
@@ -625,13 +646,23 @@ class MAEEngine:
 
     # ------------------------------------------------------------------ accounting
     def activation_bytes(self) -> int:
-        tot = 0
+        tot, seen = 0, set()
+
+        def add(t):
+            nonlocal tot
+            key = (t.data_ptr(), t.numel() * t.element_size())
+            if key not in seen:                    # (grad_ckpt: the blocks share one set of buffers)
+                seen.add(key)
+                tot += key[1]
+
         for obj in [self] + self.enc + self.dec:
             for v in vars(obj).values():
                 if isinstance(v, torch.Tensor):
-                    tot += v.numel() * v.element_size()
+                    add(v)
                 elif isinstance(v, list):
-                    tot += sum(t.numel() * t.element_size() for t in v if isinstance(t, torch.Tensor))
+                    for t in v:
+                        if isinstance(t, torch.Tensor):
+                            add(t)
         return tot
 
 

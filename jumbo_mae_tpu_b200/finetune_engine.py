@@ -19,7 +19,7 @@ import torch
 
 from . import _lib, ops
 from .config import MAEConfig
-from .engine import BF16, F32, LN_EPS, MAEEngine, _Block, fixed_sincos2d_embeddings
+from .engine import BF16, F32, LN_EPS, MAEEngine, _Block, fixed_sincos2d_embeddings, make_blocks
 from .params import ParamStore
 
 HEAD = "model/head/Dense_0"     # LinearCLS is nn.compact around one nn.Dense (src/modeling.py:214-219)
@@ -49,7 +49,8 @@ class FinetuneEngine(MAEEngine):
         self.ids_all = torch.arange(N, dtype=torch.int32, device=dev)
         self.patches = e(Me, self.Pp)
         self.xa: List[torch.Tensor] = [e(Me, d, dt=F32) for _ in range(cfg.layers + 1)]
-        self.enc = [_Block(Me, d, cfg.heads, B, self.Te, J, True, dev) for _ in range(cfg.layers)]
+        self.remat = bool(getattr(cfg, "grad_ckpt", False))
+        self.enc = make_blocks(cfg.layers, Me, d, cfg.heads, B, self.Te, J, True, dev, self.remat)
         self.dec: List[_Block] = []          # no decoder in classification mode (activation_bytes walks both lists)
         L, Jd = cfg.layers, J * d
         self.cn16_all, self.gj_all = e(L * B, Jd), e(L * B, 4 * Jd)

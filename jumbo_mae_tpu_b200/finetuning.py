@@ -158,7 +158,8 @@ def create_train_state(args: argparse.Namespace) -> TrainState:
     cfg = MAEConfig(layers=args.layers, dim=args.dim, heads=args.heads, patch_size=args.patch_size,
                     image_size=args.image_size, labels=args.labels, weight_decay=args.weight_decay,
                     adam_b1=args.adam_b1, adam_b2=args.adam_b2, adam_eps=args.adam_eps,
-                    grad_accum=getattr(args, "grad_accum", 1), posemb=getattr(args, "posemb", "sincos2d"))
+                    grad_accum=getattr(args, "grad_accum", 1), posemb=getattr(args, "posemb", "sincos2d"),
+                    grad_ckpt=bool(getattr(args, "grad_ckpt", False)))
     store = ParamStore(cfg)
     gen = torch.Generator(device="cpu").manual_seed(int(getattr(args, "init_seed", 0)))
     for name, leaf in store.leaves.items():           # truncated_normal(0.02) kernels, LN scales 1, the rest 0

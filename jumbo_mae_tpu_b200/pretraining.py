@@ -184,7 +184,8 @@ def create_train_state(args: argparse.Namespace) -> TrainState:
     cfg = module.config(learning_rate=args.learning_rate, train_batch_size=args.train_batch_size,
                         weight_decay=args.weight_decay, adam_b1=args.adam_b1, adam_b2=args.adam_b2,
                         adam_eps=args.adam_eps, warmup_steps=args.warmup_steps, training_steps=args.training_steps,
-                        grad_accum=getattr(args, "grad_accum", 1), posemb=posemb)
+                        grad_accum=getattr(args, "grad_accum", 1), posemb=posemb,
+                        grad_ckpt=bool(getattr(args, "grad_ckpt", False)))
     cfg.validate()
     store = ParamStore(cfg, device=torch.device("cuda", torch.cuda.current_device()))
     init_params_(store, getattr(args, "init_seed", 0))

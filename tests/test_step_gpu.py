@@ -407,3 +407,30 @@ def test_training_step_accepts_lr_decay():
     L = ocfg.layers
     assert abs(moved[0.5][0] / moved[1.0][0] - 0.5 ** L) <= 5e-3 * 0.5 ** L      # f32 rounding of p at steps of 1e-6
     assert abs(moved[0.5][1] / moved[1.0][1] - 1.0) <= 1e-4
+
+
+@pytest.mark.parametrize("name", ["tiny", "mid"])
+def test_grad_ckpt_recomputes_the_same_step(name):
+    """--grad-ckpt (nn.remat of every layer, src/modeling.py:232,280): one shared set of activation buffers, every
+    block's forward recomputed in front of its backward -- the same kernels on the same data, so loss and gradients
+    agree up to the order of the f32 reductions (split-K reduce-adds, vector atomics of the parameter gradients)."""
+    import dataclasses
+    from jumbo_mae_tpu_b200.engine import MAEEngine
+    from jumbo_mae_tpu_b200.params import ParamStore
+    ocfg, cfg, state, images, noise, store, eng = _setup(name)
+    dev_images, dev_noise = images.cuda(), torch.from_numpy(noise).cuda()
+    eng.forward(dev_images, dev_noise)
+    eng.backward()
+    torch.cuda.synchronize()
+    want_loss, want = eng.loss.clone(), store.g.clone()
+    cfg2 = dataclasses.replace(cfg, grad_ckpt=True)
+    store2 = ParamStore(cfg2)
+    store2.load_tree(state.params)
+    eng2 = MAEEngine(cfg2, store2, images.shape[0])
+    assert eng2.remat and eng2.enc[0].qkv.data_ptr() == eng2.enc[-1].qkv.data_ptr()     # one set of buffers
+    assert eng2.activation_bytes() < eng.activation_bytes()
+    eng2.forward(dev_images, dev_noise)
+    eng2.backward()
+    torch.cuda.synchronize()
+    assert abs(eng2.loss.item() - want_loss.item()) <= 1e-6 * abs(want_loss.item())
+    assert _rel(store2.g, want) <= 1e-4
