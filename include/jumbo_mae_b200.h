@@ -294,6 +294,17 @@ int jm_adamw(float* p, const float* g, float* m, float* v, jm_bf16* p_bf16, long
 
 int jm_cast_bf16(const float* x, jm_bf16* y, long n, void* stream);
 
+/* --optimizer lamb: the reference's modified_lamb (src/utils.py:124-139) on the `kernel` leaves of the flat buffers:
+ * Adam moments, u = m_hat / (sqrt(v_hat) + eps) + wd * p, p -= lr * (||p|| / ||u||) * u with the norms over one leaf of
+ * the Flax tree (ratio 1 where a norm is 0).  groups [n_groups, 7] int64 = {offset, rows, ld, col0, ncols, first chunk,
+ * chunk count}: a leaf is a column range of a stored [rows, ld] matrix (wq / wk / wv share one).  chunks [n_chunks, 3]
+ * int64 = {group, row0, nrows}, the chunks of a group consecutive; one thread block per chunk, norms summed in a fixed
+ * order.  Every other leaf takes jm_adamw with wd = 0.  workspace: jm_lamb_workspace(n_chunks) bytes. */
+size_t jm_lamb_workspace(int n_chunks);
+int jm_lamb(float* p, const float* g, float* m, float* v, jm_bf16* p_bf16, const int64_t* groups, int n_groups,
+            const int64_t* chunks, int n_chunks, float lr, float b1, float b2, float eps, float wd, float bc1, float bc2,
+            float grad_scale, void* workspace, size_t workspace_bytes, void* stream);
+
 /* optax.clip_by_global_norm in front of the optimizer (src/pretraining.py:243-244, --clip-grad > 0): with
  * norm = pre_scale * ||g||_2 over the whole flat gradient buffer (pre_scale = 1/(accum*world), the factor the
  * caller folds into jm_adamw), g is left unchanged if norm < max_norm and multiplied by max_norm / norm

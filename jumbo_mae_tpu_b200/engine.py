@@ -633,6 +633,33 @@ class MAEEngine:
         ops.adamw(ps.p, ps.g, ps.m, ps.v, ps.p16, ps.n_decay, lr, cfg.adam_b1, cfg.adam_b2, cfg.adam_eps,
                   cfg.weight_decay, 1.0 - cfg.adam_b1 ** t, 1.0 - cfg.adam_b2 ** t, grad_scale)
 
+    def lamb_step(self, count: int, lr: float, grad_scale: float = 1.0, lr_decay: float = 1.0) -> None:
+        """--optimizer lamb: modified_lamb (src/utils.py:124-139) update number ``count`` -- the kernel leaves take the
+        trust-ratio step (jm_lamb, one norm pair per Flax leaf), every other leaf a plain Adam step (jm_adamw without
+        weight decay); ``lr_decay < 1`` scales the step of label i's leaves as in adamw_step."""
+        cfg, ps = self.cfg, self.ps
+        t = count + 1
+        bc1, bc2 = 1.0 - cfg.adam_b1 ** t, 1.0 - cfg.adam_b2 ** t
+        labels = range(cfg.layers + 1) if lr_decay < 1.0 else [None]
+        if not hasattr(self, "_lamb_tables"):
+            self._lamb_tables = {}
+        for i in labels:
+            sel = (lambda n, i=i: get_layer_index(n, cfg.layers) == i) if i is not None else (lambda n: True)
+            step_lr = lr * (lr_decay ** (cfg.layers - i) if i is not None else 1.0)
+            if i not in self._lamb_tables:              # built once per label (host lists -> two small device tensors)
+                groups, chunks = ps.lamb_tables(sel)
+                ws = None if groups is None else torch.empty(ops.lamb_workspace(chunks.shape[0]), dtype=torch.uint8,
+                                                             device=self.dev)
+                plain = ps.ranges(lambda n, sel=sel: sel(n) and not ps.leaves[n].decay)
+                self._lamb_tables[i] = (groups, chunks, ws, plain)
+            groups, chunks, ws, plain = self._lamb_tables[i]
+            if groups is not None:
+                ops.lamb(ps.p, ps.g, ps.m, ps.v, ps.p16, groups, chunks, step_lr, cfg.adam_b1, cfg.adam_b2, cfg.adam_eps,
+                         cfg.weight_decay, bc1, bc2, grad_scale, ws)
+            for s_, e_ in plain:
+                ops.adamw(ps.p[s_:e_], ps.g[s_:e_], ps.m[s_:e_], ps.v[s_:e_], ps.p16[s_:e_], 0, step_lr, cfg.adam_b1,
+                          cfg.adam_b2, cfg.adam_eps, 0.0, bc1, bc2, grad_scale)
+
     def adamw_ranges(self, ranges, count: int, lr: float, grad_scale: float = 1.0) -> None:
         """The same update restricted to [start, end) ranges of the flat buffers (multiples of 64 elements): lets
         a data-parallel step update the parameters of a backward segment as soon as its gradients are reduced,

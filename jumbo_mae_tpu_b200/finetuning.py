@@ -90,6 +90,7 @@ class TrainState:
     lr_decay: float = 1.0
     clip_grad: float = 0.0
     droppath: float = 0.0
+    optimizer: str = "adamw"    # adamw | lamb (modified_lamb, src/utils.py:124-139; src/finetuning.py:45,232-240)
     micro_step: int = 0
     micro_in_mini: int = 1
     batch_stats: Any = None
@@ -143,8 +144,8 @@ class TrainState:
 def create_train_state(args: argparse.Namespace) -> TrainState:
     """src/finetuning.py:168-284 for the adamw + cross-entropy fine-tune recipe."""
     _lib.require_device()
-    if getattr(args, "optimizer", "adamw") != "adamw":
-        raise NotImplementedError("only --optimizer adamw is built")
+    if getattr(args, "optimizer", "adamw") not in ("adamw", "lamb"):
+        raise NotImplementedError("--optimizer must be adamw or lamb (sgd / lars are not built)")
     if getattr(args, "criterion", "ce") != "ce":
         raise NotImplementedError("only --criterion ce is built")
     if getattr(args, "mode", "finetune") == "linear":
@@ -187,7 +188,7 @@ def _new_state(args: argparse.Namespace, store: ParamStore, cfg: MAEConfig) -> T
                       label_smoothing=float(getattr(args, "label_smoothing", 0.1)), mixup=float(getattr(args, "mixup", 0.8)),
                       cutmix=float(getattr(args, "cutmix", 1.0)), lr_decay=float(getattr(args, "lr_decay", 1.0)),
                       clip_grad=float(getattr(args, "clip_grad", 0.0)), micro_in_mini=int(getattr(args, "grad_accum", 1)),
-                      droppath=float(getattr(args, "droppath", 0.0)))
+                      droppath=float(getattr(args, "droppath", 0.0)), optimizer=getattr(args, "optimizer", "adamw"))
 
 
 def _to_device(t, dev, dtype):
@@ -245,7 +246,8 @@ def training_step(state: TrainState, batch, mix: Optional[MixDraw] = None, drop_
             if not hasattr(state, "_sumsq"):
                 state._sumsq = torch.zeros(1, dtype=torch.float32, device=dev)
             ops.clip_by_global_norm(state.store.g, 1.0 / (accum * world), state.clip_grad, state._sumsq)
-        eng.adamw_step(state.step, lr, grad_scale=1.0 / (accum * world), lr_decay=state.lr_decay)
+        step_fn = eng.lamb_step if state.optimizer == "lamb" else eng.adamw_step
+        step_fn(state.step, lr, grad_scale=1.0 / (accum * world), lr_decay=state.lr_decay)
         state.step += 1
         state.micro_step = 0
     return state, {"loss": metrics[0], "acc1": metrics[1], "acc5": metrics[2], "learning_rate": lr}

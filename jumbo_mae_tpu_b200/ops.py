@@ -289,6 +289,21 @@ def gemm(A: torch.Tensor, B: torch.Tensor, M: int, N: int, K: int, *, a_mn: bool
     check(_lib.load().jm_gemm(ctypes.byref(a), stream_ptr()))
 
 
+def lamb_workspace(n_chunks: int) -> int:
+    return int(_lib.load().jm_lamb_workspace(n_chunks))
+
+
+def lamb(p: torch.Tensor, g: torch.Tensor, m: torch.Tensor, v: torch.Tensor, p_bf16: Optional[torch.Tensor],
+         groups: torch.Tensor, chunks: torch.Tensor, lr: float, b1: float, b2: float, eps: float, wd: float, bc1: float,
+         bc2: float, grad_scale: float, workspace: torch.Tensor) -> None:
+    """modified_lamb (src/utils.py:124-139) on the kernel leaves listed in ``groups`` / ``chunks`` (params.lamb_tables)."""
+    _chk(p, F32, "p"), _chk(g, F32, "g"), _chk(m, F32, "m"), _chk(v, F32, "v"), _chk(p_bf16, BF16, "p_bf16")
+    _chk(groups, torch.int64, "groups"), _chk(chunks, torch.int64, "chunks")
+    check(_lib.load().jm_lamb(ptr(p), ptr(g), ptr(m), ptr(v), ptr(p_bf16), ptr(groups), groups.shape[0], ptr(chunks),
+                              chunks.shape[0], lr, b1, b2, eps, wd, bc1, bc2, grad_scale, ptr(workspace),
+                              workspace.numel() * workspace.element_size(), stream_ptr()))
+
+
 # ------------------------------------------------------------------ attention
 def attention_fwd(qkv: torch.Tensor, batch: int, T: int, heads: int, head_dim: int, out: torch.Tensor,
                   lse: torch.Tensor) -> None:

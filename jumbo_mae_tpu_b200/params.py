@@ -166,6 +166,28 @@ class ParamStore:
                 out.append((start, end))
         return out
 
+    def lamb_tables(self, select=None, chunk_elems: int = 32768):
+        """Group / chunk tables of jm_lamb over the ``kernel`` leaves whose name satisfies ``select`` (all by default).
+        A group is one kernel leaf of the FLAX tree -- the trust ratio of modified_lamb (src/utils.py:124-139) is taken
+        per leaf -- i.e. a column range of a stored matrix: the fused ``wqkv`` kernel holds wq, wk and wv.  Returns
+        (groups int64 [G, 7], chunks int64 [C, 3]) on the store's device, or (None, None) if nothing is selected."""
+        groups, chunks = [], []
+        for leaf in sorted(self.leaves.values(), key=lambda l: l.offset):
+            if not leaf.decay or (select is not None and not select(leaf.name)):
+                continue
+            parts = 3 if leaf.name.endswith("/wqkv/kernel") else 1
+            width = leaf.cols // parts
+            for i in range(parts):
+                rows_per = max(1, chunk_elems // width)
+                first = len(chunks)
+                for r0 in range(0, leaf.rows, rows_per):
+                    chunks.append([len(groups), r0, min(rows_per, leaf.rows - r0)])
+                groups.append([leaf.offset, leaf.rows, leaf.ld, i * width, width, first, len(chunks) - first])
+        if not groups:
+            return None, None
+        return (torch.tensor(groups, dtype=torch.int64, device=self.device),
+                torch.tensor(chunks, dtype=torch.int64, device=self.device))
+
     # ------------------------------------------------------------- Flax-shaped trees
     def tree(self, buf: torch.Tensor | None = None) -> dict:
         """The reference's parameter pytree as views into ``buf`` (default: f32 masters)."""

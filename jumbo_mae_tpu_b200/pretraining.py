@@ -76,6 +76,7 @@ class TrainState:
     reducer: Optional[GradReducer] = None
     _noise_gen: Optional[np.random.Generator] = None
     lr_decay: float = 1.0       # --lr-decay: layer-wise learning-rate scale table behind adamw (src/pretraining.py:235-242)
+    optimizer: str = "adamw"    # --optimizer adamw | lamb (modified_lamb, src/utils.py:124-139)
     clip_grad: float = 0.0      # --clip-grad: optax.clip_by_global_norm in front of adamw (src/pretraining.py:243-244)
 
     @property
@@ -167,8 +168,8 @@ def create_train_state(args: argparse.Namespace) -> TrainState:
     parameters (truncated-normal(0.02) kernels, zero biases / CLS, unit LayerNorm scales) and the
     AdamW state, seeds the RNG streams with ``seed + process_index``."""
     _lib.require_device()
-    if getattr(args, "optimizer", "adamw") != "adamw":
-        raise NotImplementedError("only --optimizer adamw (both pre-training presets) is on the hot path")
+    if getattr(args, "optimizer", "adamw") not in ("adamw", "lamb"):
+        raise NotImplementedError("--optimizer must be adamw (both pre-training presets) or lamb")
     for nm in ("dropout", "dec_dropout"):
         if getattr(args, nm, 0.0) != 0.0:
             raise NotImplementedError(f"--{nm.replace('_', '-')} > 0 is not built (0.0 in both presets)")
@@ -194,7 +195,7 @@ def create_train_state(args: argparse.Namespace) -> TrainState:
                       dropout_rng=getattr(args, "dropout_seed", 0) + process_index(),
                       noise_rng=getattr(args, "noise_seed", 0) + process_index(),
                       micro_step=0, micro_in_mini=cfg.grad_accum, clip_grad=float(getattr(args, "clip_grad", 0.0)),
-                      lr_decay=float(getattr(args, "lr_decay", 1.0)))
+                      lr_decay=float(getattr(args, "lr_decay", 1.0)), optimizer=getattr(args, "optimizer", "adamw"))
 
 
 def init_params_(store: ParamStore, seed: int) -> None:
@@ -258,7 +259,8 @@ def training_step(state: TrainState, batch, noise=None) -> Tuple[TrainState, Dic
         # gradient all-reduce overlapped with the backward pass (lax.pmean(grads), :150); without gradient clipping
         # (which needs the global norm) each segment's parameters are also updated as soon as its sum has arrived
         hook = None
-        if state.clip_grad == 0 and state.lr_decay >= 1.0 and state.reducer.stream is not None:
+        if (state.clip_grad == 0 and state.lr_decay >= 1.0 and state.reducer.stream is not None
+                and state.optimizer == "adamw"):       # (lamb's trust ratios are per leaf: reduce, then update)
             lr_now, cnt = lr_schedule(state.step, state.cfg), state.step
             hook = lambda ranges: eng.adamw_ranges(ranges, cnt, lr_now, grad_scale=1.0 / (accum * world))
             updated = True
@@ -283,7 +285,8 @@ def training_step(state: TrainState, batch, noise=None) -> Tuple[TrainState, Dic
                 state._sumsq = torch.zeros(1, dtype=torch.float32, device=state.store.device)
             ops.clip_by_global_norm(state.store.g, 1.0 / (accum * world), state.clip_grad, state._sumsq)
         if not updated:
-            eng.adamw_step(state.step, lr, grad_scale=1.0 / (accum * world), lr_decay=state.lr_decay)
+            step_fn = eng.lamb_step if state.optimizer == "lamb" else eng.adamw_step
+            step_fn(state.step, lr, grad_scale=1.0 / (accum * world), lr_decay=state.lr_decay)
         state.step += 1
         state.micro_step = 0
     return state, {"loss": metrics_loss[0], "learning_rate": lr}

@@ -563,6 +563,24 @@ def adamw_leaf(p, g, m, v, count: int, lr: float, cfg: MAEConfig, decay: bool):
     return p - lr * u, m, v
 
 
+def lamb_leaf(p, g, m, v, count: int, lr: float, cfg: MAEConfig, decay: bool):
+    """One leaf update of the reference's ``modified_lamb`` (src/utils.py:124-139): optax.chain(scale_by_adam,
+    add_decayed_weights(mask), masked(scale_by_trust_ratio(), mask), scale_by_learning_rate), mask = kernel leaves.
+    scale_by_trust_ratio (optax, defaults min_norm=0, trust_coefficient=1, eps=0, restated from its published
+    definition): update * ||param|| / ||update||, and * 1 where either norm is 0."""
+    b1, b2 = cfg.adam_b1, cfg.adam_b2
+    m = b1 * m + (1.0 - b1) * g
+    v = b2 * v + (1.0 - b2) * g * g
+    t = count + 1
+    u = (m / (1.0 - b1 ** t)) / (torch.sqrt(v / (1.0 - b2 ** t)) + cfg.adam_eps)
+    if decay:
+        u = u + cfg.weight_decay * p
+        pn, un = torch.linalg.vector_norm(p), torch.linalg.vector_norm(u)
+        ratio = torch.where((pn == 0) | (un == 0), torch.ones_like(pn), pn / un)
+        u = u * ratio
+    return p - lr * u, m, v
+
+
 @dataclass
 class OracleState:
     """The numeric part of TrainState (src/pretraining.py:50-57)."""

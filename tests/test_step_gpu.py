@@ -9,6 +9,8 @@ Tolerances (bf16 operands / f32 accumulation vs an f32 reference, SURVEY.md sect
   per-leaf gradient (relative L2)      <= 3e-2, cosine >= 0.999
   k-step parameter delta (relative L2) <= 5e-2 on leaves whose update is not sign-noise
 """
+import math
+
 import numpy as np
 import pytest
 import torch
@@ -434,3 +436,56 @@ def test_grad_ckpt_recomputes_the_same_step(name):
     torch.cuda.synchronize()
     assert abs(eng2.loss.item() - want_loss.item()) <= 1e-6 * abs(want_loss.item())
     assert _rel(store2.g, want) <= 1e-4
+
+
+@pytest.mark.parametrize("lr_decay", [1.0, 0.75])
+def test_lamb_step_matches_oracle(lr_decay):
+    """--optimizer lamb (modified_lamb, src/utils.py:124-139): after one backward pass, engine.lamb_step against the
+    oracle's lamb_leaf applied to every leaf of the Flax tree with the engine's own gradients -- trust ratio per Flax
+    leaf (wq / wk / wv separately although they are stored fused), plain Adam on the non-kernel leaves, the layer-wise
+    lr table behind it, moments updated once, bf16 copy refreshed."""
+    import dataclasses
+    from jumbo_mae_tpu_b200.params import tree_leaves
+    ocfg, cfg, state, images, noise, store, eng = _setup("tiny")
+    eng.forward(images.cuda(), torch.from_numpy(noise).cuda())
+    eng.backward()
+    torch.cuda.synchronize()
+    store.m.normal_(0, 1e-3)
+    store.v.uniform_(0, 1e-6)
+    params0 = {path: p.detach().cpu().clone() for path, p in tree_leaves(store.tree(store.p))}
+    grads = {path: g.detach().cpu().clone() for path, g in tree_leaves(store.tree(store.g))}
+    mus = {path: t.detach().cpu().clone() for path, t in tree_leaves(store.tree(store.m))}
+    nus = {path: t.detach().cpu().clone() for path, t in tree_leaves(store.tree(store.v))}
+    count, lr, gscale = 3, 2e-3, 0.5
+    eng.lamb_step(count, lr, grad_scale=gscale, lr_decay=lr_decay)
+    torch.cuda.synchronize()
+    dcfg = dataclasses.replace(ocfg, lr_decay=lr_decay)
+    got_p = dict(tree_leaves(store.tree(store.p)))
+    got_m = dict(tree_leaves(store.tree(store.m)))
+    ratios = []
+    for path, p0 in params0.items():
+        decay = path[-1] == "kernel"
+        want_p, want_m, _ = O.lamb_leaf(p0, grads[path] * gscale, mus[path], nus[path], count,
+                                        lr * O.layerwise_scale(path, dcfg), dcfg, decay=decay)
+        step = (want_p - p0).abs().max().item()
+        assert (got_p[path].detach().cpu() - want_p).abs().max().item() <= 2e-4 * step + 1e-8, path
+        assert torch.allclose(got_m[path].detach().cpu(), want_m, rtol=1e-5, atol=1e-9), path
+        if decay:
+            plain, _, _ = O.adamw_leaf(p0, grads[path] * gscale, mus[path], nus[path], count,
+                                       lr * O.layerwise_scale(path, dcfg), dcfg, decay=True)
+            ratios.append(step / max((plain - p0).abs().max().item(), 1e-30))
+    assert max(ratios) / min(ratios) > 1.5            # the trust ratios differ from leaf to leaf (and from 1)
+    assert torch.equal(store.p16, store.p.to(torch.bfloat16))
+
+
+def test_training_step_accepts_lamb():
+    """create_train_state(--optimizer lamb) builds and steps (src/pretraining.py:45-46)."""
+    from jumbo_mae_tpu_b200.pretraining import create_train_state, training_step
+    ocfg = O.tiny()
+    images, noise = O.synthetic_batch(ocfg, 4, seed=5, noise_seed=6)
+    state = create_train_state(_tiny_args(optimizer="lamb")).replicate()
+    before = state.store.p.clone()
+    state, metrics = training_step(state, (images,), noise=noise)
+    torch.cuda.synchronize()
+    assert state.step == 1 and math.isfinite(metrics["loss"].item())
+    assert not torch.equal(state.store.p, before)
