@@ -110,6 +110,22 @@ int jm_posemb_grad(const float* dx, long ldx, int batch, int T, int J, int n, co
 int jm_scale_rows_bf16(jm_bf16* x, long ld, long rows, int cols, const float* scale, const float* scale_cls, int period,
                        int skip, void* stream);
 
+/* jm_scale_rows_bf16 with per-column factors as well (any of the four may be NULL = 1): col_scale [cols] on the rows
+ * r % period >= skip, col_scale_cls [skip * cols] on the others (row t of a period uses entries t * cols ...).  The
+ * gradient that enters a LayerScale-d branch is dy * scale (src/modeling.py:165-166,192-201). */
+int jm_scale_bf16(jm_bf16* x, long ld, long rows, int cols, const float* scale, const float* scale_cls, int period,
+                  int skip, const float* col_scale, const float* col_scale_cls, void* stream);
+
+/* d scale (+=) of a LayerScale vector from the ACCUMULATED gradients of the Dense it scales (call once per optimizer
+ * step, after the last micro-step / the all-reduce): dscale[n] += (sum_k W[k, n] dW[k, n] + b[n] db[n]) / scale[n]
+ * with W, dW [K, N] f32 of row stride ld; see csrc/elementwise.cu for the identity.  jm_layerscale_cls_grad is the
+ * per-layer form for scale3, whose Dense (the Jumbo MLP) is shared by all layers: dy, c_out (the layer's output CLS
+ * rows) and c (its LayerNorm-ed input) are [batch, N] f32 views, dscale[n] += sum_b dy (c_out - c) / scale[n]. */
+int jm_layerscale_grad(const float* W, const float* dW, long ld, int K, int N, const float* b, const float* db,
+                       const float* scale, float* dscale, void* stream);
+int jm_layerscale_cls_grad(const float* dy, long lddy, const float* c_out, long ldo, const float* c, long ldc, int batch,
+                           int N, const float* scale, float* dscale, void* stream);
+
 /* patch_mse_loss(patch_output, patch_target, valid=None) with explicit targets, exactly src/utils_mae.py:51-64:
  * mean over images of [ mean_L( valid > 0 ? mean_c (target - output)^2 : 0 ) / (sum(valid) / L) ].
  * patch_output / patch_target are [batch*L, P] f32 with row strides ldo / ldt; valid is [batch, L] f32 or NULL
@@ -249,6 +265,9 @@ typedef struct jm_gemm_args {
    * stats[row, 1] when loss_stats != NULL (norm_pix_loss).  jm_masked_targets produces loss_target / loss_stats.
    * A K-major, B MN-major, no other epilogue option; ld_target a multiple of 16 >= N, ldo_bf16 >= N rounded up to 8. */
   const uint8_t* loss_target; long ld_target; const float* loss_stats; float* row_loss; float loss_scale;
+  /* optional [N] (out_f32 epilogue): out_f32 = row_scale * col_scale_vec[col] * (acc + bias) + residual -- LayerScale's
+   * scale1 / scale2 / scale3 on a residual branch (src/modeling.py:159-166,185-201) */
+  const float* col_scale_vec;
 } jm_gemm_args;
 int jm_gemm(const jm_gemm_args* args, void* stream);
 

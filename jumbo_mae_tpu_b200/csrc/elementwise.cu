@@ -401,7 +401,11 @@ __global__ void posemb_grad_kernel(const float* __restrict__ dx, long ldx, int b
 // (the gradient that enters the branch is the block-output gradient times the image's keep-mask / (1 - p))
 __global__ void scale_rows_bf16_kernel(__nv_bfloat16* __restrict__ x, long ld, long rows, int cols,
                                        const float* __restrict__ scale, const float* __restrict__ scale_cls, int period,
-                                       int skip) {
+                                       int skip, const float* __restrict__ col_scale,
+                                       const float* __restrict__ col_scale_cls) {
+  // LayerScale (src/modeling.py:159-166,185-201): besides the per-image factor, a per-column one -- col_scale [cols] on
+  // the rows of the patch branch, col_scale_cls [skip * cols] on the CLS rows (scale3 spans the concatenated CLS tokens);
+  // any of the four factors may be absent (= 1)
   const int chunks = cols >> 3;
   const long total = rows * chunks;
   for (long i = static_cast<long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
@@ -409,16 +413,72 @@ __global__ void scale_rows_bf16_kernel(__nv_bfloat16* __restrict__ x, long ld, l
     const long r = i / chunks;
     const int c = static_cast<int>(i - r * chunks);
     const long img = r / period;
-    const float s = (scale_cls != nullptr && r - img * period < skip) ? scale_cls[img] : scale[img];
+    const int t = static_cast<int>(r - img * period);
+    const bool cls = t < skip;
+    const float* rs = (cls && scale_cls != nullptr) ? scale_cls : scale;
+    const float s_ = rs != nullptr ? rs[img] : 1.0f;
+    const float* cs = cls ? (col_scale_cls != nullptr ? col_scale_cls + static_cast<long>(t) * cols : nullptr) : col_scale;
     uint4* p = reinterpret_cast<uint4*>(x + r * ld + c * 8);
     uint4 v = *p;
     uint32_t w[4] = {v.x, v.y, v.z, v.w};
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
       const float2 f = unpack_bf16(w[k]);
-      w[k] = pack_bf16(f.x * s, f.y * s);
+      const float c0 = cs != nullptr ? cs[c * 8 + 2 * k] : 1.0f, c1 = cs != nullptr ? cs[c * 8 + 2 * k + 1] : 1.0f;
+      w[k] = pack_bf16(f.x * s_ * c0, f.y * s_ * c1);
     }
     *p = make_uint4(w[0], w[1], w[2], w[3]);
+  }
+}
+
+// d scale of a LayerScale vector from the accumulated parameter gradients of the Dense it scales: with y = scale * z,
+// z = a W + b, the step accumulates dW' = a^T (dy * scale) = (a^T dy) * scale and db' = colsum(dy * scale), and
+//   d scale[n] = sum_rows dy[., n] z[., n] = (sum_k W[k, n] dW'[k, n] + b[n] db'[n]) / scale[n]
+// -- no activation is kept for it.  (scale[n] == 0 gives no contribution: the formula has no value there.)
+__global__ void __launch_bounds__(256)
+layerscale_grad_kernel(const float* __restrict__ W, const float* __restrict__ dW, long ld, int K, int N,
+                       const float* __restrict__ b, const float* __restrict__ db, const float* __restrict__ gamma,
+                       float* __restrict__ dgamma) {
+  // block: 32 columns x 8 row lanes
+  __shared__ float red[8][33];
+  const int cx = threadIdx.x & 31, ry = threadIdx.x >> 5;
+  const int n = blockIdx.x * 32 + cx;
+  float acc = 0.f;
+  if (n < N)
+    for (int k = ry; k < K; k += 8) acc = fmaf(W[static_cast<long>(k) * ld + n], dW[static_cast<long>(k) * ld + n], acc);
+  red[ry][cx] = acc;
+  __syncthreads();
+  if (ry == 0 && n < N) {
+    float t = 0.f;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) t += red[j][cx];
+    t = fmaf(b[n], db[n], t);
+    const float g = gamma[n];
+    if (g != 0.f) dgamma[n] += t / g;
+  }
+}
+
+// The same for scale3 of a JumboLayer, whose Dense (the Jumbo MLP) is shared by all layers: from the layer's own CLS
+// rows, d scale3[n] = sum_b dy[b, n] (c_out[b, n] - c[b, n]) / scale3[n], since c_out - c = drop3 * scale3 * z.
+__global__ void __launch_bounds__(256)
+layerscale_cls_grad_kernel(const float* __restrict__ dy, long lddy, const float* __restrict__ c_out, long ldo,
+                           const float* __restrict__ c, long ldc, int batch, int N, const float* __restrict__ gamma,
+                           float* __restrict__ dgamma) {
+  __shared__ float red[8][33];
+  const int cx = threadIdx.x & 31, ry = threadIdx.x >> 5;
+  const int n = blockIdx.x * 32 + cx;
+  float acc = 0.f;
+  if (n < N)
+    for (int r = ry; r < batch; r += 8)
+      acc = fmaf(dy[r * lddy + n], c_out[r * ldo + n] - c[r * ldc + n], acc);
+  red[ry][cx] = acc;
+  __syncthreads();
+  if (ry == 0 && n < N) {
+    float t = 0.f;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) t += red[j][cx];
+    const float g = gamma[n];
+    if (g != 0.f) dgamma[n] += t / g;
   }
 }
 
@@ -1135,15 +1195,38 @@ extern "C" int jm_posemb_grad(const float* dx, long ldx, int batch, int T, int J
   return 0;
 }
 
-extern "C" int jm_scale_rows_bf16(jm_bf16* x, long ld, long rows, int cols, const float* scale, const float* scale_cls,
-                                  int period, int skip, void* stream) {
-  JM_CHECK(x && scale && rows > 0 && cols > 0 && period > 0, "jm_scale_rows_bf16: bad arguments");
+extern "C" int jm_scale_bf16(jm_bf16* x, long ld, long rows, int cols, const float* scale, const float* scale_cls,
+                             int period, int skip, const float* col_scale, const float* col_scale_cls, void* stream) {
+  JM_CHECK(x && period > 0 && skip >= 0 && skip <= period, "jm_scale_bf16: bad argument");
   JM_CHECK(cols % 8 == 0 && ld % 8 == 0 && (reinterpret_cast<uintptr_t>(x) & 15) == 0,
-           "jm_scale_rows_bf16: cols and ld must be multiples of 8 and x 16-byte aligned");
+           "jm_scale_bf16: cols and ld must be multiples of 8 and x 16-byte aligned");
+  if (rows == 0) return 0;
   const long total = rows * (cols / 8);
   const int blocks = static_cast<int>(total / 256 + 1 < 148L * 16 ? total / 256 + 1 : 148L * 16);
   scale_rows_bf16_kernel<<<blocks, 256, 0, STREAM>>>(reinterpret_cast<__nv_bfloat16*>(x), ld, rows, cols, scale,
-                                                     scale_cls, period, skip);
+                                                     scale_cls, period, skip, col_scale, col_scale_cls);
+  JM_AFTER_LAUNCH();
+  return 0;
+}
+
+extern "C" int jm_scale_rows_bf16(jm_bf16* x, long ld, long rows, int cols, const float* scale, const float* scale_cls,
+                                  int period, int skip, void* stream) {
+  JM_CHECK(scale, "jm_scale_rows_bf16: null argument");
+  return jm_scale_bf16(x, ld, rows, cols, scale, scale_cls, period, skip, nullptr, nullptr, stream);
+}
+
+extern "C" int jm_layerscale_grad(const float* W, const float* dW, long ld, int K, int N, const float* b,
+                                  const float* db, const float* scale, float* dscale, void* stream) {
+  JM_CHECK(W && dW && b && db && scale && dscale && K > 0 && N > 0, "jm_layerscale_grad: bad argument");
+  layerscale_grad_kernel<<<(N + 31) / 32, 256, 0, STREAM>>>(W, dW, ld, K, N, b, db, scale, dscale);
+  JM_AFTER_LAUNCH();
+  return 0;
+}
+
+extern "C" int jm_layerscale_cls_grad(const float* dy, long lddy, const float* c_out, long ldo, const float* c, long ldc,
+                                      int batch, int N, const float* scale, float* dscale, void* stream) {
+  JM_CHECK(dy && c_out && c && scale && dscale && batch > 0 && N > 0, "jm_layerscale_cls_grad: bad argument");
+  layerscale_cls_grad_kernel<<<(N + 31) / 32, 256, 0, STREAM>>>(dy, lddy, c_out, ldo, c, ldc, batch, N, scale, dscale);
   JM_AFTER_LAUNCH();
   return 0;
 }

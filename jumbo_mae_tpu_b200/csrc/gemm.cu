@@ -92,6 +92,8 @@ struct EpiParams {
   const float* loss_stats;     // optional [M, 2]: norm_pix mean and 1 / sqrt(var + eps) of the row's normalised target
   float* row_loss;             // [M, ceil(N / 16)]
   float loss_scale;
+  const float* col_vec;        // optional [N]: (acc + bias) is multiplied by col_vec[col] before row_scale and the residual
+                               // (LayerScale, src/modeling.py:159-166,185-201); f32 TMA epilogue only
 };
 
 template <int BN>
@@ -994,6 +996,13 @@ __device__ __forceinline__ void epilogue_f32_tma(const EpiParams& ep, const Gemm
       const int col = colp + 32 * i + lane;
       bs[i] = (has_bias && col < sh.N && 32 * i + lane < PART_N) ? __ldg(ep.bias + col) : 0.f;
     }
+    const bool has_cv = ep.col_vec != nullptr;
+    float gs[NB];
+#pragma unroll
+    for (int i = 0; i < NB; ++i) {
+      const int col = colp + 32 * i + lane;
+      gs[i] = (has_cv && col < sh.N && 32 * i + lane < PART_N) ? __ldg(ep.col_vec + col) : 1.f;
+    }
     // optional per-image scale of the branch output (this thread's row), applied before the residual is added
     const bool has_rs = ep.row_scale != nullptr;
     float rs = 1.f;
@@ -1039,6 +1048,12 @@ __device__ __forceinline__ void epilogue_f32_tma(const EpiParams& ep, const Gemm
             const int l0 = (16 * c) % 32 + 4 * j;
             v.x += __shfl_sync(kFull, bsrc, l0), v.y += __shfl_sync(kFull, bsrc, l0 + 1);
             v.z += __shfl_sync(kFull, bsrc, l0 + 2), v.w += __shfl_sync(kFull, bsrc, l0 + 3);
+          }
+          if (has_cv) {  // warp-uniform
+            const float gsrc = gs[(16 * c) / 32];
+            const int l0 = (16 * c) % 32 + 4 * j;
+            v.x *= __shfl_sync(kFull, gsrc, l0), v.y *= __shfl_sync(kFull, gsrc, l0 + 1);
+            v.z *= __shfl_sync(kFull, gsrc, l0 + 2), v.w *= __shfl_sync(kFull, gsrc, l0 + 3);
           }
           if (has_rs) v.x *= rs, v.y *= rs, v.z *= rs, v.w *= rs;  // warp-uniform branch
           x.x += v.x, x.y += v.y, x.z += v.z, x.w += v.w;
@@ -1891,6 +1906,7 @@ extern "C" int jm_gemm(const jm_gemm_args* a, void* stream_) {
   ep.accumulate = (a->accumulate || splits > 1) ? 1 : 0;
   ep.colsum = a->colsum;
   ep.row_scale = a->row_scale, ep.row_scale_period = a->row_scale_period;
+  ep.col_vec = a->col_scale_vec;
   ep.loss_target = a->loss_target, ep.ld_target = a->ld_target, ep.loss_stats = a->loss_stats;
   ep.row_loss = a->row_loss, ep.loss_scale = a->loss_scale;
   JM_CHECK(!a->row_scale || a->row_scale_period > 0, "jm_gemm: row_scale needs row_scale_period > 0");
@@ -1934,6 +1950,8 @@ extern "C" int jm_gemm(const jm_gemm_args* a, void* stream_) {
       return 1;
     ep.tma_store = 1;
   }
+  JM_CHECK(!ep.col_vec || (epi == EPI_F32 && ep.tma_store),
+           "jm_gemm: col_scale_vec is built for the f32 output epilogue (out_f32 only, no pe / row mask / col_scale)");
   JM_CHECK(!ep.row_scale || (epi == EPI_F32 && ep.tma_store),
            "jm_gemm: row_scale is built for the f32 output epilogue (out_f32 only, no pe / row mask / col_scale)");
   if (pair) {

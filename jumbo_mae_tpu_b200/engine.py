@@ -102,6 +102,8 @@ class MAEEngine:
         self.patches = e(self.Me, self.Pp)
         # encoder
         self.xa: List[torch.Tensor] = [e(self.Me, d, dt=F32) for _ in range(cfg.layers + 1)]
+        self.ls_enc = bool(getattr(cfg, "layerscale", False))        # LayerScale on the encoder / decoder branches
+        self.ls_dec = bool(getattr(cfg, "dec_layerscale", False))
         self.remat = bool(getattr(cfg, "grad_ckpt", False))
         self.enc = make_blocks(cfg.layers, self.Me, d, cfg.heads, B, self.Te, J, True, dev, self.remat)
         # The Jumbo MLP is ONE set of weights applied in every layer (src/modeling.py:234): its inputs and
@@ -293,13 +295,16 @@ class MAEEngine:
         ps, B, J = self.ps, self.B, self.cfg.num_cls_tokens
         hd = dim // heads
         rs = (lambda k: dict(row_scale=dp[k], row_scale_period=T)) if dp is not None else (lambda k: {})
+        ls = self.ls_enc if jumbo else self.ls_dec
+        # LayerScale (src/modeling.py:159-166,185-201): the branch output times scale_k, per column, in the same epilogue
+        cv = (lambda k: dict(col_vec=ps.f(f"{name}/scale{k}"))) if ls else (lambda k: {})
         # x_b = x + drop_path1(attn(LN1(x)))            (src/modeling.py:165 / :192)
         ops.layernorm_fwd(x_in, ps.f(f"{name}/norm1/scale"), ps.f(f"{name}/norm1/bias"), LN_EPS, s.xn1, None,
                           s.mean1, s.rstd1)
         self._fwd_linear(s.xn1, M, f"{name}/attn/wqkv", 3 * dim, dim, out_bf16=s.qkv, col_scale=hd ** -0.5,
                          col_scale_n=dim)
         ops.attention_fwd(s.qkv, B, T, heads, hd, s.att, s.lse)
-        self._fwd_linear(s.att, M, f"{name}/attn/wo", dim, dim, out_f32=s.xb, residual=x_in, **rs(0))
+        self._fwd_linear(s.att, M, f"{name}/attn/wo", dim, dim, out_f32=s.xb, residual=x_in, **rs(0), **cv(1))
         period, skip = (T, J) if jumbo else (0, 0)
         # patch tokens: x = x_b + drop_path2(ff(LN2(x_b)))       (src/modeling.py:166 / :201)
         ops.layernorm_fwd(s.xb, ps.f(f"{name}/norm2/scale"), ps.f(f"{name}/norm2/bias"), LN_EPS, s.xn2, None,
@@ -308,23 +313,24 @@ class MAEEngine:
                          row_period=period, row_skip=skip, row_mask_mode=1 if jumbo else 0)
         # (every row is written, so that the output tiles can leave by TMA; the CLS rows of a Jumbo block get
         #  x_b + bias here -- their h/g rows are zero -- and are overwritten by the Jumbo MLP just below)
-        self._fwd_linear(s.g, M, f"{name}/ff/w2", dim, 4 * dim, out_f32=x_out, residual=s.xb, **rs(1))
+        self._fwd_linear(s.g, M, f"{name}/ff/w2", dim, 4 * dim, out_f32=x_out, residual=s.xb, **rs(1), **cv(2))
         if jumbo:
             Jd = J * dim
             # c = LN3(cls concat); c = c + drop_path3(jumbo_mlp(c))      (src/modeling.py:194-199)
             ops.layernorm_fwd(s.xb, ps.f(f"{name}/norm3/scale"), ps.f(f"{name}/norm3/bias"), LN_EPS, s.cn16, s.cn,
                               s.mean3, s.rstd3, rows=B, dim=Jd, ldx=T * dim, ldy=Jd, ldyf=Jd)
             self._fwd_linear(s.cn16, B, "model/jumbo_mlp/w1", 4 * Jd, Jd, out_bf16=s.hj, out2_bf16=s.gj, act=GELU_FWD)
-            if dp is None:
+            if dp is None and not ls:
                 # w2 has few output tiles and a long K: seed the CLS rows with c + bias, then split-K accumulate
                 ops.add_bias_cast(s.cn, B, Jd, bias=ps.f("model/jumbo_mlp/w2/bias"), dst_f32=x_out, ldd=T * dim)
                 ops.gemm(s.gj, self._W("model/jumbo_mlp/w2/kernel"), B, Jd, 4 * Jd, b_mn=True,
                          ldb=ps.ld("model/jumbo_mlp/w2/kernel"), out_f32=x_out, ldo_f32=T * dim, accumulate=True)
             else:
-                # with DropPath the branch (bias included) is scaled per image before c is added: one pass over K
+                # with DropPath / LayerScale the branch (bias included) is scaled before c is added: one pass over K
                 ops.gemm(s.gj, self._W("model/jumbo_mlp/w2/kernel"), B, Jd, 4 * Jd, b_mn=True,
                          ldb=ps.ld("model/jumbo_mlp/w2/kernel"), bias=ps.f("model/jumbo_mlp/w2/bias"), residual=s.cn,
-                         ldr=Jd, out_f32=x_out, ldo_f32=T * dim, row_scale=dp[2], row_scale_period=1)
+                         ldr=Jd, out_f32=x_out, ldo_f32=T * dim, **(dict(row_scale=dp[2], row_scale_period=1) if dp is not None else {}),
+                         **cv(3))
 
     # ------------------------------------------------------------------ backward
     def backward(self, zero_grads: bool = True) -> None:
@@ -389,8 +395,8 @@ class MAEEngine:
             # The decoder's residual-gradient stream is carried in bf16 alone (like the reference's bf16 activations):
             # its LayerNorm backwards move 10 instead of 16 bytes per element.  Only the gradient that leaves the
             # decoder (layer 0's input, scattered back to the encoder's tokens) is also written in f32.
-            lowp = self.dec_lowp and not dp_on
-            dcol = None if dp_on else ps.grad(f"decoder_model/dec_layer_{cfg.dec_layers - 1}/ff/w2/bias")
+            lowp = self.dec_lowp and not dp_on and not self.ls_dec
+            dcol = None if (dp_on or self.ls_dec) else ps.grad(f"decoder_model/dec_layer_{cfg.dec_layers - 1}/ff/w2/bias")
             if self.fused_head:          # the gradient exists on the masked rows only: scattered into a zeroed dx
                 ops.layernorm_bwd_rows(dn, self.za[cfg.dec_layers], self.row_map, self.meanD, self.rstdD,
                                        ps.f("decoder_model/dec_norm/scale"), None if lowp else dx, dx16,
@@ -416,7 +422,7 @@ class MAEEngine:
             dx, dx16 = view(self.dxA, Me, d), view(self.dxA16, Me, d)
             ops.layernorm_bwd(dn, self.xa[cfg.layers], self.meanF, self.rstdF, ps.f("model/norm/scale"), None, dx,
                               dx16, ps.grad("model/norm/scale"), ps.grad("model/norm/bias"), self.ln_ws,
-                              dcol=None if dp_on else ps.grad(f"model/layer_{cfg.layers - 1}/ff/w2/bias"),
+                              dcol=None if (dp_on or self.ls_enc) else ps.grad(f"model/layer_{cfg.layers - 1}/ff/w2/bias"),
                               dcol_period=Te, dcol_skip=J)
             return
         kind, layers = self._segment_plan()[k]
@@ -426,7 +432,7 @@ class MAEEngine:
                     self._block_fwd(f"model/layer_{i}", self.enc[i], self.xa[i], self.xa[i + 1], Me, d, cfg.heads, Te,
                                     True, self._dp(i))
                 self._block_bwd(f"model/layer_{i}", self.enc[i], self.xa[i], Me, d, cfg.heads, Te, True,
-                                ps.grad(f"model/layer_{i - 1}/ff/w2/bias"), dp=self._dp(i))
+                                ps.grad(f"model/layer_{i - 1}/ff/w2/bias"), dp=self._dp(i), x_out=self.xa[i + 1])
         if kind == "jumbo":
             # layer 0's Jumbo branch alone (its patch-FFN and attention branches do not touch the CLS rows'
             # incoming gradient and run in the tail), then the shared Jumbo MLP's weight gradients over all
@@ -435,7 +441,7 @@ class MAEEngine:
                 self._block_fwd("model/layer_0", self.enc[0], self.xa[0], self.xa[1], Me, d, cfg.heads, Te, True,
                                 self._dp(0))
             self._block_bwd("model/layer_0", self.enc[0], self.xa[0], Me, d, cfg.heads, Te, True, None, part="jumbo",
-                            dp=self._dp(0))
+                            dp=self._dp(0), x_out=self.xa[1])
             L, Jd = cfg.layers, J * d
             for nm, X, dY, rows, cols in (("w1", self.cn16_all, self.dhj16_all, Jd, 4 * Jd),
                                           ("w2", self.gj_all, self.dc16_all, 4 * Jd, Jd)):
@@ -456,7 +462,7 @@ class MAEEngine:
                      accumulate=True)
 
     def _block_bwd(self, name, s: _Block, x_in, M, dim, heads, T, jumbo, dcol_below, part="all", dp=None,
-                   below_is_branch=True, lowp=0):
+                   below_is_branch=True, lowp=0, x_out=None):
         """In: d/d(block output) in dxA / dxA16.  Out: d/d(block input) in dxA / dxA16.
         ``part``: "all", or the block in two steps, "jumbo" (the Jumbo CLS branch alone: it reads and writes only
         the CLS rows, which the patch FFN branch leaves alone) followed by "rest".
@@ -479,10 +485,19 @@ class MAEEngine:
         period, skip = (T, J) if jumbo else (0, 0)
         mode = 1 if jumbo else 0
         any_dp = self.drop_masks is not None
-        if dp is not None and part != "rest":
-            # dY of ff/w2 (patch rows, drop_path2) and of the Jumbo w2 (CLS rows, drop_path3)
-            ops.scale_rows_bf16(dx16, M, dim, dp[1], T, scale_cls=dp[2] if jumbo else None, skip=J if jumbo else 0)
-        if dp is not None and part != "jumbo":
+        # LayerScale: y = scale_k * z, so the gradient that enters the branch is dy * scale_k (per column) -- folded into
+        # the same in-place scaling of the bf16 gradient copies as DropPath's per-image factor; the weight / bias
+        # gradients taken from the scaled copies are then the true ones, and d scale_k follows from them once per
+        # optimizer step (layerscale_finalize); scale3 of the shared Jumbo MLP is done per layer, below.
+        ls = self.ls_enc if jumbo else self.ls_dec
+        g_ = (lambda k: ps.f(f"{name}/scale{k}")) if ls else (lambda k: None)
+        explicit = dp is not None or ls
+        dpk = (lambda k: dp[k]) if dp is not None else (lambda k: None)
+        if explicit and part != "rest":
+            # dY of ff/w2 (patch rows, drop_path2 / scale2) and of the Jumbo w2 (CLS rows, drop_path3 / scale3)
+            ops.scale_bf16(dx16, M, dim, T, scale=dpk(1), scale_cls=dpk(2) if jumbo else None, skip=J if jumbo else 0,
+                           col_scale=g_(2), col_scale_cls=g_(3) if jumbo else None)
+        if explicit and part != "jumbo":
             # ff/w2 bias: column sums of the scaled gradient over the rows the branch produced
             ops.colsum(dx16, M, dim, ps.grad(f"{name}/ff/w2/bias"), row_period=period, row_skip=skip)
         if part != "jumbo":
@@ -499,15 +514,18 @@ class MAEEngine:
                 ops.layernorm_bwd(dn, s.xb, s.mean2, s.rstd2, ps.f(f"{name}/norm2/scale"), dx, dxb, dxb16,
                                   ps.grad(f"{name}/norm2/scale"), ps.grad(f"{name}/norm2/bias"), self.ln_ws,
                                   row_period=period, row_skip=skip,
-                                  dcol=None if dp is not None else ps.grad(f"{name}/attn/wo/bias"))
+                                  dcol=None if explicit else ps.grad(f"{name}/attn/wo/bias"))
         if jumbo and part != "rest":
             # ---- Jumbo CLS: c_out = c + w2j(gelu(w1j c)), c = LN3(cls concat); strided [B, J*dim] views
             Jd, ldc = J * dim, T * dim
             # output gradient of w2 = the CLS rows of dx: bias gradient now, a bf16 copy for the batched dW
             ops.colsum(dx16, B, Jd, ps.grad("model/jumbo_mlp/w2/bias"), ldx=ldc)
             ops.add_bias_cast(dx, B, Jd, dst_bf16=s.dc16, lds=ldc)
-            if dp is not None:
-                ops.scale_rows_bf16(s.dc16, B, Jd, dp[2], 1)
+            if explicit:
+                ops.scale_bf16(s.dc16, B, Jd, 1, scale=dpk(2), col_scale=g_(3))
+            if ls:      # d scale3 += sum_b d c_out * (c_out - c) / scale3, before d c is accumulated into the same rows
+                ops.layerscale_cls_grad(dx, x_out, s.cn, B, Jd, ps.f(f"{name}/scale3"), ps.grad(f"{name}/scale3"),
+                                        lddy=ldc, ldo=ldc, ldc=Jd)
             ops.gemm(dx16, self._W("model/jumbo_mlp/w2/kernel"), B, 4 * Jd, Jd, b_mn=False, lda=ldc,
                      ldb=ps.ld("model/jumbo_mlp/w2/kernel"), out_bf16=s.dhj16, act=GELU_BWD, aux=s.hj,
                      colsum=ps.grad("model/jumbo_mlp/w1/bias"))
@@ -518,21 +536,21 @@ class MAEEngine:
             ops.layernorm_bwd(self.dcn16, s.xb, s.mean3, s.rstd3, ps.f(f"{name}/norm3/scale"), None, dxb, dxb16,
                               ps.grad(f"{name}/norm3/scale"), ps.grad(f"{name}/norm3/bias"), self.ln_ws, rows=B,
                               dim=Jd, ldx=ldc, lddx=ldc, lddxb=ldc)
-            if dp is None:
+            if not explicit:
                 # wo bias: LN2 backward covered the patch rows, add the CLS rows LN3 backward just wrote
                 ops.colsum(dxb16, M, dim, ps.grad(f"{name}/attn/wo/bias"), row_period=T, row_skip=J, row_invert=True)
         if part == "jumbo":
             return
         # ---- attention branch: x_b = x + wo(attn(wqkv LN1(x)))
-        if dp is not None:
-            ops.scale_rows_bf16(dxb16, M, dim, dp[0], T)
+        if explicit:
+            ops.scale_bf16(dxb16, M, dim, T, scale=dpk(0), col_scale=g_(1))
             ops.colsum(dxb16, M, dim, ps.grad(f"{name}/attn/wo/bias"))
         datt, dqkv = view(self.datt16, dim), view(self.dqkv16, 3 * dim)
         self._bwd_linear(s.att, dxb16, M, f"{name}/attn/wo", dim, dim, dX16=datt, bias=False)
         ops.attention_bwd(s.qkv, s.att, datt, s.lse, B, T, heads, hd, hd ** -0.5, dqkv, self.delta_ws,
                           dbias=ps.grad(f"{name}/attn/wqkv/bias"))
         self._bwd_linear(s.xn1, dqkv, M, f"{name}/attn/wqkv", 3 * dim, dim, dX16=dn, bias=False)
-        if any_dp and below_is_branch:
+        if (any_dp or ls) and below_is_branch:
             dcol_below = None       # the block below takes its ff/w2 bias from its own scaled gradient copy
         if lowp:
             ops.layernorm_bwd_lowp(dn, x_in, s.mean1, s.rstd1, ps.f(f"{name}/norm1/scale"), dxb16,
@@ -619,6 +637,24 @@ class MAEEngine:
         return self.loss
 
     # ------------------------------------------------------------------ optimizer
+    def layerscale_finalize(self) -> None:
+        """d scale1 / d scale2 of every LayerScale-d block from the ACCUMULATED gradients of the Dense each one scales
+        (attn/wo, ff/w2): call once per optimizer step, after the last micro-step's backward (and the all-reduce: the
+        identity is linear in the gradients), before clipping and the optimizer.  No-op without LayerScale."""
+        cfg, ps = self.cfg, self.ps
+        stacks = []
+        if self.ls_enc:
+            stacks.append((f"model/layer_{{}}", cfg.layers, cfg.dim))
+        if self.ls_dec and cfg.labels <= 0:
+            stacks.append((f"decoder_model/dec_layer_{{}}", cfg.dec_layers, cfg.dec_dim))
+        for fmt, count, dim in stacks:
+            for i in range(count):
+                name = fmt.format(i)
+                for k, lin, K in ((1, "attn/wo", dim), (2, "ff/w2", 4 * dim)):
+                    ops.layerscale_grad(ps.f(f"{name}/{lin}/kernel"), ps.grad(f"{name}/{lin}/kernel"),
+                                        ps.f(f"{name}/{lin}/bias"), ps.grad(f"{name}/{lin}/bias"),
+                                        ps.f(f"{name}/scale{k}"), ps.grad(f"{name}/scale{k}"), K, dim)
+
     def adamw_step(self, count: int, lr: float, grad_scale: float = 1.0, lr_decay: float = 1.0) -> None:
         """optax.adamw update number ``count`` (0-based) over the flat buffers (src/pretraining.py:223-234).
         ``lr_decay < 1``: the layer-wise scale table chained behind it (:235-242) — the leaves of label i

@@ -50,6 +50,7 @@ class FinetuneEngine(MAEEngine):
         self.patches = e(Me, self.Pp)
         self.xa: List[torch.Tensor] = [e(Me, d, dt=F32) for _ in range(cfg.layers + 1)]
         self.remat = bool(getattr(cfg, "grad_ckpt", False))
+        self.ls_enc, self.ls_dec = bool(getattr(cfg, "layerscale", False)), False
         self.enc = make_blocks(cfg.layers, Me, d, cfg.heads, B, self.Te, J, True, dev, self.remat)
         self.dec: List[_Block] = []          # no decoder in classification mode (activation_bytes walks both lists)
         L, Jd = cfg.layers, J * d
@@ -143,7 +144,7 @@ class FinetuneEngine(MAEEngine):
         dx, dx16 = self.dxA[:Me * d].view(Me, d), self.dxA16[:Me * d].view(Me, d)
         ops.layernorm_bwd(dn, self.xa[cfg.layers], self.meanF, self.rstdF, ps.f("model/norm/scale"), None, dx, dx16,
                           ps.grad("model/norm/scale"), ps.grad("model/norm/bias"), self.ln_ws,
-                          dcol=None if self.drop_masks is not None else ps.grad(f"model/layer_{cfg.layers - 1}/ff/w2/bias"),
+                          dcol=None if (self.drop_masks is not None or self.ls_enc) else ps.grad(f"model/layer_{cfg.layers - 1}/ff/w2/bias"),
                           dcol_period=Te, dcol_skip=J)
 
     # ------------------------------------------------------------------ CUDA graphs

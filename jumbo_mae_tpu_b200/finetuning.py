@@ -154,13 +154,11 @@ def create_train_state(args: argparse.Namespace) -> TrainState:
         raise NotImplementedError("--dropout > 0 is not built (0.0 in the fine-tune recipe)")
     if not 0.0 <= float(getattr(args, "droppath", 0.0)) < 1.0:
         raise ValueError("--droppath must be in [0, 1)")
-    if getattr(args, "layerscale", False):
-        raise NotImplementedError("LayerScale is not built")
     cfg = MAEConfig(layers=args.layers, dim=args.dim, heads=args.heads, patch_size=args.patch_size,
                     image_size=args.image_size, labels=args.labels, weight_decay=args.weight_decay,
                     adam_b1=args.adam_b1, adam_b2=args.adam_b2, adam_eps=args.adam_eps,
                     grad_accum=getattr(args, "grad_accum", 1), posemb=getattr(args, "posemb", "sincos2d"),
-                    grad_ckpt=bool(getattr(args, "grad_ckpt", False)))
+                    grad_ckpt=bool(getattr(args, "grad_ckpt", False)), layerscale=bool(getattr(args, "layerscale", False)))
     store = ParamStore(cfg)
     gen = torch.Generator(device="cpu").manual_seed(int(getattr(args, "init_seed", 0)))
     for name, leaf in store.leaves.items():           # truncated_normal(0.02) kernels, LN scales 1, the rest 0
@@ -171,6 +169,8 @@ def create_train_state(args: argparse.Namespace) -> TrainState:
             view[:, :leaf.cols].copy_(w)
         elif name.endswith("/scale"):
             view.fill_(1.0)
+        elif name.rsplit("/", 1)[-1] in ("scale1", "scale2", "scale3"):
+            view.fill_(1e-4)
     store.refresh_bf16()
     state = _new_state(args, store, cfg)
     if getattr(args, "pretrained_ckpt", None) is not None:         # src/finetuning.py:215-217
@@ -242,6 +242,7 @@ def training_step(state: TrainState, batch, mix: Optional[MixDraw] = None, drop_
     if state.micro_step == accum:
         if world > 1:                                              # lax.pmean(grads) (:138,144); 1/world below
             state.reducer.all_reduce_grads()
+        eng.layerscale_finalize()
         if state.clip_grad > 0:
             if not hasattr(state, "_sumsq"):
                 state._sumsq = torch.zeros(1, dtype=torch.float32, device=dev)

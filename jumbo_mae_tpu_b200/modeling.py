@@ -122,8 +122,8 @@ class ViT(ViTBase, _Bound):
     num_cls_tokens: int = 3
 
     def __post_init__(self):
-        if self.layerscale or self.dropout:
-            raise NotImplementedError("layerscale / dropout > 0 are off in every preset and not built")
+        if self.dropout:
+            raise NotImplementedError("dropout > 0 is off in every preset and not built")
 
     def _check(self, cfg):
         if cfg.dim != self.dim or cfg.layers != self.layers or cfg.heads != self.heads or \
@@ -162,8 +162,8 @@ class MAEDecoder(MAEDecoderBase, _Bound):
     num_cls_tokens: int = 3
 
     def __post_init__(self):
-        if self.dec_layerscale or self.dec_dropout:
-            raise NotImplementedError("decoder layerscale / dropout > 0 are off in every preset and not built")
+        if self.dec_dropout:
+            raise NotImplementedError("decoder dropout > 0 is off in every preset and not built")
 
     def __call__(self, x: torch.Tensor, det: bool = True) -> torch.Tensor:
         from . import ops

@@ -134,6 +134,34 @@ def scale_rows_bf16(x: torch.Tensor, rows: int, cols: int, scale: torch.Tensor, 
                                          period, skip, stream_ptr()))
 
 
+def scale_bf16(x: torch.Tensor, rows: int, cols: int, period: int, scale: Optional[torch.Tensor] = None,
+               scale_cls: Optional[torch.Tensor] = None, skip: int = 0, col_scale: Optional[torch.Tensor] = None,
+               col_scale_cls: Optional[torch.Tensor] = None, ld: Optional[int] = None) -> None:
+    """In place x[r, c] *= row factor (DropPath) * column factor (LayerScale); CLS rows (r % period < skip) have their own."""
+    _chk(x, BF16, "x"), _chk(scale, F32, "scale"), _chk(scale_cls, F32, "scale_cls"), _chk(col_scale, F32, "col_scale")
+    _chk(col_scale_cls, F32, "col_scale_cls")
+    check(_lib.load().jm_scale_bf16(ptr(x), _ld(x) if ld is None else ld, rows, cols, ptr(scale), ptr(scale_cls), period,
+                                    skip, ptr(col_scale), ptr(col_scale_cls), stream_ptr()))
+
+
+def layerscale_grad(W: torch.Tensor, dW: torch.Tensor, b: torch.Tensor, db: torch.Tensor, scale: torch.Tensor,
+                    dscale: torch.Tensor, K: int, N: int) -> None:
+    """dscale += (colsum(W * dW) + b * db) / scale from the accumulated gradients of the scaled Dense."""
+    for t, nm in ((W, "W"), (dW, "dW"), (b, "b"), (db, "db"), (scale, "scale"), (dscale, "dscale")):
+        _chk(t, F32, nm)
+    check(_lib.load().jm_layerscale_grad(ptr(W), ptr(dW), _ld(W), K, N, ptr(b), ptr(db), ptr(scale), ptr(dscale),
+                                         stream_ptr()))
+
+
+def layerscale_cls_grad(dy: torch.Tensor, c_out: torch.Tensor, c: torch.Tensor, batch: int, N: int, scale: torch.Tensor,
+                        dscale: torch.Tensor, lddy: int, ldo: int, ldc: int) -> None:
+    """dscale3 += sum_b dy (c_out - c) / scale3 over [batch, N] f32 views (row strides given)."""
+    for t, nm in ((dy, "dy"), (c_out, "c_out"), (c, "c"), (scale, "scale"), (dscale, "dscale")):
+        _chk(t, F32, nm)
+    check(_lib.load().jm_layerscale_cls_grad(ptr(dy), lddy, ptr(c_out), ldo, ptr(c), ldc, batch, N, ptr(scale),
+                                             ptr(dscale), stream_ptr()))
+
+
 def patch_mse_loss(patch_output: torch.Tensor, patch_target: torch.Tensor, valid: Optional[torch.Tensor],
                    loss: torch.Tensor, workspace: torch.Tensor) -> None:
     """src/utils_mae.py:51-64 on explicit f32 targets [B, L, P]; valid [B, L] f32 or None."""
@@ -258,7 +286,8 @@ def gemm(A: torch.Tensor, B: torch.Tensor, M: int, N: int, K: int, *, a_mn: bool
          colsum: Optional[torch.Tensor] = None, cta_pair: int = 0,
          row_scale: Optional[torch.Tensor] = None, row_scale_period: int = 0,
          loss_target: Optional[torch.Tensor] = None, loss_stats: Optional[torch.Tensor] = None,
-         row_loss: Optional[torch.Tensor] = None, loss_scale: float = 0.0) -> None:
+         row_loss: Optional[torch.Tensor] = None, loss_scale: float = 0.0,
+         col_vec: Optional[torch.Tensor] = None) -> None:
     """D = epilogue(A @ B) through jm_gemm; see include/jumbo_mae_b200.h for the epilogue order."""
     _chk(A, BF16, "A"), _chk(B, BF16, "B"), _chk(out_f32, F32, "out_f32"), _chk(out_bf16, BF16, "out_bf16")
     _chk(out2_bf16, BF16, "out2_bf16"), _chk(bias, F32, "bias"), _chk(residual, F32, "residual")
@@ -286,6 +315,8 @@ def gemm(A: torch.Tensor, B: torch.Tensor, M: int, N: int, K: int, *, a_mn: bool
     _chk(loss_target, torch.uint8, "loss_target"), _chk(loss_stats, F32, "loss_stats"), _chk(row_loss, F32, "row_loss")
     a.loss_target, a.ld_target = ptr(loss_target), _ld(loss_target)
     a.loss_stats, a.row_loss, a.loss_scale = ptr(loss_stats), ptr(row_loss), float(loss_scale)
+    _chk(col_vec, F32, "col_vec")
+    a.col_scale_vec = ptr(col_vec)
     check(_lib.load().jm_gemm(ctypes.byref(a), stream_ptr()))
 
 

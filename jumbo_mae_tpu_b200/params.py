@@ -55,7 +55,7 @@ def _leaves(cfg: MAEConfig) -> List[Leaf]:
     def vec(name, n):
         out.append(Leaf(name, 1, n, n, False))
 
-    def block(prefix, dim, with_norm3):
+    def block(prefix, dim, with_norm3, layerscale):
         kernel(f"{prefix}/attn/wqkv/kernel", dim, 3 * dim)
         vec(f"{prefix}/attn/wqkv/bias", 3 * dim)
         kernel(f"{prefix}/attn/wo/kernel", dim, dim)
@@ -67,6 +67,11 @@ def _leaves(cfg: MAEConfig) -> List[Leaf]:
         for nm, n in (("norm1", dim), ("norm2", dim)) + ((("norm3", J * dim),) if with_norm3 else ()):
             vec(f"{prefix}/{nm}/scale", n)
             vec(f"{prefix}/{nm}/bias", n)
+        if layerscale:                  # LayerScale vectors "scale1/2/3": leaf name is not "kernel" -> no weight decay
+            vec(f"{prefix}/scale1", dim)
+            vec(f"{prefix}/scale2", dim)
+            if with_norm3:
+                vec(f"{prefix}/scale3", J * dim)
 
     kernel("model/embed/wte/kernel", P, d)
     vec("model/embed/wte/bias", d)
@@ -78,7 +83,7 @@ def _leaves(cfg: MAEConfig) -> List[Leaf]:
     kernel("model/jumbo_mlp/w2/kernel", 4 * J * d, J * d)
     vec("model/jumbo_mlp/w2/bias", J * d)
     for i in range(cfg.layers):
-        block(f"model/layer_{i}", d, True)
+        block(f"model/layer_{i}", d, True, getattr(cfg, "layerscale", False))
     vec("model/norm/scale", d)
     vec("model/norm/bias", d)
     if cfg.labels > 0:
@@ -87,7 +92,7 @@ def _leaves(cfg: MAEConfig) -> List[Leaf]:
         vec("model/head/Dense_0/bias", cfg.labels)
         return out
     for i in range(cfg.dec_layers):
-        block(f"decoder_model/dec_layer_{i}", dd, False)
+        block(f"decoder_model/dec_layer_{i}", dd, False, getattr(cfg, "dec_layerscale", False))
     vec("decoder_model/dec_norm/scale", dd)
     vec("decoder_model/dec_norm/bias", dd)
     vec("image_mask_embedding", dd)
@@ -232,6 +237,8 @@ class ParamStore:
             p = f"model/layer_{i}"
             model[f"layer_{i}"] = {"attn": attn(f"{p}/attn", cfg.dim, cfg.heads), "ff": ff(f"{p}/ff"),
                                    "norm1": ln(f"{p}/norm1"), "norm2": ln(f"{p}/norm2"), "norm3": ln(f"{p}/norm3")}
+            if getattr(cfg, "layerscale", False):
+                model[f"layer_{i}"].update({nm: v(f"{p}/{nm}") for nm in ("scale1", "scale2", "scale3")})
         if cfg.labels > 0:
             model["head"] = {"Dense_0": {"kernel": k("model/head/Dense_0/kernel"), "bias": v("model/head/Dense_0/bias")}}
             return {"model": model}
@@ -240,6 +247,8 @@ class ParamStore:
             p = f"decoder_model/dec_layer_{i}"
             dec[f"dec_layer_{i}"] = {"attn": attn(f"{p}/attn", cfg.dec_dim, cfg.dec_heads), "ff": ff(f"{p}/ff"),
                                      "norm1": ln(f"{p}/norm1"), "norm2": ln(f"{p}/norm2")}
+            if getattr(cfg, "dec_layerscale", False):
+                dec[f"dec_layer_{i}"].update({nm: v(f"{p}/{nm}") for nm in ("scale1", "scale2")})
         return {
             "model": model,
             "decoder_model": dec,

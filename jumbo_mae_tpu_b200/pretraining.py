@@ -173,8 +173,6 @@ def create_train_state(args: argparse.Namespace) -> TrainState:
     for nm in ("dropout", "dec_dropout"):
         if getattr(args, nm, 0.0) != 0.0:
             raise NotImplementedError(f"--{nm.replace('_', '-')} > 0 is not built (0.0 in both presets)")
-    if getattr(args, "layerscale", False) or getattr(args, "dec_layerscale", False):
-        raise NotImplementedError("LayerScale is off in both presets and not built")
     posemb = getattr(args, "posemb", "sincos2d")
     model = ViT(layers=args.layers, dim=args.dim, heads=args.heads, labels=getattr(args, "labels", 0),
                 patch_size=args.patch_size, image_size=args.image_size, posemb=posemb,
@@ -186,7 +184,9 @@ def create_train_state(args: argparse.Namespace) -> TrainState:
                         weight_decay=args.weight_decay, adam_b1=args.adam_b1, adam_b2=args.adam_b2,
                         adam_eps=args.adam_eps, warmup_steps=args.warmup_steps, training_steps=args.training_steps,
                         grad_accum=getattr(args, "grad_accum", 1), posemb=posemb,
-                        grad_ckpt=bool(getattr(args, "grad_ckpt", False)))
+                        grad_ckpt=bool(getattr(args, "grad_ckpt", False)),
+                        layerscale=bool(getattr(args, "layerscale", False)),
+                        dec_layerscale=bool(getattr(args, "dec_layerscale", False)))
     cfg.validate()
     store = ParamStore(cfg, device=torch.device("cuda", torch.cuda.current_device()))
     init_params_(store, getattr(args, "init_seed", 0))
@@ -215,6 +215,8 @@ def init_params_(store: ParamStore, seed: int) -> None:
                 val.copy_((t * 0.02).to(val.device))
             elif key == "scale":
                 val.fill_(1.0)
+            elif key in ("scale1", "scale2", "scale3"):                 # LayerScale: init.constant(1e-4) (src/modeling.py:160-162)
+                val.fill_(1e-4)
             else:
                 val.zero_()
     walk(tree, ())
@@ -260,7 +262,8 @@ def training_step(state: TrainState, batch, noise=None) -> Tuple[TrainState, Dic
         # (which needs the global norm) each segment's parameters are also updated as soon as its sum has arrived
         hook = None
         if (state.clip_grad == 0 and state.lr_decay >= 1.0 and state.reducer.stream is not None
-                and state.optimizer == "adamw"):       # (lamb's trust ratios are per leaf: reduce, then update)
+                and state.optimizer == "adamw" and not (state.cfg.layerscale or state.cfg.dec_layerscale)):
+            # (lamb's trust ratios are per leaf, LayerScale's d scale needs the summed gradients: reduce, then update)
             lr_now, cnt = lr_schedule(state.step, state.cfg), state.step
             hook = lambda ranges: eng.adamw_ranges(ranges, cnt, lr_now, grad_scale=1.0 / (accum * world))
             updated = True
@@ -280,6 +283,7 @@ def training_step(state: TrainState, batch, noise=None) -> Tuple[TrainState, Dic
     if state.micro_step == accum:                                    # :149-158
         if world > 1 and not reduced:
             state.reducer.all_reduce_grads()                         # lax.pmean(grads) (:150); 1/world below
+        eng.layerscale_finalize()                                    # (no-op without LayerScale)
         if state.clip_grad > 0:                                      # chain(clip_by_global_norm, adamw) (:243-244)
             if not hasattr(state, "_sumsq"):
                 state._sumsq = torch.zeros(1, dtype=torch.float32, device=state.store.device)

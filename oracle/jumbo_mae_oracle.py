@@ -61,6 +61,8 @@ class MAEConfig:
     dec_dim: int = 512
     dec_heads: int = 16
     norm_pix_loss: bool = False      # src/main_pretrain.py:139 (off in both presets)
+    layerscale: bool = False         # scale1/2/3 per JumboLayer, init.constant(1e-4) (src/modeling.py:185-189)
+    dec_layerscale: bool = False     # scale1/2 per decoder ViTLayer (src/modeling.py:159-162)
     posemb: str = "sincos2d"         # "learnable": embed/wpe is a parameter, truncated_normal(0.02) (src/modeling.py:115-118)
     labels: int = 0                  # > 0: classification mode of ViT (src/modeling.py:236-242): head, no masking, no decoder
     # optimizer: src/pretraining.py:223-259 with the preset's flags
@@ -262,8 +264,9 @@ def vit_layer(x, p: Tree, heads: int, drop=None):
     """ViTLayer (decoder block), src/modeling.py:150-167; scale1=scale2=1.0.  ``drop`` = (scale1, scale2) per-image
     DropPath factors of the two branches (the SAME nn.Dropout module is applied twice, with two draws), or None."""
     d1, d2 = drop if drop is not None else (None, None)
-    x = x + drop_path(attention(layer_norm(x, p["norm1"]["scale"], p["norm1"]["bias"]), p["attn"], heads), d1)
-    x = x + drop_path(feed_forward(layer_norm(x, p["norm2"]["scale"], p["norm2"]["bias"]), p["ff"]), d2)
+    s1, s2 = p.get("scale1", 1.0), p.get("scale2", 1.0)        # LayerScale (:159-162,165-166)
+    x = x + drop_path(s1 * attention(layer_norm(x, p["norm1"]["scale"], p["norm1"]["bias"]), p["attn"], heads), d1)
+    x = x + drop_path(s2 * feed_forward(layer_norm(x, p["norm2"]["scale"], p["norm2"]["bias"]), p["ff"]), d2)
     return x
 
 
@@ -272,13 +275,14 @@ def jumbo_layer(x, p: Tree, jumbo_mlp: Tree, heads: int, J: int, drop=None):
     residual is taken from the post-norm3 value.  ``drop`` = per-image DropPath factors (drop_path1, drop_path2,
     drop_path3), each f32 [B], or None."""
     d1, d2, d3 = drop if drop is not None else (None, None, None)
-    x = x + drop_path(attention(layer_norm(x, p["norm1"]["scale"], p["norm1"]["bias"]), p["attn"], heads), d1)
+    s1, s2, s3 = p.get("scale1", 1.0), p.get("scale2", 1.0), p.get("scale3", 1.0)     # LayerScale (:185-189)
+    x = x + drop_path(s1 * attention(layer_norm(x, p["norm1"]["scale"], p["norm1"]["bias"]), p["attn"], heads), d1)
     cls_tokens, patch_tokens = x[:, :J, :], x[:, J:, :]
     bs = cls_tokens.shape[0]
     c = cls_tokens.reshape(bs, -1)
     c = layer_norm(c, p["norm3"]["scale"], p["norm3"]["bias"])
-    c = c + drop_path(feed_forward(c, jumbo_mlp), d3)
-    patch_tokens = patch_tokens + drop_path(feed_forward(
+    c = c + drop_path(s3 * feed_forward(c, jumbo_mlp), d3)
+    patch_tokens = patch_tokens + drop_path(s2 * feed_forward(
         layer_norm(patch_tokens, p["norm2"]["scale"], p["norm2"]["bias"]), p["ff"]), d2)
     return torch.cat([c.reshape(bs, J, -1), patch_tokens], dim=1)
 
@@ -445,6 +449,10 @@ def init_params(cfg: MAEConfig, seed: int = 0, dtype=torch.float32, randomize_al
         model[f"layer_{i}"] = {"attn": _attn_p(gen, d, cfg.heads, dtype), "ff": _ff_p(gen, d, dtype),
                                "norm1": _ln_p(d, dtype), "norm2": _ln_p(d, dtype),
                                "norm3": _ln_p(J * d, dtype)}
+        if cfg.layerscale:
+            model[f"layer_{i}"].update({"scale1": torch.full((d,), 1e-4, dtype=dtype),
+                                        "scale2": torch.full((d,), 1e-4, dtype=dtype),
+                                        "scale3": torch.full((J * d,), 1e-4, dtype=dtype)})
     model["norm"] = _ln_p(d, dtype)
     if cfg.posemb == "learnable":    # drawn last, so that the sincos configurations keep their parameter values
         model["embed"]["wpe"] = _tn(torch.Generator().manual_seed(seed + 7919), (cfg.grid, cfg.grid, d), dtype)
@@ -457,12 +465,17 @@ def init_params(cfg: MAEConfig, seed: int = 0, dtype=torch.float32, randomize_al
                     leaf.add_(_tn(gen, tuple(leaf.shape), dtype))
                 elif path[-1] == "scale":
                     leaf.add_(_tn(gen, tuple(leaf.shape), dtype) * 5.0)
+                elif path[-1] in ("scale1", "scale2", "scale3"):
+                    leaf.copy_(0.5 + _tn(gen, tuple(leaf.shape), dtype) * 10.0)
         return params
     dd = cfg.dec_dim
     dec: Tree = {}
     for i in range(cfg.dec_layers):
         dec[f"dec_layer_{i}"] = {"attn": _attn_p(gen, dd, cfg.dec_heads, dtype), "ff": _ff_p(gen, dd, dtype),
                                  "norm1": _ln_p(dd, dtype), "norm2": _ln_p(dd, dtype)}
+        if cfg.dec_layerscale:
+            dec[f"dec_layer_{i}"].update({"scale1": torch.full((dd,), 1e-4, dtype=dtype),
+                                          "scale2": torch.full((dd,), 1e-4, dtype=dtype)})
     dec["dec_norm"] = _ln_p(dd, dtype)
     params: Tree = {
         "model": model,
@@ -477,6 +490,8 @@ def init_params(cfg: MAEConfig, seed: int = 0, dtype=torch.float32, randomize_al
                 leaf.add_(_tn(gen, tuple(leaf.shape), dtype))
             elif path[-1] == "scale":
                 leaf.add_(_tn(gen, tuple(leaf.shape), dtype) * 5.0)
+            elif path[-1] in ("scale1", "scale2", "scale3"):
+                leaf.copy_(0.5 + _tn(gen, tuple(leaf.shape), dtype) * 10.0)      # ~0.5 +- 0.2, away from 0
     return params
 
 

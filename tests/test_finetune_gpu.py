@@ -18,6 +18,7 @@ def _cfgs():
     return {
         "tiny": (O.tiny(labels=16), 4),
         "tiny_wpe": (O.tiny(labels=16, posemb="learnable"), 4),
+        "tiny_ls": (O.tiny(labels=16, layerscale=True), 4),       # --layerscale: scale1/2/3 on the JumboLayer branches
         "mid": (O.MAEConfig(layers=2, dim=256, heads=4, patch_size=16, image_size=64, labels=40, warmup_steps=10,
                             training_steps=100, train_batch_size=256), 8),
     }
@@ -37,7 +38,7 @@ def _setup(name):
 
 
 @pytest.mark.parametrize("name,mode", [("tiny", "plain"), ("tiny", "mixup"), ("tiny", "cutmix"), ("mid", "mixup"),
-                                       ("tiny_wpe", "plain")])
+                                       ("tiny_wpe", "plain"), ("tiny_ls", "plain")])
 def test_classification_step_matches_oracle(name, mode):
     from jumbo_mae_tpu_b200.params import tree_leaves
     ocfg, cfg, params, images, store, eng = _setup(name)
@@ -62,6 +63,7 @@ def test_classification_step_matches_oracle(name, mode):
     want_loss, want_logits, want = O.finetune_loss_and_grads(params, x, lab, ocfg)
     loss = eng.forward(images.cuda(), torch.from_numpy(idx).cuda(), label_smoothing=0.1, **kw)
     eng.backward()
+    eng.layerscale_finalize()
     torch.cuda.synchronize()
     logits = eng.logits.cpu()
     assert _rel(logits, want_logits) <= 2e-2                                   # bf16 activations, f32 accumulate
@@ -84,7 +86,7 @@ def test_classification_step_matches_oracle(name, mode):
             continue
         if w.norm().item() == 0.0:
             # only the CLS rows reach the head: the last layer's patch FFN (and its norm2) has an exactly zero gradient
-            assert path[1] == f"layer_{ocfg.layers - 1}" and path[2] in ("ff", "norm2"), path
+            assert path[1] == f"layer_{ocfg.layers - 1}" and path[2] in ("ff", "norm2", "scale2"), path
             if g.norm().item() != 0.0:
                 bad.append(("/".join(path), g.norm().item(), 0.0))
             continue
@@ -265,7 +267,7 @@ def test_classification_step_against_committed_golden():
         assert abs(got[path].norm().item() - z[key][1]) <= 3e-2 * z[key][1], key
 
 
-@pytest.mark.parametrize("name", ["tiny", "mid"])
+@pytest.mark.parametrize("name", ["tiny", "mid", "tiny_ls"])
 def test_droppath_matches_oracle(name):
     """DropPath (src/modeling.py:181-183,192,199,201; 0.1 in config/ft.sh) with the keep bits as data: some images lose
     a branch entirely, the others see it scaled by 1 / (1 - rate).  Logits, loss and every gradient leaf, same
@@ -284,6 +286,7 @@ def test_droppath_matches_oracle(name):
     eng.set_droppath(torch.from_numpy(fac).cuda())
     loss = eng.forward(images.cuda(), torch.from_numpy(idx).cuda(), label_smoothing=0.1)
     eng.backward()
+    eng.layerscale_finalize()            # (tiny_ls: DropPath and LayerScale on the same branches)
     torch.cuda.synchronize()
     assert _rel(eng.logits.cpu(), want_logits) <= 2e-2
     assert abs(loss.item() - want_loss.item()) <= 5e-3 * abs(want_loss.item())
