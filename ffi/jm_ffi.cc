@@ -293,6 +293,34 @@ static ffi::Error Colsum(cudaStream_t s, BF16 x, F32 out_in, RF32 out) {
 }
 XLA_FFI_DEFINE_HANDLER_SYMBOL(JmColsum, Colsum, ffi::Ffi::Bind().Ctx<Stream>().Arg<BF16>().Arg<F32>().Ret<F32>());
 
+// ---- modified_lamb (src/utils.py:124-139) on the kernel leaves: group / chunk tables as int64 operands, p, m, v aliased
+using S64 = ffi::Buffer<ffi::S64>;
+static ffi::Error Lamb(cudaStream_t s, F32 p_in, F32 g, F32 m_in, F32 v_in, S64 groups, S64 chunks, float lr, float b1,
+                       float b2, float eps, float wd, float bc1, float bc2, float grad_scale, RF32 p, RF32 m, RF32 v,
+                       RBF16 p16, RU8 scratch) {
+  (void)p_in, (void)m_in, (void)v_in;
+  return Rc(jm_lamb(p->typed_data(), g.typed_data(), m->typed_data(), v->typed_data(), bf(p16),
+                    reinterpret_cast<const int64_t*>(groups.typed_data()), static_cast<int>(groups.dimensions()[0]),
+                    reinterpret_cast<const int64_t*>(chunks.typed_data()), static_cast<int>(chunks.dimensions()[0]), lr,
+                    b1, b2, eps, wd, bc1, bc2, grad_scale, scratch->untyped_data(), scratch->size_bytes(), s));
+}
+XLA_FFI_DEFINE_HANDLER_SYMBOL(JmLamb, Lamb,
+                              ffi::Ffi::Bind().Ctx<Stream>().Arg<F32>().Arg<F32>().Arg<F32>().Arg<F32>().Arg<S64>().Arg<S64>()
+                                  .Attr<float>("lr").Attr<float>("b1").Attr<float>("b2").Attr<float>("eps").Attr<float>("wd")
+                                  .Attr<float>("bc1").Attr<float>("bc2").Attr<float>("grad_scale")
+                                  .Ret<F32>().Ret<F32>().Ret<F32>().Ret<BF16>().Ret<U8>());
+
+// ---- LayerScale (src/modeling.py:159-166,185-201): d scale of one scaled Dense from its accumulated gradients
+static ffi::Error LayerScaleGrad(cudaStream_t s, F32 w, F32 dw, F32 b, F32 db, F32 scale, F32 dscale_in, RF32 dscale) {
+  (void)dscale_in;  // aliased to the result
+  const auto d = w.dimensions();
+  return Rc(jm_layerscale_grad(w.typed_data(), dw.typed_data(), d[1], static_cast<int>(d[0]), static_cast<int>(d[1]),
+                               b.typed_data(), db.typed_data(), scale.typed_data(), dscale->typed_data(), s));
+}
+XLA_FFI_DEFINE_HANDLER_SYMBOL(JmLayerScaleGrad, LayerScaleGrad,
+                              ffi::Ffi::Bind().Ctx<Stream>().Arg<F32>().Arg<F32>().Arg<F32>().Arg<F32>().Arg<F32>().Arg<F32>()
+                                  .Ret<F32>());
+
 // ---- optax.adamw + apply_updates over the flat buffers (src/pretraining.py:223-234,150); p, m, v aliased in place
 static ffi::Error AdamW(cudaStream_t s, F32 p_in, F32 g, F32 m_in, F32 v_in, int64_t n_decay, float lr, float b1, float b2,
                         float eps, float wd, float bc1, float bc2, float grad_scale, RF32 p, RF32 m, RF32 v, RBF16 p16) {

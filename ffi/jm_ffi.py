@@ -14,7 +14,7 @@ TARGETS = [
     "JmMaskSort", "JmIndexSequence", "JmPatchify", "JmExtractPatches", "JmPatchLoss", "JmPatchMseLoss", "JmLayerNormFwd",
     "JmLayerNormBwd", "JmDense", "JmMaskedTargets", "JmLayerNormFwdRows", "JmLayerNormBwdRows", "JmHeadLoss",
     "JmDenseResidual", "JmDenseBwd", "JmAttentionFwd", "JmAttentionBwd", "JmFillCls",
-    "JmUnshuffleFwd", "JmUnshuffleBwd", "JmColsum", "JmAdamW", "JmClipByGlobalNorm", "JmCastBf16", "JmSoftmaxCe",
+    "JmUnshuffleFwd", "JmUnshuffleBwd", "JmColsum", "JmLamb", "JmLayerScaleGrad", "JmAdamW", "JmClipByGlobalNorm", "JmCastBf16", "JmSoftmaxCe",
 ]
 
 

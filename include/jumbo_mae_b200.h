@@ -76,6 +76,7 @@ int jm_extract_patches(const uint8_t* images, int batch, int image_size, int pat
  * rows per image.  Writes loss[0] (mean over images of mean over masked patches of the
  * per-patch MSE) and, if dpred != NULL, dpred (bf16, same shape, ld = lddp) = d loss /
  * d pred * grad_scale (zero on unmasked and CLS rows).
+ * A mask_row without any masked patch gives 0 / 0 = NaN, as the reference's division by sum(valid) does.
  * workspace: jm_patch_loss_workspace(batch, N) bytes. */
 size_t jm_patch_loss_workspace(int batch, int num_patches);
 int jm_patch_loss(const float* pred, long ldp, const uint8_t* images, const float* mask_row, int batch,

@@ -74,7 +74,7 @@ __global__ void index_sequence_kernel(const float* __restrict__ x, const int* __
 // contiguous bytes per (plane, row); 16-byte vector copies when p == 16 and the image rows keep them aligned.
 __device__ __forceinline__ void stage_patch(uint8_t* spix, const uint8_t* img, int S, int p, int gy, int gx, int lane) {
   const int runs = 3 * p;
-  if (p == 16 && (S & 15) == 0) {
+  if (p == 16 && (S & 15) == 0 && (reinterpret_cast<uintptr_t>(img) & 15) == 0) {  // 16-byte rows: vector loads
     for (int r = lane; r < runs; r += 32) {
       const int c = r >> 4, ph = r & 15;
       *reinterpret_cast<uint4*>(spix + r * 16) =
