@@ -43,6 +43,8 @@ def _cfgs():
                                        layerscale=True, dec_layerscale=True), 8),
         "vith_width": (O.MAEConfig(layers=2, dim=1280, heads=16, patch_size=14, image_size=224, dec_layers=1,
                                    warmup_steps=10, training_steps=100), 2),
+        # two ViT-L/16 blocks at their real width (BASELINE.json configs[2]): d = 1024, 16 heads of 64, decoder 512 x 16
+        "vitl_width": (O.MAEConfig(layers=2, dim=1024, heads=16, dec_layers=1, warmup_steps=10, training_steps=100), 2),
     }
 
 
@@ -69,7 +71,7 @@ def _rel(a, b):
 
 
 ALL = ["tiny", "tiny_normpix", "mid", "vitb_width", "vith_patch14", "config1_vitb16", "vith_width",
-       "tiny_learnable_wpe", "tiny_layerscale", "mid_layerscale"]
+       "tiny_learnable_wpe", "tiny_layerscale", "mid_layerscale", "vitl_width"]
 
 
 @pytest.mark.parametrize("fused_head", [True, False])
@@ -495,3 +497,42 @@ def test_training_step_accepts_lamb():
     torch.cuda.synchronize()
     assert state.step == 1 and math.isfinite(metrics["loss"].item())
     assert not torch.equal(state.store.p, before)
+
+
+@pytest.mark.parametrize("preset", ["vit_b16", "vit_l16"])
+def test_full_size_step_is_the_mean_of_its_halves(preset):
+    """Size-independent property at the presets' full shapes (12 + 8 layers of ViT-B/16, 24 + 8 of ViT-L/16, 224 px),
+    where the oracle is too slow: loss and gradient of one batch equal the mean over its two halves (same mask), with
+    the gradients accumulated over the two half-sized micro-steps as training does."""
+    from jumbo_mae_tpu_b200.config import MAEConfig
+    from jumbo_mae_tpu_b200.engine import MAEEngine
+    from jumbo_mae_tpu_b200.params import ParamStore
+    from jumbo_mae_tpu_b200.pretraining import init_params_
+    kw = dict(vit_b16=dict(), vit_l16=dict(layers=24, dim=1024, heads=16))[preset]
+    cfg = MAEConfig(**kw)
+    store = ParamStore(cfg)
+    init_params_(store, 3)
+    gen = torch.Generator().manual_seed(11)
+    for name, leaf in store.leaves.items():            # biases / LayerNorm / CLS away from their 0 / 1 initial values
+        if not leaf.decay:
+            store.f(name).add_(torch.randn(store.f(name).shape, generator=gen).cuda() * 0.02)
+    store.refresh_bf16()
+    B = 16
+    images = torch.randint(0, 256, (B, 3, 224, 224), generator=gen, dtype=torch.uint8).cuda()
+    noise = torch.rand(cfg.num_patches, generator=gen).cuda()
+    whole = MAEEngine(cfg, store, B)
+    whole.forward(images, noise)
+    whole.backward()
+    torch.cuda.synchronize()
+    loss_whole, g_whole = whole.loss.item(), store.g.clone()
+    del whole
+    half = MAEEngine(cfg, store, B // 2)
+    losses = []
+    for i in range(2):
+        half.forward(images[i * B // 2:(i + 1) * B // 2], noise)
+        half.backward(zero_grads=(i == 0))
+        torch.cuda.synchronize()
+        losses.append(half.loss.item())
+    assert abs(loss_whole - sum(losses) / 2) <= 2e-5 * abs(loss_whole)
+    assert math.isfinite(loss_whole) and g_whole.abs().max().item() > 0
+    assert _rel(store.g * 0.5, g_whole) <= 3e-3          # bf16 activations: the batched Jumbo products round differently
