@@ -171,7 +171,7 @@ def workload_config(args, micro, accum, world):
         "workload": f"MAE {args.config} 224px mask 0.75 decoder 8x512 Jumbo CLS J=3, global batch {args.global_batch} "
                     f"synthetic uint8 (BASELINE.json configs[1])",
         "global_batch": args.global_batch, "micro_batch": micro, "grad_accum": accum, "parallelism": f"dp{world}",
-        "norm_pix_loss": False,
+        "norm_pix_loss": bool(getattr(args, "norm_pix_loss", False)),
         "l2": "inputs larger than L2: every micro-batch streams tens of GB of activations through a 126 MB L2",
     }
 
@@ -201,6 +201,7 @@ def run_ours(args):
     assert micro * accum * world == args.global_batch, "global batch must divide into micro-batches"
     ns = preset_args(args.config, args.global_batch)
     ns.grad_accum = accum
+    ns.norm_pix_loss = bool(args.norm_pix_loss)
     state = create_train_state(ns).replicate()
     cfg = state.cfg
     eng = state.engine(micro)
@@ -589,6 +590,8 @@ def main():
     ap.add_argument("--micro-batch", type=int, default=None,
                     help="per-GPU micro-batch (default: 2048 for vit_b16 -- ~95 GB of saved activations --, 512 for vit_l16, 256 for vit_h14)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--norm-pix-loss", action="store_true",
+                    help="secondary measurement (SURVEY.md 8d): the norm-pix target, off in both reference presets")
     ap.add_argument("--workload", default="pretrain", choices=["pretrain", "finetune"],
                     help="pretrain: BASELINE.json configs[1..3] (the headline); finetune: configs[4]")
     ap.add_argument("--no-kernel-timings", action="store_true", help="skip the isolated GEMM re-timings (profiling runs)")
