@@ -44,6 +44,24 @@ long long jm_launch_count(void);
 int jm_mask_sort(const float* noise, int length, int keep, int32_t* ids_shuffle, int32_t* ids_restore,
                  float* mask_row, void* stream);
 
+/* Per-image masking, an opt-in extension (the reference draws ONE permutation per batch, src/utils_mae.py:88-96):
+ * jm_mask_sort over a [batch, length] noise matrix, one row per image; and the index consumers with `ids_stride` =
+ * elements between two images' index rows (jm_patchify_pi, jm_masked_targets_pi, jm_unshuffle_fwd_pi / _bwd_pi,
+ * jm_posemb_grad_pi; jm_gemm takes pe_idx_stride).  The backward variants add with vector atomics. */
+int jm_mask_sort_batched(const float* noise, int batch, int length, int keep, int32_t* ids_shuffle, int32_t* ids_restore,
+                         float* mask, void* stream);
+int jm_patchify_pi(const uint8_t* images, int batch, int image_size, int patch_size, const int32_t* ids, long ids_stride,
+                   int n_sel, int rows_per_image, int row_off, jm_bf16* out, long ldo, void* stream);
+int jm_masked_targets_pi(const uint8_t* images, int batch, int image_size, int patch_size, const int32_t* ids,
+                         long ids_stride, int n_sel, int num_cls, int norm_pix, uint8_t* targets, long ldt, float* stats,
+                         int32_t* row_map, void* stream);
+int jm_unshuffle_fwd_pi(const float* y, const int32_t* ids_restore, long ids_stride, const float* mask_emb,
+                        const float* dec_wpe, int batch, int N, int n, int J, int dim, float* out, void* stream);
+int jm_unshuffle_bwd_pi(const float* dout, const int32_t* ids_restore, long ids_stride, int batch, int N, int n, int J,
+                        int dim, jm_bf16* dy, float* dmask_emb, void* stream);
+int jm_posemb_grad_pi(const float* dx, long ldx, int batch, int T, int J, int n, const int32_t* ids, long ids_stride,
+                      int dim, float* dwpe, void* stream);
+
 /* index_sequence, src/utils_mae.py:84-85: out[b, i, :] = x[b, ids[i], :] (f32). */
 int jm_index_sequence(const float* x, const int32_t* ids, int batch, int length_in, int length_out, int dim,
                       float* out, void* stream);
@@ -269,6 +287,9 @@ typedef struct jm_gemm_args {
   /* optional [N] (out_f32 epilogue): out_f32 = row_scale * col_scale_vec[col] * (acc + bias) + residual -- LayerScale's
    * scale1 / scale2 / scale3 on a residual branch (src/modeling.py:159-166,185-201) */
   const float* col_scale_vec;
+  /* elements between two images' rows of pe_idx: 0 = one index row shared by the batch (the reference), row_period -
+   * row_skip entries per image otherwise (per-image masking) */
+  long pe_idx_stride;
 } jm_gemm_args;
 int jm_gemm(const jm_gemm_args* args, void* stream);
 

@@ -36,6 +36,7 @@ class MAEConfig:
     posemb: str = "sincos2d"           # "learnable": model/embed/wpe is a trained parameter (src/modeling.py:115-118)
     layerscale: bool = False           # per-channel scale1/2/3 on the encoder's residual branches, init 1e-4 (src/modeling.py:159-162,185-189)
     dec_layerscale: bool = False       # the same for the decoder's ViTLayers (scale1/2)
+    per_image_masking: bool = False    # opt-in extension: noise [B, N], one permutation per image (the reference shares one per batch, src/utils_mae.py:88-96)
     grad_ckpt: bool = False            # nn.remat of every layer (src/modeling.py:232,280): activations are recomputed in backward
     labels: int = 0                    # > 0: classification mode (ViT head, no masking, no decoder; src/modeling.py:239-242,252)
 

@@ -42,6 +42,9 @@ __global__ void mask_sort_kernel(const float* __restrict__ noise, int L, int kee
                                  int* __restrict__ ids_restore, float* __restrict__ mask_row) {
   extern __shared__ float s_noise[];
   const int i = threadIdx.x;
+  // one block per row of a [batch, L] problem (per-image masking); the reference's shared permutation is batch = 1
+  noise += static_cast<long>(blockIdx.x) * L, ids_shuffle += static_cast<long>(blockIdx.x) * L;
+  ids_restore += static_cast<long>(blockIdx.x) * L, mask_row += static_cast<long>(blockIdx.x) * L;
   if (i < L) s_noise[i] = noise[i];
   __syncthreads();
   if (i >= L) return;
@@ -93,7 +96,7 @@ __device__ __forceinline__ void stage_patch(uint8_t* spix, const uint8_t* img, i
 // One warp per output row, eight rows in flight per block (see patch_loss_kernel for why).
 __global__ void __launch_bounds__(256)
 patchify_kernel(const uint8_t* __restrict__ images, int S, int p, const int* __restrict__ ids, int n_sel,
-                int rows_per_image, int row_off, __nv_bfloat16* __restrict__ out, long ldo, int batch) {
+                int rows_per_image, int row_off, __nv_bfloat16* __restrict__ out, long ldo, int batch, long ids_stride) {
   __shared__ __align__(16) uint8_t spix_all[8][2048];  // per warp: the patch's 3 planes of p x p bytes (P <= 2048, checked)
   __shared__ float lut[768];
   fill_norm_lut(lut);
@@ -108,7 +111,7 @@ patchify_kernel(const uint8_t* __restrict__ images, int S, int p, const int* __r
       for (int e = lane * 4; e < ldo; e += 128) *reinterpret_cast<uint2*>(dst + e) = make_uint2(0u, 0u);
       continue;
     }
-    const int patch = ids ? ids[r - row_off] : (r - row_off);
+    const int patch = ids ? ids[b * ids_stride + r - row_off] : (r - row_off);
     const int gy = patch / g, gx = patch - gy * g;
     const uint8_t* img = images + static_cast<long>(b) * 3 * S * S;
     __syncwarp();
@@ -137,7 +140,7 @@ patchify_kernel(const uint8_t* __restrict__ images, int S, int p, const int* __r
 __global__ void __launch_bounds__(256)
 masked_targets_kernel(const uint8_t* __restrict__ images, int S, int p, const int* __restrict__ ids, int n_sel, int J,
                       int batch, int norm_pix, uint8_t* __restrict__ tgt, long ldt, float* __restrict__ stats,
-                      int* __restrict__ row_map) {
+                      int* __restrict__ row_map, long ids_stride) {
   __shared__ __align__(16) uint8_t spix_all[8][2048];
   __shared__ float lut[768];
   fill_norm_lut(lut);
@@ -147,7 +150,7 @@ masked_targets_kernel(const uint8_t* __restrict__ images, int S, int p, const in
   const long rows = static_cast<long>(batch) * n_sel;
   for (long row = static_cast<long>(blockIdx.x) * 8 + warp; row < rows; row += static_cast<long>(gridDim.x) * 8) {
     const int b = static_cast<int>(row / n_sel), k = static_cast<int>(row - static_cast<long>(b) * n_sel);
-    const int patch = ids[k];
+    const int patch = ids[b * ids_stride + k];
     const int gy = patch / g, gx = patch - gy * g;
     if (row_map && lane == 0) row_map[row] = b * (J + N) + J + patch;
     __syncwarp();
@@ -395,6 +398,16 @@ __global__ void posemb_grad_kernel(const float* __restrict__ dx, long ldx, int b
   float4 o = *dst;
   o.x += acc.x, o.y += acc.y, o.z += acc.z, o.w += acc.w;
   *dst = o;
+}
+
+// the same with one index row per image: every (kept patch, image) adds its row into dwpe[ids[b, i]] (vector atomics)
+__global__ void posemb_grad_pi_kernel(const float* __restrict__ dx, long ldx, int T, int J, int n,
+                                      const int* __restrict__ ids, long ids_stride, int dim, float* __restrict__ dwpe) {
+  const int i = blockIdx.x, b = blockIdx.y;
+  const float* src = dx + (static_cast<long>(b) * T + J + i) * ldx;
+  float* dst = dwpe + static_cast<long>(ids[b * ids_stride + i]) * dim;
+  for (int c = threadIdx.x * 4; c < dim; c += blockDim.x * 4)
+    atomicAdd(reinterpret_cast<float4*>(dst + c), *reinterpret_cast<const float4*>(src + c));
 }
 
 // x[r, :] *= (r % period < skip ? scale_cls : scale)[r / period]: the transpose of a DropPath-scaled residual branch
@@ -946,8 +959,9 @@ __global__ void fill_cls_kernel(float* __restrict__ x, int T, int J, int dim, co
 
 __global__ void unshuffle_fwd_kernel(const float* __restrict__ y, const int* __restrict__ ids_restore,
                                      const float* __restrict__ mask_emb, const float* __restrict__ wpe, int N, int n,
-                                     int J, int dim, float* __restrict__ out) {
+                                     int J, int dim, float* __restrict__ out, long ids_stride) {
   const int t = blockIdx.x, b = blockIdx.y;
+  ids_restore += b * ids_stride;
   float* dst = out + (static_cast<long>(b) * (J + N) + t) * dim;
   const float* src;
   const float* pe = nullptr;
@@ -1106,6 +1120,17 @@ extern "C" int jm_mask_sort(const float* noise, int length, int keep, int32_t* i
   return 0;
 }
 
+extern "C" int jm_mask_sort_batched(const float* noise, int batch, int length, int keep, int32_t* ids_shuffle,
+                                    int32_t* ids_restore, float* mask, void* stream) {
+  JM_CHECK(length > 0 && length <= 1024, "jm_mask_sort_batched: length must be in [1, 1024] (got %d)", length);
+  JM_CHECK(keep >= 0 && keep <= length && batch > 0, "jm_mask_sort_batched: keep / batch out of range");
+  const int threads = (length + 31) / 32 * 32;
+  mask_sort_kernel<<<batch, threads, length * sizeof(float), STREAM>>>(noise, length, keep, ids_shuffle, ids_restore,
+                                                                       mask);
+  JM_AFTER_LAUNCH();
+  return 0;
+}
+
 extern "C" int jm_index_sequence(const float* x, const int32_t* ids, int batch, int length_in, int length_out,
                                  int dim, float* out, void* stream) {
   if (batch == 0 || length_out == 0) return 0;
@@ -1125,7 +1150,25 @@ extern "C" int jm_patchify(const uint8_t* images, int batch, int image_size, int
   const long want = (static_cast<long>(batch) * rows_per_image + 7) / 8, cap = static_cast<long>(sm_count()) * 16;
   patchify_kernel<<<static_cast<int>(want < cap ? want : cap), 256, 0, STREAM>>>(
       images, image_size, patch_size, ids, n_sel, rows_per_image, row_off, reinterpret_cast<__nv_bfloat16*>(out), ldo,
-      batch);
+      batch, 0L);
+  JM_AFTER_LAUNCH();
+  return 0;
+}
+
+// Per-image index tables (opt-in extension of random_masking: noise [batch, L], one permutation per image).  The
+// entries below are the shared-permutation ones with `ids_stride` = elements between two images' index rows.
+extern "C" int jm_patchify_pi(const uint8_t* images, int batch, int image_size, int patch_size, const int32_t* ids,
+                              long ids_stride, int n_sel, int rows_per_image, int row_off, jm_bf16* out, long ldo,
+                              void* stream) {
+  JM_CHECK(images && out && ids, "jm_patchify_pi: null argument");
+  JM_CHECK(image_size % patch_size == 0 && ldo >= patch_size * patch_size * 3 && row_off + n_sel <= rows_per_image &&
+               patch_size * patch_size * 3 <= 2048 && ldo % 4 == 0 && (reinterpret_cast<uintptr_t>(out) & 7) == 0,
+           "jm_patchify_pi: bad shape (see jm_patchify)");
+  if (batch == 0) return 0;
+  const long want = (static_cast<long>(batch) * rows_per_image + 7) / 8, cap = static_cast<long>(sm_count()) * 16;
+  patchify_kernel<<<static_cast<int>(want < cap ? want : cap), 256, 0, STREAM>>>(
+      images, image_size, patch_size, ids, n_sel, rows_per_image, row_off, reinterpret_cast<__nv_bfloat16*>(out), ldo,
+      batch, ids_stride);
   JM_AFTER_LAUNCH();
   return 0;
 }
@@ -1191,6 +1234,16 @@ extern "C" int jm_posemb_grad(const float* dx, long ldx, int batch, int T, int J
   JM_CHECK(dim % 4 == 0 && ldx % 4 == 0 && ((reinterpret_cast<uintptr_t>(dx) | reinterpret_cast<uintptr_t>(dwpe)) & 15) == 0,
            "jm_posemb_grad: dim and ldx must be multiples of 4 and the buffers 16-byte aligned");
   posemb_grad_kernel<<<dim3(n, (dim / 4 + 127) / 128), 128, 0, STREAM>>>(dx, ldx, batch, T, J, n, ids, dim, dwpe);
+  JM_AFTER_LAUNCH();
+  return 0;
+}
+
+extern "C" int jm_posemb_grad_pi(const float* dx, long ldx, int batch, int T, int J, int n, const int32_t* ids,
+                                 long ids_stride, int dim, float* dwpe, void* stream) {
+  JM_CHECK(dx && dwpe && ids && batch > 0 && n > 0 && T >= J + n && dim > 0, "jm_posemb_grad_pi: bad arguments");
+  JM_CHECK(dim % 4 == 0 && ldx % 4 == 0 && ((reinterpret_cast<uintptr_t>(dx) | reinterpret_cast<uintptr_t>(dwpe)) & 15) == 0,
+           "jm_posemb_grad_pi: dim and ldx must be multiples of 4 and the buffers 16-byte aligned");
+  posemb_grad_pi_kernel<<<dim3(n, batch), 128, 0, STREAM>>>(dx, ldx, T, J, n, ids, ids_stride, dim, dwpe);
   JM_AFTER_LAUNCH();
   return 0;
 }
@@ -1452,7 +1505,23 @@ extern "C" int jm_masked_targets(const uint8_t* images, int batch, int image_siz
   if (batch == 0 || n_sel == 0) return 0;
   const long want = (static_cast<long>(batch) * n_sel + 7) / 8, cap = static_cast<long>(sm_count()) * 16;
   masked_targets_kernel<<<static_cast<int>(want < cap ? want : cap), 256, 0, STREAM>>>(
-      images, image_size, patch_size, ids, n_sel, num_cls, batch, norm_pix, targets, ldt, stats, row_map);
+      images, image_size, patch_size, ids, n_sel, num_cls, batch, norm_pix, targets, ldt, stats, row_map, 0L);
+  JM_AFTER_LAUNCH();
+  return 0;
+}
+
+extern "C" int jm_masked_targets_pi(const uint8_t* images, int batch, int image_size, int patch_size, const int32_t* ids,
+                                    long ids_stride, int n_sel, int num_cls, int norm_pix, uint8_t* targets, long ldt,
+                                    float* stats, int32_t* row_map, void* stream) {
+  JM_CHECK(images && ids && targets, "jm_masked_targets_pi: null argument");
+  const int P = patch_size * patch_size * 3;
+  JM_CHECK(image_size % patch_size == 0 && P <= 2048 && P % 4 == 0 && ldt >= P && ldt % 16 == 0 &&
+               (reinterpret_cast<uintptr_t>(targets) & 15) == 0 && (!norm_pix || stats),
+           "jm_masked_targets_pi: bad shape (see jm_masked_targets)");
+  if (batch == 0 || n_sel == 0) return 0;
+  const long want = (static_cast<long>(batch) * n_sel + 7) / 8, cap = static_cast<long>(sm_count()) * 16;
+  masked_targets_kernel<<<static_cast<int>(want < cap ? want : cap), 256, 0, STREAM>>>(
+      images, image_size, patch_size, ids, n_sel, num_cls, batch, norm_pix, targets, ldt, stats, row_map, ids_stride);
   JM_AFTER_LAUNCH();
   return 0;
 }
@@ -1483,7 +1552,49 @@ extern "C" int jm_unshuffle_fwd(const float* y, const int32_t* ids_restore, cons
                                 void* stream) {
   JM_CHECK(dim % 4 == 0, "jm_unshuffle_fwd: dim must be a multiple of 4");
   if (batch == 0) return 0;
-  unshuffle_fwd_kernel<<<dim3(J + N, batch), 128, 0, STREAM>>>(y, ids_restore, mask_emb, dec_wpe, N, n, J, dim, out);
+  unshuffle_fwd_kernel<<<dim3(J + N, batch), 128, 0, STREAM>>>(y, ids_restore, mask_emb, dec_wpe, N, n, J, dim, out, 0L);
+  JM_AFTER_LAUNCH();
+  return 0;
+}
+
+extern "C" int jm_unshuffle_fwd_pi(const float* y, const int32_t* ids_restore, long ids_stride, const float* mask_emb,
+                                   const float* dec_wpe, int batch, int N, int n, int J, int dim, float* out,
+                                   void* stream) {
+  JM_CHECK(dim % 4 == 0, "jm_unshuffle_fwd_pi: dim must be a multiple of 4");
+  if (batch == 0) return 0;
+  unshuffle_fwd_kernel<<<dim3(J + N, batch), 128, 0, STREAM>>>(y, ids_restore, mask_emb, dec_wpe, N, n, J, dim, out,
+                                                               ids_stride);
+  JM_AFTER_LAUNCH();
+  return 0;
+}
+
+// per-image permutation: every (token, image) moves on its own; mask-token rows add into dmask with vector atomics
+__global__ void unshuffle_bwd_pi_kernel(const float* __restrict__ dout, const int* __restrict__ ids_restore,
+                                        long ids_stride, int N, int n, int J, int dim, __nv_bfloat16* __restrict__ dy,
+                                        float* __restrict__ dmask) {
+  const int t = blockIdx.x, b = blockIdx.y;
+  int dst_tok;
+  if (t < J) dst_tok = t;
+  else {
+    const int r = ids_restore[b * ids_stride + t - J];
+    dst_tok = r < n ? J + r : -1;
+  }
+  for (int c = threadIdx.x * 4; c < dim; c += blockDim.x * 4) {
+    const float4 v = *reinterpret_cast<const float4*>(dout + (static_cast<long>(b) * (J + N) + t) * dim + c);
+    if (dst_tok >= 0)
+      *reinterpret_cast<uint2*>(dy + (static_cast<long>(b) * (J + n) + dst_tok) * dim + c) =
+          make_uint2(pack_bf16(v.x, v.y), pack_bf16(v.z, v.w));
+    else if (dmask) atomicAdd(reinterpret_cast<float4*>(dmask + c), v);
+  }
+}
+
+extern "C" int jm_unshuffle_bwd_pi(const float* dout, const int32_t* ids_restore, long ids_stride, int batch, int N,
+                                   int n, int J, int dim, jm_bf16* dy, float* dmask_emb, void* stream) {
+  JM_CHECK(dim % 4 == 0 && (reinterpret_cast<uintptr_t>(dmask_emb) & 15) == 0,
+           "jm_unshuffle_bwd_pi: dim must be a multiple of 4 and dmask_emb 16-byte aligned");
+  if (batch == 0) return 0;
+  unshuffle_bwd_pi_kernel<<<dim3(J + N, batch), 128, 0, STREAM>>>(dout, ids_restore, ids_stride, N, n, J, dim,
+                                                                  reinterpret_cast<__nv_bfloat16*>(dy), dmask_emb);
   JM_AFTER_LAUNCH();
   return 0;
 }

@@ -92,6 +92,7 @@ struct EpiParams {
   const float* loss_stats;     // optional [M, 2]: norm_pix mean and 1 / sqrt(var + eps) of the row's normalised target
   float* row_loss;             // [M, ceil(N / 16)]
   float loss_scale;
+  long pe_idx_stride;          // elements between two images' rows of pe_idx (0: one index row shared by the batch)
   const float* col_vec;        // optional [N]: (acc + bias) is multiplied by col_vec[col] before row_scale and the residual
                                // (LayerScale, src/modeling.py:159-166,185-201); f32 TMA epilogue only
 };
@@ -241,7 +242,7 @@ __device__ __forceinline__ void epilogue8(const EpiParams& ep, float (&v)[8], co
     store_bf16x8<FULL>(ep.out_bf16 + off_row * ep.ldo_bf16 + col, v, ncols);
   } else if constexpr (EPI == EPI_F32) {
     if (ep.pe) {
-      const float* pe = ep.pe + static_cast<long>(ep.pe_idx[row % ep.row_period - ep.row_skip]) * ep.ldpe + col;
+      const float* pe = ep.pe + static_cast<long>(ep.pe_idx[(row / ep.row_period) * ep.pe_idx_stride + row % ep.row_period - ep.row_skip]) * ep.ldpe + col;
       const float4 a = *reinterpret_cast<const float4*>(pe);
       v[0] += a.x, v[1] += a.y, v[2] += a.z, v[3] += a.w;
       if (FULL || ncols >= 8) {
@@ -301,7 +302,7 @@ __device__ __forceinline__ void epilogue8(const EpiParams& ep, float (&v)[8], co
       }
       if (ep.pe) {
         const float4 b = *reinterpret_cast<const float4*>(
-            ep.pe + static_cast<long>(ep.pe_idx[row % ep.row_period - ep.row_skip]) * ep.ldpe + c4);
+            ep.pe + static_cast<long>(ep.pe_idx[(row / ep.row_period) * ep.pe_idx_stride + row % ep.row_period - ep.row_skip]) * ep.ldpe + c4);
         x[0] += b.x, x[1] += b.y, x[2] += b.z, x[3] += b.w;
       }
       if (ep.residual) {
@@ -1907,6 +1908,7 @@ extern "C" int jm_gemm(const jm_gemm_args* a, void* stream_) {
   ep.colsum = a->colsum;
   ep.row_scale = a->row_scale, ep.row_scale_period = a->row_scale_period;
   ep.col_vec = a->col_scale_vec;
+  ep.pe_idx_stride = a->pe_idx_stride;
   ep.loss_target = a->loss_target, ep.ld_target = a->ld_target, ep.loss_stats = a->loss_stats;
   ep.row_loss = a->row_loss, ep.loss_scale = a->loss_scale;
   JM_CHECK(!a->row_scale || a->row_scale_period > 0, "jm_gemm: row_scale needs row_scale_period > 0");

@@ -96,9 +96,12 @@ class MAEEngine:
         self.wpe = fixed_sincos2d_embeddings(cfg.grid, cfg.grid, d).reshape(N, d).contiguous().to(dev)
         self.dec_wpe = fixed_sincos2d_embeddings(cfg.grid, cfg.grid, dd).reshape(N, dd).contiguous().to(dev)
 
-        self.ids_shuffle = e(N, dt=torch.int32)
-        self.ids_restore = e(N, dt=torch.int32)
-        self.mask_row = e(N, dt=F32)
+        # one permutation for the whole batch (the reference), or one row per image (cfg.per_image_masking)
+        self.per_image = bool(getattr(cfg, "per_image_masking", False)) and cfg.labels <= 0
+        ishape = (B, N) if self.per_image else (N,)
+        self.ids_shuffle = e(*ishape, dt=torch.int32)
+        self.ids_restore = e(*ishape, dt=torch.int32)
+        self.mask_row = e(*ishape, dt=F32)
         self.patches = e(self.Me, self.Pp)
         # encoder
         self.xa: List[torch.Tensor] = [e(self.Me, d, dt=F32) for _ in range(cfg.layers + 1)]
@@ -129,6 +132,8 @@ class MAEEngine:
         if fused_head is None:
             fused_head = os.environ.get("JM_HEAD_FUSED", "1") != "0"
         self.fused_head = bool(fused_head) and dd <= 512 and cfg.labels <= 0
+        if self.per_image and not self.fused_head:
+            raise NotImplementedError("per-image masking is built on the fused pixel head (dec_dim <= 512, fused_head=True)")
         self.n_mask = N - n
         self.Mh = B * self.n_mask if self.fused_head else self.Md
         self.meanD, self.rstdD = e(self.Mh, dt=F32), e(self.Mh, dt=F32)
@@ -235,8 +240,14 @@ class MAEEngine:
         lib = _lib.load()
         st = _lib.stream_ptr()
         # random_masking (src/utils_mae.py:88-96) from host-supplied noise
-        c(lib.jm_mask_sort(noise.data_ptr(), N, n, self.ids_shuffle.data_ptr(), self.ids_restore.data_ptr(),
-                           self.mask_row.data_ptr(), st))
+        if tuple(noise.shape) != tuple(self.mask_row.shape):
+            raise _lib.JmError(f"noise must have shape {tuple(self.mask_row.shape)}, got {tuple(noise.shape)}")
+        if self.per_image:
+            c(lib.jm_mask_sort_batched(noise.data_ptr(), B, N, n, self.ids_shuffle.data_ptr(), self.ids_restore.data_ptr(),
+                                       self.mask_row.data_ptr(), st))
+        else:
+            c(lib.jm_mask_sort(noise.data_ptr(), N, n, self.ids_shuffle.data_ptr(), self.ids_restore.data_ptr(),
+                               self.mask_row.data_ptr(), st))
         # pre-processing + extract kept patches (src/pretraining.py:90-91, modeling.py:246,256)
         ops.patchify(images, cfg.patch_size, self.ids_shuffle, n, Te, J, self.patches)
         x0 = self.xa[0]
@@ -273,7 +284,7 @@ class MAEEngine:
         cfg, ps = self.cfg, self.ps
         if self.fused_head:
             P, n_mask = cfg.patch_dim, self.n_mask
-            ops.masked_targets(self.images, cfg.patch_size, self.ids_shuffle[cfg.keep:], cfg.num_cls_tokens,
+            ops.masked_targets(self.images, cfg.patch_size, self.ids_shuffle[..., cfg.keep:], cfg.num_cls_tokens,
                                cfg.norm_pix_loss, self.tgt_u8, self.tgt_stats, self.row_map)
             ops.layernorm_fwd_rows(self.za[cfg.dec_layers], self.row_map, ps.f("decoder_model/dec_norm/scale"),
                                    ps.f("decoder_model/dec_norm/bias"), LN_EPS, self.dec_n, self.meanD, self.rstdD)
@@ -568,7 +579,7 @@ class MAEEngine:
         ~1800 kernel launches issued from Python."""
         cfg, B = self.cfg, self.B
         self.images_buf = torch.empty(B, 3, cfg.image_size, cfg.image_size, dtype=torch.uint8, device=self.dev)
-        self.noise_buf = torch.zeros(cfg.num_patches, dtype=F32, device=self.dev)
+        self.noise_buf = torch.zeros(tuple(self.mask_row.shape), dtype=F32, device=self.dev)
         side = torch.cuda.Stream(device=self.dev)
         side.wait_stream(torch.cuda.current_stream())
         with torch.cuda.stream(side):                  # eager warm-up: one-time function attributes, module load

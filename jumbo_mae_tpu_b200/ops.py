@@ -71,6 +71,10 @@ def patchify(images: torch.Tensor, patch_size: int, ids: Optional[torch.Tensor],
     _chk(images, U8, "images"), _chk(ids, I32, "ids"), _chk(out, BF16, "out")
     B, C, H, W = images.shape
     assert C == 3 and H == W and images.is_contiguous()
+    if ids is not None and ids.dim() == 2:         # one index row per image (per-image masking)
+        check(_lib.load().jm_patchify_pi(ptr(images), B, H, patch_size, ptr(ids), ids.stride(0), n_sel, rows_per_image,
+                                         row_off, ptr(out), _ld(out), stream_ptr()))
+        return out
     check(_lib.load().jm_patchify(ptr(images), B, H, patch_size, ptr(ids), n_sel, rows_per_image, row_off, ptr(out),
                                   _ld(out), stream_ptr()))
     return out
@@ -123,6 +127,10 @@ def posemb_grad(dx: torch.Tensor, batch: int, T: int, J: int, n: int, ids: Optio
                 dwpe: torch.Tensor) -> None:
     """dwpe[ids[i]] += sum_b dx[b*T + J + i] (learnable position embedding, src/modeling.py:115-118,123)."""
     _chk(dx, F32, "dx"), _chk(ids, I32, "ids"), _chk(dwpe, F32, "dwpe")
+    if ids is not None and ids.dim() == 2:
+        check(_lib.load().jm_posemb_grad_pi(ptr(dx), _ld(dx), batch, T, J, n, ptr(ids), ids.stride(0), dim, ptr(dwpe),
+                                            stream_ptr()))
+        return
     check(_lib.load().jm_posemb_grad(ptr(dx), _ld(dx), batch, T, J, n, ptr(ids), dim, ptr(dwpe), stream_ptr()))
 
 
@@ -255,6 +263,11 @@ def masked_targets(images: torch.Tensor, patch_size: int, ids: torch.Tensor, num
     """Byte targets (+ norm-pix statistics, + decoder rows) of the patches ``ids`` for the loss epilogue of gemm(act=5)."""
     _chk(images, torch.uint8, "images"), _chk(ids, I32, "ids"), _chk(targets, torch.uint8, "targets")
     _chk(stats, F32, "stats"), _chk(row_map, I32, "row_map")
+    if ids.dim() == 2:
+        check(_lib.load().jm_masked_targets_pi(ptr(images), images.shape[0], images.shape[-1], patch_size, ptr(ids),
+                                               ids.stride(0), ids.shape[1], num_cls, int(norm_pix), ptr(targets),
+                                               _ld(targets), ptr(stats), ptr(row_map), stream_ptr()))
+        return
     check(_lib.load().jm_masked_targets(ptr(images), images.shape[0], images.shape[-1], patch_size, ptr(ids), ids.numel(),
                                         num_cls, int(norm_pix), ptr(targets), _ld(targets), ptr(stats), ptr(row_map),
                                         stream_ptr()))
@@ -303,6 +316,7 @@ def gemm(A: torch.Tensor, B: torch.Tensor, M: int, N: int, K: int, *, a_mn: bool
     a.residual, a.ldr = ptr(residual), (_ld(residual) if ldr is None else ldr)
     a.aux, a.ldaux = ptr(aux), (_ld(aux) if ldaux is None else ldaux)
     a.pe, a.pe_idx, a.ldpe = ptr(pe), ptr(pe_idx), _ld(pe)
+    a.pe_idx_stride = pe_idx.stride(0) if (pe_idx is not None and pe_idx.dim() == 2) else 0
     a.act = act
     a.col_scale, a.col_scale_n = col_scale, col_scale_n
     a.row_period, a.row_skip, a.row_mask_mode = row_period, row_skip, row_mask_mode
@@ -364,6 +378,10 @@ def unshuffle_fwd(y: torch.Tensor, ids_restore: torch.Tensor, mask_emb: torch.Te
                   batch: int, N: int, n: int, J: int, dim: int, out: torch.Tensor) -> None:
     _chk(y, F32, "y"), _chk(ids_restore, I32, "ids_restore"), _chk(mask_emb, F32, "mask_emb")
     _chk(dec_wpe, F32, "dec_wpe"), _chk(out, F32, "out")
+    if ids_restore.dim() == 2:
+        check(_lib.load().jm_unshuffle_fwd_pi(ptr(y), ptr(ids_restore), ids_restore.stride(0), ptr(mask_emb),
+                                              ptr(dec_wpe), batch, N, n, J, dim, ptr(out), stream_ptr()))
+        return
     check(_lib.load().jm_unshuffle_fwd(ptr(y), ptr(ids_restore), ptr(mask_emb), ptr(dec_wpe), batch, N, n, J, dim,
                                        ptr(out), stream_ptr()))
 
@@ -372,6 +390,10 @@ def unshuffle_bwd(dout: torch.Tensor, ids_restore: torch.Tensor, batch: int, N: 
                   dy: torch.Tensor, dmask_emb: torch.Tensor) -> None:
     _chk(dout, F32, "dout"), _chk(ids_restore, I32, "ids_restore"), _chk(dy, BF16, "dy")
     _chk(dmask_emb, F32, "dmask_emb")
+    if ids_restore.dim() == 2:
+        check(_lib.load().jm_unshuffle_bwd_pi(ptr(dout), ptr(ids_restore), ids_restore.stride(0), batch, N, n, J, dim,
+                                              ptr(dy), ptr(dmask_emb), stream_ptr()))
+        return
     check(_lib.load().jm_unshuffle_bwd(ptr(dout), ptr(ids_restore), batch, N, n, J, dim, ptr(dy), ptr(dmask_emb),
                                        stream_ptr()))
 

@@ -98,12 +98,20 @@ class TrainState:
         self._noise_gen = np.random.Generator(np.random.Philox(key=self.noise_rng + 7919 * process_index()))
         return self
 
-    def split_rngs(self) -> Tuple[dict, dict]:
+    def noise_shape(self, batch: Optional[int]):
+        """[num_patches] (one permutation per batch, the reference) or [batch, num_patches] (--per-image-masking)."""
+        if getattr(self.cfg, "per_image_masking", False):
+            if batch is None:
+                raise _lib.JmError("per-image masking: the noise draw needs the batch size")
+            return (batch, self.cfg.num_patches)
+        return (self.cfg.num_patches,)
+
+    def split_rngs(self, batch: Optional[int] = None) -> Tuple[dict, dict]:
         """src/pretraining.py:59-66: draws this step's "noise" stream (mixup / dropout are
         identity at the recipe's rates).  Returns (rngs, updates) like the reference."""
         if self._noise_gen is None:
             self.replicate()
-        noise = self._noise_gen.random(self.cfg.num_patches, dtype=np.float32)
+        noise = self._noise_gen.random(self.noise_shape(batch), dtype=np.float32)
         return {"noise": noise}, {}
 
     def engine(self, batch: int) -> MAEEngine:
@@ -185,6 +193,7 @@ def create_train_state(args: argparse.Namespace) -> TrainState:
                         adam_eps=args.adam_eps, warmup_steps=args.warmup_steps, training_steps=args.training_steps,
                         grad_accum=getattr(args, "grad_accum", 1), posemb=posemb,
                         grad_ckpt=bool(getattr(args, "grad_ckpt", False)),
+                        per_image_masking=bool(getattr(args, "per_image_masking", False)),
                         layerscale=bool(getattr(args, "layerscale", False)),
                         dec_layerscale=bool(getattr(args, "dec_layerscale", False)))
     cfg.validate()
@@ -246,7 +255,7 @@ def training_step(state: TrainState, batch, noise=None) -> Tuple[TrainState, Dic
     ``noise`` (f32 [num_patches]) overrides the state's noise stream (parity tests).
     Returns (state, {"loss": device scalar, "learning_rate": float})."""
     images = _device_images(batch[0] if isinstance(batch, (tuple, list)) else batch)
-    rngs, _ = state.split_rngs() if noise is None else ({"noise": noise}, {})
+    rngs, _ = state.split_rngs(images.shape[0]) if noise is None else ({"noise": noise}, {})
     nz = _device_noise(rngs["noise"], state.store.device)
     eng = state.engine(images.shape[0])
     state._consume_prefetched(images)
@@ -304,7 +313,7 @@ def validation_step(state: TrainState, batch, noise=None) -> Dict[str, Any]:
         # freshly split, not stored (src/pretraining.py:164): one validation stream per rank, advanced per call
         if getattr(state, "_val_gen", None) is None:
             state._val_gen = np.random.Generator(np.random.Philox(key=state.noise_rng + 7919 * process_index() + 104729))
-        noise = state._val_gen.random(state.cfg.num_patches, dtype=np.float32)
+        noise = state._val_gen.random(state.noise_shape(images.shape[0]), dtype=np.float32)
     dev = state.store.device
     images = images.to(dev, non_blocking=True)
     nz = _device_noise(noise, dev)

@@ -146,7 +146,11 @@ def fixed_sincos2d_embeddings(ncols: int, nrows: int, dim: int, dtype=torch.floa
 # src/utils_mae.py
 # ----------------------------------------------------------------------------
 def index_sequence(x: torch.Tensor, ids: torch.Tensor) -> torch.Tensor:
-    """src/utils_mae.py:84-85."""
+    """src/utils_mae.py:84-85.  ``ids`` [B, k] (per-image masking, an extension: the reference passes one [k] row)
+    gathers every image with its own indices."""
+    if ids.dim() == 2:
+        idx = ids.long()[:, :, None].expand(-1, -1, x.shape[-1])
+        return torch.gather(x, 1, idx)
     return x[:, ids.long(), ...]
 
 
@@ -173,7 +177,14 @@ def random_masking(x: torch.Tensor, noise, keep_len: int):
     the libraries; the drop-in boundary therefore takes the noise as an input.
     """
     batch, length, _ = x.shape
-    ids_shuffle, ids_restore, mask_row = masking_from_noise(np.asarray(noise), keep_len)
+    noise = np.asarray(noise)
+    if noise.ndim == 2:              # per-image masking (extension): one permutation per image
+        rows = [masking_from_noise(noise[b], keep_len) for b in range(batch)]
+        ids_shuffle = torch.from_numpy(np.stack([r[0] for r in rows]))
+        ids_restore = torch.from_numpy(np.stack([r[1] for r in rows]))
+        mask = torch.from_numpy(np.stack([r[2] for r in rows])).to(x.dtype)
+        return index_sequence(x, ids_shuffle[:, :keep_len]), mask, ids_restore
+    ids_shuffle, ids_restore, mask_row = masking_from_noise(noise, keep_len)
     kept = index_sequence(x, torch.from_numpy(ids_shuffle[:keep_len].copy()))
     mask = torch.from_numpy(mask_row)[None, :].expand(batch, length).to(x.dtype)
     return kept, mask, torch.from_numpy(ids_restore)
@@ -381,7 +392,7 @@ def pretrain_forward(params: Tree, images_u8, noise, cfg: MAEConfig, collect=Non
     encoder_cls, image_x = x[:, :J, :], x[:, J:, :]
     bs = image_x.shape[0]
     masked = params["image_mask_embedding"].expand(
-        bs, int(ids_restore.shape[0] * cfg.image_mask_ratio), cfg.dec_dim)
+        bs, int(ids_restore.shape[-1] * cfg.image_mask_ratio), cfg.dec_dim)
     image_x = index_sequence(torch.cat([image_x, masked], dim=1), ids_restore)
     x = torch.cat([encoder_cls, image_x], dim=1)
     x = decoder_forward(x, params["decoder_model"], cfg, collect)

@@ -536,3 +536,56 @@ def test_full_size_step_is_the_mean_of_its_halves(preset):
     assert abs(loss_whole - sum(losses) / 2) <= 2e-5 * abs(loss_whole)
     assert math.isfinite(loss_whole) and g_whole.abs().max().item() > 0
     assert _rel(store.g * 0.5, g_whole) <= 3e-3          # bf16 activations: the batched Jumbo products round differently
+
+
+@pytest.mark.parametrize("base", ["tiny", "tiny_learnable_wpe", "tiny_normpix"])
+def test_per_image_masking_matches_oracle(base):
+    """cfg.per_image_masking (opt-in extension of random_masking: noise [B, N], one permutation per image): index tables
+    bit-exact per image, loss and every gradient against the oracle with the same per-image noise."""
+    import dataclasses
+    from jumbo_mae_tpu_b200.engine import MAEEngine
+    from jumbo_mae_tpu_b200.params import ParamStore, tree_leaves
+    ocfg, B = _cfgs()[base]
+    cfg = dataclasses.replace(_product_cfg(ocfg), per_image_masking=True)
+    state = O.create_state(ocfg, seed=0, randomize_all=True)
+    images, _ = O.synthetic_batch(ocfg, B, seed=1, noise_seed=1001)
+    noise = np.random.default_rng(5).random((B, ocfg.num_patches), dtype=np.float32)
+    store = ParamStore(cfg)
+    store.load_tree(state.params)
+    eng = MAEEngine(cfg, store, B)
+    collect = {}
+    want_fwd = O.pretrain_forward(state.params, images, noise, ocfg, collect)["loss"].item()
+    want_loss, want = O.loss_and_grads(state.params, images, noise, ocfg)
+    eng.forward(images.cuda(), torch.from_numpy(noise).cuda())
+    eng.backward()
+    torch.cuda.synchronize()
+    assert np.array_equal(eng.ids_restore.cpu().numpy(), collect["ids_restore"].numpy())
+    assert np.array_equal(eng.mask_row.cpu().numpy(), collect["mask"].numpy())
+    assert len({tuple(r) for r in eng.ids_restore.cpu().numpy().tolist()}) == B          # the images really differ
+    assert abs(eng.loss.item() - want_fwd) <= 5e-3 * abs(want_fwd)
+    got = dict(tree_leaves(store.tree(store.g)))
+    bad = []
+    ref = dict(O.tree_leaves(want))
+    for path, w in ref.items():
+        g = got[path].detach().cpu().reshape(w.shape)
+        if path[-2:] == ("wk", "bias"):
+            continue
+        r = _rel(g, w)
+        cos = (g.flatten() @ w.flatten() / (g.norm() * w.norm() + 1e-20)).item()
+        if not (r <= 3e-2 and cos >= 0.999):
+            bad.append(("/".join(path), r, cos))
+    assert not bad, bad
+    with pytest.raises(Exception):                                     # a shared [N] noise row is refused
+        eng.forward(images.cuda(), torch.from_numpy(noise[0]).cuda())
+
+
+def test_training_step_draws_per_image_noise():
+    from jumbo_mae_tpu_b200.pretraining import create_train_state, training_step, validation_step
+    ocfg = O.tiny()
+    images, _ = O.synthetic_batch(ocfg, 4, seed=5, noise_seed=6)
+    state = create_train_state(_tiny_args(per_image_masking=True)).replicate()
+    state, metrics = training_step(state, (images,))
+    torch.cuda.synchronize()
+    eng = state.engine(4)
+    assert tuple(eng.ids_restore.shape) == (4, ocfg.num_patches) and math.isfinite(metrics["loss"].item())
+    assert math.isfinite(validation_step(state, (images,))["loss"].item())
