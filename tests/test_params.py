@@ -99,3 +99,47 @@ def test_classification_tree_and_segment_ranges():
     seen = sorted(r for k in range(eng.num_bwd_segments()) for r in eng.segment_grad_ranges(k))
     assert all(a[1] <= b[0] for a, b in zip(seen, seen[1:]))
     assert sum(e - s for s, e in seen) == store.total
+
+
+def test_layerscale_leaves_follow_the_reference_tree():
+    """--layerscale / --dec-layerscale: scale1/2/3 vectors beside the norms (src/modeling.py:159-162,185-189), no weight decay
+    (the mask keeps leaves named ``kernel``), layer-wise lr label of their layer."""
+    from jumbo_mae_tpu_b200.params import get_layer_index
+    ocfg = O.tiny(layerscale=True, dec_layerscale=True)
+    store = ParamStore(_pc(ocfg), device="cpu")
+    got = dict(tree_leaves(store.tree()))
+    ref = dict(O.tree_leaves(O.init_params(ocfg, 0)))
+    assert set(got) == set(ref)
+    J, d, dd = ocfg.num_cls_tokens, ocfg.dim, ocfg.dec_dim
+    assert tuple(got[("model", "layer_1", "scale3")].shape) == (J * d,)
+    assert tuple(got[("decoder_model", "dec_layer_0", "scale2")].shape) == (dd,)
+    assert ("decoder_model", "dec_layer_0", "scale3") not in got
+    for name, leaf in store.leaves.items():
+        if name.rsplit("/", 1)[-1].startswith("scale") and name.rsplit("/", 1)[-1] != "scale":
+            assert not leaf.decay and leaf.offset >= store.n_decay
+    assert get_layer_index("model/layer_1/scale2", ocfg.layers) == 2
+
+
+def test_lamb_tables_cover_every_kernel_leaf_once_with_wqkv_split():
+    """params.lamb_tables: one group per ``kernel`` leaf of the FLAX tree (the fused wqkv matrix gives three), chunks
+    consecutive per group and covering every row exactly once."""
+    ocfg = O.tiny()
+    store = ParamStore(_pc(ocfg), device="cpu")
+    groups, chunks = store.lamb_tables(chunk_elems=1000)
+    flax_kernels = [p for p, _ in O.tree_leaves(O.init_params(ocfg, 0)) if p[-1] == "kernel"]
+    assert groups.shape == (len(flax_kernels), 7) and chunks.shape[1] == 3
+    covered = torch.zeros(store.total, dtype=torch.int32)
+    for gi, (off, rows, ld, col0, ncols, c0, nc) in enumerate(groups.tolist()):
+        mine = chunks[c0:c0 + nc]
+        assert bool((mine[:, 0] == gi).all())
+        assert mine[:, 2].sum().item() == rows and mine[0, 1].item() == 0
+        assert torch.equal(mine[1:, 1], (mine[:-1, 1] + mine[:-1, 2]))
+        for r in range(rows):
+            covered[off + r * ld + col0: off + r * ld + col0 + ncols] += 1
+    kernel_elems = sum(l.rows * l.cols for l in store.leaves.values() if l.decay)
+    assert int((covered == 1).sum()) == kernel_elems and int(covered.max()) == 1
+    assert bool((covered[store.n_decay:] == 0).all())
+    # restricted to one layer-wise lr label
+    g1, _ = store.lamb_tables(lambda n: n.startswith("model/layer_0/"))
+    assert g1.shape[0] == 6            # wq, wk, wv, wo, w1, w2
+    assert store.lamb_tables(lambda n: False) == (None, None)
