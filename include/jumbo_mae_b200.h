@@ -335,6 +335,10 @@ int jm_adamw(float* p, const float* g, float* m, float* v, jm_bf16* p_bf16, long
 
 int jm_cast_bf16(const float* x, jm_bf16* y, long n, void* stream);
 
+/* Zeroes `bytes` bytes on the stream (cudaMemsetAsync): the gradient accumulator at the first micro-step of an optimizer
+ * step (jax.tree_map(jnp.zeros_like, ...), src/pretraining.py:154-156). */
+int jm_zero(void* ptr, size_t bytes, void* stream);
+
 /* --optimizer lamb: the reference's modified_lamb (src/utils.py:124-139) on the `kernel` leaves of the flat buffers:
  * Adam moments, u = m_hat / (sqrt(v_hat) + eps) + wd * p, p -= lr * (||p|| / ||u||) * u with the norms over one leaf of
  * the Flax tree (ratio 1 where a norm is 0).  groups [n_groups, 7] int64 = {offset, rows, ld, col0, ncols, first chunk,

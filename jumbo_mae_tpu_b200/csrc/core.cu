@@ -73,3 +73,10 @@ extern "C" int jm_device_ok(void) {
   if (cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev) != cudaSuccess) return 0;
   return major == 10 ? 1 : 0;
 }
+
+extern "C" int jm_zero(void* ptr, size_t bytes, void* stream) {
+  if (bytes == 0) return 0;
+  JM_CHECK(ptr != nullptr, "jm_zero: null pointer");
+  JM_CUDA(cudaMemsetAsync(ptr, 0, bytes, static_cast<cudaStream_t>(stream)));
+  return 0;
+}

@@ -394,7 +394,7 @@ class MAEEngine:
         view = lambda buf, M, w: buf[:M * w].view(M, w)
         if k == 0:
             if zero_grads:
-                ps.g.zero_()
+                ops.zero_(ps.g)
             # ---- pixel head
             Mh = self.Mh
             dn = view(self.dn16, Mh, dd)
@@ -598,7 +598,7 @@ class MAEEngine:
                 self.backward(zero_grads=zero)
             self.graph_launches = lib.jm_launch_count() - l0
             self.graphs[zero] = g
-        self.ps.g.zero_()
+        ops.zero_(self.ps.g)
 
     def capture_segment_graphs(self) -> None:
         """Graphs for a data-parallel rank's LAST micro-step of an optimizer step: forward + backward
@@ -616,7 +616,7 @@ class MAEEngine:
                     self.backward_segment(k, zero_grads=zero)
                 graphs.append(g)
             self.seg_graphs[zero] = graphs
-        self.ps.g.zero_()
+        ops.zero_(self.ps.g)
 
     def run_graph_overlapped(self, images: torch.Tensor, noise: torch.Tensor, zero_grads: bool, reducer,
                              after_reduce=None) -> torch.Tensor:

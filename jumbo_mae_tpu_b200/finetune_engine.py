@@ -135,11 +135,11 @@ class FinetuneEngine(MAEEngine):
         cfg, ps, B = self.cfg, self.ps, self.B
         J, d, C, Te, Me = cfg.num_cls_tokens, cfg.dim, cfg.labels, self.Te, self.Me
         if zero_grads:
-            ps.g.zero_()
+            ops.zero_(ps.g)
         # head: dW += cls^T dlogits, db += colsum, d cls = dlogits W^T into the CLS rows; patch rows get no gradient
         ops.add_bias_cast(self.dlogits, B, C, dst_bf16=self.dlog16)
         dn = self.dn16[:Me * d].view(Me, d)
-        dn.zero_()
+        ops.zero_(dn)
         self._bwd_linear(self.enc_n, self.dlog16, B, HEAD, C, J * d, dX16=dn, x_ld=Te * d, ldo_bf16=Te * d)
         dx, dx16 = self.dxA[:Me * d].view(Me, d), self.dxA16[:Me * d].view(Me, d)
         ops.layernorm_bwd(dn, self.xa[cfg.layers], self.meanF, self.rstdF, ps.f("model/norm/scale"), None, dx, dx16,
@@ -176,7 +176,7 @@ class FinetuneEngine(MAEEngine):
                 self.backward(zero_grads=zero)
             self.graph_launches = lib.jm_launch_count() - l0
             self.graphs[zero] = g
-        self.ps.g.zero_()
+        ops.zero_(self.ps.g)
 
     def run_graph(self, images: torch.Tensor, labels: torch.Tensor, zero_grads: bool,
                   perm: Optional[torch.Tensor] = None) -> torch.Tensor:

@@ -349,6 +349,13 @@ def lamb(p: torch.Tensor, g: torch.Tensor, m: torch.Tensor, v: torch.Tensor, p_b
                               workspace.numel() * workspace.element_size(), stream_ptr()))
 
 
+def zero_(t: torch.Tensor) -> None:
+    """Zeroes a contiguous device tensor with a memset on the current stream (no kernel launch)."""
+    if not t.is_cuda or not t.is_contiguous():
+        raise _lib.JmError("zero_ takes a contiguous CUDA tensor")
+    check(_lib.load().jm_zero(ptr(t), t.numel() * t.element_size(), stream_ptr()))
+
+
 # ------------------------------------------------------------------ attention
 def attention_fwd(qkv: torch.Tensor, batch: int, T: int, heads: int, head_dim: int, out: torch.Tensor,
                   lse: torch.Tensor) -> None:
