@@ -403,9 +403,11 @@ class MAEEngine:
             # (every LayerNorm backward also emits the column sums of the dx it produces: that dx is the
             #  output gradient of the previous block's ff/w2, i.e. its bias gradient)
             dp_on = self.drop_masks is not None     # then every block sums its ff/w2 bias from its scaled gradient copy
-            # The decoder's residual-gradient stream is carried in bf16 alone (like the reference's bf16 activations):
-            # its LayerNorm backwards move 10 instead of 16 bytes per element.  Only the gradient that leaves the
-            # decoder (layer 0's input, scattered back to the encoder's tokens) is also written in f32.
+            # The decoder's residual-gradient stream is carried in bf16 alone: its LayerNorm backwards move 10 instead
+            # of 16 bytes per element.  (A stated deviation: the reference's gradients are f32 end to end; every
+            # gradient leaf stays inside the parity tolerances with it, JM_DEC_LOWP=0 restores the f32 stream.)  Only
+            # the gradient that leaves the decoder (layer 0's input, scattered back to the encoder's tokens) is also
+            # written in f32.
             lowp = self.dec_lowp and not dp_on and not self.ls_dec
             dcol = None if (dp_on or self.ls_dec) else ps.grad(f"decoder_model/dec_layer_{cfg.dec_layers - 1}/ff/w2/bias")
             if self.fused_head:          # the gradient exists on the masked rows only: scattered into a zeroed dx
