@@ -198,11 +198,21 @@ int jm_layernorm_bwd(const jm_bf16* dy, long lddy, const float* x, long ldx, con
 
 /* jm_layernorm_bwd with the incoming residual gradient in bf16 (dres_bf16, may be NULL) and dx optional (NULL: only the
  * bf16 copy dx_bf16 is written): the decoder's gradient stream kept in bf16 only, 10 instead of 16 bytes per element
- * (dim <= 512).  Same arithmetic otherwise; no row skipping. */
+ * (dim <= 1280).  Same arithmetic otherwise; no row skipping. */
 int jm_layernorm_bwd_lowp(const jm_bf16* dy, long lddy, const float* x, long ldx, const float* mean, const float* rstd,
                           const float* gamma, int rows, int dim, const jm_bf16* dres_bf16, long lddres, float* dx,
                           long lddx, jm_bf16* dx_bf16, long lddxb, float* dgamma, float* dbeta, float* dcol,
                           void* workspace, size_t workspace_bytes, void* stream);
+
+/* The general form of jm_layernorm_bwd_lowp (dim <= 1280): residual gradient read from bf16 (dres_bf16, may be NULL),
+ * row skipping and column-sum selection as jm_layernorm_bwd, and the f32 copy dx (may be NULL) written only for the rows
+ * with row % f32_period < f32_skip (f32_period == 0: every row) -- the encoder's gradient stream in bf16, with f32 kept
+ * for the CLS rows whose Jumbo-MLP gradient is accumulated in f32 (src/modeling.py:191-206). */
+int jm_layernorm_bwd_stream16(const jm_bf16* dy, long lddy, const float* x, long ldx, const float* mean, const float* rstd,
+                              const float* gamma, int rows, int dim, const jm_bf16* dres_bf16, long lddres, float* dx,
+                              long lddx, int f32_period, int f32_skip, jm_bf16* dx_bf16, long lddxb, int row_period,
+                              int row_skip, float* dgamma, float* dbeta, float* dcol, int dcol_period, int dcol_skip,
+                              void* workspace, size_t workspace_bytes, void* stream);
 
 /* LayerNorm over a subset of rows: output row r (compact) is LayerNorm(x[row_map[r], :]); mean / rstd are compact too.
  * jm_layernorm_bwd_rows is its backward: dy, mean, rstd compact [rows], x and dx / dx_bf16 scattered through row_map;

@@ -657,6 +657,13 @@ struct LnDirect {
   int on;
 };
 
+// The residual-gradient stream in bf16: the incoming residual gradient is read from a bf16 tensor (ld in bf16 elements,
+// through the `dres` pointer), and the f32 copy of dx is written only for the rows with row % f32_period < f32_skip (the
+// CLS rows of a Jumbo block, whose Jumbo-MLP gradient is accumulated in f32); f32_period == 0: every row.
+struct LnStream {
+  int res_bf16, f32_period, f32_skip;
+};
+
 template <int NV>
 #ifndef JM_LN_REG_CTAS
 #define JM_LN_REG_CTAS 4  // dim 768: 127 registers without spills, four resident CTAs: 81 -> 77 us at the encoder shape
@@ -667,7 +674,7 @@ layernorm_bwd_reg_kernel(const __nv_bfloat16* __restrict__ dy, long lddy, const 
                          const float* __restrict__ gamma, int rows, int D, const float* __restrict__ dres,
                          long lddres, float* __restrict__ dx, long lddx, __nv_bfloat16* __restrict__ dxb, long lddxb,
                          int row_period, int row_skip, float* __restrict__ ws, int want_dcol, int dcol_period,
-                         int dcol_skip, LnDirect direct) {
+                         int dcol_skip, LnDirect direct, LnStream st) {
   pdl_wait();  // programmatic dependent launch: nothing above touches global memory
   pdl_launch_dependents();
   extern __shared__ __align__(16) float s_acc[];  // [warps][3][D]: dgamma, dbeta, column sums of dx
@@ -689,8 +696,17 @@ layernorm_bwd_reg_kernel(const __nv_bfloat16* __restrict__ dy, long lddy, const 
     for (int k = 0; k < NV; ++k) {
       const int c = lane * 4 + k * 128;
       rres[k] = make_float4(0.f, 0.f, 0.f, 0.f);
-      if (dres && c < D) rres[k] = *reinterpret_cast<const float4*>(dres + row * lddres + c);
+      if (dres && c < D) {
+        if (st.res_bf16) {
+          const uint2 u = *reinterpret_cast<const uint2*>(reinterpret_cast<const __nv_bfloat16*>(dres) + row * lddres + c);
+          const float2 a = unpack_bf16(u.x), b = unpack_bf16(u.y);
+          rres[k] = make_float4(a.x, a.y, b.x, b.y);
+        } else {
+          rres[k] = *reinterpret_cast<const float4*>(dres + row * lddres + c);
+        }
+      }
     }
+    const bool f32_row = dx != nullptr && (st.f32_period == 0 || (row % st.f32_period) < st.f32_skip);
 #pragma unroll
     for (int k = 0; k < NV; ++k) {
       const int c = lane * 4 + k * 128;
@@ -731,7 +747,7 @@ layernorm_bwd_reg_kernel(const __nv_bfloat16* __restrict__ dy, long lddy, const 
 #pragma unroll
         for (int j = 0; j < 4; ++j) o[j] = rs * (d[k][j] - c1 - xh[k][j] * c2);
         o[0] += rres[k].x, o[1] += rres[k].y, o[2] += rres[k].z, o[3] += rres[k].w;
-        if (dx) *reinterpret_cast<float4*>(dx + row * lddx + c) = make_float4(o[0], o[1], o[2], o[3]);
+        if (f32_row) *reinterpret_cast<float4*>(dx + row * lddx + c) = make_float4(o[0], o[1], o[2], o[3]);
         if (dxb) {
           uint2 w = {pack_bf16(o[0], o[1]), pack_bf16(o[2], o[3])};
           *reinterpret_cast<uint2*>(dxb + row * lddxb + c) = w;
@@ -781,7 +797,8 @@ layernorm_bwd_pipe_kernel(const __nv_bfloat16* __restrict__ dy, long lddy, const
                          const float* __restrict__ gamma, int rows, int D, const float* __restrict__ dres,
                          long lddres, float* __restrict__ dx, long lddx, __nv_bfloat16* __restrict__ dxb, long lddxb,
                          int row_period, int row_skip, float* __restrict__ ws, int want_dcol, int dcol_period,
-                         int dcol_skip, LnDirect direct, int res_bf16, const int* __restrict__ row_map) {
+                         int dcol_skip, LnDirect direct, LnStream st, const int* __restrict__ row_map) {
+  const int res_bf16 = st.res_bf16;
   pdl_wait();  // programmatic dependent launch: nothing above touches global memory
   pdl_launch_dependents();
   extern __shared__ __align__(16) float s_acc[];  // [warps][3][D]: dgamma, dbeta, column sums of dx
@@ -882,7 +899,8 @@ layernorm_bwd_pipe_kernel(const __nv_bfloat16* __restrict__ dy, long lddy, const
 #pragma unroll
         for (int j = 0; j < 4; ++j) o[j] = rs * (d[k][j] - c1 - xh[k][j] * c2);
         o[0] += rres[k].x, o[1] += rres[k].y, o[2] += rres[k].z, o[3] += rres[k].w;
-        if (dx) *reinterpret_cast<float4*>(dx + cur.xrow * lddx + c) = make_float4(o[0], o[1], o[2], o[3]);
+        if (dx != nullptr && (st.f32_period == 0 || (row % st.f32_period) < st.f32_skip))
+          *reinterpret_cast<float4*>(dx + cur.xrow * lddx + c) = make_float4(o[0], o[1], o[2], o[3]);
         if (dxb) {
           uint2 w = {pack_bf16(o[0], o[1]), pack_bf16(o[2], o[3])};
           *reinterpret_cast<uint2*>(dxb + cur.xrow * lddxb + c) = w;
@@ -1400,11 +1418,12 @@ static int layernorm_bwd_impl(const jm_bf16* dy, long lddy, const float* x, long
                               long lddres, int res_bf16, float* dx, long lddx, jm_bf16* dx_bf16, long lddxb,
                               int row_period, int row_skip, float* dgamma, float* dbeta, float* dcol, int dcol_period,
                               int dcol_skip, void* workspace, size_t workspace_bytes, void* stream,
-                              const int32_t* row_map = nullptr) {
+                              const int32_t* row_map = nullptr, int f32_period = 0, int f32_skip = 0) {
   JM_CHECK(dim % 4 == 0 && ldx % 4 == 0 && lddy % 4 == 0, "jm_layernorm_bwd: dim/ld must be multiples of 4");
   JM_CHECK(!row_map || dim <= 512, "jm_layernorm_bwd_rows: the scattered variant is built for dim <= 512");
-  JM_CHECK(!res_bf16 || (dim <= 512 && lddres % 4 == 0),
-           "jm_layernorm_bwd_lowp: the bf16 residual-gradient input is built for dim <= 512");
+  JM_CHECK(!res_bf16 || (dim <= 1280 && lddres % 4 == 0),
+           "jm_layernorm_bwd_lowp: the bf16 residual-gradient input is built for dim <= 1280");
+  const LnStream st{res_bf16, f32_period, f32_skip};
   JM_CHECK(dim * 3 * sizeof(float) <= 96 * 1024, "jm_layernorm_bwd: dim %d too large", dim);
   JM_CHECK(dcol == nullptr || dim <= 1280, "jm_layernorm_bwd: dcol is only produced for dim <= 1280");
   if (rows == 0) return 0;
@@ -1430,20 +1449,20 @@ static int layernorm_bwd_impl(const jm_bf16* dy, long lddy, const float* x, long
               ((reinterpret_cast<uintptr_t>(dgamma) | reinterpret_cast<uintptr_t>(dbeta) |
                 reinterpret_cast<uintptr_t>(dcol)) & 15) == 0;
 #define JM_LN_BWD_ARGS_D JM_LN_BWD_ARGS, direct
-  if (dim <= 128) JM_LAUNCH_PDL(layernorm_bwd_pipe_kernel<1>, grid, tr, smem_reg, STREAM, JM_LN_BWD_ARGS_D, res_bf16, static_cast<const int*>(row_map));
-  else if (dim <= 256) JM_LAUNCH_PDL(layernorm_bwd_pipe_kernel<2>, grid, tr, smem_reg, STREAM, JM_LN_BWD_ARGS_D, res_bf16, static_cast<const int*>(row_map));
-  else if (dim <= 512) JM_LAUNCH_PDL(layernorm_bwd_pipe_kernel<4>, grid, tr, smem_reg, STREAM, JM_LN_BWD_ARGS_D, res_bf16, static_cast<const int*>(row_map));
+  if (dim <= 128) JM_LAUNCH_PDL(layernorm_bwd_pipe_kernel<1>, grid, tr, smem_reg, STREAM, JM_LN_BWD_ARGS_D, st, static_cast<const int*>(row_map));
+  else if (dim <= 256) JM_LAUNCH_PDL(layernorm_bwd_pipe_kernel<2>, grid, tr, smem_reg, STREAM, JM_LN_BWD_ARGS_D, st, static_cast<const int*>(row_map));
+  else if (dim <= 512) JM_LAUNCH_PDL(layernorm_bwd_pipe_kernel<4>, grid, tr, smem_reg, STREAM, JM_LN_BWD_ARGS_D, st, static_cast<const int*>(row_map));
 #ifdef JM_LN_PIPE6
-  else if (dim <= 768) JM_LAUNCH_PDL(layernorm_bwd_pipe_kernel<6>, grid, tr, smem_reg, STREAM, JM_LN_BWD_ARGS_D, 0, static_cast<const int*>(nullptr));
+  else if (dim <= 768) JM_LAUNCH_PDL(layernorm_bwd_pipe_kernel<6>, grid, tr, smem_reg, STREAM, JM_LN_BWD_ARGS_D, st, static_cast<const int*>(nullptr));
 #else
-  else if (dim <= 768) JM_LAUNCH_PDL(layernorm_bwd_reg_kernel<6>, grid, tr, smem_reg, STREAM, JM_LN_BWD_ARGS_D);
+  else if (dim <= 768) JM_LAUNCH_PDL(layernorm_bwd_reg_kernel<6>, grid, tr, smem_reg, STREAM, JM_LN_BWD_ARGS_D, st);
 #endif
   else if (dim <= 1024) {
     JM_CUDA(cudaFuncSetAttribute(layernorm_bwd_reg_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
-    JM_LAUNCH_PDL(layernorm_bwd_reg_kernel<8>, grid, tr, smem_reg, STREAM, JM_LN_BWD_ARGS_D);
+    JM_LAUNCH_PDL(layernorm_bwd_reg_kernel<8>, grid, tr, smem_reg, STREAM, JM_LN_BWD_ARGS_D, st);
   } else if (dim <= 1280) {
     JM_CUDA(cudaFuncSetAttribute(layernorm_bwd_reg_kernel<10>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
-    JM_LAUNCH_PDL(layernorm_bwd_reg_kernel<10>, grid, tr, smem_reg, STREAM, JM_LN_BWD_ARGS_D);
+    JM_LAUNCH_PDL(layernorm_bwd_reg_kernel<10>, grid, tr, smem_reg, STREAM, JM_LN_BWD_ARGS_D, st);
   } else {
     const int g8 = (rows + kLnWarps - 1) / kLnWarps < grid ? (rows + kLnWarps - 1) / kLnWarps : grid;
     grid = g8;
@@ -1477,6 +1496,21 @@ extern "C" int jm_layernorm_bwd_lowp(const jm_bf16* dy, long lddy, const float* 
   return layernorm_bwd_impl(dy, lddy, x, ldx, mean, rstd, gamma, rows, dim, reinterpret_cast<const float*>(dres_bf16),
                             lddres, dres_bf16 != nullptr ? 1 : 0, dx, lddx, dx_bf16, lddxb, 0, 0, dgamma, dbeta, dcol,
                             0, 0, workspace, workspace_bytes, stream);
+}
+
+extern "C" int jm_layernorm_bwd_stream16(const jm_bf16* dy, long lddy, const float* x, long ldx, const float* mean,
+                                         const float* rstd, const float* gamma, int rows, int dim,
+                                         const jm_bf16* dres_bf16, long lddres, float* dx, long lddx, int f32_period,
+                                         int f32_skip, jm_bf16* dx_bf16, long lddxb, int row_period, int row_skip,
+                                         float* dgamma, float* dbeta, float* dcol, int dcol_period, int dcol_skip,
+                                         void* workspace, size_t workspace_bytes, void* stream) {
+  JM_CHECK(dim <= 1280, "jm_layernorm_bwd_stream16: built for dim <= 1280");
+  JM_CHECK(f32_period >= 0 && f32_skip >= 0 && (f32_period == 0 || f32_skip <= f32_period),
+           "jm_layernorm_bwd_stream16: bad f32 row selection");
+  return layernorm_bwd_impl(dy, lddy, x, ldx, mean, rstd, gamma, rows, dim, reinterpret_cast<const float*>(dres_bf16),
+                            lddres, dres_bf16 != nullptr ? 1 : 0, dx, lddx, dx_bf16, lddxb, row_period, row_skip, dgamma,
+                            dbeta, dcol, dcol_period, dcol_skip, workspace, workspace_bytes, stream, nullptr, f32_period,
+                            f32_skip);
 }
 
 extern "C" int jm_layernorm_bwd_rows(const jm_bf16* dy, long lddy, const float* x, long ldx, const int32_t* row_map,

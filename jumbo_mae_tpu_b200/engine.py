@@ -168,6 +168,9 @@ class MAEEngine:
         self.drop_masks = None
         # decoder residual-gradient stream in bf16 alone (LayerNorm backward's dim <= 512 kernel); JM_DEC_LOWP=0: f32
         self.dec_lowp = dd <= 512 and os.environ.get("JM_DEC_LOWP", "1") != "0"
+        # the same for the encoder: bf16 stream for every row, plus an f32 copy of the CLS rows only (the Jumbo branch
+        # accumulates its split-K gradient into them in f32); a learnable wpe reads f32 patch rows -> f32 stream
+        self.enc_lowp = (d <= 1280 and cfg.posemb != "learnable" and os.environ.get("JM_ENC_LOWP", "1") != "0")
 
     # ------------------------------------------------------------------ DropPath (src/modeling.py:157,181-183)
     def set_droppath(self, masks: Optional[torch.Tensor]) -> None:
@@ -433,6 +436,13 @@ class MAEEngine:
             dn = view(self.dn16, Me, d)
             self._bwd_linear(self.enc_n, self.dy16, Me, "decoder_proj", dd, d, dX16=dn)
             dx, dx16 = view(self.dxA, Me, d), view(self.dxA16, Me, d)
+            if self.enc_lowp and not dp_on and not self.ls_enc:
+                ops.layernorm_bwd_stream16(dn, self.xa[cfg.layers], self.meanF, self.rstdF, ps.f("model/norm/scale"), None,
+                                           dx, dx16, ps.grad("model/norm/scale"), ps.grad("model/norm/bias"), self.ln_ws,
+                                           f32_period=Te, f32_skip=J,
+                                           dcol=ps.grad(f"model/layer_{cfg.layers - 1}/ff/w2/bias"), dcol_period=Te,
+                                           dcol_skip=J)
+                return
             ops.layernorm_bwd(dn, self.xa[cfg.layers], self.meanF, self.rstdF, ps.f("model/norm/scale"), None, dx,
                               dx16, ps.grad("model/norm/scale"), ps.grad("model/norm/bias"), self.ln_ws,
                               dcol=None if (dp_on or self.ls_enc) else ps.grad(f"model/layer_{cfg.layers - 1}/ff/w2/bias"),
@@ -505,6 +515,9 @@ class MAEEngine:
         ls = self.ls_enc if jumbo else self.ls_dec
         g_ = (lambda k: ps.f(f"{name}/scale{k}")) if ls else (lambda k: None)
         explicit = dp is not None or ls
+        # encoder blocks: gradient stream in bf16, f32 only on the CLS rows (see enc_lowp); not with DropPath / LayerScale,
+        # whose in-place scaling changes the bf16 copies that would be the residual
+        enc16 = jumbo and self.enc_lowp and not explicit and not any_dp
         dpk = (lambda k: dp[k]) if dp is not None else (lambda k: None)
         if explicit and part != "rest":
             # dY of ff/w2 (patch rows, drop_path2 / scale2) and of the Jumbo w2 (CLS rows, drop_path3 / scale3)
@@ -523,6 +536,10 @@ class MAEEngine:
                 ops.layernorm_bwd_lowp(dn, s.xb, s.mean2, s.rstd2, ps.f(f"{name}/norm2/scale"), dx16, None, dxb16,
                                        ps.grad(f"{name}/norm2/scale"), ps.grad(f"{name}/norm2/bias"), self.ln_ws,
                                        dcol=ps.grad(f"{name}/attn/wo/bias"))
+            elif enc16:
+                ops.layernorm_bwd_stream16(dn, s.xb, s.mean2, s.rstd2, ps.f(f"{name}/norm2/scale"), dx16, None, dxb16,
+                                           ps.grad(f"{name}/norm2/scale"), ps.grad(f"{name}/norm2/bias"), self.ln_ws,
+                                           row_period=period, row_skip=skip, dcol=ps.grad(f"{name}/attn/wo/bias"))
             else:
                 ops.layernorm_bwd(dn, s.xb, s.mean2, s.rstd2, ps.f(f"{name}/norm2/scale"), dx, dxb, dxb16,
                                   ps.grad(f"{name}/norm2/scale"), ps.grad(f"{name}/norm2/bias"), self.ln_ws,
@@ -569,6 +586,11 @@ class MAEEngine:
             ops.layernorm_bwd_lowp(dn, x_in, s.mean1, s.rstd1, ps.f(f"{name}/norm1/scale"), dxb16,
                                    dx if lowp == 2 else None, dx16, ps.grad(f"{name}/norm1/scale"),
                                    ps.grad(f"{name}/norm1/bias"), self.ln_ws, dcol=dcol_below)
+            return
+        if enc16:
+            ops.layernorm_bwd_stream16(dn, x_in, s.mean1, s.rstd1, ps.f(f"{name}/norm1/scale"), dxb16, dx, dx16,
+                                       ps.grad(f"{name}/norm1/scale"), ps.grad(f"{name}/norm1/bias"), self.ln_ws,
+                                       f32_period=T, f32_skip=J, dcol=dcol_below, dcol_period=period, dcol_skip=skip)
             return
         ops.layernorm_bwd(dn, x_in, s.mean1, s.rstd1, ps.f(f"{name}/norm1/scale"), dxb, dx, dx16,
                           ps.grad(f"{name}/norm1/scale"), ps.grad(f"{name}/norm1/bias"), self.ln_ws,

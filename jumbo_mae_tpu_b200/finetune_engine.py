@@ -13,6 +13,7 @@ RNG draws (beta sample, permutation, box, DropPath keep bits) are caller data.
 """
 from __future__ import annotations
 
+import os
 from typing import List, Optional
 
 import torch
@@ -51,6 +52,7 @@ class FinetuneEngine(MAEEngine):
         self.xa: List[torch.Tensor] = [e(Me, d, dt=F32) for _ in range(cfg.layers + 1)]
         self.remat = bool(getattr(cfg, "grad_ckpt", False))
         self.ls_enc, self.ls_dec = bool(getattr(cfg, "layerscale", False)), False
+        self.enc_lowp = (d <= 1280 and cfg.posemb != "learnable" and os.environ.get("JM_ENC_LOWP", "1") != "0")
         self.enc = make_blocks(cfg.layers, Me, d, cfg.heads, B, self.Te, J, True, dev, self.remat)
         self.dec: List[_Block] = []          # no decoder in classification mode (activation_bytes walks both lists)
         L, Jd = cfg.layers, J * d

@@ -234,6 +234,23 @@ def layernorm_bwd_lowp(dy: torch.Tensor, x: torch.Tensor, mean: torch.Tensor, rs
         workspace.numel() * workspace.element_size(), stream_ptr()))
 
 
+def layernorm_bwd_stream16(dy: torch.Tensor, x: torch.Tensor, mean: torch.Tensor, rstd: torch.Tensor,
+                           gamma: torch.Tensor, dres_bf16: Optional[torch.Tensor], dx: Optional[torch.Tensor],
+                           dx_bf16: torch.Tensor, dgamma: torch.Tensor, dbeta: torch.Tensor, workspace: torch.Tensor,
+                           f32_period: int = 0, f32_skip: int = 0, row_period: int = 0, row_skip: int = 0,
+                           dcol: Optional[torch.Tensor] = None, dcol_period: int = 0, dcol_skip: int = 0) -> None:
+    """LayerNorm backward on the bf16 gradient stream (dim <= 1280); f32 dx only for rows r % f32_period < f32_skip."""
+    _chk(dy, BF16, "dy"), _chk(x, F32, "x"), _chk(mean, F32, "mean"), _chk(rstd, F32, "rstd"), _chk(gamma, F32, "gamma")
+    _chk(dres_bf16, BF16, "dres_bf16"), _chk(dx, F32, "dx"), _chk(dx_bf16, BF16, "dx_bf16"), _chk(dcol, F32, "dcol")
+    _chk(dgamma, F32, "dgamma"), _chk(dbeta, F32, "dbeta")
+    rows, dim = x.shape[0], x.shape[-1]
+    check(_lib.load().jm_layernorm_bwd_stream16(
+        ptr(dy), _ld(dy), ptr(x), _ld(x), ptr(mean), ptr(rstd), ptr(gamma), rows, dim, ptr(dres_bf16), _ld(dres_bf16),
+        ptr(dx), _ld(dx), f32_period, f32_skip, ptr(dx_bf16), _ld(dx_bf16), row_period, row_skip, ptr(dgamma),
+        ptr(dbeta), ptr(dcol), dcol_period, dcol_skip, ptr(workspace), workspace.numel() * workspace.element_size(),
+        stream_ptr()))
+
+
 def layernorm_fwd_rows(x: torch.Tensor, row_map: torch.Tensor, gamma: torch.Tensor, beta: torch.Tensor, eps: float,
                        y_bf16: torch.Tensor, mean: torch.Tensor, rstd: torch.Tensor) -> None:
     """y[r] = LayerNorm(x[row_map[r]]): the rows that matter, compact (dec_norm in front of the pixel head)."""

@@ -300,13 +300,51 @@ def test_layernorm_bwd_lowp(ops, rows, D, with_f32):
     assert torch.allclose(dcol.cpu() - 1, want_dx.sum(0), rtol=1e-4, atol=1e-3 * scale)
     assert torch.allclose(dgamma.cpu() - 1, gamma.grad, rtol=1e-4, atol=1e-4 * scale)
     assert torch.allclose(dbeta.cpu() - 1, beta.grad, rtol=1e-4, atol=1e-4 * scale)
-    with pytest.raises(RuntimeError):        # the wide-row kernels do not have the bf16 input
-        ops.layernorm_bwd_lowp(torch.zeros(4, 768, dtype=BF16, device="cuda"), torch.zeros(4, 768, device="cuda"),
+    with pytest.raises(RuntimeError):        # rows wider than 1280 do not have the bf16 input
+        W = 1536
+        ops.layernorm_bwd_lowp(torch.zeros(4, W, dtype=BF16, device="cuda"), torch.zeros(4, W, device="cuda"),
                                torch.zeros(4, device="cuda"), torch.ones(4, device="cuda"),
-                               torch.ones(768, device="cuda"), torch.zeros(4, 768, dtype=BF16, device="cuda"), None,
-                               torch.zeros(4, 768, dtype=BF16, device="cuda"), torch.zeros(768, device="cuda"),
-                               torch.zeros(768, device="cuda"),
-                               torch.empty(ops.layernorm_bwd_workspace(4, 768), dtype=torch.uint8, device="cuda"))
+                               torch.ones(W, device="cuda"), torch.zeros(4, W, dtype=BF16, device="cuda"), None,
+                               torch.zeros(4, W, dtype=BF16, device="cuda"), torch.zeros(W, device="cuda"),
+                               torch.zeros(W, device="cuda"),
+                               torch.empty(ops.layernorm_bwd_workspace(4, W), dtype=torch.uint8, device="cuda"))
+
+
+@pytest.mark.parametrize("rows,D", [(260, 768), (130, 1024), (65, 1280), (260, 256)])
+def test_layernorm_bwd_stream16(ops, rows, D):
+    """jm_layernorm_bwd_stream16 (the encoder's bf16 gradient stream): bf16 residual in, rows r % 13 < 3 skipped
+    (untouched), bf16 dx for every processed row, the f32 copy only for rows r % 7 < 2, column sums over rows r % 5 >= 1."""
+    g = torch.Generator().manual_seed(D + rows)
+    x = (torch.randn(rows, D, generator=g) * 2 + 0.5).requires_grad_(True)
+    gamma = torch.randn(D, generator=g).requires_grad_(True)
+    beta = torch.randn(D, generator=g).requires_grad_(True)
+    dy = torch.randn(rows, D, generator=g).to(BF16)
+    dres = torch.randn(rows, D, generator=g).to(BF16)
+    r = torch.arange(rows)
+    keep = (r % 13) >= 3
+    y = O.layer_norm(x, gamma, beta)
+    (y * dy.float() * keep[:, None]).sum().backward()
+    want_dx = x.grad + dres.float()
+    mean = x.detach().mean(-1)
+    rstd = torch.rsqrt(torch.clamp((x.detach() ** 2).mean(-1) - mean ** 2, min=0) + 1e-6)
+    dx = torch.full((rows, D), 5.0, device="cuda")
+    dxb = torch.full((rows, D), 5.0, dtype=BF16, device="cuda")
+    dgamma, dbeta, dcol = (torch.zeros(D, device="cuda") for _ in range(3))
+    ws = torch.empty(ops.layernorm_bwd_workspace(rows, D), dtype=torch.uint8, device="cuda")
+    ops.layernorm_bwd_stream16(dev(dy), dev(x.detach()), dev(mean), dev(rstd), dev(gamma.detach()), dev(dres), dx, dxb,
+                               dgamma, dbeta, ws, f32_period=7, f32_skip=2, row_period=13, row_skip=3, dcol=dcol,
+                               dcol_period=5, dcol_skip=1)
+    f32_rows = keep & ((r % 7) < 2)
+    got, gotb = dx.cpu(), dxb.float().cpu()
+    assert torch.allclose(got[f32_rows], want_dx[f32_rows], rtol=1e-4, atol=1e-4)
+    assert torch.equal(got[~f32_rows], torch.full_like(got[~f32_rows], 5.0))          # no f32 copy elsewhere
+    assert torch.allclose(gotb[keep], want_dx[keep], rtol=2 ** -7, atol=1e-3)
+    assert torch.equal(gotb[~keep], torch.full_like(gotb[~keep], 5.0))                # skipped rows untouched
+    scale = max(1.0, math.sqrt(rows))
+    sel = keep & ((r % 5) >= 1)
+    assert torch.allclose(dcol.cpu(), want_dx[sel].sum(0), rtol=1e-4, atol=1e-3 * scale)
+    assert torch.allclose(dgamma.cpu(), gamma.grad, rtol=1e-4, atol=1e-4 * scale)
+    assert torch.allclose(dbeta.cpu(), beta.grad, rtol=1e-4, atol=1e-4 * scale)
 
 
 # ------------------------------------------------------------------ token assembly
