@@ -327,3 +327,61 @@ def test_f32_classification_oracle_close_to_f64_golden():
     for path, g in O.tree_leaves(grads):
         s = z["grad_stats/" + "/".join(path)]
         assert abs(g.double().norm().item() - s[1]) <= 1e-4 * s[1] + 1e-7
+
+
+def test_lamb_leaf_trust_ratio_and_zero_norm_rule():
+    """modified_lamb (src/utils.py:124-139): kernel leaves take u * ||p|| / ||u|| with u = adam + wd * p; a zero parameter
+    (or update) norm gives ratio 1; other leaves are a plain Adam step without weight decay."""
+    cfg = O.tiny()
+    g = torch.Generator().manual_seed(0)
+    p, grad = torch.randn(6, 5, generator=g), torch.randn(6, 5, generator=g) * 1e-2
+    z = torch.zeros_like(p)
+    new_p, m, v = O.lamb_leaf(p, grad, z, z, 0, 1e-2, cfg, decay=True)
+    m_hat, v_hat = m / (1 - cfg.adam_b1), v / (1 - cfg.adam_b2)
+    u = m_hat / (torch.sqrt(v_hat) + cfg.adam_eps) + cfg.weight_decay * p
+    want = p - 1e-2 * u * (p.norm() / u.norm())
+    assert torch.allclose(new_p, want, rtol=1e-6, atol=1e-8)
+    assert torch.allclose((new_p - p).norm(), torch.tensor(1e-2) * p.norm(), rtol=1e-5)   # step length = lr * ||p||
+    zero_p, _, _ = O.lamb_leaf(z, grad, z, z, 0, 1e-2, cfg, decay=True)                    # ||p|| = 0 -> ratio 1
+    plain, _, _ = O.adamw_leaf(z, grad, z, z, 0, 1e-2, cfg, decay=True)
+    assert torch.allclose(zero_p, plain)
+    nodecay, _, _ = O.lamb_leaf(p, grad, z, z, 0, 1e-2, cfg, decay=False)
+    adam, _, _ = O.adamw_leaf(p, grad, z, z, 0, 1e-2, cfg, decay=False)
+    assert torch.allclose(nodecay, adam)
+
+
+def test_per_image_masking_is_the_shared_rule_applied_row_by_row():
+    """The per-image extension of random_masking (noise [B, L]): every image gets what the reference's rule
+    (src/utils_mae.py:88-96) gives for its own noise row."""
+    g = torch.Generator().manual_seed(1)
+    B, L, D, keep = 3, 16, 4, 4
+    x = torch.randn(B, L, D, generator=g)
+    noise = np.random.default_rng(2).random((B, L), dtype=np.float32)
+    kept, mask, ids_restore = O.random_masking(x, noise, keep)
+    assert kept.shape == (B, keep, D) and mask.shape == (B, L) and ids_restore.shape == (B, L)
+    for b in range(B):
+        k1, m1, r1 = O.random_masking(x[b:b + 1], noise[b], keep)
+        assert torch.equal(kept[b], k1[0]) and torch.equal(mask[b], m1[0]) and torch.equal(ids_restore[b], r1)
+    # un-shuffling the kept tokens + mask tokens with ids_restore puts every kept token back at its own position
+    full = torch.cat([kept, torch.zeros(B, L - keep, D)], dim=1)
+    restored = O.index_sequence(full, ids_restore)
+    assert torch.equal(restored[mask == 0], x[mask == 0])
+
+
+def test_layerscale_scales_the_branches():
+    """scale1/2/3 multiply the branch outputs (src/modeling.py:165-166,192-201): with all scales 0 a block is the identity
+    on the patch tokens and LayerNorm-3 on the CLS tokens; the parameter tree carries them at 1e-4 (init.constant)."""
+    cfg = O.tiny(layerscale=True, dec_layerscale=True)
+    p = O.init_params(cfg, 0)
+    lay = p["model"]["layer_0"]
+    assert torch.all(lay["scale1"] == 1e-4) and lay["scale3"].shape == (cfg.num_cls_tokens * cfg.dim,)
+    assert torch.all(p["decoder_model"]["dec_layer_0"]["scale2"] == 1e-4)
+    g = torch.Generator().manual_seed(3)
+    x = torch.randn(2, cfg.num_cls_tokens + 5, cfg.dim, generator=g)
+    zeroed = {**lay, "scale1": torch.zeros(cfg.dim), "scale2": torch.zeros(cfg.dim),
+              "scale3": torch.zeros(cfg.num_cls_tokens * cfg.dim)}
+    y = O.jumbo_layer(x, zeroed, p["model"]["jumbo_mlp"], cfg.heads, cfg.num_cls_tokens)
+    J = cfg.num_cls_tokens
+    assert torch.equal(y[:, J:], x[:, J:])
+    c = O.layer_norm(x[:, :J].reshape(2, -1), lay["norm3"]["scale"], lay["norm3"]["bias"])
+    assert torch.allclose(y[:, :J].reshape(2, -1), c)
