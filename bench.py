@@ -492,6 +492,8 @@ def run_finetune(args):
     drop_buf = torch.ones(cfg.layers, 3, micro, device=dev)
     eng.set_droppath(drop_buf)
     eng.capture_graphs(label_smoothing=0.1, mixup=True)
+    if reducer is not None:
+        eng.capture_segment_graphs()
     perm = torch.arange(micro, dtype=torch.int32, device=dev).flip(0).contiguous()
     counter = {"step": 0}
 
@@ -504,9 +506,11 @@ def run_finetune(args):
         for i in range(accum):
             keep = dgen.random((cfg.layers, 3, micro)) >= droppath
             drop_buf.copy_(torch.from_numpy(keep.astype(np.float32) / np.float32(1 - droppath)), non_blocking=True)
-            eng.run_graph(dev_images[i], dev_labels[i], i == 0, perm=perm)
-        if reducer is not None:
-            reducer.all_reduce_grads()
+            if reducer is not None and i == accum - 1:
+                # last micro-step: the gradient all-reduce of each backward segment overlaps the next segment
+                eng.run_graph_overlapped(dev_images[i], dev_labels[i], i == 0, reducer, perm=perm)
+            else:
+                eng.run_graph(dev_images[i], dev_labels[i], i == 0, perm=perm)
         eng.adamw_step(counter["step"], FT.lr_schedule(counter["step"], state), grad_scale=1.0 / (accum * world),
                        lr_decay=0.75)
         counter["step"] += 1

@@ -160,6 +160,7 @@ class FinetuneEngine(MAEEngine):
         self.labels_buf = torch.zeros(B, dtype=torch.int32, device=self.dev)
         self.perm_buf = torch.arange(B, dtype=torch.int32, device=self.dev).flip(0).contiguous() if mixup else None
         kw = dict(label_smoothing=label_smoothing, perm=self.perm_buf, ratio=0.5 if mixup else 1.0)
+        self._graph_kw = kw
         side = torch.cuda.Stream(device=self.dev)
         side.wait_stream(torch.cuda.current_stream())
         with torch.cuda.stream(side):                  # eager warm-up: one-time function attributes, module load
@@ -193,7 +194,43 @@ class FinetuneEngine(MAEEngine):
         return self.loss
 
     def capture_segment_graphs(self) -> None:
-        """The classification step all-reduces its gradients after the last micro-step (finetuning.training_step,
-        bench.py --workload finetune): its backward segments exist (segment_grad_ranges) but are not captured one by
-        one -- the per-segment overlap of the pre-training step is not wired into this engine."""
-        raise NotImplementedError("per-segment CUDA graphs are not wired into the classification engine")
+        """Graphs for a data-parallel rank's LAST micro-step of an optimizer step: forward + head / final-norm backward,
+        then one graph per encoder segment (the pre-training engine's plan), so that the gradient all-reduce of a
+        segment runs while the next one computes."""
+        if not hasattr(self, "graphs"):
+            self.capture_graphs()
+        kw = self._graph_kw
+        self.seg_graphs = {}
+        for zero in (True, False):
+            graphs = []
+            for k in range(self.num_bwd_segments()):
+                g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g):
+                    if k == 0:
+                        self.forward(self.images_buf, self.labels_buf, **kw)
+                    self.backward_segment(k, zero_grads=zero)
+                graphs.append(g)
+            self.seg_graphs[zero] = graphs
+        ops.zero_(self.ps.g)
+
+    def run_graph_overlapped(self, images: torch.Tensor, labels: torch.Tensor, zero_grads: bool, reducer,
+                             perm: Optional[torch.Tensor] = None, after_reduce=None) -> torch.Tensor:
+        """Last micro-step of a data-parallel optimizer step: every backward segment is followed by the all-reduce of
+        the gradients it finalised, on the reducer's stream, overlapping the next segment."""
+        if not hasattr(self, "seg_graphs"):
+            self.capture_segment_graphs()
+        self.images_buf.copy_(images, non_blocking=True)
+        self.labels_buf.copy_(labels, non_blocking=True)
+        if perm is not None and self.perm_buf is not None:
+            self.perm_buf.copy_(perm, non_blocking=True)
+        for k, g in enumerate(self.seg_graphs[bool(zero_grads)]):
+            g.replay()
+            ev = torch.cuda.Event()
+            ev.record()
+            ranges = self.segment_grad_ranges(k)
+            reducer.all_reduce_ranges(ranges, after_event=ev)
+            if after_reduce is not None and reducer.stream is not None:
+                with torch.cuda.stream(reducer.stream):
+                    after_reduce(ranges)
+        reducer.join()
+        return self.loss

@@ -93,9 +93,29 @@ def main():
         if not (r_ <= 3e-2 and cos >= 0.999):
             bad.append(("/".join(path), r_, cos))
     assert not bad, bad
+    # ---- 4: classification engine, overlapped per-segment all-reduce == one all-reduce after the backward pass
+    from jumbo_mae_tpu_b200.finetune_engine import FinetuneEngine
+    ccfg = MAEConfig(layers=4, dim=128, heads=2, patch_size=16, image_size=64, labels=16)
+    cstate = O.init_params(O.MAEConfig(layers=4, dim=128, heads=2, patch_size=16, image_size=64, labels=16), seed=0,
+                           randomize_all=True)
+    cstore = ParamStore(ccfg)
+    cstore.load_tree(cstate)
+    ceng = FinetuneEngine(ccfg, cstore, 8)
+    ceng.capture_graphs(label_smoothing=0.1, mixup=False)
+    ceng.capture_segment_graphs()
+    cred = parallel.GradReducer(cstore)
+    labels = torch.randint(0, 16, (8,), generator=g).to(torch.int32).cuda()
+    ceng.run_graph(batches[0].cuda(), labels, True)
+    cred.all_reduce_grads()
+    torch.cuda.synchronize()
+    g_plain = cstore.g.clone()
+    ceng.run_graph_overlapped(batches[0].cuda(), labels, True, cred)
+    torch.cuda.synchronize()
+    crel = ((cstore.g - g_plain).norm() / g_plain.norm()).item()
+    assert crel <= 2e-4, f"classification engine, overlapped vs plain all-reduce: rel-L2 {crel}"   # (two passes: f32 atomics order)
     dist.barrier()
     if rank == 0:
-        print(f"dp_worker ok: world {world}, overlap vs plain rel {rel:.2e}")
+        print(f"dp_worker ok: world {world}, overlap vs plain rel {rel:.2e}, classification {crel:.2e}")
     dist.destroy_process_group()
 
 
