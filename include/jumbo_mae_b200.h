@@ -85,6 +85,11 @@ int jm_patchify(const uint8_t* images, int batch, int image_size, int patch_size
 int jm_patchify_mix(const uint8_t* images, int batch, int image_size, int patch_size, const int32_t* ids, int n_sel,
                     int rows_per_image, int row_off, jm_bf16* out, long ldo, const int32_t* perm, int mode,
                     float ratio, const uint8_t* xmask, const uint8_t* ymask, void* stream);
+/* The same with the Mixup ratio read from device memory (one f32), so that a captured CUDA graph can be replayed with
+ * a new draw every step (the reference draws a ratio per step, src/utils.py:92-111). */
+int jm_patchify_mix_dev(const uint8_t* images, int batch, int image_size, int patch_size, const int32_t* ids, int n_sel,
+                        int rows_per_image, int row_off, jm_bf16* out, long ldo, const int32_t* perm, int mode,
+                        const float* ratio_dev, const uint8_t* xmask, const uint8_t* ymask, void* stream);
 
 /* extract_patches on the normalised image as f32 (reference signature; tests only). */
 int jm_extract_patches(const uint8_t* images, int batch, int image_size, int patch_size, float* out, void* stream);
@@ -388,6 +393,10 @@ int jm_add_bias_cast(const float* src, long lds, int rows, int cols, const float
 int jm_softmax_ce(const float* logits, const float* labels_soft, const int* labels_idx, const int* perm,
                   float ratio, double label_smoothing, int B, int C, float grad_scale, float* loss_rows,
                   float* acc1, float* acc5, float* metrics, float* dlogits, void* stream);
+/* jm_softmax_ce with the label ratio of Mixup / CutMix read from device memory (see jm_patchify_mix_dev). */
+int jm_softmax_ce_dev(const float* logits, const float* labels_soft, const int* labels_idx, const int* perm,
+                      const float* ratio_dev, double label_smoothing, int B, int C, float grad_scale, float* loss_rows,
+                      float* acc1, float* acc5, float* metrics, float* dlogits, void* stream);
 
 #ifdef __cplusplus
 }

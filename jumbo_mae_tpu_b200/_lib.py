@@ -21,7 +21,7 @@ EXPORTS = [
     "jm_layernorm_bwd_workspace", "jm_layernorm_bwd", "jm_gemm", "jm_attention_fwd", "jm_attention_bwd",
     "jm_fill_cls", "jm_unshuffle_fwd", "jm_unshuffle_bwd", "jm_colsum", "jm_adamw", "jm_cast_bf16",
     "jm_add_bias_cast", "jm_clip_by_global_norm", "jm_softmax_ce", "jm_patchify_mix", "jm_patch_mse_loss", "jm_scale_rows_bf16", "jm_rrc_flip_workspace", "jm_rrc_flip", "jm_posemb_grad", "jm_layernorm_bwd_lowp",
-    "jm_layernorm_fwd_rows", "jm_layernorm_bwd_rows", "jm_masked_targets", "jm_row_loss_workspace", "jm_row_loss_finalize", "jm_lamb_workspace", "jm_lamb", "jm_zero", "jm_layernorm_bwd_stream16", "jm_mask_sort_batched", "jm_patchify_pi", "jm_masked_targets_pi",
+    "jm_layernorm_fwd_rows", "jm_layernorm_bwd_rows", "jm_masked_targets", "jm_row_loss_workspace", "jm_row_loss_finalize", "jm_lamb_workspace", "jm_lamb", "jm_zero", "jm_patchify_mix_dev", "jm_softmax_ce_dev", "jm_layernorm_bwd_stream16", "jm_mask_sort_batched", "jm_patchify_pi", "jm_masked_targets_pi",
     "jm_unshuffle_fwd_pi", "jm_unshuffle_bwd_pi", "jm_posemb_grad_pi", "jm_scale_bf16", "jm_layerscale_grad", "jm_layerscale_cls_grad",
 ]
 
@@ -132,6 +132,8 @@ def load() -> ctypes.CDLL:
         "jm_clip_by_global_norm": [P, c_long, c_float, c_float, P, P],
         "jm_patchify_mix": [P, c_int, c_int, c_int, P, c_int, c_int, c_int, P, c_long, P, c_int, c_float, P, P, P],
         "jm_softmax_ce": [P, P, P, P, c_float, ctypes.c_double, c_int, c_int, c_float, P, P, P, P, P, P],
+        "jm_softmax_ce_dev": [P, P, P, P, P, ctypes.c_double, c_int, c_int, c_float, P, P, P, P, P, P],
+        "jm_patchify_mix_dev": [P, c_int, c_int, c_int, P, c_int, c_int, c_int, P, c_long, P, c_int, P, P, P, P],
     }
     for name, argtypes in sig.items():
         fn = getattr(lib, name)

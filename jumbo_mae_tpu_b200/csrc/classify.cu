@@ -22,6 +22,7 @@ struct CeArgs {
   const int* labels_idx;
   const int* perm;
   float ratio, one_minus_alpha, alpha_over_c, grad_scale, inv_b;
+  const float* ratio_dev;  // optional: the label ratio read from device memory (a captured graph replays with new draws)
   int B, C;
   float *loss_rows, *acc1, *acc5, *metrics, *dlogits;
 };
@@ -64,13 +65,14 @@ __global__ void __launch_bounds__(kCeThreads) softmax_ce_kernel(const CeArgs a) 
   float* lab = ce_smem + a.C;
   const int b = blockIdx.x, C = a.C;
   const int other = a.perm ? a.perm[b] : b;
-  const float one_minus_r = __fsub_rn(1.f, a.ratio);
+  const float ratio = a.ratio_dev ? *a.ratio_dev : a.ratio;
+  const float one_minus_r = __fsub_rn(1.f, ratio);
 
   float mx = -INFINITY, lmx = -INFINITY, lsum = 0.f;
   for (int c = threadIdx.x; c < C; c += kCeThreads) {
     const float x = a.logits[static_cast<long>(b) * C + c];
     float l = ce_smoothed(a, b, c);
-    if (a.perm) l = __fadd_rn(__fmul_rn(a.ratio, l), __fmul_rn(one_minus_r, ce_smoothed(a, other, c)));
+    if (a.perm) l = __fadd_rn(__fmul_rn(ratio, l), __fmul_rn(one_minus_r, ce_smoothed(a, other, c)));
     lg[c] = x, lab[c] = l;
     mx = fmaxf(mx, x), lmx = fmaxf(lmx, l), lsum += l;
   }
@@ -143,9 +145,9 @@ __global__ void __launch_bounds__(kCeThreads) softmax_ce_kernel(const CeArgs a) 
 }  // namespace
 }  // namespace jm
 
-extern "C" int jm_softmax_ce(const float* logits, const float* labels_soft, const int* labels_idx, const int* perm,
-                             float ratio, double label_smoothing, int B, int C, float grad_scale, float* loss_rows,
-                             float* acc1, float* acc5, float* metrics, float* dlogits, void* stream) {
+static int softmax_ce_impl(const float* logits, const float* labels_soft, const int* labels_idx, const int* perm,
+                           float ratio, const float* ratio_dev, double label_smoothing, int B, int C, float grad_scale,
+                           float* loss_rows, float* acc1, float* acc5, float* metrics, float* dlogits, void* stream) {
   using namespace jm;
   JM_CHECK(logits, "jm_softmax_ce: logits is null");
   JM_CHECK((labels_soft != nullptr) != (labels_idx != nullptr),
@@ -156,7 +158,7 @@ extern "C" int jm_softmax_ce(const float* logits, const float* labels_soft, cons
   if (B == 0) return 0;
   CeArgs a;
   a.logits = logits, a.labels_soft = labels_soft, a.labels_idx = labels_idx, a.perm = perm;
-  a.ratio = ratio;
+  a.ratio = ratio, a.ratio_dev = ratio_dev;
   a.one_minus_alpha = static_cast<float>(1.0 - label_smoothing);  // Python-float arithmetic, then f32
   a.alpha_over_c = static_cast<float>(label_smoothing / C);
   a.grad_scale = grad_scale, a.inv_b = 1.f / static_cast<float>(B);
@@ -170,4 +172,20 @@ extern "C" int jm_softmax_ce(const float* logits, const float* labels_soft, cons
   softmax_ce_kernel<<<B, kCeThreads, smem, s>>>(a);
   JM_AFTER_LAUNCH();
   return 0;
+}
+
+extern "C" int jm_softmax_ce(const float* logits, const float* labels_soft, const int* labels_idx, const int* perm,
+                             float ratio, double label_smoothing, int B, int C, float grad_scale, float* loss_rows,
+                             float* acc1, float* acc5, float* metrics, float* dlogits, void* stream) {
+  return softmax_ce_impl(logits, labels_soft, labels_idx, perm, ratio, nullptr, label_smoothing, B, C, grad_scale,
+                         loss_rows, acc1, acc5, metrics, dlogits, stream);
+}
+
+extern "C" int jm_softmax_ce_dev(const float* logits, const float* labels_soft, const int* labels_idx, const int* perm,
+                                 const float* ratio_dev, double label_smoothing, int B, int C, float grad_scale,
+                                 float* loss_rows, float* acc1, float* acc5, float* metrics, float* dlogits,
+                                 void* stream) {
+  JM_CHECK(ratio_dev != nullptr, "jm_softmax_ce_dev: ratio_dev is null");
+  return softmax_ce_impl(logits, labels_soft, labels_idx, perm, 1.f, ratio_dev, label_smoothing, B, C, grad_scale,
+                         loss_rows, acc1, acc5, metrics, dlogits, stream);
 }

@@ -214,8 +214,9 @@ __global__ void __launch_bounds__(256) row_loss_final_kernel(const float* __rest
 __global__ void __launch_bounds__(256)
 patchify_mix_kernel(const uint8_t* __restrict__ images, int S, int p, const int* __restrict__ ids, int n_sel,
                     int rows_per_image, int row_off, __nv_bfloat16* __restrict__ out, long ldo, int batch,
-                    const int* __restrict__ perm, int mode, float ratio, const uint8_t* __restrict__ xmask,
-                    const uint8_t* __restrict__ ymask) {
+                    const int* __restrict__ perm, int mode, float ratio_arg, const uint8_t* __restrict__ xmask,
+                    const uint8_t* __restrict__ ymask, const float* __restrict__ ratio_dev) {
+  const float ratio = ratio_dev ? *ratio_dev : ratio_arg;  // device scalar: a captured graph replays with new draws
   __shared__ __align__(16) uint8_t spix_all[8][2][2048];
   __shared__ float lut[768];
   fill_norm_lut(lut);
@@ -1191,9 +1192,10 @@ extern "C" int jm_patchify_pi(const uint8_t* images, int batch, int image_size, 
   return 0;
 }
 
-extern "C" int jm_patchify_mix(const uint8_t* images, int batch, int image_size, int patch_size, const int32_t* ids,
-                               int n_sel, int rows_per_image, int row_off, jm_bf16* out, long ldo, const int32_t* perm,
-                               int mode, float ratio, const uint8_t* xmask, const uint8_t* ymask, void* stream) {
+static int patchify_mix_impl(const uint8_t* images, int batch, int image_size, int patch_size, const int32_t* ids,
+                             int n_sel, int rows_per_image, int row_off, jm_bf16* out, long ldo, const int32_t* perm,
+                             int mode, float ratio, const float* ratio_dev, const uint8_t* xmask, const uint8_t* ymask,
+                             void* stream) {
   JM_CHECK(mode == 1 || mode == 2, "jm_patchify_mix: mode must be 1 (mixup) or 2 (cutmix); use jm_patchify without mixing");
   JM_CHECK(images && out && perm, "jm_patchify_mix: null argument");
   JM_CHECK(mode == 1 || (xmask && ymask), "jm_patchify_mix: cutmix needs xmask [image_size] and ymask [image_size]");
@@ -1206,9 +1208,25 @@ extern "C" int jm_patchify_mix(const uint8_t* images, int batch, int image_size,
   const long want = (static_cast<long>(batch) * rows_per_image + 7) / 8, cap = static_cast<long>(sm_count()) * 16;
   patchify_mix_kernel<<<static_cast<int>(want < cap ? want : cap), 256, 0, STREAM>>>(
       images, image_size, patch_size, ids, n_sel, rows_per_image, row_off, reinterpret_cast<__nv_bfloat16*>(out), ldo,
-      batch, perm, mode, ratio, xmask, ymask);
+      batch, perm, mode, ratio, xmask, ymask, ratio_dev);
   JM_AFTER_LAUNCH();
   return 0;
+}
+
+extern "C" int jm_patchify_mix(const uint8_t* images, int batch, int image_size, int patch_size, const int32_t* ids,
+                               int n_sel, int rows_per_image, int row_off, jm_bf16* out, long ldo, const int32_t* perm,
+                               int mode, float ratio, const uint8_t* xmask, const uint8_t* ymask, void* stream) {
+  return patchify_mix_impl(images, batch, image_size, patch_size, ids, n_sel, rows_per_image, row_off, out, ldo, perm,
+                           mode, ratio, nullptr, xmask, ymask, stream);
+}
+
+extern "C" int jm_patchify_mix_dev(const uint8_t* images, int batch, int image_size, int patch_size, const int32_t* ids,
+                                   int n_sel, int rows_per_image, int row_off, jm_bf16* out, long ldo,
+                                   const int32_t* perm, int mode, const float* ratio_dev, const uint8_t* xmask,
+                                   const uint8_t* ymask, void* stream) {
+  JM_CHECK(ratio_dev != nullptr, "jm_patchify_mix_dev: ratio_dev is null");
+  return patchify_mix_impl(images, batch, image_size, patch_size, ids, n_sel, rows_per_image, row_off, out, ldo, perm,
+                           mode, 1.f, ratio_dev, xmask, ymask, stream);
 }
 
 extern "C" int jm_extract_patches(const uint8_t* images, int batch, int image_size, int patch_size, float* out,

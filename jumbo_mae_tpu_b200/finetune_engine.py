@@ -84,13 +84,15 @@ class FinetuneEngine(MAEEngine):
     def forward(self, images: torch.Tensor, labels: torch.Tensor, *, label_smoothing: float = 0.0,
                 perm: Optional[torch.Tensor] = None, ratio: float = 1.0, label_ratio: Optional[float] = None,
                 xmask: Optional[torch.Tensor] = None, ymask: Optional[torch.Tensor] = None,
-                want_grad: bool = True, grad_scale: float = 1.0) -> torch.Tensor:
+                want_grad: bool = True, grad_scale: float = 1.0,
+                ratio_dev: Optional[torch.Tensor] = None) -> torch.Tensor:
         """images uint8 [B,3,H,W], labels int32 [B] or f32 [B, C] (device) -> mean loss (device tensor [1]);
         ``metrics`` = (loss, acc1, acc5) batch means, ``logits`` f32 [B, C].
 
         Training (det=False, src/finetuning.py:93-95): ``label_smoothing`` and, with ``perm``, Mixup
         (``ratio`` = the beta sample) or CutMix (``xmask`` / ``ymask`` = the box, ``label_ratio`` = the mean of the
-        image mask).  Evaluation: defaults."""
+        image mask).  ``ratio_dev`` (f32 [2] on the device: pixel ratio, label ratio) replaces the two host scalars, so
+        that a captured graph can be replayed with new draws.  Evaluation: defaults."""
         cfg, ps, B = self.cfg, self.ps, self.B
         J, N, d, P, C, Te, Me = cfg.num_cls_tokens, cfg.num_patches, cfg.dim, cfg.patch_dim, cfg.labels, self.Te, self.Me
         if tuple(images.shape) != (B, 3, cfg.image_size, cfg.image_size):
@@ -101,7 +103,7 @@ class FinetuneEngine(MAEEngine):
             ops.patchify(images, cfg.patch_size, None, N, Te, J, self.patches)
         else:
             ops.patchify_mix(images, cfg.patch_size, None, N, Te, J, self.patches, perm, ratio=ratio, xmask=xmask,
-                             ymask=ymask)
+                             ymask=ymask, ratio_dev=None if ratio_dev is None else ratio_dev[0:1])
         x0 = self.xa[0]
         ops.fill_cls(x0, B, Te, J, d, ps.f("model/cls_tokens"))
         self._fwd_linear(self.patches, Me, "model/embed/wte", d, P, lda=self.Pp, out_f32=x0, pe=self._wpe_table(),
@@ -119,10 +121,16 @@ class FinetuneEngine(MAEEngine):
         idx = labels if labels.dim() == 1 else None
         ops._chk(soft, F32, "labels"), ops._chk(idx, torch.int32, "labels"), ops._chk(perm, torch.int32, "perm")
         lr = ratio if label_ratio is None else label_ratio
-        _lib.check(_lib.load().jm_softmax_ce(
-            _lib.ptr(self.logits), _lib.ptr(soft), _lib.ptr(idx), _lib.ptr(perm), lr, float(label_smoothing), B, C,
-            grad_scale / B, _lib.ptr(self.loss_rows), _lib.ptr(self.acc1), _lib.ptr(self.acc5), _lib.ptr(self.metrics),
-            _lib.ptr(self.dlogits) if want_grad else None, _lib.stream_ptr()))
+        lib = _lib.load()
+        common = (float(label_smoothing), B, C, grad_scale / B, _lib.ptr(self.loss_rows), _lib.ptr(self.acc1),
+                  _lib.ptr(self.acc5), _lib.ptr(self.metrics), _lib.ptr(self.dlogits) if want_grad else None,
+                  _lib.stream_ptr())
+        if ratio_dev is not None and perm is not None:
+            _lib.check(lib.jm_softmax_ce_dev(_lib.ptr(self.logits), _lib.ptr(soft), _lib.ptr(idx), _lib.ptr(perm),
+                                             _lib.ptr(ratio_dev[1:2]), *common))
+        else:
+            _lib.check(lib.jm_softmax_ce(_lib.ptr(self.logits), _lib.ptr(soft), _lib.ptr(idx), _lib.ptr(perm), lr,
+                                         *common))
         return self.loss
 
     # ------------------------------------------------------------------ backward
@@ -150,17 +158,35 @@ class FinetuneEngine(MAEEngine):
                           dcol_period=Te, dcol_skip=J)
 
     # ------------------------------------------------------------------ CUDA graphs
-    def capture_graphs(self, label_smoothing: float = 0.0, mixup: bool = False) -> None:
-        """Records forward + backward of one micro-batch into two CUDA graphs (gradients zeroed first / accumulated)
-        over static input buffers: images, class indices and, with ``mixup``, the batch permutation; the Mixup ratio
-        is baked into the graph's kernel arguments, so a training loop that draws a new ratio per step runs eagerly
-        or re-captures (CutMix likewise)."""
+    def _ensure_static_inputs(self) -> None:
+        if hasattr(self, "images_buf"):
+            return
         cfg, B = self.cfg, self.B
         self.images_buf = torch.empty(B, 3, cfg.image_size, cfg.image_size, dtype=torch.uint8, device=self.dev)
         self.labels_buf = torch.zeros(B, dtype=torch.int32, device=self.dev)
-        self.perm_buf = torch.arange(B, dtype=torch.int32, device=self.dev).flip(0).contiguous() if mixup else None
-        kw = dict(label_smoothing=label_smoothing, perm=self.perm_buf, ratio=0.5 if mixup else 1.0)
-        self._graph_kw = kw
+        self.perm_buf = torch.arange(B, dtype=torch.int32, device=self.dev).flip(0).contiguous()
+        self.ratio_buf = torch.full((2,), 0.5, dtype=F32, device=self.dev)      # pixel ratio, label ratio
+        self.xmask_buf = torch.zeros(cfg.image_size, dtype=torch.uint8, device=self.dev)
+        self.ymask_buf = torch.zeros(cfg.image_size, dtype=torch.uint8, device=self.dev)
+        self.graphs_by_mode, self.seg_graphs_by_mode, self._mode_kw = {}, {}, {}
+
+    def capture_graphs(self, label_smoothing: float = 0.0, mixup: bool = False, mode: Optional[str] = None) -> None:
+        """Records forward + backward of one micro-batch into two CUDA graphs (gradients zeroed first / accumulated)
+        over static input buffers: images, class indices and, by ``mode`` ("plain", "mixup", "cutmix"), the batch
+        permutation, the two Mixup / CutMix ratios (device scalars) and the CutMix box vectors -- everything a step
+        draws is data in device memory, so the same graph replays with new draws (src/utils.py:92-111).  DropPath is
+        captured as set by ``set_droppath`` (a persistent device buffer, or off).  Call while no gradient is being
+        accumulated: the warm-up pass overwrites the gradient buffer."""
+        mode = mode or ("mixup" if mixup else "plain")
+        self._ensure_static_inputs()
+        kw = dict(label_smoothing=label_smoothing)
+        if mode != "plain":
+            kw.update(perm=self.perm_buf, ratio_dev=self.ratio_buf)
+        if mode == "cutmix":
+            kw.update(xmask=self.xmask_buf, ymask=self.ymask_buf)
+        self._mode_kw[mode] = kw
+        self._graph_kw, self._default_mode = kw, mode
+        self._graph_droppath = self.drop_masks is not None      # the graphs bake in whether DropPath scaling is on
         side = torch.cuda.Stream(device=self.dev)
         side.wait_stream(torch.cuda.current_stream())
         with torch.cuda.stream(side):                  # eager warm-up: one-time function attributes, module load
@@ -169,7 +195,7 @@ class FinetuneEngine(MAEEngine):
             self.backward(zero_grads=True)
         torch.cuda.current_stream().wait_stream(side)
         torch.cuda.synchronize()
-        self.graphs = {}
+        graphs = {}
         lib = _lib.load()
         for zero in (True, False):
             g = torch.cuda.CUDAGraph()
@@ -178,29 +204,43 @@ class FinetuneEngine(MAEEngine):
                 self.forward(self.images_buf, self.labels_buf, **kw)
                 self.backward(zero_grads=zero)
             self.graph_launches = lib.jm_launch_count() - l0
-            self.graphs[zero] = g
+            graphs[zero] = g
+        self.graphs_by_mode[mode] = graphs
+        self.graphs = graphs
         ops.zero_(self.ps.g)
 
-    def run_graph(self, images: torch.Tensor, labels: torch.Tensor, zero_grads: bool,
-                  perm: Optional[torch.Tensor] = None) -> torch.Tensor:
-        """forward + backward through the captured graph; images may be a pinned host tensor."""
-        if not hasattr(self, "graphs"):
-            self.capture_graphs()
+    def _stage_inputs(self, images, labels, perm, ratios, xmask, ymask) -> None:
         self.images_buf.copy_(images, non_blocking=True)
         self.labels_buf.copy_(labels, non_blocking=True)
-        if perm is not None and self.perm_buf is not None:
+        if perm is not None:
             self.perm_buf.copy_(perm, non_blocking=True)
-        self.graphs[bool(zero_grads)].replay()
+        if ratios is not None:
+            self.ratio_buf.copy_(torch.tensor([float(ratios[0]), float(ratios[1])], dtype=F32), non_blocking=False)
+        if xmask is not None:
+            self.xmask_buf.copy_(xmask, non_blocking=True)
+            self.ymask_buf.copy_(ymask, non_blocking=True)
+
+    def run_graph(self, images: torch.Tensor, labels: torch.Tensor, zero_grads: bool,
+                  perm: Optional[torch.Tensor] = None, mode: Optional[str] = None, ratios=None,
+                  xmask: Optional[torch.Tensor] = None, ymask: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """forward + backward through the captured graph of ``mode``; images may be a pinned host tensor; ``ratios`` =
+        (pixel ratio, label ratio) of this step's Mixup / CutMix draw."""
+        if not hasattr(self, "graphs"):
+            self.capture_graphs()
+        mode = mode or self._default_mode
+        self._stage_inputs(images, labels, perm, ratios, xmask, ymask)
+        self.graphs_by_mode[mode][bool(zero_grads)].replay()
         return self.loss
 
-    def capture_segment_graphs(self) -> None:
+    def capture_segment_graphs(self, mode: Optional[str] = None) -> None:
         """Graphs for a data-parallel rank's LAST micro-step of an optimizer step: forward + head / final-norm backward,
         then one graph per encoder segment (the pre-training engine's plan), so that the gradient all-reduce of a
         segment runs while the next one computes."""
         if not hasattr(self, "graphs"):
             self.capture_graphs()
-        kw = self._graph_kw
-        self.seg_graphs = {}
+        mode = mode or self._default_mode
+        kw = self._mode_kw[mode]
+        out = {}
         for zero in (True, False):
             graphs = []
             for k in range(self.num_bwd_segments()):
@@ -210,20 +250,23 @@ class FinetuneEngine(MAEEngine):
                         self.forward(self.images_buf, self.labels_buf, **kw)
                     self.backward_segment(k, zero_grads=zero)
                 graphs.append(g)
-            self.seg_graphs[zero] = graphs
+            out[zero] = graphs
+        self.seg_graphs_by_mode[mode] = out
+        self.seg_graphs = out
         ops.zero_(self.ps.g)
 
     def run_graph_overlapped(self, images: torch.Tensor, labels: torch.Tensor, zero_grads: bool, reducer,
-                             perm: Optional[torch.Tensor] = None, after_reduce=None) -> torch.Tensor:
+                             perm: Optional[torch.Tensor] = None, after_reduce=None, mode: Optional[str] = None,
+                             ratios=None, xmask: Optional[torch.Tensor] = None,
+                             ymask: Optional[torch.Tensor] = None) -> torch.Tensor:
         """Last micro-step of a data-parallel optimizer step: every backward segment is followed by the all-reduce of
         the gradients it finalised, on the reducer's stream, overlapping the next segment."""
-        if not hasattr(self, "seg_graphs"):
-            self.capture_segment_graphs()
-        self.images_buf.copy_(images, non_blocking=True)
-        self.labels_buf.copy_(labels, non_blocking=True)
-        if perm is not None and self.perm_buf is not None:
-            self.perm_buf.copy_(perm, non_blocking=True)
-        for k, g in enumerate(self.seg_graphs[bool(zero_grads)]):
+        mode = mode or getattr(self, "_default_mode", None)
+        if mode is None or mode not in getattr(self, "seg_graphs_by_mode", {}):
+            self.capture_segment_graphs(mode)
+            mode = mode or self._default_mode
+        self._stage_inputs(images, labels, perm, ratios, xmask, ymask)
+        for k, g in enumerate(self.seg_graphs_by_mode[mode][bool(zero_grads)]):
             g.replay()
             ev = torch.cuda.Event()
             ev.record()

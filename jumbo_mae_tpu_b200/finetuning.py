@@ -37,6 +37,7 @@ from .config import MAEConfig
 from .finetune_engine import FinetuneEngine
 from .parallel import GradReducer, process_count, process_index
 from .params import ParamStore
+from .pretraining import USE_CUDA_GRAPH
 
 
 @dataclass
@@ -232,15 +233,39 @@ def training_step(state: TrainState, batch, mix: Optional[MixDraw] = None, drop_
     if world > 1 and getattr(state, "reducer", None) is None:
         state.reducer = GradReducer(state.store)
     _set_droppath(state, eng, drop_keep if drop_keep is not None else state.draw_drop_keep(B))
-    eng.forward(images, labels, label_smoothing=state.label_smoothing, **kw)
-    eng.backward(zero_grads=(state.micro_step == 0))
+    mode = "plain" if mix is None else ("cutmix" if mix.box is not None else "mixup")
+    first = state.micro_step == 0
+    reduced = False
+    # Graph replay on a single rank only.  With several ranks the kind of step (captured graph or eager fallback) could
+    # differ from rank to rank -- the Mixup / CutMix draws are per rank -- and every rank has to issue the same sequence
+    # of collectives, so the data-parallel step keeps one code path: eager launches, one all-reduce after the backward.
+    use_graph = USE_CUDA_GRAPH and labels.dim() == 1 and world == 1
+    if use_graph and not getattr(eng, "graphs_by_mode", None):
+        if first:
+            # every kind of step this state can draw is captured once, before any gradient is being accumulated (the
+            # capture's warm-up pass overwrites the gradient buffer); the draws themselves -- permutation, ratios, box
+            # vectors, DropPath factors -- are data in device buffers the graphs read
+            modes = (["mixup"] if state.mixup > 0 else []) + (["cutmix"] if state.cutmix > 0 else [])
+            for m in dict.fromkeys(modes + [mode]):
+                eng.capture_graphs(label_smoothing=state.label_smoothing, mode=m)
+        else:
+            use_graph = False
+    if use_graph and (mode not in eng.graphs_by_mode or eng._graph_droppath != (eng.drop_masks is not None)):
+        use_graph = False                                          # (a kind of step that was not captured: eager)
+    if use_graph:
+        gkw = dict(mode=mode, perm=kw.get("perm"), xmask=kw.get("xmask"), ymask=kw.get("ymask"),
+                   ratios=None if mix is None else (kw["ratio"], kw.get("label_ratio", kw["ratio"])))
+        eng.run_graph(images, labels, first, **gkw)
+    else:
+        eng.forward(images, labels, label_smoothing=state.label_smoothing, **kw)
+        eng.backward(zero_grads=first)
     metrics = eng.metrics.clone()
     if world > 1:                                                  # lax.pmean(metrics) (src/finetuning.py:131)
         state.reducer.mean_scalar(metrics)
     state.micro_step += 1
     lr = lr_schedule(state.step, state)
     if state.micro_step == accum:
-        if world > 1:                                              # lax.pmean(grads) (:138,144); 1/world below
+        if world > 1 and not reduced:                              # lax.pmean(grads) (:138,144); 1/world below
             state.reducer.all_reduce_grads()
         eng.layerscale_finalize()
         if state.clip_grad > 0:

@@ -82,7 +82,8 @@ def patchify(images: torch.Tensor, patch_size: int, ids: Optional[torch.Tensor],
 
 def patchify_mix(images: torch.Tensor, patch_size: int, ids: Optional[torch.Tensor], n_sel: int, rows_per_image: int,
                  row_off: int, out: torch.Tensor, perm: torch.Tensor, *, ratio: float = 1.0,
-                 xmask: Optional[torch.Tensor] = None, ymask: Optional[torch.Tensor] = None) -> torch.Tensor:
+                 xmask: Optional[torch.Tensor] = None, ymask: Optional[torch.Tensor] = None,
+                 ratio_dev: Optional[torch.Tensor] = None) -> torch.Tensor:
     """patchify with Mixup (``xmask is None``: ratio * a + (1 - ratio) * a[perm]) or CutMix (uint8 ``xmask`` /
     ``ymask`` [image_size]: a[perm] inside the box) on the normalised pixels (jm_patchify_mix; src/utils.py:67-90)."""
     _chk(images, U8, "images"), _chk(ids, I32, "ids"), _chk(out, BF16, "out"), _chk(perm, I32, "perm")
@@ -93,6 +94,12 @@ def patchify_mix(images: torch.Tensor, patch_size: int, ids: Optional[torch.Tens
     _expect((xmask is None) == (ymask is None), "give both xmask and ymask (cutmix) or neither (mixup)")
     if xmask is not None:
         _expect(xmask.numel() == W and ymask.numel() == H, "xmask / ymask must have image_size entries")
+    if ratio_dev is not None:              # the ratio as a device scalar (graph replays with new draws)
+        _chk(ratio_dev, F32, "ratio_dev")
+        check(_lib.load().jm_patchify_mix_dev(ptr(images), B, H, patch_size, ptr(ids), n_sel, rows_per_image, row_off,
+                                              ptr(out), _ld(out), ptr(perm), 1 if xmask is None else 2, ptr(ratio_dev),
+                                              ptr(xmask), ptr(ymask), stream_ptr()))
+        return out
     check(_lib.load().jm_patchify_mix(ptr(images), B, H, patch_size, ptr(ids), n_sel, rows_per_image, row_off, ptr(out),
                                       _ld(out), ptr(perm), 1 if xmask is None else 2, ratio, ptr(xmask), ptr(ymask),
                                       stream_ptr()))
